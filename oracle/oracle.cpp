@@ -1,0 +1,928 @@
+/*
+ * oracle/oracle.cpp — TEST INFRASTRUCTURE ONLY.
+ *
+ * CPU oracle: dependency-free C++17 restatement of the reference's scan-to-map registration hot path.
+ * The product (libb200reg.so) never links, loads or executes this file; only tests/, __graft_entry__.smoke()
+ * and bench.py's cpu_baseline / --impl reference legs use it, and only as the checker / reported baseline.
+ *
+ * PARITY STATUS: the reference cannot be built here (Eigen, boost, yaml-cpp, libnabo, Open3D absent), so this
+ * restatement is pinned against the reference's own fixtures (car_cloud400/401 + validT3d, icpSingular, icpIdentity,
+ * Conditioning tolerances; see tests/test_oracle_*.py).  Quantities the reference's tests never pin (kNN ids,
+ * voxel membership, centroids, normals) are ORACLE-DEFINED ("parity unpinned" beyond the ICP-level fixtures).
+ *
+ * All citations are relative to /root/reference/.
+ * Build: g++ -O3 -std=c++17 -ffp-contract=off -fopenmp -shared -fPIC oracle.cpp -o liboracle.so
+ *        (-ffp-contract=off: every fp32 operation is individually rounded, as SURVEY 9.1 defines.)
+ */
+#include "oracle.h"
+
+#include <algorithm>
+#include <array>
+#include <chrono>
+#include <cmath>
+#include <cstring>
+#include <limits>
+#include <map>
+#include <numeric>
+#include <tuple>
+#include <vector>
+#ifdef _OPENMP
+#include <omp.h>
+#endif
+
+namespace {
+
+constexpr float kInf = std::numeric_limits<float>::infinity();
+
+// ------------------------------------------------------------------------------------------------------------
+// small dense helpers (row-major, runtime n <= 6)
+// ------------------------------------------------------------------------------------------------------------
+template <typename S>
+struct Mat4 {
+  S m[16];
+  static Mat4 identity() {
+    Mat4 r;
+    for (int i = 0; i < 16; ++i) r.m[i] = (i % 5 == 0) ? S(1) : S(0);
+    return r;
+  }
+  S& operator()(int r, int c) { return m[4 * r + c]; }
+  S operator()(int r, int c) const { return m[4 * r + c]; }
+};
+
+// 4x4 product, depth accumulated sequentially k = 0..3 (Eigen's GEBP order without FMA; SURVEY 9.1 contract)
+template <typename S>
+Mat4<S> mul(const Mat4<S>& a, const Mat4<S>& b) {
+  Mat4<S> r;
+  for (int i = 0; i < 4; ++i)
+    for (int j = 0; j < 4; ++j) {
+      S acc = a(i, 0) * b(0, j);
+      acc = acc + a(i, 1) * b(1, j);
+      acc = acc + a(i, 2) * b(2, j);
+      acc = acc + a(i, 3) * b(3, j);
+      r(i, j) = acc;
+    }
+  return r;
+}
+
+template <typename S>
+S det3(const Mat4<S>& T) {
+  return T(0, 0) * (T(1, 1) * T(2, 2) - T(1, 2) * T(2, 1)) - T(0, 1) * (T(1, 0) * T(2, 2) - T(1, 2) * T(2, 0)) +
+         T(0, 2) * (T(1, 0) * T(2, 1) - T(1, 1) * T(2, 0));
+}
+
+// Eigen::Quaternion(Matrix3) (Eigen/src/Geometry/Quaternion.h, Shepperd's method) -> (w,x,y,z)
+template <typename S>
+void quatFromRot(const Mat4<S>& T, S q[4]) {
+  S t = T(0, 0) + T(1, 1) + T(2, 2);
+  if (t > S(0)) {
+    t = std::sqrt(t + S(1));
+    q[0] = S(0.5) * t;
+    t = S(0.5) / t;
+    q[1] = (T(2, 1) - T(1, 2)) * t;
+    q[2] = (T(0, 2) - T(2, 0)) * t;
+    q[3] = (T(1, 0) - T(0, 1)) * t;
+  } else {
+    int i = 0;
+    if (T(1, 1) > T(0, 0)) i = 1;
+    if (T(2, 2) > T(i, i)) i = 2;
+    int j = (i + 1) % 3, k = (j + 1) % 3;
+    t = std::sqrt(T(i, i) - T(j, j) - T(k, k) + S(1));
+    q[1 + i] = S(0.5) * t;
+    t = S(0.5) / t;
+    q[0] = (T(k, j) - T(j, k)) * t;
+    q[1 + j] = (T(j, i) + T(i, j)) * t;
+    q[1 + k] = (T(k, i) + T(i, k)) * t;
+  }
+}
+
+// Eigen QuaternionBase::angularDistance: d = a * conj(b); 2*atan2(|d.vec|, |d.w|)
+template <typename S>
+S quatAngularDistance(const S a[4], const S b[4]) {
+  const S bw = b[0], bx = -b[1], by = -b[2], bz = -b[3];
+  const S w = a[0] * bw - a[1] * bx - a[2] * by - a[3] * bz;
+  const S x = a[0] * bx + a[1] * bw + a[2] * bz - a[3] * by;
+  const S y = a[0] * by + a[2] * bw + a[3] * bx - a[1] * bz;
+  const S z = a[0] * bz + a[3] * bw + a[1] * by - a[2] * bx;
+  return S(2) * std::atan2(std::sqrt(x * x + y * y + z * z), std::fabs(w));
+}
+
+// ------------------------------------------------------------------------------------------------------------
+// fp32 squared distance, fixed operation order ((dx*dx + dy*dy) + dz*dz), every op rounded
+// ------------------------------------------------------------------------------------------------------------
+inline float dist2f(const float* a, const float* b) {
+  const float dx = a[0] - b[0], dy = a[1] - b[1], dz = a[2] - b[2];
+  return (dx * dx + dy * dy) + dz * dz;
+}
+
+// sorted (d2,id) result list of capacity k, ascending, ties -> smaller id first
+struct KnnList {
+  int k, count = 0;
+  float* d2;
+  int32_t* id;
+  KnnList(int k_, float* d, int32_t* i) : k(k_), d2(d), id(i) {
+    for (int j = 0; j < k; ++j) { d2[j] = kInf; id[j] = -1; }
+  }
+  inline bool full() const { return count == k; }
+  inline float worst() const { return d2[k - 1]; }
+  inline void offer(float d, int32_t i) {
+    if (count == k) {
+      if (d > d2[k - 1] || (d == d2[k - 1] && i > id[k - 1])) return;
+    }
+    int pos = (count < k) ? count : k - 1;
+    while (pos > 0 && (d2[pos - 1] > d || (d2[pos - 1] == d && id[pos - 1] > i))) {
+      d2[pos] = d2[pos - 1];
+      id[pos] = id[pos - 1];
+      --pos;
+    }
+    d2[pos] = d;
+    id[pos] = i;
+    if (count < k) ++count;
+  }
+};
+
+// ------------------------------------------------------------------------------------------------------------
+// k-d tree — restates the *public contract* of libnabo as used at MatchersImpl.cpp:113,129 (libnabo itself is an
+// un-vendored dependency, ">= 1.0.7"): squared L2 over the first 3 rows, radius test d2 < maxDist^2,
+// (-1, inf) padding, ALLOW_SELF_MATCH, touched-point count returned.  Exact search (epsilon treated as 0), ties ->
+// smallest reference index.  Bucket size 8 as libnabo's default.
+// ------------------------------------------------------------------------------------------------------------
+struct KdNode {
+  float lo[3], hi[3];
+  int32_t left, right;   // children (internal) or [begin,end) into idx (leaf, left = -1 - begin)
+  int32_t begin, end;
+};
+
+struct KdTree {
+  const float* feat;
+  int stride;
+  int64_t n;
+  std::vector<int32_t> idx;
+  std::vector<float> pts;  // leaf-ordered copy: x y z per point (cache-friendly scan)
+  std::vector<KdNode> nodes;
+
+  int build(int32_t b, int32_t e) {
+    KdNode nd;
+    for (int d = 0; d < 3; ++d) { nd.lo[d] = kInf; nd.hi[d] = -kInf; }
+    for (int32_t i = b; i < e; ++i) {
+      const float* p = feat + (int64_t)idx[i] * stride;
+      for (int d = 0; d < 3; ++d) { nd.lo[d] = std::min(nd.lo[d], p[d]); nd.hi[d] = std::max(nd.hi[d], p[d]); }
+    }
+    nd.begin = b; nd.end = e; nd.left = nd.right = -1;
+    const int me = (int)nodes.size();
+    nodes.push_back(nd);
+    if (e - b > 8) {
+      int dim = 0;
+      float ext = nd.hi[0] - nd.lo[0];
+      for (int d = 1; d < 3; ++d) if (nd.hi[d] - nd.lo[d] > ext) { ext = nd.hi[d] - nd.lo[d]; dim = d; }
+      if (ext > 0.f) {
+        const int32_t mid = b + (e - b) / 2;
+        std::nth_element(idx.begin() + b, idx.begin() + mid, idx.begin() + e, [&](int32_t x, int32_t y) {
+          const float fx = feat[(int64_t)x * stride + dim], fy = feat[(int64_t)y * stride + dim];
+          return fx < fy || (fx == fy && x < y);
+        });
+        const int l = build(b, mid);
+        const int r = build(mid, e);
+        nodes[me].left = l;
+        nodes[me].right = r;
+      }
+    }
+    return me;
+  }
+
+  static inline float boxLb(const KdNode& nd, const float* q) {
+    float g[3];
+    for (int d = 0; d < 3; ++d) {
+      const float a = nd.lo[d] - q[d], b = q[d] - nd.hi[d];
+      g[d] = std::max(0.f, std::max(a, b));
+    }
+    return (g[0] * g[0] + g[1] * g[1]) + g[2] * g[2];   // same op order as dist2f => monotone lower bound
+  }
+
+  void search(int node, const float* q, float maxd2, int64_t selfSkip, KnnList& res, uint64_t& visits) const {
+    const KdNode& nd = nodes[node];
+    if (nd.left < 0) {
+      for (int32_t i = nd.begin; i < nd.end; ++i) {
+        if (idx[i] == selfSkip) continue;
+        const float d = dist2f(q, &pts[3 * (size_t)i]);
+        ++visits;
+        if (d < maxd2) res.offer(d, idx[i]);
+      }
+      return;
+    }
+    const float ll = boxLb(nodes[nd.left], q), lr = boxLb(nodes[nd.right], q);
+    const int first = (ll <= lr) ? nd.left : nd.right, second = (ll <= lr) ? nd.right : nd.left;
+    const float lf = std::min(ll, lr), ls = std::max(ll, lr);
+    if (lf < maxd2 && !(res.full() && lf > res.worst())) search(first, q, maxd2, selfSkip, res, visits);
+    if (ls < maxd2 && !(res.full() && ls > res.worst())) search(second, q, maxd2, selfSkip, res, visits);
+  }
+};
+
+inline float maxDist2(float maxDist) { return maxDist * maxDist; }   // fp32 product (inf stays inf)
+
+}  // namespace
+
+extern "C" {
+
+void* orc_kdtree_build(const float* feat, int32_t stride, int64_t n) {
+  KdTree* t = new KdTree();
+  t->feat = feat; t->stride = stride; t->n = n;
+  t->idx.resize((size_t)n);
+  std::iota(t->idx.begin(), t->idx.end(), 0);
+  t->nodes.reserve((size_t)(n / 4 + 16));
+  if (n > 0) t->build(0, (int32_t)n);
+  t->pts.resize(3 * (size_t)n);
+  for (int64_t i = 0; i < n; ++i)
+    for (int d = 0; d < 3; ++d) t->pts[3 * i + d] = feat[(int64_t)t->idx[i] * stride + d];
+  return t;
+}
+
+void orc_kdtree_free(void* tree) { delete (KdTree*)tree; }
+
+uint64_t orc_kdtree_knn(const void* tree, const float* q, int32_t qstride, int64_t nq, int32_t k, float max_dist,
+                        int32_t allow_self, int32_t* ids, float* d2, int32_t nthreads) {
+  const KdTree* t = (const KdTree*)tree;
+  const float md2 = maxDist2(max_dist);
+  uint64_t visits = 0;
+#pragma omp parallel for schedule(dynamic, 1024) num_threads(nthreads > 0 ? nthreads : 1) reduction(+ : visits)
+  for (int64_t i = 0; i < nq; ++i) {
+    KnnList res(k, d2 + (int64_t)k * i, ids + (int64_t)k * i);
+    uint64_t v = 0;
+    if (t->n > 0) t->search(0, q + i * qstride, md2, allow_self ? -1 : i, res, v);
+    visits += v;
+  }
+  return visits;
+}
+
+uint64_t orc_knn_brute(const float* ref, int32_t rstride, int64_t m, const float* q, int32_t qstride, int64_t nq, int32_t k,
+                       float max_dist, int32_t* ids, float* d2, int32_t nthreads) {
+  const float md2 = maxDist2(max_dist);
+#pragma omp parallel for schedule(static) num_threads(nthreads > 0 ? nthreads : 1)
+  for (int64_t i = 0; i < nq; ++i) {
+    KnnList res(k, d2 + (int64_t)k * i, ids + (int64_t)k * i);
+    for (int64_t j = 0; j < m; ++j) {
+      const float d = dist2f(q + i * qstride, ref + j * rstride);
+      if (d < md2) res.offer(d, (int32_t)j);
+    }
+  }
+  return (uint64_t)m * (uint64_t)nq;
+}
+
+}  // extern "C"
+
+// ================================================================================================================
+// RigidTransformation::inPlaceCompute / checkParameters  (libpointmatcher/pointmatcher/TransformationsImpl.cpp:61-114)
+// ================================================================================================================
+namespace {
+
+// features <- T * features; normals <- R * normals.  fp32, depth accumulated k = 0..3, no FMA.
+void transformCloud(const Mat4<float>& T, float* feat, int stride, float* normals, int64_t n) {
+  for (int64_t i = 0; i < n; ++i) {
+    float* p = feat + i * stride;
+    const float x = p[0], y = p[1], z = p[2], w = (stride >= 4) ? p[3] : 1.f;
+    for (int r = 0; r < 3; ++r) p[r] = ((T(r, 0) * x + T(r, 1) * y) + T(r, 2) * z) + T(r, 3) * w;
+    if (stride >= 4) p[3] = ((T(3, 0) * x + T(3, 1) * y) + T(3, 2) * z) + T(3, 3) * w;
+    if (normals) {
+      float* nn = normals + 3 * i;
+      const float a = nn[0], b = nn[1], c = nn[2];
+      for (int r = 0; r < 3; ++r) nn[r] = (T(r, 0) * a + T(r, 1) * b) + T(r, 2) * c;
+    }
+  }
+}
+
+bool checkRigid(const Mat4<float>& T) {   // TransformationsImpl.cpp:100-114, epsilon 0.001
+  return !(std::fabs(1.f - det3(T)) > 0.001f);
+}
+
+Mat4<float> loadT(const float T[16]) {
+  Mat4<float> r;
+  std::memcpy(r.m, T, sizeof(r.m));
+  return r;
+}
+
+}  // namespace
+
+extern "C" int32_t orc_transform(const float T[16], float* feat, int32_t stride, float* normals, int64_t n) {
+  const Mat4<float> M = loadT(T);
+  if (!checkRigid(M)) return ORC_E_TRANSFORM;
+  transformCloud(M, feat, stride, normals, n);
+  return ORC_OK;
+}
+
+// ================================================================================================================
+// Outlier filters
+// ================================================================================================================
+namespace {
+
+// Matches::getDistsQuantile (Matches.cpp:61-87): finite values only; rank = size_t(float(n) * quantile) (float
+// multiply, truncation); quantile == 1 -> max.
+int distsQuantile(const float* d2, int64_t count, float quantile, float* out) {
+  std::vector<float> values;
+  values.reserve((size_t)count);
+  for (int64_t i = 0; i < count; ++i)
+    if (d2[i] != kInf) values.push_back(d2[i]);
+  if (values.empty()) return ORC_E_CONVERGENCE;
+  if (quantile < 0.0f || quantile > 1.0f) return ORC_E_CONVERGENCE;
+  if (quantile == 1.0f) {
+    *out = *std::max_element(values.begin(), values.end());
+    return ORC_OK;
+  }
+  const size_t rank = (size_t)((float)values.size() * quantile);
+  std::nth_element(values.begin(), values.begin() + rank, values.end());
+  *out = values[rank];
+  return ORC_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+// TrimmedDistOutlierFilter::compute (OutlierFiltersImpl.cpp:140-147): w = (d2 <= limit)
+int32_t orc_trimmed_dist(const float* d2, int64_t count, float ratio, float* tau_out, float* w_out) {
+  float tau = 0.f;
+  const int st = distsQuantile(d2, count, ratio, &tau);
+  if (st != ORC_OK) return st;
+  if (tau_out) *tau_out = tau;
+  if (w_out)
+    for (int64_t i = 0; i < count; ++i) w_out[i] = (d2[i] <= tau) ? 1.f : 0.f;
+  return ORC_OK;
+}
+
+// SurfaceNormalOutlierFilter::compute (OutlierFiltersImpl.cpp:236-281): eps = cos(maxAngle) in T = float;
+// w = 0 if id invalid or dot < eps, else 1; all ones if either cloud lacks normals.
+void orc_surface_normal_outlier(const float* nrm_read, const float* nrm_ref, const int32_t* ids, int32_t k, int64_t n,
+                                float max_angle, float* w_out) {
+  const float eps = std::cos(max_angle);
+  for (int64_t i = 0; i < n; ++i)
+    for (int j = 0; j < k; ++j) {
+      const int64_t o = (int64_t)k * i + j;
+      if (!nrm_read || !nrm_ref) { w_out[o] = 1.f; continue; }
+      const int32_t id = ids[o];
+      if (id == -1) { w_out[o] = 0.f; continue; }
+      const float* a = nrm_read + 3 * i;
+      const float* b = nrm_ref + 3 * (int64_t)id;
+      const float v = (a[0] * b[0] + a[1] * b[1]) + a[2] * b[2];
+      w_out[o] = (v < eps) ? 0.f : 1.f;
+    }
+}
+
+// OutlierFilters::compute with an empty chain (OutlierFilter.cpp:70-85)
+void orc_no_filter_weights(const float* d2, int64_t count, float* w_out) {
+  for (int64_t i = 0; i < count; ++i) w_out[i] = (d2[i] == kInf) ? 0.f : 1.f;
+}
+
+}  // extern "C"
+
+// ================================================================================================================
+// Small dense linear algebra used by PointToPlane::solvePossiblyUnderdeterminedLinearSystem (PointToPlane.cpp:185-238)
+// — restates the Eigen calls at that site: fullPivHouseholderQr().isInvertible()/rank(), llt().solve(), and the
+// rank-reduced minimum-norm solution.  Eigen is an un-vendored dependency; algorithms per its documentation.
+// ================================================================================================================
+namespace {
+
+template <typename S>
+struct FullPivQR {
+  int n;
+  std::vector<S> R;        // n x n row-major, upper triangular after factorisation
+  std::vector<S> Q;        // n x n row-major, accumulated (A * P = Q * R)
+  std::vector<int> colPerm;  // P: column j of A*P is column colPerm[j] of A
+  int rank;
+  bool invertible;
+
+  // Householder QR with full pivoting (largest remaining |entry| moved to the pivot position by a row and a column
+  // transposition; Eigen/src/QR/FullPivHouseholderQR.h).  rank = #pivots with |pivot| > eps * n * maxpivot.
+  FullPivQR(const std::vector<S>& A, int n_) : n(n_), R(A), Q((size_t)n_ * n_, S(0)), colPerm(n_), rank(0) {
+    for (int i = 0; i < n; ++i) { Q[(size_t)i * n + i] = S(1); colPerm[i] = i; }
+    std::vector<S> pivots(n, S(0));
+    S maxpivot = S(0);
+    for (int k = 0; k < n; ++k) {
+      int pr = k, pc = k;
+      S best = S(-1);
+      for (int i = k; i < n; ++i)
+        for (int j = k; j < n; ++j)
+          if (std::fabs(R[(size_t)i * n + j]) > best) { best = std::fabs(R[(size_t)i * n + j]); pr = i; pc = j; }
+      if (best <= S(0)) break;
+      if (pr != k) {   // row swap: R rows, and the matching columns of Q (Q * Rowswap * Rowswap * R)
+        for (int j = 0; j < n; ++j) std::swap(R[(size_t)pr * n + j], R[(size_t)k * n + j]);
+        for (int i = 0; i < n; ++i) std::swap(Q[(size_t)i * n + pr], Q[(size_t)i * n + k]);
+      }
+      if (pc != k) {
+        for (int i = 0; i < n; ++i) std::swap(R[(size_t)i * n + pc], R[(size_t)i * n + k]);
+        std::swap(colPerm[pc], colPerm[k]);
+      }
+      // Householder vector for column k, rows k..n-1
+      S norm2 = S(0);
+      for (int i = k; i < n; ++i) norm2 += R[(size_t)i * n + k] * R[(size_t)i * n + k];
+      const S x0 = R[(size_t)k * n + k];
+      const S alpha = (x0 >= S(0)) ? -std::sqrt(norm2) : std::sqrt(norm2);
+      std::vector<S> v(n, S(0));
+      v[k] = x0 - alpha;
+      for (int i = k + 1; i < n; ++i) v[i] = R[(size_t)i * n + k];
+      S vnorm2 = S(0);
+      for (int i = k; i < n; ++i) vnorm2 += v[i] * v[i];
+      if (vnorm2 > S(0)) {
+        for (int j = k; j < n; ++j) {   // R <- (I - 2 v v^T / v^T v) R
+          S dot = S(0);
+          for (int i = k; i < n; ++i) dot += v[i] * R[(size_t)i * n + j];
+          const S f = S(2) * dot / vnorm2;
+          for (int i = k; i < n; ++i) R[(size_t)i * n + j] -= f * v[i];
+        }
+        for (int i = 0; i < n; ++i) {   // Q <- Q (I - 2 v v^T / v^T v)
+          S dot = S(0);
+          for (int j = k; j < n; ++j) dot += Q[(size_t)i * n + j] * v[j];
+          const S f = S(2) * dot / vnorm2;
+          for (int j = k; j < n; ++j) Q[(size_t)i * n + j] -= f * v[j];
+        }
+      }
+      for (int i = k + 1; i < n; ++i) R[(size_t)i * n + k] = S(0);
+      pivots[k] = std::fabs(R[(size_t)k * n + k]);
+      maxpivot = std::max(maxpivot, pivots[k]);
+    }
+    const S thr = std::numeric_limits<S>::epsilon() * S(n) * maxpivot;
+    for (int k = 0; k < n; ++k)
+      if (pivots[k] > thr) ++rank;
+    invertible = (rank == n);
+  }
+};
+
+// x = A.llt().solve(b) for SPD A (n x n row-major)
+template <typename S>
+void lltSolve(const std::vector<S>& A, const std::vector<S>& b, int n, std::vector<S>& x) {
+  std::vector<S> L((size_t)n * n, S(0));
+  for (int j = 0; j < n; ++j) {
+    S d = A[(size_t)j * n + j];
+    for (int k = 0; k < j; ++k) d -= L[(size_t)j * n + k] * L[(size_t)j * n + k];
+    d = std::sqrt(d);
+    L[(size_t)j * n + j] = d;
+    for (int i = j + 1; i < n; ++i) {
+      S s = A[(size_t)i * n + j];
+      for (int k = 0; k < j; ++k) s -= L[(size_t)i * n + k] * L[(size_t)j * n + k];
+      L[(size_t)i * n + j] = s / d;
+    }
+  }
+  std::vector<S> y(n);
+  for (int i = 0; i < n; ++i) {
+    S s = b[i];
+    for (int k = 0; k < i; ++k) s -= L[(size_t)i * n + k] * y[k];
+    y[i] = s / L[(size_t)i * n + i];
+  }
+  x.assign(n, S(0));
+  for (int i = n - 1; i >= 0; --i) {
+    S s = y[i];
+    for (int k = i + 1; k < n; ++k) s -= L[(size_t)k * n + i] * x[k];
+    x[i] = s / L[(size_t)i * n + i];
+  }
+}
+
+// Minimum-norm least-squares solve via one-sided Jacobi eigen-decomposition of the symmetric A in double — stands in
+// for the `jacobiSvd(ComputeThinU|ComputeThinV).solve()` fallback at PointToPlane.cpp:221 (double precision there too).
+void symPinvSolve(const std::vector<double>& A, const std::vector<double>& b, int n, std::vector<double>& x) {
+  std::vector<double> a(A), V((size_t)n * n, 0.0);
+  for (int i = 0; i < n; ++i) V[(size_t)i * n + i] = 1.0;
+  for (int sweep = 0; sweep < 60; ++sweep) {
+    double off = 0;
+    for (int p = 0; p < n; ++p)
+      for (int q = p + 1; q < n; ++q) off += a[(size_t)p * n + q] * a[(size_t)p * n + q];
+    if (off < 1e-300) break;
+    for (int p = 0; p < n; ++p)
+      for (int q = p + 1; q < n; ++q) {
+        const double apq = a[(size_t)p * n + q];
+        if (apq == 0.0) continue;
+        const double theta = (a[(size_t)q * n + q] - a[(size_t)p * n + p]) / (2.0 * apq);
+        const double t = ((theta >= 0) ? 1.0 : -1.0) / (std::fabs(theta) + std::sqrt(theta * theta + 1.0));
+        const double c = 1.0 / std::sqrt(t * t + 1.0), s = t * c;
+        for (int k = 0; k < n; ++k) {
+          const double akp = a[(size_t)k * n + p], akq = a[(size_t)k * n + q];
+          a[(size_t)k * n + p] = c * akp - s * akq;
+          a[(size_t)k * n + q] = s * akp + c * akq;
+        }
+        for (int k = 0; k < n; ++k) {
+          const double apk = a[(size_t)p * n + k], aqk = a[(size_t)q * n + k];
+          a[(size_t)p * n + k] = c * apk - s * aqk;
+          a[(size_t)q * n + k] = s * apk + c * aqk;
+        }
+        for (int k = 0; k < n; ++k) {
+          const double vkp = V[(size_t)k * n + p], vkq = V[(size_t)k * n + q];
+          V[(size_t)k * n + p] = c * vkp - s * vkq;
+          V[(size_t)k * n + q] = s * vkp + c * vkq;
+        }
+      }
+  }
+  double lmax = 0;
+  for (int i = 0; i < n; ++i) lmax = std::max(lmax, std::fabs(a[(size_t)i * n + i]));
+  const double thr = std::numeric_limits<double>::epsilon() * n * lmax;
+  x.assign(n, 0.0);
+  for (int i = 0; i < n; ++i) {
+    const double l = a[(size_t)i * n + i];
+    if (std::fabs(l) <= thr) continue;
+    double proj = 0;
+    for (int k = 0; k < n; ++k) proj += V[(size_t)k * n + i] * b[k];
+    proj /= l;
+    for (int k = 0; k < n; ++k) x[k] += V[(size_t)k * n + i] * proj;
+  }
+}
+
+// solvePossiblyUnderdeterminedLinearSystem (PointToPlane.cpp:185-238)
+template <typename S>
+void solvePossiblyUnderdetermined(const std::vector<S>& A, const std::vector<S>& b, int n, std::vector<S>& x) {
+  FullPivQR<S> qr(A, n);
+  if (!qr.invertible) {
+    const int rank = qr.rank;
+    x.assign(n, S(0));
+    if (rank == 0) return;
+    // R1 = top `rank` rows of R (= (Q1^T A P)), upper-trapezoidal; rhs = Q1^T b
+    std::vector<S> rhs(rank, S(0));
+    for (int i = 0; i < rank; ++i)
+      for (int k = 0; k < n; ++k) rhs[i] += qr.Q[(size_t)k * n + i] * b[k];
+    // x_p = R1^T (R1 R1^T)^-1 rhs   (minimum-norm solution, :205-207)
+    std::vector<S> G((size_t)rank * rank, S(0));
+    for (int i = 0; i < rank; ++i)
+      for (int j = 0; j < rank; ++j) {
+        S s = S(0);
+        for (int k = std::max(i, j); k < n; ++k) s += qr.R[(size_t)i * n + k] * qr.R[(size_t)j * n + k];
+        G[(size_t)i * rank + j] = s;
+      }
+    std::vector<S> y;
+    lltSolve(G, rhs, rank, y);
+    std::vector<S> xp(n, S(0));
+    for (int k = 0; k < n; ++k)
+      for (int i = 0; i <= std::min(k, rank - 1); ++i) xp[k] += qr.R[(size_t)i * n + k] * y[i];
+    for (int j = 0; j < n; ++j) x[qr.colPerm[j]] = xp[j];   // x = P * x_p (:214)
+    // accuracy check (:216-232): !b.isApprox(A x, 1e-5) -> double-precision SVD re-solve
+    S diff2 = S(0), nb2 = S(0), nax2 = S(0);
+    for (int i = 0; i < n; ++i) {
+      S ax = S(0);
+      for (int k = 0; k < n; ++k) ax += A[(size_t)i * n + k] * x[k];
+      diff2 += (b[i] - ax) * (b[i] - ax);
+      nb2 += b[i] * b[i];
+      nax2 += ax * ax;
+    }
+    if (!(diff2 <= S(1e-5) * S(1e-5) * std::min(nb2, nax2))) {
+      std::vector<double> Ad(A.begin(), A.end()), bd(b.begin(), b.end()), xd;
+      symPinvSolve(Ad, bd, n, xd);
+      for (int i = 0; i < n; ++i) x[i] = (S)xd[i];
+    }
+  } else {
+    lltSolve(A, b, n, x);   // :236
+  }
+}
+
+}  // namespace
+
+// ================================================================================================================
+// ErrorElements (ErrorMinimizer.cpp:59-193) + PointToPlaneErrorMinimizer::compute (PointToPlane.cpp:240-368)
+// S = float  : ORC_REF32  (means, centring, G G^T, solve, Rodrigues all in fp32 like the reference's T = float)
+// S = double : ORC_MIXED  (same fp32 inputs, fp64 sums + solve — the contract of the CUDA path)
+// ================================================================================================================
+namespace {
+
+struct Pair { int64_t read; int32_t ref; float w; };
+
+template <typename S>
+struct P2PlaneResult {
+  int dim = 6;
+  std::vector<S> A, b, x;
+  Mat4<S> T;
+  int kept = 0;
+  float pointUsedRatio = 0, weightedPointUsedRatio = 0;
+};
+
+template <typename S>
+int pointToPlane(const float* readFeat, int rstride, int64_t n, const float* refFeat, int fstride, const float* refNormals,
+                 const int32_t* ids, const float* d2, const float* w, int k, bool force2D, bool force4DOF,
+                 P2PlaneResult<S>& out) {
+  if (!refNormals) return ORC_E_FIELD;   // getDescriptorViewByName("normals") throws InvalidField (PointToPlane.cpp:115)
+  // --- ErrorElements: keep (k,i) pairs with finite dist and non-zero weight, reading-major order (:98-129)
+  std::vector<Pair> pairs;
+  int64_t nonZero = 0;
+  for (int64_t i = 0; i < n * k; ++i) nonZero += (w[i] != 0.f);
+  if (nonZero == 0) return ORC_E_CONVERGENCE;   // "no point to minimize" (:76-77)
+  pairs.reserve((size_t)nonZero);
+  float wsum = 0.f;
+  for (int64_t i = 0; i < n; ++i)
+    for (int j = 0; j < k; ++j) {
+      const int64_t o = (int64_t)k * i + j;
+      if (d2[o] == kInf) continue;
+      if (w[o] != 0.f) {
+        pairs.push_back({i, ids[o], w[o]});
+        wsum += w[o];
+      }
+    }
+  const int64_t K = (int64_t)pairs.size();
+  out.kept = (int)K;
+  out.pointUsedRatio = float(K) / float((int64_t)k * n);          // :139
+  out.weightedPointUsedRatio = wsum / float((int64_t)k * n);      // :140
+  if (K == 0) return ORC_E_CONVERGENCE;
+
+  // --- means of the matched clouds (PointToPlane.cpp:263-264); force2D overwrites row 2 with ones first (:247-254)
+  const int sdim = force2D ? 2 : 3;   // spatial dims that take part
+  S meanR[3] = {0, 0, 0}, meanQ[3] = {0, 0, 0};
+  for (const Pair& p : pairs)
+    for (int d = 0; d < sdim; ++d) {
+      meanR[d] += (S)readFeat[p.read * rstride + d];
+      meanQ[d] += (S)refFeat[(int64_t)p.ref * fstride + d];
+    }
+  for (int d = 0; d < sdim; ++d) { meanR[d] /= (S)K; meanQ[d] /= (S)K; }
+
+  // --- G = [cross; n], h = (p' - q') . n ; A = G G^T ; b = -G h^T   (:107-156; weights NOT applied, :153-155)
+  const int dim = force2D ? 3 : (force4DOF ? 4 : 6);
+  out.dim = dim;
+  std::vector<S> A((size_t)dim * dim, S(0)), b(dim, S(0));
+  for (const Pair& p : pairs) {
+    S r[3] = {0, 0, 0}, q[3] = {0, 0, 0}, nn[3] = {0, 0, 0};
+    for (int d = 0; d < sdim; ++d) {
+      r[d] = (S)readFeat[p.read * rstride + d] - meanR[d];            // :267
+      q[d] = (S)refFeat[(int64_t)p.ref * fstride + d] - meanQ[d];     // :268
+      nn[d] = (S)refNormals[3 * (int64_t)p.ref + d];
+    }
+    S g[6];
+    if (force2D) {          // 2D: cross = x*ny - y*nx (ErrorMinimizer.cpp:282-315, dim 3 branch)
+      g[0] = r[0] * nn[1] - r[1] * nn[0];
+      g[1] = nn[0]; g[2] = nn[1];
+    } else if (force4DOF) { // diag((Gamma P)^T N) = -py*nx + px*ny   (PointToPlane.cpp:128-134)
+      g[0] = -r[1] * nn[0] + r[0] * nn[1];
+      g[1] = nn[0]; g[2] = nn[1]; g[3] = nn[2];
+    } else {                // cross = p x n   (ErrorMinimizer.cpp:304-306)
+      g[0] = r[1] * nn[2] - r[2] * nn[1];
+      g[1] = r[2] * nn[0] - r[0] * nn[2];
+      g[2] = r[0] * nn[1] - r[1] * nn[0];
+      g[3] = nn[0]; g[4] = nn[1]; g[5] = nn[2];
+    }
+    S h = S(0);
+    for (int d = 0; d < sdim; ++d) h += (r[d] - q[d]) * nn[d];       // :144-148
+    for (int a = 0; a < dim; ++a) {
+      for (int c = 0; c < dim; ++c) A[(size_t)a * dim + c] += g[a] * g[c];
+      b[a] -= g[a] * h;
+    }
+  }
+  std::vector<S> x;
+  solvePossiblyUnderdetermined(A, b, dim, x);
+  out.A = A; out.b = b; out.x = x;
+
+  // --- parameters -> matrix (:282-366)
+  Mat4<S> R = Mat4<S>::identity();
+  S t[3] = {0, 0, 0};
+  if (!force2D) {
+    S axis[3] = {0, 0, 1}, angle;
+    if (!force4DOF) {
+      angle = std::sqrt(x[0] * x[0] + x[1] * x[1] + x[2] * x[2]);     // x.head(3).norm()
+      // stableNormalized(): scale by the max |coeff| first; zero vector stays zero
+      const S wmax = std::max(std::fabs(x[0]), std::max(std::fabs(x[1]), std::fabs(x[2])));
+      S v[3] = {x[0], x[1], x[2]};
+      if (wmax > S(0)) {
+        const S z = (v[0] / wmax) * (v[0] / wmax) + (v[1] / wmax) * (v[1] / wmax) + (v[2] / wmax) * (v[2] / wmax);
+        if (z > S(0)) for (int d = 0; d < 3; ++d) v[d] = v[d] / (std::sqrt(z) * wmax);
+      }
+      for (int d = 0; d < 3; ++d) axis[d] = v[d];
+      t[0] = x[3]; t[1] = x[4]; t[2] = x[5];
+    } else {
+      angle = x[0];
+      t[0] = x[1]; t[1] = x[2]; t[2] = x[3];
+    }
+    // Eigen::AngleAxis::toRotationMatrix
+    const S s = std::sin(angle), c = std::cos(angle);
+    const S cx = (S(1) - c) * axis[0], cy = (S(1) - c) * axis[1], cz = (S(1) - c) * axis[2];
+    const S sx = s * axis[0], sy = s * axis[1], sz = s * axis[2];
+    S tmp;
+    tmp = cx * axis[1]; R(0, 1) = tmp - sz; R(1, 0) = tmp + sz;
+    tmp = cx * axis[2]; R(0, 2) = tmp + sy; R(2, 0) = tmp - sy;
+    tmp = cy * axis[2]; R(1, 2) = tmp - sx; R(2, 1) = tmp + sx;
+    R(0, 0) = cx * axis[0] + c; R(1, 1) = cy * axis[1] + c; R(2, 2) = cz * axis[2] + c;
+  } else {
+    const S angle = x[0];
+    R(0, 0) = std::cos(angle); R(0, 1) = -std::sin(angle); R(1, 0) = std::sin(angle); R(1, 1) = std::cos(angle);
+    t[0] = x[1]; t[1] = x[2];
+  }
+  // T = Trans(meanQ) * [R t] * Trans(-meanR)   (:316-324 / :341-349)
+  Mat4<S> T = R;
+  for (int r = 0; r < 3; ++r) {
+    S acc = S(0);
+    for (int c = 0; c < 3; ++c) acc += R(r, c) * (-meanR[c]);
+    T(r, 3) = acc + (t[r] + meanQ[r]);
+  }
+  bool hasNaN = false;
+  for (int i = 0; i < 16; ++i) hasNaN |= (T.m[i] != T.m[i]);
+  if (hasNaN)   // :326-332 — rotation block replaced by identity
+    for (int r = 0; r < 3; ++r)
+      for (int c = 0; c < 3; ++c) T(r, c) = (r == c) ? S(1) : S(0);
+  out.T = T;
+  return ORC_OK;
+}
+
+template <typename S>
+Mat4<float> toFloat(const Mat4<S>& a) {
+  Mat4<float> r;
+  for (int i = 0; i < 16; ++i) r.m[i] = (float)a.m[i];
+  return r;
+}
+
+}  // namespace
+
+extern "C" int32_t orc_point_to_plane(const float* read_feat, int32_t rstride, int64_t n, const float* ref_feat, int32_t fstride,
+                                      const float* ref_normals, const int32_t* ids, const float* d2, const float* w, int32_t k,
+                                      int32_t force2D, int32_t force4DOF, int32_t precision, float T_out[16], double* A_out,
+                                      double* b_out, double* x_out, int32_t* kept_out, float* point_used_ratio,
+                                      float* weighted_point_used_ratio) {
+  auto emit = [&](auto& res) {
+    const Mat4<float> Tf = toFloat(res.T);
+    if (T_out) std::memcpy(T_out, Tf.m, sizeof(Tf.m));
+    const int dim = res.dim;
+    if (A_out) for (int i = 0; i < dim * dim; ++i) A_out[i] = (double)res.A[i];
+    if (b_out) for (int i = 0; i < dim; ++i) b_out[i] = (double)res.b[i];
+    if (x_out) for (int i = 0; i < dim; ++i) x_out[i] = (double)res.x[i];
+  };
+  int st;
+  int kept = 0;
+  float pur = 0, wpur = 0;
+  if (precision == ORC_REF32) {
+    P2PlaneResult<float> res;
+    st = pointToPlane<float>(read_feat, rstride, n, ref_feat, fstride, ref_normals, ids, d2, w, k, force2D, force4DOF, res);
+    kept = res.kept; pur = res.pointUsedRatio; wpur = res.weightedPointUsedRatio;
+    if (st == ORC_OK) emit(res);
+  } else {
+    P2PlaneResult<double> res;
+    st = pointToPlane<double>(read_feat, rstride, n, ref_feat, fstride, ref_normals, ids, d2, w, k, force2D, force4DOF, res);
+    kept = res.kept; pur = res.pointUsedRatio; wpur = res.weightedPointUsedRatio;
+    if (st == ORC_OK) emit(res);
+  }
+  if (kept_out) *kept_out = kept;
+  if (point_used_ratio) *point_used_ratio = pur;
+  if (weighted_point_used_ratio) *weighted_point_used_ratio = wpur;
+  return st;
+}
+
+// ================================================================================================================
+// Transformation checkers (TransformationCheckersImpl.cpp:58-225) and the ICP driver (ICP.cpp:258-468)
+// ================================================================================================================
+namespace {
+
+struct Checkers {
+  const orc_icp_config& cfg;
+  int counter = 0;
+  std::vector<std::array<float, 4>> rotations;
+  std::vector<std::array<float, 3>> translations;
+  float initQ[4];
+  float initT[3];
+  explicit Checkers(const orc_icp_config& c) : cfg(c) {}
+
+  void init(const Mat4<float>& T) {
+    counter = 0;                                         // Counter::init :58-61
+    rotations.clear(); translations.clear();             // Differential::init :103-124
+    std::array<float, 4> q;
+    quatFromRot(T, q.data());
+    rotations.push_back(q);
+    translations.push_back({T(0, 3), T(1, 3), T(2, 3)});
+    quatFromRot(T, initQ);                               // Bound::init :198-211
+    initT[0] = T(0, 3); initT[1] = T(1, 3); initT[2] = T(2, 3);
+  }
+
+  // returns ORC_OK or an error; sets iterate / maxIterReached.  Checker order: Differential, Counter, Bound is
+  // irrelevant for the outcome except which one fires first within the same iteration.
+  int check(const Mat4<float>& T, bool& iterate, bool& maxIterReached) {
+    int status = ORC_OK;
+    if (cfg.smooth_length >= 0) {                        // Differential::check :127-158
+      std::array<float, 4> q;
+      quatFromRot(T, q.data());
+      rotations.push_back(q);
+      translations.push_back({T(0, 3), T(1, 3), T(2, 3)});
+      float cv0 = 0.f, cv1 = 0.f;
+      const size_t sl = (size_t)cfg.smooth_length;
+      if (rotations.size() > sl) {
+        for (size_t i = rotations.size() - 1; i >= rotations.size() - sl && sl > 0; --i) {
+          cv0 += std::fabs(quatAngularDistance(rotations[i].data(), rotations[i - 1].data()));
+          const float dx = translations[i][0] - translations[i - 1][0], dy = translations[i][1] - translations[i - 1][1],
+                      dz = translations[i][2] - translations[i - 1][2];
+          cv1 += std::fabs(std::sqrt(dx * dx + dy * dy + dz * dz));
+        }
+        cv0 /= (float)sl; cv1 /= (float)sl;
+        if (cv0 < cfg.min_diff_rot && cv1 < cfg.min_diff_trans) iterate = false;
+      }
+      if (cv0 != cv0 || cv1 != cv1) status = ORC_E_CONVERGENCE;
+    }
+    if (cfg.bound_rot >= 0.f && status == ORC_OK) {      // Bound::check :198-225
+      float q[4];
+      quatFromRot(T, q);
+      const float rot = quatAngularDistance(q, initQ);
+      const float dx = T(0, 3) - initT[0], dy = T(1, 3) - initT[1], dz = T(2, 3) - initT[2];
+      const float tr = std::sqrt(dx * dx + dy * dy + dz * dz);
+      if (rot > cfg.bound_rot || tr > cfg.bound_trans) status = ORC_E_CONVERGENCE;
+    }
+    if (cfg.max_iter > 0 && status == ORC_OK) {          // Counter::check :64-76 (throws, caught at ICP.cpp:441-445)
+      ++counter;
+      if (counter >= cfg.max_iter) { iterate = false; maxIterReached = true; }
+    }
+    return status;
+  }
+};
+
+double nowSec() {
+  return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count();
+}
+
+}  // namespace
+
+extern "C" int32_t orc_icp(const orc_icp_config* cfg, const float* ref_feat, int32_t ref_stride, const float* ref_normals, int64_t m,
+                           const float* read_feat, int32_t read_stride, const float* read_normals, int64_t n,
+                           const float T_init[16], float T_out[16], orc_icp_stats* stats) {
+  orc_icp_stats st;
+  std::memset(&st, 0, sizeof(st));
+  auto finish = [&](int code) { st.status = code; if (stats) *stats = st; return code; };
+  if (m == 0) return finish(ORC_E_EMPTY);
+  const double t0 = nowSec();
+
+  // ---- initReference (ICP.cpp:293-328): copy, (no reference filters here), mean, centre, matcher->init
+  std::vector<float> ref(4 * (size_t)m);
+  double sum[3] = {0, 0, 0};
+  for (int64_t i = 0; i < m; ++i) {
+    for (int d = 0; d < 3; ++d) { ref[4 * i + d] = ref_feat[i * ref_stride + d]; sum[d] += ref[4 * i + d]; }
+    ref[4 * i + 3] = 1.f;
+  }
+  // meanReference = features.rowwise().mean() (:313).  Eigen's fp32 reduction order is unspecified; the contract is the
+  // fp64 sum rounded once to fp32.
+  float mean[3];
+  for (int d = 0; d < 3; ++d) { mean[d] = (float)(sum[d] / (double)m); st.mean_ref[d] = mean[d]; }
+  for (int64_t i = 0; i < m; ++i)
+    for (int d = 0; d < 3; ++d) ref[4 * i + d] = ref[4 * i + d] - mean[d];   // :320
+  Mat4<float> T_refIn_refMean = Mat4<float>::identity();
+  for (int d = 0; d < 3; ++d) T_refIn_refMean(d, 3) = mean[d];
+  void* tree = nullptr;
+  if (cfg->matcher_kind == 0) tree = orc_kdtree_build(ref.data(), 4, m);
+  st.t_reference_s = nowSec() - t0;
+  const double t1 = nowSec();
+
+  // ---- computeWithTransformedReference (ICP.cpp:332-468)
+  if (n == 0) { if (tree) orc_kdtree_free(tree); return finish(ORC_E_EMPTY); }
+  std::vector<float> reading(4 * (size_t)n), readingN;
+  for (int64_t i = 0; i < n; ++i) {
+    for (int d = 0; d < 3; ++d) reading[4 * i + d] = read_feat[i * read_stride + d];
+    reading[4 * i + 3] = 1.f;
+  }
+  if (read_normals) readingN.assign(read_normals, read_normals + 3 * (size_t)n);
+  // meanReading forced to zero in this fork (:363-364) => T_readIn_readMean = I
+  Mat4<float> T_refMean_refIn = Mat4<float>::identity();   // inverse of a pure translation
+  for (int d = 0; d < 3; ++d) T_refMean_refIn(d, 3) = -mean[d];
+  const Mat4<float> Tinit = loadT(T_init);
+  const Mat4<float> T_refMean_readMean = mul(T_refMean_refIn, Tinit);   // :373
+  if (!checkRigid(T_refMean_readMean)) { if (tree) orc_kdtree_free(tree); return finish(ORC_E_TRANSFORM); }
+  transformCloud(T_refMean_readMean, reading.data(), 4, read_normals ? readingN.data() : nullptr, n);   // :375
+
+  Mat4<float> T_iter = Mat4<float>::identity();
+  bool iterate = true, maxIterReached = false;
+  Checkers checkers(*cfg);
+  checkers.init(T_iter);
+
+  const int k = (cfg->matcher_kind == 1) ? 1 : cfg->knn;
+  std::vector<float> step(4 * (size_t)n), stepN, d2((size_t)k * n), w((size_t)k * n), w2;
+  std::vector<int32_t> ids((size_t)k * n);
+  int status = ORC_OK;
+  int iterations = 0;
+  while (iterate) {
+    step = reading;                                             // :401
+    if (read_normals) stepN = readingN;
+    if (!checkRigid(T_iter)) { status = ORC_E_TRANSFORM; break; }
+    transformCloud(T_iter, step.data(), 4, read_normals ? stepN.data() : nullptr, n);   // :409
+    if (cfg->matcher_kind == 1) {                               // MirrorMatcher (MatchersImpl.cpp:65-84)
+      for (int64_t i = 0; i < n; ++i) { ids[i] = (int32_t)i; d2[i] = 0.f; }
+    } else {                                                    // :413
+      st.points_touched += orc_kdtree_knn(tree, step.data(), 4, n, k, cfg->max_dist, 1, ids.data(), d2.data(), cfg->nthreads);
+    }
+    // outlier filters (:417, OutlierFilter.cpp:64-103)
+    bool any = false;
+    if (cfg->trim_ratio > 0.f) {
+      status = orc_trimmed_dist(d2.data(), (int64_t)k * n, cfg->trim_ratio, &st.last_tau, w.data());
+      if (status != ORC_OK) break;
+      any = true;
+    }
+    if (cfg->max_angle >= 0.f) {
+      if (!any) {
+        orc_surface_normal_outlier(read_normals ? stepN.data() : nullptr, ref_normals, ids.data(), k, n, cfg->max_angle, w.data());
+      } else {
+        w2.resize(w.size());
+        orc_surface_normal_outlier(read_normals ? stepN.data() : nullptr, ref_normals, ids.data(), k, n, cfg->max_angle, w2.data());
+        for (size_t i = 0; i < w.size(); ++i) w[i] = w[i] * w2[i];
+      }
+      any = true;
+    }
+    if (!any) orc_no_filter_weights(d2.data(), (int64_t)k * n, w.data());
+    // error minimisation (:433)
+    Mat4<float> Tstep;
+    int kept = 0;
+    status = orc_point_to_plane(step.data(), 4, n, ref.data(), 4, ref_normals, ids.data(), d2.data(), w.data(), k, cfg->force2D,
+                                cfg->force4DOF, cfg->precision, Tstep.m, nullptr, nullptr, nullptr, &kept, &st.point_used_ratio,
+                                &st.weighted_point_used_ratio);
+    st.kept_last = kept;
+    if (status != ORC_OK) break;
+    T_iter = mul(Tstep, T_iter);
+    status = checkers.check(T_iter, iterate, maxIterReached);   // :437-445
+    ++iterations;
+    if (status != ORC_OK) break;
+  }
+  if (tree) orc_kdtree_free(tree);
+  st.iterations = iterations;
+  st.max_iterations_reached = maxIterReached ? 1 : 0;
+  st.t_converge_s = nowSec() - t1;
+  if (status != ORC_OK) return finish(status);
+  // :459-465  T_refIn_refMean * (T_iter * T_refMean_readMean) * T_readIn_readMean^-1 (= I)
+  const Mat4<float> out = mul(T_refIn_refMean, mul(T_iter, T_refMean_readMean));
+  std::memcpy(T_out, out.m, sizeof(out.m));
+  return finish(ORC_OK);
+}

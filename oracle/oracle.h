@@ -1,0 +1,120 @@
+/*
+ * oracle/oracle.h — TEST INFRASTRUCTURE ONLY (never linked into, imported by or executed from the product).
+ *
+ * C API of the CPU oracle: a dependency-free restatement of the reference's scan-to-map registration hot path
+ * (libpointmatcher ICP chain + open3d_slam voxel-map crop/insert).  The reference itself cannot be compiled in
+ * this environment (Eigen, boost, yaml-cpp, libnabo, Open3D are absent), so each function restates the algorithm of
+ * the reference file:line cited beside its definition in oracle.cpp.
+ *
+ * Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may load liboracle.so.
+ *
+ * Layout conventions (identical to the reference's Eigen column-major matrices):
+ *   features : `stride` floats per point, xyz first (stride 4 = x y z pad, pad == 1)
+ *   normals  : 3 floats per point
+ *   matches  : ids[k*i + j], d2[k*i + j] = j-th neighbour of reading point i (k contiguous values per point),
+ *              invalid = (-1, +inf); distances are SQUARED (PointMatcher.h:444-451)
+ *   4x4 transforms are ROW-MAJOR float[16] at this C boundary.
+ */
+#ifndef B200REG_ORACLE_H
+#define B200REG_ORACLE_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* precision of the error-minimiser arithmetic */
+enum { ORC_REF32 = 0 /* fp32 everywhere the reference is fp32 */, ORC_MIXED = 1 /* fp32 data path, fp64 sums+solve (the GPU contract) */ };
+
+typedef struct orc_icp_config {
+  int32_t matcher_kind;   /* 0 = KDTreeMatcher, 1 = MirrorMatcher (fixture for Conditioning tests) */
+  int32_t knn;            /* MatchersImpl.h:97 */
+  float   max_dist;       /* MatchersImpl.h:100 (inf allowed) */
+  float   epsilon;        /* parsed, treated as 0 */
+  float   trim_ratio;     /* TrimmedDistOutlierFilter ratio; <= 0 : filter absent */
+  float   max_angle;      /* SurfaceNormalOutlierFilter maxAngle; < 0 : filter absent */
+  int32_t force2D;        /* PointToPlane.h:74 */
+  int32_t force4DOF;      /* PointToPlane.h:75 */
+  int32_t max_iter;       /* CounterTransformationChecker; <= 0 : absent */
+  float   min_diff_rot;   /* DifferentialTransformationChecker */
+  float   min_diff_trans;
+  int32_t smooth_length;  /* < 0 : checker absent */
+  float   bound_rot;      /* BoundTransformationChecker; < 0 : absent */
+  float   bound_trans;
+  int32_t precision;      /* ORC_REF32 | ORC_MIXED */
+  int32_t nthreads;       /* OpenMP threads for kNN (1 = the reference's execution model) */
+} orc_icp_config;
+
+typedef struct orc_icp_stats {
+  int32_t iterations;               /* IterationsCount (ICP.cpp:452) */
+  int32_t max_iterations_reached;   /* ICP.cpp:444 */
+  int32_t status;                   /* 0 ok, <0 error (see ORC_E_*) */
+  int32_t kept_last;                /* pairs kept in the last iteration */
+  uint64_t points_touched;          /* PointCountTouched (ICP.cpp:453) */
+  float   point_used_ratio;         /* ErrorMinimizer.cpp:139 */
+  float   weighted_point_used_ratio;/* ErrorMinimizer.cpp:140 = OverlapRatio stat */
+  float   last_tau;                 /* last trimmed-distance limit */
+  float   mean_ref[3];              /* T_refIn_refMean translation */
+  double  t_reference_s;            /* ReferencePreprocessingDuration */
+  double  t_converge_s;             /* ConvergenceDuration */
+} orc_icp_stats;
+
+enum { ORC_OK = 0, ORC_E_CONVERGENCE = -1, ORC_E_TRANSFORM = -2, ORC_E_PARAM = -3, ORC_E_EMPTY = -4, ORC_E_FIELD = -5 };
+
+/* ---- matcher (MatchersImpl.cpp:109-132 + libnabo public contract) ---- */
+void*    orc_kdtree_build(const float* feat, int32_t stride, int64_t n);
+void     orc_kdtree_free(void* tree);
+uint64_t orc_kdtree_knn(const void* tree, const float* q, int32_t qstride, int64_t nq, int32_t k, float max_dist,
+                        int32_t allow_self, int32_t* ids, float* d2, int32_t nthreads);
+uint64_t orc_knn_brute(const float* ref, int32_t rstride, int64_t m, const float* q, int32_t qstride, int64_t nq, int32_t k,
+                       float max_dist, int32_t* ids, float* d2, int32_t nthreads);
+
+/* ---- RigidTransformation (TransformationsImpl.cpp:61-114) ---- */
+int32_t orc_transform(const float T[16], float* feat, int32_t stride, float* normals, int64_t n);
+
+/* ---- outlier filters ---- */
+int32_t orc_trimmed_dist(const float* d2, int64_t count, float ratio, float* tau_out, float* w_out);   /* OutlierFiltersImpl.cpp:140-147, Matches.cpp:61-87 */
+void    orc_surface_normal_outlier(const float* nrm_read, const float* nrm_ref, const int32_t* ids, int32_t k, int64_t n,
+                                   float max_angle, float* w_out);                                     /* OutlierFiltersImpl.cpp:226-281 */
+void    orc_no_filter_weights(const float* d2, int64_t count, float* w_out);                            /* OutlierFilter.cpp:70-85 */
+
+/* ---- ErrorElements + PointToPlaneErrorMinimizer (ErrorMinimizer.cpp:59-193, PointToPlane.cpp:107-368) ----
+ * A_out (dim x dim row-major, dim = 6 | 4 (force4DOF) | 3 (force2D)), b_out, x_out are filled for inspection. */
+int32_t orc_point_to_plane(const float* read_feat, int32_t rstride, int64_t n, const float* ref_feat, int32_t fstride,
+                           const float* ref_normals, const int32_t* ids, const float* d2, const float* w, int32_t k,
+                           int32_t force2D, int32_t force4DOF, int32_t precision, float T_out[16], double* A_out, double* b_out,
+                           double* x_out, int32_t* kept_out, float* point_used_ratio, float* weighted_point_used_ratio);
+
+/* ---- whole registration (ICP.cpp:258-468) ---- */
+int32_t orc_icp(const orc_icp_config* cfg, const float* ref_feat, int32_t ref_stride, const float* ref_normals, int64_t m,
+                const float* read_feat, int32_t read_stride, const float* read_normals, int64_t n, const float T_init[16],
+                float T_out[16], orc_icp_stats* stats);
+
+/* ---- VoxelGridDataPointsFilter (VoxelGrid.cpp:71-344); in place, returns the number of points kept or <0 ---- */
+int64_t orc_voxelgrid(float* feat, int32_t stride, float* desc, int32_t desc_dim, int64_t n, float vx, float vy, float vz,
+                      int32_t use_centroid, int32_t average_descriptors, uint32_t* cell_of_point_out /* nullable, n entries */);
+
+/* ---- SurfaceNormalDataPointsFilter (SurfaceNormal.cpp:83-330); outputs nullable ---- */
+int32_t orc_surface_normals(const float* feat, int32_t stride, int64_t n, int32_t knn, float max_dist, int32_t precision,
+                            int32_t nthreads, const float* orient_origin /* nullable: flip toward this point */,
+                            float* normals, float* densities, float* eig_values, float* eig_vectors, float* matched_ids,
+                            float* mean_dists, float* lin_plan_curv, int32_t* degenerate_count);
+
+/* ---- open3d_slam side (fp64) ---- */
+enum { ORC_CROP_MAX_RADIUS = 0, ORC_CROP_MIN_RADIUS = 1, ORC_CROP_MINMAX_RADIUS = 2, ORC_CROP_CYLINDER = 3 };
+typedef struct orc_crop_spec {
+  int32_t kind; int32_t invert;
+  double center[3];            /* pose_.translation() — rotation is ignored (croppers.cpp:122) */
+  double rmin, rmax, zmin, zmax;
+} orc_crop_spec;
+int64_t orc_crop(const orc_crop_spec* spec, const double* xyz, const double* nrm, int64_t n, double* xyz_out, double* nrm_out,
+                 uint8_t* mask_out);                                                  /* croppers.cpp:53-167 */
+void    orc_transform_f64(const double T[16], const double* xyz, const double* nrm, int64_t n, double* xyz_out, double* nrm_out); /* helpers.cpp:283-318 (no identity-duplication) */
+int64_t orc_voxelize_within_volume(double voxel, const orc_crop_spec* spec, const double* xyz, const double* nrm, int64_t n,
+                                   double* xyz_out, double* nrm_out, int64_t* n_passthrough);   /* helpers.cpp:117-192; output = pass-through, then voxels in ascending (x,y,z) key order */
+int64_t orc_voxel_down_sample(double voxel, const double* xyz, const double* nrm, int64_t n, double* xyz_out, double* nrm_out); /* Open3D v0.15.1 VoxelDownSample, ascending key order */
+void    orc_o3d_to_pm(const double* xyz, const double* nrm, int64_t n, float* feat4, float* nrm3);   /* open3d_conversions.cpp:57-118 */
+
+#ifdef __cplusplus
+}
+#endif
+#endif
