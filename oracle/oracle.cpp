@@ -926,3 +926,371 @@ extern "C" int32_t orc_icp(const orc_icp_config* cfg, const float* ref_feat, int
   std::memcpy(T_out, out.m, sizeof(out.m));
   return finish(ORC_OK);
 }
+
+// ================================================================================================================
+// VoxelGridDataPointsFilter::inPlaceFilter (DataPointsFilters/VoxelGrid.cpp:71-344), 3D clouds (featDim == 4)
+// ================================================================================================================
+extern "C" int64_t orc_voxelgrid(float* feat, int32_t stride, float* desc, int32_t desc_dim, int64_t n, float vx, float vy, float vz,
+                                 int32_t use_centroid, int32_t average_descriptors, uint32_t* cell_of_point_out) {
+  if (n == 0) return 0;
+  float mn[3] = {kInf, kInf, kInf}, mx[3] = {-kInf, -kInf, -kInf};
+  for (int64_t i = 0; i < n; ++i)
+    for (int d = 0; d < 3; ++d) { mn[d] = std::min(mn[d], feat[i * stride + d]); mx[d] = std::max(mx[d], feat[i * stride + d]); }
+  const float vs[3] = {vx, vy, vz};
+  float minB[3], maxB[3];
+  for (int d = 0; d < 3; ++d) { minB[d] = mn[d] / vs[d]; maxB[d] = mx[d] / vs[d]; }   // :100-111
+  const unsigned numDivX = (unsigned)(1 + maxB[0] - minB[0]);                          // :115-121 (float arithmetic)
+  const unsigned numDivY = (unsigned)(1 + maxB[1] - minB[1]);
+  const unsigned numDivZ = (unsigned)(1 + maxB[2] - minB[2]);
+  const unsigned numVox = numDivX * numDivY * numDivZ;                                 // unsigned wrap like the reference
+  if (numVox == 0) return ORC_E_PARAM;                                                 // :127-130
+  struct Voxel { unsigned numPoints = 0, firstPoint = 0; };
+  // the reference allocates a dense vector<Voxel>(numVox) (:143-153); a map gives the same membership without the allocation
+  std::map<unsigned, Voxel> voxels;
+  std::vector<unsigned> indices((size_t)n);
+  for (int64_t p = 0; p < n; ++p) {                                                    // :155-182
+    const unsigned i = (unsigned)std::floor(feat[p * stride + 0] / vx - minB[0]);
+    const unsigned j = (unsigned)std::floor(feat[p * stride + 1] / vy - minB[1]);
+    const unsigned k = (unsigned)std::floor(feat[p * stride + 2] / vz - minB[2]);
+    const unsigned idx = i + j * numDivX + k * numDivX * numDivY;
+    Voxel& v = voxels[idx];
+    if (++v.numPoints == 1) v.firstPoint = (unsigned)p;
+    indices[p] = idx;
+    if (cell_of_point_out) cell_of_point_out[p] = idx;
+  }
+  std::vector<unsigned> keep;
+  if (use_centroid) {
+    for (int64_t p = 0; p < n; ++p) {                                                  // :192-222 sums in input order, fp32
+      const unsigned fp = voxels[indices[p]].firstPoint;
+      if (fp != (unsigned)p) {
+        for (int f = 0; f < 3; ++f) feat[(int64_t)fp * stride + f] += feat[p * stride + f];
+        if (average_descriptors && desc)
+          for (int d = 0; d < desc_dim; ++d) desc[(int64_t)fp * desc_dim + d] += desc[p * desc_dim + d];
+      }
+    }
+    for (auto& kv : voxels) {                                                          // :227-243
+      const unsigned np = kv.second.numPoints, fp = kv.second.firstPoint;
+      for (int f = 0; f < 3; ++f) feat[(int64_t)fp * stride + f] /= (float)np;
+      if (average_descriptors && desc)
+        for (int d = 0; d < desc_dim; ++d) desc[(int64_t)fp * desc_dim + d] /= (float)np;
+      keep.push_back(fp);
+    }
+  } else {
+    // cell-centre mode.  The reference's branch (:285-304) writes rows 1,2,3 and omits the bbox origin;
+    // the contract implemented here (and on the GPU) is the corrected one: centre = (minB + idx + 0.5) * vSize.
+    if (average_descriptors && desc)
+      for (int64_t p = 0; p < n; ++p) {
+        const unsigned fp = voxels[indices[p]].firstPoint;
+        if (fp != (unsigned)p)
+          for (int d = 0; d < desc_dim; ++d) desc[(int64_t)fp * desc_dim + d] += desc[p * desc_dim + d];
+      }
+    for (auto& kv : voxels) {
+      const unsigned idx = kv.first, np = kv.second.numPoints, fp = kv.second.firstPoint;
+      const unsigned k = idx / (numDivX * numDivY);
+      const unsigned j = (idx - k * numDivX * numDivY) / numDivX;
+      const unsigned i = idx - k * numDivX * numDivY - j * numDivX;
+      feat[(int64_t)fp * stride + 0] = (minB[0] + (float)i + 0.5f) * vx;
+      feat[(int64_t)fp * stride + 1] = (minB[1] + (float)j + 0.5f) * vy;
+      feat[(int64_t)fp * stride + 2] = (minB[2] + (float)k + 0.5f) * vz;
+      if (average_descriptors && desc)
+        for (int d = 0; d < desc_dim; ++d) desc[(int64_t)fp * desc_dim + d] /= (float)np;
+      keep.push_back(fp);
+    }
+  }
+  std::sort(keep.begin(), keep.end());                                                 // :322
+  for (size_t o = 0; o < keep.size(); ++o) {                                           // :324-334
+    const unsigned kq = keep[o];
+    for (int f = 0; f < stride; ++f) feat[o * stride + f] = feat[(int64_t)kq * stride + f];
+    if (desc)
+      for (int d = 0; d < desc_dim; ++d) desc[o * desc_dim + d] = desc[(int64_t)kq * desc_dim + d];
+  }
+  return (int64_t)keep.size();
+}
+
+// ================================================================================================================
+// SurfaceNormalDataPointsFilter::inPlaceFilter (DataPointsFilters/SurfaceNormal.cpp:83-330)
+// ================================================================================================================
+namespace {
+
+// symmetric 3x3 eigen-decomposition (cyclic Jacobi, double) — stands in for Eigen::EigenSolver at SurfaceNormal.cpp:212-214
+// (general real solver on a symmetric PSD matrix; eigenvector signs/order are not pinned by any reference test).
+// Output: eigenvalues ascending, eigenvectors as columns v[r][c].
+void symEig3(const double Cin[9], double val[3], double vec[3][3]) {
+  double a[3][3], V[3][3] = {{1, 0, 0}, {0, 1, 0}, {0, 0, 1}};
+  for (int i = 0; i < 3; ++i) for (int j = 0; j < 3; ++j) a[i][j] = Cin[3 * i + j];
+  for (int sweep = 0; sweep < 64; ++sweep) {
+    const double off = a[0][1] * a[0][1] + a[0][2] * a[0][2] + a[1][2] * a[1][2];
+    if (off == 0.0) break;
+    for (int p = 0; p < 3; ++p)
+      for (int q = p + 1; q < 3; ++q) {
+        if (a[p][q] == 0.0) continue;
+        const double theta = (a[q][q] - a[p][p]) / (2.0 * a[p][q]);
+        const double t = ((theta >= 0) ? 1.0 : -1.0) / (std::fabs(theta) + std::sqrt(theta * theta + 1.0));
+        const double c = 1.0 / std::sqrt(t * t + 1.0), s = t * c;
+        for (int k = 0; k < 3; ++k) { const double x = a[k][p], y = a[k][q]; a[k][p] = c * x - s * y; a[k][q] = s * x + c * y; }
+        for (int k = 0; k < 3; ++k) { const double x = a[p][k], y = a[q][k]; a[p][k] = c * x - s * y; a[q][k] = s * x + c * y; }
+        for (int k = 0; k < 3; ++k) { const double x = V[k][p], y = V[k][q]; V[k][p] = c * x - s * y; V[k][q] = s * x + c * y; }
+      }
+  }
+  int order[3] = {0, 1, 2};
+  std::sort(order, order + 3, [&](int x, int y) { return a[x][x] < a[y][y]; });
+  for (int c = 0; c < 3; ++c) {
+    val[c] = a[order[c]][order[c]];
+    for (int r = 0; r < 3; ++r) vec[r][c] = V[r][order[c]];
+  }
+}
+
+}  // namespace
+
+extern "C" int32_t orc_surface_normals(const float* feat, int32_t stride, int64_t n, int32_t knn, float max_dist, int32_t precision,
+                                       int32_t nthreads, const float* orient_origin, float* normals, float* densities,
+                                       float* eig_values, float* eig_vectors, float* matched_ids, float* mean_dists,
+                                       float* lin_plan_curv, int32_t* degenerate_count) {
+  if (knn < 3) return ORC_E_PARAM;   // SurfaceNormal.h:69 (min 3)
+  // self-kNN incl. the point itself through an own KDTreeMatcher (:170-179)
+  std::vector<int32_t> ids((size_t)knn * n);
+  std::vector<float> d2((size_t)knn * n);
+  void* tree = orc_kdtree_build(feat, stride, n);
+  orc_kdtree_knn(tree, feat, stride, n, knn, max_dist, 1, ids.data(), d2.data(), nthreads);
+  orc_kdtree_free(tree);
+  int degenerate = 0;
+#pragma omp parallel for schedule(static) num_threads(nthreads > 0 ? nthreads : 1) reduction(+ : degenerate)
+  for (int64_t i = 0; i < n; ++i) {
+    // gather neighbours (:190-198)
+    std::vector<double> d;   // 3 x realKnn, values are fp32 coordinates
+    d.reserve(3 * (size_t)knn);
+    int realKnn = 0;
+    for (int j = 0; j < knn; ++j)
+      if (d2[(size_t)knn * i + j] != kInf) {
+        const float* p = feat + (int64_t)ids[(size_t)knn * i + j] * stride;
+        d.push_back(p[0]); d.push_back(p[1]); d.push_back(p[2]);
+        ++realKnn;
+      }
+    double mean[3] = {0, 0, 0}, C[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+    double maxSq = 0;
+    if (precision == ORC_REF32) {   // fp32 mean / NN / covariance (:201-204)
+      float mf[3] = {0, 0, 0};
+      for (int j = 0; j < realKnn; ++j) for (int c = 0; c < 3; ++c) mf[c] += (float)d[3 * j + c];
+      for (int c = 0; c < 3; ++c) mf[c] /= (float)realKnn;
+      float Cf[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+      float maxSqF = 0.f;
+      for (int j = 0; j < realKnn; ++j) {
+        float nn[3];
+        for (int c = 0; c < 3; ++c) nn[c] = (float)d[3 * j + c] - mf[c];
+        for (int r = 0; r < 3; ++r) for (int c = 0; c < 3; ++c) Cf[3 * r + c] += nn[r] * nn[c];
+        maxSqF = std::max(maxSqF, (nn[0] * nn[0] + nn[1] * nn[1]) + nn[2] * nn[2]);
+      }
+      for (int q = 0; q < 9; ++q) C[q] = Cf[q] / (float)realKnn;
+      for (int c = 0; c < 3; ++c) mean[c] = mf[c];
+      maxSq = maxSqF;
+    } else {
+      for (int j = 0; j < realKnn; ++j) for (int c = 0; c < 3; ++c) mean[c] += d[3 * j + c];
+      for (int c = 0; c < 3; ++c) mean[c] /= (double)realKnn;
+      for (int j = 0; j < realKnn; ++j) {
+        double nn[3];
+        for (int c = 0; c < 3; ++c) nn[c] = d[3 * j + c] - mean[c];
+        for (int r = 0; r < 3; ++r) for (int c = 0; c < 3; ++c) C[3 * r + c] += nn[r] * nn[c];
+        maxSq = std::max(maxSq, nn[0] * nn[0] + nn[1] * nn[1] + nn[2] * nn[2]);
+      }
+      for (int q = 0; q < 9; ++q) C[q] /= (double)realKnn;
+    }
+    // rank test: C.fullPivHouseholderQr().rank() + 1 >= 3 (:210), in the reference's T = float
+    bool isDegenerate;
+    {
+      std::vector<float> Cf(9);
+      for (int q = 0; q < 9; ++q) Cf[q] = (float)C[q];
+      FullPivQR<float> qr(Cf, 3);
+      isDegenerate = !(qr.rank + 1 >= 3);
+      if (realKnn == 0) isDegenerate = true;
+    }
+    double val[3] = {0, 0, 0}, vec[3][3] = {{0, 0, 0}, {0, 0, 0}, {0, 0, 0}};
+    if (!isDegenerate) symEig3(C, val, vec); else ++degenerate;
+    if (normals) {   // eigenvector of the smallest eigenvalue (:237-246), clamped to [-1,1]
+      double nv[3] = {vec[0][0], vec[1][0], vec[2][0]};
+      if (orient_origin && !isDegenerate) {   // SurfaceNormalEstimatorPCA.cpp:69-84 semantics
+        const float* p = feat + i * stride;
+        const double dot = (orient_origin[0] - p[0]) * nv[0] + (orient_origin[1] - p[1]) * nv[1] + (orient_origin[2] - p[2]) * nv[2];
+        if (dot < 0) for (int c = 0; c < 3; ++c) nv[c] = -nv[c];
+      }
+      for (int c = 0; c < 3; ++c) normals[3 * i + c] = (float)std::min(1.0, std::max(-1.0, nv[c]));
+    }
+    if (densities) {   // utils.h:105-128
+      if (isDegenerate) densities[i] = 0.f;
+      else {
+        const float m2 = (float)maxSq;
+        const float volume = (float)(4. / 3.) * (float)M_PI * (m2 * std::sqrt(m2));
+        densities[i] = (volume > 0) ? ((float)realKnn / volume) : 0.f;
+      }
+    }
+    if (eig_values) for (int c = 0; c < 3; ++c) eig_values[3 * i + c] = (float)val[c];
+    if (eig_vectors)   // serializeEigVec: row-major (utils.h:90-101)
+      for (int r = 0; r < 3; ++r) for (int c = 0; c < 3; ++c) eig_vectors[9 * i + 3 * r + c] = (float)vec[r][c];
+    if (mean_dists) {
+      if (isDegenerate) mean_dists[i] = (float)std::numeric_limits<std::size_t>::max();
+      else {
+        const float* p = feat + i * stride;
+        const double dx = p[0] - mean[0], dy = p[1] - mean[1], dz = p[2] - mean[2];
+        mean_dists[i] = (float)std::sqrt(dx * dx + dy * dy + dz * dz);
+      }
+    }
+    if (lin_plan_curv) {   // SurfaceNormalEstimatorPCA.cpp:86-99 on ascending eigenvalues
+      if (isDegenerate) { lin_plan_curv[3 * i] = lin_plan_curv[3 * i + 1] = lin_plan_curv[3 * i + 2] = 0.f; }
+      else {
+        const float s1 = std::sqrt((float)val[0]), s2 = std::sqrt((float)val[1]), s3 = std::sqrt((float)val[2]);
+        lin_plan_curv[3 * i + 0] = (s3 - s2) / s3;
+        lin_plan_curv[3 * i + 1] = (s2 - s1) / s3;
+        lin_plan_curv[3 * i + 2] = s1 / (s1 + s2 + s3);
+      }
+    }
+    if (matched_ids) for (int j = 0; j < knn; ++j) matched_ids[(size_t)knn * i + j] = (float)ids[(size_t)knn * i + j];   // :294-297
+  }
+  if (degenerate_count) *degenerate_count = degenerate;
+  return ORC_OK;
+}
+
+// ================================================================================================================
+// open3d_slam side (fp64): croppers, transform, map voxelisation, Open3D VoxelDownSample, Open3D -> pointmatcher
+// citations relative to open3d_slam_rsl/open3d_slam/open3d_slam/
+// ================================================================================================================
+namespace {
+
+// CroppingVolume::isWithinVolume (src/croppers.cpp:53-55,121-167): only pose_.translation() is used; inclusive tests;
+// the cylinder's z range is absolute.
+inline bool withinVolume(const orc_crop_spec& s, const double* p) {
+  const double dx = p[0] - s.center[0], dy = p[1] - s.center[1], dz = p[2] - s.center[2];
+  bool in;
+  switch (s.kind) {
+    case ORC_CROP_MAX_RADIUS: in = std::sqrt(dx * dx + dy * dy + dz * dz) <= s.rmax; break;
+    case ORC_CROP_MIN_RADIUS: in = std::sqrt(dx * dx + dy * dy + dz * dz) >= s.rmin; break;
+    case ORC_CROP_MINMAX_RADIUS: {
+      const double d = std::sqrt(dx * dx + dy * dy + dz * dz);
+      in = d <= s.rmax && d >= s.rmin;
+      break;
+    }
+    default: in = p[2] >= s.zmin && p[2] <= s.zmax && std::sqrt(dx * dx + dy * dy) <= s.rmax; break;
+  }
+  return s.invert ? !in : in;
+}
+
+struct Acc {   // AccumulatedPoint (src/helpers.cpp:30-73)
+  int n = 0;
+  double p[3] = {0, 0, 0}, nn[3] = {0, 0, 0};
+};
+typedef std::tuple<int, int, int> Key;   // ordered (x, y, z) — our deterministic emission order
+
+}  // namespace
+
+extern "C" {
+
+// CroppingVolume::crop (src/croppers.cpp:76-106): order-preserving compaction of points (+ normals)
+int64_t orc_crop(const orc_crop_spec* spec, const double* xyz, const double* nrm, int64_t n, double* xyz_out, double* nrm_out,
+                 uint8_t* mask_out) {
+  int64_t o = 0;
+  for (int64_t i = 0; i < n; ++i) {
+    const bool in = withinVolume(*spec, xyz + 3 * i);
+    if (mask_out) mask_out[i] = in ? 1 : 0;
+    if (in) {
+      if (xyz_out) for (int d = 0; d < 3; ++d) xyz_out[3 * o + d] = xyz[3 * i + d];
+      if (nrm_out && nrm) for (int d = 0; d < 3; ++d) nrm_out[3 * o + d] = nrm[3 * i + d];
+      ++o;
+    }
+  }
+  return o;
+}
+
+// o3d_slam::transform (src/helpers.cpp:283-318): p' = (T [p;1]).head3 / w ; n' = (T [n;0]).head3.
+// The reference's duplicate-on-identity quirk (:285-288) is NOT reproduced.
+void orc_transform_f64(const double T[16], const double* xyz, const double* nrm, int64_t n, double* xyz_out, double* nrm_out) {
+  for (int64_t i = 0; i < n; ++i) {
+    const double* p = xyz + 3 * i;
+    double q[4];
+    for (int r = 0; r < 4; ++r) q[r] = ((T[4 * r + 0] * p[0] + T[4 * r + 1] * p[1]) + T[4 * r + 2] * p[2]) + T[4 * r + 3] * 1.0;
+    for (int r = 0; r < 3; ++r) xyz_out[3 * i + r] = q[r] / q[3];
+    if (nrm && nrm_out) {
+      const double* a = nrm + 3 * i;
+      for (int r = 0; r < 3; ++r) nrm_out[3 * i + r] = ((T[4 * r + 0] * a[0] + T[4 * r + 1] * a[1]) + T[4 * r + 2] * a[2]) + T[4 * r + 3] * 0.0;
+    }
+  }
+}
+
+// voxelizeWithinCroppingVolume (src/helpers.cpp:117-192) with key = int(floor(p * (1/v))) (VoxelHashMap.hpp:43-51).
+// Output: pass-through points (outside the volume) in input order, then one point per voxel: mean position,
+// normalised mean normal (NaN normals skipped in the sum, :35-37), voxels in ascending (x,y,z) key order.
+int64_t orc_voxelize_within_volume(double voxel, const orc_crop_spec* spec, const double* xyz, const double* nrm, int64_t n,
+                                   double* xyz_out, double* nrm_out, int64_t* n_passthrough) {
+  const double inv = 1.0 / voxel;
+  std::map<Key, Acc> acc;
+  int64_t o = 0;
+  for (int64_t i = 0; i < n; ++i) {
+    const double* p = xyz + 3 * i;
+    if (withinVolume(*spec, p)) {
+      const Key key((int)std::floor(p[0] * inv), (int)std::floor(p[1] * inv), (int)std::floor(p[2] * inv));
+      Acc& a = acc[key];
+      for (int d = 0; d < 3; ++d) a.p[d] += p[d];
+      if (nrm) {
+        const double* q = nrm + 3 * i;
+        if (!std::isnan(q[0]) && !std::isnan(q[1]) && !std::isnan(q[2])) for (int d = 0; d < 3; ++d) a.nn[d] += q[d];
+      }
+      a.n++;
+    } else {
+      for (int d = 0; d < 3; ++d) xyz_out[3 * o + d] = p[d];
+      if (nrm && nrm_out) for (int d = 0; d < 3; ++d) nrm_out[3 * o + d] = nrm[3 * i + d];
+      ++o;
+    }
+  }
+  if (n_passthrough) *n_passthrough = o;
+  for (auto& kv : acc) {
+    const Acc& a = kv.second;
+    for (int d = 0; d < 3; ++d) xyz_out[3 * o + d] = a.p[d] / (double)a.n;
+    if (nrm && nrm_out) {
+      double m[3];
+      for (int d = 0; d < 3; ++d) m[d] = a.nn[d] / (double)a.n;
+      const double nrm2 = std::sqrt(m[0] * m[0] + m[1] * m[1] + m[2] * m[2]);   // Eigen normalized(): divides if norm > 0
+      for (int d = 0; d < 3; ++d) nrm_out[3 * o + d] = (nrm2 > 0.0) ? m[d] / nrm2 : m[d];
+    }
+    ++o;
+  }
+  return o;
+}
+
+// Open3D v0.15.1 PointCloud::VoxelDownSample as called at src/helpers.cpp:108-115 (Open3D is an un-vendored dependency,
+// pinned by open3d_catkin/CMakeLists.txt:106-107): voxel_min_bound = min_bound - voxel/2, key = floor((p - min)/voxel),
+// mean position, mean normal (not re-normalised).  Emission order: ascending key (Open3D's is hash order — unpinned).
+int64_t orc_voxel_down_sample(double voxel, const double* xyz, const double* nrm, int64_t n, double* xyz_out, double* nrm_out) {
+  if (n == 0) return 0;
+  double mn[3] = {xyz[0], xyz[1], xyz[2]};
+  for (int64_t i = 1; i < n; ++i) for (int d = 0; d < 3; ++d) mn[d] = std::min(mn[d], xyz[3 * i + d]);
+  for (int d = 0; d < 3; ++d) mn[d] = mn[d] - voxel * 0.5;
+  std::map<Key, Acc> acc;
+  for (int64_t i = 0; i < n; ++i) {
+    const double* p = xyz + 3 * i;
+    const Key key((int)std::floor((p[0] - mn[0]) / voxel), (int)std::floor((p[1] - mn[1]) / voxel), (int)std::floor((p[2] - mn[2]) / voxel));
+    Acc& a = acc[key];
+    for (int d = 0; d < 3; ++d) a.p[d] += p[d];
+    if (nrm) {
+      const double* q = nrm + 3 * i;
+      if (!std::isnan(q[0]) && !std::isnan(q[1]) && !std::isnan(q[2])) for (int d = 0; d < 3; ++d) a.nn[d] += q[d];
+    }
+    a.n++;
+  }
+  int64_t o = 0;
+  for (auto& kv : acc) {
+    const Acc& a = kv.second;
+    for (int d = 0; d < 3; ++d) xyz_out[3 * o + d] = a.p[d] / (double)a.n;
+    if (nrm && nrm_out) for (int d = 0; d < 3; ++d) nrm_out[3 * o + d] = a.nn[d] / (double)a.n;
+    ++o;
+  }
+  return o;
+}
+
+// open3dToPointmatcher (open3d_slam_rsl/open3d_utils/open3d_conversions/src/open3d_conversions.cpp:21-118):
+// features 4 x N float (x y z pad=1), normals 3 x N float, fp64 -> fp32 round-to-nearest.
+void orc_o3d_to_pm(const double* xyz, const double* nrm, int64_t n, float* feat4, float* nrm3) {
+  for (int64_t i = 0; i < n; ++i) {
+    for (int d = 0; d < 3; ++d) feat4[4 * i + d] = (float)xyz[3 * i + d];
+    feat4[4 * i + 3] = 1.f;
+    if (nrm && nrm3) for (int d = 0; d < 3; ++d) nrm3[3 * i + d] = (float)nrm[3 * i + d];
+  }
+}
+
+}  // extern "C"

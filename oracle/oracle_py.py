@@ -1,0 +1,287 @@
+"""ctypes binding of oracle/liboracle.so — TEST INFRASTRUCTURE ONLY.
+
+Imported only by tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs.
+The product package never imports this module.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB = None
+
+ORC_REF32, ORC_MIXED = 0, 1
+CROP_MAX_RADIUS, CROP_MIN_RADIUS, CROP_MINMAX_RADIUS, CROP_CYLINDER = 0, 1, 2, 3
+
+
+class IcpConfig(C.Structure):
+    _fields_ = [("matcher_kind", C.c_int32), ("knn", C.c_int32), ("max_dist", C.c_float), ("epsilon", C.c_float),
+                ("trim_ratio", C.c_float), ("max_angle", C.c_float), ("force2D", C.c_int32), ("force4DOF", C.c_int32),
+                ("max_iter", C.c_int32), ("min_diff_rot", C.c_float), ("min_diff_trans", C.c_float),
+                ("smooth_length", C.c_int32), ("bound_rot", C.c_float), ("bound_trans", C.c_float),
+                ("precision", C.c_int32), ("nthreads", C.c_int32)]
+
+
+class IcpStats(C.Structure):
+    _fields_ = [("iterations", C.c_int32), ("max_iterations_reached", C.c_int32), ("status", C.c_int32),
+                ("kept_last", C.c_int32), ("points_touched", C.c_uint64), ("point_used_ratio", C.c_float),
+                ("weighted_point_used_ratio", C.c_float), ("last_tau", C.c_float), ("mean_ref", C.c_float * 3),
+                ("t_reference_s", C.c_double), ("t_converge_s", C.c_double)]
+
+
+class CropSpec(C.Structure):
+    _fields_ = [("kind", C.c_int32), ("invert", C.c_int32), ("center", C.c_double * 3), ("rmin", C.c_double),
+                ("rmax", C.c_double), ("zmin", C.c_double), ("zmax", C.c_double)]
+
+
+def build(force=False):
+    so = os.path.join(_HERE, "liboracle.so")
+    src = os.path.join(_HERE, "oracle.cpp")
+    if force or not os.path.exists(so) or (os.path.exists(src) and os.path.getmtime(src) > os.path.getmtime(so)):
+        subprocess.check_call(["make", "-C", _HERE, "-s"])
+    return so
+
+
+def lib():
+    global _LIB
+    if _LIB is None:
+        _LIB = C.CDLL(build())
+        L = _LIB
+        L.orc_kdtree_build.restype = C.c_void_p
+        L.orc_kdtree_build.argtypes = [C.c_void_p, C.c_int32, C.c_int64]
+        L.orc_kdtree_free.argtypes = [C.c_void_p]
+        L.orc_kdtree_knn.restype = C.c_uint64
+        L.orc_kdtree_knn.argtypes = [C.c_void_p, C.c_void_p, C.c_int32, C.c_int64, C.c_int32, C.c_float, C.c_int32,
+                                     C.c_void_p, C.c_void_p, C.c_int32]
+        L.orc_knn_brute.restype = C.c_uint64
+        L.orc_knn_brute.argtypes = [C.c_void_p, C.c_int32, C.c_int64, C.c_void_p, C.c_int32, C.c_int64, C.c_int32, C.c_float,
+                                    C.c_void_p, C.c_void_p, C.c_int32]
+        L.orc_transform.restype = C.c_int32
+        L.orc_transform.argtypes = [C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_int64]
+        L.orc_trimmed_dist.restype = C.c_int32
+        L.orc_trimmed_dist.argtypes = [C.c_void_p, C.c_int64, C.c_float, C.c_void_p, C.c_void_p]
+        L.orc_surface_normal_outlier.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int64, C.c_float, C.c_void_p]
+        L.orc_no_filter_weights.argtypes = [C.c_void_p, C.c_int64, C.c_void_p]
+        L.orc_point_to_plane.restype = C.c_int32
+        L.orc_point_to_plane.argtypes = [C.c_void_p, C.c_int32, C.c_int64, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p,
+                                         C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_void_p,
+                                         C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.orc_icp.restype = C.c_int32
+        L.orc_icp.argtypes = [C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_int64, C.c_void_p, C.c_int32, C.c_void_p,
+                              C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.orc_voxelgrid.restype = C.c_int64
+        L.orc_voxelgrid.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_int32, C.c_int64, C.c_float, C.c_float, C.c_float,
+                                    C.c_int32, C.c_int32, C.c_void_p]
+        L.orc_surface_normals.restype = C.c_int32
+        L.orc_surface_normals.argtypes = [C.c_void_p, C.c_int32, C.c_int64, C.c_int32, C.c_float, C.c_int32, C.c_int32,
+                                          C.c_void_p] + [C.c_void_p] * 8
+        L.orc_crop.restype = C.c_int64
+        L.orc_crop.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.orc_transform_f64.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]
+        L.orc_voxelize_within_volume.restype = C.c_int64
+        L.orc_voxelize_within_volume.argtypes = [C.c_double, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p,
+                                                 C.c_void_p, C.c_void_p]
+        L.orc_voxel_down_sample.restype = C.c_int64
+        L.orc_voxel_down_sample.argtypes = [C.c_double, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]
+        L.orc_o3d_to_pm.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]
+    return _LIB
+
+
+def _p(a):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+def _f32(a):
+    return None if a is None else np.ascontiguousarray(a, dtype=np.float32)
+
+
+def _f64(a):
+    return None if a is None else np.ascontiguousarray(a, dtype=np.float64)
+
+
+def feat4(xyz):
+    """N x 3 -> N x 4 float32 (x y z 1): the memory layout of Eigen's column-major 4 x N `features`."""
+    xyz = np.asarray(xyz, dtype=np.float32)
+    out = np.ones((xyz.shape[0], 4), dtype=np.float32)
+    out[:, :3] = xyz[:, :3]
+    return out
+
+
+class KdTree:
+    def __init__(self, feat):
+        self.feat = _f32(feat)
+        self.n, self.stride = self.feat.shape
+        self.h = lib().orc_kdtree_build(_p(self.feat), self.stride, self.n)
+
+    def knn(self, q, k=1, max_dist=np.inf, allow_self=True, nthreads=1):
+        q = _f32(q)
+        ids = np.empty((q.shape[0], k), dtype=np.int32)
+        d2 = np.empty((q.shape[0], k), dtype=np.float32)
+        visits = lib().orc_kdtree_knn(self.h, _p(q), q.shape[1], q.shape[0], k, max_dist, int(allow_self), _p(ids), _p(d2), nthreads)
+        return ids, d2, visits
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            lib().orc_kdtree_free(self.h)
+            self.h = None
+
+
+def knn_brute(ref, q, k=1, max_dist=np.inf, nthreads=8):
+    ref, q = _f32(ref), _f32(q)
+    ids = np.empty((q.shape[0], k), dtype=np.int32)
+    d2 = np.empty((q.shape[0], k), dtype=np.float32)
+    lib().orc_knn_brute(_p(ref), ref.shape[1], ref.shape[0], _p(q), q.shape[1], q.shape[0], k, max_dist, _p(ids), _p(d2), nthreads)
+    return ids, d2
+
+
+def transform(T, feat, normals=None):
+    T = _f32(T).reshape(16)
+    feat = _f32(feat).copy()
+    normals = None if normals is None else _f32(normals).copy()
+    st = lib().orc_transform(_p(T), _p(feat), feat.shape[1], _p(normals), feat.shape[0])
+    return st, feat, normals
+
+
+def trimmed_dist(d2, ratio):
+    d2 = _f32(d2)
+    tau = C.c_float(0)
+    w = np.empty(d2.shape, dtype=np.float32)
+    st = lib().orc_trimmed_dist(_p(d2), d2.size, ratio, C.byref(tau), _p(w))
+    return st, tau.value, w
+
+
+def surface_normal_outlier(nrm_read, nrm_ref, ids, max_angle):
+    ids = np.ascontiguousarray(ids, dtype=np.int32)
+    n, k = ids.shape
+    w = np.empty((n, k), dtype=np.float32)
+    lib().orc_surface_normal_outlier(_p(_f32(nrm_read)), _p(_f32(nrm_ref)), _p(ids), k, n, max_angle, _p(w))
+    return w
+
+
+def no_filter_weights(d2):
+    d2 = _f32(d2)
+    w = np.empty(d2.shape, dtype=np.float32)
+    lib().orc_no_filter_weights(_p(d2), d2.size, _p(w))
+    return w
+
+
+def point_to_plane(read_feat, ref_feat, ref_normals, ids, d2, w, force2D=False, force4DOF=False, precision=ORC_MIXED):
+    read_feat, ref_feat, ref_normals = _f32(read_feat), _f32(ref_feat), _f32(ref_normals)
+    ids = np.ascontiguousarray(ids, dtype=np.int32)
+    d2, w = _f32(d2), _f32(w)
+    n = read_feat.shape[0]
+    k = ids.size // n
+    dim = 3 if force2D else (4 if force4DOF else 6)
+    T = np.empty(16, dtype=np.float32)
+    A = np.zeros(dim * dim, dtype=np.float64)
+    b = np.zeros(dim, dtype=np.float64)
+    x = np.zeros(dim, dtype=np.float64)
+    kept = C.c_int32(0)
+    pur, wpur = C.c_float(0), C.c_float(0)
+    st = lib().orc_point_to_plane(_p(read_feat), read_feat.shape[1], n, _p(ref_feat), ref_feat.shape[1], _p(ref_normals), _p(ids),
+                                  _p(d2), _p(w), k, int(force2D), int(force4DOF), precision, _p(T), _p(A), _p(b), _p(x),
+                                  C.byref(kept), C.byref(pur), C.byref(wpur))
+    return dict(status=st, T=T.reshape(4, 4), A=A.reshape(dim, dim), b=b, x=x, kept=kept.value,
+                point_used_ratio=pur.value, weighted_point_used_ratio=wpur.value)
+
+
+def icp_config(**kw):
+    c = IcpConfig(matcher_kind=0, knn=1, max_dist=float("inf"), epsilon=0.0, trim_ratio=0.85, max_angle=-1.0, force2D=0,
+                  force4DOF=0, max_iter=40, min_diff_rot=0.001, min_diff_trans=0.01, smooth_length=3, bound_rot=-1.0,
+                  bound_trans=-1.0, precision=ORC_REF32, nthreads=1)
+    for k, v in kw.items():
+        if not hasattr(c, k):
+            raise AttributeError(k)
+        setattr(c, k, v)
+    return c
+
+
+def icp(cfg, ref_feat, ref_normals, read_feat, read_normals=None, T_init=None):
+    ref_feat, ref_normals, read_feat, read_normals = _f32(ref_feat), _f32(ref_normals), _f32(read_feat), _f32(read_normals)
+    T_init = np.eye(4, dtype=np.float32) if T_init is None else _f32(T_init)
+    T = np.zeros(16, dtype=np.float32)
+    st = IcpStats()
+    code = lib().orc_icp(C.byref(cfg), _p(ref_feat), ref_feat.shape[1], _p(ref_normals), ref_feat.shape[0], _p(read_feat),
+                         read_feat.shape[1], _p(read_normals), read_feat.shape[0], _p(T_init.reshape(16)), _p(T), C.byref(st))
+    return code, T.reshape(4, 4), st
+
+
+def voxelgrid(feat, desc, vx, vy, vz, use_centroid=True, average_descriptors=True):
+    feat = _f32(feat).copy()
+    desc = None if desc is None else _f32(desc).copy()
+    n = feat.shape[0]
+    cells = np.empty(n, dtype=np.uint32)
+    m = lib().orc_voxelgrid(_p(feat), feat.shape[1], _p(desc), 0 if desc is None else desc.shape[1], n, vx, vy, vz,
+                            int(use_centroid), int(average_descriptors), _p(cells))
+    if m < 0:
+        return m, None, None, cells
+    return m, feat[:m], (None if desc is None else desc[:m]), cells
+
+
+def surface_normals(feat, knn, max_dist=np.inf, precision=ORC_MIXED, nthreads=8, orient_origin=None, keep=("normals",)):
+    feat = _f32(feat)
+    n = feat.shape[0]
+    shapes = dict(normals=(n, 3), densities=(n,), eig_values=(n, 3), eig_vectors=(n, 9), matched_ids=(n, knn),
+                  mean_dists=(n,), lin_plan_curv=(n, 3))
+    out = {k: (np.zeros(s, dtype=np.float32) if k in keep else None) for k, s in shapes.items()}
+    deg = C.c_int32(0)
+    oo = None if orient_origin is None else _f32(orient_origin)
+    st = lib().orc_surface_normals(_p(feat), feat.shape[1], n, knn, max_dist, precision, nthreads, _p(oo), _p(out["normals"]),
+                                   _p(out["densities"]), _p(out["eig_values"]), _p(out["eig_vectors"]), _p(out["matched_ids"]),
+                                   _p(out["mean_dists"]), _p(out["lin_plan_curv"]), C.byref(deg))
+    out["status"] = st
+    out["degenerate"] = deg.value
+    return out
+
+
+def crop_spec(kind, center, rmin=0.0, rmax=0.0, zmin=0.0, zmax=0.0, invert=False):
+    s = CropSpec(kind=kind, invert=int(invert), rmin=rmin, rmax=rmax, zmin=zmin, zmax=zmax)
+    for i in range(3):
+        s.center[i] = float(center[i])
+    return s
+
+
+def crop(spec, xyz, nrm=None):
+    xyz, nrm = _f64(xyz), _f64(nrm)
+    n = xyz.shape[0]
+    xo = np.empty_like(xyz)
+    no = None if nrm is None else np.empty_like(nrm)
+    mask = np.empty(n, dtype=np.uint8)
+    m = lib().orc_crop(C.byref(spec), _p(xyz), _p(nrm), n, _p(xo), _p(no), _p(mask))
+    return xo[:m], (None if no is None else no[:m]), mask.astype(bool)
+
+
+def transform_f64(T, xyz, nrm=None):
+    T, xyz, nrm = _f64(T).reshape(16), _f64(xyz), _f64(nrm)
+    xo = np.empty_like(xyz)
+    no = None if nrm is None else np.empty_like(nrm)
+    lib().orc_transform_f64(_p(T), _p(xyz), _p(nrm), xyz.shape[0], _p(xo), _p(no))
+    return xo, no
+
+
+def voxelize_within_volume(voxel, spec, xyz, nrm=None):
+    xyz, nrm = _f64(xyz), _f64(nrm)
+    xo = np.empty_like(xyz)
+    no = None if nrm is None else np.empty_like(nrm)
+    npass = C.c_int64(0)
+    m = lib().orc_voxelize_within_volume(voxel, C.byref(spec), _p(xyz), _p(nrm), xyz.shape[0], _p(xo), _p(no), C.byref(npass))
+    return xo[:m], (None if no is None else no[:m]), npass.value
+
+
+def voxel_down_sample(voxel, xyz, nrm=None):
+    xyz, nrm = _f64(xyz), _f64(nrm)
+    xo = np.empty_like(xyz)
+    no = None if nrm is None else np.empty_like(nrm)
+    m = lib().orc_voxel_down_sample(voxel, _p(xyz), _p(nrm), xyz.shape[0], _p(xo), _p(no))
+    return xo[:m], (None if no is None else no[:m])
+
+
+def o3d_to_pm(xyz, nrm=None):
+    xyz, nrm = _f64(xyz), _f64(nrm)
+    n = xyz.shape[0]
+    f = np.empty((n, 4), dtype=np.float32)
+    nn = None if nrm is None else np.empty((n, 3), dtype=np.float32)
+    lib().orc_o3d_to_pm(_p(xyz), _p(nrm), n, _p(f), _p(nn))
+    return f, nn
