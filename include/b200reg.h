@@ -1,0 +1,195 @@
+/*
+ * include/b200reg.h — C ABI of libb200reg.so: the B200 (sm_100a) scan-to-map registration hot path.
+ *
+ * Drop-in boundary for the path the reference implements in libpointmatcher's registrable modules and open3d_slam's
+ * Mapper.  Plain pointers and sizes only; no C++ types, no exceptions, no torch types.  Each entry
+ * point cites the reference interface it replaces (paths relative to /root/reference/).
+ *
+ * Conventions
+ *   - every function returns int32_t status: B200REG_OK (0) or a negative B200REG_E_* code; b200reg_last_error(ctx)
+ *     returns the message the C++ shim re-throws as the matching libpointmatcher exception type.
+ *   - one ctx per (thread, device); calls on one ctx are ordered on its CUDA stream; a ctx is NOT thread-safe,
+ *     distinct ctxs are independent (libpointmatcher modules are stateful and non re-entrant too).
+ *   - host cloud layout == Eigen column-major DataPoints (PointMatcher.h:229-431): features = `feat_stride` floats per
+ *     point with x y z first (stride 4: x y z pad), normals = 3 floats per point.  Copy semantics; caller owns host memory.
+ *   - matches (PointMatcher.h:444-464): ids[k*i + j], d2[k*i + j] = j-th neighbour of reading point i, SQUARED distances,
+ *     invalid = (-1, +inf).
+ *   - 4x4 transforms are ROW-MAJOR float[16] / double[16] at this boundary.
+ *   - there is NO CPU fallback: without a CUDA device every call fails with B200REG_E_CUDA.
+ */
+#ifndef B200REG_H
+#define B200REG_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200REG_ABI_VERSION 1
+
+enum {
+  B200REG_OK = 0,
+  B200REG_E_INVALID_PARAM = -1,   /* PointMatcherSupport::InvalidParameter (Parametrizable.h)            */
+  B200REG_E_INVALID_FIELD = -2,   /* DataPoints::InvalidField (PointMatcher.h:304-307)                    */
+  B200REG_E_NO_POINTS = -3,       /* runtime_error "The reading point cloud is empty" (ICP.cpp:357-359)   */
+  B200REG_E_NOT_CONVERGED = -4,   /* PointMatcher::ConvergenceError (PointMatcher.h:100-103)              */
+  B200REG_E_TRANSFORM = -5,       /* TransformationError (TransformationsImpl.cpp:74)                     */
+  B200REG_E_CUDA = -6,
+  B200REG_E_OOM = -7
+};
+
+typedef struct b200reg_ctx b200reg_ctx;
+typedef struct b200reg_cloud b200reg_cloud;   /* device-resident DataPoints mirror: float4 xyz(+pad), float4 normal */
+typedef struct b200reg_index b200reg_index;   /* radix-sorted voxel-grid index over a (centred) reference cloud    */
+typedef struct b200reg_map b200reg_map;       /* resident fp64 voxel map (open3d_slam Submap::mapCloud_)           */
+
+/* ---- context ------------------------------------------------------------------------------------------------ */
+int32_t b200reg_abi_version(void);
+int32_t b200reg_ctx_create(int32_t device, b200reg_ctx** out);
+void    b200reg_ctx_destroy(b200reg_ctx* ctx);
+const char* b200reg_last_error(const b200reg_ctx* ctx);
+int32_t b200reg_ctx_sync(b200reg_ctx* ctx);
+/* number of kernels this ctx has launched since creation (bench.py "gpu_launches") */
+uint64_t b200reg_ctx_launch_count(const b200reg_ctx* ctx);
+
+/* ---- clouds: replaces DataPoints construction/copies (PointMatcher.h:229-431) and open3dToPointmatcher
+ *      (open3d_slam_rsl/open3d_utils/open3d_conversions/src/open3d_conversions.cpp:21-118) -------------------------- */
+int32_t b200reg_cloud_upload_f32(b200reg_ctx* ctx, const float* feat, int32_t feat_stride, const float* normals, int64_t n,
+                                 b200reg_cloud** out);
+int32_t b200reg_cloud_upload_f64(b200reg_ctx* ctx, const double* xyz, const double* normals, int64_t n, b200reg_cloud** out);
+int32_t b200reg_cloud_download_f32(b200reg_ctx* ctx, const b200reg_cloud* cloud, float* feat, int32_t feat_stride, float* normals);
+int64_t b200reg_cloud_size(const b200reg_cloud* cloud);
+int32_t b200reg_cloud_has_normals(const b200reg_cloud* cloud);
+void    b200reg_cloud_free(b200reg_ctx* ctx, b200reg_cloud* cloud);
+
+/* ---- RigidTransformation::inPlaceCompute (libpointmatcher/pointmatcher/TransformationsImpl.cpp:61-114) -------------- */
+int32_t b200reg_cloud_transform(b200reg_ctx* ctx, b200reg_cloud* inout, const float T[16]);
+
+/* ---- KDTreeMatcher::init (MatchersImpl.cpp:109-114) -> index build; KDTreeMatcher::findClosests (:117-132) -> knn ---- */
+/* cell <= 0 : automatic cell size.  The index copies what it needs; `ref` may be freed afterwards. */
+int32_t b200reg_index_build(b200reg_ctx* ctx, const b200reg_cloud* ref, float cell, b200reg_index** out);
+void    b200reg_index_free(b200reg_ctx* ctx, b200reg_index* index);
+int64_t b200reg_index_size(const b200reg_index* index);
+float   b200reg_index_cell(const b200reg_index* index);
+/* T (nullable): applied to every query on the fly (fp32, fixed op order) before the search — the fused
+ * `transformations.apply(stepReading, T_iter)` + `matcher->findClosests(stepReading)` of ICP.cpp:409-413.
+ * ids_out / d2_out : HOST buffers of k*n entries (nullable).  visit_count (nullable) = points distance-tested
+ * (Matcher::visitCounter, Matcher.cpp:46-72).  epsilon is accepted for YAML compatibility and treated as 0. */
+int32_t b200reg_knn(b200reg_ctx* ctx, const b200reg_index* index, const b200reg_cloud* query, const float* T, int32_t k,
+                    float max_dist, float epsilon, int32_t allow_self, int32_t* ids_out, float* d2_out, uint64_t* visit_count);
+
+/* ---- one ICP iteration's device work (ICP.cpp:409-433 minus the 6x6 solve):
+ *      transform + match (a4,a6), TrimmedDistOutlierFilter (OutlierFiltersImpl.cpp:140-147 + Matches.cpp:61-87),
+ *      SurfaceNormalOutlierFilter (OutlierFiltersImpl.cpp:226-281), ErrorElements statistics (ErrorMinimizer.cpp:59-140)
+ *      and the point-to-plane normal equations A = G G^T, b = -G h^T (PointToPlane.cpp:107-156) ---------------------- */
+typedef struct b200reg_step_stats {
+  int64_t kept;                       /* pairs with non-zero weight and finite distance               */
+  int64_t n_finite;                   /* finite matches (input of the quantile)                       */
+  double  weight_sum;                 /* sum of weights                                              */
+  float   tau;                        /* trimmed-distance limit (bit-exact nth_element value); inf if filter off */
+  float   point_used_ratio;           /* ErrorMinimizer.cpp:139                                      */
+  float   weighted_point_used_ratio;  /* ErrorMinimizer.cpp:140                                      */
+  uint64_t visit_count;
+  double  mean_reading[3];            /* mean of kept (transformed) reading points  (PointToPlane.cpp:263) */
+  double  mean_reference[3];          /* mean of matched reference points           (PointToPlane.cpp:264) */
+} b200reg_step_stats;
+
+/* A_out: 6x6 row-major (unknown order alpha beta gamma tx ty tz), formed on the mean-centred pairs exactly as
+ * PointToPlane.cpp:263-268 does; b_out: 6.  trim_ratio <= 0 / max_angle < 0 switch the respective filter off
+ * (both off = OutlierFilters::compute with an empty chain, OutlierFilter.cpp:70-85).  force2D != 0 drops the z components
+ * of points and normals before forming G and h (PointToPlane.cpp:247-254). */
+int32_t b200reg_icp_step(b200reg_ctx* ctx, const b200reg_index* index, const b200reg_cloud* reading, const float* T_iter,
+                         int32_t k, float max_dist, float trim_ratio, float max_angle, int32_t force2D, double A_out[36],
+                         double b_out[6], b200reg_step_stats* stats);
+
+/* PointToPlaneErrorMinimizer::compute tail (PointToPlane.cpp:185-368): solve (LLT, rank-reduced minimum norm when
+ * singular), Rodrigues, un-centre.  Host arithmetic in fp64; T_out = the 4x4 step transform rounded to fp32. */
+int32_t b200reg_solve_point_to_plane(const double A[36], const double b[6], const double mean_reading[3],
+                                     const double mean_reference[3], int32_t force2D, int32_t force4DOF, float T_out[16],
+                                     double x_out[6]);
+
+/* ---- whole registration: ICP::initReference + ICP::computeWithTransformedReference (ICP.cpp:258-468) ---------------- */
+typedef struct b200reg_icp_config {
+  int32_t knn;            /* KDTreeMatcher knn (MatchersImpl.h:97)                                   */
+  float   max_dist;       /* KDTreeMatcher maxDist (MatchersImpl.h:100), inf allowed                 */
+  float   epsilon;        /* accepted, treated as 0                                                  */
+  float   trim_ratio;     /* TrimmedDistOutlierFilter ratio (OutlierFiltersImpl.h:137); <= 0 absent   */
+  float   max_angle;      /* SurfaceNormalOutlierFilter maxAngle; < 0 absent                          */
+  int32_t force2D;        /* PointToPlane.h:74                                                       */
+  int32_t force4DOF;      /* PointToPlane.h:75                                                       */
+  int32_t max_iter;       /* CounterTransformationChecker maxIterationCount; <= 0 absent             */
+  float   min_diff_rot;   /* DifferentialTransformationChecker (TransformationCheckersImpl.h:88-93)  */
+  float   min_diff_trans;
+  int32_t smooth_length;  /* < 0 : checker absent                                                    */
+  float   bound_rot;      /* BoundTransformationChecker; < 0 absent                                  */
+  float   bound_trans;
+  float   cell;           /* index cell size for b200reg_icp_set_reference; <= 0 automatic           */
+} b200reg_icp_config;
+
+typedef struct b200reg_icp_stats {   /* the reference's Inspector stat names (ICP.cpp:282-284,391-393,452-456) */
+  int32_t iterations;                 /* IterationsCount                 */
+  int32_t max_iterations_reached;     /* ICP.cpp:444                     */
+  int64_t reference_point_count;      /* ReferencePointCount             */
+  int64_t reading_point_count;        /* ReadingPointCount               */
+  uint64_t points_touched;            /* PointCountTouched               */
+  float   overlap_ratio;              /* OverlapRatio = weightedPointUsedRatio */
+  float   point_used_ratio;
+  float   last_tau;
+  int64_t kept_last;
+  double  reference_preprocessing_s;  /* ReferencePreprocessingDuration  */
+  double  reading_preprocessing_s;    /* ReadingPreprocessingDuration    */
+  double  convergence_s;              /* ConvergenceDuration             */
+  double  device_ms;                  /* CUDA-event time of the iterate loop */
+} b200reg_icp_stats;
+
+typedef struct b200reg_icp b200reg_icp;   /* PointMatcher<float>::ICP with the CUDA chain inside */
+int32_t b200reg_icp_create(b200reg_ctx* ctx, const b200reg_icp_config* cfg, b200reg_icp** out);
+void    b200reg_icp_destroy(b200reg_icp* icp);
+/* ICP::initReference (ICP.cpp:293-328): mean, centring, index build.  Keeps its own copy of what it needs. */
+int32_t b200reg_icp_set_reference(b200reg_icp* icp, const b200reg_cloud* reference);
+/* ICP::compute(reading, <empty>, T_init, initializeMatcher=false) (ICP.cpp:258-290 + 332-468), as Mapper.cpp:391-393 calls it */
+int32_t b200reg_icp_register(b200reg_icp* icp, const b200reg_cloud* reading, const float T_init[16], float T_out[16],
+                             b200reg_icp_stats* stats);
+const b200reg_index* b200reg_icp_index(const b200reg_icp* icp);
+int32_t b200reg_icp_reference_mean(const b200reg_icp* icp, float mean_out[3]);
+
+/* ---- DataPointsFilters -------------------------------------------------------------------------------------------- */
+/* VoxelGridDataPointsFilter::inPlaceFilter (DataPointsFilters/VoxelGrid.cpp:71-344); origin_mode 0 = libpointmatcher
+ * bbox convention.  use_centroid 0 = cell centre (corrected).  Normals are averaged like any descriptor
+ * when average_descriptors != 0, else the first point's are kept. */
+int32_t b200reg_voxelgrid(b200reg_ctx* ctx, b200reg_cloud* inout, float vx, float vy, float vz, int32_t use_centroid,
+                          int32_t average_descriptors);
+/* SurfaceNormalDataPointsFilter::inPlaceFilter (DataPointsFilters/SurfaceNormal.cpp:83-330).  Writes the cloud's
+ * normals; optional HOST outputs (nullable): densities[n], eig_values[3n] ascending, lin_plan_curv[3n].
+ * orient_origin (nullable float[3]): flip normals toward that point (CloudRegistration.cpp:71-74 usage). */
+int32_t b200reg_surface_normals(b200reg_ctx* ctx, b200reg_cloud* inout, int32_t knn, float max_dist, float epsilon,
+                                const float* orient_origin, float* densities_out, float* eig_values_out,
+                                float* lin_plan_curv_out, int32_t* degenerate_count);
+
+/* ---- open3d_slam voxel-map crop / insert (fp64) --------------------------------------------------------------------- */
+enum { B200REG_CROP_MAX_RADIUS = 0, B200REG_CROP_MIN_RADIUS = 1, B200REG_CROP_MINMAX_RADIUS = 2, B200REG_CROP_CYLINDER = 3 };
+typedef struct b200reg_crop_spec {   /* CroppingVolume (open3d_slam/src/croppers.cpp:53-167) */
+  int32_t kind;
+  int32_t invert;
+  double  center[3];   /* pose_.translation(); rotation ignored like the reference */
+  double  rmin, rmax, zmin, zmax;
+} b200reg_crop_spec;
+
+int32_t b200reg_map_create(b200reg_ctx* ctx, double voxel_size, b200reg_map** out);
+void    b200reg_map_destroy(b200reg_ctx* ctx, b200reg_map* map);
+int64_t b200reg_map_size(const b200reg_map* map);
+/* Submap::insertScan (open3d_slam/src/Submap.cpp:39-96): transform (helpers.cpp:283-318), append, re-voxelise inside
+ * `volume` (helpers.cpp:117-192).  scan_xyz / scan_nrm: HOST fp64 arrays (nrm nullable). */
+int32_t b200reg_map_insert(b200reg_ctx* ctx, b200reg_map* map, const double* scan_xyz, const double* scan_nrm, int64_t n,
+                           const double T_map_scan[16], const b200reg_crop_spec* volume);
+/* ScanToMapRegistration::cropSubmap (open3d_slam/src/ScanToMapRegistration.cpp:90-96) + open3dToPointmatcher:
+ * order-preserving crop of the resident map into a float cloud ready for b200reg_icp_set_reference. */
+int32_t b200reg_map_crop(b200reg_ctx* ctx, const b200reg_map* map, const b200reg_crop_spec* volume, b200reg_cloud** out);
+int32_t b200reg_map_download(b200reg_ctx* ctx, const b200reg_map* map, double* xyz, double* nrm);
+/* CroppingVolume::crop on a host fp64 cloud (croppers.cpp:76-106): returns the kept count, writes compacted output */
+int32_t b200reg_crop_f64(b200reg_ctx* ctx, const b200reg_crop_spec* volume, const double* xyz, const double* nrm, int64_t n,
+                         double* xyz_out, double* nrm_out, int64_t* n_out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200REG_H */

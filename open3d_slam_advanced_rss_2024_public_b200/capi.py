@@ -1,0 +1,415 @@
+"""ctypes binding of libb200reg.so (include/b200reg.h) — the call a Python user makes.
+
+There is no CPU fallback: if the CUDA library is missing or no GPU is visible, every entry point raises.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libb200reg.so")
+_LIB = None
+
+OK = 0
+E_INVALID_PARAM, E_INVALID_FIELD, E_NO_POINTS, E_NOT_CONVERGED, E_TRANSFORM, E_CUDA, E_OOM = -1, -2, -3, -4, -5, -6, -7
+CROP_MAX_RADIUS, CROP_MIN_RADIUS, CROP_MINMAX_RADIUS, CROP_CYLINDER = 0, 1, 2, 3
+
+
+# exception types mirror libpointmatcher's (PointMatcher.h:86-103,156-159,304-307); all derive from RuntimeError
+class B200RegError(RuntimeError):
+    code = None
+
+
+class InvalidParameter(B200RegError):
+    code = E_INVALID_PARAM
+
+
+class InvalidField(B200RegError):
+    code = E_INVALID_FIELD
+
+
+class NoPoints(B200RegError):
+    code = E_NO_POINTS
+
+
+class ConvergenceError(B200RegError):
+    code = E_NOT_CONVERGED
+
+
+class TransformationError(B200RegError):
+    code = E_TRANSFORM
+
+
+class CudaError(B200RegError):
+    code = E_CUDA
+
+
+class OutOfMemory(B200RegError):
+    code = E_OOM
+
+
+_EXC = {c.code: c for c in (InvalidParameter, InvalidField, NoPoints, ConvergenceError, TransformationError, CudaError, OutOfMemory)}
+
+
+class StepStats(C.Structure):
+    _fields_ = [("kept", C.c_int64), ("n_finite", C.c_int64), ("weight_sum", C.c_double), ("tau", C.c_float),
+                ("point_used_ratio", C.c_float), ("weighted_point_used_ratio", C.c_float), ("visit_count", C.c_uint64),
+                ("mean_reading", C.c_double * 3), ("mean_reference", C.c_double * 3)]
+
+
+class IcpConfig(C.Structure):
+    _fields_ = [("knn", C.c_int32), ("max_dist", C.c_float), ("epsilon", C.c_float), ("trim_ratio", C.c_float),
+                ("max_angle", C.c_float), ("force2D", C.c_int32), ("force4DOF", C.c_int32), ("max_iter", C.c_int32),
+                ("min_diff_rot", C.c_float), ("min_diff_trans", C.c_float), ("smooth_length", C.c_int32),
+                ("bound_rot", C.c_float), ("bound_trans", C.c_float), ("cell", C.c_float)]
+
+
+class IcpStats(C.Structure):
+    _fields_ = [("iterations", C.c_int32), ("max_iterations_reached", C.c_int32), ("reference_point_count", C.c_int64),
+                ("reading_point_count", C.c_int64), ("points_touched", C.c_uint64), ("overlap_ratio", C.c_float),
+                ("point_used_ratio", C.c_float), ("last_tau", C.c_float), ("kept_last", C.c_int64),
+                ("reference_preprocessing_s", C.c_double), ("reading_preprocessing_s", C.c_double),
+                ("convergence_s", C.c_double), ("device_ms", C.c_double)]
+
+
+class CropSpec(C.Structure):
+    _fields_ = [("kind", C.c_int32), ("invert", C.c_int32), ("center", C.c_double * 3), ("rmin", C.c_double),
+                ("rmax", C.c_double), ("zmin", C.c_double), ("zmax", C.c_double)]
+
+
+# every symbol include/b200reg.h declares: name -> (restype, argtypes)
+_VP = C.c_void_p
+SYMBOLS = {
+    "b200reg_abi_version": (C.c_int32, []),
+    "b200reg_ctx_create": (C.c_int32, [C.c_int32, C.POINTER(_VP)]),
+    "b200reg_ctx_destroy": (None, [_VP]),
+    "b200reg_last_error": (C.c_char_p, [_VP]),
+    "b200reg_ctx_sync": (C.c_int32, [_VP]),
+    "b200reg_ctx_launch_count": (C.c_uint64, [_VP]),
+    "b200reg_cloud_upload_f32": (C.c_int32, [_VP, _VP, C.c_int32, _VP, C.c_int64, C.POINTER(_VP)]),
+    "b200reg_cloud_upload_f64": (C.c_int32, [_VP, _VP, _VP, C.c_int64, C.POINTER(_VP)]),
+    "b200reg_cloud_download_f32": (C.c_int32, [_VP, _VP, _VP, C.c_int32, _VP]),
+    "b200reg_cloud_size": (C.c_int64, [_VP]),
+    "b200reg_cloud_has_normals": (C.c_int32, [_VP]),
+    "b200reg_cloud_free": (None, [_VP, _VP]),
+    "b200reg_cloud_transform": (C.c_int32, [_VP, _VP, _VP]),
+    "b200reg_index_build": (C.c_int32, [_VP, _VP, C.c_float, C.POINTER(_VP)]),
+    "b200reg_index_free": (None, [_VP, _VP]),
+    "b200reg_index_size": (C.c_int64, [_VP]),
+    "b200reg_index_cell": (C.c_float, [_VP]),
+    "b200reg_knn": (C.c_int32, [_VP, _VP, _VP, _VP, C.c_int32, C.c_float, C.c_float, C.c_int32, _VP, _VP, C.POINTER(C.c_uint64)]),
+    "b200reg_icp_step": (C.c_int32, [_VP, _VP, _VP, _VP, C.c_int32, C.c_float, C.c_float, C.c_float, C.c_int32, _VP, _VP, C.POINTER(StepStats)]),
+    "b200reg_solve_point_to_plane": (C.c_int32, [_VP, _VP, _VP, _VP, C.c_int32, C.c_int32, _VP, _VP]),
+    "b200reg_icp_create": (C.c_int32, [_VP, C.POINTER(IcpConfig), C.POINTER(_VP)]),
+    "b200reg_icp_destroy": (None, [_VP]),
+    "b200reg_icp_set_reference": (C.c_int32, [_VP, _VP]),
+    "b200reg_icp_register": (C.c_int32, [_VP, _VP, _VP, _VP, C.POINTER(IcpStats)]),
+    "b200reg_icp_index": (_VP, [_VP]),
+    "b200reg_icp_reference_mean": (C.c_int32, [_VP, _VP]),
+    "b200reg_voxelgrid": (C.c_int32, [_VP, _VP, C.c_float, C.c_float, C.c_float, C.c_int32, C.c_int32]),
+    "b200reg_surface_normals": (C.c_int32, [_VP, _VP, C.c_int32, C.c_float, C.c_float, _VP, _VP, _VP, _VP, C.POINTER(C.c_int32)]),
+    "b200reg_map_create": (C.c_int32, [_VP, C.c_double, C.POINTER(_VP)]),
+    "b200reg_map_destroy": (None, [_VP, _VP]),
+    "b200reg_map_size": (C.c_int64, [_VP]),
+    "b200reg_map_insert": (C.c_int32, [_VP, _VP, _VP, _VP, C.c_int64, _VP, C.POINTER(CropSpec)]),
+    "b200reg_map_crop": (C.c_int32, [_VP, _VP, C.POINTER(CropSpec), C.POINTER(_VP)]),
+    "b200reg_map_download": (C.c_int32, [_VP, _VP, _VP, _VP]),
+    "b200reg_crop_f64": (C.c_int32, [_VP, C.POINTER(CropSpec), _VP, _VP, C.c_int64, _VP, _VP, C.POINTER(C.c_int64)]),
+}
+
+
+def lib():
+    """Load libb200reg.so; fails loudly when the CUDA extension has not been built."""
+    global _LIB
+    if _LIB is None:
+        if not os.path.exists(LIB_PATH):
+            raise ImportError(f"{LIB_PATH} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                              "(there is no CPU fallback)")
+        L = C.CDLL(LIB_PATH)
+        for name, (res, args) in SYMBOLS.items():
+            fn = getattr(L, name)   # AttributeError if the library does not export a declared symbol
+            fn.restype = res
+            fn.argtypes = args
+        _LIB = L
+    return _LIB
+
+
+def _p(a):
+    return None if a is None else a.ctypes.data_as(_VP)
+
+
+def _f32(a):
+    return None if a is None else np.ascontiguousarray(a, dtype=np.float32)
+
+
+def _f64(a):
+    return None if a is None else np.ascontiguousarray(a, dtype=np.float64)
+
+
+def crop_spec(kind, center, rmin=0.0, rmax=0.0, zmin=0.0, zmax=0.0, invert=False):
+    s = CropSpec(kind=kind, invert=int(invert), rmin=rmin, rmax=rmax, zmin=zmin, zmax=zmax)
+    for i in range(3):
+        s.center[i] = float(center[i])
+    return s
+
+
+def icp_config(**kw):
+    """Defaults = the CPU twins' defaults (MatchersImpl.h:97-100, OutlierFiltersImpl.h:137, TransformationCheckersImpl.h)."""
+    c = IcpConfig(knn=1, max_dist=float("inf"), epsilon=0.0, trim_ratio=0.85, max_angle=-1.0, force2D=0, force4DOF=0,
+                  max_iter=40, min_diff_rot=0.001, min_diff_trans=0.01, smooth_length=3, bound_rot=-1.0, bound_trans=-1.0,
+                  cell=0.0)
+    for k, v in kw.items():
+        if not hasattr(c, k):
+            raise AttributeError(k)
+        setattr(c, k, v)
+    return c
+
+
+class Context:
+    def __init__(self, device=0):
+        self.h = _VP()
+        code = lib().b200reg_ctx_create(device, C.byref(self.h))
+        if code != OK:
+            self.h = None
+            raise _EXC.get(code, B200RegError)(f"b200reg_ctx_create(device={device}) failed with {code}: no usable CUDA device "
+                                               "(this library has no CPU fallback)")
+
+    def check(self, code):
+        if code != OK:
+            msg = lib().b200reg_last_error(self.h)
+            raise _EXC.get(code, B200RegError)((msg or b"").decode("utf-8", "replace"))
+
+    def sync(self):
+        self.check(lib().b200reg_ctx_sync(self.h))
+
+    @property
+    def launch_count(self):
+        return int(lib().b200reg_ctx_launch_count(self.h))
+
+    def close(self):
+        if self.h:
+            lib().b200reg_ctx_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---- clouds
+    def upload(self, feat, normals=None):
+        """feat: N x stride float32 (stride >= 3, xyz first) or float64 N x 3 (open3d side)."""
+        feat = np.asarray(feat)
+        if feat.dtype == np.float64:
+            xyz, nrm = _f64(feat[:, :3]), _f64(normals)
+            h = _VP()
+            self.check(lib().b200reg_cloud_upload_f64(self.h, _p(xyz), _p(nrm), xyz.shape[0], C.byref(h)))
+        else:
+            feat, nrm = _f32(feat), _f32(normals)
+            h = _VP()
+            self.check(lib().b200reg_cloud_upload_f32(self.h, _p(feat), feat.shape[1], _p(nrm), feat.shape[0], C.byref(h)))
+        return Cloud(self, h)
+
+    def build_index(self, cloud, cell=0.0):
+        h = _VP()
+        self.check(lib().b200reg_index_build(self.h, cloud.h, cell, C.byref(h)))
+        return Index(self, h)
+
+    def knn(self, index, query, T=None, k=1, max_dist=np.inf, epsilon=0.0, allow_self=True, want=True):
+        n = query.size
+        ids = np.empty((n, k), dtype=np.int32) if want else None
+        d2 = np.empty((n, k), dtype=np.float32) if want else None
+        visits = C.c_uint64(0)
+        Tm = None if T is None else _f32(T).reshape(16)
+        self.check(lib().b200reg_knn(self.h, index.h, query.h, _p(Tm), k, max_dist, epsilon, int(allow_self), _p(ids), _p(d2), C.byref(visits)))
+        return ids, d2, visits.value
+
+    def icp_step(self, index, reading, T=None, k=1, max_dist=np.inf, trim_ratio=-1.0, max_angle=-1.0, force2D=False):
+        A = np.zeros((6, 6), dtype=np.float64)
+        b = np.zeros(6, dtype=np.float64)
+        st = StepStats()
+        Tm = None if T is None else _f32(T).reshape(16)
+        self.check(lib().b200reg_icp_step(self.h, index.h, reading.h, _p(Tm), k, max_dist, trim_ratio, max_angle, int(force2D), _p(A), _p(b), C.byref(st)))
+        return A, b, st
+
+    def crop_f64(self, spec, xyz, nrm=None):
+        xyz, nrm = _f64(xyz), _f64(nrm)
+        xo = np.empty_like(xyz)
+        no = None if nrm is None else np.empty_like(nrm)
+        m = C.c_int64(0)
+        self.check(lib().b200reg_crop_f64(self.h, C.byref(spec), _p(xyz), _p(nrm), xyz.shape[0], _p(xo), _p(no), C.byref(m)))
+        return xo[:m.value], (None if no is None else no[:m.value])
+
+
+def solve_point_to_plane(A, b, mean_reading, mean_reference, force2D=False, force4DOF=False):
+    A, b = _f64(A).reshape(36), _f64(b)
+    mr, ms = _f64(mean_reading), _f64(mean_reference)
+    T = np.empty(16, dtype=np.float32)
+    x = np.zeros(6, dtype=np.float64)
+    code = lib().b200reg_solve_point_to_plane(_p(A), _p(b), _p(mr), _p(ms), int(force2D), int(force4DOF), _p(T), _p(x))
+    if code != OK:
+        raise _EXC.get(code, B200RegError)("solve_point_to_plane failed")
+    return T.reshape(4, 4), x
+
+
+class Cloud:
+    def __init__(self, ctx, h):
+        self.ctx, self.h = ctx, h
+
+    @property
+    def size(self):
+        return int(lib().b200reg_cloud_size(self.h))
+
+    @property
+    def has_normals(self):
+        return bool(lib().b200reg_cloud_has_normals(self.h))
+
+    def download(self, stride=4, normals=None):
+        n = self.size
+        feat = np.empty((n, stride), dtype=np.float32)
+        want_n = self.has_normals if normals is None else normals
+        nrm = np.empty((n, 3), dtype=np.float32) if want_n else None
+        self.ctx.check(lib().b200reg_cloud_download_f32(self.ctx.h, self.h, _p(feat), stride, _p(nrm)))
+        return feat, nrm
+
+    def transform(self, T):
+        T = _f32(T).reshape(16)
+        self.ctx.check(lib().b200reg_cloud_transform(self.ctx.h, self.h, _p(T)))
+
+    def voxelgrid(self, vx, vy, vz, use_centroid=True, average_descriptors=True):
+        self.ctx.check(lib().b200reg_voxelgrid(self.ctx.h, self.h, vx, vy, vz, int(use_centroid), int(average_descriptors)))
+
+    def surface_normals(self, knn, max_dist=np.inf, epsilon=0.0, orient_origin=None, keep=()):
+        n = self.size
+        oo = None if orient_origin is None else _f32(orient_origin)
+        dens = np.empty(n, dtype=np.float32) if "densities" in keep else None
+        ev = np.empty((n, 3), dtype=np.float32) if "eig_values" in keep else None
+        lpc = np.empty((n, 3), dtype=np.float32) if "lin_plan_curv" in keep else None
+        deg = C.c_int32(0)
+        self.ctx.check(lib().b200reg_surface_normals(self.ctx.h, self.h, knn, max_dist, epsilon, _p(oo), _p(dens), _p(ev), _p(lpc), C.byref(deg)))
+        return dict(densities=dens, eig_values=ev, lin_plan_curv=lpc, degenerate=deg.value)
+
+    def free(self):
+        if self.h:
+            lib().b200reg_cloud_free(self.ctx.h, self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            if self.ctx.h:
+                self.free()
+        except Exception:
+            pass
+
+
+class Index:
+    def __init__(self, ctx, h, owned=True):
+        self.ctx, self.h, self.owned = ctx, h, owned
+
+    @property
+    def size(self):
+        return int(lib().b200reg_index_size(self.h))
+
+    @property
+    def cell(self):
+        return float(lib().b200reg_index_cell(self.h))
+
+    def free(self):
+        if self.h and self.owned:
+            lib().b200reg_index_free(self.ctx.h, self.h)
+        self.h = None
+
+    def __del__(self):
+        try:
+            if self.ctx.h:
+                self.free()
+        except Exception:
+            pass
+
+
+class ICP:
+    """PointMatcher<float>::ICP with the CUDA chain: KDTree matcher + TrimmedDist/SurfaceNormal filters + PointToPlane."""
+
+    def __init__(self, ctx, cfg=None, **kw):
+        self.ctx = ctx
+        self.cfg = cfg if cfg is not None else icp_config(**kw)
+        self.h = _VP()
+        ctx.check(lib().b200reg_icp_create(ctx.h, C.byref(self.cfg), C.byref(self.h)))
+
+    def set_reference(self, cloud):
+        self.ctx.check(lib().b200reg_icp_set_reference(self.h, cloud.h))
+
+    @property
+    def index(self):
+        return Index(self.ctx, lib().b200reg_icp_index(self.h), owned=False)
+
+    @property
+    def reference_mean(self):
+        m = np.zeros(3, dtype=np.float32)
+        lib().b200reg_icp_reference_mean(self.h, _p(m))
+        return m
+
+    def register(self, reading, T_init=None):
+        T_init = np.eye(4, dtype=np.float32) if T_init is None else _f32(T_init)
+        T = np.zeros(16, dtype=np.float32)
+        st = IcpStats()
+        code = lib().b200reg_icp_register(self.h, reading.h, _p(T_init.reshape(16)), _p(T), C.byref(st))
+        self.last_stats = st
+        self.ctx.check(code)
+        return T.reshape(4, 4), st
+
+    def close(self):
+        if self.h:
+            lib().b200reg_icp_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            if self.ctx.h:
+                self.close()
+        except Exception:
+            pass
+
+
+class VoxelMap:
+    """Resident fp64 voxel map (open3d_slam Submap::mapCloud_ + insertScan + cropSubmap)."""
+
+    def __init__(self, ctx, voxel_size):
+        self.ctx = ctx
+        self.h = _VP()
+        ctx.check(lib().b200reg_map_create(ctx.h, voxel_size, C.byref(self.h)))
+
+    @property
+    def size(self):
+        return int(lib().b200reg_map_size(self.h))
+
+    def insert(self, scan_xyz, scan_nrm, T_map_scan, volume):
+        xyz, nrm = _f64(scan_xyz), _f64(scan_nrm)
+        T = _f64(T_map_scan).reshape(16)
+        self.ctx.check(lib().b200reg_map_insert(self.ctx.h, self.h, _p(xyz), _p(nrm), xyz.shape[0], _p(T), C.byref(volume)))
+
+    def crop(self, volume):
+        h = _VP()
+        self.ctx.check(lib().b200reg_map_crop(self.ctx.h, self.h, C.byref(volume), C.byref(h)))
+        return Cloud(self.ctx, h)
+
+    def download(self):
+        n = self.size
+        xyz = np.empty((n, 3), dtype=np.float64)
+        nrm = np.empty((n, 3), dtype=np.float64)
+        self.ctx.check(lib().b200reg_map_download(self.ctx.h, self.h, _p(xyz), _p(nrm)))
+        return xyz, nrm
+
+    def close(self):
+        if self.h:
+            lib().b200reg_map_destroy(self.ctx.h, self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            if self.ctx.h:
+                self.close()
+        except Exception:
+            pass

@@ -1,0 +1,247 @@
+// csrc/cloud.cu — context, device clouds (DataPoints mirror), uploads/downloads, RigidTransformation.
+#include "common.cuh"
+
+int setErr(b200reg_ctx* ctx, int code, const char* fmt, ...) {
+  if (ctx) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(ctx->err, sizeof(ctx->err), fmt, ap);
+    va_end(ap);
+  }
+  return code;
+}
+
+int ensureBuf(b200reg_ctx* ctx, DevBuf& b, size_t bytes) {
+  if (bytes <= b.cap) return B200REG_OK;
+  if (b.p) {
+    CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+    CUDA_TRY(ctx, cudaFree(b.p));
+    b.p = nullptr;
+    b.cap = 0;
+  }
+  size_t want = bytes + bytes / 4 + 256;
+  CUDA_TRY(ctx, cudaMalloc(&b.p, want));
+  b.cap = want;
+  return B200REG_OK;
+}
+
+int ensurePinned(b200reg_ctx* ctx, size_t bytes) {
+  if (bytes <= ctx->pinned_cap) return B200REG_OK;
+  if (ctx->pinned) {
+    CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+    CUDA_TRY(ctx, cudaFreeHost(ctx->pinned));
+    ctx->pinned = nullptr;
+  }
+  CUDA_TRY(ctx, cudaMallocHost(&ctx->pinned, bytes));
+  ctx->pinned_cap = bytes;
+  return B200REG_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// kernels
+// ---------------------------------------------------------------------------------------------------------------
+__global__ void packF32Kernel(const float* __restrict__ feat, int stride, const float* __restrict__ nrm, int64_t n,
+                              float4* __restrict__ xyz, float4* __restrict__ outN) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const float* p = feat + i * stride;
+  xyz[i] = make_float4(p[0], p[1], p[2], stride >= 4 ? p[3] : 1.f);
+  if (nrm) outN[i] = make_float4(nrm[3 * i], nrm[3 * i + 1], nrm[3 * i + 2], 0.f);
+}
+
+// open3dToPointmatcher (open3d_conversions.cpp:57-118): fp64 -> fp32 round-to-nearest, pad = 1
+__global__ void packF64Kernel(const double* __restrict__ xyzIn, const double* __restrict__ nrm, int64_t n,
+                              float4* __restrict__ xyz, float4* __restrict__ outN) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  xyz[i] = make_float4(__double2float_rn(xyzIn[3 * i]), __double2float_rn(xyzIn[3 * i + 1]), __double2float_rn(xyzIn[3 * i + 2]), 1.f);
+  if (nrm) outN[i] = make_float4(__double2float_rn(nrm[3 * i]), __double2float_rn(nrm[3 * i + 1]), __double2float_rn(nrm[3 * i + 2]), 0.f);
+}
+
+__global__ void unpackF32Kernel(const float4* __restrict__ xyz, const float4* __restrict__ nrm, int64_t n, float* __restrict__ feat,
+                                int stride, float* __restrict__ outN) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const float4 p = xyz[i];
+  float* o = feat + i * stride;
+  o[0] = p.x; o[1] = p.y; o[2] = p.z;
+  if (stride >= 4) o[3] = p.w;
+  if (outN && nrm) {
+    const float4 q = nrm[i];
+    outN[3 * i] = q.x; outN[3 * i + 1] = q.y; outN[3 * i + 2] = q.z;
+  }
+}
+
+// RigidTransformation::inPlaceCompute (TransformationsImpl.cpp:61-96)
+__global__ void transformKernel(float4* __restrict__ xyz, float4* __restrict__ nrm, int64_t n, Rigid12 T, float t30, float t31,
+                                float t32, float t33) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const float4 p = xyz[i];
+  const float3 r = xformPoint(T, p.x, p.y, p.z, p.w);
+  const float w = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(t30, p.x), __fmul_rn(t31, p.y)), __fmul_rn(t32, p.z)), __fmul_rn(t33, p.w));
+  xyz[i] = make_float4(r.x, r.y, r.z, w);
+  if (nrm) {
+    const float4 q = nrm[i];
+    const float3 s = xformNormal(T, q.x, q.y, q.z);
+    nrm[i] = make_float4(s.x, s.y, s.z, 0.f);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// C ABI
+// ---------------------------------------------------------------------------------------------------------------
+extern "C" {
+
+int32_t b200reg_abi_version(void) { return B200REG_ABI_VERSION; }
+
+int32_t b200reg_ctx_create(int32_t device, b200reg_ctx** out) {
+  if (!out) return B200REG_E_INVALID_PARAM;
+  *out = nullptr;
+  int count = 0;
+  if (cudaGetDeviceCount(&count) != cudaSuccess || count <= 0 || device < 0 || device >= count) return B200REG_E_CUDA;   // no CPU fallback
+  b200reg_ctx* ctx = new b200reg_ctx();
+  ctx->device = device;
+  if (cudaSetDevice(device) != cudaSuccess) { delete ctx; return B200REG_E_CUDA; }
+  cudaDeviceProp prop;
+  if (cudaGetDeviceProperties(&prop, device) == cudaSuccess) ctx->sm_count = prop.multiProcessorCount;
+  if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess) { delete ctx; return B200REG_E_CUDA; }
+  cudaEventCreate(&ctx->ev0);
+  cudaEventCreate(&ctx->ev1);
+  if (cudaMalloc(&ctx->dstate, 65536) != cudaSuccess) { delete ctx; return B200REG_E_OOM; }
+  cudaMemsetAsync(ctx->dstate, 0, 65536, ctx->stream);
+  if (ensurePinned(ctx, 1 << 16) != B200REG_OK) { delete ctx; return B200REG_E_OOM; }
+  *out = ctx;
+  return B200REG_OK;
+}
+
+void b200reg_ctx_destroy(b200reg_ctx* ctx) {
+  if (!ctx) return;
+  cudaSetDevice(ctx->device);
+  cudaStreamSynchronize(ctx->stream);
+  DevBuf* bufs[] = {&ctx->keys0, &ctx->keys1, &ctx->vals0, &ctx->vals1, &ctx->cubtmp, &ctx->misc, &ctx->partials,
+                    &ctx->matchIds, &ctx->matchD2, &ctx->matchPos, &ctx->flags};
+  for (DevBuf* b : bufs)
+    if (b->p) cudaFree(b->p);
+  if (ctx->pinned) cudaFreeHost(ctx->pinned);
+  if (ctx->dstate) cudaFree(ctx->dstate);
+  cudaEventDestroy(ctx->ev0);
+  cudaEventDestroy(ctx->ev1);
+  cudaStreamDestroy(ctx->stream);
+  delete ctx;
+}
+
+const char* b200reg_last_error(const b200reg_ctx* ctx) { return ctx ? ctx->err : "null context"; }
+
+int32_t b200reg_ctx_sync(b200reg_ctx* ctx) {
+  if (!ctx) return B200REG_E_INVALID_PARAM;
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  return B200REG_OK;
+}
+
+uint64_t b200reg_ctx_launch_count(const b200reg_ctx* ctx) { return ctx ? ctx->launches : 0; }
+
+static int allocCloud(b200reg_ctx* ctx, int64_t n, bool normals, b200reg_cloud** out) {
+  b200reg_cloud* c = new b200reg_cloud();
+  c->n = n;
+  c->cap = n > 0 ? n : 1;
+  cudaError_t e = cudaMalloc(&c->xyz, sizeof(float4) * (size_t)c->cap);
+  if (e == cudaSuccess && normals) e = cudaMalloc(&c->nrm, sizeof(float4) * (size_t)c->cap);
+  if (e != cudaSuccess) {
+    if (c->xyz) cudaFree(c->xyz);
+    delete c;
+    return setErr(ctx, B200REG_E_OOM, "cloud allocation of %lld points failed: %s", (long long)n, cudaGetErrorString(e));
+  }
+  *out = c;
+  return B200REG_OK;
+}
+
+int32_t b200reg_cloud_upload_f32(b200reg_ctx* ctx, const float* feat, int32_t feat_stride, const float* normals, int64_t n,
+                                 b200reg_cloud** out) {
+  if (!ctx || !out || n < 0 || (n > 0 && !feat) || feat_stride < 3) return setErr(ctx, B200REG_E_INVALID_PARAM, "cloud_upload_f32: bad arguments");
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  b200reg_cloud* c = nullptr;
+  TRY(allocCloud(ctx, n, normals != nullptr, &c));
+  if (n > 0) {
+    const size_t fb = sizeof(float) * (size_t)n * feat_stride, nb = normals ? sizeof(float) * 3 * (size_t)n : 0;
+    if (feat_stride == 4 && !normals) {
+      CUDA_TRY(ctx, cudaMemcpyAsync(c->xyz, feat, fb, cudaMemcpyHostToDevice, ctx->stream));
+    } else {
+      TRY(ensureBuf(ctx, ctx->misc, fb + nb + 16));
+      float* dfeat = (float*)ctx->misc.p;
+      float* dn = normals ? (float*)((char*)ctx->misc.p + ((fb + 15) / 16) * 16) : nullptr;
+      CUDA_TRY(ctx, cudaMemcpyAsync(dfeat, feat, fb, cudaMemcpyHostToDevice, ctx->stream));
+      if (normals) CUDA_TRY(ctx, cudaMemcpyAsync(dn, normals, nb, cudaMemcpyHostToDevice, ctx->stream));
+      packF32Kernel<<<divUp(n, 256), 256, 0, ctx->stream>>>(dfeat, feat_stride, dn, n, c->xyz, c->nrm);
+      LAUNCH_CHECK(ctx);
+    }
+    CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));   // host buffers may be reused by the caller on return
+  }
+  *out = c;
+  return B200REG_OK;
+}
+
+int32_t b200reg_cloud_upload_f64(b200reg_ctx* ctx, const double* xyz, const double* normals, int64_t n, b200reg_cloud** out) {
+  if (!ctx || !out || n < 0 || (n > 0 && !xyz)) return setErr(ctx, B200REG_E_INVALID_PARAM, "cloud_upload_f64: bad arguments");
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  b200reg_cloud* c = nullptr;
+  TRY(allocCloud(ctx, n, normals != nullptr, &c));
+  if (n > 0) {
+    const size_t fb = sizeof(double) * 3 * (size_t)n;
+    TRY(ensureBuf(ctx, ctx->misc, 2 * fb));
+    double* dx = (double*)ctx->misc.p;
+    double* dn = normals ? dx + 3 * (size_t)n : nullptr;
+    CUDA_TRY(ctx, cudaMemcpyAsync(dx, xyz, fb, cudaMemcpyHostToDevice, ctx->stream));
+    if (normals) CUDA_TRY(ctx, cudaMemcpyAsync(dn, normals, fb, cudaMemcpyHostToDevice, ctx->stream));
+    packF64Kernel<<<divUp(n, 256), 256, 0, ctx->stream>>>(dx, dn, n, c->xyz, c->nrm);
+    LAUNCH_CHECK(ctx);
+    CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  }
+  *out = c;
+  return B200REG_OK;
+}
+
+int32_t b200reg_cloud_download_f32(b200reg_ctx* ctx, const b200reg_cloud* cloud, float* feat, int32_t feat_stride, float* normals) {
+  if (!ctx || !cloud || feat_stride < 3) return setErr(ctx, B200REG_E_INVALID_PARAM, "cloud_download_f32: bad arguments");
+  if (normals && !cloud->nrm) return setErr(ctx, B200REG_E_INVALID_FIELD, "cloud has no 'normals' descriptor");
+  const int64_t n = cloud->n;
+  if (n == 0) return B200REG_OK;
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  const size_t fb = sizeof(float) * (size_t)n * feat_stride, nb = normals ? sizeof(float) * 3 * (size_t)n : 0;
+  TRY(ensureBuf(ctx, ctx->misc, fb + nb + 16));
+  float* dfeat = (float*)ctx->misc.p;
+  float* dn = normals ? (float*)((char*)ctx->misc.p + ((fb + 15) / 16) * 16) : nullptr;
+  unpackF32Kernel<<<divUp(n, 256), 256, 0, ctx->stream>>>(cloud->xyz, cloud->nrm, n, dfeat, feat_stride, dn);
+  LAUNCH_CHECK(ctx);
+  if (feat) CUDA_TRY(ctx, cudaMemcpyAsync(feat, dfeat, fb, cudaMemcpyDeviceToHost, ctx->stream));
+  if (normals) CUDA_TRY(ctx, cudaMemcpyAsync(normals, dn, nb, cudaMemcpyDeviceToHost, ctx->stream));
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  return B200REG_OK;
+}
+
+int64_t b200reg_cloud_size(const b200reg_cloud* cloud) { return cloud ? cloud->n : 0; }
+int32_t b200reg_cloud_has_normals(const b200reg_cloud* cloud) { return (cloud && cloud->nrm) ? 1 : 0; }
+
+void b200reg_cloud_free(b200reg_ctx* ctx, b200reg_cloud* cloud) {
+  if (!cloud) return;
+  if (ctx) { cudaSetDevice(ctx->device); cudaStreamSynchronize(ctx->stream); }
+  if (cloud->xyz) cudaFree(cloud->xyz);
+  if (cloud->nrm) cudaFree(cloud->nrm);
+  delete cloud;
+}
+
+int32_t b200reg_cloud_transform(b200reg_ctx* ctx, b200reg_cloud* inout, const float T[16]) {
+  if (!ctx || !inout || !T) return setErr(ctx, B200REG_E_INVALID_PARAM, "cloud_transform: bad arguments");
+  // checkParameters (TransformationsImpl.cpp:100-114): |1 - det R| > 1e-3 -> TransformationError
+  const float det = T[0] * (T[5] * T[10] - T[6] * T[9]) - T[1] * (T[4] * T[10] - T[6] * T[8]) + T[2] * (T[4] * T[9] - T[5] * T[8]);
+  if (fabsf(1.f - det) > 0.001f) return setErr(ctx, B200REG_E_TRANSFORM, "RigidTransformation: Error, rotation matrix is not orthogonal.");
+  if (inout->n == 0) return B200REG_OK;
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  Rigid12 R;
+  memcpy(R.m, T, sizeof(R.m));
+  transformKernel<<<divUp(inout->n, 256), 256, 0, ctx->stream>>>(inout->xyz, inout->nrm, inout->n, R, T[12], T[13], T[14], T[15]);
+  LAUNCH_CHECK(ctx);
+  return B200REG_OK;
+}
+
+}  // extern "C"

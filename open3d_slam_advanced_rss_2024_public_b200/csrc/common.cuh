@@ -1,0 +1,109 @@
+// csrc/common.cuh — internal types shared by the libb200reg.so translation units (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+
+#include <math_constants.h>
+
+#include "../../include/b200reg.h"
+
+#define B200_SM_COUNT 148   // B200: 2 dies x 74 SMs; grids are sized in multiples of this
+
+struct DevBuf {   // growable device scratch (never shrinks; freed with the ctx)
+  void* p = nullptr;
+  size_t cap = 0;
+};
+
+struct b200reg_ctx {
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  int sm_count = B200_SM_COUNT;
+  char err[512] = {0};
+  uint64_t launches = 0;
+  // scratch
+  DevBuf keys0, keys1, vals0, vals1, cubtmp, misc, partials, matchIds, matchD2, matchPos, flags;
+  void* pinned = nullptr;   // pinned host staging for small D2H results
+  size_t pinned_cap = 0;
+  void* dstate = nullptr;   // small device state block (select state, counters)
+};
+
+struct b200reg_cloud {
+  int64_t n = 0;
+  int64_t cap = 0;
+  float4* xyz = nullptr;   // x y z pad
+  float4* nrm = nullptr;   // nx ny nz 0 (nullable)
+};
+
+struct GridDesc {
+  float ox, oy, oz;        // origin (bbox min of the centred reference)
+  float cell, inv_cell;
+  float slack;             // conservative bound on fp32 cell-assignment / bound-evaluation error (see knn.cu)
+  int nx, ny, nz;
+};
+
+struct b200reg_index {
+  int64_t m = 0;
+  float4* pts = nullptr;       // sorted by cell: x y z (centred) + original index bits in .w
+  float4* nrm = nullptr;       // sorted normals (nullable)
+  uint32_t* cellStart = nullptr;   // numCells + 1
+  GridDesc g{};
+  float mean[3] = {0, 0, 0};   // subtracted reference mean (0 if built un-centred)
+  double build_ms = 0;
+};
+
+int setErr(b200reg_ctx* ctx, int code, const char* fmt, ...);
+int ensureBuf(b200reg_ctx* ctx, DevBuf& b, size_t bytes);
+int ensurePinned(b200reg_ctx* ctx, size_t bytes);
+
+#define CUDA_TRY(ctx, expr)                                                                         \
+  do {                                                                                              \
+    cudaError_t _e = (expr);                                                                        \
+    if (_e != cudaSuccess)                                                                          \
+      return setErr((ctx), (_e == cudaErrorMemoryAllocation) ? B200REG_E_OOM : B200REG_E_CUDA,      \
+                    "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__, __LINE__);    \
+  } while (0)
+
+#define LAUNCH_CHECK(ctx)                  \
+  do {                                     \
+    (ctx)->launches++;                     \
+    CUDA_TRY((ctx), cudaGetLastError());   \
+  } while (0)
+
+#define TRY(expr)                 \
+  do {                            \
+    int _s = (expr);              \
+    if (_s != B200REG_OK) return _s; \
+  } while (0)
+
+static inline int divUp(int64_t a, int64_t b) { return (int)((a + b - 1) / b); }
+
+// fp32 arithmetic with every operation individually rounded (no FMA contraction) — SURVEY 9.1 contract.
+__device__ __forceinline__ float dist2_rn(float qx, float qy, float qz, float px, float py, float pz) {
+  const float dx = __fsub_rn(qx, px), dy = __fsub_rn(qy, py), dz = __fsub_rn(qz, pz);
+  return __fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz));
+}
+
+struct Rigid12 {   // rows 0..2 of a 4x4 (row-major)
+  float m[12];
+};
+
+// features <- T * features, depth accumulated k = 0..3 without FMA (TransformationsImpl.cpp:79 under the SURVEY 9.1 contract)
+__device__ __forceinline__ float3 xformPoint(const Rigid12& T, float x, float y, float z, float w) {
+  float3 r;
+  r.x = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(T.m[0], x), __fmul_rn(T.m[1], y)), __fmul_rn(T.m[2], z)), __fmul_rn(T.m[3], w));
+  r.y = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(T.m[4], x), __fmul_rn(T.m[5], y)), __fmul_rn(T.m[6], z)), __fmul_rn(T.m[7], w));
+  r.z = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(T.m[8], x), __fmul_rn(T.m[9], y)), __fmul_rn(T.m[10], z)), __fmul_rn(T.m[11], w));
+  return r;
+}
+__device__ __forceinline__ float3 xformNormal(const Rigid12& T, float x, float y, float z) {
+  float3 r;
+  r.x = __fadd_rn(__fadd_rn(__fmul_rn(T.m[0], x), __fmul_rn(T.m[1], y)), __fmul_rn(T.m[2], z));
+  r.y = __fadd_rn(__fadd_rn(__fmul_rn(T.m[4], x), __fmul_rn(T.m[5], y)), __fmul_rn(T.m[6], z));
+  r.z = __fadd_rn(__fadd_rn(__fmul_rn(T.m[8], x), __fmul_rn(T.m[9], y)), __fmul_rn(T.m[10], z));
+  return r;
+}

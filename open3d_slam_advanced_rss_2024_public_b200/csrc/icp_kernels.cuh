@@ -1,0 +1,207 @@
+// csrc/icp_kernels.cuh — device kernels of one ICP iteration after the match:
+//   (1) radix select of the trimmed-distance limit  (Matches::getDistsQuantile, Matches.cpp:61-87)
+//   (2) fused outlier gates + ErrorElements statistics + point-to-plane moment reduction (fp64)
+//       (OutlierFiltersImpl.cpp:140-147,226-281; ErrorMinimizer.cpp:59-140; PointToPlane.cpp:107-156,263-268)
+#pragma once
+#include "common.cuh"
+
+// ---- device state block layout (ctx->dstate, 64 KB) -------------------------------------------------------------
+struct SelState {
+  unsigned prefix;     // selected high digits so far
+  unsigned rank;       // remaining rank inside the selected bucket
+  unsigned nFinite;    // finite matches
+  unsigned tauBits;    // result: bit pattern of the limit
+  unsigned ticket[4];  // last-block tickets (3 select passes + reduce)
+  int error;           // 1: no finite match
+  int pad[7];
+};
+#define DSTATE_VISITS_OFF 0
+#define DSTATE_SEL_OFF 64
+#define DSTATE_HIST_OFF 256              /* 2048 x uint32 */
+#define DSTATE_RESULT_OFF (256 + 8192)   /* NUM_MOM doubles */
+
+#define NUM_MOM 36
+// moment slots
+enum {
+  M_CNT = 0, M_VALID = 1,
+  M_R = 2,      // sum r (3)
+  M_S = 5,      // sum s (3)
+  M_UU = 8,     // sum u u^T: xx xy xz yy yz zz (6)
+  M_UN = 14,    // sum u n^T row-major (9)
+  M_NN = 23,    // sum n n^T: xx xy xz yy yz zz (6)
+  M_UE = 29,    // sum u e (3)
+  M_NE = 32,    // sum n e (3)
+  M_SPARE = 35
+};
+
+// pass 0: digit = bits[31:21]; pass 1: bits[20:10]; pass 2: bits[9:0].  Values are non-negative floats, so the
+// uint32 order of the bit patterns is the float order.  The last block to finish picks the bucket.
+template <int PASS>
+__global__ void __launch_bounds__(256) selectPassKernel(const float* __restrict__ d2, int64_t count, float ratio, SelState* st,
+                                                        unsigned* __restrict__ hist) {
+  __shared__ unsigned sh[2048];
+  __shared__ unsigned scan[256];
+  __shared__ bool last;
+  constexpr int NB = (PASS == 2) ? 1024 : 2048;
+  for (int b = threadIdx.x; b < NB; b += blockDim.x) sh[b] = 0;
+  __syncthreads();
+  const unsigned prefix = (PASS == 0) ? 0u : st->prefix;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < count; i += (int64_t)gridDim.x * blockDim.x) {
+    const unsigned v = __float_as_uint(d2[i]);
+    if (v == 0x7f800000u) continue;   // dists != inf (Matches.cpp:70)
+    if (PASS == 0) atomicAdd(&sh[v >> 21], 1u);
+    else if (PASS == 1) { if ((v >> 21) == prefix) atomicAdd(&sh[(v >> 10) & 0x7ffu], 1u); }
+    else { if ((v >> 10) == prefix) atomicAdd(&sh[v & 0x3ffu], 1u); }
+  }
+  __syncthreads();
+  for (int b = threadIdx.x; b < NB; b += blockDim.x)
+    if (sh[b]) atomicAdd(&hist[b], sh[b]);
+  __threadfence();
+  if (threadIdx.x == 0) last = (atomicAdd(&st->ticket[PASS], 1u) == gridDim.x - 1);
+  __syncthreads();
+  if (!last) return;
+  __threadfence();
+  // ---- finalisation by the last block: find the bucket holding the wanted rank
+  constexpr int PER = NB / 256;
+  unsigned local[PER];
+  unsigned sum = 0;
+  for (int j = 0; j < PER; ++j) { local[j] = __ldcg(&hist[threadIdx.x * PER + j]); sum += local[j]; }
+  scan[threadIdx.x] = sum;
+  __syncthreads();
+  for (int o = 1; o < 256; o <<= 1) {   // inclusive Hillis-Steele scan
+    unsigned v = (threadIdx.x >= o) ? scan[threadIdx.x - o] : 0u;
+    __syncthreads();
+    scan[threadIdx.x] += v;
+    __syncthreads();
+  }
+  __shared__ unsigned sRank;
+  if (threadIdx.x == 0) {
+    unsigned rank = st->rank;
+    if (PASS == 0) {
+      const unsigned nF = scan[255];
+      st->nFinite = nF;
+      st->error = (nF == 0) ? 1 : 0;
+      if (nF > 0) {
+        // rank = size_t(float(n) * quantile) — float multiply + truncation (Matches.cpp:85); quantile 1 -> max (:83)
+        rank = (ratio == 1.0f) ? nF - 1 : (unsigned)__fmul_rn((float)nF, ratio);
+        if (rank > nF - 1) rank = nF - 1;
+      } else rank = 0;
+    }
+    sRank = rank;
+  }
+  __syncthreads();
+  const unsigned rank = sRank;
+  const unsigned incl = scan[threadIdx.x], excl = incl - sum;
+  if (rank >= excl && rank < incl) {   // exactly one thread (when nFinite > 0)
+    unsigned acc = excl;
+    for (int j = 0; j < PER; ++j) {
+      if (rank < acc + local[j]) {
+        const unsigned digit = threadIdx.x * PER + j;
+        if (PASS == 0) st->prefix = digit;
+        else if (PASS == 1) st->prefix = (prefix << 11) | digit;
+        else st->tauBits = (prefix << 10) | digit;
+        st->rank = rank - acc;
+        break;
+      }
+      acc += local[j];
+    }
+  }
+  for (int b = threadIdx.x; b < 2048; b += blockDim.x) hist[b] = 0;   // ready for the next pass / next iteration
+  if (threadIdx.x == 0) st->ticket[PASS] = 0;
+}
+
+struct ReduceParams {
+  const float4* reading;       // pre-iteration reading (already in the refMean frame)
+  const float4* readingNrm;    // nullable
+  const float4* refPts;        // sorted reference points
+  const float4* refNrm;        // sorted reference normals
+  const int* ids;
+  const float* d2;
+  const int* pos;
+  int64_t n;
+  int k;
+  int hasT;
+  Rigid12 T;
+  int useTrim;
+  int useAngle;
+  float cosAngle;              // eps = cos(maxAngle) in float (OutlierFiltersImpl.cpp:228)
+  int force2D;
+};
+
+__device__ __forceinline__ double warpSum(double v) {
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+// One thread per (reading point, neighbour slot).  Weights are binary and act only through compaction — exactly the
+// fork's A = G G^T, b = -G h^T (PointToPlane.cpp:153-155).  Moments are un-centred; the host applies the matched-mean
+// centring of PointToPlane.cpp:263-268 algebraically.
+__global__ void __launch_bounds__(256) reduceKernel(ReduceParams P, const SelState* __restrict__ st, double* __restrict__ partials,
+                                                    unsigned* ticket, double* __restrict__ result) {
+  double m[NUM_MOM];
+#pragma unroll
+  for (int j = 0; j < NUM_MOM; ++j) m[j] = 0.0;
+  const float tau = P.useTrim ? __uint_as_float(st->tauBits) : CUDART_INF_F;
+  const int64_t total = P.n * P.k;
+  for (int64_t o = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; o < total; o += (int64_t)gridDim.x * blockDim.x) {
+    const float d = P.d2[o];
+    if (d == CUDART_INF_F) continue;          // ErrorMinimizer.cpp:103-106
+    m[M_VALID] += 1.0;
+    if (P.useTrim && !(d <= tau)) continue;   // OutlierFiltersImpl.cpp:146
+    const int64_t i = o / P.k;
+    const int pos = P.pos[o];
+    if (pos < 0) continue;
+    const float4 q4 = P.reading[i];
+    float3 r = make_float3(q4.x, q4.y, q4.z);
+    if (P.hasT) r = xformPoint(P.T, q4.x, q4.y, q4.z, q4.w);
+    const float4 nn4 = P.refNrm[pos];
+    if (P.useAngle && P.readingNrm) {          // OutlierFiltersImpl.cpp:259-264
+      const float4 a4 = P.readingNrm[i];
+      float3 a = make_float3(a4.x, a4.y, a4.z);
+      if (P.hasT) a = xformNormal(P.T, a4.x, a4.y, a4.z);
+      const float dot = __fadd_rn(__fadd_rn(__fmul_rn(a.x, nn4.x), __fmul_rn(a.y, nn4.y)), __fmul_rn(a.z, nn4.z));
+      if (dot < P.cosAngle) continue;
+    }
+    const float4 s4 = P.refPts[pos];
+    double rx = r.x, ry = r.y, rz = r.z, sx = s4.x, sy = s4.y, sz = s4.z, nx = nn4.x, ny = nn4.y, nz = nn4.z;
+    if (P.force2D) { rz = 0.0; sz = 0.0; nz = 0.0; }
+    const double ux = ry * nz - rz * ny, uy = rz * nx - rx * nz, uz = rx * ny - ry * nx;   // u = r x n
+    const double e = (rx - sx) * nx + (ry - sy) * ny + (rz - sz) * nz;
+    m[M_CNT] += 1.0;
+    m[M_R] += rx; m[M_R + 1] += ry; m[M_R + 2] += rz;
+    m[M_S] += sx; m[M_S + 1] += sy; m[M_S + 2] += sz;
+    m[M_UU] += ux * ux; m[M_UU + 1] += ux * uy; m[M_UU + 2] += ux * uz; m[M_UU + 3] += uy * uy; m[M_UU + 4] += uy * uz; m[M_UU + 5] += uz * uz;
+    m[M_UN] += ux * nx; m[M_UN + 1] += ux * ny; m[M_UN + 2] += ux * nz;
+    m[M_UN + 3] += uy * nx; m[M_UN + 4] += uy * ny; m[M_UN + 5] += uy * nz;
+    m[M_UN + 6] += uz * nx; m[M_UN + 7] += uz * ny; m[M_UN + 8] += uz * nz;
+    m[M_NN] += nx * nx; m[M_NN + 1] += nx * ny; m[M_NN + 2] += nx * nz; m[M_NN + 3] += ny * ny; m[M_NN + 4] += ny * nz; m[M_NN + 5] += nz * nz;
+    m[M_UE] += ux * e; m[M_UE + 1] += uy * e; m[M_UE + 2] += uz * e;
+    m[M_NE] += nx * e; m[M_NE + 1] += ny * e; m[M_NE + 2] += nz * e;
+  }
+  // warp shuffle -> block tree (shared) -> per-block partial; the last block adds the partials in fixed order
+  __shared__ double sm[8][NUM_MOM];
+  __shared__ bool last;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+#pragma unroll
+  for (int j = 0; j < NUM_MOM; ++j) {
+    const double v = warpSum(m[j]);
+    if (lane == 0) sm[warp][j] = v;
+  }
+  __syncthreads();
+  if (threadIdx.x < NUM_MOM) {
+    double v = 0.0;
+    for (int w = 0; w < 8; ++w) v += sm[w][threadIdx.x];
+    partials[(size_t)blockIdx.x * NUM_MOM + threadIdx.x] = v;
+  }
+  __threadfence();
+  if (threadIdx.x == 0) last = (atomicAdd(ticket, 1u) == gridDim.x - 1);
+  __syncthreads();
+  if (!last) return;
+  __threadfence();
+  if (threadIdx.x < NUM_MOM) {
+    double v = 0.0;
+    for (unsigned b = 0; b < gridDim.x; ++b) v += __ldcg(&partials[(size_t)b * NUM_MOM + threadIdx.x]);
+    result[threadIdx.x] = v;
+  }
+  if (threadIdx.x == 0) *ticket = 0;
+}

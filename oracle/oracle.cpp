@@ -437,7 +437,8 @@ struct FullPivQR {
       pivots[k] = std::fabs(R[(size_t)k * n + k]);
       maxpivot = std::max(maxpivot, pivots[k]);
     }
-    const S thr = std::numeric_limits<S>::epsilon() * S(n) * maxpivot;
+    // threshold in the reference's scalar T = float in BOTH precisions (the rank decision is part of the contract)
+    const S thr = (S)std::numeric_limits<float>::epsilon() * S(n) * maxpivot;
     for (int k = 0; k < n; ++k)
       if (pivots[k] > thr) ++rank;
     invertible = (rank == n);
