@@ -51,6 +51,11 @@ int32_t b200reg_ctx_sync(b200reg_ctx* ctx);
 /* number of kernels this ctx has launched since creation (bench.py "gpu_launches") */
 uint64_t b200reg_ctx_launch_count(const b200reg_ctx* ctx);
 
+/* measurement helpers (bench.py): CUDA-event timer on the ctx stream, and an L2 flush (writes a buffer larger than L2) */
+int32_t b200reg_ctx_timer_start(b200reg_ctx* ctx);
+int32_t b200reg_ctx_timer_stop(b200reg_ctx* ctx, float* elapsed_ms);   /* synchronises on the stop event */
+int32_t b200reg_ctx_flush_l2(b200reg_ctx* ctx);
+
 /* ---- clouds: replaces DataPoints construction/copies (PointMatcher.h:229-431) and open3dToPointmatcher
  *      (open3d_slam_rsl/open3d_utils/open3d_conversions/src/open3d_conversions.cpp:21-118) -------------------------- */
 int32_t b200reg_cloud_upload_f32(b200reg_ctx* ctx, const float* feat, int32_t feat_stride, const float* normals, int64_t n,

@@ -87,6 +87,9 @@ SYMBOLS = {
     "b200reg_last_error": (C.c_char_p, [_VP]),
     "b200reg_ctx_sync": (C.c_int32, [_VP]),
     "b200reg_ctx_launch_count": (C.c_uint64, [_VP]),
+    "b200reg_ctx_timer_start": (C.c_int32, [_VP]),
+    "b200reg_ctx_timer_stop": (C.c_int32, [_VP, C.POINTER(C.c_float)]),
+    "b200reg_ctx_flush_l2": (C.c_int32, [_VP]),
     "b200reg_cloud_upload_f32": (C.c_int32, [_VP, _VP, C.c_int32, _VP, C.c_int64, C.POINTER(_VP)]),
     "b200reg_cloud_upload_f64": (C.c_int32, [_VP, _VP, _VP, C.c_int64, C.POINTER(_VP)]),
     "b200reg_cloud_download_f32": (C.c_int32, [_VP, _VP, _VP, C.c_int32, _VP]),
@@ -182,6 +185,17 @@ class Context:
 
     def sync(self):
         self.check(lib().b200reg_ctx_sync(self.h))
+
+    def timer_start(self):
+        self.check(lib().b200reg_ctx_timer_start(self.h))
+
+    def timer_stop(self):
+        ms = C.c_float(0)
+        self.check(lib().b200reg_ctx_timer_stop(self.h, C.byref(ms)))
+        return ms.value
+
+    def flush_l2(self):
+        self.check(lib().b200reg_ctx_flush_l2(self.h))
 
     @property
     def launch_count(self):

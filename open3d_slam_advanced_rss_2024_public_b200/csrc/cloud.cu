@@ -108,6 +108,8 @@ int32_t b200reg_ctx_create(int32_t device, b200reg_ctx** out) {
   if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess) { delete ctx; return B200REG_E_CUDA; }
   cudaEventCreate(&ctx->ev0);
   cudaEventCreate(&ctx->ev1);
+  cudaEventCreate(&ctx->tev0);
+  cudaEventCreate(&ctx->tev1);
   if (cudaMalloc(&ctx->dstate, 65536) != cudaSuccess) { delete ctx; return B200REG_E_OOM; }
   cudaMemsetAsync(ctx->dstate, 0, 65536, ctx->stream);
   if (ensurePinned(ctx, 1 << 16) != B200REG_OK) { delete ctx; return B200REG_E_OOM; }
@@ -120,13 +122,15 @@ void b200reg_ctx_destroy(b200reg_ctx* ctx) {
   cudaSetDevice(ctx->device);
   cudaStreamSynchronize(ctx->stream);
   DevBuf* bufs[] = {&ctx->keys0, &ctx->keys1, &ctx->vals0, &ctx->vals1, &ctx->cubtmp, &ctx->misc, &ctx->partials,
-                    &ctx->matchIds, &ctx->matchD2, &ctx->matchPos, &ctx->flags};
+                    &ctx->matchIds, &ctx->matchD2, &ctx->matchPos, &ctx->flags, &ctx->flush};
   for (DevBuf* b : bufs)
     if (b->p) cudaFree(b->p);
   if (ctx->pinned) cudaFreeHost(ctx->pinned);
   if (ctx->dstate) cudaFree(ctx->dstate);
   cudaEventDestroy(ctx->ev0);
   cudaEventDestroy(ctx->ev1);
+  cudaEventDestroy(ctx->tev0);
+  cudaEventDestroy(ctx->tev1);
   cudaStreamDestroy(ctx->stream);
   delete ctx;
 }
@@ -140,6 +144,32 @@ int32_t b200reg_ctx_sync(b200reg_ctx* ctx) {
 }
 
 uint64_t b200reg_ctx_launch_count(const b200reg_ctx* ctx) { return ctx ? ctx->launches : 0; }
+
+int32_t b200reg_ctx_timer_start(b200reg_ctx* ctx) {
+  if (!ctx) return B200REG_E_INVALID_PARAM;
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  CUDA_TRY(ctx, cudaEventRecord(ctx->tev0, ctx->stream));
+  return B200REG_OK;
+}
+
+int32_t b200reg_ctx_timer_stop(b200reg_ctx* ctx, float* elapsed_ms) {
+  if (!ctx || !elapsed_ms) return B200REG_E_INVALID_PARAM;
+  CUDA_TRY(ctx, cudaEventRecord(ctx->tev1, ctx->stream));
+  CUDA_TRY(ctx, cudaEventSynchronize(ctx->tev1));
+  CUDA_TRY(ctx, cudaEventElapsedTime(elapsed_ms, ctx->tev0, ctx->tev1));
+  return B200REG_OK;
+}
+
+int32_t b200reg_ctx_flush_l2(b200reg_ctx* ctx) {
+  if (!ctx) return B200REG_E_INVALID_PARAM;
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  const size_t bytes = (size_t)256 << 20;   // > 126 MB L2
+  TRY(ensureBuf(ctx, ctx->flush, bytes));
+  ctx->flushToggle ^= 1;
+  CUDA_TRY(ctx, cudaMemsetAsync(ctx->flush.p, ctx->flushToggle, bytes, ctx->stream));
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  return B200REG_OK;
+}
 
 static int allocCloud(b200reg_ctx* ctx, int64_t n, bool normals, b200reg_cloud** out) {
   b200reg_cloud* c = new b200reg_cloud();

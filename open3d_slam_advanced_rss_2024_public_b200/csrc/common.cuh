@@ -21,12 +21,13 @@ struct DevBuf {   // growable device scratch (never shrinks; freed with the ctx)
 struct b200reg_ctx {
   int device = 0;
   cudaStream_t stream = nullptr;
-  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr, tev0 = nullptr, tev1 = nullptr;
   int sm_count = B200_SM_COUNT;
   char err[512] = {0};
   uint64_t launches = 0;
   // scratch
-  DevBuf keys0, keys1, vals0, vals1, cubtmp, misc, partials, matchIds, matchD2, matchPos, flags;
+  DevBuf keys0, keys1, vals0, vals1, cubtmp, misc, partials, matchIds, matchD2, matchPos, flags, flush;
+  int flushToggle = 0;
   void* pinned = nullptr;   // pinned host staging for small D2H results
   size_t pinned_cap = 0;
   void* dstate = nullptr;   // small device state block (select state, counters)

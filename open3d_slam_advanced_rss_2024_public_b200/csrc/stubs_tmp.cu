@@ -1,7 +1,6 @@
 // TEMPORARY: entry points not implemented yet (replaced by filters.cu / map.cu)
 #include "common.cuh"
 extern "C" {
-int32_t b200reg_voxelgrid(b200reg_ctx* ctx, b200reg_cloud*, float, float, float, int32_t, int32_t) { return setErr(ctx, B200REG_E_INVALID_PARAM, "not implemented"); }
 int32_t b200reg_surface_normals(b200reg_ctx* ctx, b200reg_cloud*, int32_t, float, float, const float*, float*, float*, float*, int32_t*) { return setErr(ctx, B200REG_E_INVALID_PARAM, "not implemented"); }
 int32_t b200reg_map_create(b200reg_ctx* ctx, double, b200reg_map**) { return setErr(ctx, B200REG_E_INVALID_PARAM, "not implemented"); }
 void b200reg_map_destroy(b200reg_ctx*, b200reg_map*) {}

@@ -821,33 +821,65 @@ double nowSec() {
 
 }  // namespace
 
-extern "C" int32_t orc_icp(const orc_icp_config* cfg, const float* ref_feat, int32_t ref_stride, const float* ref_normals, int64_t m,
-                           const float* read_feat, int32_t read_stride, const float* read_normals, int64_t n,
-                           const float T_init[16], float T_out[16], orc_icp_stats* stats) {
-  orc_icp_stats st;
-  std::memset(&st, 0, sizeof(st));
-  auto finish = [&](int code) { st.status = code; if (stats) *stats = st; return code; };
-  if (m == 0) return finish(ORC_E_EMPTY);
-  const double t0 = nowSec();
+namespace {
+struct IcpRef {   // state kept by ICP::initReference: referenceFiltered (centred), T_refIn_refMean, the matcher's tree
+  std::vector<float> ref;
+  std::vector<float> normals;
+  bool hasNormals = false;
+  int64_t m = 0;
+  float mean[3] = {0, 0, 0};
+  void* tree = nullptr;
+  double t_reference_s = 0;
+};
+}  // namespace
 
-  // ---- initReference (ICP.cpp:293-328): copy, (no reference filters here), mean, centre, matcher->init
-  std::vector<float> ref(4 * (size_t)m);
+// ICP::initReference (ICP.cpp:293-328): copy, (no reference filters here), mean, centre, matcher->init
+extern "C" void* orc_icp_ref_create(const orc_icp_config* cfg, const float* ref_feat, int32_t ref_stride, const float* ref_normals, int64_t m) {
+  if (m == 0) return nullptr;
+  const double t0 = nowSec();
+  IcpRef* R = new IcpRef();
+  R->m = m;
+  R->ref.resize(4 * (size_t)m);
   double sum[3] = {0, 0, 0};
   for (int64_t i = 0; i < m; ++i) {
-    for (int d = 0; d < 3; ++d) { ref[4 * i + d] = ref_feat[i * ref_stride + d]; sum[d] += ref[4 * i + d]; }
-    ref[4 * i + 3] = 1.f;
+    for (int d = 0; d < 3; ++d) { R->ref[4 * i + d] = ref_feat[i * ref_stride + d]; sum[d] += R->ref[4 * i + d]; }
+    R->ref[4 * i + 3] = 1.f;
   }
   // meanReference = features.rowwise().mean() (:313).  Eigen's fp32 reduction order is unspecified; the contract is the
   // fp64 sum rounded once to fp32.
-  float mean[3];
-  for (int d = 0; d < 3; ++d) { mean[d] = (float)(sum[d] / (double)m); st.mean_ref[d] = mean[d]; }
+  for (int d = 0; d < 3; ++d) R->mean[d] = (float)(sum[d] / (double)m);
   for (int64_t i = 0; i < m; ++i)
-    for (int d = 0; d < 3; ++d) ref[4 * i + d] = ref[4 * i + d] - mean[d];   // :320
+    for (int d = 0; d < 3; ++d) R->ref[4 * i + d] = R->ref[4 * i + d] - R->mean[d];   // :320
+  if (ref_normals) { R->normals.assign(ref_normals, ref_normals + 3 * (size_t)m); R->hasNormals = true; }
+  if (cfg->matcher_kind == 0) R->tree = orc_kdtree_build(R->ref.data(), 4, m);
+  R->t_reference_s = nowSec() - t0;
+  return R;
+}
+
+extern "C" void orc_icp_ref_free(void* h) {
+  IcpRef* R = (IcpRef*)h;
+  if (!R) return;
+  if (R->tree) orc_kdtree_free(R->tree);
+  delete R;
+}
+
+// ICP::computeWithTransformedReference (ICP.cpp:332-468) against a prepared reference
+extern "C" int32_t orc_icp_compute(const orc_icp_config* cfg, const void* refHandle, const float* read_feat, int32_t read_stride,
+                                   const float* read_normals, int64_t n, const float T_init[16], float T_out[16], orc_icp_stats* stats) {
+  orc_icp_stats st;
+  std::memset(&st, 0, sizeof(st));
+  auto finish = [&](int code) { st.status = code; if (stats) *stats = st; return code; };
+  const IcpRef* R = (const IcpRef*)refHandle;
+  if (!R) return finish(ORC_E_EMPTY);
+  const std::vector<float>& ref = R->ref;
+  const float* ref_normals = R->hasNormals ? R->normals.data() : nullptr;
+  const float* mean = R->mean;
+  void* tree = nullptr;            // owned by the handle; never freed here
+  const void* ctree = R->tree;
+  for (int d = 0; d < 3; ++d) st.mean_ref[d] = mean[d];
+  st.t_reference_s = R->t_reference_s;
   Mat4<float> T_refIn_refMean = Mat4<float>::identity();
   for (int d = 0; d < 3; ++d) T_refIn_refMean(d, 3) = mean[d];
-  void* tree = nullptr;
-  if (cfg->matcher_kind == 0) tree = orc_kdtree_build(ref.data(), 4, m);
-  st.t_reference_s = nowSec() - t0;
   const double t1 = nowSec();
 
   // ---- computeWithTransformedReference (ICP.cpp:332-468)
@@ -884,7 +916,7 @@ extern "C" int32_t orc_icp(const orc_icp_config* cfg, const float* ref_feat, int
     if (cfg->matcher_kind == 1) {                               // MirrorMatcher (MatchersImpl.cpp:65-84)
       for (int64_t i = 0; i < n; ++i) { ids[i] = (int32_t)i; d2[i] = 0.f; }
     } else {                                                    // :413
-      st.points_touched += orc_kdtree_knn(tree, step.data(), 4, n, k, cfg->max_dist, 1, ids.data(), d2.data(), cfg->nthreads);
+      st.points_touched += orc_kdtree_knn(ctree, step.data(), 4, n, k, cfg->max_dist, 1, ids.data(), d2.data(), cfg->nthreads);
     }
     // outlier filters (:417, OutlierFilter.cpp:64-103)
     bool any = false;
@@ -926,6 +958,20 @@ extern "C" int32_t orc_icp(const orc_icp_config* cfg, const float* ref_feat, int
   const Mat4<float> out = mul(T_refIn_refMean, mul(T_iter, T_refMean_readMean));
   std::memcpy(T_out, out.m, sizeof(out.m));
   return finish(ORC_OK);
+}
+
+// ICP::compute (ICP.cpp:258-290) = initReference + computeWithTransformedReference
+extern "C" int32_t orc_icp(const orc_icp_config* cfg, const float* ref_feat, int32_t ref_stride, const float* ref_normals, int64_t m,
+                           const float* read_feat, int32_t read_stride, const float* read_normals, int64_t n,
+                           const float T_init[16], float T_out[16], orc_icp_stats* stats) {
+  void* R = orc_icp_ref_create(cfg, ref_feat, ref_stride, ref_normals, m);
+  if (!R) {
+    if (stats) { std::memset(stats, 0, sizeof(*stats)); stats->status = ORC_E_EMPTY; }
+    return ORC_E_EMPTY;
+  }
+  const int32_t code = orc_icp_compute(cfg, R, read_feat, read_stride, read_normals, n, T_init, T_out, stats);
+  orc_icp_ref_free(R);
+  return code;
 }
 
 // ================================================================================================================

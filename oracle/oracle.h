@@ -89,6 +89,12 @@ int32_t orc_icp(const orc_icp_config* cfg, const float* ref_feat, int32_t ref_st
                 const float* read_feat, int32_t read_stride, const float* read_normals, int64_t n, const float T_init[16],
                 float T_out[16], orc_icp_stats* stats);
 
+/* the same, split the way Mapper uses it (Mapper.cpp:363,391-393): initReference once, compute many times */
+void*   orc_icp_ref_create(const orc_icp_config* cfg, const float* ref_feat, int32_t ref_stride, const float* ref_normals, int64_t m);
+void    orc_icp_ref_free(void* ref);
+int32_t orc_icp_compute(const orc_icp_config* cfg, const void* ref, const float* read_feat, int32_t read_stride,
+                        const float* read_normals, int64_t n, const float T_init[16], float T_out[16], orc_icp_stats* stats);
+
 /* ---- VoxelGridDataPointsFilter (VoxelGrid.cpp:71-344); in place, returns the number of points kept or <0 ---- */
 int64_t orc_voxelgrid(float* feat, int32_t stride, float* desc, int32_t desc_dim, int64_t n, float vx, float vy, float vz,
                       int32_t use_centroid, int32_t average_descriptors, uint32_t* cell_of_point_out /* nullable, n entries */);

@@ -47,6 +47,7 @@ def build(force=False):
 def lib():
     global _LIB
     if _LIB is None:
+        os.environ.setdefault("OMP_WAIT_POLICY", "passive")   # spinning workers starve each other on shared hosts
         _LIB = C.CDLL(build())
         L = _LIB
         L.orc_kdtree_build.restype = C.c_void_p
@@ -71,6 +72,12 @@ def lib():
         L.orc_icp.restype = C.c_int32
         L.orc_icp.argtypes = [C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_int64, C.c_void_p, C.c_int32, C.c_void_p,
                               C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.orc_icp_ref_create.restype = C.c_void_p
+        L.orc_icp_ref_create.argtypes = [C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_int64]
+        L.orc_icp_ref_free.argtypes = [C.c_void_p]
+        L.orc_icp_compute.restype = C.c_int32
+        L.orc_icp_compute.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_int64, C.c_void_p,
+                                      C.c_void_p, C.c_void_p]
         L.orc_voxelgrid.restype = C.c_int64
         L.orc_voxelgrid.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_int32, C.c_int64, C.c_float, C.c_float, C.c_float,
                                     C.c_int32, C.c_int32, C.c_void_p]
@@ -206,6 +213,30 @@ def icp(cfg, ref_feat, ref_normals, read_feat, read_normals=None, T_init=None):
     code = lib().orc_icp(C.byref(cfg), _p(ref_feat), ref_feat.shape[1], _p(ref_normals), ref_feat.shape[0], _p(read_feat),
                          read_feat.shape[1], _p(read_normals), read_feat.shape[0], _p(T_init.reshape(16)), _p(T), C.byref(st))
     return code, T.reshape(4, 4), st
+
+
+class IcpReference:
+    """ICP::initReference done once (Mapper.cpp:363), then compute() many times (Mapper.cpp:391-393)."""
+
+    def __init__(self, cfg, ref_feat, ref_normals):
+        self.cfg = cfg
+        ref_feat, ref_normals = _f32(ref_feat), _f32(ref_normals)
+        self.h = lib().orc_icp_ref_create(C.byref(cfg), _p(ref_feat), ref_feat.shape[1], _p(ref_normals), ref_feat.shape[0])
+
+    def compute(self, read_feat, read_normals=None, T_init=None, cfg=None):
+        cfg = self.cfg if cfg is None else cfg
+        read_feat, read_normals = _f32(read_feat), _f32(read_normals)
+        T_init = np.eye(4, dtype=np.float32) if T_init is None else _f32(T_init)
+        T = np.zeros(16, dtype=np.float32)
+        st = IcpStats()
+        code = lib().orc_icp_compute(C.byref(cfg), self.h, _p(read_feat), read_feat.shape[1], _p(read_normals),
+                                     read_feat.shape[0], _p(T_init.reshape(16)), _p(T), C.byref(st))
+        return code, T.reshape(4, 4), st
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            lib().orc_icp_ref_free(self.h)
+            self.h = None
 
 
 def voxelgrid(feat, desc, vx, vy, vz, use_centroid=True, average_descriptors=True):
