@@ -182,6 +182,7 @@ typedef struct b200reg_crop_spec {   /* CroppingVolume (open3d_slam/src/croppers
 int32_t b200reg_map_create(b200reg_ctx* ctx, double voxel_size, b200reg_map** out);
 void    b200reg_map_destroy(b200reg_ctx* ctx, b200reg_map* map);
 int64_t b200reg_map_size(const b200reg_map* map);
+int32_t b200reg_map_has_normals(const b200reg_map* map);
 /* Submap::insertScan (open3d_slam/src/Submap.cpp:39-96): transform (helpers.cpp:283-318), append, re-voxelise inside
  * `volume` (helpers.cpp:117-192).  scan_xyz / scan_nrm: HOST fp64 arrays (nrm nullable). */
 int32_t b200reg_map_insert(b200reg_ctx* ctx, b200reg_map* map, const double* scan_xyz, const double* scan_nrm, int64_t n,

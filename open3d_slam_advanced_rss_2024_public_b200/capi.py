@@ -115,6 +115,7 @@ SYMBOLS = {
     "b200reg_map_create": (C.c_int32, [_VP, C.c_double, C.POINTER(_VP)]),
     "b200reg_map_destroy": (None, [_VP, _VP]),
     "b200reg_map_size": (C.c_int64, [_VP]),
+    "b200reg_map_has_normals": (C.c_int32, [_VP]),
     "b200reg_map_insert": (C.c_int32, [_VP, _VP, _VP, _VP, C.c_int64, _VP, C.POINTER(CropSpec)]),
     "b200reg_map_crop": (C.c_int32, [_VP, _VP, C.POINTER(CropSpec), C.POINTER(_VP)]),
     "b200reg_map_download": (C.c_int32, [_VP, _VP, _VP, _VP]),
@@ -412,7 +413,7 @@ class VoxelMap:
     def download(self):
         n = self.size
         xyz = np.empty((n, 3), dtype=np.float64)
-        nrm = np.empty((n, 3), dtype=np.float64)
+        nrm = np.empty((n, 3), dtype=np.float64) if lib().b200reg_map_has_normals(self.h) else None
         self.ctx.check(lib().b200reg_map_download(self.ctx.h, self.h, _p(xyz), _p(nrm)))
         return xyz, nrm
 

@@ -1,0 +1,378 @@
+// csrc/map.cu — open3d_slam voxel-map crop / insert on the device, fp64 (paths relative to
+// /root/reference/open3d_slam_rsl/open3d_slam/open3d_slam/):
+//   CroppingVolume::isWithinVolume / crop        src/croppers.cpp:53-167
+//   o3d_slam::transform                          src/helpers.cpp:283-318
+//   Submap::insertScan                           src/Submap.cpp:39-96
+//   voxelizeWithinCroppingVolume                 src/helpers.cpp:117-192, key = int(floor(p * (1/v))) (VoxelHashMap.hpp:43-51)
+//   ScanToMapRegistration::cropSubmap            src/ScanToMapRegistration.cpp:90-96
+//
+// The map stays resident as plain fp64 SoA-of-3 arrays (a cloud of per-voxel means, exactly the reference's
+// `mapCloud_`).  Insert = transform + append + [predicate -> compaction of pass-through points | 63-bit key radix sort of
+// the points inside the volume -> one thread per voxel accumulates its points in ascending input order (the reference's
+// accumulation order, so means are bit-exact)].  Output order: pass-through points in input order, then voxels in
+// ascending (x,y,z) key order (the reference's is unordered_map order — implementation-defined).
+// Compiled with --fmad=false (each fp64 op individually rounded, like the oracle).
+#include <cub/device/device_radix_sort.cuh>
+#include <cub/device/device_scan.cuh>
+
+#include <cmath>
+
+#include "common.cuh"
+
+struct b200reg_map {
+  double voxel = 0.0;
+  int64_t n = 0, cap = 0;
+  double* xyz = nullptr;   // 3 doubles per point
+  double* nrm = nullptr;   // 3 doubles per point (allocated with xyz; valid iff hasNormals)
+  double* xyz2 = nullptr;  // double buffer for the rebuilt map
+  double* nrm2 = nullptr;
+  bool hasNormals = false;
+};
+
+namespace {
+
+typedef unsigned long long u64;
+
+__device__ __forceinline__ bool withinVolume(const b200reg_crop_spec& s, double x, double y, double z) {
+  const double dx = x - s.center[0], dy = y - s.center[1], dz = z - s.center[2];
+  bool in;
+  if (s.kind == B200REG_CROP_MAX_RADIUS) in = sqrt(dx * dx + dy * dy + dz * dz) <= s.rmax;
+  else if (s.kind == B200REG_CROP_MIN_RADIUS) in = sqrt(dx * dx + dy * dy + dz * dz) >= s.rmin;
+  else if (s.kind == B200REG_CROP_MINMAX_RADIUS) { const double d = sqrt(dx * dx + dy * dy + dz * dz); in = d <= s.rmax && d >= s.rmin; }
+  else in = z >= s.zmin && z <= s.zmax && sqrt(dx * dx + dy * dy) <= s.rmax;   // cylinder: absolute z range (croppers.cpp:166)
+  return s.invert ? !in : in;
+}
+
+// p' = (T [p;1]).head3 / w ; n' = (T [n;0]).head3   (helpers.cpp:296-309)
+__global__ void transformF64Kernel(const double* __restrict__ xyz, const double* __restrict__ nrm, int64_t n, const double* __restrict__ Tm,
+                                   double* __restrict__ oxyz, double* __restrict__ onrm) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  double T[16];
+  for (int j = 0; j < 16; ++j) T[j] = Tm[j];
+  const double x = xyz[3 * i], y = xyz[3 * i + 1], z = xyz[3 * i + 2];
+  double q[4];
+  for (int r = 0; r < 4; ++r) q[r] = ((T[4 * r] * x + T[4 * r + 1] * y) + T[4 * r + 2] * z) + T[4 * r + 3] * 1.0;
+  for (int r = 0; r < 3; ++r) oxyz[3 * i + r] = q[r] / q[3];
+  if (nrm && onrm) {
+    const double a = nrm[3 * i], b = nrm[3 * i + 1], c = nrm[3 * i + 2];
+    for (int r = 0; r < 3; ++r) onrm[3 * i + r] = ((T[4 * r] * a + T[4 * r + 1] * b) + T[4 * r + 2] * c) + T[4 * r + 3] * 0.0;
+  }
+}
+
+// inside flag (+ voxel key for inside points); outFlag = 1 - inside for the pass-through compaction
+__global__ void classifyKernel(const double* __restrict__ xyz, int64_t n, b200reg_crop_spec spec, double inv, unsigned* __restrict__ inFlag,
+                               unsigned* __restrict__ outFlag, u64* __restrict__ keys, int* __restrict__ err) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const double x = xyz[3 * i], y = xyz[3 * i + 1], z = xyz[3 * i + 2];
+  const bool in = withinVolume(spec, x, y, z);
+  inFlag[i] = in ? 1u : 0u;
+  if (outFlag) outFlag[i] = in ? 0u : 1u;
+  if (keys) {
+    u64 key = ~0ull;
+    if (in) {
+      const double fx = floor(x * inv), fy = floor(y * inv), fz = floor(z * inv);   // getVoxelIdx (VoxelHashMap.hpp:48-51)
+      const double lim = 1048575.0;
+      if (!(fabs(fx) <= lim) || !(fabs(fy) <= lim) || !(fabs(fz) <= lim)) { *err = 1; }
+      else key = ((u64)((long long)fx + 1048576ll) << 42) | ((u64)((long long)fy + 1048576ll) << 21) | (u64)((long long)fz + 1048576ll);
+    }
+    keys[i] = key;
+  }
+}
+
+__global__ void compactPairsKernel(const unsigned* __restrict__ inFlag, const unsigned* __restrict__ inOff, const u64* __restrict__ keys,
+                                   int64_t n, u64* __restrict__ ckeys, unsigned* __restrict__ cvals) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n || !inFlag[i]) return;
+  const unsigned o = inOff[i];
+  ckeys[o] = keys[i];
+  cvals[o] = (unsigned)i;
+}
+
+__global__ void headFlagKernel(const u64* __restrict__ skeys, int64_t m, unsigned* __restrict__ head) {
+  const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= m) return;
+  head[j] = (j == 0 || skeys[j] != skeys[j - 1]) ? 1u : 0u;
+}
+
+// AccumulatedPoint (helpers.cpp:30-73): one thread per voxel head walks the voxel's points in ascending input index
+__global__ void voxelReduceKernel(const u64* __restrict__ skeys, const unsigned* __restrict__ svals, const unsigned* __restrict__ head,
+                                  const unsigned* __restrict__ headOff, int64_t m, const double* __restrict__ xyz,
+                                  const double* __restrict__ nrm, int64_t outBase, double* __restrict__ oxyz, double* __restrict__ onrm) {
+  const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= m || !head[j]) return;
+  const u64 key = skeys[j];
+  double p[3] = {0, 0, 0}, a[3] = {0, 0, 0};
+  int cnt = 0;
+  for (int64_t t = j; t < m && skeys[t] == key; ++t) {
+    const unsigned i = svals[t];
+    p[0] += xyz[3 * (size_t)i]; p[1] += xyz[3 * (size_t)i + 1]; p[2] += xyz[3 * (size_t)i + 2];
+    if (nrm) {
+      const double nx = nrm[3 * (size_t)i], ny = nrm[3 * (size_t)i + 1], nz = nrm[3 * (size_t)i + 2];
+      if (!isnan(nx) && !isnan(ny) && !isnan(nz)) { a[0] += nx; a[1] += ny; a[2] += nz; }   // helpers.cpp:35-37
+    }
+    ++cnt;
+  }
+  const int64_t o = outBase + headOff[j];
+  const double c = (double)cnt;
+  oxyz[3 * o] = p[0] / c; oxyz[3 * o + 1] = p[1] / c; oxyz[3 * o + 2] = p[2] / c;
+  if (nrm && onrm) {
+    const double m0 = a[0] / c, m1 = a[1] / c, m2 = a[2] / c;
+    const double nn = sqrt(m0 * m0 + m1 * m1 + m2 * m2);   // .normalized() (helpers.cpp:181)
+    onrm[3 * o] = (nn > 0.0) ? m0 / nn : m0;
+    onrm[3 * o + 1] = (nn > 0.0) ? m1 / nn : m1;
+    onrm[3 * o + 2] = (nn > 0.0) ? m2 / nn : m2;
+  }
+}
+
+__global__ void scatterSelectedKernel(const unsigned* __restrict__ flag, const unsigned* __restrict__ off, int64_t n,
+                                      const double* __restrict__ xyz, const double* __restrict__ nrm, double* __restrict__ oxyz,
+                                      double* __restrict__ onrm) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n || !flag[i]) return;
+  const size_t o = off[i];
+  for (int d = 0; d < 3; ++d) oxyz[3 * o + d] = xyz[3 * (size_t)i + d];
+  if (nrm && onrm) for (int d = 0; d < 3; ++d) onrm[3 * o + d] = nrm[3 * (size_t)i + d];
+}
+
+// crop + open3dToPointmatcher (open3d_conversions.cpp:57-118): fp64 -> fp32 cloud, pad = 1
+__global__ void scatterSelectedF32Kernel(const unsigned* __restrict__ flag, const unsigned* __restrict__ off, int64_t n,
+                                         const double* __restrict__ xyz, const double* __restrict__ nrm, float4* __restrict__ oxyz,
+                                         float4* __restrict__ onrm) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n || !flag[i]) return;
+  const size_t o = off[i];
+  oxyz[o] = make_float4((float)xyz[3 * (size_t)i], (float)xyz[3 * (size_t)i + 1], (float)xyz[3 * (size_t)i + 2], 1.f);
+  if (nrm && onrm) onrm[o] = make_float4((float)nrm[3 * (size_t)i], (float)nrm[3 * (size_t)i + 1], (float)nrm[3 * (size_t)i + 2], 0.f);
+}
+
+int scanFlags(b200reg_ctx* ctx, const unsigned* flags, unsigned* offs, int64_t n) {
+  size_t tmp = 0;
+  CUDA_TRY(ctx, cub::DeviceScan::ExclusiveSum(nullptr, tmp, flags, offs, (int)n, ctx->stream));
+  TRY(ensureBuf(ctx, ctx->cubtmp, tmp));
+  tmp = ctx->cubtmp.cap;
+  CUDA_TRY(ctx, cub::DeviceScan::ExclusiveSum(ctx->cubtmp.p, tmp, flags, offs, (int)n, ctx->stream));
+  ctx->launches += 2;
+  return B200REG_OK;
+}
+
+// total of an exclusive scan: offs[n-1] + flags[n-1] (synchronises)
+int scanTotal(b200reg_ctx* ctx, const unsigned* flags, const unsigned* offs, int64_t n, int64_t* total) {
+  unsigned* h = (unsigned*)ctx->pinned;
+  CUDA_TRY(ctx, cudaMemcpyAsync(h, offs + (n - 1), sizeof(unsigned), cudaMemcpyDeviceToHost, ctx->stream));
+  CUDA_TRY(ctx, cudaMemcpyAsync(h + 1, flags + (n - 1), sizeof(unsigned), cudaMemcpyDeviceToHost, ctx->stream));
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  *total = (int64_t)h[0] + (int64_t)h[1];
+  return B200REG_OK;
+}
+
+int mapReserve(b200reg_ctx* ctx, b200reg_map* map, int64_t want) {
+  if (want <= map->cap) return B200REG_OK;
+  const int64_t cap = want + want / 2 + 1024;
+  double* nx = nullptr; double* nn = nullptr; double* nx2 = nullptr; double* nn2 = nullptr;
+  cudaError_t e = cudaMalloc(&nx, sizeof(double) * 3 * (size_t)cap);
+  if (e == cudaSuccess) e = cudaMalloc(&nn, sizeof(double) * 3 * (size_t)cap);
+  if (e == cudaSuccess) e = cudaMalloc(&nx2, sizeof(double) * 3 * (size_t)cap);
+  if (e == cudaSuccess) e = cudaMalloc(&nn2, sizeof(double) * 3 * (size_t)cap);
+  if (e != cudaSuccess) {
+    cudaFree(nx); cudaFree(nn); cudaFree(nx2); cudaFree(nn2);
+    return setErr(ctx, B200REG_E_OOM, "map: cannot reserve %lld points: %s", (long long)cap, cudaGetErrorString(e));
+  }
+  if (map->n > 0) {
+    CUDA_TRY(ctx, cudaMemcpyAsync(nx, map->xyz, sizeof(double) * 3 * (size_t)map->n, cudaMemcpyDeviceToDevice, ctx->stream));
+    CUDA_TRY(ctx, cudaMemcpyAsync(nn, map->nrm, sizeof(double) * 3 * (size_t)map->n, cudaMemcpyDeviceToDevice, ctx->stream));
+  }
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  cudaFree(map->xyz); cudaFree(map->nrm); cudaFree(map->xyz2); cudaFree(map->nrm2);
+  map->xyz = nx; map->nrm = nn; map->xyz2 = nx2; map->nrm2 = nn2;
+  map->cap = cap;
+  return B200REG_OK;
+}
+
+// voxelizeWithinCroppingVolume over `total` points of (xyz,nrm) -> (oxyz,onrm); returns the new size
+int revoxelize(b200reg_ctx* ctx, double voxel, const b200reg_crop_spec& spec, const double* xyz, const double* nrm, int64_t total,
+               double* oxyz, double* onrm, int64_t* newSize) {
+  const size_t u4 = sizeof(unsigned) * (size_t)total, k8 = sizeof(u64) * (size_t)total;
+  TRY(ensureBuf(ctx, ctx->flags, 6 * u4 + 64));
+  unsigned* inFlag = (unsigned*)ctx->flags.p;
+  unsigned* outFlag = inFlag + total;
+  unsigned* inOff = outFlag + total;
+  unsigned* outOff = inOff + total;
+  unsigned* head = outOff + total;
+  unsigned* headOff = head + total;
+  TRY(ensureBuf(ctx, ctx->keys0, k8));
+  TRY(ensureBuf(ctx, ctx->keys1, k8));
+  TRY(ensureBuf(ctx, ctx->vals0, u4));
+  TRY(ensureBuf(ctx, ctx->vals1, u4));
+  TRY(ensureBuf(ctx, ctx->misc, k8));
+  u64* keysAll = (u64*)ctx->misc.p;
+  int* dErr = (int*)((char*)ctx->dstate + 32768 + 64);
+  CUDA_TRY(ctx, cudaMemsetAsync(dErr, 0, sizeof(int), ctx->stream));
+  classifyKernel<<<divUp(total, 256), 256, 0, ctx->stream>>>(xyz, total, spec, 1.0 / voxel, inFlag, outFlag, keysAll, dErr);
+  LAUNCH_CHECK(ctx);
+  TRY(scanFlags(ctx, inFlag, inOff, total));
+  TRY(scanFlags(ctx, outFlag, outOff, total));
+  int64_t nIn = 0, nOut = 0;
+  TRY(scanTotal(ctx, inFlag, inOff, total, &nIn));
+  nOut = total - nIn;
+  CUDA_TRY(ctx, cudaMemcpyAsync(ctx->pinned, dErr, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  if (*(const int*)ctx->pinned) return setErr(ctx, B200REG_E_INVALID_PARAM, "map: voxel index outside +-2^20 (voxel size too small for the map extent)");
+  // pass-through points first, in input order (helpers.cpp:162-174)
+  scatterSelectedKernel<<<divUp(total, 256), 256, 0, ctx->stream>>>(outFlag, outOff, total, xyz, nrm, oxyz, onrm);
+  LAUNCH_CHECK(ctx);
+  int64_t nVox = 0;
+  if (nIn > 0) {
+    compactPairsKernel<<<divUp(total, 256), 256, 0, ctx->stream>>>(inFlag, inOff, keysAll, total, (u64*)ctx->keys0.p, (unsigned*)ctx->vals0.p);
+    LAUNCH_CHECK(ctx);
+    cub::DoubleBuffer<u64> dk((u64*)ctx->keys0.p, (u64*)ctx->keys1.p);
+    cub::DoubleBuffer<unsigned> dv((unsigned*)ctx->vals0.p, (unsigned*)ctx->vals1.p);
+    size_t tmp = 0;
+    CUDA_TRY(ctx, cub::DeviceRadixSort::SortPairs(nullptr, tmp, dk, dv, (int)nIn, 0, 63, ctx->stream));
+    TRY(ensureBuf(ctx, ctx->cubtmp, tmp));
+    tmp = ctx->cubtmp.cap;
+    CUDA_TRY(ctx, cub::DeviceRadixSort::SortPairs(ctx->cubtmp.p, tmp, dk, dv, (int)nIn, 0, 63, ctx->stream));
+    ctx->launches += 9;
+    headFlagKernel<<<divUp(nIn, 256), 256, 0, ctx->stream>>>(dk.Current(), nIn, head);
+    LAUNCH_CHECK(ctx);
+    TRY(scanFlags(ctx, head, headOff, nIn));
+    voxelReduceKernel<<<divUp(nIn, 256), 256, 0, ctx->stream>>>(dk.Current(), dv.Current(), head, headOff, nIn, xyz, nrm, nOut, oxyz, onrm);
+    LAUNCH_CHECK(ctx);
+    TRY(scanTotal(ctx, head, headOff, nIn, &nVox));
+  }
+  *newSize = nOut + nVox;
+  return B200REG_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int32_t b200reg_map_create(b200reg_ctx* ctx, double voxel_size, b200reg_map** out) {
+  if (!ctx || !out) return setErr(ctx, B200REG_E_INVALID_PARAM, "map_create: bad arguments");
+  b200reg_map* m = new b200reg_map();
+  m->voxel = voxel_size;
+  *out = m;
+  return B200REG_OK;
+}
+
+void b200reg_map_destroy(b200reg_ctx* ctx, b200reg_map* map) {
+  if (!map) return;
+  if (ctx) { cudaSetDevice(ctx->device); cudaStreamSynchronize(ctx->stream); }
+  cudaFree(map->xyz); cudaFree(map->nrm); cudaFree(map->xyz2); cudaFree(map->nrm2);
+  delete map;
+}
+
+int64_t b200reg_map_size(const b200reg_map* map) { return map ? map->n : 0; }
+int32_t b200reg_map_has_normals(const b200reg_map* map) { return (map && map->hasNormals) ? 1 : 0; }
+
+int32_t b200reg_map_insert(b200reg_ctx* ctx, b200reg_map* map, const double* scan_xyz, const double* scan_nrm, int64_t n,
+                           const double T_map_scan[16], const b200reg_crop_spec* volume) {
+  if (!ctx || !map || n < 0 || (n > 0 && !scan_xyz) || !T_map_scan || !volume) return setErr(ctx, B200REG_E_INVALID_PARAM, "map_insert: bad arguments");
+  if (n == 0) return B200REG_OK;
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  const int64_t total = map->n + n;
+  if (total >= (int64_t)0x7fffffff) return setErr(ctx, B200REG_E_INVALID_PARAM, "map_insert: map too large");
+  TRY(mapReserve(ctx, map, total));
+  // `mapCloud_ += transformedCloud` (Submap.cpp:84): Open3D keeps normals only if both sides have them
+  const bool normals = (map->n == 0 || map->hasNormals) && scan_nrm != nullptr;
+  const size_t fb = sizeof(double) * 3 * (size_t)n;
+  TRY(ensureBuf(ctx, ctx->misc, 2 * fb + 256));
+  double* dIn = (double*)ctx->misc.p;
+  double* dInN = scan_nrm ? dIn + 3 * (size_t)n : nullptr;
+  double* dT = (double*)((char*)ctx->dstate + 40960);
+  CUDA_TRY(ctx, cudaMemcpyAsync(dIn, scan_xyz, fb, cudaMemcpyHostToDevice, ctx->stream));
+  if (scan_nrm) CUDA_TRY(ctx, cudaMemcpyAsync(dInN, scan_nrm, fb, cudaMemcpyHostToDevice, ctx->stream));
+  CUDA_TRY(ctx, cudaMemcpyAsync(dT, T_map_scan, sizeof(double) * 16, cudaMemcpyHostToDevice, ctx->stream));
+  transformF64Kernel<<<divUp(n, 256), 256, 0, ctx->stream>>>(dIn, normals ? dInN : nullptr, n, dT, map->xyz + 3 * (size_t)map->n,
+                                                             normals ? map->nrm + 3 * (size_t)map->n : nullptr);
+  LAUNCH_CHECK(ctx);
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));   // host scan buffers may be reused; misc is reused below
+  map->hasNormals = normals;
+  if (!(map->voxel > 0.0)) {   // voxel_size <= 0: plain append (helpers.cpp:121-124)
+    map->n = total;
+    return B200REG_OK;
+  }
+  int64_t newSize = 0;
+  TRY(revoxelize(ctx, map->voxel, *volume, map->xyz, normals ? map->nrm : nullptr, total, map->xyz2, normals ? map->nrm2 : nullptr, &newSize));
+  double* t = map->xyz; map->xyz = map->xyz2; map->xyz2 = t;
+  t = map->nrm; map->nrm = map->nrm2; map->nrm2 = t;
+  map->n = newSize;
+  return B200REG_OK;
+}
+
+int32_t b200reg_map_crop(b200reg_ctx* ctx, const b200reg_map* map, const b200reg_crop_spec* volume, b200reg_cloud** out) {
+  if (!ctx || !map || !volume || !out) return setErr(ctx, B200REG_E_INVALID_PARAM, "map_crop: bad arguments");
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  const int64_t n = map->n;
+  int64_t m = 0;
+  unsigned* flag = nullptr; unsigned* off = nullptr;
+  if (n > 0) {
+    TRY(ensureBuf(ctx, ctx->flags, 2 * sizeof(unsigned) * (size_t)n + 64));
+    flag = (unsigned*)ctx->flags.p;
+    off = flag + n;
+    classifyKernel<<<divUp(n, 256), 256, 0, ctx->stream>>>(map->xyz, n, *volume, 0.0, flag, nullptr, nullptr, nullptr);
+    LAUNCH_CHECK(ctx);
+    TRY(scanFlags(ctx, flag, off, n));
+    TRY(scanTotal(ctx, flag, off, n, &m));
+  }
+  b200reg_cloud* c = new b200reg_cloud();
+  c->n = m;
+  c->cap = m > 0 ? m : 1;
+  cudaError_t e = cudaMalloc(&c->xyz, sizeof(float4) * (size_t)c->cap);
+  if (e == cudaSuccess && map->hasNormals) e = cudaMalloc(&c->nrm, sizeof(float4) * (size_t)c->cap);
+  if (e != cudaSuccess) { cudaFree(c->xyz); delete c; return setErr(ctx, B200REG_E_OOM, "map_crop: %s", cudaGetErrorString(e)); }
+  if (m > 0) {
+    scatterSelectedF32Kernel<<<divUp(n, 256), 256, 0, ctx->stream>>>(flag, off, n, map->xyz, map->hasNormals ? map->nrm : nullptr, c->xyz, c->nrm);
+    LAUNCH_CHECK(ctx);
+  }
+  *out = c;
+  return B200REG_OK;
+}
+
+int32_t b200reg_map_download(b200reg_ctx* ctx, const b200reg_map* map, double* xyz, double* nrm) {
+  if (!ctx || !map) return setErr(ctx, B200REG_E_INVALID_PARAM, "map_download: bad arguments");
+  if (map->n == 0) return B200REG_OK;
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  if (xyz) CUDA_TRY(ctx, cudaMemcpyAsync(xyz, map->xyz, sizeof(double) * 3 * (size_t)map->n, cudaMemcpyDeviceToHost, ctx->stream));
+  if (nrm) {
+    if (!map->hasNormals) return setErr(ctx, B200REG_E_INVALID_FIELD, "map has no normals");
+    CUDA_TRY(ctx, cudaMemcpyAsync(nrm, map->nrm, sizeof(double) * 3 * (size_t)map->n, cudaMemcpyDeviceToHost, ctx->stream));
+  }
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  return B200REG_OK;
+}
+
+int32_t b200reg_crop_f64(b200reg_ctx* ctx, const b200reg_crop_spec* volume, const double* xyz, const double* nrm, int64_t n,
+                         double* xyz_out, double* nrm_out, int64_t* n_out) {
+  if (!ctx || !volume || n < 0 || (n > 0 && !xyz) || !n_out) return setErr(ctx, B200REG_E_INVALID_PARAM, "crop_f64: bad arguments");
+  *n_out = 0;
+  if (n == 0) return B200REG_OK;
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  const size_t fb = sizeof(double) * 3 * (size_t)n;
+  TRY(ensureBuf(ctx, ctx->misc, 4 * fb + 64));
+  double* dIn = (double*)ctx->misc.p;
+  double* dInN = dIn + 3 * (size_t)n;
+  double* dOut = dInN + 3 * (size_t)n;
+  double* dOutN = dOut + 3 * (size_t)n;
+  TRY(ensureBuf(ctx, ctx->flags, 2 * sizeof(unsigned) * (size_t)n + 64));
+  unsigned* flag = (unsigned*)ctx->flags.p;
+  unsigned* off = flag + n;
+  CUDA_TRY(ctx, cudaMemcpyAsync(dIn, xyz, fb, cudaMemcpyHostToDevice, ctx->stream));
+  if (nrm) CUDA_TRY(ctx, cudaMemcpyAsync(dInN, nrm, fb, cudaMemcpyHostToDevice, ctx->stream));
+  classifyKernel<<<divUp(n, 256), 256, 0, ctx->stream>>>(dIn, n, *volume, 0.0, flag, nullptr, nullptr, nullptr);
+  LAUNCH_CHECK(ctx);
+  TRY(scanFlags(ctx, flag, off, n));
+  scatterSelectedKernel<<<divUp(n, 256), 256, 0, ctx->stream>>>(flag, off, n, dIn, nrm ? dInN : nullptr, dOut, dOutN);
+  LAUNCH_CHECK(ctx);
+  int64_t m = 0;
+  TRY(scanTotal(ctx, flag, off, n, &m));
+  if (m > 0 && xyz_out) CUDA_TRY(ctx, cudaMemcpyAsync(xyz_out, dOut, sizeof(double) * 3 * (size_t)m, cudaMemcpyDeviceToHost, ctx->stream));
+  if (m > 0 && nrm && nrm_out) CUDA_TRY(ctx, cudaMemcpyAsync(nrm_out, dOutN, sizeof(double) * 3 * (size_t)m, cudaMemcpyDeviceToHost, ctx->stream));
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  *n_out = m;
+  return B200REG_OK;
+}
+
+}  // extern "C"

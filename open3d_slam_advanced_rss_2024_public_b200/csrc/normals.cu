@@ -1,0 +1,218 @@
+// csrc/normals.cu — SurfaceNormalDataPointsFilter::inPlaceFilter (DataPointsFilters/SurfaceNormal.cpp:83-330):
+// self-kNN (incl. the point itself) over a voxel-grid index of the cloud, per-point mean / covariance in fp64 over the
+// fp32 neighbour coordinates, rank test, symmetric 3x3 eigen-decomposition, normal = eigenvector of the smallest
+// eigenvalue, optional densities / eigenvalues / linearity-planarity-curvature, optional orientation toward a point.
+//
+// This file is compiled with --fmad=false: every fp operation is individually rounded, so the arithmetic below is the
+// same sequence of IEEE operations the oracle's mixed-precision mode performs.
+#include <cmath>
+
+#include "common.cuh"
+
+int runKnn(b200reg_ctx* ctx, const b200reg_index* ix, const float4* queries, int64_t n, const float* T, int k, float maxDist, int allowSelf);
+int cloudStats(b200reg_ctx* ctx, const b200reg_cloud* c, double sum[3], float mn[3], float mx[3]);
+int buildIndex(b200reg_ctx* ctx, const b200reg_cloud* ref, const float mean[3], const float bbMin[3], const float bbMax[3], float cell,
+               b200reg_index** out);
+
+namespace {
+
+// rank of a 3x3 matrix by Householder QR with full pivoting in fp32 — the test `C.fullPivHouseholderQr().rank() + 1 >= 3`
+// of SurfaceNormal.cpp:210 in the reference's scalar T = float (threshold eps * size * max pivot).
+__device__ int rank3Fp32(const double* C) {
+  float R[3][3];
+  for (int i = 0; i < 3; ++i) for (int j = 0; j < 3; ++j) R[i][j] = (float)C[3 * i + j];
+  float piv[3] = {0.f, 0.f, 0.f};
+  float maxpivot = 0.f;
+  for (int k = 0; k < 3; ++k) {
+    int pr = k, pc = k;
+    float best = -1.f;
+    for (int i = k; i < 3; ++i)
+      for (int j = k; j < 3; ++j)
+        if (fabsf(R[i][j]) > best) { best = fabsf(R[i][j]); pr = i; pc = j; }
+    if (best <= 0.f) break;
+    if (pr != k) for (int j = 0; j < 3; ++j) { const float t = R[pr][j]; R[pr][j] = R[k][j]; R[k][j] = t; }
+    if (pc != k) for (int i = 0; i < 3; ++i) { const float t = R[i][pc]; R[i][pc] = R[i][k]; R[i][k] = t; }
+    float norm2 = 0.f;
+    for (int i = k; i < 3; ++i) norm2 += R[i][k] * R[i][k];
+    const float x0 = R[k][k];
+    const float alpha = (x0 >= 0.f) ? -sqrtf(norm2) : sqrtf(norm2);
+    float v[3] = {0.f, 0.f, 0.f};
+    v[k] = x0 - alpha;
+    for (int i = k + 1; i < 3; ++i) v[i] = R[i][k];
+    float vnorm2 = 0.f;
+    for (int i = k; i < 3; ++i) vnorm2 += v[i] * v[i];
+    if (vnorm2 > 0.f) {
+      for (int j = k; j < 3; ++j) {
+        float dot = 0.f;
+        for (int i = k; i < 3; ++i) dot += v[i] * R[i][j];
+        const float f = 2.f * dot / vnorm2;
+        for (int i = k; i < 3; ++i) R[i][j] -= f * v[i];
+      }
+    }
+    for (int i = k + 1; i < 3; ++i) R[i][k] = 0.f;
+    piv[k] = fabsf(R[k][k]);
+    maxpivot = fmaxf(maxpivot, piv[k]);
+  }
+  const float thr = 1.1920928955078125e-7f * 3.f * maxpivot;
+  int rank = 0;
+  for (int k = 0; k < 3; ++k) rank += (piv[k] > thr) ? 1 : 0;
+  return rank;
+}
+
+// symmetric 3x3 eigen-decomposition, cyclic Jacobi in fp64; eigenvalues ascending, eigenvectors in columns
+__device__ void symEig3(const double* Cin, double val[3], double vec[3][3]) {
+  double a[3][3], V[3][3] = {{1, 0, 0}, {0, 1, 0}, {0, 0, 1}};
+  for (int i = 0; i < 3; ++i) for (int j = 0; j < 3; ++j) a[i][j] = Cin[3 * i + j];
+  for (int sweep = 0; sweep < 64; ++sweep) {
+    const double off = a[0][1] * a[0][1] + a[0][2] * a[0][2] + a[1][2] * a[1][2];
+    if (off == 0.0) break;
+#pragma unroll
+    for (int p = 0; p < 3; ++p)
+#pragma unroll
+      for (int q = p + 1; q < 3; ++q) {
+        if (a[p][q] == 0.0) continue;
+        const double theta = (a[q][q] - a[p][p]) / (2.0 * a[p][q]);
+        const double t = ((theta >= 0) ? 1.0 : -1.0) / (fabs(theta) + sqrt(theta * theta + 1.0));
+        const double c = 1.0 / sqrt(t * t + 1.0), s = t * c;
+#pragma unroll
+        for (int k = 0; k < 3; ++k) { const double x = a[k][p], y = a[k][q]; a[k][p] = c * x - s * y; a[k][q] = s * x + c * y; }
+#pragma unroll
+        for (int k = 0; k < 3; ++k) { const double x = a[p][k], y = a[q][k]; a[p][k] = c * x - s * y; a[q][k] = s * x + c * y; }
+#pragma unroll
+        for (int k = 0; k < 3; ++k) { const double x = V[k][p], y = V[k][q]; V[k][p] = c * x - s * y; V[k][q] = s * x + c * y; }
+      }
+  }
+  // ascending order; stable for equal values (matches std::sort on distinct diagonals; ties are measure-zero)
+  int o0 = 0, o1 = 1, o2 = 2;
+  if (a[o1][o1] < a[o0][o0]) { const int t = o0; o0 = o1; o1 = t; }
+  if (a[o2][o2] < a[o1][o1]) { const int t = o1; o1 = o2; o2 = t; }
+  if (a[o1][o1] < a[o0][o0]) { const int t = o0; o0 = o1; o1 = t; }
+  const int order[3] = {o0, o1, o2};
+#pragma unroll
+  for (int c = 0; c < 3; ++c) {
+    double v = 0.0;
+#pragma unroll
+    for (int r = 0; r < 3; ++r) v = (order[c] == r) ? a[r][r] : v;
+    val[c] = v;
+#pragma unroll
+    for (int r = 0; r < 3; ++r) {
+      double e = 0.0;
+#pragma unroll
+      for (int cc = 0; cc < 3; ++cc) e = (order[c] == cc) ? V[r][cc] : e;
+      vec[r][c] = e;
+    }
+  }
+}
+
+__global__ void __launch_bounds__(128) normalsKernel(const float4* __restrict__ xyz, const float4* __restrict__ sortedPts,
+                                                     const int* __restrict__ pos, const float* __restrict__ d2, int64_t n, int k,
+                                                     int orient, float ox, float oy, float oz, float4* __restrict__ outN,
+                                                     float* __restrict__ dens, float* __restrict__ eigv, float* __restrict__ lpc,
+                                                     int* __restrict__ degenerate) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const int* myPos = pos + (int64_t)k * i;
+  const float* myD = d2 + (int64_t)k * i;
+  // mean of the valid neighbours (SurfaceNormal.cpp:190-201), neighbour order = ascending (d2, id)
+  double mean[3] = {0, 0, 0};
+  int realKnn = 0;
+  for (int j = 0; j < k; ++j) {
+    if (myD[j] == CUDART_INF_F) continue;
+    const float4 p = sortedPts[myPos[j]];
+    mean[0] += (double)p.x; mean[1] += (double)p.y; mean[2] += (double)p.z;
+    ++realKnn;
+  }
+  double C[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+  double maxSq = 0.0;
+  if (realKnn > 0) {
+    for (int c = 0; c < 3; ++c) mean[c] /= (double)realKnn;
+    for (int j = 0; j < k; ++j) {
+      if (myD[j] == CUDART_INF_F) continue;
+      const float4 p = sortedPts[myPos[j]];
+      const double nn[3] = {(double)p.x - mean[0], (double)p.y - mean[1], (double)p.z - mean[2]};
+      for (int r = 0; r < 3; ++r) for (int c = 0; c < 3; ++c) C[3 * r + c] += nn[r] * nn[c];   // :203-204
+      maxSq = fmax(maxSq, nn[0] * nn[0] + nn[1] * nn[1] + nn[2] * nn[2]);
+    }
+    for (int q = 0; q < 9; ++q) C[q] /= (double)realKnn;
+  }
+  const bool isDeg = (realKnn == 0) || !(rank3Fp32(C) + 1 >= 3);   // :210
+  double val[3] = {0, 0, 0}, vec[3][3] = {{0, 0, 0}, {0, 0, 0}, {0, 0, 0}};
+  if (!isDeg) symEig3(C, val, vec);
+  else atomicAdd(degenerate, 1);
+  const float4 p = xyz[i];
+  double nv[3] = {vec[0][0], vec[1][0], vec[2][0]};   // eigenvector of the smallest eigenvalue (:237-243)
+  if (orient && !isDeg) {                              // SurfaceNormalEstimatorPCA.cpp:69-84
+    const double dot = (double)(ox - p.x) * nv[0] + (double)(oy - p.y) * nv[1] + (double)(oz - p.z) * nv[2];
+    if (dot < 0) { nv[0] = -nv[0]; nv[1] = -nv[1]; nv[2] = -nv[2]; }
+  }
+  outN[i] = make_float4((float)fmin(1.0, fmax(-1.0, nv[0])), (float)fmin(1.0, fmax(-1.0, nv[1])), (float)fmin(1.0, fmax(-1.0, nv[2])), 0.f);   // :245
+  if (dens) {   // utils.h:105-128
+    float dd = 0.f;
+    if (!isDeg) {
+      const float m2 = (float)maxSq;
+      const float volume = (float)(4. / 3.) * 3.14159274101257324f * (m2 * sqrtf(m2));
+      dd = (volume > 0.f) ? ((float)realKnn / volume) : 0.f;
+    }
+    dens[i] = dd;
+  }
+  if (eigv) { eigv[3 * i] = (float)val[0]; eigv[3 * i + 1] = (float)val[1]; eigv[3 * i + 2] = (float)val[2]; }
+  if (lpc) {   // SurfaceNormalEstimatorPCA.cpp:86-99
+    float l = 0.f, pl = 0.f, cu = 0.f;
+    if (!isDeg) {
+      const float s1 = sqrtf((float)val[0]), s2 = sqrtf((float)val[1]), s3 = sqrtf((float)val[2]);
+      l = (s3 - s2) / s3;
+      pl = (s2 - s1) / s3;
+      cu = s1 / (s1 + s2 + s3);
+    }
+    lpc[3 * i] = l; lpc[3 * i + 1] = pl; lpc[3 * i + 2] = cu;
+  }
+}
+
+}  // namespace
+
+extern "C" int32_t b200reg_surface_normals(b200reg_ctx* ctx, b200reg_cloud* inout, int32_t knn, float max_dist, float epsilon,
+                                           const float* orient_origin, float* densities_out, float* eig_values_out,
+                                           float* lin_plan_curv_out, int32_t* degenerate_count) {
+  if (!ctx || !inout) return setErr(ctx, B200REG_E_INVALID_PARAM, "surface_normals: bad arguments");
+  if (knn < 3) return setErr(ctx, B200REG_E_INVALID_PARAM, "SurfaceNormalDataPointsFilter: knn must be >= 3");   // SurfaceNormal.h:69
+  if (!(epsilon >= 0.f) || !(max_dist >= 0.f)) return setErr(ctx, B200REG_E_INVALID_PARAM, "SurfaceNormalDataPointsFilter: epsilon/maxDist must be >= 0");
+  const int64_t n = inout->n;
+  if (degenerate_count) *degenerate_count = 0;
+  if (n == 0) return B200REG_OK;
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  // own matcher over the cloud itself (SurfaceNormal.cpp:170-179): un-centred index
+  double sum[3];
+  float mn[3], mx[3];
+  TRY(cloudStats(ctx, inout, sum, mn, mx));
+  const float zero[3] = {0.f, 0.f, 0.f};
+  b200reg_index* ix = nullptr;
+  TRY(buildIndex(ctx, inout, zero, mn, mx, 0.f, &ix));
+  int st = runKnn(ctx, ix, inout->xyz, n, nullptr, knn, max_dist, 1);
+  if (st != B200REG_OK) { b200reg_index_free(ctx, ix); return st; }
+  if (!inout->nrm) {
+    cudaError_t e = cudaMalloc(&inout->nrm, sizeof(float4) * (size_t)inout->cap);
+    if (e != cudaSuccess) { b200reg_index_free(ctx, ix); return setErr(ctx, B200REG_E_OOM, "surface_normals: %s", cudaGetErrorString(e)); }
+  }
+  const size_t extra = sizeof(float) * (size_t)n * 7 + 64;
+  st = ensureBuf(ctx, ctx->misc, extra);
+  if (st != B200REG_OK) { b200reg_index_free(ctx, ix); return st; }
+  float* dDens = densities_out ? (float*)ctx->misc.p : nullptr;
+  float* dEig = eig_values_out ? (float*)ctx->misc.p + n : nullptr;
+  float* dLpc = lin_plan_curv_out ? (float*)ctx->misc.p + 4 * n : nullptr;
+  int* dDeg = (int*)((char*)ctx->dstate + 32768);
+  cudaMemsetAsync(dDeg, 0, sizeof(int), ctx->stream);
+  const float ox = orient_origin ? orient_origin[0] : 0.f, oy = orient_origin ? orient_origin[1] : 0.f, oz = orient_origin ? orient_origin[2] : 0.f;
+  normalsKernel<<<divUp(n, 128), 128, 0, ctx->stream>>>(inout->xyz, ix->pts, (const int*)ctx->matchPos.p, (const float*)ctx->matchD2.p, n, knn,
+                                                        orient_origin ? 1 : 0, ox, oy, oz, inout->nrm, dDens, dEig, dLpc, dDeg);
+  ctx->launches++;
+  cudaError_t e = cudaGetLastError();
+  if (e == cudaSuccess && densities_out) e = cudaMemcpyAsync(densities_out, dDens, sizeof(float) * (size_t)n, cudaMemcpyDeviceToHost, ctx->stream);
+  if (e == cudaSuccess && eig_values_out) e = cudaMemcpyAsync(eig_values_out, dEig, sizeof(float) * 3 * (size_t)n, cudaMemcpyDeviceToHost, ctx->stream);
+  if (e == cudaSuccess && lin_plan_curv_out) e = cudaMemcpyAsync(lin_plan_curv_out, dLpc, sizeof(float) * 3 * (size_t)n, cudaMemcpyDeviceToHost, ctx->stream);
+  if (e == cudaSuccess) e = cudaMemcpyAsync(ctx->pinned, dDeg, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+  b200reg_index_free(ctx, ix);
+  if (e != cudaSuccess) return setErr(ctx, B200REG_E_CUDA, "surface_normals: %s", cudaGetErrorString(e));
+  if (degenerate_count) *degenerate_count = *(const int*)ctx->pinned;
+  return B200REG_OK;
+}
