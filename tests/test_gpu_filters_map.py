@@ -23,7 +23,7 @@ def random_cloud(n, seed, scale=10.0):
                                               (20_000, (0.25, 0.25, 0.25), 0, 1), (1, (1.0, 1.0, 1.0), 1, 1)])
 def test_voxelgrid_random_bit_exact(ctx, oracle, n, v, centroid, avg):
     """utest/ui/DataFilters.cpp:616-673 shape (random cloud, fewer points out) + exact membership/order/centroids."""
-    pts = oracle.feat4(random_cloud(n, 7 + n))
+    pts = oracle.feat4(random_cloud(n, 7 + n, scale=2.0 if n <= 100 else 10.0))
     nrm = random_cloud(n, 8 + n, scale=2.0)
     m, f_o, d_o, cells = oracle.voxelgrid(pts, nrm, *v, use_centroid=bool(centroid), average_descriptors=bool(avg))
     c = ctx.upload(pts, nrm)

@@ -1,0 +1,268 @@
+"""CPU tests (-m "not gpu"): pin the oracle against the reference's own fixtures and known answers, and
+cross-check its pieces against independent numpy / scipy computations.  The oracle is the checker for the GPU tests, so it
+has to be right first."""
+import numpy as np
+import pytest
+from scipy.spatial import cKDTree
+
+import scenes
+
+
+def rot_angle(Ra, Rb):
+    R = Ra.T.astype(np.float64) @ Rb.astype(np.float64)
+    sk = np.array([R[2, 1] - R[1, 2], R[0, 2] - R[2, 0], R[1, 0] - R[0, 1]]) / 2     # robust near identity (arccos is not)
+    return float(np.arctan2(np.linalg.norm(sk), (np.trace(R) - 1) / 2))
+
+
+# ---- reference fixture: car_cloud400 <- car_cloud401, validT3d (utest/utest.cpp:74-89, tolerance utest.h:65-86) ----------
+@pytest.mark.parametrize("precision", [0, 1])
+def test_car_clouds_reach_validT3d(oracle, golden, precision):
+    car = golden["car"]
+    ref, rn, q = oracle.feat4(car["ref_xyz"]), car["ref_normals"], oracle.feat4(car["data_xyz"])
+    assert ref.shape[0] == 24989 and q.shape[0] == 25193
+    code, T, st = oracle.icp(oracle.icp_config(precision=precision, nthreads=4), ref, rn, q)
+    assert code == 0 and 3 <= st.iterations < 40 and not st.max_iterations_reached
+    V = golden["T"]["validT3d"]
+    assert abs(np.linalg.norm(V[:3, 3]) - np.linalg.norm(T[:3, 3])) < 0.1      # utest.h:83
+    assert rot_angle(V[:3, :3], T[:3, :3]) < 0.1                               # utest.h:84
+
+
+@pytest.mark.parametrize("knn,eps,maxd", [(1, 0.0, 1.0), (2, 0.2, 1.0), (3, 0.0, 0.5)])
+def test_matcher_grid_reaches_validT3d(oracle, golden, knn, eps, maxd):
+    """utest/ui/Matcher.cpp:68-92"""
+    car = golden["car"]
+    code, T, st = oracle.icp(oracle.icp_config(knn=knn, epsilon=eps, max_dist=maxd, nthreads=4), oracle.feat4(car["ref_xyz"]),
+                             car["ref_normals"], oracle.feat4(car["data_xyz"]))
+    V = golden["T"]["validT3d"]
+    assert code == 0
+    assert abs(np.linalg.norm(V[:3, 3]) - np.linalg.norm(T[:3, 3])) < 0.1 and rot_angle(V[:3, :3], T[:3, :3]) < 0.1
+
+
+def test_trimmed_outlier_filter_ratio_085(oracle, golden):
+    """utest/ui/Outliers.cpp:106-111"""
+    car = golden["car"]
+    code, T, st = oracle.icp(oracle.icp_config(trim_ratio=0.85, nthreads=4), oracle.feat4(car["ref_xyz"]), car["ref_normals"],
+                             oracle.feat4(car["data_xyz"]))
+    assert code == 0 and abs(st.weighted_point_used_ratio - 0.85) < 1e-3
+
+
+def test_golden_ref_trans_point_to_plane_chain(oracle, golden):
+    """GeneralTests.cpp:70-150 acceptance (median relative point error < 5 %) for the on-path golden config
+    defaultPointToPlaneMinDistDataPointsFilter (KDTree k1 + TrimmedDist 0.75 + PointToPlane + Counter 40 + Differential
+    1e-3/1e-2/4).  Its two DataPointsFilters are out of scope: MinDist 1.0 is applied here in numpy, and the reference
+    normals come from the oracle's SurfaceNormal (knn 10) instead of SamplingSurfaceNormal — allowed by the 5 % bar."""
+    c0, c1 = golden["vtk"]["cloud0"], golden["vtk"]["cloud1"]
+    ref = oracle.feat4(c0)
+    rn = oracle.surface_normals(ref, 10, nthreads=4)["normals"]
+    reading = c1[np.linalg.norm(c1, axis=1) > 1.0]                             # MinDistDataPointsFilter minDist 1
+    cfg = oracle.icp_config(trim_ratio=0.75, smooth_length=4, max_iter=40, nthreads=4)
+    code, T, st = oracle.icp(cfg, ref, rn, oracle.feat4(reading))
+    assert code == 0
+    G = golden["T"]["defaultPointToPlaneMinDistDataPointsFilter"]
+    P = np.concatenate([c1.astype(np.float64), np.ones((c1.shape[0], 1))], axis=1).T
+    err = np.linalg.norm((T.astype(np.float64) @ P - G @ P)[:3], axis=0)
+    mag = np.linalg.norm((T.astype(np.float64) @ P)[:3], axis=0)
+    assert np.median(err) / np.median(mag) < 0.05                              # GeneralTests.cpp:136-148
+
+
+def test_icp_singular_and_identity(oracle, golden):
+    """GeneralTests.cpp:152-210"""
+    nX, d = 10, 0.1
+    xs = np.array([[d * x - nX * d / 2, d * y - nX * d / 2, 0.0] for x in range(nX) for y in range(nX)], dtype=np.float32)
+    ref = xs.copy()
+    ref[:, 2] = 1.0
+    rn = np.tile(np.array([[0, 0, 1]], dtype=np.float32), (100, 1))
+    expected = np.eye(4)
+    expected[2, 3] = 1
+    for prec in (0, 1):
+        code, T, _ = oracle.icp(oracle.icp_config(precision=prec, trim_ratio=1.0, smooth_length=4), oracle.feat4(ref), rn, oracle.feat4(xs))
+        assert code == 0 and np.allclose(T, expected, atol=1e-5)
+    pts = oracle.feat4(golden["vtk"]["cloud0"])
+    nrm = oracle.surface_normals(pts, 10, nthreads=4)["normals"]
+    code, T, _ = oracle.icp(oracle.icp_config(precision=0, trim_ratio=1.0, smooth_length=4, nthreads=4), pts, nrm, pts)
+    assert code == 0 and np.allclose(T, np.eye(4), atol=1e-4)
+
+
+@pytest.mark.parametrize("shift", [(0, 0, 0), (100.0, -30.0, 35.0)])
+def test_conditioning_mirror_matcher(oracle, shift):
+    """utest/ui/icp/Conditioning.cpp:354-372 shape: icp_point_to_plane.yaml (MirrorMatcher, no filters, PointToPlane,
+    Differential 1e-5/1e-4/3, Counter 30) on a 10 000-point 1x3x5 box; same cloud displaced -> error < 1e-5 relative scale."""
+    rng = np.random.default_rng(4)
+    # box surface samples with analytic normals
+    n = 10_000
+    face = rng.integers(0, 6, n)
+    u, v = rng.random(n), rng.random(n)
+    dims = np.array([1.0, 3.0, 5.0])
+    pts = np.zeros((n, 3)); nrm = np.zeros((n, 3))
+    for f in range(6):
+        ax = f // 2
+        o = [a for a in range(3) if a != ax]
+        m = face == f
+        pts[m, ax] = dims[ax] * (f % 2) - dims[ax] / 2
+        pts[m, o[0]] = (u[m] - 0.5) * dims[o[0]]
+        pts[m, o[1]] = (v[m] - 0.5) * dims[o[1]]
+        nrm[m, ax] = 1.0 if f % 2 else -1.0
+    pts += np.array(shift)
+    T_true = scenes.rigid(scenes.rot_axis_angle([0.3, -1, 0.5], 0.05), [0.05, -0.02, 0.03])
+    reading = (np.linalg.inv(T_true) @ np.concatenate([pts, np.ones((n, 1))], axis=1).T).T[:, :3]
+    cfg = oracle.icp_config(matcher_kind=1, trim_ratio=-1.0, max_iter=30, min_diff_rot=1e-5, min_diff_trans=1e-4, smooth_length=3, precision=1)
+    code, T, st = oracle.icp(cfg, oracle.feat4(pts), nrm.astype(np.float32), oracle.feat4(reading))
+    assert code == 0
+    E = np.linalg.inv(T_true) @ T.astype(np.float64)
+    tol = 2e-5 if shift == (0, 0, 0) else 2e-4      # fp32 coordinates: ulp grows with the 100 m offset
+    assert np.abs(E[:3, 3]).max() < tol and rot_angle(np.eye(3), E[:3, :3]) < tol
+
+
+# ---- known answers / independent cross-checks ------------------------------------------------------------------------
+def test_quantile_rank_is_float_multiply_truncation(oracle):
+    """Matches.cpp:61-87: rank = size_t(float(n) * ratio).  KAT values from utest/ui/Outliers.cpp:126-151 (dists 4,5,5,5,5)."""
+    d = np.array([4, 5, 5, 5, 5], dtype=np.float32)
+    st, tau, w = oracle.trimmed_dist(d, 0.1)
+    assert st == 0 and tau == 4.0 and w.tolist() == [1, 0, 0, 0, 0]
+    st, tau, w = oracle.trimmed_dist(d, 0.5)
+    assert tau == 5.0 and w.sum() == 5
+    n = 131072
+    rng = np.random.default_rng(0)
+    x = rng.random(n).astype(np.float32)
+    st, tau, w = oracle.trimmed_dist(x, 0.8)
+    rank = int(np.float32(n) * np.float32(0.8))
+    assert rank == 104857
+    assert tau == np.sort(x)[rank]
+    x2 = x.copy()
+    x2[:10] = np.inf
+    st, tau2, w2 = oracle.trimmed_dist(x2, 1.0)
+    assert tau2 == x2[np.isfinite(x2)].max() and w2[:10].sum() == 0
+    st, _, _ = oracle.trimmed_dist(np.full(4, np.inf, dtype=np.float32), 0.5)
+    assert st == -1      # ConvergenceError "No matches available"
+
+
+def test_kdtree_vs_brute_and_scipy(oracle):
+    rng = np.random.default_rng(3)
+    ref = oracle.feat4(rng.normal(size=(20000, 3)).astype(np.float32))
+    q = oracle.feat4(rng.normal(size=(3000, 3)).astype(np.float32))
+    tree = oracle.KdTree(ref)
+    for k, md in [(1, np.inf), (5, 0.3), (12, np.inf)]:
+        ids, d2, visits = tree.knn(q, k=k, max_dist=md, nthreads=4)
+        ids_b, d2_b = oracle.knn_brute(ref, q, k=k, max_dist=md, nthreads=4)
+        assert np.array_equal(ids, ids_b) and np.array_equal(d2.view(np.uint32), d2_b.view(np.uint32))
+        assert visits < 0.2 * ref.shape[0] * q.shape[0]
+    # fp64 scipy agrees except on fp32 rounding ties
+    ids, d2, _ = tree.knn(q, k=1)
+    dd, ii = cKDTree(ref[:, :3].astype(np.float64)).query(q[:, :3].astype(np.float64), k=1)
+    differ = ids[:, 0] != ii
+    assert differ.mean() < 1e-3
+    assert np.allclose(np.sqrt(d2[:, 0]), dd, rtol=1e-5, atol=1e-6)
+    # padding
+    ids, d2, _ = tree.knn(q[:5] + 100, k=3, max_dist=1.0)
+    assert (ids == -1).all() and np.isinf(d2).all()
+
+
+def test_point_to_plane_system_vs_numpy(oracle):
+    rng = np.random.default_rng(8)
+    n = 4000
+    ref = rng.normal(size=(n, 3)) * 3
+    nrm = rng.normal(size=(n, 3)); nrm /= np.linalg.norm(nrm, axis=1, keepdims=True)
+    T = scenes.rigid(scenes.rot_axis_angle([1, 2, 3], 0.01), [0.01, 0.02, -0.01])
+    reading = (np.linalg.inv(T) @ np.concatenate([ref, np.ones((n, 1))], 1).T).T[:, :3].astype(np.float32)
+    ref32, nrm32 = ref.astype(np.float32), nrm.astype(np.float32)
+    ids = np.arange(n, dtype=np.int32).reshape(n, 1)
+    d2 = np.zeros((n, 1), dtype=np.float32)
+    w = np.ones((n, 1), dtype=np.float32)
+    w[::7] = 0
+    d2[5::11] = np.inf
+    o = oracle.point_to_plane(oracle.feat4(reading), oracle.feat4(ref32), nrm32, ids, d2, w, precision=1)
+    keep = (w[:, 0] != 0) & np.isfinite(d2[:, 0])
+    assert o["kept"] == keep.sum()
+    p = reading[keep].astype(np.float64); q = ref32[keep].astype(np.float64); nn = nrm32[keep].astype(np.float64)
+    p = p - p.mean(0); qc = q - q.mean(0)
+    G = np.concatenate([np.cross(p, nn), nn], axis=1).T
+    h = np.sum((p - qc) * nn, axis=1)
+    A = G @ G.T
+    b = -G @ h
+    assert np.allclose(o["A"], A, rtol=1e-10, atol=1e-9) and np.allclose(o["b"], b, rtol=1e-9, atol=1e-9)
+    assert np.allclose(o["x"], np.linalg.solve(A, b), rtol=1e-8)
+    E = np.linalg.inv(T) @ o["T"].astype(np.float64)
+    assert np.abs(E - np.eye(4)).max() < 5e-4            # one linearised step from 0.01 rad: second-order residual
+    o32 = oracle.point_to_plane(oracle.feat4(reading), oracle.feat4(ref32), nrm32, ids, d2, w, precision=0)
+    assert np.abs(o32["T"] - o["T"]).max() < 1e-5
+    # force4DOF: rows/cols {gamma, tx, ty, tz}
+    o4 = oracle.point_to_plane(oracle.feat4(reading), oracle.feat4(ref32), nrm32, ids, d2, w, force4DOF=True, precision=1)
+    assert np.allclose(o4["A"], A[2:, 2:], rtol=1e-10, atol=1e-9)
+    assert np.allclose(o4["T"][2, :3], [0, 0, 1], atol=1e-7)
+
+
+def test_voxelgrid_membership_vs_numpy(oracle):
+    rng = np.random.default_rng(2)
+    pts = (rng.random((20000, 3)) * 8 - 4).astype(np.float32)
+    v = np.float32(0.37)
+    m, f, _, cells = oracle.voxelgrid(oracle.feat4(pts), None, v, v, v)
+    minB = pts.min(0) / v
+    ijk = np.floor(pts / v - minB).astype(np.int64)
+    nd = (np.float32(1) + pts.max(0) / v - minB).astype(np.int64)
+    lin = ijk[:, 0] + ijk[:, 1] * nd[0] + ijk[:, 2] * nd[0] * nd[1]
+    assert np.array_equal(lin, cells.astype(np.int64))
+    uniq, first = np.unique(lin, return_index=True)
+    assert m == uniq.size
+    order = np.sort(first)
+    # centroids: fp32 accumulation; compare with fp64 means loosely and with order of first appearance exactly
+    for o_idx in (0, m // 2, m - 1):
+        members = np.nonzero(lin == lin[order[o_idx]])[0]
+        assert np.allclose(f[o_idx, :3], pts[members].astype(np.float64).mean(0), atol=1e-5)
+
+
+def test_surface_normals_plane_and_descriptors(oracle):
+    rng = np.random.default_rng(6)
+    n = 3000
+    xy = rng.random((n, 2)) * 4
+    pts = np.stack([xy[:, 0], xy[:, 1], 0.3 * xy[:, 0] + 0.001 * rng.normal(size=n)], axis=1).astype(np.float32)
+    o = oracle.surface_normals(oracle.feat4(pts), 12, nthreads=4, keep=("normals", "densities", "eig_values", "eig_vectors", "matched_ids", "mean_dists", "lin_plan_curv"))
+    expect = np.array([-0.3, 0, 1.0]) / np.linalg.norm([-0.3, 0, 1.0])
+    cosang = np.abs(o["normals"] @ expect)
+    assert np.median(cosang) > 0.9999
+    assert (np.diff(o["eig_values"], axis=1) >= 0).all()                       # ascending (our documented order)
+    assert np.array_equal(o["matched_ids"][:, 0], np.arange(n, dtype=np.float32))   # self is the first neighbour
+    assert (o["densities"] > 0).all() and o["degenerate"] == 0
+    assert (o["lin_plan_curv"][:, 1] > 0.5).mean() > 0.9                       # planar
+
+
+def test_open3d_slam_ops_vs_numpy(oracle):
+    rng = np.random.default_rng(12)
+    xyz = rng.normal(size=(50000, 3)) * 4
+    nrm = rng.normal(size=(50000, 3))
+    c = np.array([0.5, -0.3, 0.2])
+    d = np.linalg.norm(xyz - c, axis=1)
+    for kind, kw, expect in [(0, dict(rmax=3.0), d <= 3.0), (1, dict(rmin=3.0), d >= 3.0), (2, dict(rmin=1.0, rmax=3.0), (d <= 3.0) & (d >= 1.0)),
+                             (3, dict(rmax=2.0, zmin=-1.0, zmax=1.0), (xyz[:, 2] >= -1) & (xyz[:, 2] <= 1) & (np.linalg.norm((xyz - c)[:, :2], axis=1) <= 2.0))]:
+        xo, no, mask = oracle.crop(oracle.crop_spec(kind, c, **kw), xyz, nrm)
+        assert np.array_equal(mask, expect) and np.array_equal(xo, xyz[expect]) and np.array_equal(no, nrm[expect])
+        xo2, _, mask2 = oracle.crop(oracle.crop_spec(kind, c, invert=True, **kw), xyz, nrm)
+        assert np.array_equal(mask2, ~expect)
+    # voxelize within volume: membership + means vs numpy
+    spec = oracle.crop_spec(0, c, rmax=3.0)
+    xo, no, npass = oracle.voxelize_within_volume(0.5, spec, xyz, nrm)
+    inside = d <= 3.0
+    assert npass == (~inside).sum() and np.array_equal(xo[:npass], xyz[~inside])
+    key = np.floor(xyz[inside] * (1.0 / 0.5)).astype(np.int64)
+    uniq, inv = np.unique(key, axis=0, return_inverse=True)
+    assert xo.shape[0] == npass + uniq.shape[0]
+    means = np.zeros((uniq.shape[0], 3)); np.add.at(means, inv.ravel(), xyz[inside]); means /= np.bincount(inv.ravel())[:, None]
+    assert np.allclose(xo[npass:], means, atol=1e-12)                          # np.unique(axis=0) sorts lexicographically like our key order
+    assert np.allclose(np.linalg.norm(no[npass:], axis=1), 1.0)
+    # Open3D VoxelDownSample convention: origin = min_bound - voxel/2
+    xd, nd = oracle.voxel_down_sample(0.5, xyz, nrm)
+    key = np.floor((xyz - (xyz.min(0) - 0.25)) / 0.5).astype(np.int64)
+    assert xd.shape[0] == np.unique(key, axis=0).shape[0]
+    f, n32 = oracle.o3d_to_pm(xyz, nrm)
+    assert np.array_equal(f[:, :3], xyz.astype(np.float32)) and (f[:, 3] == 1).all() and np.array_equal(n32, nrm.astype(np.float32))
+
+
+def test_transform_and_determinant_check(oracle):
+    rng = np.random.default_rng(1)
+    pts = oracle.feat4(rng.normal(size=(1000, 3)).astype(np.float32))
+    T = scenes.rigid(scenes.rot_axis_angle([0, 1, 1], 0.4), [1, 2, 3]).astype(np.float32)
+    st, out, _ = oracle.transform(T, pts)
+    assert st == 0 and np.allclose(out[:, :3], pts[:, :3] @ T[:3, :3].T + T[:3, 3], atol=1e-5) and (out[:, 3] == 1).all()
+    bad = T.copy()
+    bad[:3, :3] *= 1.01
+    st, _, _ = oracle.transform(bad, pts)
+    assert st == -2      # TransformationError (TransformationsImpl.cpp:74)
