@@ -106,6 +106,19 @@ int32_t b200reg_icp_step(b200reg_ctx* ctx, const b200reg_index* index, const b20
                          int32_t k, float max_dist, float trim_ratio, float max_angle, int32_t force2D, double A_out[36],
                          double b_out[6], b200reg_step_stats* stats);
 
+/* ---- the same kernels behind the individual modules' Eigen-shaped interfaces (HOST arrays in / out): what the C++ shim
+ *      classes call when a chain mixes CPU and CUDA modules --------------------------------------------------------- */
+/* TrimmedDistOutlierFilter::compute (OutlierFiltersImpl.cpp:140-147): tau = quantile of the finite d2, w = (d2 <= tau) */
+int32_t b200reg_trimmed_dist(b200reg_ctx* ctx, const float* d2, int64_t count, float ratio, float* tau_out, float* w_out);
+/* SurfaceNormalOutlierFilter::compute (OutlierFiltersImpl.cpp:236-281); normals 3 floats per point, nullable = filter off */
+int32_t b200reg_surface_normal_outlier(b200reg_ctx* ctx, const float* normals_reading, const float* normals_reference,
+                                       int64_t n_reference, const int32_t* ids, int32_t k, int64_t n, float max_angle, float* w_out);
+/* ErrorMinimizer::compute(reading, reference, weights, matches) (ErrorMinimizer.cpp:218-232 + PointToPlane.cpp:107-156):
+ * explicit matches and OutlierWeights (k*n each, HOST) over two device clouds; reference in its ORIGINAL order. */
+int32_t b200reg_point_to_plane(b200reg_ctx* ctx, const b200reg_cloud* reading, const b200reg_cloud* reference, const int32_t* ids,
+                               const float* d2, const float* w, int32_t k, int32_t force2D, double A_out[36], double b_out[6],
+                               b200reg_step_stats* stats);
+
 /* PointToPlaneErrorMinimizer::compute tail (PointToPlane.cpp:185-368): solve (LLT, rank-reduced minimum norm when
  * singular), Rodrigues, un-centre.  Host arithmetic in fp64; T_out = the 4x4 step transform rounded to fp32. */
 int32_t b200reg_solve_point_to_plane(const double A[36], const double b[6], const double mean_reading[3],

@@ -103,6 +103,9 @@ SYMBOLS = {
     "b200reg_index_cell": (C.c_float, [_VP]),
     "b200reg_knn": (C.c_int32, [_VP, _VP, _VP, _VP, C.c_int32, C.c_float, C.c_float, C.c_int32, _VP, _VP, C.POINTER(C.c_uint64)]),
     "b200reg_icp_step": (C.c_int32, [_VP, _VP, _VP, _VP, C.c_int32, C.c_float, C.c_float, C.c_float, C.c_int32, _VP, _VP, C.POINTER(StepStats)]),
+    "b200reg_trimmed_dist": (C.c_int32, [_VP, _VP, C.c_int64, C.c_float, C.POINTER(C.c_float), _VP]),
+    "b200reg_surface_normal_outlier": (C.c_int32, [_VP, _VP, _VP, C.c_int64, _VP, C.c_int32, C.c_int64, C.c_float, _VP]),
+    "b200reg_point_to_plane": (C.c_int32, [_VP, _VP, _VP, _VP, _VP, _VP, C.c_int32, C.c_int32, _VP, _VP, C.POINTER(StepStats)]),
     "b200reg_solve_point_to_plane": (C.c_int32, [_VP, _VP, _VP, _VP, C.c_int32, C.c_int32, _VP, _VP]),
     "b200reg_icp_create": (C.c_int32, [_VP, C.POINTER(IcpConfig), C.POINTER(_VP)]),
     "b200reg_icp_destroy": (None, [_VP]),
@@ -247,6 +250,31 @@ class Context:
         st = StepStats()
         Tm = None if T is None else _f32(T).reshape(16)
         self.check(lib().b200reg_icp_step(self.h, index.h, reading.h, _p(Tm), k, max_dist, trim_ratio, max_angle, int(force2D), _p(A), _p(b), C.byref(st)))
+        return A, b, st
+
+    def trimmed_dist(self, d2, ratio):
+        d2 = _f32(d2)
+        tau = C.c_float(0)
+        w = np.empty(d2.shape, dtype=np.float32)
+        self.check(lib().b200reg_trimmed_dist(self.h, _p(d2), d2.size, ratio, C.byref(tau), _p(w)))
+        return tau.value, w
+
+    def surface_normal_outlier(self, nrm_read, nrm_ref, ids, max_angle):
+        ids = np.ascontiguousarray(ids, dtype=np.int32)
+        n, k = ids.shape
+        nr, nf = _f32(nrm_read), _f32(nrm_ref)
+        w = np.empty((n, k), dtype=np.float32)
+        self.check(lib().b200reg_surface_normal_outlier(self.h, _p(nr), _p(nf), 0 if nf is None else nf.shape[0], _p(ids), k, n, max_angle, _p(w)))
+        return w
+
+    def point_to_plane(self, reading, reference, ids, d2, w, force2D=False):
+        ids = np.ascontiguousarray(ids, dtype=np.int32)
+        d2, w = _f32(d2), _f32(w)
+        k = ids.size // max(reading.size, 1)
+        A = np.zeros((6, 6), dtype=np.float64)
+        b = np.zeros(6, dtype=np.float64)
+        st = StepStats()
+        self.check(lib().b200reg_point_to_plane(self.h, reading.h, reference.h, _p(ids), _p(d2), _p(w), k, int(force2D), _p(A), _p(b), C.byref(st)))
         return A, b, st
 
     def crop_f64(self, spec, xyz, nrm=None):

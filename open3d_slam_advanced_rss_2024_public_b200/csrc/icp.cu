@@ -57,6 +57,7 @@ int enqueueStep(b200reg_ctx* ctx, const b200reg_index* ix, const float4* reading
   P.useAngle = (maxAngle >= 0.f) ? 1 : 0;
   P.cosAngle = cosf(maxAngle);
   P.force2D = force2D;
+  P.w = nullptr;
   const int rblocks = (int)fmax(1.0, fmin((double)divUp(total, 256), (double)(4 * ctx->sm_count)));
   TRY(ensureBuf(ctx, ctx->partials, sizeof(double) * NUM_MOM * (size_t)rblocks));
   reduceKernel<<<rblocks, 256, 0, ctx->stream>>>(P, st, (double*)ctx->partials.p, &st->ticket[3], resultPtr(ctx));
@@ -562,6 +563,146 @@ int32_t b200reg_icp_register(b200reg_icp* icp, const b200reg_cloud* reading, con
   mul4(T_iter, Tpre, tmp);
   mul4(Tref, tmp, T_out);
   return done(B200REG_OK);
+}
+
+}  // extern "C"
+
+// =================================================================================================================
+// Standalone-module lane: the same kernels behind the Eigen-shaped interfaces of the individual libpointmatcher
+// modules (host matrices in, host matrices out) — what the C++ shim classes call when a chain mixes CPU and CUDA modules.
+// =================================================================================================================
+namespace {
+
+__global__ void trimWeightsKernel(const float* __restrict__ d2, int64_t count, const SelState* __restrict__ st, float* __restrict__ w) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= count) return;
+  w[i] = (d2[i] <= __uint_as_float(st->tauBits)) ? 1.f : 0.f;   // OutlierFiltersImpl.cpp:146
+}
+
+// SurfaceNormalOutlierFilter::compute (OutlierFiltersImpl.cpp:236-281) on explicit arrays (normals: 3 floats per point)
+__global__ void normalGateKernel(const float* __restrict__ nRead, const float* __restrict__ nRef, const int* __restrict__ ids, int k,
+                                 int64_t total, float eps, float* __restrict__ w) {
+  const int64_t o = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (o >= total) return;
+  const int id = ids[o];
+  if (id == -1) { w[o] = 0.f; return; }
+  const float* a = nRead + 3 * (o / k);
+  const float* b = nRef + 3 * (int64_t)id;
+  const float v = __fadd_rn(__fadd_rn(__fmul_rn(a[0], b[0]), __fmul_rn(a[1], b[1])), __fmul_rn(a[2], b[2]));
+  w[o] = (v < eps) ? 0.f : 1.f;
+}
+
+}  // namespace
+
+extern "C" {
+
+int32_t b200reg_trimmed_dist(b200reg_ctx* ctx, const float* d2, int64_t count, float ratio, float* tau_out, float* w_out) {
+  if (!ctx || count < 0 || (count > 0 && !d2)) return setErr(ctx, B200REG_E_INVALID_PARAM, "trimmed_dist: bad arguments");
+  if (!(ratio >= 0.f) || ratio > 1.f) return setErr(ctx, B200REG_E_NOT_CONVERGED, "Distance quantile of matches must lie in the range [0,1]");
+  if (count == 0) return setErr(ctx, B200REG_E_NOT_CONVERGED, "No matches available for computing distance quantiles");
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  TRY(ensureBuf(ctx, ctx->matchD2, sizeof(float) * (size_t)count));
+  TRY(ensureBuf(ctx, ctx->misc, sizeof(float) * (size_t)count));
+  float* dd = (float*)ctx->matchD2.p;
+  float* dw = (float*)ctx->misc.p;
+  CUDA_TRY(ctx, cudaMemcpyAsync(dd, d2, sizeof(float) * (size_t)count, cudaMemcpyHostToDevice, ctx->stream));
+  SelState* st = selState(ctx);
+  const int blocks = (int)fmax(1.0, fmin((double)divUp(count, 256 * 4), (double)(2 * ctx->sm_count)));
+  selectPassKernel<0><<<blocks, 256, 0, ctx->stream>>>(dd, count, ratio, st, histPtr(ctx));
+  LAUNCH_CHECK(ctx);
+  selectPassKernel<1><<<blocks, 256, 0, ctx->stream>>>(dd, count, ratio, st, histPtr(ctx));
+  LAUNCH_CHECK(ctx);
+  selectPassKernel<2><<<blocks, 256, 0, ctx->stream>>>(dd, count, ratio, st, histPtr(ctx));
+  LAUNCH_CHECK(ctx);
+  trimWeightsKernel<<<divUp(count, 256), 256, 0, ctx->stream>>>(dd, count, st, dw);
+  LAUNCH_CHECK(ctx);
+  SelState* h = (SelState*)ctx->pinned;
+  CUDA_TRY(ctx, cudaMemcpyAsync(h, st, sizeof(SelState), cudaMemcpyDeviceToHost, ctx->stream));
+  if (w_out) CUDA_TRY(ctx, cudaMemcpyAsync(w_out, dw, sizeof(float) * (size_t)count, cudaMemcpyDeviceToHost, ctx->stream));
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  if (h->error) return setErr(ctx, B200REG_E_NOT_CONVERGED, "No matches available for computing distance quantiles");
+  if (tau_out) memcpy(tau_out, &h->tauBits, sizeof(float));
+  return B200REG_OK;
+}
+
+int32_t b200reg_surface_normal_outlier(b200reg_ctx* ctx, const float* normals_reading, const float* normals_reference, int64_t n_reference,
+                                       const int32_t* ids, int32_t k, int64_t n, float max_angle, float* w_out) {
+  if (!ctx || !ids || !w_out || k < 1 || n < 0) return setErr(ctx, B200REG_E_INVALID_PARAM, "surface_normal_outlier: bad arguments");
+  const int64_t total = n * k;
+  if (!normals_reading || !normals_reference) {   // "surface normals not available. Skipping filtering" (:268-277)
+    for (int64_t i = 0; i < total; ++i) w_out[i] = 1.f;
+    return B200REG_OK;
+  }
+  if (total == 0) return B200REG_OK;
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  const size_t bR = sizeof(float) * 3 * (size_t)n, bF = sizeof(float) * 3 * (size_t)n_reference, bI = sizeof(int) * (size_t)total;
+  TRY(ensureBuf(ctx, ctx->misc, bR + bF + bI + sizeof(float) * (size_t)total + 64));
+  float* dR = (float*)ctx->misc.p;
+  float* dF = dR + 3 * (size_t)n;
+  int* dI = (int*)(dF + 3 * (size_t)n_reference);
+  float* dW = (float*)(dI + total);
+  CUDA_TRY(ctx, cudaMemcpyAsync(dR, normals_reading, bR, cudaMemcpyHostToDevice, ctx->stream));
+  CUDA_TRY(ctx, cudaMemcpyAsync(dF, normals_reference, bF, cudaMemcpyHostToDevice, ctx->stream));
+  CUDA_TRY(ctx, cudaMemcpyAsync(dI, ids, bI, cudaMemcpyHostToDevice, ctx->stream));
+  normalGateKernel<<<divUp(total, 256), 256, 0, ctx->stream>>>(dR, dF, dI, k, total, cosf(max_angle), dW);
+  LAUNCH_CHECK(ctx);
+  CUDA_TRY(ctx, cudaMemcpyAsync(w_out, dW, sizeof(float) * (size_t)total, cudaMemcpyDeviceToHost, ctx->stream));
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  return B200REG_OK;
+}
+
+// ErrorMinimizer::compute(reading, reference, weights, matches) (ErrorMinimizer.cpp:218-232) without materialising
+// ErrorElements: explicit matches + weights in, normal equations + ErrorElements statistics out.
+int32_t b200reg_point_to_plane(b200reg_ctx* ctx, const b200reg_cloud* reading, const b200reg_cloud* reference, const int32_t* ids,
+                               const float* d2, const float* w, int32_t k, int32_t force2D, double A_out[36], double b_out[6],
+                               b200reg_step_stats* stats) {
+  if (!ctx || !reading || !reference || !ids || !d2 || !w || k < 1) return setErr(ctx, B200REG_E_INVALID_PARAM, "point_to_plane: bad arguments");
+  if (!reference->nrm) return setErr(ctx, B200REG_E_INVALID_FIELD, "PointToPlaneErrorMinimizer: reference cloud has no 'normals' descriptor");
+  const int64_t n = reading->n, total = n * k;
+  if (total == 0) return setErr(ctx, B200REG_E_NOT_CONVERGED, "ErrorMnimizer: no point to minimize");
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  TRY(ensureBuf(ctx, ctx->matchIds, sizeof(int) * (size_t)total));
+  TRY(ensureBuf(ctx, ctx->matchD2, sizeof(float) * (size_t)total));
+  TRY(ensureBuf(ctx, ctx->misc, sizeof(float) * (size_t)total));
+  CUDA_TRY(ctx, cudaMemcpyAsync(ctx->matchIds.p, ids, sizeof(int) * (size_t)total, cudaMemcpyHostToDevice, ctx->stream));
+  CUDA_TRY(ctx, cudaMemcpyAsync(ctx->matchD2.p, d2, sizeof(float) * (size_t)total, cudaMemcpyHostToDevice, ctx->stream));
+  CUDA_TRY(ctx, cudaMemcpyAsync(ctx->misc.p, w, sizeof(float) * (size_t)total, cudaMemcpyHostToDevice, ctx->stream));
+  ReduceParams P;
+  memset(&P, 0, sizeof(P));
+  P.reading = reading->xyz;
+  P.refPts = reference->xyz;
+  P.refNrm = reference->nrm;
+  P.ids = (const int*)ctx->matchIds.p;
+  P.d2 = (const float*)ctx->matchD2.p;
+  P.pos = (const int*)ctx->matchIds.p;   // reference in original order: position == id
+  P.n = n;
+  P.k = k;
+  P.force2D = force2D;
+  P.w = (const float*)ctx->misc.p;
+  SelState* st = selState(ctx);
+  const int rblocks = (int)fmax(1.0, fmin((double)divUp(total, 256), (double)(4 * ctx->sm_count)));
+  TRY(ensureBuf(ctx, ctx->partials, sizeof(double) * NUM_MOM * (size_t)rblocks));
+  reduceKernel<<<rblocks, 256, 0, ctx->stream>>>(P, st, (double*)ctx->partials.p, &st->ticket[3], resultPtr(ctx));
+  LAUNCH_CHECK(ctx);
+  HostStep* h = (HostStep*)ctx->pinned;
+  CUDA_TRY(ctx, cudaMemcpyAsync(h->mom, resultPtr(ctx), sizeof(double) * NUM_MOM, cudaMemcpyDeviceToHost, ctx->stream));
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  if (stats) {
+    memset(stats, 0, sizeof(*stats));
+    stats->kept = (int64_t)h->mom[M_CNT];
+    stats->n_finite = (int64_t)h->mom[M_VALID];
+    stats->weight_sum = h->mom[M_SPARE];
+    stats->tau = INFINITY;
+    stats->point_used_ratio = (float)h->mom[M_CNT] / (float)total;
+    stats->weighted_point_used_ratio = (float)h->mom[M_SPARE] / (float)total;
+  }
+  if (h->mom[M_CNT] < 1.0) return setErr(ctx, B200REG_E_NOT_CONVERGED, "ErrorMnimizer: no point to minimize");
+  double A[36], b[6], mr[3], ms[3];
+  momentsToSystem(h->mom, A, b, mr, ms);
+  if (A_out) memcpy(A_out, A, sizeof(A));
+  if (b_out) memcpy(b_out, b, sizeof(b));
+  if (stats) for (int d = 0; d < 3; ++d) { stats->mean_reading[d] = mr[d]; stats->mean_reference[d] = ms[d]; }
+  return B200REG_OK;
 }
 
 }  // extern "C"

@@ -126,6 +126,7 @@ struct ReduceParams {
   int useAngle;
   float cosAngle;              // eps = cos(maxAngle) in float (OutlierFiltersImpl.cpp:228)
   int force2D;
+  const float* w;              // explicit OutlierWeights (standalone-module lane); nullable. When set, the gates are skipped.
 };
 
 __device__ __forceinline__ double warpSum(double v) {
@@ -147,7 +148,8 @@ __global__ void __launch_bounds__(256) reduceKernel(ReduceParams P, const SelSta
     const float d = P.d2[o];
     if (d == CUDART_INF_F) continue;          // ErrorMinimizer.cpp:103-106
     m[M_VALID] += 1.0;
-    if (P.useTrim && !(d <= tau)) continue;   // OutlierFiltersImpl.cpp:146
+    if (P.w) { if (P.w[o] == 0.f) continue; }   // ErrorMinimizer.cpp:108
+    else if (P.useTrim && !(d <= tau)) continue;   // OutlierFiltersImpl.cpp:146
     const int64_t i = o / P.k;
     const int pos = P.pos[o];
     if (pos < 0) continue;
@@ -155,7 +157,7 @@ __global__ void __launch_bounds__(256) reduceKernel(ReduceParams P, const SelSta
     float3 r = make_float3(q4.x, q4.y, q4.z);
     if (P.hasT) r = xformPoint(P.T, q4.x, q4.y, q4.z, q4.w);
     const float4 nn4 = P.refNrm[pos];
-    if (P.useAngle && P.readingNrm) {          // OutlierFiltersImpl.cpp:259-264
+    if (!P.w && P.useAngle && P.readingNrm) {          // OutlierFiltersImpl.cpp:259-264
       const float4 a4 = P.readingNrm[i];
       float3 a = make_float3(a4.x, a4.y, a4.z);
       if (P.hasT) a = xformNormal(P.T, a4.x, a4.y, a4.z);
@@ -168,6 +170,7 @@ __global__ void __launch_bounds__(256) reduceKernel(ReduceParams P, const SelSta
     const double ux = ry * nz - rz * ny, uy = rz * nx - rx * nz, uz = rx * ny - ry * nx;   // u = r x n
     const double e = (rx - sx) * nx + (ry - sy) * ny + (rz - sz) * nz;
     m[M_CNT] += 1.0;
+    m[M_SPARE] += P.w ? (double)P.w[o] : 1.0;   // sum of weights (ErrorMinimizer.cpp:123)
     m[M_R] += rx; m[M_R + 1] += ry; m[M_R + 2] += rz;
     m[M_S] += sx; m[M_S + 1] += sy; m[M_S + 2] += sz;
     m[M_UU] += ux * ux; m[M_UU + 1] += ux * uy; m[M_UU + 2] += ux * uz; m[M_UU + 3] += uy * uy; m[M_UU + 4] += uy * uz; m[M_UU + 5] += uz * uz;

@@ -1,0 +1,296 @@
+// host/cuda_modules.cpp — the registrable CUDA modules: thin C++ classes over the C ABI (include/b200reg.h).
+// Host matrices cross the boundary as plain pointers in Eigen's column-major layout; status codes come back and are
+// re-thrown as the libpointmatcher exception types callers already catch (Mapper.cpp:420 catches std::runtime_error).
+#include "cuda_modules.h"
+
+#include <map>
+#include <mutex>
+#include <thread>
+
+namespace b200 {
+
+typedef PM::Parametrizable P;
+
+// ---------------------------------------------------------------------------------------------------------------
+// contexts + error translation
+// ---------------------------------------------------------------------------------------------------------------
+b200reg_ctx* contextFor(int device) {
+  struct Holder {
+    std::map<int, b200reg_ctx*> ctxs;
+    ~Holder() { for (auto& kv : ctxs) b200reg_ctx_destroy(kv.second); }
+  };
+  thread_local Holder holder;   // one ctx per (thread, device): ctxs are not thread-safe, distinct ctxs are independent
+  auto it = holder.ctxs.find(device);
+  if (it != holder.ctxs.end()) return it->second;
+  b200reg_ctx* ctx = nullptr;
+  const int32_t st = b200reg_ctx_create(device, &ctx);
+  if (st != B200REG_OK) throw std::runtime_error("b200reg: no usable CUDA device " + std::to_string(device) + " (there is no CPU fallback)");
+  holder.ctxs[device] = ctx;
+  return ctx;
+}
+
+void throwStatus(b200reg_ctx* ctx, int32_t status) {
+  const std::string msg = b200reg_last_error(ctx);
+  switch (status) {
+    case B200REG_E_INVALID_PARAM: throw PM::InvalidParameter(msg);
+    case B200REG_E_INVALID_FIELD: throw PM::DataPoints::InvalidField(msg);
+    case B200REG_E_NOT_CONVERGED: throw PM::ConvergenceError(msg);
+    case B200REG_E_TRANSFORM: throw PM::TransformationError(msg);
+    default: throw std::runtime_error(msg.empty() ? "b200reg: error " + std::to_string(status) : msg);
+  }
+}
+static inline void check(b200reg_ctx* ctx, int32_t st) { if (st != B200REG_OK) throwStatus(ctx, st); }
+
+namespace {
+struct CloudGuard {   // frees a device cloud on scope exit (exceptions included)
+  b200reg_ctx* ctx;
+  b200reg_cloud* c = nullptr;
+  explicit CloudGuard(b200reg_ctx* x) : ctx(x) {}
+  ~CloudGuard() { if (c) b200reg_cloud_free(ctx, c); }
+};
+
+// DataPoints -> device cloud (features as they lie in memory; "normals" rows gathered into 3 floats per point)
+void upload(b200reg_ctx* ctx, const PM::DataPoints& dp, bool withNormals, CloudGuard& g) {
+  const int64_t n = dp.features.cols();
+  std::vector<float> normals;
+  const float* np = nullptr;
+  if (withNormals && dp.descriptorExists("normals") && n > 0) {
+    const int row = dp.getDescriptorStartingRow("normals");
+    normals.resize(3 * (size_t)n);
+    for (int64_t c = 0; c < n; ++c) for (int r = 0; r < 3; ++r) normals[3 * c + r] = dp.descriptors(row + r, c);
+    np = normals.data();
+  }
+  check(ctx, b200reg_cloud_upload_f32(ctx, dp.features.data(), (int32_t)dp.features.rows(), np, n, &g.c));
+}
+
+std::vector<float> normalsOf(const PM::DataPoints& dp) {
+  std::vector<float> out;
+  if (!dp.descriptorExists("normals")) return out;
+  const int64_t n = dp.features.cols();
+  const int row = dp.getDescriptorStartingRow("normals");
+  out.resize(3 * (size_t)n);
+  for (int64_t c = 0; c < n; ++c) for (int r = 0; r < 3; ++r) out[3 * c + r] = dp.descriptors(row + r, c);
+  return out;
+}
+}  // namespace
+
+// ---------------------------------------------------------------------------------------------------------------
+// CudaVoxelGridDataPointsFilter
+// ---------------------------------------------------------------------------------------------------------------
+const PM::ParametersDoc CudaVoxelGridDataPointsFilter::availableParameters() {
+  return {{"vSizeX", "Dimension of each voxel cell in x direction", "1.0", "0.001", "+inf", &P::Comp<float>},
+          {"vSizeY", "Dimension of each voxel cell in y direction", "1.0", "0.001", "+inf", &P::Comp<float>},
+          {"vSizeZ", "Dimension of each voxel cell in z direction", "1.0", "0.001", "+inf", &P::Comp<float>},
+          {"useCentroid", "If 1 (true), down-sample by using centroid of voxel cell.  If false (0), use center of voxel cell.", "1", "0", "1", P::Comp<bool>},
+          {"averageExistingDescriptors", "whether the filter keep the existing point descriptors and average them or should it drop them", "1", "0", "1", P::Comp<bool>},
+          {"device", "CUDA device ordinal", "0", "0", "1023", &P::Comp<int>}};
+}
+CudaVoxelGridDataPointsFilter::CudaVoxelGridDataPointsFilter(const PM::Parameters& params)
+    : PM::DataPointsFilter("CudaVoxelGridDataPointsFilter", availableParameters(), params), vSizeX(get<float>("vSizeX")), vSizeY(get<float>("vSizeY")),
+      vSizeZ(get<float>("vSizeZ")), useCentroid(get<bool>("useCentroid")), averageExistingDescriptors(get<bool>("averageExistingDescriptors")),
+      device(get<int>("device")) {}
+PM::DataPoints CudaVoxelGridDataPointsFilter::filter(const PM::DataPoints& input) { PM::DataPoints o(input); inPlaceFilter(o); return o; }
+void CudaVoxelGridDataPointsFilter::inPlaceFilter(PM::DataPoints& cloud) {
+  if (cloud.features.rows() != 4) throw PM::InvalidParameter("CudaVoxelGridDataPointsFilter: only 3D clouds (4 x N features) are supported");
+  // descriptors other than "normals" do not live on the device: refuse rather than silently drop them (VoxelGrid.cpp:81-89 validates too)
+  size_t dsum = 0;
+  for (auto& l : cloud.descriptorLabels) dsum += l.span;
+  if ((int64_t)dsum != cloud.descriptors.rows()) throw PM::DataPoints::InvalidField("VoxelGridDataPointsFilter: Error, descriptor labels do not match descriptor data");
+  for (auto& l : cloud.descriptorLabels)
+    if (l.text != "normals") throw PM::DataPoints::InvalidField("CudaVoxelGridDataPointsFilter: descriptor '" + l.text + "' is not carried on the device (only 'normals')");
+  if (cloud.times.rows() != 0) throw PM::DataPoints::InvalidField("CudaVoxelGridDataPointsFilter: times are not carried on the device");
+  b200reg_ctx* ctx = contextFor(device);
+  CloudGuard g(ctx);
+  upload(ctx, cloud, true, g);
+  check(ctx, b200reg_voxelgrid(ctx, g.c, vSizeX, vSizeY, vSizeZ, useCentroid, averageExistingDescriptors));
+  const int64_t m = b200reg_cloud_size(g.c);
+  const bool hasN = cloud.descriptorExists("normals");
+  std::vector<float> nrm(hasN ? 3 * (size_t)m : 0);
+  cloud.conservativeResize(m);
+  check(ctx, b200reg_cloud_download_f32(ctx, g.c, cloud.features.data(), 4, hasN ? nrm.data() : nullptr));
+  if (hasN) {
+    const int row = cloud.getDescriptorStartingRow("normals");
+    for (int64_t c = 0; c < m; ++c) for (int r = 0; r < 3; ++r) cloud.descriptors(row + r, c) = nrm[3 * c + r];
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// CudaSurfaceNormalDataPointsFilter
+// ---------------------------------------------------------------------------------------------------------------
+const PM::ParametersDoc CudaSurfaceNormalDataPointsFilter::availableParameters() {
+  return {{"knn", "number of nearest neighbors to consider, including the point itself", "5", "3", "2147483647", &P::Comp<unsigned>},
+          {"maxDist", "maximum distance to consider for neighbors", "inf", "0", "inf", &P::Comp<float>},
+          {"epsilon", "approximation to use for the nearest-neighbor search", "0", "0", "inf", &P::Comp<float>},
+          {"keepNormals", "whether the normals should be added as descriptors to the resulting cloud", "1"},
+          {"keepDensities", "whether the point densities should be added as descriptors to the resulting cloud", "0"},
+          {"keepEigenValues", "whether the eigen values should be added as descriptors to the resulting cloud", "0"},
+          {"keepEigenVectors", "whether the eigen vectors should be added as descriptors to the resulting cloud", "0"},
+          {"keepMatchedIds", "whether the identifiers of matches points should be added as descriptors to the resulting cloud", "0"},
+          {"keepMeanDist", "whether the distance to the nearest neighbor mean should be added as descriptors to the resulting cloud", "0"},
+          {"keepSurfaceDescriptors", "whether local surface descriptors (linearity, planarity and curvature) should be added to the resulting cloud", "1"},
+          {"sortEigen", "whether the eigenvalues and eigenvectors should be sorted (ascending) based on the eigenvalues", "0"},
+          {"smoothNormals", "whether the normal vector should be average with the nearest neighbors", "0"},
+          {"device", "CUDA device ordinal", "0", "0", "1023", &P::Comp<int>}};
+}
+CudaSurfaceNormalDataPointsFilter::CudaSurfaceNormalDataPointsFilter(const PM::Parameters& params)
+    : PM::DataPointsFilter("CudaSurfaceNormalDataPointsFilter", availableParameters(), params), knn(get<unsigned>("knn")), maxDist(get<float>("maxDist")),
+      epsilon(get<float>("epsilon")), keepNormals(get<bool>("keepNormals")), keepDensities(get<bool>("keepDensities")),
+      keepEigenValues(get<bool>("keepEigenValues")), keepEigenVectors(get<bool>("keepEigenVectors")), keepMatchedIds(get<bool>("keepMatchedIds")),
+      keepMeanDist(get<bool>("keepMeanDist")), keepSurfaceDescriptors(get<bool>("keepSurfaceDescriptors")), sortEigen(get<bool>("sortEigen")),
+      smoothNormals(get<bool>("smoothNormals")), device(get<int>("device")) {
+  // descriptors this round's kernel does not produce are refused loudly instead of being left uninitialised
+  if (keepEigenVectors || keepMatchedIds || keepMeanDist) throw PM::InvalidParameter("CudaSurfaceNormalDataPointsFilter: keepEigenVectors / keepMatchedIds / keepMeanDist are not produced by the device kernel yet");
+  if (smoothNormals) throw PM::InvalidParameter("CudaSurfaceNormalDataPointsFilter: smoothNormals is not supported (order-dependent in the reference, SURVEY 9.5)");
+}
+PM::DataPoints CudaSurfaceNormalDataPointsFilter::filter(const PM::DataPoints& input) { PM::DataPoints o(input); inPlaceFilter(o); return o; }
+void CudaSurfaceNormalDataPointsFilter::inPlaceFilter(PM::DataPoints& cloud) {
+  if (cloud.features.rows() != 4) throw PM::InvalidParameter("CudaSurfaceNormalDataPointsFilter: only 3D clouds (4 x N features) are supported");
+  size_t dsum = 0;
+  for (auto& l : cloud.descriptorLabels) dsum += l.span;
+  if ((int64_t)dsum != cloud.descriptors.rows()) throw PM::DataPoints::InvalidField("SurfaceNormalDataPointsFilter: Error, descriptor labels do not match descriptor data");
+  const int64_t n = cloud.features.cols();
+  // label order of the reference (SurfaceNormal.cpp:126-144); allocateDescriptor reuses / appends like DataPoints::allocateFields
+  int rowN = -1, rowD = -1, rowE = -1, rowL = -1, rowP = -1, rowC = -1;
+  if (keepNormals) rowN = cloud.allocateDescriptor("normals", 3);
+  if (keepDensities) rowD = cloud.allocateDescriptor("densities", 1);
+  if (keepEigenValues) rowE = cloud.allocateDescriptor("eigValues", 3);
+  if (keepSurfaceDescriptors) { rowL = cloud.allocateDescriptor("linearity", 1); rowP = cloud.allocateDescriptor("planarity", 1); rowC = cloud.allocateDescriptor("curvature", 1); }
+  if (n == 0) return;
+  b200reg_ctx* ctx = contextFor(device);
+  CloudGuard g(ctx);
+  check(ctx, b200reg_cloud_upload_f32(ctx, cloud.features.data(), 4, nullptr, n, &g.c));
+  std::vector<float> dens(keepDensities ? (size_t)n : 0), eig(keepEigenValues ? 3 * (size_t)n : 0), lpc(keepSurfaceDescriptors ? 3 * (size_t)n : 0), nrm(3 * (size_t)n);
+  int32_t degenerate = 0;
+  check(ctx, b200reg_surface_normals(ctx, g.c, (int32_t)knn, maxDist, epsilon, nullptr, keepDensities ? dens.data() : nullptr,
+                                     keepEigenValues ? eig.data() : nullptr, keepSurfaceDescriptors ? lpc.data() : nullptr, &degenerate));
+  check(ctx, b200reg_cloud_download_f32(ctx, g.c, nullptr, 4, nrm.data()));
+  for (int64_t c = 0; c < n; ++c) {
+    if (keepNormals) for (int r = 0; r < 3; ++r) cloud.descriptors(rowN + r, c) = nrm[3 * c + r];
+    if (keepDensities) cloud.descriptors(rowD, c) = dens[c];
+    if (keepEigenValues) for (int r = 0; r < 3; ++r) cloud.descriptors(rowE + r, c) = eig[3 * c + r];   // ascending (documented order; sortEigen is therefore always honoured)
+    if (keepSurfaceDescriptors) { cloud.descriptors(rowL, c) = lpc[3 * c]; cloud.descriptors(rowP, c) = lpc[3 * c + 1]; cloud.descriptors(rowC, c) = lpc[3 * c + 2]; }
+  }
+  (void)degenerate;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// CudaKDTreeMatcher
+// ---------------------------------------------------------------------------------------------------------------
+const PM::ParametersDoc CudaKDTreeMatcher::availableParameters() {
+  return {{"knn", "number of nearest neighbors to consider it the reference", "1", "1", "2147483647", &P::Comp<unsigned>},
+          {"epsilon", "approximation to use for the nearest-neighbor search (accepted, treated as 0: the search is exact)", "0", "0", "inf", &P::Comp<float>},
+          {"searchType", "Nabo search type (accepted for YAML compatibility, ignored: the index is a radix-sorted voxel grid)", "1", "0", "2", &P::Comp<unsigned>},
+          {"maxDist", "maximum distance to consider for neighbors", "inf", "0", "inf", &P::Comp<float>},
+          {"cell", "voxel-grid cell size in metres; 0 = automatic", "0", "0", "inf", &P::Comp<float>},
+          {"device", "CUDA device ordinal", "0", "0", "1023", &P::Comp<int>}};
+}
+CudaKDTreeMatcher::CudaKDTreeMatcher(const PM::Parameters& params)
+    : PM::Matcher("CudaKDTreeMatcher", availableParameters(), params), knn((int)get<unsigned>("knn")), epsilon(get<float>("epsilon")),
+      searchType(get<unsigned>("searchType")), maxDist(get<float>("maxDist")), cell(get<float>("cell")), device(get<int>("device")) {}
+CudaKDTreeMatcher::~CudaKDTreeMatcher() {
+  if (index) b200reg_index_free(contextFor(device), index);
+}
+void CudaKDTreeMatcher::init(const PM::DataPoints& filteredReference) {   // MatchersImpl.cpp:109-114
+  b200reg_ctx* ctx = contextFor(device);
+  if (index) { b200reg_index_free(ctx, index); index = nullptr; }
+  CloudGuard g(ctx);
+  upload(ctx, filteredReference, true, g);
+  check(ctx, b200reg_index_build(ctx, g.c, cell, &index));   // the index keeps its own sorted copy; the cloud can go
+}
+PM::Matches CudaKDTreeMatcher::findClosests(const PM::DataPoints& filteredReading) {   // MatchersImpl.cpp:117-132
+  if (!index) throw std::runtime_error("CudaKDTreeMatcher: init() must be called before findClosests()");
+  b200reg_ctx* ctx = contextFor(device);
+  const int64_t n = filteredReading.features.cols();
+  PM::Matches matches(knn, n);
+  CloudGuard g(ctx);
+  upload(ctx, filteredReading, false, g);
+  uint64_t visits = 0;
+  check(ctx, b200reg_knn(ctx, index, g.c, nullptr, knn, maxDist, epsilon, 1 /*ALLOW_SELF_MATCH*/, matches.ids.data(), matches.dists.data(), &visits));
+  this->visitCounter += (unsigned long)visits;
+  return matches;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// CudaTrimmedDistOutlierFilter / CudaSurfaceNormalOutlierFilter
+// ---------------------------------------------------------------------------------------------------------------
+const PM::ParametersDoc CudaTrimmedDistOutlierFilter::availableParameters() {
+  return {{"ratio", "percentage to keep", "0.85", "0.0000001", "1.0", &P::Comp<float>}, {"device", "CUDA device ordinal", "0", "0", "1023", &P::Comp<int>}};
+}
+CudaTrimmedDistOutlierFilter::CudaTrimmedDistOutlierFilter(const PM::Parameters& params)
+    : PM::OutlierFilter("CudaTrimmedDistOutlierFilter", availableParameters(), params), ratio(get<float>("ratio")), device(get<int>("device")) {}
+PM::OutlierWeights CudaTrimmedDistOutlierFilter::compute(const PM::DataPoints&, const PM::DataPoints&, const PM::Matches& input) {
+  b200reg_ctx* ctx = contextFor(device);
+  PM::OutlierWeights w(input.dists.rows(), input.dists.cols());
+  float tau = 0.f;
+  check(ctx, b200reg_trimmed_dist(ctx, input.dists.data(), (int64_t)input.dists.d.size(), ratio, &tau, w.data()));
+  return w;
+}
+
+const PM::ParametersDoc CudaSurfaceNormalOutlierFilter::availableParameters() {
+  return {{"maxAngle", "Maximum authorised angle between the 2 surface normals (in radian)", "1.57", "0.0", "3.1416", &P::Comp<float>},
+          {"device", "CUDA device ordinal", "0", "0", "1023", &P::Comp<int>}};
+}
+CudaSurfaceNormalOutlierFilter::CudaSurfaceNormalOutlierFilter(const PM::Parameters& params)
+    : PM::OutlierFilter("CudaSurfaceNormalOutlierFilter", availableParameters(), params), maxAngle(get<float>("maxAngle")), device(get<int>("device")) {}
+PM::OutlierWeights CudaSurfaceNormalOutlierFilter::compute(const PM::DataPoints& filteredReading, const PM::DataPoints& filteredReference, const PM::Matches& input) {
+  b200reg_ctx* ctx = contextFor(device);
+  PM::OutlierWeights w(input.dists.rows(), input.dists.cols());
+  const std::vector<float> nr = normalsOf(filteredReading), nf = normalsOf(filteredReference);
+  check(ctx, b200reg_surface_normal_outlier(ctx, nr.empty() ? nullptr : nr.data(), nf.empty() ? nullptr : nf.data(), filteredReference.features.cols(),
+                                            input.ids.data(), (int32_t)input.ids.rows(), input.ids.cols(), maxAngle, w.data()));
+  return w;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// CudaPointToPlaneErrorMinimizer
+// ---------------------------------------------------------------------------------------------------------------
+const PM::ParametersDoc CudaPointToPlaneErrorMinimizer::availableParameters() {
+  return {{"force2D", "If set to true(1), the minimization will be forced to give a solution in 2D (i.e., on the XY-plane) even with 3D inputs.", "0", "0", "1", &P::Comp<bool>},
+          {"force4DOF", "If set to true(1), the minimization will optimize only yaw and translation, pitch and roll will follow the prior.", "0", "0", "1", &P::Comp<bool>},
+          {"device", "CUDA device ordinal", "0", "0", "1023", &P::Comp<int>}};
+}
+CudaPointToPlaneErrorMinimizer::CudaPointToPlaneErrorMinimizer(const PM::Parameters& params)
+    : PM::ErrorMinimizer("CudaPointToPlaneErrorMinimizer", availableParameters(), params), force2D(get<bool>("force2D")), force4DOF(get<bool>("force4DOF")),
+      device(get<int>("device")) {}
+PM::TransformationParameters CudaPointToPlaneErrorMinimizer::compute(const PM::DataPoints& filteredReading, const PM::DataPoints& filteredReference,
+                                                                     const PM::OutlierWeights& outlierWeights, const PM::Matches& matches) {
+  b200reg_ctx* ctx = contextFor(device);
+  if (!filteredReference.descriptorExists("normals")) throw PM::DataPoints::InvalidField("Field normals not found");   // PointToPlane.cpp:115
+  CloudGuard gr(ctx), gf(ctx);
+  upload(ctx, filteredReading, false, gr);
+  upload(ctx, filteredReference, true, gf);
+  double A[36], b[6];
+  b200reg_step_stats st;
+  check(ctx, b200reg_point_to_plane(ctx, gr.c, gf.c, matches.ids.data(), matches.dists.data(), outlierWeights.data(), (int32_t)matches.ids.rows(),
+                                    force2D ? 1 : 0, A, b, &st));
+  this->pointUsedRatio = st.point_used_ratio;
+  this->weightedPointUsedRatio = st.weighted_point_used_ratio;
+  float T[16];
+  b200reg_solve_point_to_plane(A, b, st.mean_reading, st.mean_reference, force2D ? 1 : 0, force4DOF ? 1 : 0, T, nullptr);
+  PM::TransformationParameters out(4, 4);
+  for (int i = 0; i < 4; ++i) for (int j = 0; j < 4; ++j) out(i, j) = T[4 * i + j];
+  return out;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// registration (the ADD_TO_REGISTRAR lines a maintainer adds to Registry.cpp, or calls out-of-tree — INTEGRATION.md)
+// ---------------------------------------------------------------------------------------------------------------
+void registerCudaModules(PM& pm) {
+  using PointMatcherSupport::Registrar;
+  auto& DataPointsFilterRegistrar = pm.DataPointsFilterRegistrar;
+  auto& MatcherRegistrar = pm.MatcherRegistrar;
+  auto& OutlierFilterRegistrar = pm.OutlierFilterRegistrar;
+  auto& ErrorMinimizerRegistrar = pm.ErrorMinimizerRegistrar;
+  typedef PM::DataPointsFilter DataPointsFilter;
+  typedef PM::Matcher Matcher;
+  typedef PM::OutlierFilter OutlierFilter;
+  typedef PM::ErrorMinimizer ErrorMinimizer;
+  ADD_TO_REGISTRAR(DataPointsFilter, CudaVoxelGridDataPointsFilter, CudaVoxelGridDataPointsFilter)
+  ADD_TO_REGISTRAR(DataPointsFilter, CudaSurfaceNormalDataPointsFilter, CudaSurfaceNormalDataPointsFilter)
+  ADD_TO_REGISTRAR(Matcher, CudaKDTreeMatcher, CudaKDTreeMatcher)
+  ADD_TO_REGISTRAR(OutlierFilter, CudaTrimmedDistOutlierFilter, CudaTrimmedDistOutlierFilter)
+  ADD_TO_REGISTRAR(OutlierFilter, CudaSurfaceNormalOutlierFilter, CudaSurfaceNormalOutlierFilter)
+  ADD_TO_REGISTRAR(ErrorMinimizer, CudaPointToPlaneErrorMinimizer, CudaPointToPlaneErrorMinimizer)
+}
+
+}  // namespace b200

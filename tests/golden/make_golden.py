@@ -67,6 +67,19 @@ def main():
         gold[name] = np.loadtxt(f"{REF}/examples/data/icp_data/{name}.ref_trans").tolist()
     with open(f"{OUT}/golden_transforms.json", "w") as f:
         json.dump(gold, f, indent=1)
+    # ICP chain configuration files (data fixtures): the YAML the registrable-module boundary has to load
+    ydir = os.path.join(OUT, "yaml")
+    os.makedirs(ydir, exist_ok=True)
+    import shutil
+    for rel in ["libpointmatcher/examples/data/default.yaml", "libpointmatcher/examples/data/default-identity.yaml",
+                "libpointmatcher/examples/data/icp_point_to_plane.yaml",
+                "libpointmatcher/examples/data/icp_data/defaultPointToPlaneMinDistDataPointsFilter.yaml",
+                "libpointmatcher/examples/data/icp_data/force4DOFForPointToPlaneMinimizer.yaml",
+                "libpointmatcher/examples/data/unit_tests/badIcpConfig_InvalidModuleType.yaml",
+                "libpointmatcher/examples/data/unit_tests/badIcpConfig_InvalidParameter.yaml",
+                "open3d_slam_rsl/ros/open3d_slam_ros/param/icp.yaml"]:
+        dst = os.path.basename(rel) if "open3d_slam" not in rel else "open3d_slam_icp.yaml"
+        shutil.copyfile(os.path.join("/root/reference", rel), os.path.join(ydir, dst))
     print("car_cloud400", d400.shape, "car_cloud401", d401.shape, "cloud0", c0.shape, "cloud1", c1.shape)
 
 
