@@ -156,7 +156,8 @@ def test_default_chain_on_car_clouds(shim, oracle, golden):
     icp = shim.ICP()
     icp.set_default()
     T, s = icp(q, ref, None, None, rn)
-    code, T_o, st_o = oracle.icp(oracle.icp_config(precision=oracle.ORC_MIXED, nthreads=8), ref, rn, q)
+    # module defaults (TransformationCheckersImpl.h:90-92): minDiffRotErr 0.001, minDiffTransErr 0.001, smoothLength 3; Counter 40; ratio 0.85
+    code, T_o, st_o = oracle.icp(oracle.icp_config(min_diff_trans=0.001, precision=oracle.ORC_MIXED, nthreads=8), ref, rn, q)
     assert s["fast_lane"] and s["iterations"] == st_o.iterations
     _assert_same_T(T, T_o)
     V = golden["T"]["validT3d"]
@@ -208,7 +209,7 @@ def test_filters_by_name_match_oracle(shim, oracle, golden):
     assert [l[0] for l in labels] == ["normals", "densities", "eigValues", "linearity", "planarity", "curvature"]
     dot = np.abs(np.sum(n2.astype(np.float64) * o["normals"], axis=1))
     ok = ~np.all(o["normals"] == 0, axis=1)
-    assert np.all(dot[ok] > 1 - 1e-9)
+    assert np.all(dot[ok] > 1 - 1e-6)      # fp32 storage of unit normals
     with pytest.raises(shim.InvalidParameter):
         shim.apply_filter("CudaSurfaceNormalDataPointsFilter", {"knn": 5, "keepMatchedIds": 1}, pts)
 
