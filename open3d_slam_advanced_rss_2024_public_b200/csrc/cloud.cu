@@ -1,4 +1,6 @@
 // csrc/cloud.cu — context, device clouds (DataPoints mirror), uploads/downloads, RigidTransformation.
+#include <cstdlib>
+
 #include "common.cuh"
 
 int setErr(b200reg_ctx* ctx, int code, const char* fmt, ...) {
@@ -113,6 +115,8 @@ int32_t b200reg_ctx_create(int32_t device, b200reg_ctx** out) {
   if (cudaMalloc(&ctx->dstate, 65536) != cudaSuccess) { delete ctx; return B200REG_E_OOM; }
   cudaMemsetAsync(ctx->dstate, 0, 65536, ctx->stream);
   if (ensurePinned(ctx, 1 << 16) != B200REG_OK) { delete ctx; return B200REG_E_OOM; }
+  const char* one = getenv("B200REG_KNN_ONE_THREAD");
+  ctx->knnOneThread = (one && one[0] == '1') ? 1 : 0;
   *out = ctx;
   return B200REG_OK;
 }

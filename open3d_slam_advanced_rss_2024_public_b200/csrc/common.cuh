@@ -28,6 +28,7 @@ struct b200reg_ctx {
   // scratch
   DevBuf keys0, keys1, vals0, vals1, cubtmp, misc, partials, matchIds, matchD2, matchPos, flags, flush;
   int flushToggle = 0;
+  int knnOneThread = 0;      // debug/A-B switch (env B200REG_KNN_ONE_THREAD=1): k = 1 through the one-thread-per-query kernel
   void* pinned = nullptr;   // pinned host staging for small D2H results
   size_t pinned_cap = 0;
   void* dstate = nullptr;   // small device state block (select state, counters)
