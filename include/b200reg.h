@@ -55,6 +55,17 @@ uint64_t b200reg_ctx_launch_count(const b200reg_ctx* ctx);
 int32_t b200reg_ctx_timer_start(b200reg_ctx* ctx);
 int32_t b200reg_ctx_timer_stop(b200reg_ctx* ctx, float* elapsed_ms);   /* synchronises on the stop event */
 int32_t b200reg_ctx_flush_l2(b200reg_ctx* ctx);
+/* kernel-only timing of the match kernel (the roofline's dominant kernel): while profiling is on, every k-NN launch on this
+ * ctx — standalone or inside b200reg_icp_register — is bracketed by its own CUDA event pair on the ctx stream (up to 256
+ * launches; the graph-driven registration loop is replaced by the host-driven one so the brackets exist).
+ * profile_read synchronises, writes the per-launch durations in launch order, and clears the list. */
+int32_t b200reg_ctx_set_profiling(b200reg_ctx* ctx, int32_t on);
+int32_t b200reg_ctx_profile_read(b200reg_ctx* ctx, float* ms_out, int32_t cap, int32_t* count);
+/* device-side trace of the graph-resident registration loop (a profiler does not see inside a conditional graph node): while
+ * on, the first thread of every kernel of the loop stamps %globaltimer.  trace_read returns the stamps of the LAST
+ * registration: (kernel tag << 56) | nanoseconds; tags 1 match, 2-4 select passes, 5 reduce, 6 tail start, 7 tail end. */
+int32_t b200reg_ctx_set_trace(b200reg_ctx* ctx, int32_t on);
+int32_t b200reg_ctx_trace_read(b200reg_ctx* ctx, uint64_t* out, int32_t cap, int32_t* count);
 
 /* ---- clouds: replaces DataPoints construction/copies (PointMatcher.h:229-431) and open3dToPointmatcher
  *      (open3d_slam_rsl/open3d_utils/open3d_conversions/src/open3d_conversions.cpp:21-118) -------------------------- */

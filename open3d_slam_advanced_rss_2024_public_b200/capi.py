@@ -90,6 +90,10 @@ SYMBOLS = {
     "b200reg_ctx_timer_start": (C.c_int32, [_VP]),
     "b200reg_ctx_timer_stop": (C.c_int32, [_VP, C.POINTER(C.c_float)]),
     "b200reg_ctx_flush_l2": (C.c_int32, [_VP]),
+    "b200reg_ctx_set_profiling": (C.c_int32, [_VP, C.c_int32]),
+    "b200reg_ctx_profile_read": (C.c_int32, [_VP, _VP, C.c_int32, C.POINTER(C.c_int32)]),
+    "b200reg_ctx_set_trace": (C.c_int32, [_VP, C.c_int32]),
+    "b200reg_ctx_trace_read": (C.c_int32, [_VP, _VP, C.c_int32, C.POINTER(C.c_int32)]),
     "b200reg_cloud_upload_f32": (C.c_int32, [_VP, _VP, C.c_int32, _VP, C.c_int64, C.POINTER(_VP)]),
     "b200reg_cloud_upload_f64": (C.c_int32, [_VP, _VP, _VP, C.c_int64, C.POINTER(_VP)]),
     "b200reg_cloud_download_f32": (C.c_int32, [_VP, _VP, _VP, C.c_int32, _VP]),
@@ -200,6 +204,27 @@ class Context:
 
     def flush_l2(self):
         self.check(lib().b200reg_ctx_flush_l2(self.h))
+
+    def set_profiling(self, on=True):
+        """Bracket every match-kernel launch with its own CUDA event pair (kernel-only time for the roofline)."""
+        self.check(lib().b200reg_ctx_set_profiling(self.h, int(on)))
+
+    def profile_read(self, cap=256):
+        ms = np.zeros(cap, dtype=np.float32)
+        cnt = C.c_int32(0)
+        self.check(lib().b200reg_ctx_profile_read(self.h, _p(ms), cap, C.byref(cnt)))
+        return ms[:cnt.value].copy()
+
+    def set_trace(self, on=True):
+        self.check(lib().b200reg_ctx_set_trace(self.h, int(on)))
+
+    def trace_read(self, cap=2047):
+        """[(tag, t_ns)] stamped by the kernels of the last graph-resident registration."""
+        buf = np.zeros(cap, dtype=np.uint64)
+        cnt = C.c_int32(0)
+        self.check(lib().b200reg_ctx_trace_read(self.h, _p(buf), cap, C.byref(cnt)))
+        v = buf[:cnt.value]
+        return [(int(x >> np.uint64(56)), int(x & np.uint64(0x00ffffffffffffff))) for x in v]
 
     @property
     def launch_count(self):

@@ -27,6 +27,13 @@ int ensureBuf(b200reg_ctx* ctx, DevBuf& b, size_t bytes) {
   return B200REG_OK;
 }
 
+void profBegin(b200reg_ctx* ctx) {
+  if (ctx->profile && ctx->profCount < B200_PROF_MAX) cudaEventRecord(ctx->profEv[2 * ctx->profCount], ctx->stream);
+}
+void profEnd(b200reg_ctx* ctx) {
+  if (ctx->profile && ctx->profCount < B200_PROF_MAX) { cudaEventRecord(ctx->profEv[2 * ctx->profCount + 1], ctx->stream); ++ctx->profCount; }
+}
+
 int ensurePinned(b200reg_ctx* ctx, size_t bytes) {
   if (bytes <= ctx->pinned_cap) return B200REG_OK;
   if (ctx->pinned) {
@@ -115,9 +122,53 @@ int32_t b200reg_ctx_create(int32_t device, b200reg_ctx** out) {
   if (cudaMalloc(&ctx->dstate, 65536) != cudaSuccess) { delete ctx; return B200REG_E_OOM; }
   cudaMemsetAsync(ctx->dstate, 0, 65536, ctx->stream);
   if (ensurePinned(ctx, 1 << 16) != B200REG_OK) { delete ctx; return B200REG_E_OOM; }
-  const char* one = getenv("B200REG_KNN_ONE_THREAD");
-  ctx->knnOneThread = (one && one[0] == '1') ? 1 : 0;
+  const char* hl = getenv("B200REG_HOST_LOOP");
+  ctx->hostLoop = (hl && hl[0] == '1') ? 1 : 0;
+  const char* lanes = getenv("B200REG_KNN_LANES");
+  if (lanes && (lanes[0] == '1' || lanes[0] == '4' || lanes[0] == '8')) ctx->knnLanes = lanes[0] - '0';
   *out = ctx;
+  return B200REG_OK;
+}
+
+int32_t b200reg_ctx_set_profiling(b200reg_ctx* ctx, int32_t on) {
+  if (!ctx) return B200REG_E_INVALID_PARAM;
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  if (on && !ctx->profEv) {
+    ctx->profEv = new cudaEvent_t[2 * B200_PROF_MAX];
+    for (int i = 0; i < 2 * B200_PROF_MAX; ++i) CUDA_TRY(ctx, cudaEventCreate(&ctx->profEv[i]));
+  }
+  ctx->profile = on ? 1 : 0;
+  ctx->profCount = 0;
+  return B200REG_OK;
+}
+
+int32_t b200reg_ctx_profile_read(b200reg_ctx* ctx, float* ms_out, int32_t cap, int32_t* count) {
+  if (!ctx || !count) return B200REG_E_INVALID_PARAM;
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  int n = ctx->profCount < cap ? ctx->profCount : cap;
+  for (int i = 0; i < n; ++i) CUDA_TRY(ctx, cudaEventElapsedTime(&ms_out[i], ctx->profEv[2 * i], ctx->profEv[2 * i + 1]));
+  *count = n;
+  ctx->profCount = 0;
+  return B200REG_OK;
+}
+
+int32_t b200reg_ctx_set_trace(b200reg_ctx* ctx, int32_t on) {
+  if (!ctx) return B200REG_E_INVALID_PARAM;
+  ctx->trace = on ? 1 : 0;
+  return B200REG_OK;
+}
+
+int32_t b200reg_ctx_trace_read(b200reg_ctx* ctx, uint64_t* out, int32_t cap, int32_t* count) {
+  if (!ctx || !count || cap < 0) return B200REG_E_INVALID_PARAM;
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  unsigned long long cnt = 0;
+  CUDA_TRY(ctx, cudaMemcpy(&cnt, (char*)ctx->dstate + DSTATE_TRACE_OFF, sizeof(cnt), cudaMemcpyDeviceToHost));
+  int n = (int)(cnt < (unsigned long long)TRACE_MAX ? cnt : TRACE_MAX);
+  if (n > cap) n = cap;
+  if (n > 0) CUDA_TRY(ctx, cudaMemcpy(out, (char*)ctx->dstate + DSTATE_TRACE_OFF + 8, sizeof(uint64_t) * (size_t)n, cudaMemcpyDeviceToHost));
+  *count = n;
   return B200REG_OK;
 }
 
@@ -125,6 +176,10 @@ void b200reg_ctx_destroy(b200reg_ctx* ctx) {
   if (!ctx) return;
   cudaSetDevice(ctx->device);
   cudaStreamSynchronize(ctx->stream);
+  if (ctx->profEv) {
+    for (int i = 0; i < 2 * B200_PROF_MAX; ++i) cudaEventDestroy(ctx->profEv[i]);
+    delete[] ctx->profEv;
+  }
   DevBuf* bufs[] = {&ctx->keys0, &ctx->keys1, &ctx->vals0, &ctx->vals1, &ctx->cubtmp, &ctx->misc, &ctx->partials,
                     &ctx->matchIds, &ctx->matchD2, &ctx->matchPos, &ctx->flags, &ctx->flush};
   for (DevBuf* b : bufs)

@@ -4,6 +4,7 @@
 #include <stdint.h>
 
 #include <cstdarg>
+#include <cstddef>
 #include <cstdio>
 #include <cstring>
 
@@ -11,6 +12,7 @@
 
 #include "../../include/b200reg.h"
 
+#define B200_PROF_MAX 256
 #define B200_SM_COUNT 148   // B200: 2 dies x 74 SMs; grids are sized in multiples of this
 
 struct DevBuf {   // growable device scratch (never shrinks; freed with the ctx)
@@ -28,7 +30,12 @@ struct b200reg_ctx {
   // scratch
   DevBuf keys0, keys1, vals0, vals1, cubtmp, misc, partials, matchIds, matchD2, matchPos, flags, flush;
   int flushToggle = 0;
-  int knnOneThread = 0;      // debug/A-B switch (env B200REG_KNN_ONE_THREAD=1): k = 1 through the one-thread-per-query kernel
+  int profile = 0;           // b200reg_ctx_set_profiling
+  int profCount = 0;
+  cudaEvent_t* profEv = nullptr;   // 2 x B200_PROF_MAX events, created on first use
+  int trace = 0;             // b200reg_ctx_set_trace: stamp kernel starts of the device-resident loop
+  int hostLoop = 0;          // env B200REG_HOST_LOOP=1: keep the ICP iterate loop on the host (A/B against the graph loop)
+  int knnLanes = 8;          // lanes per query of the k = 1 match kernel: 8, 4, or 1 (the general kernel); env B200REG_KNN_LANES for A/B runs
   void* pinned = nullptr;   // pinned host staging for small D2H results
   size_t pinned_cap = 0;
   void* dstate = nullptr;   // small device state block (select state, counters)
@@ -45,6 +52,7 @@ struct GridDesc {
   float ox, oy, oz;        // origin (bbox min of the centred reference)
   float cell, inv_cell;
   float slack;             // conservative bound on fp32 cell-assignment / bound-evaluation error (see knn.cu)
+  float ring2Safe;         // every point two or more cells away from the query's cell has d2 >= this
   int nx, ny, nz;
 };
 
@@ -58,9 +66,67 @@ struct b200reg_index {
   double build_ms = 0;
 };
 
+// ---- device-resident registration loop (CUDA-graph while node, icp.cu): everything a kernel of the loop body needs is read
+// from these two blocks in HBM, so ONE instantiated graph serves every reading size, reference and configuration.
+#define CHK_HIST 64   // transforms remembered by the DifferentialTransformationChecker ring (smoothLength <= CHK_HIST - 1)
+struct CheckerState {   // Counter / Differential / Bound checkers (TransformationCheckersImpl.cpp:58-225)
+  int counter;
+  int count;                 // transforms pushed so far
+  float rot[CHK_HIST][4];    // quaternions (w x y z), entry i at i % CHK_HIST
+  float tr[CHK_HIST][3];
+  float q0[4], t0[3];
+  int pad;
+};
+enum { ICPERR_NONE = 0, ICPERR_ROT_NAN, ICPERR_TRANS_NAN, ICPERR_BOUND, ICPERR_NO_QUANTILE, ICPERR_NO_POINTS, ICPERR_NOT_RIGID };
+struct IcpDevParams {   // written by the host once per registration
+  const float4* pts;
+  const float4* nrm;
+  const uint32_t* cellStart;
+  GridDesc g;
+  const float4* reading;
+  const float4* readingNrm;
+  long long n;
+  int* ids;
+  float* d2;
+  int* pos;
+  double* partials;
+  float maxd2, trimRatio, cosAngle;
+  int useTrim, useAngle, force2D, force4DOF;
+  int maxIter, smoothLength;
+  float minDiffRot, minDiffTrans, boundRot, boundTrans;
+  unsigned long long* trace;   // nullable: [0] = entry count, [1 + i] = (kernel tag << 56) | %globaltimer at the start of the i-th kernel of the loop
+};
+struct IcpDevState {    // initialised by the host, advanced by icpTailKernel every iteration, read back once at the end
+  float T[16];          // T_iter (row-major)
+  int iterate, errKind, iterations, maxIterReached;
+  float errA, errB, errC, errD;
+  double kept, valid;
+  float tau;
+  int pad;
+  unsigned long long visits;
+  CheckerState chk;
+};
+#define ICP_STATE_HEAD_BYTES offsetof(IcpDevState, chk)
+
+#define DSTATE_TRACE_OFF 16384   /* 1 + 2047 x uint64 inside ctx->dstate */
+#define TRACE_MAX 2047
+#ifdef __CUDACC__
+// device-side trace of the graph loop (ncu does not see inside a conditional node): one thread per kernel stamps its start
+__device__ __forceinline__ void traceStamp(unsigned long long* trace, unsigned tag) {
+  if (trace && blockIdx.x == 0 && threadIdx.x == 0) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    const unsigned long long i = atomicAdd(trace, 1ull);
+    if (i < TRACE_MAX) trace[1 + i] = ((unsigned long long)tag << 56) | (t & 0x00ffffffffffffffull);
+  }
+}
+#endif
 int setErr(b200reg_ctx* ctx, int code, const char* fmt, ...);
 int ensureBuf(b200reg_ctx* ctx, DevBuf& b, size_t bytes);
 int ensurePinned(b200reg_ctx* ctx, size_t bytes);
+// event bracket around the match kernel while profiling is on (no-ops otherwise)
+void profBegin(b200reg_ctx* ctx);
+void profEnd(b200reg_ctx* ctx);
 
 #define CUDA_TRY(ctx, expr)                                                                         \
   do {                                                                                              \

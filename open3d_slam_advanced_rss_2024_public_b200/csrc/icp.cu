@@ -2,10 +2,10 @@
 // (PointToPlane.cpp:185-368) and the TransformationCheckers (TransformationCheckersImpl.cpp:58-225).
 #include <chrono>
 #include <cmath>
-#include <vector>
 
 #include "icp_kernels.cuh"
 
+int launchKnn1Loop(b200reg_ctx* ctx, const IcpDevParams* P, const IcpDevState* S, int blocks);
 int runKnn(b200reg_ctx* ctx, const b200reg_index* ix, const float4* queries, int64_t n, const float* T, int k, float maxDist, int allowSelf);
 int cloudStats(b200reg_ctx* ctx, const b200reg_cloud* c, double sum[3], float mn[3], float mx[3]);
 int buildIndex(b200reg_ctx* ctx, const b200reg_cloud* ref, const float mean[3], const float bbMin[3], const float bbMax[3], float cell,
@@ -33,11 +33,11 @@ int enqueueStep(b200reg_ctx* ctx, const b200reg_index* ix, const float4* reading
   const bool useTrim = trimRatio > 0.f;
   if (useTrim) {
     const int blocks = (int)fmin((double)divUp(total, 256 * 4), (double)(2 * ctx->sm_count));
-    selectPassKernel<0><<<blocks, 256, 0, ctx->stream>>>((const float*)ctx->matchD2.p, total, trimRatio, st, histPtr(ctx));
+    selectPassKernel<0><<<blocks, 256, 0, ctx->stream>>>((const float*)ctx->matchD2.p, total, trimRatio, st, histPtr(ctx), nullptr);
     LAUNCH_CHECK(ctx);
-    selectPassKernel<1><<<blocks, 256, 0, ctx->stream>>>((const float*)ctx->matchD2.p, total, trimRatio, st, histPtr(ctx));
+    selectPassKernel<1><<<blocks, 256, 0, ctx->stream>>>((const float*)ctx->matchD2.p, total, trimRatio, st, histPtr(ctx), nullptr);
     LAUNCH_CHECK(ctx);
-    selectPassKernel<2><<<blocks, 256, 0, ctx->stream>>>((const float*)ctx->matchD2.p, total, trimRatio, st, histPtr(ctx));
+    selectPassKernel<2><<<blocks, 256, 0, ctx->stream>>>((const float*)ctx->matchD2.p, total, trimRatio, st, histPtr(ctx), nullptr);
     LAUNCH_CHECK(ctx);
   }
   ReduceParams P;
@@ -58,9 +58,9 @@ int enqueueStep(b200reg_ctx* ctx, const b200reg_index* ix, const float4* reading
   P.cosAngle = cosf(maxAngle);
   P.force2D = force2D;
   P.w = nullptr;
-  const int rblocks = (int)fmax(1.0, fmin((double)divUp(total, 256), (double)(4 * ctx->sm_count)));
+  const int rblocks = (int)fmax(1.0, fmin((double)divUp(total, 512), (double)(2 * ctx->sm_count)));
   TRY(ensureBuf(ctx, ctx->partials, sizeof(double) * NUM_MOM * (size_t)rblocks));
-  reduceKernel<<<rblocks, 256, 0, ctx->stream>>>(P, st, (double*)ctx->partials.p, &st->ticket[3], resultPtr(ctx));
+  reduceKernel<<<rblocks, 256, 0, ctx->stream>>>(P, st, (double*)ctx->partials.p, &st->ticket[3], resultPtr(ctx), nullptr, nullptr);
   LAUNCH_CHECK(ctx);
   HostStep* h = (HostStep*)ctx->pinned;
   CUDA_TRY(ctx, cudaMemcpyAsync(h->mom, resultPtr(ctx), sizeof(double) * NUM_MOM, cudaMemcpyDeviceToHost, ctx->stream));
@@ -69,14 +69,14 @@ int enqueueStep(b200reg_ctx* ctx, const b200reg_index* ix, const float4* reading
   return B200REG_OK;
 }
 
-inline void cross3(const double a[3], const double b[3], double o[3]) {
+__host__ __device__ inline void cross3(const double a[3], const double b[3], double o[3]) {
   o[0] = a[1] * b[2] - a[2] * b[1];
   o[1] = a[2] * b[0] - a[0] * b[2];
   o[2] = a[0] * b[1] - a[1] * b[0];
 }
 
 // un-centred moments -> A = G G^T, b = -G h^T on the matched-mean-centred pairs (PointToPlane.cpp:263-268,107-156)
-void momentsToSystem(const double* m, double A[36], double b[6], double meanR[3], double meanS[3]) {
+__host__ __device__ void momentsToSystem(const double* m, double A[36], double b[6], double meanR[3], double meanS[3]) {
   const double K = m[M_CNT];
   for (int d = 0; d < 3; ++d) { meanR[d] = m[M_R + d] / K; meanS[d] = m[M_S + d] / K; }
   double Suu[3][3] = {{m[M_UU], m[M_UU + 1], m[M_UU + 2]}, {m[M_UU + 1], m[M_UU + 3], m[M_UU + 4]}, {m[M_UU + 2], m[M_UU + 4], m[M_UU + 5]}};
@@ -123,7 +123,7 @@ void momentsToSystem(const double* m, double A[36], double b[6], double meanR[3]
 }
 
 // ---- dense helpers for the host solve (fp64) -------------------------------------------------------------------
-bool cholSolve(const double* A, const double* b, int n, double* x) {
+__host__ __device__ bool cholSolve(const double* A, const double* b, int n, double* x) {
   double L[36];
   for (int j = 0; j < n; ++j) {
     double d = A[j * n + j];
@@ -152,7 +152,7 @@ bool cholSolve(const double* A, const double* b, int n, double* x) {
 }
 
 // symmetric eigen-decomposition, cyclic Jacobi; eigenvalues on the diagonal of a, eigenvectors in columns of V
-void jacobiEig(double* a, double* V, int n) {
+__host__ __device__ void jacobiEig(double* a, double* V, int n) {
   for (int i = 0; i < n * n; ++i) V[i] = 0.0;
   for (int i = 0; i < n; ++i) V[i * n + i] = 1.0;
   for (int sweep = 0; sweep < 80; ++sweep) {
@@ -175,7 +175,80 @@ void jacobiEig(double* a, double* V, int n) {
 
 // solvePossiblyUnderdeterminedLinearSystem (PointToPlane.cpp:185-238): the invertibility decision uses the
 // reference's scalar (float) epsilon x size relative to the largest eigenvalue; singular -> minimum-norm solution.
-void solveSym(const double* A, const double* b, int n, double* x) {
+//
+// Fast decision (what makes the solve affordable for ONE device thread): for a symmetric positive definite A,
+// lambda_min >= 1 / ||A^-1||_F and lambda_max <= trace(A).  If 1 / ||A^-1||_F > eps * n * trace(A) the eigenvalue test of
+// the slow path would certainly report full rank, so the Cholesky solution it would return is returned directly; anything
+// closer to singular (or not positive definite) takes the eigen-decomposition path.  Sizes are template parameters so
+// the device compiler keeps the small matrices in registers.
+template <int N>
+__host__ __device__ __forceinline__ bool cholFactorT(const double* A, double* L) {
+#pragma unroll
+  for (int j = 0; j < N; ++j) {
+    double d = A[j * N + j];
+#pragma unroll
+    for (int k = 0; k < j; ++k) d -= L[j * N + k] * L[j * N + k];
+    if (!(d > 0.0)) return false;
+    d = sqrt(d);
+    L[j * N + j] = d;
+#pragma unroll
+    for (int i = j + 1; i < N; ++i) {
+      double s = A[i * N + j];
+#pragma unroll
+      for (int k = 0; k < j; ++k) s -= L[i * N + k] * L[j * N + k];
+      L[i * N + j] = s / d;
+    }
+  }
+  return true;
+}
+template <int N>
+__host__ __device__ __forceinline__ void cholSolveT(const double* L, const double* b, double* x) {
+  double y[N];
+#pragma unroll
+  for (int i = 0; i < N; ++i) {
+    double s = b[i];
+#pragma unroll
+    for (int k = 0; k < i; ++k) s -= L[i * N + k] * y[k];
+    y[i] = s / L[i * N + i];
+  }
+#pragma unroll
+  for (int i = N - 1; i >= 0; --i) {
+    double s = y[i];
+#pragma unroll
+    for (int k = i + 1; k < N; ++k) s -= L[k * N + i] * x[k];
+    x[i] = s / L[i * N + i];
+  }
+}
+template <int N>
+__host__ __device__ __forceinline__ bool certainlyFullRankT(const double* A, const double* L) {
+  double Li[N * N];   // L^-1 (lower triangular); A^-1 = Li^T Li
+#pragma unroll
+  for (int c = 0; c < N; ++c)
+#pragma unroll
+    for (int r = c; r < N; ++r) {
+      double s = (r == c) ? 1.0 : 0.0;
+#pragma unroll
+      for (int k = c; k < r; ++k) s -= L[r * N + k] * Li[k * N + c];
+      Li[r * N + c] = s / L[r * N + r];
+    }
+  double fro2 = 0.0, tr = 0.0;
+#pragma unroll
+  for (int r = 0; r < N; ++r) {
+    tr += A[r * N + r];
+#pragma unroll
+    for (int c = 0; c <= r; ++c) {   // symmetric: off-diagonal entries counted twice
+      double v = 0.0;
+#pragma unroll
+      for (int k = r; k < N; ++k) v += Li[k * N + r] * Li[k * N + c];
+      fro2 += (c == r) ? v * v : 2.0 * (v * v);
+    }
+  }
+  if (!(fro2 > 0.0) || !(tr > 0.0) || !(fro2 < 1.0e300)) return false;
+  const double rhs = 4.0 * 1.1920928955078125e-7 * N * tr;   // factor 4: margin over the rounding of this estimate
+  return 1.0 > rhs * rhs * fro2;
+}
+
+__host__ __device__ __noinline__ void solveSymSlow(const double* A, const double* b, int n, double* x) {
   double a[36], V[36];
   for (int i = 0; i < n * n; ++i) a[i] = A[i];
   jacobiEig(a, V, n);
@@ -196,8 +269,15 @@ void solveSym(const double* A, const double* b, int n, double* x) {
   }
 }
 
+template <int N>
+__host__ __device__ __forceinline__ void solveSym(const double* A, const double* b, double* x) {
+  double L[N * N];
+  if (cholFactorT<N>(A, L) && certainlyFullRankT<N>(A, L)) { cholSolveT<N>(L, b, x); return; }
+  solveSymSlow(A, b, N, x);
+}
+
 // ---- fp32 4x4 helpers (row-major), depth accumulated k = 0..3 ----------------------------------------------------
-void mul4(const float* a, const float* b, float* r) {
+__host__ __device__ void mul4(const float* a, const float* b, float* r) {
   float t[16];
   for (int i = 0; i < 4; ++i)
     for (int j = 0; j < 4; ++j) {
@@ -207,13 +287,13 @@ void mul4(const float* a, const float* b, float* r) {
       acc = acc + a[4 * i + 3] * b[12 + j];
       t[4 * i + j] = acc;
     }
-  memcpy(r, t, sizeof(t));
+  for (int i = 0; i < 16; ++i) r[i] = t[i];
 }
-bool rigidOk(const float* T) {
+__host__ __device__ bool rigidOk(const float* T) {
   const float det = T[0] * (T[5] * T[10] - T[6] * T[9]) - T[1] * (T[4] * T[10] - T[6] * T[8]) + T[2] * (T[4] * T[9] - T[5] * T[8]);
   return !(fabsf(1.f - det) > 0.001f);
 }
-void quatOf(const float* T, float q[4]) {   // Eigen::Quaternion(Matrix3): (w, x, y, z)
+__host__ __device__ void quatOf(const float* T, float q[4]) {   // Eigen::Quaternion(Matrix3): (w, x, y, z)
   float t = T[0] + T[5] + T[10];
   if (t > 0.f) {
     t = sqrtf(t + 1.f);
@@ -233,7 +313,7 @@ void quatOf(const float* T, float q[4]) {   // Eigen::Quaternion(Matrix3): (w, x
     q[1 + k] = (T[4 * k + i] + T[4 * i + k]) * t;
   }
 }
-float quatDist(const float a[4], const float b[4]) {   // QuaternionBase::angularDistance
+__host__ __device__ float quatDist(const float a[4], const float b[4]) {   // QuaternionBase::angularDistance
   const float bw = b[0], bx = -b[1], by = -b[2], bz = -b[3];
   const float w = a[0] * bw - a[1] * bx - a[2] * by - a[3] * bz;
   const float x = a[0] * bx + a[1] * bw + a[2] * bz - a[3] * by;
@@ -242,59 +322,77 @@ float quatDist(const float a[4], const float b[4]) {   // QuaternionBase::angula
   return 2.f * atan2f(sqrtf(x * x + y * y + z * z), fabsf(w));
 }
 
-struct Checkers {   // Counter / Differential / Bound (TransformationCheckersImpl.cpp:58-225)
-  const b200reg_icp_config& c;
-  int counter = 0;
-  std::vector<float> rot, tr;   // 4 / 3 floats per pushed transform
-  float q0[4], t0[3];
-  explicit Checkers(const b200reg_icp_config& cfg) : c(cfg) {}
-  void init(const float* T) {
-    counter = 0;
-    rot.clear(); tr.clear();
-    push(T);
-    quatOf(T, q0);
-    t0[0] = T[3]; t0[1] = T[7]; t0[2] = T[11];
+// Counter / Differential / Bound checkers (TransformationCheckersImpl.cpp:58-225) on a POD state, shared by the host-driven
+// loop and the device-resident one (icpTailKernel).
+struct CheckerCfg {
+  int maxIter, smoothLength;
+  float minDiffRot, minDiffTrans, boundRot, boundTrans;
+};
+__host__ __device__ void checkersPush(CheckerState& c, const float* T) {
+  const int slot = c.count % CHK_HIST;
+  quatOf(T, c.rot[slot]);
+  c.tr[slot][0] = T[3]; c.tr[slot][1] = T[7]; c.tr[slot][2] = T[11];
+  ++c.count;
+}
+__host__ __device__ void checkersInit(CheckerState& c, const float* T) {
+  c.counter = 0;
+  c.count = 0;
+  checkersPush(c, T);
+  quatOf(T, c.q0);
+  c.t0[0] = T[3]; c.t0[1] = T[7]; c.t0[2] = T[11];
+}
+// returns ICPERR_*; may clear `iterate` / set `maxIter`; err[] = the values the reference puts in its message
+__host__ __device__ int checkersCheck(const CheckerCfg& cfg, CheckerState& c, const float* T, bool& iterate, bool& maxIter, float err[4]) {
+  if (cfg.smoothLength >= 0) {
+    checkersPush(c, T);
+    const int sl = cfg.smoothLength, cnt = c.count;
+    float cv0 = 0.f, cv1 = 0.f;
+    if (cnt > sl) {
+      for (int i = cnt - 1; sl > 0 && i >= cnt - sl; --i) {
+        const int a = i % CHK_HIST, b = (i - 1) % CHK_HIST;
+        cv0 += fabsf(quatDist(c.rot[a], c.rot[b]));
+        const float dx = c.tr[a][0] - c.tr[b][0], dy = c.tr[a][1] - c.tr[b][1], dz = c.tr[a][2] - c.tr[b][2];
+        cv1 += fabsf(sqrtf(dx * dx + dy * dy + dz * dz));
+      }
+      cv0 /= (float)sl; cv1 /= (float)sl;
+      if (cv0 < cfg.minDiffRot && cv1 < cfg.minDiffTrans) iterate = false;
+    }
+    if (cv0 != cv0) return ICPERR_ROT_NAN;
+    if (cv1 != cv1) return ICPERR_TRANS_NAN;
   }
-  void push(const float* T) {
+  if (cfg.boundRot >= 0.f) {
     float q[4];
     quatOf(T, q);
-    rot.insert(rot.end(), q, q + 4);
-    tr.push_back(T[3]); tr.push_back(T[7]); tr.push_back(T[11]);
+    const float r = quatDist(q, c.q0);
+    const float dx = T[3] - c.t0[0], dy = T[7] - c.t0[1], dz = T[11] - c.t0[2];
+    const float t = sqrtf(dx * dx + dy * dy + dz * dz);
+    if (r > cfg.boundRot || t > cfg.boundTrans) {
+      err[0] = r; err[1] = cfg.boundRot; err[2] = t; err[3] = cfg.boundTrans;
+      return ICPERR_BOUND;
+    }
   }
-  // 0 ok, <0 ConvergenceError; may clear `iterate` / set `maxIter`
-  int check(b200reg_ctx* ctx, const float* T, bool& iterate, bool& maxIter) {
-    if (c.smooth_length >= 0) {
-      push(T);
-      const size_t sl = (size_t)c.smooth_length, cnt = rot.size() / 4;
-      float cv0 = 0.f, cv1 = 0.f;
-      if (cnt > sl) {
-        for (size_t i = cnt - 1; sl > 0 && i >= cnt - sl; --i) {
-          cv0 += fabsf(quatDist(&rot[4 * i], &rot[4 * (i - 1)]));
-          const float dx = tr[3 * i] - tr[3 * (i - 1)], dy = tr[3 * i + 1] - tr[3 * (i - 1) + 1], dz = tr[3 * i + 2] - tr[3 * (i - 1) + 2];
-          cv1 += fabsf(sqrtf(dx * dx + dy * dy + dz * dz));
-        }
-        cv0 /= (float)sl; cv1 /= (float)sl;
-        if (cv0 < c.min_diff_rot && cv1 < c.min_diff_trans) iterate = false;
-      }
-      if (cv0 != cv0) return setErr(ctx, B200REG_E_NOT_CONVERGED, "abs rotation norm not a number");
-      if (cv1 != cv1) return setErr(ctx, B200REG_E_NOT_CONVERGED, "abs translation norm not a number");
-    }
-    if (c.bound_rot >= 0.f) {
-      float q[4];
-      quatOf(T, q);
-      const float r = quatDist(q, q0);
-      const float dx = T[3] - t0[0], dy = T[7] - t0[1], dz = T[11] - t0[2];
-      const float t = sqrtf(dx * dx + dy * dy + dz * dz);
-      if (r > c.bound_rot || t > c.bound_trans)
-        return setErr(ctx, B200REG_E_NOT_CONVERGED, "limit out of bounds: rot: %g/%g tr: %g/%g", r, c.bound_rot, t, c.bound_trans);
-    }
-    if (c.max_iter > 0) {
-      ++counter;
-      if (counter >= c.max_iter) { iterate = false; maxIter = true; }   // MaxNumIterationsReached, caught at ICP.cpp:441-445
-    }
-    return B200REG_OK;
+  if (cfg.maxIter > 0) {
+    ++c.counter;
+    if (c.counter >= cfg.maxIter) { iterate = false; maxIter = true; }   // MaxNumIterationsReached, caught at ICP.cpp:441-445
   }
-};
+  return ICPERR_NONE;
+}
+int icpErrToStatus(b200reg_ctx* ctx, int kind, const float err[4]) {
+  switch (kind) {
+    case ICPERR_NONE: return B200REG_OK;
+    case ICPERR_ROT_NAN: return setErr(ctx, B200REG_E_NOT_CONVERGED, "abs rotation norm not a number");
+    case ICPERR_TRANS_NAN: return setErr(ctx, B200REG_E_NOT_CONVERGED, "abs translation norm not a number");
+    case ICPERR_BOUND:
+      return setErr(ctx, B200REG_E_NOT_CONVERGED, "limit out of bounds: rot: %g/%g tr: %g/%g", err[0], err[1], err[2], err[3]);
+    case ICPERR_NO_QUANTILE: return setErr(ctx, B200REG_E_NOT_CONVERGED, "No matches available for computing distance quantiles");
+    case ICPERR_NO_POINTS: return setErr(ctx, B200REG_E_NOT_CONVERGED, "ErrorMnimizer: no point to minimize");
+    case ICPERR_NOT_RIGID: return setErr(ctx, B200REG_E_TRANSFORM, "RigidTransformation: Error, rotation matrix is not orthogonal.");
+  }
+  return setErr(ctx, B200REG_E_CUDA, "ICP: unknown device error %d", kind);
+}
+
+__host__ __device__ void solveP2P(const double* A, const double* b, const double* mean_reading, const double* mean_reference, int force2D,
+                                  int force4DOF, float* T_out, double* x_out);
 
 double nowSec() { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
 
@@ -307,6 +405,13 @@ struct b200reg_icp {
   float mean[3] = {0, 0, 0};        // T_refIn_refMean translation
   double refPrepS = 0;
   DevBuf reading, readingNrm;       // `reading` of ICP.cpp:352-375 (in the refMean frame)
+  // device-resident iterate loop (k = 1): a CUDA graph whose body is a `while` conditional node
+  IcpDevParams* dP = nullptr;
+  IcpDevState* dS = nullptr;
+  cudaGraph_t graph = nullptr;
+  cudaGraphExec_t exec = nullptr;
+  int graphState = 0;               // 0 not built yet, 1 ready, -1 unavailable (host-driven loop is used)
+  int graphNodes = 0;               // kernels per iteration of the body
 };
 
 extern "C" {
@@ -315,13 +420,22 @@ int32_t b200reg_solve_point_to_plane(const double A[36], const double b[6], cons
                                      const double mean_reference[3], int32_t force2D, int32_t force4DOF, float T_out[16],
                                      double x_out[6]) {
   if (!A || !b || !mean_reading || !mean_reference || !T_out) return B200REG_E_INVALID_PARAM;
+  solveP2P(A, b, mean_reading, mean_reference, force2D, force4DOF, T_out, x_out);
+  return B200REG_OK;
+}
+
+}  // extern "C"
+
+namespace {
+__host__ __device__ void solveP2P(const double* A, const double* b, const double* mean_reading, const double* mean_reference, int force2D,
+                                  int force4DOF, float* T_out, double* x_out) {
   double x[6] = {0, 0, 0, 0, 0, 0};
   double R[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1}, t[3] = {0, 0, 0};
   if (force2D) {   // unknowns [gamma, tx, ty] = rows/cols {2,3,4} (PointToPlane.cpp:247-254, 334-366)
     const int sel[3] = {2, 3, 4};
     double As[9], bs[3], xs[3];
     for (int r = 0; r < 3; ++r) { bs[r] = b[sel[r]]; for (int c = 0; c < 3; ++c) As[3 * r + c] = A[6 * sel[r] + sel[c]]; }
-    solveSym(As, bs, 3, xs);
+    solveSym<3>(As, bs, xs);
     x[0] = xs[0]; x[1] = xs[1]; x[2] = xs[2];
     R[0] = cos(xs[0]); R[1] = -sin(xs[0]); R[3] = sin(xs[0]); R[4] = cos(xs[0]);
     t[0] = xs[1]; t[1] = xs[2];
@@ -331,12 +445,12 @@ int32_t b200reg_solve_point_to_plane(const double A[36], const double b[6], cons
       const int sel[4] = {2, 3, 4, 5};
       double As[16], bs[4], xs[4];
       for (int r = 0; r < 4; ++r) { bs[r] = b[sel[r]]; for (int c = 0; c < 4; ++c) As[4 * r + c] = A[6 * sel[r] + sel[c]]; }
-      solveSym(As, bs, 4, xs);
+      solveSym<4>(As, bs, xs);
       for (int i = 0; i < 4; ++i) x[i] = xs[i];
       angle = xs[0];
       t[0] = xs[1]; t[1] = xs[2]; t[2] = xs[3];
     } else {
-      solveSym(A, b, 6, x);
+      solveSym<6>(A, b, x);
       angle = sqrt(x[0] * x[0] + x[1] * x[1] + x[2] * x[2]);
       const double wmax = fmax(fabs(x[0]), fmax(fabs(x[1]), fabs(x[2])));   // stableNormalized()
       double v[3] = {x[0], x[1], x[2]};
@@ -370,8 +484,10 @@ int32_t b200reg_solve_point_to_plane(const double A[36], const double b[6], cons
     for (int r = 0; r < 3; ++r) for (int c = 0; c < 3; ++c) T[4 * r + c] = (r == c) ? 1.0 : 0.0;
   for (int i = 0; i < 16; ++i) T_out[i] = (float)T[i];
   if (x_out) for (int i = 0; i < 6; ++i) x_out[i] = x[i];
-  return B200REG_OK;
 }
+}  // namespace
+
+extern "C" {
 
 int32_t b200reg_icp_step(b200reg_ctx* ctx, const b200reg_index* index, const b200reg_cloud* reading, const float* T_iter,
                          int32_t k, float max_dist, float trim_ratio, float max_angle, int32_t force2D, double A_out[36],
@@ -429,6 +545,117 @@ __global__ void prepReadingKernel(const float4* __restrict__ xyz, const float4* 
 
 }  // namespace
 
+namespace {
+
+// Everything the host-driven loop does between two iterations (ICP.cpp:418-446), by one device thread: ErrorElements
+// checks, A/b from the moments, the 6x6 solve, T_iter <- T_step * T_iter, the transformation checkers, and the loop
+// condition of the graph's while node.  Same __host__ __device__ arithmetic as the host loop (this file is built with
+// --fmad=false), so both loops take the same decisions.
+__global__ void __launch_bounds__(32) icpTailKernel(const IcpDevParams* __restrict__ P, IcpDevState* __restrict__ S,
+                                                    const double* __restrict__ result, const SelState* __restrict__ st,
+                                                    const unsigned long long* __restrict__ visitCounter,
+                                                    cudaGraphConditionalHandle handle) {
+  if (threadIdx.x != 0) return;
+  traceStamp(P->trace, 6);
+  double mom[NUM_MOM];
+  for (int j = 0; j < NUM_MOM; ++j) mom[j] = result[j];
+  int err = ICPERR_NONE;
+  bool iterate = true, maxIter = false;
+  float errv[4] = {0.f, 0.f, 0.f, 0.f};
+  if (P->useTrim && st->error) err = ICPERR_NO_QUANTILE;
+  else if (mom[M_CNT] < 1.0) err = ICPERR_NO_POINTS;
+  else {
+    double A[36], b[6], mr[3], ms[3];
+    momentsToSystem(mom, A, b, mr, ms);
+    float Tstep[16], Told[16], Tnew[16];
+    solveP2P(A, b, mr, ms, P->force2D, P->force4DOF, Tstep, nullptr);
+    for (int i = 0; i < 16; ++i) Told[i] = S->T[i];
+    mul4(Tstep, Told, Tnew);   // T_iter = T_step * T_iter (ICP.cpp:433)
+    for (int i = 0; i < 16; ++i) S->T[i] = Tnew[i];
+    const CheckerCfg ccfg{P->maxIter, P->smoothLength, P->minDiffRot, P->minDiffTrans, P->boundRot, P->boundTrans};
+    err = checkersCheck(ccfg, S->chk, Tnew, iterate, maxIter, errv);
+    S->iterations = S->iterations + 1;
+    if (err == ICPERR_NONE && iterate && !rigidOk(Tnew)) err = ICPERR_NOT_RIGID;   // the next iteration's RigidTransformation check
+  }
+  if (err != ICPERR_NONE) iterate = false;
+  S->kept = mom[M_CNT];
+  S->valid = mom[M_VALID];
+  S->tau = P->useTrim ? __uint_as_float(st->tauBits) : CUDART_INF_F;
+  S->visits = *visitCounter;
+  S->errKind = err;
+  S->errA = errv[0]; S->errB = errv[1]; S->errC = errv[2]; S->errD = errv[3];
+  S->maxIterReached = maxIter ? 1 : 0;
+  S->iterate = iterate ? 1 : 0;
+  cudaGraphSetConditional(handle, iterate ? 1u : 0u);
+  traceStamp(P->trace, 7);   // end of the tail
+}
+
+#define GRAPH_TRY(expr)                                                    \
+  do {                                                                     \
+    cudaError_t _e = (expr);                                               \
+    if (_e != cudaSuccess) { why = #expr; code = _e; goto fail; }          \
+  } while (0)
+
+// Build the while-graph once per ICP object.  Every kernel of the body takes its arguments from icp->dP / icp->dS and
+// runs on a fixed grid (a multiple of the SM count), so the graph never has to be updated or re-instantiated.
+int buildLoopGraph(b200reg_icp* icp) {
+  b200reg_ctx* ctx = icp->ctx;
+  const char* why = "";
+  cudaError_t code = cudaSuccess;
+  cudaGraph_t g = nullptr, body = nullptr, captured = nullptr;
+  cudaGraphExec_t exec = nullptr;
+  bool capturing = false;
+  const bool useTrim = icp->cfg.trim_ratio > 0.f;
+  SelState* st = selState(ctx);
+  const int knnBlocks = 24 * ctx->sm_count, selBlocks = 2 * ctx->sm_count, redBlocks = 2 * ctx->sm_count;
+  if (ensureBuf(ctx, ctx->partials, sizeof(double) * NUM_MOM * (size_t)redBlocks) != B200REG_OK) return -1;
+  {
+    cudaGraphConditionalHandle handle;
+    cudaGraphNodeParams np = {cudaGraphNodeTypeConditional};
+    cudaGraphNode_t node;
+    GRAPH_TRY(cudaGraphCreate(&g, 0));
+    GRAPH_TRY(cudaGraphConditionalHandleCreate(&handle, g, 1, cudaGraphCondAssignDefault));
+    np.type = cudaGraphNodeTypeConditional;
+    np.conditional.handle = handle;
+    np.conditional.type = cudaGraphCondTypeWhile;
+    np.conditional.size = 1;
+    GRAPH_TRY(cudaGraphAddNode(&node, g, nullptr, 0, &np));
+    body = np.conditional.phGraph_out[0];
+    GRAPH_TRY(cudaStreamBeginCaptureToGraph(ctx->stream, body, nullptr, nullptr, 0, cudaStreamCaptureModeThreadLocal));
+    capturing = true;
+    int nodes = 0;
+    launchKnn1Loop(ctx, icp->dP, icp->dS, knnBlocks);
+    ++nodes;
+    if (useTrim) {
+      selectPassKernel<0><<<selBlocks, 256, 0, ctx->stream>>>(nullptr, 0, 0.f, st, histPtr(ctx), icp->dP);
+      selectPassKernel<1><<<selBlocks, 256, 0, ctx->stream>>>(nullptr, 0, 0.f, st, histPtr(ctx), icp->dP);
+      selectPassKernel<2><<<selBlocks, 256, 0, ctx->stream>>>(nullptr, 0, 0.f, st, histPtr(ctx), icp->dP);
+      nodes += 3;
+    }
+    ReduceParams RP;
+    memset(&RP, 0, sizeof(RP));
+    reduceKernel<<<redBlocks, 256, 0, ctx->stream>>>(RP, st, nullptr, &st->ticket[3], resultPtr(ctx), icp->dP, icp->dS);
+    icpTailKernel<<<1, 32, 0, ctx->stream>>>(icp->dP, icp->dS, resultPtr(ctx), st, (const unsigned long long*)ctx->dstate, handle);
+    nodes += 2;
+    GRAPH_TRY(cudaGetLastError());
+    capturing = false;
+    GRAPH_TRY(cudaStreamEndCapture(ctx->stream, &captured));
+    GRAPH_TRY(cudaGraphInstantiate(&exec, g, 0));
+    icp->graph = g;
+    icp->exec = exec;
+    icp->graphNodes = nodes;
+    return 0;
+  }
+fail:
+  if (capturing) cudaStreamEndCapture(ctx->stream, &captured);
+  if (g) cudaGraphDestroy(g);
+  cudaGetLastError();
+  if (getenv("B200REG_VERBOSE")) fprintf(stderr, "b200reg: device-resident loop unavailable (%s: %s); using the host-driven loop\n", why, cudaGetErrorString(code));
+  return -1;
+}
+
+}  // namespace
+
 extern "C" {
 
 int32_t b200reg_icp_create(b200reg_ctx* ctx, const b200reg_icp_config* cfg, b200reg_icp** out) {
@@ -439,9 +666,17 @@ int32_t b200reg_icp_create(b200reg_ctx* ctx, const b200reg_icp_config* cfg, b200
   if (!(cfg->max_dist >= 0.f)) return setErr(ctx, B200REG_E_INVALID_PARAM, "KDTreeMatcher: maxDist must be >= 0");      // :100
   if (cfg->trim_ratio > 1.0f) return setErr(ctx, B200REG_E_INVALID_PARAM, "TrimmedDistOutlierFilter: ratio must be in [1e-7, 1]");   // OutlierFiltersImpl.h:137
   if (cfg->max_angle > 3.1416f) return setErr(ctx, B200REG_E_INVALID_PARAM, "SurfaceNormalOutlierFilter: maxAngle must be in [0, 3.1416]");
+  if (cfg->smooth_length > CHK_HIST - 1)
+    return setErr(ctx, B200REG_E_INVALID_PARAM, "DifferentialTransformationChecker: smoothLength above %d is not supported", CHK_HIST - 1);
   b200reg_icp* icp = new b200reg_icp();
   icp->ctx = ctx;
   icp->cfg = *cfg;
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  if (cudaMalloc(&icp->dP, sizeof(IcpDevParams)) != cudaSuccess || cudaMalloc(&icp->dS, sizeof(IcpDevState)) != cudaSuccess) {
+    if (icp->dP) cudaFree(icp->dP);
+    delete icp;
+    return setErr(ctx, B200REG_E_OOM, "icp_create: allocation failed");
+  }
   *out = icp;
   return B200REG_OK;
 }
@@ -454,6 +689,10 @@ void b200reg_icp_destroy(b200reg_icp* icp) {
   if (icp->index) b200reg_index_free(ctx, icp->index);
   if (icp->reading.p) cudaFree(icp->reading.p);
   if (icp->readingNrm.p) cudaFree(icp->readingNrm.p);
+  if (icp->exec) cudaGraphExecDestroy(icp->exec);
+  if (icp->graph) cudaGraphDestroy(icp->graph);
+  if (icp->dP) cudaFree(icp->dP);
+  if (icp->dS) cudaFree(icp->dS);
   delete icp;
 }
 
@@ -519,13 +758,77 @@ int32_t b200reg_icp_register(b200reg_icp* icp, const b200reg_cloud* reading, con
   const double t1 = nowSec();
   float T_iter[16] = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1};
   bool iterate = true, maxIter = false;
-  Checkers checkers(cfg);
-  checkers.init(T_iter);
+  const double total = (double)n * cfg.knn;
+  // ---- device-resident loop: the whole iterate loop is ONE graph launch; the host comes back for the final state only
+  const bool wantGraph = cfg.knn == 1 && !ctx->profile && !ctx->hostLoop;
+  if (wantGraph && icp->graphState == 0) icp->graphState = (buildLoopGraph(icp) == 0) ? 1 : -1;
+  if (wantGraph && icp->graphState == 1) {
+    TRY(ensureBuf(ctx, ctx->matchIds, sizeof(int) * (size_t)n));
+    TRY(ensureBuf(ctx, ctx->matchD2, sizeof(float) * (size_t)n));
+    TRY(ensureBuf(ctx, ctx->matchPos, sizeof(int) * (size_t)n));
+    char* pin = (char*)ctx->pinned;
+    IcpDevParams* hP = (IcpDevParams*)(pin + 8192);
+    IcpDevState* hS = (IcpDevState*)(pin + 12288);
+    IcpDevState* hR = (IcpDevState*)(pin + 16384);
+    memset(hP, 0, sizeof(*hP));
+    hP->pts = icp->index->pts; hP->nrm = icp->index->nrm; hP->cellStart = icp->index->cellStart; hP->g = icp->index->g;
+    hP->reading = (const float4*)icp->reading.p;
+    hP->readingNrm = needNrm ? (const float4*)icp->readingNrm.p : nullptr;
+    hP->n = n;
+    hP->ids = (int*)ctx->matchIds.p; hP->d2 = (float*)ctx->matchD2.p; hP->pos = (int*)ctx->matchPos.p;
+    hP->partials = (double*)ctx->partials.p;
+    hP->maxd2 = cfg.max_dist * cfg.max_dist;
+    hP->trimRatio = cfg.trim_ratio;
+    hP->cosAngle = cosf(cfg.max_angle);
+    hP->useTrim = cfg.trim_ratio > 0.f ? 1 : 0;
+    hP->useAngle = cfg.max_angle >= 0.f ? 1 : 0;
+    hP->force2D = cfg.force2D; hP->force4DOF = cfg.force4DOF;
+    hP->maxIter = cfg.max_iter; hP->smoothLength = cfg.smooth_length;
+    hP->minDiffRot = cfg.min_diff_rot; hP->minDiffTrans = cfg.min_diff_trans;
+    hP->boundRot = cfg.bound_rot; hP->boundTrans = cfg.bound_trans;
+    hP->trace = ctx->trace ? (unsigned long long*)((char*)ctx->dstate + DSTATE_TRACE_OFF) : nullptr;
+    if (ctx->trace) CUDA_TRY(ctx, cudaMemsetAsync((char*)ctx->dstate + DSTATE_TRACE_OFF, 0, sizeof(unsigned long long), ctx->stream));
+    memset(hS, 0, sizeof(*hS));
+    memcpy(hS->T, T_iter, sizeof(T_iter));
+    hS->iterate = 1;
+    checkersInit(hS->chk, T_iter);
+    CUDA_TRY(ctx, cudaMemcpyAsync(icp->dP, hP, sizeof(*hP), cudaMemcpyHostToDevice, ctx->stream));
+    CUDA_TRY(ctx, cudaMemcpyAsync(icp->dS, hS, sizeof(*hS), cudaMemcpyHostToDevice, ctx->stream));
+    CUDA_TRY(ctx, cudaMemsetAsync(ctx->dstate, 0, sizeof(unsigned long long), ctx->stream));
+    CUDA_TRY(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
+    CUDA_TRY(ctx, cudaGraphLaunch(icp->exec, ctx->stream));
+    CUDA_TRY(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
+    CUDA_TRY(ctx, cudaMemcpyAsync(hR, icp->dS, ICP_STATE_HEAD_BYTES, cudaMemcpyDeviceToHost, ctx->stream));
+    CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+    float gms = 0;
+    cudaEventElapsedTime(&gms, ctx->ev0, ctx->ev1);
+    st.device_ms = gms;
+    st.iterations = hR->iterations;
+    st.max_iterations_reached = hR->maxIterReached;
+    st.points_touched = hR->visits;
+    st.kept_last = (int64_t)hR->kept;
+    st.point_used_ratio = (float)hR->kept / (float)total;
+    st.overlap_ratio = st.point_used_ratio;
+    st.last_tau = hR->tau;
+    st.convergence_s = nowSec() - t1;
+    // kernels of the graph: (iterations that ran the full body) x nodes; an iteration that failed early still ran them all
+    ctx->launches += (uint64_t)icp->graphNodes * (uint64_t)(hR->iterations + ((hR->errKind == ICPERR_NO_QUANTILE || hR->errKind == ICPERR_NO_POINTS) ? 1 : 0));
+    const float errv[4] = {hR->errA, hR->errB, hR->errC, hR->errD};
+    const int gstatus = icpErrToStatus(ctx, hR->errKind, errv);
+    if (gstatus != B200REG_OK) return done(gstatus);
+    float Tref[16] = {1, 0, 0, icp->mean[0], 0, 1, 0, icp->mean[1], 0, 0, 1, icp->mean[2], 0, 0, 0, 1};
+    float tmp[16];
+    mul4(hR->T, Tpre, tmp);
+    mul4(Tref, tmp, T_out);
+    return done(B200REG_OK);
+  }
+  const CheckerCfg ccfg{cfg.max_iter, cfg.smooth_length, cfg.min_diff_rot, cfg.min_diff_trans, cfg.bound_rot, cfg.bound_trans};
+  CheckerState chk;
+  checkersInit(chk, T_iter);
   CUDA_TRY(ctx, cudaMemsetAsync(ctx->dstate, 0, sizeof(unsigned long long), ctx->stream));
   CUDA_TRY(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
   int status = B200REG_OK;
   const HostStep* h = (const HostStep*)ctx->pinned;
-  const double total = (double)n * cfg.knn;
   while (iterate) {
     if (!rigidOk(T_iter)) { status = setErr(ctx, B200REG_E_TRANSFORM, "RigidTransformation: Error, rotation matrix is not orthogonal."); break; }
     status = enqueueStep(ctx, icp->index, (const float4*)icp->reading.p, needNrm ? (const float4*)icp->readingNrm.p : nullptr, n, T_iter,
@@ -542,9 +845,10 @@ int32_t b200reg_icp_register(b200reg_icp* icp, const b200reg_cloud* reading, con
     double A[36], b[6], mr[3], ms[3];
     momentsToSystem(h->mom, A, b, mr, ms);
     float Tstep[16];
-    b200reg_solve_point_to_plane(A, b, mr, ms, cfg.force2D, cfg.force4DOF, Tstep, nullptr);
+    solveP2P(A, b, mr, ms, cfg.force2D, cfg.force4DOF, Tstep, nullptr);
     mul4(Tstep, T_iter, T_iter);   // T_iter = T_step * T_iter (ICP.cpp:433)
-    status = checkers.check(ctx, T_iter, iterate, maxIter);
+    float errv[4] = {0, 0, 0, 0};
+    status = icpErrToStatus(ctx, checkersCheck(ccfg, chk, T_iter, iterate, maxIter, errv), errv);
     ++st.iterations;
     if (status != B200REG_OK) break;
   }
@@ -608,11 +912,11 @@ int32_t b200reg_trimmed_dist(b200reg_ctx* ctx, const float* d2, int64_t count, f
   CUDA_TRY(ctx, cudaMemcpyAsync(dd, d2, sizeof(float) * (size_t)count, cudaMemcpyHostToDevice, ctx->stream));
   SelState* st = selState(ctx);
   const int blocks = (int)fmax(1.0, fmin((double)divUp(count, 256 * 4), (double)(2 * ctx->sm_count)));
-  selectPassKernel<0><<<blocks, 256, 0, ctx->stream>>>(dd, count, ratio, st, histPtr(ctx));
+  selectPassKernel<0><<<blocks, 256, 0, ctx->stream>>>(dd, count, ratio, st, histPtr(ctx), nullptr);
   LAUNCH_CHECK(ctx);
-  selectPassKernel<1><<<blocks, 256, 0, ctx->stream>>>(dd, count, ratio, st, histPtr(ctx));
+  selectPassKernel<1><<<blocks, 256, 0, ctx->stream>>>(dd, count, ratio, st, histPtr(ctx), nullptr);
   LAUNCH_CHECK(ctx);
-  selectPassKernel<2><<<blocks, 256, 0, ctx->stream>>>(dd, count, ratio, st, histPtr(ctx));
+  selectPassKernel<2><<<blocks, 256, 0, ctx->stream>>>(dd, count, ratio, st, histPtr(ctx), nullptr);
   LAUNCH_CHECK(ctx);
   trimWeightsKernel<<<divUp(count, 256), 256, 0, ctx->stream>>>(dd, count, st, dw);
   LAUNCH_CHECK(ctx);
@@ -680,9 +984,9 @@ int32_t b200reg_point_to_plane(b200reg_ctx* ctx, const b200reg_cloud* reading, c
   P.force2D = force2D;
   P.w = (const float*)ctx->misc.p;
   SelState* st = selState(ctx);
-  const int rblocks = (int)fmax(1.0, fmin((double)divUp(total, 256), (double)(4 * ctx->sm_count)));
+  const int rblocks = (int)fmax(1.0, fmin((double)divUp(total, 512), (double)(2 * ctx->sm_count)));
   TRY(ensureBuf(ctx, ctx->partials, sizeof(double) * NUM_MOM * (size_t)rblocks));
-  reduceKernel<<<rblocks, 256, 0, ctx->stream>>>(P, st, (double*)ctx->partials.p, &st->ticket[3], resultPtr(ctx));
+  reduceKernel<<<rblocks, 256, 0, ctx->stream>>>(P, st, (double*)ctx->partials.p, &st->ticket[3], resultPtr(ctx), nullptr, nullptr);
   LAUNCH_CHECK(ctx);
   HostStep* h = (HostStep*)ctx->pinned;
   CUDA_TRY(ctx, cudaMemcpyAsync(h->mom, resultPtr(ctx), sizeof(double) * NUM_MOM, cudaMemcpyDeviceToHost, ctx->stream));

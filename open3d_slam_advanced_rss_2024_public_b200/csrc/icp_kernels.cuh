@@ -3,6 +3,8 @@
 //   (2) fused outlier gates + ErrorElements statistics + point-to-plane moment reduction (fp64)
 //       (OutlierFiltersImpl.cpp:140-147,226-281; ErrorMinimizer.cpp:59-140; PointToPlane.cpp:107-156,263-268)
 #pragma once
+#include <cstddef>
+
 #include "common.cuh"
 
 // ---- device state block layout (ctx->dstate, 64 KB) -------------------------------------------------------------
@@ -38,7 +40,8 @@ enum {
 // uint32 order of the bit patterns is the float order.  The last block to finish picks the bucket.
 template <int PASS>
 __global__ void __launch_bounds__(256) selectPassKernel(const float* __restrict__ d2, int64_t count, float ratio, SelState* st,
-                                                        unsigned* __restrict__ hist) {
+                                                        unsigned* __restrict__ hist, const IcpDevParams* __restrict__ DP) {
+  if (DP) { d2 = DP->d2; count = DP->n; ratio = DP->trimRatio; traceStamp(DP->trace, 2 + PASS); }   // graph-driven loop (k = 1)
   __shared__ unsigned sh[2048];
   __shared__ unsigned scan[256];
   __shared__ bool last;
@@ -134,54 +137,96 @@ __device__ __forceinline__ double warpSum(double v) {
   return v;
 }
 
-// One thread per (reading point, neighbour slot).  Weights are binary and act only through compaction — exactly the
-// fork's A = G G^T, b = -G h^T (PointToPlane.cpp:153-155).  Moments are un-centred; the host applies the matched-mean
-// centring of PointToPlane.cpp:263-268 algebraically.
-__global__ void __launch_bounds__(256) reduceKernel(ReduceParams P, const SelState* __restrict__ st, double* __restrict__ partials,
-                                                    unsigned* ticket, double* __restrict__ result) {
+// one kept pair -> the 36 un-centred moments
+__device__ __forceinline__ void accumulatePair(double* m, const ReduceParams& P, float3 r, const float4 s4, const float4 nn4, double w) {
+  double rx = r.x, ry = r.y, rz = r.z, sx = s4.x, sy = s4.y, sz = s4.z, nx = nn4.x, ny = nn4.y, nz = nn4.z;
+  if (P.force2D) { rz = 0.0; sz = 0.0; nz = 0.0; }
+  const double ux = ry * nz - rz * ny, uy = rz * nx - rx * nz, uz = rx * ny - ry * nx;   // u = r x n
+  const double e = (rx - sx) * nx + (ry - sy) * ny + (rz - sz) * nz;
+  m[M_CNT] += 1.0;
+  m[M_SPARE] += w;   // sum of weights (ErrorMinimizer.cpp:123)
+  m[M_R] += rx; m[M_R + 1] += ry; m[M_R + 2] += rz;
+  m[M_S] += sx; m[M_S + 1] += sy; m[M_S + 2] += sz;
+  m[M_UU] += ux * ux; m[M_UU + 1] += ux * uy; m[M_UU + 2] += ux * uz; m[M_UU + 3] += uy * uy; m[M_UU + 4] += uy * uz; m[M_UU + 5] += uz * uz;
+  m[M_UN] += ux * nx; m[M_UN + 1] += ux * ny; m[M_UN + 2] += ux * nz;
+  m[M_UN + 3] += uy * nx; m[M_UN + 4] += uy * ny; m[M_UN + 5] += uy * nz;
+  m[M_UN + 6] += uz * nx; m[M_UN + 7] += uz * ny; m[M_UN + 8] += uz * nz;
+  m[M_NN] += nx * nx; m[M_NN + 1] += nx * ny; m[M_NN + 2] += nx * nz; m[M_NN + 3] += ny * ny; m[M_NN + 4] += ny * nz; m[M_NN + 5] += nz * nz;
+  m[M_UE] += ux * e; m[M_UE + 1] += uy * e; m[M_UE + 2] += uz * e;
+  m[M_NE] += nx * e; m[M_NE + 1] += ny * e; m[M_NE + 2] += nz * e;
+}
+
+// gates of one (reading point, neighbour slot) pair: true = the pair enters the normal equations.  On true, pos is valid.
+__device__ __forceinline__ bool pairKept(const ReduceParams& P, int64_t o, float d, float tau, double* m) {
+  if (d == CUDART_INF_F) return false;          // ErrorMinimizer.cpp:103-106
+  m[M_VALID] += 1.0;
+  if (P.w) return P.w[o] != 0.f;                 // ErrorMinimizer.cpp:108
+  return !(P.useTrim && !(d <= tau));            // OutlierFiltersImpl.cpp:146
+}
+
+// Grid-stride over (reading point, neighbour slot) pairs, two pairs in flight per thread so the dependent gathers
+// (d2 -> sorted position -> reference point + normal) of one overlap those of the other.  Weights are binary and act
+// only through compaction — exactly the fork's A = G G^T, b = -G h^T (PointToPlane.cpp:153-155).  Moments are
+// un-centred; the matched-mean centring of PointToPlane.cpp:263-268 is applied algebraically afterwards.
+// Reduction: 36 fp64 moments per thread -> warp shuffle -> block tree -> per-block partial -> the last block adds the
+// partials in a fixed order (deterministic for a given grid).
+__global__ void __launch_bounds__(256, 2) reduceKernel(ReduceParams P, const SelState* __restrict__ st, double* __restrict__ partials,
+                                                    unsigned* ticket, double* __restrict__ result, const IcpDevParams* __restrict__ DP,
+                                                    const IcpDevState* __restrict__ DS) {
+  if (DP) {   // graph-driven loop: arguments from the device-resident blocks, T_iter from the loop state
+    P.reading = DP->reading; P.readingNrm = DP->readingNrm; P.refPts = DP->pts; P.refNrm = DP->nrm;
+    P.ids = DP->ids; P.d2 = DP->d2; P.pos = DP->pos; P.n = DP->n; P.k = 1; P.hasT = 1;
+#pragma unroll
+    for (int j = 0; j < 12; ++j) P.T.m[j] = DS->T[j];
+    P.useTrim = DP->useTrim; P.useAngle = DP->useAngle; P.cosAngle = DP->cosAngle; P.force2D = DP->force2D; P.w = nullptr;
+    partials = DP->partials;
+    traceStamp(DP->trace, 5);
+  }
   double m[NUM_MOM];
 #pragma unroll
   for (int j = 0; j < NUM_MOM; ++j) m[j] = 0.0;
   const float tau = P.useTrim ? __uint_as_float(st->tauBits) : CUDART_INF_F;
   const int64_t total = P.n * P.k;
-  for (int64_t o = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; o < total; o += (int64_t)gridDim.x * blockDim.x) {
-    const float d = P.d2[o];
-    if (d == CUDART_INF_F) continue;          // ErrorMinimizer.cpp:103-106
-    m[M_VALID] += 1.0;
-    if (P.w) { if (P.w[o] == 0.f) continue; }   // ErrorMinimizer.cpp:108
-    else if (P.useTrim && !(d <= tau)) continue;   // OutlierFiltersImpl.cpp:146
-    const int64_t i = o / P.k;
-    const int pos = P.pos[o];
-    if (pos < 0) continue;
-    const float4 q4 = P.reading[i];
-    float3 r = make_float3(q4.x, q4.y, q4.z);
-    if (P.hasT) r = xformPoint(P.T, q4.x, q4.y, q4.z, q4.w);
-    const float4 nn4 = P.refNrm[pos];
-    if (!P.w && P.useAngle && P.readingNrm) {          // OutlierFiltersImpl.cpp:259-264
-      const float4 a4 = P.readingNrm[i];
-      float3 a = make_float3(a4.x, a4.y, a4.z);
-      if (P.hasT) a = xformNormal(P.T, a4.x, a4.y, a4.z);
-      const float dot = __fadd_rn(__fadd_rn(__fmul_rn(a.x, nn4.x), __fmul_rn(a.y, nn4.y)), __fmul_rn(a.z, nn4.z));
-      if (dot < P.cosAngle) continue;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  const bool angleGate = !P.w && P.useAngle && P.readingNrm;
+  for (int64_t o0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; o0 < total; o0 += 2 * stride) {
+    const int64_t o1 = o0 + stride;
+    const bool has1 = o1 < total;
+    const float d0 = P.d2[o0];
+    const float d1 = has1 ? P.d2[o1] : CUDART_INF_F;
+    bool k0 = pairKept(P, o0, d0, tau, m);
+    bool k1 = has1 && pairKept(P, o1, d1, tau, m);
+    const int p0 = k0 ? P.pos[o0] : -1, p1 = k1 ? P.pos[o1] : -1;
+    k0 = k0 && p0 >= 0;
+    k1 = k1 && p1 >= 0;
+    const int64_t i0 = o0 / P.k, i1 = has1 ? o1 / P.k : 0;
+    float4 q0 = make_float4(0.f, 0.f, 0.f, 1.f), q1 = q0, n0 = q0, n1 = q0, s0 = q0, s1 = q0, a0 = q0, a1 = q0;
+    if (k0) { q0 = P.reading[i0]; n0 = P.refNrm[p0]; s0 = P.refPts[p0]; if (angleGate) a0 = P.readingNrm[i0]; }
+    if (k1) { q1 = P.reading[i1]; n1 = P.refNrm[p1]; s1 = P.refPts[p1]; if (angleGate) a1 = P.readingNrm[i1]; }
+    if (k0) {
+      float3 r = make_float3(q0.x, q0.y, q0.z);
+      if (P.hasT) r = xformPoint(P.T, q0.x, q0.y, q0.z, q0.w);
+      bool keep = true;
+      if (angleGate) {          // OutlierFiltersImpl.cpp:259-264
+        float3 a = make_float3(a0.x, a0.y, a0.z);
+        if (P.hasT) a = xformNormal(P.T, a0.x, a0.y, a0.z);
+        keep = !(__fadd_rn(__fadd_rn(__fmul_rn(a.x, n0.x), __fmul_rn(a.y, n0.y)), __fmul_rn(a.z, n0.z)) < P.cosAngle);
+      }
+      if (keep) accumulatePair(m, P, r, s0, n0, P.w ? (double)P.w[o0] : 1.0);
     }
-    const float4 s4 = P.refPts[pos];
-    double rx = r.x, ry = r.y, rz = r.z, sx = s4.x, sy = s4.y, sz = s4.z, nx = nn4.x, ny = nn4.y, nz = nn4.z;
-    if (P.force2D) { rz = 0.0; sz = 0.0; nz = 0.0; }
-    const double ux = ry * nz - rz * ny, uy = rz * nx - rx * nz, uz = rx * ny - ry * nx;   // u = r x n
-    const double e = (rx - sx) * nx + (ry - sy) * ny + (rz - sz) * nz;
-    m[M_CNT] += 1.0;
-    m[M_SPARE] += P.w ? (double)P.w[o] : 1.0;   // sum of weights (ErrorMinimizer.cpp:123)
-    m[M_R] += rx; m[M_R + 1] += ry; m[M_R + 2] += rz;
-    m[M_S] += sx; m[M_S + 1] += sy; m[M_S + 2] += sz;
-    m[M_UU] += ux * ux; m[M_UU + 1] += ux * uy; m[M_UU + 2] += ux * uz; m[M_UU + 3] += uy * uy; m[M_UU + 4] += uy * uz; m[M_UU + 5] += uz * uz;
-    m[M_UN] += ux * nx; m[M_UN + 1] += ux * ny; m[M_UN + 2] += ux * nz;
-    m[M_UN + 3] += uy * nx; m[M_UN + 4] += uy * ny; m[M_UN + 5] += uy * nz;
-    m[M_UN + 6] += uz * nx; m[M_UN + 7] += uz * ny; m[M_UN + 8] += uz * nz;
-    m[M_NN] += nx * nx; m[M_NN + 1] += nx * ny; m[M_NN + 2] += nx * nz; m[M_NN + 3] += ny * ny; m[M_NN + 4] += ny * nz; m[M_NN + 5] += nz * nz;
-    m[M_UE] += ux * e; m[M_UE + 1] += uy * e; m[M_UE + 2] += uz * e;
-    m[M_NE] += nx * e; m[M_NE + 1] += ny * e; m[M_NE + 2] += nz * e;
+    if (k1) {
+      float3 r = make_float3(q1.x, q1.y, q1.z);
+      if (P.hasT) r = xformPoint(P.T, q1.x, q1.y, q1.z, q1.w);
+      bool keep = true;
+      if (angleGate) {
+        float3 a = make_float3(a1.x, a1.y, a1.z);
+        if (P.hasT) a = xformNormal(P.T, a1.x, a1.y, a1.z);
+        keep = !(__fadd_rn(__fadd_rn(__fmul_rn(a.x, n1.x), __fmul_rn(a.y, n1.y)), __fmul_rn(a.z, n1.z)) < P.cosAngle);
+      }
+      if (keep) accumulatePair(m, P, r, s1, n1, P.w ? (double)P.w[o1] : 1.0);
+    }
   }
-  // warp shuffle -> block tree (shared) -> per-block partial; the last block adds the partials in fixed order
+  // warp shuffle -> block tree (shared) -> per-block partial
   __shared__ double sm[8][NUM_MOM];
   __shared__ bool last;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -201,9 +246,19 @@ __global__ void __launch_bounds__(256) reduceKernel(ReduceParams P, const SelSta
   __syncthreads();
   if (!last) return;
   __threadfence();
+  // the last block: 7 slices x 36 moments; slice s adds partials s, s+7, ... in order, then the slices are added in order
+  constexpr int SL = 7;
+  const int j = threadIdx.x % NUM_MOM, sl = threadIdx.x / NUM_MOM;
+  if (sl < SL) {
+    double v = 0.0;
+#pragma unroll 4
+    for (unsigned b = sl; b < gridDim.x; b += SL) v += __ldcg(&partials[(size_t)b * NUM_MOM + j]);
+    sm[sl][j] = v;
+  }
+  __syncthreads();
   if (threadIdx.x < NUM_MOM) {
     double v = 0.0;
-    for (unsigned b = 0; b < gridDim.x; ++b) v += __ldcg(&partials[(size_t)b * NUM_MOM + threadIdx.x]);
+    for (int s = 0; s < SL; ++s) v += sm[s][threadIdx.x];
     result[threadIdx.x] = v;
   }
   if (threadIdx.x == 0) *ticket = 0;

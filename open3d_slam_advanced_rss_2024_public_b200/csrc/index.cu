@@ -145,6 +145,10 @@ int buildIndex(b200reg_ctx* ctx, const b200reg_cloud* ref, const float mean[3], 
   g.nz = (int)floorf(ext[2] / cell) + 1;
   // slack >= error of fl((p-o)*inv) cell assignment + error of evaluating cell bounds in fp32 (see knn.cu)
   g.slack = 16.f * 1.1920929e-7f * (maxAbs + fmaxf(ext[0], fmaxf(ext[1], ext[2])) + cell);
+  {   // (cell - 4 slack)^2 with a 1 % margin, rounded toward zero: a point >= 2 cells away cannot have a smaller fp32 d2
+    const double c = (double)cell - 4.0 * (double)g.slack;
+    g.ring2Safe = (c > 0.0) ? nextafterf((float)(0.99 * c * c), 0.f) : 0.f;
+  }
   const size_t numCells = (size_t)g.nx * g.ny * g.nz;
 
   cudaError_t e = cudaMalloc(&ix->pts, sizeof(float4) * (size_t)m);

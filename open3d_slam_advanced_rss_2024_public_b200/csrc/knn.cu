@@ -178,37 +178,40 @@ __global__ void __launch_bounds__(128) knnKernel(const float4* __restrict__ pts,
 // The result is the lexicographic minimum of (d2, index) over every candidate with d2 < maxDist^2 that pruning cannot
 // exclude, so it is identical to the one-thread kernel and to the oracle (ties -> smallest index).
 struct Best1 {
-  float d;
-  int id, pos;
+  unsigned long long key;   // (bit pattern of d2) << 32 | original index: unsigned order == (d2, index) lexicographic order (d2 >= 0)
+  int pos;                  // sorted position of the holder (feeds the gather of the reduction)
+  __device__ __forceinline__ float d() const { return __uint_as_float((unsigned)(key >> 32)); }
 };
-__device__ __forceinline__ void offer1(Best1& b, float d, int id, int pos) {
-  if (d < b.d || (d == b.d && (unsigned)id < (unsigned)b.id)) { b.d = d; b.id = id; b.pos = pos; }
+__device__ __forceinline__ unsigned long long packKey(float d, int id) {
+  return ((unsigned long long)__float_as_uint(d) << 32) | (unsigned)id;
 }
-__device__ __forceinline__ void groupMin8(Best1& b) {
+template <int G>
+__device__ __forceinline__ void groupMin(Best1& b) {
 #pragma unroll
-  for (int o = 4; o > 0; o >>= 1) {
-    const float d = __shfl_xor_sync(0xffffffffu, b.d, o);
-    const int id = __shfl_xor_sync(0xffffffffu, b.id, o);
+  for (int o = G / 2; o > 0; o >>= 1) {
+    const unsigned long long k = __shfl_xor_sync(0xffffffffu, b.key, o);
     const int pos = __shfl_xor_sync(0xffffffffu, b.pos, o);
-    offer1(b, d, id, pos);
+    if (k < b.key) { b.key = k; b.pos = pos; }
   }
 }
-__device__ __forceinline__ void test1(const float4 p, uint32_t j, const float3 q, float maxd2, int selfId, Best1& b, unsigned& visits) {
+template <bool SELFCHK>
+__device__ __forceinline__ void test1(const float4 p, uint32_t j, const float3 q, int selfId, Best1& b, unsigned& visits) {
   const int id = __float_as_int(p.w);
-  if (id == selfId) return;
-  const float d = dist2_rn(q.x, q.y, q.z, p.x, p.y, p.z);
+  if (SELFCHK && id == selfId) return;
+  const unsigned long long k = packKey(dist2_rn(q.x, q.y, q.z, p.x, p.y, p.z), id);
   ++visits;
-  if (d < maxd2) offer1(b, d, id, (int)j);
+  if (k < b.key) { b.key = k; b.pos = (int)j; }
 }
 // lanes of a group stride through [s, e); two independent loads in flight per lane
-__device__ __forceinline__ void scanCoop8(const float4* __restrict__ pts, uint32_t s, uint32_t e, int l, const float3 q, float maxd2,
-                                          int selfId, Best1& b, unsigned& visits) {
-  for (uint32_t j = s + l; j < e; j += 16) {
-    const bool h1 = (j + 8 < e);
+template <int G, bool SELFCHK>
+__device__ __forceinline__ void scanCoop(const float4* __restrict__ pts, uint32_t s, uint32_t e, int l, const float3 q, int selfId, Best1& b,
+                                         unsigned& visits) {
+  for (uint32_t j = s + l; j < e; j += 2 * G) {
+    const bool h1 = (j + G < e);
     const float4 p0 = pts[j];
-    const float4 p1 = pts[h1 ? j + 8 : j];
-    test1(p0, j, q, maxd2, selfId, b, visits);
-    if (h1) test1(p1, j + 8, q, maxd2, selfId, b, visits);
+    const float4 p1 = pts[h1 ? j + G : j];
+    test1<SELFCHK>(p0, j, q, selfId, b, visits);
+    if (h1) test1<SELFCHK>(p1, j + G, q, selfId, b, visits);
   }
 }
 __device__ __forceinline__ float ringLowerBound(const AxisGeom& ax, const AxisGeom& ay, const AxisGeom& az, int r, float cell, float slack) {
@@ -219,98 +222,108 @@ __device__ __forceinline__ float ringLowerBound(const AxisGeom& ax, const AxisGe
   return lb3(0.f, 0.f, f);
 }
 
-__global__ void __launch_bounds__(256) knn1GroupKernel(const float4* __restrict__ pts, const uint32_t* __restrict__ cellStart, GridDesc g,
-                                                       const float4* __restrict__ queries, int64_t n, int hasT, Rigid12 T,
-                                                       const float* __restrict__ Tdev, float maxd2, int allowSelf,
-                                                       int* __restrict__ outIds, float* __restrict__ outD2, int* __restrict__ outPos,
-                                                       unsigned long long* __restrict__ visitCounter) {
-  const unsigned FULL = 0xffffffffu;
-  const int lane = threadIdx.x & 31, l = lane & 7, gbase = lane & 24;
-  const int64_t qi = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 3;
+// One query of an aligned G-lane group (G = 4 or 8); SELFCHK: exclude the query's own index (allowSelf == 0).  Every lane
+// of the warp must call this together (the group loops are closed with warp-wide votes).
+template <int G, bool SELFCHK>
+__device__ __forceinline__ void knn1Query(const float4* __restrict__ pts, const uint32_t* __restrict__ cellStart, const GridDesc& g,
+                                          const float4* __restrict__ queries, int64_t n, int64_t qi, int hasT, const Rigid12& T, float maxd2,
+                                          int* __restrict__ outIds, float* __restrict__ outD2, int* __restrict__ outPos, unsigned& visits) {
+  constexpr unsigned FULL = 0xffffffffu;
+  constexpr int NR = 8 / G;   // non-centre rows owned by each lane
+  const int lane = threadIdx.x & 31, l = lane & (G - 1), gbase = lane & (32 - G);
   const bool live = qi < n;
-  if (Tdev) {   // device-resident iteration transform (graph-driven loop): rows 0..2 of the row-major 4x4
-#pragma unroll
-    for (int j = 0; j < 12; ++j) T.m[j] = Tdev[j];
-    hasT = 1;
-  }
   float4 q4 = make_float4(0.f, 0.f, 0.f, 1.f);
   if (live) q4 = queries[qi];
   float3 q = make_float3(q4.x, q4.y, q4.z);
   if (hasT) q = xformPoint(T, q4.x, q4.y, q4.z, q4.w);
   const bool finite = live && (fabsf(q.x) <= FLT_MAX) && (fabsf(q.y) <= FLT_MAX) && (fabsf(q.z) <= FLT_MAX);
-  const int selfId = allowSelf ? -2 : (int)qi;
+  const int selfId = (int)qi;
   const float lim = 1.0e9f;
   const AxisGeom ax{q.x, g.ox, finite ? (int)floorf(fminf(fmaxf(__fmul_rn(__fsub_rn(q.x, g.ox), g.inv_cell), -lim), lim)) : 0};
   const AxisGeom ay{q.y, g.oy, finite ? (int)floorf(fminf(fmaxf(__fmul_rn(__fsub_rn(q.y, g.oy), g.inv_cell), -lim), lim)) : 0};
   const AxisGeom az{q.z, g.oz, finite ? (int)floorf(fminf(fmaxf(__fmul_rn(__fsub_rn(q.z, g.oz), g.inv_cell), -lim), lim)) : 0};
-  Best1 best{CUDART_INF_F, -1, -1};
-  unsigned visits = 0;
+  // a candidate must beat (maxDist^2, index 0): d2 < maxDist^2 strictly, any index (NaN patterns sort above +inf and never win)
+  const unsigned long long initKey = packKey(maxd2, 0);
+  Best1 best{initKey, -1};
 
   // ---- rings 0 and 1: nine (y,z) rows, each the contiguous x range [cx-1, cx+1]
-  uint32_t sC = 0, eC = 0, sL = 0, eL = 0;
-  float lbL = CUDART_INF_F;
+  uint32_t sC = 0, eC = 0, sL[NR], eL[NR];
+  float lbL[NR];
+#pragma unroll
+  for (int t = 0; t < NR; ++t) { sL[t] = 0; eL[t] = 0; lbL[t] = CUDART_INF_F; }
   {
     const int xa = max(ax.c - 1, 0), xb = min(ax.c + 1, g.nx - 1);
     if (finite && xa <= xb) {
-      if (ay.c >= 0 && ay.c < g.ny && az.c >= 0 && az.c < g.nz) {
-        const size_t base = (size_t)g.nx * ((size_t)ay.c + (size_t)g.ny * (size_t)az.c);
+      if ((unsigned)ay.c < (unsigned)g.ny && (unsigned)az.c < (unsigned)g.nz) {
+        const uint32_t base = (uint32_t)g.nx * ((uint32_t)ay.c + (uint32_t)g.ny * (uint32_t)az.c);
         sC = cellStart[base + xa];
         eC = cellStart[base + xb + 1];
       }
-      const int ri = l + (l >= 4 ? 1 : 0);
-      const int iy = ay.c + (ri % 3) - 1, iz = az.c + (ri / 3) - 1;
-      if (iy >= 0 && iy < g.ny && iz >= 0 && iz < g.nz) {
-        const size_t base = (size_t)g.nx * ((size_t)iy + (size_t)g.ny * (size_t)iz);
-        sL = cellStart[base + xa];
-        eL = cellStart[base + xb + 1];
-        lbL = lb3(0.f, axisGap(ay, iy, g.cell, g.slack), axisGap(az, iz, g.cell, g.slack));
+#pragma unroll
+      for (int t = 0; t < NR; ++t) {
+        const int rr = l + t * G;
+        const int ri = rr + (rr >= 4 ? 1 : 0);
+        const int iy = ay.c + (ri % 3) - 1, iz = az.c + (ri / 3) - 1;
+        if ((unsigned)iy < (unsigned)g.ny && (unsigned)iz < (unsigned)g.nz) {
+          const uint32_t base = (uint32_t)g.nx * ((uint32_t)iy + (uint32_t)g.ny * (uint32_t)iz);
+          sL[t] = cellStart[base + xa];
+          eL[t] = cellStart[base + xb + 1];
+          lbL[t] = lb3(0.f, axisGap(ay, iy, g.cell, g.slack), axisGap(az, iz, g.cell, g.slack));
+        }
       }
     }
   }
-  scanCoop8(pts, sC, eC, l, q, maxd2, selfId, best, visits);
-  groupMin8(best);
+  scanCoop<G, SELFCHK>(pts, sC, eC, l, q, selfId, best, visits);
+  groupMin<G>(best);
   {
-    const bool alive = (eL > sL) && (lbL < maxd2) && !(lbL > best.d);
-    unsigned m = (__ballot_sync(FULL, alive) >> gbase) & 0xffu;
+    unsigned m = 0;
+#pragma unroll
+    for (int t = 0; t < NR; ++t) {
+      const bool alive = (eL[t] > sL[t]) && !(lbL[t] > best.d());
+      m |= ((__ballot_sync(FULL, alive) >> gbase) & ((1u << G) - 1u)) << (t * G);
+    }
     while (__any_sync(FULL, m != 0u)) {
       const int r = m ? (__ffs(m) - 1) : 0;
-      const uint32_t s = __shfl_sync(FULL, sL, gbase + r);
-      uint32_t e = __shfl_sync(FULL, eL, gbase + r);
-      const float lb = __shfl_sync(FULL, lbL, gbase + r);
-      if (!m || lb > best.d) e = s;   // lane-local re-prune (its own best only improves)
+      const int src = gbase + (r & (G - 1));
+      uint32_t s = __shfl_sync(FULL, sL[0], src), e = __shfl_sync(FULL, eL[0], src);
+      float lb = __shfl_sync(FULL, lbL[0], src);
+      if (NR == 2) {
+        const uint32_t s1 = __shfl_sync(FULL, sL[NR - 1], src), e1 = __shfl_sync(FULL, eL[NR - 1], src);
+        const float lb1 = __shfl_sync(FULL, lbL[NR - 1], src);
+        if (r >= G) { s = s1; e = e1; lb = lb1; }
+      }
+      if (!m || lb > best.d()) e = s;   // lane-local re-prune (a lane's own best only improves)
       m &= m - 1u;
-      scanCoop8(pts, s, e, l, q, maxd2, selfId, best, visits);
+      scanCoop<G, SELFCHK>(pts, s, e, l, q, selfId, best, visits);
     }
-    groupMin8(best);
+    groupMin<G>(best);
   }
 
-  // ---- rings >= 2: the (y,z) rows of each shell are dealt to the 8 lanes
+  // ---- rings >= 2: the (y,z) rows of each shell are dealt to the G lanes.  Any point of a ring >= 2 is farther than
+  // sqrt(ring2Safe) (one whole cell minus the fp32 assignment slack), so a closer best ends the search here.
   {
     const int r0 = max(max(max(-ax.c, ax.c - (g.nx - 1)), max(-ay.c, ay.c - (g.ny - 1))), max(max(-az.c, az.c - (g.nz - 1)), 0));
     const int rEnd = max(max(max(ax.c, g.nx - 1 - ax.c), max(ay.c, g.ny - 1 - ay.c)), max(az.c, g.nz - 1 - az.c));
     int r = max(2, r0);
-    bool need = finite && r <= rEnd;
-    if (need) {
-      const float rl = ringLowerBound(ax, ay, az, r, g.cell, g.slack);
-      need = (rl < maxd2) && !(rl > best.d);
-    }
+    bool need = finite && r <= rEnd && !(best.d() < g.ring2Safe);
+    if (need) need = !(ringLowerBound(ax, ay, az, r, g.cell, g.slack) > best.d());
     while (__any_sync(FULL, need)) {
       if (need) {
         const int w = 2 * r + 1;
-        for (int t = l; t < w * w; t += 8) {
+        for (int t = l; t < w * w; t += G) {
           const int dy = t % w - r, dz = t / w - r;
           const int iy = ay.c + dy, iz = az.c + dz;
-          if (iy < 0 || iy >= g.ny || iz < 0 || iz >= g.nz) continue;
+          if ((unsigned)iy >= (unsigned)g.ny || (unsigned)iz >= (unsigned)g.nz) continue;
           const float rowLb = lb3(0.f, axisGap(ay, iy, g.cell, g.slack), axisGap(az, iz, g.cell, g.slack));
-          if (rowLb >= maxd2 || rowLb > best.d) continue;
+          const float bound = best.d();   // starts at maxDist^2
+          if (rowLb > bound) continue;
           const bool shellRow = (abs(dz) == r) || (abs(dy) == r);
-          const float bound = fminf(best.d, maxd2);
           int xr = r;
           if (bound < CUDART_INF_F) {   // x reach implied by the current bound (conservative: +1 cell on both sides)
             const float reach = __fadd_rn(sqrtf(fmaxf(__fsub_rn(bound, rowLb), 0.f)), g.slack);
             xr = min(r, (int)fminf(__fmul_rn(reach, g.inv_cell), 1.0e9f) + 2);
           }
-          const size_t rowBase = (size_t)g.nx * ((size_t)iy + (size_t)g.ny * (size_t)iz);
+          const uint32_t rowBase = (uint32_t)g.nx * ((uint32_t)iy + (uint32_t)g.ny * (uint32_t)iz);
 #pragma unroll 1
           for (int seg = 0; seg < 2; ++seg) {
             int xa, xb;
@@ -325,34 +338,94 @@ __global__ void __launch_bounds__(256) knn1GroupKernel(const float4* __restrict_
             xb = min(xb, g.nx - 1);
             if (xa > xb) continue;
             const uint32_t s = cellStart[rowBase + xa], e = cellStart[rowBase + xb + 1];
-            for (uint32_t j = s; j < e; ++j) test1(pts[j], j, q, maxd2, selfId, best, visits);
+            for (uint32_t j = s; j < e; ++j) test1<SELFCHK>(pts[j], j, q, selfId, best, visits);
           }
         }
       }
-      groupMin8(best);
+      groupMin<G>(best);
       if (need) {
         ++r;
-        need = r <= rEnd;
-        if (need) {
-          const float rl = ringLowerBound(ax, ay, az, r, g.cell, g.slack);
-          need = (rl < maxd2) && !(rl > best.d);
-        }
+        need = r <= rEnd && !(ringLowerBound(ax, ay, az, r, g.cell, g.slack) > best.d());
       }
     }
   }
   if (live && l == 0) {
-    outIds[qi] = best.id;
-    outD2[qi] = best.d;
-    outPos[qi] = best.pos;
+    const bool found = best.key != initKey;
+    outIds[qi] = found ? (int)(unsigned)best.key : -1;
+    outD2[qi] = found ? best.d() : CUDART_INF_F;
+    outPos[qi] = found ? best.pos : -1;
   }
-  // touched-point statistic (Matcher::visitCounter): warp shuffle -> shared -> one atomic per block
-  __shared__ unsigned blockVisits;
-  if (threadIdx.x == 0) blockVisits = 0;
+}
+
+// touched-point statistic (Matcher::visitCounter): warp shuffle -> shared; the last warp out adds the block total (no barrier
+// at the end of the kernel: warps retire as they finish)
+__device__ __forceinline__ void flushVisits(unsigned visits, unsigned* sVisits, unsigned* sTicket, unsigned long long* visitCounter) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) visits += __shfl_xor_sync(0xffffffffu, visits, o);
+  if ((threadIdx.x & 31) == 0) {
+    atomicAdd(sVisits, visits);
+    __threadfence_block();
+    if (atomicAdd(sTicket, 1u) == (blockDim.x >> 5) - 1u) {
+      const unsigned total = atomicAdd(sVisits, 0u);
+      if (total) atomicAdd(visitCounter, (unsigned long long)total);
+    }
+  }
+}
+
+template <int G, bool SELFCHK>
+__global__ void __launch_bounds__(256) knn1GroupKernel(const float4* __restrict__ pts, const uint32_t* __restrict__ cellStart, GridDesc g,
+                                                       const float4* __restrict__ queries, int64_t n, int hasT, Rigid12 T, float maxd2,
+                                                       int* __restrict__ outIds, float* __restrict__ outD2, int* __restrict__ outPos,
+                                                       unsigned long long* __restrict__ visitCounter) {
+  constexpr int LOG2G = (G == 8) ? 3 : 2;
+  __shared__ unsigned sVisits, sTicket;
+  if (threadIdx.x == 0) { sVisits = 0; sTicket = 0; }
+  __syncthreads();   // all warps are at the start here: nobody waits on a straggler
+  unsigned visits = 0;
+  const int64_t qi = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> LOG2G;
+  knn1Query<G, SELFCHK>(pts, cellStart, g, queries, n, qi, hasT, T, maxd2, outIds, outD2, outPos, visits);
+  flushVisits(visits, &sVisits, &sTicket, visitCounter);
+}
+
+// The same search inside the device-resident registration loop (icp.cu): arguments and the iteration transform are read from
+// the loop's blocks in HBM, the grid is fixed (a multiple of the SM count) and strides over the queries, so one
+// instantiated CUDA graph serves every reading size and reference.
+template <int G>
+__global__ void __launch_bounds__(256, 6) knn1LoopKernel(const IcpDevParams* __restrict__ P, const IcpDevState* __restrict__ S,
+                                                      unsigned long long* __restrict__ visitCounter) {
+  constexpr int LOG2G = (G == 8) ? 3 : 2;
+  __shared__ unsigned sVisits, sTicket;
+  if (threadIdx.x == 0) { sVisits = 0; sTicket = 0; }
   __syncthreads();
-  for (int o = 16; o > 0; o >>= 1) visits += __shfl_xor_sync(FULL, visits, o);
-  if (lane == 0 && visits) atomicAdd(&blockVisits, visits);
-  __syncthreads();
-  if (threadIdx.x == 0 && blockVisits) atomicAdd(visitCounter, (unsigned long long)blockVisits);
+  traceStamp(P->trace, 1);
+  const GridDesc g = P->g;
+  const float4* pts = P->pts;
+  const uint32_t* cellStart = P->cellStart;
+  const float4* queries = P->reading;
+  const int64_t n = P->n;
+  const float maxd2 = P->maxd2;
+  int* ids = P->ids;
+  float* d2 = P->d2;
+  int* pos = P->pos;
+  Rigid12 T;
+#pragma unroll
+  for (int j = 0; j < 12; ++j) T.m[j] = S->T[j];
+  unsigned visits = 0;
+  const int64_t groupsPerGrid = ((int64_t)gridDim.x * blockDim.x) >> LOG2G;
+  const int64_t first = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> LOG2G;
+  const int64_t blockFirst = ((int64_t)blockIdx.x * blockDim.x) >> LOG2G;
+  for (int64_t base = 0; blockFirst + base < n; base += groupsPerGrid)   // trip count uniform over the block
+    knn1Query<G, false>(pts, cellStart, g, queries, n, first + base, 1, T, maxd2, ids, d2, pos, visits);
+  flushVisits(visits, &sVisits, &sTicket, visitCounter);
+}
+
+template <int G>
+void launchKnn1(b200reg_ctx* ctx, const b200reg_index* ix, const float4* q, int64_t n, int hasT, const Rigid12& T, float maxd2, int allowSelf, int* ids, float* d2, int* pos, unsigned long long* visits) {
+  const int blocks = divUp(n * G, 256);
+  if (allowSelf)
+    knn1GroupKernel<G, false><<<blocks, 256, 0, ctx->stream>>>(ix->pts, ix->cellStart, ix->g, q, n, hasT, T, maxd2, ids, d2, pos, visits);
+  else
+    knn1GroupKernel<G, true><<<blocks, 256, 0, ctx->stream>>>(ix->pts, ix->cellStart, ix->g, q, n, hasT, T, maxd2, ids, d2, pos, visits);
 }
 
 template <int K>
@@ -362,6 +435,14 @@ void launchKnn(b200reg_ctx* ctx, const b200reg_index* ix, const float4* q, int64
 }
 
 }  // namespace
+
+// k = 1 match of the device-resident loop; `blocks` is fixed by the caller (graph capture)
+int launchKnn1Loop(b200reg_ctx* ctx, const IcpDevParams* P, const IcpDevState* S, int blocks) {
+  unsigned long long* visits = (unsigned long long*)ctx->dstate;
+  if (ctx->knnLanes == 4) knn1LoopKernel<4><<<blocks, 256, 0, ctx->stream>>>(P, S, visits);
+  else knn1LoopKernel<8><<<blocks, 256, 0, ctx->stream>>>(P, S, visits);
+  return B200REG_OK;
+}
 
 // Device-side entry shared with icp.cu / normals.cu.  Results land in ctx->matchIds / matchD2 / matchPos (k*n entries);
 // the touched-point counter is dstate[0] (unsigned long long), accumulated.
@@ -381,15 +462,16 @@ int runKnn(b200reg_ctx* ctx, const b200reg_index* ix, const float4* queries, int
   int* pos = (int*)ctx->matchPos.p;
   unsigned long long* visits = (unsigned long long*)ctx->dstate;
   const int hasT = T ? 1 : 0;
-  if (k == 1 && !ctx->knnOneThread)
-    knn1GroupKernel<<<divUp(n * 8, 256), 256, 0, ctx->stream>>>(ix->pts, ix->cellStart, ix->g, queries, n, hasT, R, nullptr, maxd2, allowSelf,
-                                                                ids, d2, pos, visits);
+  profBegin(ctx);
+  if (k == 1 && ctx->knnLanes == 8) launchKnn1<8>(ctx, ix, queries, n, hasT, R, maxd2, allowSelf, ids, d2, pos, visits);
+  else if (k == 1 && ctx->knnLanes == 4) launchKnn1<4>(ctx, ix, queries, n, hasT, R, maxd2, allowSelf, ids, d2, pos, visits);
   else if (k == 1) launchKnn<1>(ctx, ix, queries, n, hasT, R, k, maxd2, allowSelf, ids, d2, pos, visits);
   else if (k <= 4) launchKnn<4>(ctx, ix, queries, n, hasT, R, k, maxd2, allowSelf, ids, d2, pos, visits);
   else if (k <= 8) launchKnn<8>(ctx, ix, queries, n, hasT, R, k, maxd2, allowSelf, ids, d2, pos, visits);
   else if (k <= 16) launchKnn<16>(ctx, ix, queries, n, hasT, R, k, maxd2, allowSelf, ids, d2, pos, visits);
   else if (k <= 32) launchKnn<32>(ctx, ix, queries, n, hasT, R, k, maxd2, allowSelf, ids, d2, pos, visits);
   else launchKnn<64>(ctx, ix, queries, n, hasT, R, k, maxd2, allowSelf, ids, d2, pos, visits);
+  profEnd(ctx);
   LAUNCH_CHECK(ctx);
   return B200REG_OK;
 }

@@ -1,0 +1,41 @@
+#!/usr/bin/env python3
+"""profiles/loop_trace.py — per-kernel timeline of the graph-resident registration loop on BASELINE config #2, from the
+device-side %globaltimer stamps (b200reg_ctx_set_trace); L2 flushed before each registration."""
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+import scenes  # noqa: E402
+from open3d_slam_advanced_rss_2024_public_b200 import capi  # noqa: E402
+
+c = scenes.config2(m=int(os.environ.get("PROF_MAP", 5_000_000)), n_beams=128, n_az=1024, scene_seed=1001)
+f4 = lambda a: np.concatenate([a.astype(np.float32), np.ones((a.shape[0], 1), np.float32)], axis=1)  # noqa: E731
+ctx = capi.Context(0)
+icp = capi.ICP(ctx, knn=1, max_dist=1.0, trim_ratio=0.8, max_iter=40, min_diff_rot=1e-3, min_diff_trans=1e-2, smooth_length=3)
+icp.set_reference(ctx.upload(f4(c["map_xyz"]), c["map_nrm"].astype(np.float32)))
+scan = ctx.upload(f4(c["scan"]))
+Ti = c["T_init"].astype(np.float32)
+for _ in range(3):
+    icp.register(scan, Ti)
+ctx.set_trace(True)
+NAMES = {1: "match", 2: "select0", 3: "select1", 4: "select2", 5: "reduce", 6: "tail", 7: "tail_end"}
+acc = {}
+for rep in range(10):
+    ctx.flush_l2()
+    ctx.timer_start()
+    T, st = icp.register(scan, Ti)
+    tot = ctx.timer_stop()
+    tr = ctx.trace_read()
+    t0 = tr[0][1]
+    line = []
+    for i, (tag, t) in enumerate(tr):
+        nxt = tr[i + 1][1] if i + 1 < len(tr) else t
+        acc.setdefault((i, NAMES.get(tag, tag)), []).append((nxt - t) / 1e3)
+    if rep == 9:
+        print(f"registration {tot*1e3:.1f} us event-timed, {st.iterations} iterations, trace span {(tr[-1][1]-t0)/1e3:.1f} us")
+for (i, name), v in acc.items():
+    print(f"  {i:3d} {name:9s} start->next start {np.mean(v):7.1f} us")
