@@ -2,6 +2,7 @@
 // (PointToPlane.cpp:185-368) and the TransformationCheckers (TransformationCheckersImpl.cpp:58-225).
 #include <chrono>
 #include <cmath>
+#include <cstdlib>
 
 #include "icp_kernels.cuh"
 
@@ -17,6 +18,22 @@ inline SelState* selState(b200reg_ctx* ctx) { return (SelState*)((char*)ctx->dst
 inline unsigned* histPtr(b200reg_ctx* ctx) { return (unsigned*)((char*)ctx->dstate + DSTATE_HIST_OFF); }
 inline double* resultPtr(b200reg_ctx* ctx) { return (double*)((char*)ctx->dstate + DSTATE_RESULT_OFF); }
 
+// Trimmed-distance selection (Matches::getDistsQuantile): three multi-block radix passes.  DP != nullptr: arguments from the
+// loop block.  (A single-launch variant that kept the distances in the distributed shared memory of one 8-CTA cluster was
+// measured at 19.6 us against 16 us for these three launches — same-bank shared atomics serialise at 32 cycles per warp and
+// only 8 SMs work — and was dropped; profiles/r1_notes.md.)
+int launchSelect(b200reg_ctx* ctx, const float* d2, int64_t count, float ratio, const IcpDevParams* DP) {
+  SelState* st = selState(ctx);
+  const int blocks = DP ? 2 * ctx->sm_count : (int)fmax(1.0, fmin((double)divUp(count, 256 * 4), (double)(2 * ctx->sm_count)));
+  selectPassKernel<0><<<blocks, 256, 0, ctx->stream>>>(d2, count, ratio, st, histPtr(ctx), DP);
+  LAUNCH_CHECK(ctx);
+  selectPassKernel<1><<<blocks, 256, 0, ctx->stream>>>(d2, count, ratio, st, histPtr(ctx), DP);
+  LAUNCH_CHECK(ctx);
+  selectPassKernel<2><<<blocks, 256, 0, ctx->stream>>>(d2, count, ratio, st, histPtr(ctx), DP);
+  LAUNCH_CHECK(ctx);
+  return B200REG_OK;
+}
+
 struct HostStep {   // what one iteration brings back over PCIe: NUM_MOM doubles + the select state + the visit counter
   double mom[NUM_MOM];
   SelState sel;
@@ -31,15 +48,7 @@ int enqueueStep(b200reg_ctx* ctx, const b200reg_index* ix, const float4* reading
   const int64_t total = n * k;
   SelState* st = selState(ctx);
   const bool useTrim = trimRatio > 0.f;
-  if (useTrim) {
-    const int blocks = (int)fmin((double)divUp(total, 256 * 4), (double)(2 * ctx->sm_count));
-    selectPassKernel<0><<<blocks, 256, 0, ctx->stream>>>((const float*)ctx->matchD2.p, total, trimRatio, st, histPtr(ctx), nullptr);
-    LAUNCH_CHECK(ctx);
-    selectPassKernel<1><<<blocks, 256, 0, ctx->stream>>>((const float*)ctx->matchD2.p, total, trimRatio, st, histPtr(ctx), nullptr);
-    LAUNCH_CHECK(ctx);
-    selectPassKernel<2><<<blocks, 256, 0, ctx->stream>>>((const float*)ctx->matchD2.p, total, trimRatio, st, histPtr(ctx), nullptr);
-    LAUNCH_CHECK(ctx);
-  }
+  if (useTrim) TRY(launchSelect(ctx, (const float*)ctx->matchD2.p, total, trimRatio, nullptr));
   ReduceParams P;
   P.reading = reading;
   P.readingNrm = readingNrm;
@@ -182,7 +191,7 @@ __host__ __device__ void jacobiEig(double* a, double* V, int n) {
 // closer to singular (or not positive definite) takes the eigen-decomposition path.  Sizes are template parameters so
 // the device compiler keeps the small matrices in registers.
 template <int N>
-__host__ __device__ __forceinline__ bool cholFactorT(const double* A, double* L) {
+__host__ __device__ __forceinline__ bool cholFactorT(const double* A, double* L, double* invDiag) {
 #pragma unroll
   for (int j = 0; j < N; ++j) {
     double d = A[j * N + j];
@@ -191,36 +200,38 @@ __host__ __device__ __forceinline__ bool cholFactorT(const double* A, double* L)
     if (!(d > 0.0)) return false;
     d = sqrt(d);
     L[j * N + j] = d;
+    const double inv = 1.0 / d;   // one division per column; the column and both substitutions multiply by it
+    invDiag[j] = inv;
 #pragma unroll
     for (int i = j + 1; i < N; ++i) {
       double s = A[i * N + j];
 #pragma unroll
       for (int k = 0; k < j; ++k) s -= L[i * N + k] * L[j * N + k];
-      L[i * N + j] = s / d;
+      L[i * N + j] = s * inv;
     }
   }
   return true;
 }
 template <int N>
-__host__ __device__ __forceinline__ void cholSolveT(const double* L, const double* b, double* x) {
+__host__ __device__ __forceinline__ void cholSolveT(const double* L, const double* invDiag, const double* b, double* x) {
   double y[N];
 #pragma unroll
   for (int i = 0; i < N; ++i) {
     double s = b[i];
 #pragma unroll
     for (int k = 0; k < i; ++k) s -= L[i * N + k] * y[k];
-    y[i] = s / L[i * N + i];
+    y[i] = s * invDiag[i];
   }
 #pragma unroll
   for (int i = N - 1; i >= 0; --i) {
     double s = y[i];
 #pragma unroll
     for (int k = i + 1; k < N; ++k) s -= L[k * N + i] * x[k];
-    x[i] = s / L[i * N + i];
+    x[i] = s * invDiag[i];
   }
 }
 template <int N>
-__host__ __device__ __forceinline__ bool certainlyFullRankT(const double* A, const double* L) {
+__host__ __device__ __forceinline__ bool certainlyFullRankT(const double* A, const double* L, const double* invDiag) {
   double Li[N * N];   // L^-1 (lower triangular); A^-1 = Li^T Li
 #pragma unroll
   for (int c = 0; c < N; ++c)
@@ -229,7 +240,7 @@ __host__ __device__ __forceinline__ bool certainlyFullRankT(const double* A, con
       double s = (r == c) ? 1.0 : 0.0;
 #pragma unroll
       for (int k = c; k < r; ++k) s -= L[r * N + k] * Li[k * N + c];
-      Li[r * N + c] = s / L[r * N + r];
+      Li[r * N + c] = s * invDiag[r];
     }
   double fro2 = 0.0, tr = 0.0;
 #pragma unroll
@@ -271,8 +282,8 @@ __host__ __device__ __noinline__ void solveSymSlow(const double* A, const double
 
 template <int N>
 __host__ __device__ __forceinline__ void solveSym(const double* A, const double* b, double* x) {
-  double L[N * N];
-  if (cholFactorT<N>(A, L) && certainlyFullRankT<N>(A, L)) { cholSolveT<N>(L, b, x); return; }
+  double L[N * N], invDiag[N];
+  if (cholFactorT<N>(A, L, invDiag) && certainlyFullRankT<N>(A, L, invDiag)) { cholSolveT<N>(L, invDiag, b, x); return; }
   solveSymSlow(A, b, N, x);
 }
 
@@ -557,22 +568,31 @@ __global__ void __launch_bounds__(32) icpTailKernel(const IcpDevParams* __restri
                                                     cudaGraphConditionalHandle handle) {
   if (threadIdx.x != 0) return;
   traceStamp(P->trace, 6);
+  // every global read up front and independent of the others: one memory round trip instead of a chain of them
+  const IcpDevParams p = *P;
   double mom[NUM_MOM];
-  for (int j = 0; j < NUM_MOM; ++j) mom[j] = result[j];
+#pragma unroll
+  for (int j = 0; j < NUM_MOM; ++j) mom[j] = __ldcg(result + j);
+  const int selError = __ldcg(&st->error);
+  const unsigned tauBits = __ldcg(&st->tauBits);
+  const unsigned long long visits = __ldcg(visitCounter);
+  float Told[16];
+#pragma unroll
+  for (int i = 0; i < 16; ++i) Told[i] = S->T[i];
   int err = ICPERR_NONE;
   bool iterate = true, maxIter = false;
   float errv[4] = {0.f, 0.f, 0.f, 0.f};
-  if (P->useTrim && st->error) err = ICPERR_NO_QUANTILE;
+  if (p.useTrim && selError) err = ICPERR_NO_QUANTILE;
   else if (mom[M_CNT] < 1.0) err = ICPERR_NO_POINTS;
   else {
     double A[36], b[6], mr[3], ms[3];
     momentsToSystem(mom, A, b, mr, ms);
-    float Tstep[16], Told[16], Tnew[16];
-    solveP2P(A, b, mr, ms, P->force2D, P->force4DOF, Tstep, nullptr);
-    for (int i = 0; i < 16; ++i) Told[i] = S->T[i];
+    float Tstep[16], Tnew[16];
+    solveP2P(A, b, mr, ms, p.force2D, p.force4DOF, Tstep, nullptr);
     mul4(Tstep, Told, Tnew);   // T_iter = T_step * T_iter (ICP.cpp:433)
+#pragma unroll
     for (int i = 0; i < 16; ++i) S->T[i] = Tnew[i];
-    const CheckerCfg ccfg{P->maxIter, P->smoothLength, P->minDiffRot, P->minDiffTrans, P->boundRot, P->boundTrans};
+    const CheckerCfg ccfg{p.maxIter, p.smoothLength, p.minDiffRot, p.minDiffTrans, p.boundRot, p.boundTrans};
     err = checkersCheck(ccfg, S->chk, Tnew, iterate, maxIter, errv);
     S->iterations = S->iterations + 1;
     if (err == ICPERR_NONE && iterate && !rigidOk(Tnew)) err = ICPERR_NOT_RIGID;   // the next iteration's RigidTransformation check
@@ -580,8 +600,8 @@ __global__ void __launch_bounds__(32) icpTailKernel(const IcpDevParams* __restri
   if (err != ICPERR_NONE) iterate = false;
   S->kept = mom[M_CNT];
   S->valid = mom[M_VALID];
-  S->tau = P->useTrim ? __uint_as_float(st->tauBits) : CUDART_INF_F;
-  S->visits = *visitCounter;
+  S->tau = p.useTrim ? __uint_as_float(tauBits) : CUDART_INF_F;
+  S->visits = visits;
   S->errKind = err;
   S->errA = errv[0]; S->errB = errv[1]; S->errC = errv[2]; S->errD = errv[3];
   S->maxIterReached = maxIter ? 1 : 0;
@@ -607,7 +627,7 @@ int buildLoopGraph(b200reg_icp* icp) {
   bool capturing = false;
   const bool useTrim = icp->cfg.trim_ratio > 0.f;
   SelState* st = selState(ctx);
-  const int knnBlocks = 24 * ctx->sm_count, selBlocks = 2 * ctx->sm_count, redBlocks = 2 * ctx->sm_count;
+  const int knnBlocks = 24 * ctx->sm_count, redBlocks = 2 * ctx->sm_count;
   if (ensureBuf(ctx, ctx->partials, sizeof(double) * NUM_MOM * (size_t)redBlocks) != B200REG_OK) return -1;
   {
     cudaGraphConditionalHandle handle;
@@ -626,12 +646,10 @@ int buildLoopGraph(b200reg_icp* icp) {
     int nodes = 0;
     launchKnn1Loop(ctx, icp->dP, icp->dS, knnBlocks);
     ++nodes;
-    if (useTrim) {
-      selectPassKernel<0><<<selBlocks, 256, 0, ctx->stream>>>(nullptr, 0, 0.f, st, histPtr(ctx), icp->dP);
-      selectPassKernel<1><<<selBlocks, 256, 0, ctx->stream>>>(nullptr, 0, 0.f, st, histPtr(ctx), icp->dP);
-      selectPassKernel<2><<<selBlocks, 256, 0, ctx->stream>>>(nullptr, 0, 0.f, st, histPtr(ctx), icp->dP);
-      nodes += 3;
-    }
+    const uint64_t l0 = ctx->launches;
+    if (useTrim && launchSelect(ctx, nullptr, 0, 0.f, icp->dP) != B200REG_OK) { why = "select launch"; code = cudaErrorUnknown; goto fail; }
+    nodes += (int)(ctx->launches - l0);
+    ctx->launches = l0;
     ReduceParams RP;
     memset(&RP, 0, sizeof(RP));
     reduceKernel<<<redBlocks, 256, 0, ctx->stream>>>(RP, st, nullptr, &st->ticket[3], resultPtr(ctx), icp->dP, icp->dS);
@@ -911,13 +929,7 @@ int32_t b200reg_trimmed_dist(b200reg_ctx* ctx, const float* d2, int64_t count, f
   float* dw = (float*)ctx->misc.p;
   CUDA_TRY(ctx, cudaMemcpyAsync(dd, d2, sizeof(float) * (size_t)count, cudaMemcpyHostToDevice, ctx->stream));
   SelState* st = selState(ctx);
-  const int blocks = (int)fmax(1.0, fmin((double)divUp(count, 256 * 4), (double)(2 * ctx->sm_count)));
-  selectPassKernel<0><<<blocks, 256, 0, ctx->stream>>>(dd, count, ratio, st, histPtr(ctx), nullptr);
-  LAUNCH_CHECK(ctx);
-  selectPassKernel<1><<<blocks, 256, 0, ctx->stream>>>(dd, count, ratio, st, histPtr(ctx), nullptr);
-  LAUNCH_CHECK(ctx);
-  selectPassKernel<2><<<blocks, 256, 0, ctx->stream>>>(dd, count, ratio, st, histPtr(ctx), nullptr);
-  LAUNCH_CHECK(ctx);
+  TRY(launchSelect(ctx, dd, count, ratio, nullptr));
   trimWeightsKernel<<<divUp(count, 256), 256, 0, ctx->stream>>>(dd, count, st, dw);
   LAUNCH_CHECK(ctx);
   SelState* h = (SelState*)ctx->pinned;

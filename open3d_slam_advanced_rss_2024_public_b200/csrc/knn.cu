@@ -69,6 +69,11 @@ __device__ __forceinline__ float axisGap(const AxisGeom& a, int i, float cell, f
   else         g = __fsub_rn(a.q, __fadd_rn(a.o, __fmul_rn((float)(i + 1), cell)));     // q - hi(i)
   return fmaxf(__fsub_rn(g, slack), 0.f);
 }
+// the index build's cell function (index.cu cellCoord): monotone non-decreasing in p, clamped into the grid
+__device__ __forceinline__ int cellOfClamped(float p, float o, float inv, int nmax) {
+  const float c = floorf(__fmul_rn(__fsub_rn(p, o), inv));
+  return (int)fminf(fmaxf(c, 0.f), (float)(nmax - 1));
+}
 __device__ __forceinline__ float lb3(float gx, float gy, float gz) {
   return __fadd_rn(__fadd_rn(__fmul_rn(gx, gx), __fmul_rn(gy, gy)), __fmul_rn(gz, gz));
 }
@@ -307,39 +312,49 @@ __device__ __forceinline__ void knn1Query(const float4* __restrict__ pts, const 
     int r = max(2, r0);
     bool need = finite && r <= rEnd && !(best.d() < g.ring2Safe);
     if (need) need = !(ringLowerBound(ax, ay, az, r, g.cell, g.slack) > best.d());
+    const unsigned gmask = ((1u << G) - 1u) << gbase;
+    float bound = best.d();   // group-wide pruning bound (starts at maxDist^2); lane-local bests are merged after each ring
     while (__any_sync(FULL, need)) {
       if (need) {
-        const int w = 2 * r + 1;
-        for (int t = l; t < w * w; t += G) {
+        const int w = 2 * r + 1, nrows = w * w;
+        for (int t0 = 0; t0 < nrows; t0 += G) {   // one round = G rows, one per lane; the group stays converged
+          const int t = t0 + l;
           const int dy = t % w - r, dz = t / w - r;
           const int iy = ay.c + dy, iz = az.c + dz;
-          if ((unsigned)iy >= (unsigned)g.ny || (unsigned)iz >= (unsigned)g.nz) continue;
-          const float rowLb = lb3(0.f, axisGap(ay, iy, g.cell, g.slack), axisGap(az, iz, g.cell, g.slack));
-          const float bound = best.d();   // starts at maxDist^2
-          if (rowLb > bound) continue;
-          const bool shellRow = (abs(dz) == r) || (abs(dy) == r);
-          int xr = r;
-          if (bound < CUDART_INF_F) {   // x reach implied by the current bound (conservative: +1 cell on both sides)
-            const float reach = __fadd_rn(sqrtf(fmaxf(__fsub_rn(bound, rowLb), 0.f)), g.slack);
-            xr = min(r, (int)fminf(__fmul_rn(reach, g.inv_cell), 1.0e9f) + 2);
-          }
-          const uint32_t rowBase = (uint32_t)g.nx * ((uint32_t)iy + (uint32_t)g.ny * (uint32_t)iz);
+          if (t < nrows && (unsigned)iy < (unsigned)g.ny && (unsigned)iz < (unsigned)g.nz) {
+            const float rowLb = lb3(0.f, axisGap(ay, iy, g.cell, g.slack), axisGap(az, iz, g.cell, g.slack));
+            if (!(rowLb > bound)) {
+              const bool shellRow = (abs(dz) == r) || (abs(dy) == r);
+              // x cells a better point of this row can lie in: the index build's own (monotone) cell function applied to
+              // q.x -+ reach, reach = sqrt(bound - rowLb) + slack  =>  no point with d2 <= bound falls outside [xlo, xhi]
+              int xlo = 0, xhi = g.nx - 1;
+              if (bound < CUDART_INF_F) {
+                const float reach = __fadd_rn(sqrtf(fmaxf(__fsub_rn(bound, rowLb), 0.f)), g.slack);
+                xlo = cellOfClamped(__fsub_rn(__fsub_rn(q.x, reach), g.slack), g.ox, g.inv_cell, g.nx);
+                xhi = cellOfClamped(__fadd_rn(__fadd_rn(q.x, reach), g.slack), g.ox, g.inv_cell, g.nx);
+              }
+              const uint32_t rowBase = (uint32_t)g.nx * ((uint32_t)iy + (uint32_t)g.ny * (uint32_t)iz);
 #pragma unroll 1
-          for (int seg = 0; seg < 2; ++seg) {
-            int xa, xb;
-            if (shellRow) {
-              if (seg == 1) break;
-              xa = ax.c - xr; xb = ax.c + xr;
-            } else {   // interior row of the shell: only its two end cells (beyond reach if xr < r)
-              if (xr < r) break;
-              xa = xb = (seg == 0) ? ax.c - r : ax.c + r;
+              for (int seg = 0; seg < 2; ++seg) {
+                int xa, xb;
+                if (shellRow) {
+                  if (seg == 1) break;
+                  xa = ax.c - r; xb = ax.c + r;
+                } else {   // interior row of the shell: only its two end cells
+                  xa = xb = (seg == 0) ? ax.c - r : ax.c + r;
+                }
+                xa = max(xa, xlo);
+                xb = min(xb, xhi);
+                if (xa > xb) continue;
+                const uint32_t s = cellStart[rowBase + xa], e = cellStart[rowBase + xb + 1];
+                for (uint32_t j = s; j < e; ++j) test1<SELFCHK>(pts[j], j, q, selfId, best, visits);
+              }
+              bound = fminf(bound, best.d());
             }
-            xa = max(xa, 0);
-            xb = min(xb, g.nx - 1);
-            if (xa > xb) continue;
-            const uint32_t s = cellStart[rowBase + xa], e = cellStart[rowBase + xb + 1];
-            for (uint32_t j = s; j < e; ++j) test1<SELFCHK>(pts[j], j, q, selfId, best, visits);
           }
+          // the first hit of any lane tightens everybody's row and x-reach pruning from the next round on
+#pragma unroll
+          for (int o = G / 2; o > 0; o >>= 1) bound = fminf(bound, __shfl_xor_sync(gmask, bound, o));
         }
       }
       groupMin<G>(best);
