@@ -199,6 +199,11 @@ __device__ __forceinline__ void groupMin(Best1& b) {
     if (k < b.key) { b.key = k; b.pos = pos; }
   }
 }
+__device__ __forceinline__ float4 ldPoint(const float4* p) {
+  float4 v;
+  asm volatile("ld.global.nc.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
+  return v;
+}
 template <bool SELFCHK>
 __device__ __forceinline__ void test1(const float4 p, uint32_t j, const float3 q, int selfId, Best1& b, unsigned& visits) {
   const int id = __float_as_int(p.w);
@@ -213,8 +218,10 @@ __device__ __forceinline__ void scanCoop(const float4* __restrict__ pts, uint32_
                                          unsigned& visits) {
   for (uint32_t j = s + l; j < e; j += 2 * G) {
     const bool h1 = (j + G < e);
-    const float4 p0 = pts[j];
-    const float4 p1 = pts[h1 ? j + G : j];
+    // both loads are issued before either is used (volatile asm keeps the compiler from sinking the second one
+    // behind the first candidate's compare)
+    const float4 p0 = ldPoint(pts + j);
+    const float4 p1 = ldPoint(pts + (h1 ? j + G : j));
     test1<SELFCHK>(p0, j, q, selfId, b, visits);
     if (h1) test1<SELFCHK>(p1, j + G, q, selfId, b, visits);
   }
@@ -279,12 +286,15 @@ __device__ __forceinline__ void knn1Query(const float4* __restrict__ pts, const 
     }
   }
   scanCoop<G, SELFCHK>(pts, sC, eC, l, q, selfId, best, visits);
-  groupMin<G>(best);
   {
+    // pruning needs only the group's best DISTANCE so far (3 shuffles); the lane-local (key, pos) pairs are merged once, below
+    float bound = best.d();
+#pragma unroll
+    for (int o = G / 2; o > 0; o >>= 1) bound = fminf(bound, __shfl_xor_sync(FULL, bound, o));
     unsigned m = 0;
 #pragma unroll
     for (int t = 0; t < NR; ++t) {
-      const bool alive = (eL[t] > sL[t]) && !(lbL[t] > best.d());
+      const bool alive = (eL[t] > sL[t]) && !(lbL[t] > bound);
       m |= ((__ballot_sync(FULL, alive) >> gbase) & ((1u << G) - 1u)) << (t * G);
     }
     while (__any_sync(FULL, m != 0u)) {
@@ -297,7 +307,7 @@ __device__ __forceinline__ void knn1Query(const float4* __restrict__ pts, const 
         const float lb1 = __shfl_sync(FULL, lbL[NR - 1], src);
         if (r >= G) { s = s1; e = e1; lb = lb1; }
       }
-      if (!m || lb > best.d()) e = s;   // lane-local re-prune (a lane's own best only improves)
+      if (!m || lb > fminf(bound, best.d())) e = s;   // lane-local re-prune (a lane's own best only improves)
       m &= m - 1u;
       scanCoop<G, SELFCHK>(pts, s, e, l, q, selfId, best, visits);
     }
@@ -307,11 +317,14 @@ __device__ __forceinline__ void knn1Query(const float4* __restrict__ pts, const 
   // ---- rings >= 2: the (y,z) rows of each shell are dealt to the G lanes.  Any point of a ring >= 2 is farther than
   // sqrt(ring2Safe) (one whole cell minus the fp32 assignment slack), so a closer best ends the search here.
   {
-    const int r0 = max(max(max(-ax.c, ax.c - (g.nx - 1)), max(-ay.c, ay.c - (g.ny - 1))), max(max(-az.c, az.c - (g.nz - 1)), 0));
-    const int rEnd = max(max(max(ax.c, g.nx - 1 - ax.c), max(ay.c, g.ny - 1 - ay.c)), max(az.c, g.nz - 1 - az.c));
-    int r = max(2, r0);
-    bool need = finite && r <= rEnd && !(best.d() < g.ring2Safe);
-    if (need) need = !(ringLowerBound(ax, ay, az, r, g.cell, g.slack) > best.d());
+    int r = 2, rEnd = 0;
+    bool need = finite && !(best.d() < g.ring2Safe);
+    if (need) {
+      const int r0 = max(max(max(-ax.c, ax.c - (g.nx - 1)), max(-ay.c, ay.c - (g.ny - 1))), max(max(-az.c, az.c - (g.nz - 1)), 0));
+      rEnd = max(max(max(ax.c, g.nx - 1 - ax.c), max(ay.c, g.ny - 1 - ay.c)), max(az.c, g.nz - 1 - az.c));
+      r = max(2, r0);
+      need = r <= rEnd && !(ringLowerBound(ax, ay, az, r, g.cell, g.slack) > best.d());
+    }
     const unsigned gmask = ((1u << G) - 1u) << gbase;
     float bound = best.d();   // group-wide pruning bound (starts at maxDist^2); lane-local bests are merged after each ring
     while (__any_sync(FULL, need)) {
