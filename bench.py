@@ -28,6 +28,7 @@ sys.path.insert(0, os.path.join(ROOT, "tests"))
 B_KNN1 = 536          # algorithmic bytes per k=1 query   (SURVEY 8d / BASELINE.md §5)
 B_ITER = 600          # algorithmic bytes per reading point per ICP iteration
 B_BUILD = 156         # algorithmic bytes per reference point for the index build
+NCU_TRAFFIC_BYTES = None   # dram__bytes_read + write per match launch from the committed `ncu --set full` capture (profiles/)
 ICP_KW = dict(knn=1, max_dist=1.0, trim_ratio=0.8, max_iter=40, min_diff_rot=1e-3, min_diff_trans=1e-2, smooth_length=3)
 
 
@@ -247,22 +248,27 @@ def main():
     value = world * 1000.0 / ms_per_step
     e2e_value = world * 1000.0 / (e2e_total_ms / args.steps)
 
-    # ---------------- roofline of the dominant kernel (kNN), timed live with CUDA events on the launching stream
+    # ---------------- roofline of the dominant kernel (the k = 1 match), timed live with CUDA events on the launching stream:
+    # profiling mode brackets EVERY match launch of a registration with its own event pair (kernel-only time, no host
+    # work inside the bracket); the same registrations as the timed steps, L2 flushed before each one.
     index = icp.index
-    knn_ms = []
+    ctx.set_profiling(True)
+    per_launch = []
+    for r in range(2 + args.knn_reps):
+        ctx.flush_l2()
+        icp.register(cscan, w["T_init"])
+        ms = ctx.profile_read()
+        if r >= 2:
+            per_launch.append(ms)
+    ctx.set_profiling(False)
+    per_launch = np.array(per_launch)                   # reps x iterations
+    knn_t = float(per_launch.mean())                    # average launch duration over the registrations
+    knn_conv = float(per_launch[:, -1].mean())          # the launch at the converged pose
     mean = icp.reference_mean
     Tpre = np.eye(4, dtype=np.float32)
     Tpre[:3, 3] = -mean
     Tq = (Tpre.astype(np.float64) @ T.astype(np.float64)).astype(np.float32)    # converged pose in the refMean frame
-    for r in range(3 + args.knn_reps):
-        ctx.flush_l2()
-        ctx.timer_start()
-        ctx.knn(index, cscan, T=Tq, k=1, max_dist=1.0, want=False)
-        dt = ctx.timer_stop()
-        if r >= 3:
-            knn_ms.append(dt)
     _, _, visits = ctx.knn(index, cscan, T=Tq, k=1, max_dist=1.0, want=False)
-    knn_t = float(np.mean(knn_ms))
     peak, peak_src = hbm_peak()
     achieved = B_KNN1 * n / (knn_t * 1e-3) / 1e9
     iter_gbs = B_ITER * n * iters / (float(np.mean(dev_ms)) * 1e-3) / 1e9
@@ -285,11 +291,15 @@ def main():
                    "translation_error_vs_truth_m": err_t, "device_ms_per_registration": float(np.mean(dev_ms)),
                    "wall_s_timed_region": wall_s},
         "knn_queries_per_s": n / (knn_t * 1e-3), "knn_visits_per_query": visits / n,
-        "roofline": {"bound": "hbm", "kernel": "knnKernel<1>", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": None, "peak_source": peak_src, "algorithmic_bytes_per_launch": B_KNN1 * n, "avg_launch_ms": knn_t,
+        "roofline": {"bound": "hbm", "kernel": "knn1GroupKernel<8> (k = 1 match; knn1LoopKernel is the same body inside the graph loop)",
+                     "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                     "traffic": NCU_TRAFFIC_BYTES, "peak_source": peak_src, "algorithmic_bytes_per_launch": B_KNN1 * n, "avg_launch_ms": knn_t,
+                     "launch_ms_by_iteration": [float(x) for x in per_launch.mean(0)],
+                     "converged_launch_ms": knn_conv, "converged_frac": B_KNN1 * n / (knn_conv * 1e-3) / 1e9 / peak,
+                     "timing": "CUDA event pair around every match launch of %d registrations (host-driven loop, same kernels), L2 flushed before each" % per_launch.shape[0],
                      "iteration_gbs_600B_per_pt": iter_gbs, "iteration_frac": iter_gbs / peak},
         "e2e": {"value": e2e_value, "unit": "registrations/s", "h2d_bytes_per_step": int(scan_host.nbytes + 64),
-                "d2h_bytes_per_step": int(iters * (36 * 8 + 64 + 8) + 64), "ms_per_step": e2e_total_ms / args.steps},
+                "d2h_bytes_per_step": 144, "ms_per_step": e2e_total_ms / args.steps},
         "gpu_launches": int(launches), "clocks": clocks,
     }
     if not args.no_cpu_baseline:

@@ -35,7 +35,8 @@ struct b200reg_ctx {
   cudaEvent_t* profEv = nullptr;   // 2 x B200_PROF_MAX events, created on first use
   int trace = 0;             // b200reg_ctx_set_trace: stamp kernel starts of the device-resident loop
   int hostLoop = 0;          // env B200REG_HOST_LOOP=1: keep the ICP iterate loop on the host (A/B against the graph loop)
-  int knnLanes = 8;          // lanes per query of the k = 1 match kernel: 8, 4, or 1 (the general kernel); env B200REG_KNN_LANES for A/B runs
+  int knnLanes = 0;          // lanes per query of the k = 1 match kernel: 0 automatic (8; the loop switches to 4 once far queries are rare),
+                             // 8, 4, or 1 (the general kernel) forced by env B200REG_KNN_LANES for A/B runs
   void* pinned = nullptr;   // pinned host staging for small D2H results
   size_t pinned_cap = 0;
   void* dstate = nullptr;   // small device state block (select state, counters)
@@ -94,6 +95,7 @@ struct IcpDevParams {   // written by the host once per registration
   int useTrim, useAngle, force2D, force4DOF;
   int maxIter, smoothLength;
   float minDiffRot, minDiffTrans, boundRot, boundTrans;
+  int lanesForced;             // 0: chosen per iteration from the far-query count
   unsigned long long* trace;   // nullable: [0] = entry count, [1 + i] = (kernel tag << 56) | %globaltimer at the start of the i-th kernel of the loop
 };
 struct IcpDevState {    // initialised by the host, advanced by icpTailKernel every iteration, read back once at the end
@@ -104,6 +106,9 @@ struct IcpDevState {    // initialised by the host, advanced by icpTailKernel ev
   float tau;
   int pad;
   unsigned long long visits;
+  unsigned long long farPrev;   // far-query counter at the end of the previous iteration
+  int lanes;                    // lanes per query of the next match launch
+  int pad2;
   CheckerState chk;
 };
 #define ICP_STATE_HEAD_BYTES offsetof(IcpDevState, chk)

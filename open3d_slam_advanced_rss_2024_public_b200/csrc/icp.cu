@@ -6,7 +6,7 @@
 
 #include "icp_kernels.cuh"
 
-int launchKnn1Loop(b200reg_ctx* ctx, const IcpDevParams* P, const IcpDevState* S, int blocks);
+int launchKnn1Loop(b200reg_ctx* ctx, const IcpDevParams* P, const IcpDevState* S, unsigned long long* counters, int blocks);
 int runKnn(b200reg_ctx* ctx, const b200reg_index* ix, const float4* queries, int64_t n, const float* T, int k, float maxDist, int allowSelf);
 int cloudStats(b200reg_ctx* ctx, const b200reg_cloud* c, double sum[3], float mn[3], float mx[3]);
 int buildIndex(b200reg_ctx* ctx, const b200reg_cloud* ref, const float mean[3], const float bbMin[3], const float bbMax[3], float cell,
@@ -16,6 +16,8 @@ namespace {
 
 inline SelState* selState(b200reg_ctx* ctx) { return (SelState*)((char*)ctx->dstate + DSTATE_SEL_OFF); }
 inline unsigned* histPtr(b200reg_ctx* ctx) { return (unsigned*)((char*)ctx->dstate + DSTATE_HIST_OFF); }
+#define LOOP_PARAMS_OFF 64
+#define LOOP_STATE_OFF 512
 inline double* resultPtr(b200reg_ctx* ctx) { return (double*)((char*)ctx->dstate + DSTATE_RESULT_OFF); }
 
 // Trimmed-distance selection (Matches::getDistsQuantile): three multi-block radix passes.  DP != nullptr: arguments from the
@@ -417,6 +419,7 @@ struct b200reg_icp {
   double refPrepS = 0;
   DevBuf reading, readingNrm;       // `reading` of ICP.cpp:352-375 (in the refMean frame)
   // device-resident iterate loop (k = 1): a CUDA graph whose body is a `while` conditional node
+  char* dBlock = nullptr;           // ONE device block: [visit / far counters, 64 B | IcpDevParams, 448 B | IcpDevState]: one H2D copy per registration
   IcpDevParams* dP = nullptr;
   IcpDevState* dS = nullptr;
   cudaGraph_t graph = nullptr;
@@ -576,6 +579,8 @@ __global__ void __launch_bounds__(32) icpTailKernel(const IcpDevParams* __restri
   const int selError = __ldcg(&st->error);
   const unsigned tauBits = __ldcg(&st->tauBits);
   const unsigned long long visits = __ldcg(visitCounter);
+  const unsigned long long farNow = __ldcg(visitCounter + 1);
+  const unsigned long long farPrev = S->farPrev;
   float Told[16];
 #pragma unroll
   for (int i = 0; i < 16; ++i) Told[i] = S->T[i];
@@ -602,6 +607,8 @@ __global__ void __launch_bounds__(32) icpTailKernel(const IcpDevParams* __restri
   S->valid = mom[M_VALID];
   S->tau = p.useTrim ? __uint_as_float(tauBits) : CUDART_INF_F;
   S->visits = visits;
+  S->farPrev = farNow;
+  S->lanes = p.lanesForced ? p.lanesForced : (((farNow - farPrev) * 16ull < (unsigned long long)p.n) ? 4 : 8);
   S->errKind = err;
   S->errA = errv[0]; S->errB = errv[1]; S->errC = errv[2]; S->errD = errv[3];
   S->maxIterReached = maxIter ? 1 : 0;
@@ -644,7 +651,7 @@ int buildLoopGraph(b200reg_icp* icp) {
     GRAPH_TRY(cudaStreamBeginCaptureToGraph(ctx->stream, body, nullptr, nullptr, 0, cudaStreamCaptureModeThreadLocal));
     capturing = true;
     int nodes = 0;
-    launchKnn1Loop(ctx, icp->dP, icp->dS, knnBlocks);
+    launchKnn1Loop(ctx, icp->dP, icp->dS, (unsigned long long*)icp->dBlock, knnBlocks);
     ++nodes;
     const uint64_t l0 = ctx->launches;
     if (useTrim && launchSelect(ctx, nullptr, 0, 0.f, icp->dP) != B200REG_OK) { why = "select launch"; code = cudaErrorUnknown; goto fail; }
@@ -653,7 +660,7 @@ int buildLoopGraph(b200reg_icp* icp) {
     ReduceParams RP;
     memset(&RP, 0, sizeof(RP));
     reduceKernel<<<redBlocks, 256, 0, ctx->stream>>>(RP, st, nullptr, &st->ticket[3], resultPtr(ctx), icp->dP, icp->dS);
-    icpTailKernel<<<1, 32, 0, ctx->stream>>>(icp->dP, icp->dS, resultPtr(ctx), st, (const unsigned long long*)ctx->dstate, handle);
+    icpTailKernel<<<1, 32, 0, ctx->stream>>>(icp->dP, icp->dS, resultPtr(ctx), st, (const unsigned long long*)icp->dBlock, handle);
     nodes += 2;
     GRAPH_TRY(cudaGetLastError());
     capturing = false;
@@ -690,11 +697,13 @@ int32_t b200reg_icp_create(b200reg_ctx* ctx, const b200reg_icp_config* cfg, b200
   icp->ctx = ctx;
   icp->cfg = *cfg;
   CUDA_TRY(ctx, cudaSetDevice(ctx->device));
-  if (cudaMalloc(&icp->dP, sizeof(IcpDevParams)) != cudaSuccess || cudaMalloc(&icp->dS, sizeof(IcpDevState)) != cudaSuccess) {
-    if (icp->dP) cudaFree(icp->dP);
+  static_assert(sizeof(IcpDevParams) <= LOOP_STATE_OFF - LOOP_PARAMS_OFF, "loop block layout");
+  if (cudaMalloc(&icp->dBlock, LOOP_STATE_OFF + sizeof(IcpDevState)) != cudaSuccess) {
     delete icp;
     return setErr(ctx, B200REG_E_OOM, "icp_create: allocation failed");
   }
+  icp->dP = (IcpDevParams*)(icp->dBlock + LOOP_PARAMS_OFF);
+  icp->dS = (IcpDevState*)(icp->dBlock + LOOP_STATE_OFF);
   *out = icp;
   return B200REG_OK;
 }
@@ -709,8 +718,7 @@ void b200reg_icp_destroy(b200reg_icp* icp) {
   if (icp->readingNrm.p) cudaFree(icp->readingNrm.p);
   if (icp->exec) cudaGraphExecDestroy(icp->exec);
   if (icp->graph) cudaGraphDestroy(icp->graph);
-  if (icp->dP) cudaFree(icp->dP);
-  if (icp->dS) cudaFree(icp->dS);
+  if (icp->dBlock) cudaFree(icp->dBlock);
   delete icp;
 }
 
@@ -785,9 +793,11 @@ int32_t b200reg_icp_register(b200reg_icp* icp, const b200reg_cloud* reading, con
     TRY(ensureBuf(ctx, ctx->matchD2, sizeof(float) * (size_t)n));
     TRY(ensureBuf(ctx, ctx->matchPos, sizeof(int) * (size_t)n));
     char* pin = (char*)ctx->pinned;
-    IcpDevParams* hP = (IcpDevParams*)(pin + 8192);
-    IcpDevState* hS = (IcpDevState*)(pin + 12288);
+    char* hBlock = pin + 8192;   // host image of the loop block
+    IcpDevParams* hP = (IcpDevParams*)(hBlock + LOOP_PARAMS_OFF);
+    IcpDevState* hS = (IcpDevState*)(hBlock + LOOP_STATE_OFF);
     IcpDevState* hR = (IcpDevState*)(pin + 16384);
+    memset(hBlock, 0, LOOP_PARAMS_OFF);   // visit / far counters
     memset(hP, 0, sizeof(*hP));
     hP->pts = icp->index->pts; hP->nrm = icp->index->nrm; hP->cellStart = icp->index->cellStart; hP->g = icp->index->g;
     hP->reading = (const float4*)icp->reading.p;
@@ -804,15 +814,16 @@ int32_t b200reg_icp_register(b200reg_icp* icp, const b200reg_cloud* reading, con
     hP->maxIter = cfg.max_iter; hP->smoothLength = cfg.smooth_length;
     hP->minDiffRot = cfg.min_diff_rot; hP->minDiffTrans = cfg.min_diff_trans;
     hP->boundRot = cfg.bound_rot; hP->boundTrans = cfg.bound_trans;
+    hP->lanesForced = (ctx->knnLanes == 4 || ctx->knnLanes == 8) ? ctx->knnLanes : 0;
     hP->trace = ctx->trace ? (unsigned long long*)((char*)ctx->dstate + DSTATE_TRACE_OFF) : nullptr;
     if (ctx->trace) CUDA_TRY(ctx, cudaMemsetAsync((char*)ctx->dstate + DSTATE_TRACE_OFF, 0, sizeof(unsigned long long), ctx->stream));
     memset(hS, 0, sizeof(*hS));
     memcpy(hS->T, T_iter, sizeof(T_iter));
     hS->iterate = 1;
+    hS->lanes = (ctx->knnLanes == 4) ? 4 : 8;
     checkersInit(hS->chk, T_iter);
-    CUDA_TRY(ctx, cudaMemcpyAsync(icp->dP, hP, sizeof(*hP), cudaMemcpyHostToDevice, ctx->stream));
-    CUDA_TRY(ctx, cudaMemcpyAsync(icp->dS, hS, sizeof(*hS), cudaMemcpyHostToDevice, ctx->stream));
-    CUDA_TRY(ctx, cudaMemsetAsync(ctx->dstate, 0, sizeof(unsigned long long), ctx->stream));
+    // counters + parameters + the part of the state the loop reads before writing it (head, checker counters, first ring slot)
+    CUDA_TRY(ctx, cudaMemcpyAsync(icp->dBlock, hBlock, LOOP_STATE_OFF + sizeof(IcpDevState), cudaMemcpyHostToDevice, ctx->stream));
     CUDA_TRY(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
     CUDA_TRY(ctx, cudaGraphLaunch(icp->exec, ctx->stream));
     CUDA_TRY(ctx, cudaEventRecord(ctx->ev1, ctx->stream));

@@ -239,7 +239,7 @@ __device__ __forceinline__ float ringLowerBound(const AxisGeom& ax, const AxisGe
 template <int G, bool SELFCHK>
 __device__ __forceinline__ void knn1Query(const float4* __restrict__ pts, const uint32_t* __restrict__ cellStart, const GridDesc& g,
                                           const float4* __restrict__ queries, int64_t n, int64_t qi, int hasT, const Rigid12& T, float maxd2,
-                                          int* __restrict__ outIds, float* __restrict__ outD2, int* __restrict__ outPos, unsigned& visits) {
+                                          int* __restrict__ outIds, float* __restrict__ outD2, int* __restrict__ outPos, unsigned& visits, unsigned& farQ) {
   constexpr unsigned FULL = 0xffffffffu;
   constexpr int NR = 8 / G;   // non-centre rows owned by each lane
   const int lane = threadIdx.x & 31, l = lane & (G - 1), gbase = lane & (32 - G);
@@ -325,6 +325,7 @@ __device__ __forceinline__ void knn1Query(const float4* __restrict__ pts, const 
       r = max(2, r0);
       need = r <= rEnd && !(ringLowerBound(ax, ay, az, r, g.cell, g.slack) > best.d());
     }
+    if (need && l == 0) ++farQ;   // statistic: queries the 3x3x3 neighbourhood could not settle (drives the lanes-per-query choice)
     const unsigned gmask = ((1u << G) - 1u) << gbase;
     float bound = best.d();   // group-wide pruning bound (starts at maxDist^2); lane-local bests are merged after each ring
     while (__any_sync(FULL, need)) {
@@ -387,15 +388,21 @@ __device__ __forceinline__ void knn1Query(const float4* __restrict__ pts, const 
 
 // touched-point statistic (Matcher::visitCounter): warp shuffle -> shared; the last warp out adds the block total (no barrier
 // at the end of the kernel: warps retire as they finish)
-__device__ __forceinline__ void flushVisits(unsigned visits, unsigned* sVisits, unsigned* sTicket, unsigned long long* visitCounter) {
+__device__ __forceinline__ void flushVisits(unsigned visits, unsigned farQ, unsigned* sVisits, unsigned* sFarQ, unsigned* sTicket,
+                                            unsigned long long* visitCounter) {
 #pragma unroll
-  for (int o = 16; o > 0; o >>= 1) visits += __shfl_xor_sync(0xffffffffu, visits, o);
+  for (int o = 16; o > 0; o >>= 1) {
+    visits += __shfl_xor_sync(0xffffffffu, visits, o);
+    farQ += __shfl_xor_sync(0xffffffffu, farQ, o);
+  }
   if ((threadIdx.x & 31) == 0) {
     atomicAdd(sVisits, visits);
+    if (farQ) atomicAdd(sFarQ, farQ);
     __threadfence_block();
     if (atomicAdd(sTicket, 1u) == (blockDim.x >> 5) - 1u) {
-      const unsigned total = atomicAdd(sVisits, 0u);
+      const unsigned total = atomicAdd(sVisits, 0u), far = atomicAdd(sFarQ, 0u);
       if (total) atomicAdd(visitCounter, (unsigned long long)total);
+      if (far) atomicAdd(visitCounter + 1, (unsigned long long)far);   // dstate[1]: far-query count
     }
   }
 }
@@ -406,26 +413,22 @@ __global__ void __launch_bounds__(256) knn1GroupKernel(const float4* __restrict_
                                                        int* __restrict__ outIds, float* __restrict__ outD2, int* __restrict__ outPos,
                                                        unsigned long long* __restrict__ visitCounter) {
   constexpr int LOG2G = (G == 8) ? 3 : 2;
-  __shared__ unsigned sVisits, sTicket;
-  if (threadIdx.x == 0) { sVisits = 0; sTicket = 0; }
+  __shared__ unsigned sVisits, sFarQ, sTicket;
+  if (threadIdx.x == 0) { sVisits = 0; sFarQ = 0; sTicket = 0; }
   __syncthreads();   // all warps are at the start here: nobody waits on a straggler
-  unsigned visits = 0;
+  unsigned visits = 0, farQ = 0;
   const int64_t qi = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> LOG2G;
-  knn1Query<G, SELFCHK>(pts, cellStart, g, queries, n, qi, hasT, T, maxd2, outIds, outD2, outPos, visits);
-  flushVisits(visits, &sVisits, &sTicket, visitCounter);
+  knn1Query<G, SELFCHK>(pts, cellStart, g, queries, n, qi, hasT, T, maxd2, outIds, outD2, outPos, visits, farQ);
+  flushVisits(visits, farQ, &sVisits, &sFarQ, &sTicket, visitCounter);
 }
 
 // The same search inside the device-resident registration loop (icp.cu): arguments and the iteration transform are read from
 // the loop's blocks in HBM, the grid is fixed (a multiple of the SM count) and strides over the queries, so one
 // instantiated CUDA graph serves every reading size and reference.
 template <int G>
-__global__ void __launch_bounds__(256, 6) knn1LoopKernel(const IcpDevParams* __restrict__ P, const IcpDevState* __restrict__ S,
-                                                      unsigned long long* __restrict__ visitCounter) {
+__device__ __forceinline__ void knn1LoopBody(const IcpDevParams* __restrict__ P, const IcpDevState* __restrict__ S, unsigned& visits,
+                                             unsigned& farQ) {
   constexpr int LOG2G = (G == 8) ? 3 : 2;
-  __shared__ unsigned sVisits, sTicket;
-  if (threadIdx.x == 0) { sVisits = 0; sTicket = 0; }
-  __syncthreads();
-  traceStamp(P->trace, 1);
   const GridDesc g = P->g;
   const float4* pts = P->pts;
   const uint32_t* cellStart = P->cellStart;
@@ -438,13 +441,25 @@ __global__ void __launch_bounds__(256, 6) knn1LoopKernel(const IcpDevParams* __r
   Rigid12 T;
 #pragma unroll
   for (int j = 0; j < 12; ++j) T.m[j] = S->T[j];
-  unsigned visits = 0;
   const int64_t groupsPerGrid = ((int64_t)gridDim.x * blockDim.x) >> LOG2G;
   const int64_t first = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> LOG2G;
   const int64_t blockFirst = ((int64_t)blockIdx.x * blockDim.x) >> LOG2G;
   for (int64_t base = 0; blockFirst + base < n; base += groupsPerGrid)   // trip count uniform over the block
-    knn1Query<G, false>(pts, cellStart, g, queries, n, first + base, 1, T, maxd2, ids, d2, pos, visits);
-  flushVisits(visits, &sVisits, &sTicket, visitCounter);
+    knn1Query<G, false>(pts, cellStart, g, queries, n, first + base, 1, T, maxd2, ids, d2, pos, visits, farQ);
+}
+
+// S->lanes (written by the loop's tail from the previous iteration's far-query count) picks the decomposition: 8 lanes per
+// query while many queries need rings >= 2 (the first iterations of a badly aligned scan), 4 once they are rare.
+__global__ void __launch_bounds__(256, 6) knn1LoopKernel(const IcpDevParams* __restrict__ P, const IcpDevState* __restrict__ S,
+                                                         unsigned long long* __restrict__ visitCounter) {
+  __shared__ unsigned sVisits, sFarQ, sTicket;
+  if (threadIdx.x == 0) { sVisits = 0; sFarQ = 0; sTicket = 0; }
+  __syncthreads();
+  traceStamp(P->trace, 1);
+  unsigned visits = 0, farQ = 0;
+  if (S->lanes == 4) knn1LoopBody<4>(P, S, visits, farQ);
+  else knn1LoopBody<8>(P, S, visits, farQ);
+  flushVisits(visits, farQ, &sVisits, &sFarQ, &sTicket, visitCounter);
 }
 
 template <int G>
@@ -465,10 +480,8 @@ void launchKnn(b200reg_ctx* ctx, const b200reg_index* ix, const float4* q, int64
 }  // namespace
 
 // k = 1 match of the device-resident loop; `blocks` is fixed by the caller (graph capture)
-int launchKnn1Loop(b200reg_ctx* ctx, const IcpDevParams* P, const IcpDevState* S, int blocks) {
-  unsigned long long* visits = (unsigned long long*)ctx->dstate;
-  if (ctx->knnLanes == 4) knn1LoopKernel<4><<<blocks, 256, 0, ctx->stream>>>(P, S, visits);
-  else knn1LoopKernel<8><<<blocks, 256, 0, ctx->stream>>>(P, S, visits);
+int launchKnn1Loop(b200reg_ctx* ctx, const IcpDevParams* P, const IcpDevState* S, unsigned long long* counters, int blocks) {
+  knn1LoopKernel<<<blocks, 256, 0, ctx->stream>>>(P, S, counters);
   return B200REG_OK;
 }
 
@@ -491,7 +504,7 @@ int runKnn(b200reg_ctx* ctx, const b200reg_index* ix, const float4* queries, int
   unsigned long long* visits = (unsigned long long*)ctx->dstate;
   const int hasT = T ? 1 : 0;
   profBegin(ctx);
-  if (k == 1 && ctx->knnLanes == 8) launchKnn1<8>(ctx, ix, queries, n, hasT, R, maxd2, allowSelf, ids, d2, pos, visits);
+  if (k == 1 && (ctx->knnLanes == 8 || ctx->knnLanes == 0)) launchKnn1<8>(ctx, ix, queries, n, hasT, R, maxd2, allowSelf, ids, d2, pos, visits);
   else if (k == 1 && ctx->knnLanes == 4) launchKnn1<4>(ctx, ix, queries, n, hasT, R, maxd2, allowSelf, ids, d2, pos, visits);
   else if (k == 1) launchKnn<1>(ctx, ix, queries, n, hasT, R, k, maxd2, allowSelf, ids, d2, pos, visits);
   else if (k <= 4) launchKnn<4>(ctx, ix, queries, n, hasT, R, k, maxd2, allowSelf, ids, d2, pos, visits);
