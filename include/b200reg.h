@@ -71,6 +71,10 @@ int32_t b200reg_ctx_trace_read(b200reg_ctx* ctx, uint64_t* out, int32_t cap, int
  *      (open3d_slam_rsl/open3d_utils/open3d_conversions/src/open3d_conversions.cpp:21-118) -------------------------- */
 int32_t b200reg_cloud_upload_f32(b200reg_ctx* ctx, const float* feat, int32_t feat_stride, const float* normals, int64_t n,
                                  b200reg_cloud** out);
+/* streaming re-fill of an existing device cloud (no allocation once its capacity suffices).  async != 0: enqueue only; the host
+ * arrays must stay valid and unmodified until the next synchronising call on this ctx (pinned memory: upload + registration = one sync) */
+int32_t b200reg_cloud_update_f32(b200reg_ctx* ctx, b200reg_cloud* cloud, const float* feat, int32_t feat_stride, const float* normals,
+                                 int64_t n, int32_t async);
 int32_t b200reg_cloud_upload_f64(b200reg_ctx* ctx, const double* xyz, const double* normals, int64_t n, b200reg_cloud** out);
 int32_t b200reg_cloud_download_f32(b200reg_ctx* ctx, const b200reg_cloud* cloud, float* feat, int32_t feat_stride, float* normals);
 int64_t b200reg_cloud_size(const b200reg_cloud* cloud);

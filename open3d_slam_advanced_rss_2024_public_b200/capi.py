@@ -95,6 +95,7 @@ SYMBOLS = {
     "b200reg_ctx_set_trace": (C.c_int32, [_VP, C.c_int32]),
     "b200reg_ctx_trace_read": (C.c_int32, [_VP, _VP, C.c_int32, C.POINTER(C.c_int32)]),
     "b200reg_cloud_upload_f32": (C.c_int32, [_VP, _VP, C.c_int32, _VP, C.c_int64, C.POINTER(_VP)]),
+    "b200reg_cloud_update_f32": (C.c_int32, [_VP, _VP, _VP, C.c_int32, _VP, C.c_int64, C.c_int32]),
     "b200reg_cloud_upload_f64": (C.c_int32, [_VP, _VP, _VP, C.c_int64, C.POINTER(_VP)]),
     "b200reg_cloud_download_f32": (C.c_int32, [_VP, _VP, _VP, C.c_int32, _VP]),
     "b200reg_cloud_size": (C.c_int64, [_VP]),
@@ -333,6 +334,13 @@ class Cloud:
     @property
     def has_normals(self):
         return bool(lib().b200reg_cloud_has_normals(self.h))
+
+    def update(self, feat, normals=None, wait=True):
+        """Re-fill this device cloud from host arrays.  wait=False only enqueues the copy: keep `feat` alive and untouched
+        until the next result-returning call (use pinned memory, e.g. torch's pin_memory, for a truly asynchronous copy)."""
+        feat, nrm = _f32(feat), _f32(normals)
+        self._keep = (feat, nrm)
+        self.ctx.check(lib().b200reg_cloud_update_f32(self.ctx.h, self.h, _p(feat), feat.shape[1], _p(nrm), feat.shape[0], 0 if wait else 1))
 
     def download(self, stride=4, normals=None):
         n = self.size

@@ -270,6 +270,46 @@ int32_t b200reg_cloud_upload_f32(b200reg_ctx* ctx, const float* feat, int32_t fe
   return B200REG_OK;
 }
 
+// Re-fill an existing device cloud from host memory (the streaming case: one scan buffer reused for every scan).  Capacity
+// grows when needed and never shrinks.  async != 0: the copy is only enqueued — the caller keeps `feat` / `normals` valid and
+// unmodified until the next call on this ctx that synchronises (any call returning results, or b200reg_ctx_sync); with
+// pinned host memory upload and registration then cost a single synchronisation.
+int32_t b200reg_cloud_update_f32(b200reg_ctx* ctx, b200reg_cloud* c, const float* feat, int32_t feat_stride, const float* normals,
+                                 int64_t n, int32_t async) {
+  if (!ctx || !c || n < 0 || (n > 0 && !feat) || feat_stride < 3) return setErr(ctx, B200REG_E_INVALID_PARAM, "cloud_update_f32: bad arguments");
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  if (n > c->cap || (normals && !c->nrm)) {
+    CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+    const int64_t cap = n > c->cap ? n : c->cap;
+    float4 *nx = nullptr, *nn = nullptr;
+    cudaError_t e = cudaMalloc(&nx, sizeof(float4) * (size_t)cap);
+    if (e == cudaSuccess && (normals || c->nrm)) e = cudaMalloc(&nn, sizeof(float4) * (size_t)cap);
+    if (e != cudaSuccess) {
+      if (nx) cudaFree(nx);
+      return setErr(ctx, B200REG_E_OOM, "cloud_update_f32: allocation of %lld points failed: %s", (long long)cap, cudaGetErrorString(e));
+    }
+    if (c->xyz) cudaFree(c->xyz);
+    if (c->nrm) cudaFree(c->nrm);
+    c->xyz = nx; c->nrm = nn; c->cap = cap;
+  }
+  c->n = n;
+  if (n == 0) return B200REG_OK;
+  const size_t fb = sizeof(float) * (size_t)n * feat_stride, nb = normals ? sizeof(float) * 3 * (size_t)n : 0;
+  if (feat_stride == 4 && !normals) {
+    CUDA_TRY(ctx, cudaMemcpyAsync(c->xyz, feat, fb, cudaMemcpyHostToDevice, ctx->stream));
+  } else {
+    TRY(ensureBuf(ctx, ctx->misc, fb + nb + 16));
+    float* dfeat = (float*)ctx->misc.p;
+    float* dn = normals ? (float*)((char*)ctx->misc.p + ((fb + 15) / 16) * 16) : nullptr;
+    CUDA_TRY(ctx, cudaMemcpyAsync(dfeat, feat, fb, cudaMemcpyHostToDevice, ctx->stream));
+    if (normals) CUDA_TRY(ctx, cudaMemcpyAsync(dn, normals, nb, cudaMemcpyHostToDevice, ctx->stream));
+    packF32Kernel<<<divUp(n, 256), 256, 0, ctx->stream>>>(dfeat, feat_stride, dn, n, c->xyz, normals ? c->nrm : nullptr);
+    LAUNCH_CHECK(ctx);
+  }
+  if (!async) CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  return B200REG_OK;
+}
+
 int32_t b200reg_cloud_upload_f64(b200reg_ctx* ctx, const double* xyz, const double* normals, int64_t n, b200reg_cloud** out) {
   if (!ctx || !out || n < 0 || (n > 0 && !xyz)) return setErr(ctx, B200REG_E_INVALID_PARAM, "cloud_upload_f64: bad arguments");
   CUDA_TRY(ctx, cudaSetDevice(ctx->device));
