@@ -182,6 +182,14 @@ int32_t b200reg_icp_set_reference(b200reg_icp* icp, const b200reg_cloud* referen
 /* ICP::compute(reading, <empty>, T_init, initializeMatcher=false) (ICP.cpp:258-290 + 332-468), as Mapper.cpp:391-393 calls it */
 int32_t b200reg_icp_register(b200reg_icp* icp, const b200reg_cloud* reading, const float T_init[16], float T_out[16],
                              b200reg_icp_stats* stats);
+/* n independent registrations on this ctx's device: pair i = initReference(refs[i]) + compute(readings[i], T_init + 16 i)
+ * -> T_out + 16 i (the loop-closure refinement loop, open3d_slam/src/PlaceRecognition.cpp:71-174).  One call per
+ * GPU; sharding pairs over GPUs and gathering the results is the caller's (batch.py: pair i -> rank i mod G, one all_gather).
+ * stats / status: arrays of n, nullable.  With `status` the call returns OK and reports per-pair codes (a failed pair
+ * keeps T_out = T_init); without it the first failure code is returned. */
+int32_t b200reg_icp_register_batch(b200reg_ctx* ctx, const b200reg_icp_config* cfg, int32_t n, const b200reg_cloud* const* refs,
+                                   const b200reg_cloud* const* readings, const float* T_init, float* T_out, b200reg_icp_stats* stats,
+                                   int32_t* status);
 const b200reg_index* b200reg_icp_index(const b200reg_icp* icp);
 int32_t b200reg_icp_reference_mean(const b200reg_icp* icp, float mean_out[3]);
 

@@ -116,6 +116,7 @@ SYMBOLS = {
     "b200reg_icp_destroy": (None, [_VP]),
     "b200reg_icp_set_reference": (C.c_int32, [_VP, _VP]),
     "b200reg_icp_register": (C.c_int32, [_VP, _VP, _VP, _VP, C.POINTER(IcpStats)]),
+    "b200reg_icp_register_batch": (C.c_int32, [_VP, C.POINTER(IcpConfig), C.c_int32, _VP, _VP, _VP, _VP, _VP, _VP]),
     "b200reg_icp_index": (_VP, [_VP]),
     "b200reg_icp_reference_mean": (C.c_int32, [_VP, _VP]),
     "b200reg_voxelgrid": (C.c_int32, [_VP, _VP, C.c_float, C.c_float, C.c_float, C.c_int32, C.c_int32]),
@@ -447,6 +448,22 @@ class ICP:
                 self.close()
         except Exception:
             pass
+
+
+def register_batch(ctx, cfg, refs, readings, T_init):
+    """n independent registrations on ctx's device (b200reg_icp_register_batch).  refs / readings: lists of Cloud;
+    T_init: n x 4 x 4.  Returns (T n x 4 x 4 float32, [IcpStats], status int32[n])."""
+    n = len(refs)
+    assert len(readings) == n
+    Ti = np.ascontiguousarray(np.asarray(T_init, dtype=np.float32).reshape(n, 16))
+    To = np.zeros((n, 16), dtype=np.float32)
+    stats = (IcpStats * max(n, 1))()
+    status = np.zeros(max(n, 1), dtype=np.int32)
+    rh = (_VP * max(n, 1))(*[c.h.value if isinstance(c.h, _VP) else c.h for c in refs])
+    qh = (_VP * max(n, 1))(*[c.h.value if isinstance(c.h, _VP) else c.h for c in readings])
+    ctx.check(lib().b200reg_icp_register_batch(ctx.h, C.byref(cfg), n, C.cast(rh, _VP), C.cast(qh, _VP), _p(Ti), _p(To), C.cast(stats, _VP),
+                                               _p(status)))
+    return To.reshape(n, 4, 4), list(stats)[:n], status[:n]
 
 
 class VoxelMap:

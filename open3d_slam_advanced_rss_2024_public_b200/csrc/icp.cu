@@ -898,6 +898,34 @@ int32_t b200reg_icp_register(b200reg_icp* icp, const b200reg_cloud* reading, con
   return done(B200REG_OK);
 }
 
+// Batch of independent registrations on this ctx's device (loop-closure candidate refinement, PlaceRecognition.cpp:71-174:
+// independent iterations of a `for` loop).  Pair i: initReference(refs[i]) + compute(readings[i], T_init[i]).
+// A failing pair does not stop the batch: its status is recorded and its T_out is T_init (what Mapper.cpp:420-428 falls
+// back to when ICP throws).
+int32_t b200reg_icp_register_batch(b200reg_ctx* ctx, const b200reg_icp_config* cfg, int32_t n, const b200reg_cloud* const* refs,
+                                   const b200reg_cloud* const* readings, const float* T_init, float* T_out, b200reg_icp_stats* stats,
+                                   int32_t* status) {
+  if (!ctx || !cfg || n < 0 || (n > 0 && (!refs || !readings || !T_init || !T_out)))
+    return setErr(ctx, B200REG_E_INVALID_PARAM, "icp_register_batch: bad arguments");
+  b200reg_icp* icp = nullptr;
+  TRY(b200reg_icp_create(ctx, cfg, &icp));
+  int first = B200REG_OK;
+  for (int32_t i = 0; i < n; ++i) {
+    int code = (refs[i] && readings[i]) ? b200reg_icp_set_reference(icp, refs[i]) : B200REG_E_INVALID_PARAM;
+    b200reg_icp_stats st;
+    memset(&st, 0, sizeof(st));
+    if (code == B200REG_OK) code = b200reg_icp_register(icp, readings[i], T_init + 16 * (size_t)i, T_out + 16 * (size_t)i, &st);
+    if (code != B200REG_OK) {
+      memcpy(T_out + 16 * (size_t)i, T_init + 16 * (size_t)i, 16 * sizeof(float));
+      if (first == B200REG_OK) first = code;
+    }
+    if (stats) stats[i] = st;
+    if (status) status[i] = code;
+  }
+  b200reg_icp_destroy(icp);
+  return status ? B200REG_OK : first;   // with a status array the per-pair codes are the result
+}
+
 }  // extern "C"
 
 // =================================================================================================================

@@ -337,3 +337,108 @@ def test_icp_errors(ctx, oracle, golden):
         capi.ICP(ctx, knn=0)
     with pytest.raises(capi.InvalidParameter):
         capi.ICP(ctx, trim_ratio=1.5)
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# device-resident loop, batch, streaming upload
+# ---------------------------------------------------------------------------------------------------------------
+def test_graph_loop_equals_host_loop(ctx, oracle, golden):
+    """The CUDA-graph while loop (match, select, reduce, tail on the device) and the host-driven loop share their
+    arithmetic (__host__ __device__, no FMA contraction): same iteration count, transforms within one fp32 ulp-scale
+    step (device sin/cos vs glibc), both within tolerance of the oracle."""
+    from open3d_slam_advanced_rss_2024_public_b200 import capi
+    car = golden["car"]
+    ref, rn, q = oracle.feat4(car["ref_xyz"]), car["ref_normals"], oracle.feat4(car["data_xyz"])
+    kw = dict(knn=1, max_dist=1.0, trim_ratio=0.85, max_iter=40)
+    Ti = small_T(3, t=0.1, deg=2.0)
+    icp = capi.ICP(ctx, **kw)
+    icp.set_reference(ctx.upload(ref, rn))
+    cq = ctx.upload(q)
+    T_graph, st_graph = icp.register(cq, Ti)
+    ctx.set_profiling(True)          # profiling brackets force the host-driven loop
+    T_host, st_host = icp.register(cq, Ti)
+    ms = ctx.profile_read()
+    ctx.set_profiling(False)
+    assert len(ms) == st_host.iterations and (ms > 0).all()
+    assert st_graph.iterations == st_host.iterations
+    assert st_graph.kept_last == st_host.kept_last and st_graph.last_tau == st_host.last_tau
+    assert st_graph.points_touched > 0 and st_host.points_touched > 0   # (the count depends on the lanes-per-query decomposition)
+    assert np.abs(T_graph.astype(np.float64) - T_host).max() <= 2e-6
+    code, T_o, st_o = oracle.icp(oracle.icp_config(precision=oracle.ORC_MIXED, nthreads=8, **kw), ref, rn, q, None, Ti)
+    assert code == 0 and st_o.iterations == st_graph.iterations
+    assert_same_T(T_graph, T_o)
+    assert_same_T(T_host, T_o)
+    icp.close()
+
+
+def test_graph_loop_trace_and_reuse_across_sizes(ctx, oracle, golden):
+    """One instantiated graph serves every reading size / reference; the device trace shows the body's kernels per iteration."""
+    from open3d_slam_advanced_rss_2024_public_b200 import capi
+    car = golden["car"]
+    ref, rn, q = oracle.feat4(car["ref_xyz"]), car["ref_normals"], oracle.feat4(car["data_xyz"])
+    kw = dict(knn=1, max_dist=1.0, trim_ratio=0.85, max_iter=40)
+    icp = capi.ICP(ctx, **kw)
+    icp.set_reference(ctx.upload(ref, rn))
+    ctx.set_trace(True)
+    for n in (q.shape[0], 5000, 777, q.shape[0]):
+        T_g, st = icp.register(ctx.upload(q[:n]))
+        tr = ctx.trace_read()
+        tags = [t for t, _ in tr]
+        assert tags.count(1) == st.iterations and tags.count(5) == st.iterations and tags.count(7) == st.iterations
+        code, T_o, st_o = oracle.icp(oracle.icp_config(precision=oracle.ORC_MIXED, nthreads=8, **kw), ref, rn, q[:n])
+        assert code == 0 and st_o.iterations == st.iterations
+        assert_same_T(T_g, T_o)
+    ctx.set_trace(False)
+    icp.set_reference(ctx.upload(ref[::2], rn[::2]))     # new reference, same graph
+    T_g, st = icp.register(ctx.upload(q))
+    code, T_o, st_o = oracle.icp(oracle.icp_config(precision=oracle.ORC_MIXED, nthreads=8, **kw), ref[::2], rn[::2], q)
+    assert code == 0 and st_o.iterations == st.iterations
+    assert_same_T(T_g, T_o)
+    icp.close()
+
+
+def test_register_batch_matches_individual(ctx, oracle):
+    """b200reg_icp_register_batch (BASELINE config #4 shape, small): every pair equals its stand-alone registration and the
+    oracle; a failing pair reports its status and keeps T_init without stopping the batch."""
+    from open3d_slam_advanced_rss_2024_public_b200 import capi
+    kw = dict(knn=1, max_dist=1.0, trim_ratio=0.8, max_iter=40)
+    cfg = capi.icp_config(**kw)
+    refs, reads, Tis, expect = [], [], [], []
+    for i in range(3):
+        c = scenes.config2(m=60_000, n_beams=16, n_az=256, scene_seed=3000 + i)
+        ref, rn, q = oracle.feat4(c["map_xyz"]), c["map_nrm"].astype(np.float32), oracle.feat4(c["scan"])
+        refs.append(ctx.upload(ref, rn))
+        reads.append(ctx.upload(q))
+        Tis.append(c["T_init"].astype(np.float32))
+        code, T_o, st_o = oracle.icp(oracle.icp_config(precision=oracle.ORC_MIXED, nthreads=8, **kw), ref, rn, q, None, Tis[-1])
+        assert code == 0
+        expect.append((T_o, st_o.iterations))
+    far = np.eye(4, dtype=np.float32)
+    far[:3, 3] = 1000.0
+    refs.append(refs[0]); reads.append(reads[0]); Tis.append(far)
+    T, stats, status = capi.register_batch(ctx, cfg, refs, reads, np.stack(Tis))
+    assert list(status[:3]) == [0, 0, 0] and status[3] == capi.E_NOT_CONVERGED
+    assert np.array_equal(T[3], far)
+    for i in range(3):
+        assert stats[i].iterations == expect[i][1]
+        assert_same_T(T[i], expect[i][0])
+        icp = capi.ICP(ctx, **kw)
+        icp.set_reference(refs[i])
+        T_one, _ = icp.register(reads[i], Tis[i])
+        assert np.array_equal(T_one, T[i])
+        icp.close()
+
+
+def test_cloud_update_streaming(ctx, oracle, golden):
+    """b200reg_cloud_update_f32: re-fill (grow, shrink, async) == a fresh upload."""
+    car = golden["car"]
+    q = oracle.feat4(car["data_xyz"])
+    c = ctx.upload(q[:100])
+    for n, wait in ((5000, True), (50, True), (q.shape[0], False), (1234, False)):
+        c.update(q[:n], wait=wait)
+        f, _ = c.download()
+        assert c.size == n and np.array_equal(f, q[:n])
+    nrm = car["ref_normals"][:1234]
+    c.update(q[:1234, :3], normals=nrm)        # stride 3 + normals through the pack kernel
+    f, nn = c.download(normals=True)
+    assert np.array_equal(f[:, :3], q[:1234, :3]) and np.array_equal(nn, nrm)
