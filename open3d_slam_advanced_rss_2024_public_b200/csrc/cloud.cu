@@ -119,9 +119,11 @@ int32_t b200reg_ctx_create(int32_t device, b200reg_ctx** out) {
   cudaEventCreate(&ctx->ev1);
   cudaEventCreate(&ctx->tev0);
   cudaEventCreate(&ctx->tev1);
-  if (cudaMalloc(&ctx->dstate, 65536) != cudaSuccess) { delete ctx; return B200REG_E_OOM; }
-  cudaMemsetAsync(ctx->dstate, 0, 65536, ctx->stream);
+  if (cudaMalloc(&ctx->dstate, DSTATE_BYTES) != cudaSuccess) { delete ctx; return B200REG_E_OOM; }
+  cudaMemsetAsync(ctx->dstate, 0, DSTATE_BYTES, ctx->stream);
   if (ensurePinned(ctx, 1 << 16) != B200REG_OK) { delete ctx; return B200REG_E_OOM; }
+  const char* s3 = getenv("B200REG_SELECT_3PASS");
+  ctx->select3 = (s3 && s3[0] == '1') ? 1 : 0;
   const char* hl = getenv("B200REG_HOST_LOOP");
   ctx->hostLoop = (hl && hl[0] == '1') ? 1 : 0;
   const char* lanes = getenv("B200REG_KNN_LANES");
@@ -181,7 +183,7 @@ void b200reg_ctx_destroy(b200reg_ctx* ctx) {
     delete[] ctx->profEv;
   }
   DevBuf* bufs[] = {&ctx->keys0, &ctx->keys1, &ctx->vals0, &ctx->vals1, &ctx->cubtmp, &ctx->misc, &ctx->partials,
-                    &ctx->matchIds, &ctx->matchD2, &ctx->matchPos, &ctx->flags, &ctx->flush};
+                    &ctx->matchIds, &ctx->matchD2, &ctx->matchPos, &ctx->flags, &ctx->flush, &ctx->cand};
   for (DevBuf* b : bufs)
     if (b->p) cudaFree(b->p);
   if (ctx->pinned) cudaFreeHost(ctx->pinned);

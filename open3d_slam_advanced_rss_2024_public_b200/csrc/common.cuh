@@ -28,12 +28,13 @@ struct b200reg_ctx {
   char err[512] = {0};
   uint64_t launches = 0;
   // scratch
-  DevBuf keys0, keys1, vals0, vals1, cubtmp, misc, partials, matchIds, matchD2, matchPos, flags, flush;
+  DevBuf keys0, keys1, vals0, vals1, cubtmp, misc, partials, matchIds, matchD2, matchPos, flags, flush, cand;
   int flushToggle = 0;
   int profile = 0;           // b200reg_ctx_set_profiling
   int profCount = 0;
   cudaEvent_t* profEv = nullptr;   // 2 x B200_PROF_MAX events, created on first use
   int trace = 0;             // b200reg_ctx_set_trace: stamp kernel starts of the device-resident loop
+  int select3 = 0;           // env B200REG_SELECT_3PASS=1: three-launch radix select inside the graph loop too (A/B)
   int hostLoop = 0;          // env B200REG_HOST_LOOP=1: keep the ICP iterate loop on the host (A/B against the graph loop)
   int knnLanes = 0;          // lanes per query of the k = 1 match kernel: 0 automatic (8; the loop switches to 4 once far queries are rare),
                              // 8, 4, or 1 (the general kernel) forced by env B200REG_KNN_LANES for A/B runs
@@ -96,6 +97,11 @@ struct IcpDevParams {   // written by the host once per registration
   int maxIter, smoothLength;
   float minDiffRot, minDiffTrans, boundRot, boundTrans;
   int lanesForced;             // 0: chosen per iteration from the far-query count
+  // fused trimmed-distance selection (nullable = filter off): the match kernel histograms the top 11 bits of d2 into fhist0
+  unsigned* fhist0;            // 2048 bins, zero between iterations
+  unsigned* fhist1;            // 2048 bins
+  unsigned* fcnt;              // [0] candidate count, [1] last-block ticket
+  unsigned* cand;              // bit patterns of the distances in the selected 11-bit bucket (capacity n)
   unsigned long long* trace;   // nullable: [0] = entry count, [1 + i] = (kernel tag << 56) | %globaltimer at the start of the i-th kernel of the loop
 };
 struct IcpDevState {    // initialised by the host, advanced by icpTailKernel every iteration, read back once at the end
@@ -113,7 +119,11 @@ struct IcpDevState {    // initialised by the host, advanced by icpTailKernel ev
 };
 #define ICP_STATE_HEAD_BYTES offsetof(IcpDevState, chk)
 
+#define DSTATE_BYTES 131072      /* ctx->dstate; [32768, 49152) is scratch of normals.cu / map.cu */
 #define DSTATE_TRACE_OFF 16384   /* 1 + 2047 x uint64 inside ctx->dstate */
+#define DSTATE_FH0_OFF 65536     /* fused select: pass-0 histogram, 2048 x uint32 */
+#define DSTATE_FH1_OFF 73728     /* fused select: pass-1 histogram, 2048 x uint32 */
+#define DSTATE_FCNT_OFF 81920    /* fused select: candidate count, ticket */
 #define TRACE_MAX 2047
 #ifdef __CUDACC__
 // device-side trace of the graph loop (ncu does not see inside a conditional node): one thread per kernel stamps its start

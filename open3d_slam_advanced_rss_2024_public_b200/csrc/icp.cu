@@ -654,7 +654,10 @@ int buildLoopGraph(b200reg_icp* icp) {
     launchKnn1Loop(ctx, icp->dP, icp->dS, (unsigned long long*)icp->dBlock, knnBlocks);
     ++nodes;
     const uint64_t l0 = ctx->launches;
-    if (useTrim && launchSelect(ctx, nullptr, 0, 0.f, icp->dP) != B200REG_OK) { why = "select launch"; code = cudaErrorUnknown; goto fail; }
+    if (useTrim && !ctx->select3) {
+      selectFusedKernel<<<ctx->sm_count, SELF_THREADS, 0, ctx->stream>>>(icp->dP, st);
+      LAUNCH_CHECK(ctx);
+    } else if (useTrim && launchSelect(ctx, nullptr, 0, 0.f, icp->dP) != B200REG_OK) { why = "select launch"; code = cudaErrorUnknown; goto fail; }
     nodes += (int)(ctx->launches - l0);
     ctx->launches = l0;
     ReduceParams RP;
@@ -814,6 +817,13 @@ int32_t b200reg_icp_register(b200reg_icp* icp, const b200reg_cloud* reading, con
     hP->maxIter = cfg.max_iter; hP->smoothLength = cfg.smooth_length;
     hP->minDiffRot = cfg.min_diff_rot; hP->minDiffTrans = cfg.min_diff_trans;
     hP->boundRot = cfg.bound_rot; hP->boundTrans = cfg.bound_trans;
+    if (cfg.trim_ratio > 0.f && !ctx->select3) {
+      TRY(ensureBuf(ctx, ctx->cand, sizeof(unsigned) * (size_t)n));
+      hP->fhist0 = (unsigned*)((char*)ctx->dstate + DSTATE_FH0_OFF);
+      hP->fhist1 = (unsigned*)((char*)ctx->dstate + DSTATE_FH1_OFF);
+      hP->fcnt = (unsigned*)((char*)ctx->dstate + DSTATE_FCNT_OFF);
+      hP->cand = (unsigned*)ctx->cand.p;
+    }
     hP->lanesForced = (ctx->knnLanes == 4 || ctx->knnLanes == 8) ? ctx->knnLanes : 0;
     hP->trace = ctx->trace ? (unsigned long long*)((char*)ctx->dstate + DSTATE_TRACE_OFF) : nullptr;
     if (ctx->trace) CUDA_TRY(ctx, cudaMemsetAsync((char*)ctx->dstate + DSTATE_TRACE_OFF, 0, sizeof(unsigned long long), ctx->stream));

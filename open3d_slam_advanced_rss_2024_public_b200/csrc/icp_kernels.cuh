@@ -113,6 +113,128 @@ __global__ void __launch_bounds__(256) selectPassKernel(const float* __restrict_
   if (threadIdx.x == 0) st->ticket[PASS] = 0;
 }
 
+// ---- the selection of the device-resident loop: ONE launch after the match --------------------------------------------
+// The match kernel has already histogrammed the top 11 bits of every finite d2 (pass 0) into fhist0.  Here every block
+// re-derives the pass-0 bucket from that histogram (2048 loads, redundant but off the critical path of nothing), runs
+// pass 1 over its share of d2 and, in the same sweep, compacts the distances of the pass-0 bucket into `cand`; the last
+// block to finish picks the pass-1 digit and runs pass 2 over the compacted candidates only.  Same tau bits as the
+// three-launch version (selectPassKernel), which remains for the standalone module and the host-driven loop.
+#define SELF_THREADS 1024
+
+__device__ __forceinline__ unsigned blockExclusiveScan1024(unsigned v, unsigned* warpSums, unsigned& total) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  unsigned incl = v;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const unsigned t = __shfl_up_sync(0xffffffffu, incl, o);
+    if (lane >= o) incl += t;
+  }
+  __syncthreads();   // warpSums may still be read from a previous call
+  if (lane == 31) warpSums[warp] = incl;
+  __syncthreads();
+  if (warp == 0) {
+    const unsigned w = warpSums[lane];
+    unsigned wi = w;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const unsigned t = __shfl_up_sync(0xffffffffu, wi, o);
+      if (lane >= o) wi += t;
+    }
+    warpSums[lane] = wi - w;             // exclusive prefix of the warp sums
+    if (lane == 31) warpSums[32] = wi;   // grand total
+  }
+  __syncthreads();
+  total = warpSums[32];
+  return warpSums[warp] + incl - v;
+}
+
+// picks the bin holding `rank` out of per-thread counts (c0, c1) of bins (2 tid, 2 tid + 1); result through bcast[0..1]
+__device__ __forceinline__ void pickBin2(unsigned c0, unsigned c1, unsigned rank, unsigned* warpSums, unsigned* bcast, unsigned& total) {
+  const unsigned excl = blockExclusiveScan1024(c0 + c1, warpSums, total);
+  if (rank >= excl && rank < excl + c0) { bcast[0] = 2 * threadIdx.x; bcast[1] = rank - excl; }
+  else if (rank >= excl + c0 && rank < excl + c0 + c1) { bcast[0] = 2 * threadIdx.x + 1; bcast[1] = rank - excl - c0; }
+  __syncthreads();
+}
+
+__global__ void __launch_bounds__(SELF_THREADS, 1) selectFusedKernel(const IcpDevParams* __restrict__ DP, SelState* st) {
+  __shared__ unsigned hist[2048];
+  __shared__ unsigned warpSums[40];
+  __shared__ unsigned bcast[2];
+  __shared__ bool last;
+  traceStamp(DP->trace, 2);
+  const float* __restrict__ d2 = DP->d2;
+  const int64_t count = DP->n;
+  const float ratio = DP->trimRatio;
+  unsigned* g0 = DP->fhist0;
+  unsigned* g1 = DP->fhist1;
+  unsigned* cnt = DP->fcnt;
+  unsigned* cand = DP->cand;
+  const int tid = threadIdx.x;
+  // ---- pass 0 bucket, from the histogram the match kernel accumulated
+  unsigned nF;
+  pickBin2(__ldcg(&g0[2 * tid]), __ldcg(&g0[2 * tid + 1]), 0xffffffffu, warpSums, bcast, nF);   // rank unknown yet: only the total
+  if (nF == 0) {   // no finite match at all (uniform over the grid): "No matches available for computing distance quantiles"
+    if (blockIdx.x == 0 && tid == 0) { st->nFinite = 0; st->error = 1; }
+    return;        // fhist0 is all zero already, nothing was compacted
+  }
+  // rank = size_t(float(n) * quantile) — float multiply + truncation (Matches.cpp:85); quantile 1 -> max (:83)
+  unsigned rank = (ratio == 1.0f) ? nF - 1 : (unsigned)__fmul_rn((float)nF, ratio);
+  if (rank > nF - 1) rank = nF - 1;
+  unsigned dummy;
+  pickBin2(__ldcg(&g0[2 * tid]), __ldcg(&g0[2 * tid + 1]), rank, warpSums, bcast, dummy);
+  const unsigned digit0 = bcast[0], rank0 = bcast[1];
+  // ---- pass 1 over this block's share + compaction of the pass-0 bucket
+  hist[2 * tid] = 0;
+  hist[2 * tid + 1] = 0;
+  __syncthreads();
+  for (int64_t base = (int64_t)blockIdx.x * SELF_THREADS; base < count; base += (int64_t)gridDim.x * SELF_THREADS) {
+    const int64_t i = base + tid;
+    const unsigned v = (i < count) ? __float_as_uint(d2[i]) : 0x7f800000u;
+    const bool match = (v != 0x7f800000u) && (v >> 21) == digit0;   // dists != inf (Matches.cpp:70)
+    if (match) atomicAdd(&hist[(v >> 10) & 0x7ffu], 1u);
+    const unsigned m = __ballot_sync(0xffffffffu, match);
+    if (m) {
+      const int lane = tid & 31, leader = __ffs(m) - 1;
+      unsigned slot = 0;
+      if (lane == leader) slot = atomicAdd(&cnt[0], (unsigned)__popc(m));
+      slot = __shfl_sync(0xffffffffu, slot, leader) + __popc(m & ((1u << lane) - 1u));
+      if (match) cand[slot] = v;
+    }
+  }
+  __syncthreads();
+  if (hist[2 * tid]) atomicAdd(&g1[2 * tid], hist[2 * tid]);
+  if (hist[2 * tid + 1]) atomicAdd(&g1[2 * tid + 1], hist[2 * tid + 1]);
+  __threadfence();
+  __syncthreads();
+  if (tid == 0) last = (atomicAdd(&cnt[1], 1u) == gridDim.x - 1);
+  __syncthreads();
+  if (!last) return;
+  __threadfence();
+  // ---- the last block: pass-1 digit, then pass 2 over the candidates
+  pickBin2(__ldcg(&g1[2 * tid]), __ldcg(&g1[2 * tid + 1]), rank0, warpSums, bcast, dummy);
+  const unsigned digit1 = bcast[0], rank1 = bcast[1];
+  hist[2 * tid] = 0;
+  hist[2 * tid + 1] = 0;
+  __syncthreads();
+  const unsigned nc = __ldcg(&cnt[0]);
+  for (unsigned i = tid; i < nc; i += SELF_THREADS) {
+    const unsigned v = __ldcg(&cand[i]);
+    if (((v >> 10) & 0x7ffu) == digit1) atomicAdd(&hist[v & 0x3ffu], 1u);
+  }
+  __syncthreads();
+  pickBin2(hist[2 * tid], hist[2 * tid + 1], rank1, warpSums, bcast, dummy);   // bins >= 1024 are empty
+  const unsigned digit2 = bcast[0];
+  if (tid == 0) {
+    st->nFinite = nF;
+    st->error = 0;
+    st->tauBits = (digit0 << 21) | (digit1 << 10) | digit2;
+    cnt[0] = 0;
+    cnt[1] = 0;
+  }
+  g0[2 * tid] = 0; g0[2 * tid + 1] = 0;   // ready for the next iteration
+  g1[2 * tid] = 0; g1[2 * tid + 1] = 0;
+}
+
 struct ReduceParams {
   const float4* reading;       // pre-iteration reading (already in the refMean frame)
   const float4* readingNrm;    // nullable

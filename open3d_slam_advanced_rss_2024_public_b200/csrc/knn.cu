@@ -239,7 +239,8 @@ __device__ __forceinline__ float ringLowerBound(const AxisGeom& ax, const AxisGe
 template <int G, bool SELFCHK>
 __device__ __forceinline__ void knn1Query(const float4* __restrict__ pts, const uint32_t* __restrict__ cellStart, const GridDesc& g,
                                           const float4* __restrict__ queries, int64_t n, int64_t qi, int hasT, const Rigid12& T, float maxd2,
-                                          int* __restrict__ outIds, float* __restrict__ outD2, int* __restrict__ outPos, unsigned& visits, unsigned& farQ) {
+                                          int* __restrict__ outIds, float* __restrict__ outD2, int* __restrict__ outPos, unsigned& visits, unsigned& farQ,
+                                          unsigned* __restrict__ sHist) {
   constexpr unsigned FULL = 0xffffffffu;
   constexpr int NR = 8 / G;   // non-centre rows owned by each lane
   const int lane = threadIdx.x & 31, l = lane & (G - 1), gbase = lane & (32 - G);
@@ -383,26 +384,47 @@ __device__ __forceinline__ void knn1Query(const float4* __restrict__ pts, const 
     outIds[qi] = found ? (int)(unsigned)best.key : -1;
     outD2[qi] = found ? best.d() : CUDART_INF_F;
     outPos[qi] = found ? best.pos : -1;
+    if (sHist && found && best.d() != CUDART_INF_F) {   // pass 0 of the trimmed-distance radix select, fused (icp_kernels.cuh)
+      const unsigned bin = (unsigned)(best.key >> 53);   // top 11 bits of the d2 pattern
+      atomicAdd(&sHist[bin], 1u);
+      atomicMin(&sHist[2048], bin);
+      atomicMax(&sHist[2049], bin);
+    }
   }
 }
 
 // touched-point statistic (Matcher::visitCounter): warp shuffle -> shared; the last warp out adds the block total (no barrier
 // at the end of the kernel: warps retire as they finish)
 __device__ __forceinline__ void flushVisits(unsigned visits, unsigned farQ, unsigned* sVisits, unsigned* sFarQ, unsigned* sTicket,
-                                            unsigned long long* visitCounter) {
+                                            unsigned long long* visitCounter, const unsigned* sHist = nullptr, unsigned* gHist = nullptr) {
+  __syncwarp();   // the group leaders' shared-memory atomics are ordered before lane 0's ticket
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) {
     visits += __shfl_xor_sync(0xffffffffu, visits, o);
     farQ += __shfl_xor_sync(0xffffffffu, farQ, o);
   }
+  unsigned lastOut = 0;
   if ((threadIdx.x & 31) == 0) {
     atomicAdd(sVisits, visits);
     if (farQ) atomicAdd(sFarQ, farQ);
     __threadfence_block();
-    if (atomicAdd(sTicket, 1u) == (blockDim.x >> 5) - 1u) {
+    lastOut = (atomicAdd(sTicket, 1u) == (blockDim.x >> 5) - 1u) ? 1u : 0u;
+    if (lastOut) {
       const unsigned total = atomicAdd(sVisits, 0u), far = atomicAdd(sFarQ, 0u);
       if (total) atomicAdd(visitCounter, (unsigned long long)total);
-      if (far) atomicAdd(visitCounter + 1, (unsigned long long)far);   // dstate[1]: far-query count
+      if (far) atomicAdd(visitCounter + 1, (unsigned long long)far);   // counters[1]: far-query count
+    }
+  }
+  if (sHist) {   // the last warp out adds the block's touched bins to the global pass-0 histogram
+    lastOut = __shfl_sync(0xffffffffu, lastOut, 0);
+    if (lastOut) {
+      __threadfence_block();
+      const unsigned lo = ((volatile const unsigned*)sHist)[2048], hi = ((volatile const unsigned*)sHist)[2049];
+      if (lo <= hi)
+        for (unsigned b = lo + (threadIdx.x & 31); b <= hi; b += 32) {
+          const unsigned c = ((volatile const unsigned*)sHist)[b];
+          if (c) atomicAdd(&gHist[b], c);
+        }
     }
   }
 }
@@ -418,7 +440,7 @@ __global__ void __launch_bounds__(256) knn1GroupKernel(const float4* __restrict_
   __syncthreads();   // all warps are at the start here: nobody waits on a straggler
   unsigned visits = 0, farQ = 0;
   const int64_t qi = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> LOG2G;
-  knn1Query<G, SELFCHK>(pts, cellStart, g, queries, n, qi, hasT, T, maxd2, outIds, outD2, outPos, visits, farQ);
+  knn1Query<G, SELFCHK>(pts, cellStart, g, queries, n, qi, hasT, T, maxd2, outIds, outD2, outPos, visits, farQ, nullptr);
   flushVisits(visits, farQ, &sVisits, &sFarQ, &sTicket, visitCounter);
 }
 
@@ -427,7 +449,7 @@ __global__ void __launch_bounds__(256) knn1GroupKernel(const float4* __restrict_
 // instantiated CUDA graph serves every reading size and reference.
 template <int G>
 __device__ __forceinline__ void knn1LoopBody(const IcpDevParams* __restrict__ P, const IcpDevState* __restrict__ S, unsigned& visits,
-                                             unsigned& farQ) {
+                                             unsigned& farQ, unsigned* __restrict__ sHist) {
   constexpr int LOG2G = (G == 8) ? 3 : 2;
   const GridDesc g = P->g;
   const float4* pts = P->pts;
@@ -445,7 +467,7 @@ __device__ __forceinline__ void knn1LoopBody(const IcpDevParams* __restrict__ P,
   const int64_t first = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> LOG2G;
   const int64_t blockFirst = ((int64_t)blockIdx.x * blockDim.x) >> LOG2G;
   for (int64_t base = 0; blockFirst + base < n; base += groupsPerGrid)   // trip count uniform over the block
-    knn1Query<G, false>(pts, cellStart, g, queries, n, first + base, 1, T, maxd2, ids, d2, pos, visits, farQ);
+    knn1Query<G, false>(pts, cellStart, g, queries, n, first + base, 1, T, maxd2, ids, d2, pos, visits, farQ, sHist);
 }
 
 // S->lanes (written by the loop's tail from the previous iteration's far-query count) picks the decomposition: 8 lanes per
@@ -453,13 +475,20 @@ __device__ __forceinline__ void knn1LoopBody(const IcpDevParams* __restrict__ P,
 __global__ void __launch_bounds__(256, 6) knn1LoopKernel(const IcpDevParams* __restrict__ P, const IcpDevState* __restrict__ S,
                                                          unsigned long long* __restrict__ visitCounter) {
   __shared__ unsigned sVisits, sFarQ, sTicket;
+  __shared__ unsigned sHistBuf[2050];   // pass-0 histogram of the block's d2 + touched bin range
+  unsigned* gHist = P->fhist0;
+  unsigned* sHist = gHist ? sHistBuf : nullptr;
   if (threadIdx.x == 0) { sVisits = 0; sFarQ = 0; sTicket = 0; }
+  if (sHist) {
+    for (int b = threadIdx.x; b < 2048; b += blockDim.x) sHistBuf[b] = 0;
+    if (threadIdx.x == 0) { sHistBuf[2048] = 0xffffffffu; sHistBuf[2049] = 0; }
+  }
   __syncthreads();
   traceStamp(P->trace, 1);
   unsigned visits = 0, farQ = 0;
-  if (S->lanes == 4) knn1LoopBody<4>(P, S, visits, farQ);
-  else knn1LoopBody<8>(P, S, visits, farQ);
-  flushVisits(visits, farQ, &sVisits, &sFarQ, &sTicket, visitCounter);
+  if (S->lanes == 4) knn1LoopBody<4>(P, S, visits, farQ, sHist);
+  else knn1LoopBody<8>(P, S, visits, farQ, sHist);
+  flushVisits(visits, farQ, &sVisits, &sFarQ, &sTicket, visitCounter, sHist, gHist);
 }
 
 template <int G>
