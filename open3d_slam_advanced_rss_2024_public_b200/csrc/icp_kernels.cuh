@@ -259,6 +259,24 @@ __device__ __forceinline__ double warpSum(double v) {
   return v;
 }
 
+// Warp reduction of N values per lane by recursive halving: at each butterfly step a lane keeps one half of its values and
+// trades the other half with its partner, so 36 moments cost 18 + 9 + 5 + 3 + 2 = 37 shuffles instead of 36 x 5.  After the
+// last step lane L holds the warp totals of the index range [lo, lo + len) (len <= 2); the ranges of the 32 lanes tile [0, N).
+template <int N>
+__device__ __forceinline__ void halveStep(const double (&a)[N], double (&b)[(N + 1) / 2], int off, int& lo, int& len) {
+  constexpr int H = (N + 1) / 2;
+  const bool upper = (threadIdx.x & off) != 0;
+#pragma unroll
+  for (int j = 0; j < H; ++j) {
+    const double lowV = a[j];
+    const double highV = (H + j < N) ? a[H + j] : 0.0;
+    const double recv = __shfl_xor_sync(0xffffffffu, upper ? lowV : highV, off);
+    b[j] = (upper ? highV : lowV) + recv;
+  }
+  if (upper) { lo += H; len -= H; } else len = (len < H) ? len : H;
+  if (len < 0) len = 0;
+}
+
 // one kept pair -> the 36 un-centred moments
 __device__ __forceinline__ void accumulatePair(double* m, const ReduceParams& P, float3 r, const float4 s4, const float4 nn4, double w) {
   double rx = r.x, ry = r.y, rz = r.z, sx = s4.x, sy = s4.y, sz = s4.z, nx = nn4.x, ny = nn4.y, nz = nn4.z;
@@ -352,10 +370,17 @@ __global__ void __launch_bounds__(256, 2) reduceKernel(ReduceParams P, const Sel
   __shared__ double sm[8][NUM_MOM];
   __shared__ bool last;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-#pragma unroll
-  for (int j = 0; j < NUM_MOM; ++j) {
-    const double v = warpSum(m[j]);
-    if (lane == 0) sm[warp][j] = v;
+  {
+    double a18[18], a9[9], a5[5], a3[3], a2[2];
+    int lo = 0, len = NUM_MOM;
+    halveStep<36>(m, a18, 16, lo, len);
+    halveStep<18>(a18, a9, 8, lo, len);
+    halveStep<9>(a9, a5, 4, lo, len);
+    halveStep<5>(a5, a3, 2, lo, len);
+    halveStep<3>(a3, a2, 1, lo, len);
+    if (len > 0) sm[warp][lo] = a2[0];
+    if (len > 1) sm[warp][lo + 1] = a2[1];
+    (void)lane;
   }
   __syncthreads();
   if (threadIdx.x < NUM_MOM) {

@@ -362,7 +362,14 @@ __device__ __forceinline__ void knn1Query(const float4* __restrict__ pts, const 
                 xb = min(xb, xhi);
                 if (xa > xb) continue;
                 const uint32_t s = cellStart[rowBase + xa], e = cellStart[rowBase + xb + 1];
-                for (uint32_t j = s; j < e; ++j) test1<SELFCHK>(pts[j], j, q, selfId, best, visits);
+                for (uint32_t j = s; j < e; j += 4) {   // four independent loads in flight per lane (this loop is latency bound)
+                  const uint32_t j1 = min(j + 1, e - 1), j2 = min(j + 2, e - 1), j3 = min(j + 3, e - 1);
+                  const float4 p0 = ldPoint(pts + j), p1 = ldPoint(pts + j1), p2 = ldPoint(pts + j2), p3 = ldPoint(pts + j3);
+                  test1<SELFCHK>(p0, j, q, selfId, best, visits);
+                  if (j + 1 < e) test1<SELFCHK>(p1, j1, q, selfId, best, visits);
+                  if (j + 2 < e) test1<SELFCHK>(p2, j2, q, selfId, best, visits);
+                  if (j + 3 < e) test1<SELFCHK>(p3, j3, q, selfId, best, visits);
+                }
               }
               bound = fminf(bound, best.d());
             }

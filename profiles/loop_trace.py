@@ -39,3 +39,13 @@ for rep in range(10):
         print(f"registration {tot*1e3:.1f} us event-timed, {st.iterations} iterations, trace span {(tr[-1][1]-t0)/1e3:.1f} us")
 for (i, name), v in acc.items():
     print(f"  {i:3d} {name:9s} start->next start {np.mean(v):7.1f} us")
+print(f"host: reading_preprocessing {st.reading_preprocessing_s*1e6:.1f} us, convergence (graph launch -> result on host) {st.convergence_s*1e6:.1f} us, "
+      f"device loop {st.device_ms*1e3:.1f} us")
+import time
+ts = []
+for _ in range(20):
+    ctx.sync()
+    t0 = time.perf_counter()
+    icp.register(scan, Ti)
+    ts.append(time.perf_counter() - t0)
+print(f"host wall per register (L2 warm): min {min(ts)*1e6:.1f} us median {sorted(ts)[10]*1e6:.1f} us")
