@@ -231,6 +231,12 @@ int32_t b200reg_map_download(b200reg_ctx* ctx, const b200reg_map* map, double* x
 int32_t b200reg_crop_f64(b200reg_ctx* ctx, const b200reg_crop_spec* volume, const double* xyz, const double* nrm, int64_t n,
                          double* xyz_out, double* nrm_out, int64_t* n_out);
 
+/* o3d_slam::voxelize (open3d_slam/src/helpers.cpp:108-115) -> Open3D v0.15.1 PointCloud::VoxelDownSample (external, pinned by
+ * open3d_catkin/CMakeLists.txt:106-107) on a HOST fp64 cloud: per-voxel mean position and mean normal, grid anchored at
+ * min_bound - voxel/2; output in ascending (x,y,z) key order.  xyz_out / nrm_out: room for n points. */
+int32_t b200reg_voxel_down_sample_f64(b200reg_ctx* ctx, double voxel_size, const double* xyz, const double* nrm, int64_t n,
+                                      double* xyz_out, double* nrm_out, int64_t* n_out);
+
 #ifdef __cplusplus
 }
 #endif

@@ -128,6 +128,7 @@ SYMBOLS = {
     "b200reg_map_insert": (C.c_int32, [_VP, _VP, _VP, _VP, C.c_int64, _VP, C.POINTER(CropSpec)]),
     "b200reg_map_crop": (C.c_int32, [_VP, _VP, C.POINTER(CropSpec), C.POINTER(_VP)]),
     "b200reg_map_download": (C.c_int32, [_VP, _VP, _VP, _VP]),
+    "b200reg_voxel_down_sample_f64": (C.c_int32, [_VP, C.c_double, _VP, _VP, C.c_int64, _VP, _VP, C.POINTER(C.c_int64)]),
     "b200reg_crop_f64": (C.c_int32, [_VP, C.POINTER(CropSpec), _VP, _VP, C.c_int64, _VP, _VP, C.POINTER(C.c_int64)]),
 }
 
@@ -303,6 +304,15 @@ class Context:
         st = StepStats()
         self.check(lib().b200reg_point_to_plane(self.h, reading.h, reference.h, _p(ids), _p(d2), _p(w), k, int(force2D), _p(A), _p(b), C.byref(st)))
         return A, b, st
+
+    def voxel_down_sample(self, voxel, xyz, nrm=None):
+        """o3d_slam::voxelize / Open3D VoxelDownSample on a host fp64 cloud (ascending key order)."""
+        xyz, nrm = _f64(xyz), _f64(nrm)
+        xo = np.empty_like(xyz)
+        no = None if nrm is None else np.empty_like(nrm)
+        m = C.c_int64(0)
+        self.check(lib().b200reg_voxel_down_sample_f64(self.h, float(voxel), _p(xyz), _p(nrm), xyz.shape[0], _p(xo), _p(no), C.byref(m)))
+        return xo[:m.value], (None if no is None else no[:m.value])
 
     def crop_f64(self, spec, xyz, nrm=None):
         xyz, nrm = _f64(xyz), _f64(nrm)

@@ -99,7 +99,8 @@ __global__ void headFlagKernel(const u64* __restrict__ skeys, int64_t m, unsigne
 // AccumulatedPoint (helpers.cpp:30-73): one thread per voxel head walks the voxel's points in ascending input index
 __global__ void voxelReduceKernel(const u64* __restrict__ skeys, const unsigned* __restrict__ svals, const unsigned* __restrict__ head,
                                   const unsigned* __restrict__ headOff, int64_t m, const double* __restrict__ xyz,
-                                  const double* __restrict__ nrm, int64_t outBase, double* __restrict__ oxyz, double* __restrict__ onrm) {
+                                  const double* __restrict__ nrm, int64_t outBase, double* __restrict__ oxyz, double* __restrict__ onrm,
+                                  int normalize) {
   const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (j >= m || !head[j]) return;
   const u64 key = skeys[j];
@@ -119,7 +120,7 @@ __global__ void voxelReduceKernel(const u64* __restrict__ skeys, const unsigned*
   oxyz[3 * o] = p[0] / c; oxyz[3 * o + 1] = p[1] / c; oxyz[3 * o + 2] = p[2] / c;
   if (nrm && onrm) {
     const double m0 = a[0] / c, m1 = a[1] / c, m2 = a[2] / c;
-    const double nn = sqrt(m0 * m0 + m1 * m1 + m2 * m2);   // .normalized() (helpers.cpp:181)
+    const double nn = normalize ? sqrt(m0 * m0 + m1 * m1 + m2 * m2) : 0.0;   // .normalized() (helpers.cpp:181); Open3D's VoxelDownSample keeps the plain mean
     onrm[3 * o] = (nn > 0.0) ? m0 / nn : m0;
     onrm[3 * o + 1] = (nn > 0.0) ? m1 / nn : m1;
     onrm[3 * o + 2] = (nn > 0.0) ? m2 / nn : m2;
@@ -145,6 +146,41 @@ __global__ void scatterSelectedF32Kernel(const unsigned* __restrict__ flag, cons
   const size_t o = off[i];
   oxyz[o] = make_float4((float)xyz[3 * (size_t)i], (float)xyz[3 * (size_t)i + 1], (float)xyz[3 * (size_t)i + 2], 1.f);
   if (nrm && onrm) onrm[o] = make_float4((float)nrm[3 * (size_t)i], (float)nrm[3 * (size_t)i + 1], (float)nrm[3 * (size_t)i + 2], 0.f);
+}
+
+// per-block minimum of the coordinates (Open3D GetMinBound)
+__global__ void minBoundKernel(const double* __restrict__ xyz, int64_t n, double* __restrict__ partial) {
+  double m0 = CUDART_INF, m1 = CUDART_INF, m2 = CUDART_INF;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    m0 = fmin(m0, xyz[3 * i]); m1 = fmin(m1, xyz[3 * i + 1]); m2 = fmin(m2, xyz[3 * i + 2]);
+  }
+  for (int o = 16; o > 0; o >>= 1) {
+    m0 = fmin(m0, __shfl_xor_sync(0xffffffffu, m0, o));
+    m1 = fmin(m1, __shfl_xor_sync(0xffffffffu, m1, o));
+    m2 = fmin(m2, __shfl_xor_sync(0xffffffffu, m2, o));
+  }
+  __shared__ double sm[8][3];
+  if ((threadIdx.x & 31) == 0) { sm[threadIdx.x >> 5][0] = m0; sm[threadIdx.x >> 5][1] = m1; sm[threadIdx.x >> 5][2] = m2; }
+  __syncthreads();
+  if (threadIdx.x < 3) {
+    double v = sm[0][threadIdx.x];
+    for (int w = 1; w < (int)(blockDim.x >> 5); ++w) v = fmin(v, sm[w][threadIdx.x]);
+    partial[3 * blockIdx.x + threadIdx.x] = v;
+  }
+}
+
+// Open3D VoxelDownSample key: floor((p - voxel_min_bound) / voxel), voxel_min_bound = min_bound - voxel / 2
+__global__ void o3dKeyKernel(const double* __restrict__ xyz, int64_t n, double mx, double my, double mz, double voxel, u64* __restrict__ keys,
+                             unsigned* __restrict__ vals, int* __restrict__ err) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const double fx = floor((xyz[3 * i] - mx) / voxel), fy = floor((xyz[3 * i + 1] - my) / voxel), fz = floor((xyz[3 * i + 2] - mz) / voxel);
+  const double lim = 2097151.0;   // 21 bits per axis, keys are non-negative by construction
+  u64 key = ~0ull >> 1;
+  if (!(fx >= 0.0 && fx <= lim) || !(fy >= 0.0 && fy <= lim) || !(fz >= 0.0 && fz <= lim)) *err = 1;
+  else key = ((u64)fx << 42) | ((u64)fy << 21) | (u64)fz;
+  keys[i] = key;
+  vals[i] = (unsigned)i;
 }
 
 int scanFlags(b200reg_ctx* ctx, const unsigned* flags, unsigned* offs, int64_t n) {
@@ -237,7 +273,7 @@ int revoxelize(b200reg_ctx* ctx, double voxel, const b200reg_crop_spec& spec, co
     headFlagKernel<<<divUp(nIn, 256), 256, 0, ctx->stream>>>(dk.Current(), nIn, head);
     LAUNCH_CHECK(ctx);
     TRY(scanFlags(ctx, head, headOff, nIn));
-    voxelReduceKernel<<<divUp(nIn, 256), 256, 0, ctx->stream>>>(dk.Current(), dv.Current(), head, headOff, nIn, xyz, nrm, nOut, oxyz, onrm);
+    voxelReduceKernel<<<divUp(nIn, 256), 256, 0, ctx->stream>>>(dk.Current(), dv.Current(), head, headOff, nIn, xyz, nrm, nOut, oxyz, onrm, 1);
     LAUNCH_CHECK(ctx);
     TRY(scanTotal(ctx, head, headOff, nIn, &nVox));
   }
@@ -372,6 +408,71 @@ int32_t b200reg_crop_f64(b200reg_ctx* ctx, const b200reg_crop_spec* volume, cons
   if (m > 0 && nrm && nrm_out) CUDA_TRY(ctx, cudaMemcpyAsync(nrm_out, dOutN, sizeof(double) * 3 * (size_t)m, cudaMemcpyDeviceToHost, ctx->stream));
   CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
   *n_out = m;
+  return B200REG_OK;
+}
+
+// o3d_slam::voxelize (helpers.cpp:108-115) -> Open3D v0.15.1 PointCloud::VoxelDownSample on a HOST fp64 cloud: mean position
+// and mean normal (not re-normalised) per voxel of the grid anchored at min_bound - voxel/2; output in ascending (x,y,z) key
+// order (Open3D's is hash order — unpinned).  xyz_out / nrm_out hold n points; *n_out = voxels.
+int32_t b200reg_voxel_down_sample_f64(b200reg_ctx* ctx, double voxel, const double* xyz, const double* nrm, int64_t n, double* xyz_out,
+                                      double* nrm_out, int64_t* n_out) {
+  if (!ctx || n < 0 || (n > 0 && (!xyz || !xyz_out)) || !n_out) return setErr(ctx, B200REG_E_INVALID_PARAM, "voxel_down_sample: bad arguments");
+  if (!(voxel > 0.0)) return setErr(ctx, B200REG_E_INVALID_PARAM, "voxel_down_sample: voxel_size <= 0");   // Open3D throws too
+  *n_out = 0;
+  if (n == 0) return B200REG_OK;
+  if (n >= (int64_t)0x7fffffff) return setErr(ctx, B200REG_E_INVALID_PARAM, "voxel_down_sample: too many points");
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  const size_t fb = sizeof(double) * 3 * (size_t)n, u4 = sizeof(unsigned) * (size_t)n, k8 = sizeof(u64) * (size_t)n;
+  TRY(ensureBuf(ctx, ctx->misc, 4 * fb + 64));
+  double* dIn = (double*)ctx->misc.p;
+  double* dInN = dIn + 3 * (size_t)n;
+  double* dOut = dInN + 3 * (size_t)n;
+  double* dOutN = dOut + 3 * (size_t)n;
+  TRY(ensureBuf(ctx, ctx->flags, 2 * u4 + 64));
+  unsigned* head = (unsigned*)ctx->flags.p;
+  unsigned* headOff = head + n;
+  TRY(ensureBuf(ctx, ctx->keys0, k8));
+  TRY(ensureBuf(ctx, ctx->keys1, k8));
+  TRY(ensureBuf(ctx, ctx->vals0, u4));
+  TRY(ensureBuf(ctx, ctx->vals1, u4));
+  CUDA_TRY(ctx, cudaMemcpyAsync(dIn, xyz, fb, cudaMemcpyHostToDevice, ctx->stream));
+  if (nrm) CUDA_TRY(ctx, cudaMemcpyAsync(dInN, nrm, fb, cudaMemcpyHostToDevice, ctx->stream));
+  const int mb = (int)fmin((double)(2 * ctx->sm_count), (double)divUp(n, 256));
+  TRY(ensureBuf(ctx, ctx->partials, sizeof(double) * 3 * (size_t)mb));
+  minBoundKernel<<<mb, 256, 0, ctx->stream>>>(dIn, n, (double*)ctx->partials.p);
+  LAUNCH_CHECK(ctx);
+  TRY(ensurePinned(ctx, sizeof(double) * 3 * (size_t)mb + 64));
+  CUDA_TRY(ctx, cudaMemcpyAsync(ctx->pinned, ctx->partials.p, sizeof(double) * 3 * (size_t)mb, cudaMemcpyDeviceToHost, ctx->stream));
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  double mn[3] = {INFINITY, INFINITY, INFINITY};
+  for (int b = 0; b < mb; ++b) for (int d = 0; d < 3; ++d) mn[d] = fmin(mn[d], ((const double*)ctx->pinned)[3 * b + d]);
+  for (int d = 0; d < 3; ++d) mn[d] = mn[d] - voxel * 0.5;
+  int* dErr = (int*)((char*)ctx->dstate + 32768 + 64);
+  CUDA_TRY(ctx, cudaMemsetAsync(dErr, 0, sizeof(int), ctx->stream));
+  o3dKeyKernel<<<divUp(n, 256), 256, 0, ctx->stream>>>(dIn, n, mn[0], mn[1], mn[2], voxel, (u64*)ctx->keys0.p, (unsigned*)ctx->vals0.p, dErr);
+  LAUNCH_CHECK(ctx);
+  cub::DoubleBuffer<u64> dk((u64*)ctx->keys0.p, (u64*)ctx->keys1.p);
+  cub::DoubleBuffer<unsigned> dv((unsigned*)ctx->vals0.p, (unsigned*)ctx->vals1.p);
+  size_t tmp = 0;
+  CUDA_TRY(ctx, cub::DeviceRadixSort::SortPairs(nullptr, tmp, dk, dv, (int)n, 0, 63, ctx->stream));
+  TRY(ensureBuf(ctx, ctx->cubtmp, tmp));
+  tmp = ctx->cubtmp.cap;
+  CUDA_TRY(ctx, cub::DeviceRadixSort::SortPairs(ctx->cubtmp.p, tmp, dk, dv, (int)n, 0, 63, ctx->stream));
+  ctx->launches += 9;
+  headFlagKernel<<<divUp(n, 256), 256, 0, ctx->stream>>>(dk.Current(), n, head);
+  LAUNCH_CHECK(ctx);
+  TRY(scanFlags(ctx, head, headOff, n));
+  voxelReduceKernel<<<divUp(n, 256), 256, 0, ctx->stream>>>(dk.Current(), dv.Current(), head, headOff, n, dIn, nrm ? dInN : nullptr, 0, dOut,
+                                                             nrm ? dOutN : nullptr, 0);
+  LAUNCH_CHECK(ctx);
+  int64_t nVox = 0;
+  TRY(scanTotal(ctx, head, headOff, n, &nVox));
+  CUDA_TRY(ctx, cudaMemcpyAsync(ctx->pinned, dErr, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+  CUDA_TRY(ctx, cudaMemcpyAsync(xyz_out, dOut, sizeof(double) * 3 * (size_t)nVox, cudaMemcpyDeviceToHost, ctx->stream));
+  if (nrm && nrm_out) CUDA_TRY(ctx, cudaMemcpyAsync(nrm_out, dOutN, sizeof(double) * 3 * (size_t)nVox, cudaMemcpyDeviceToHost, ctx->stream));
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  if (*(const int*)ctx->pinned) return setErr(ctx, B200REG_E_INVALID_PARAM, "voxel_down_sample: voxel size too small for the cloud extent (index beyond 2^21)");
+  *n_out = nVox;
   return B200REG_OK;
 }
 

@@ -1,0 +1,222 @@
+// host/mapper.cpp — see mapper.h.  Poses are fp64 4x4 row-major on this side and are cast to fp32 for ICP and back
+// (Mapper.cpp:323,435).
+#include "mapper.h"
+
+#include <cmath>
+#include <cstring>
+
+namespace b200 {
+namespace {
+
+void identity(double* T) {
+  for (int i = 0; i < 16; ++i) T[i] = (i % 5 == 0) ? 1.0 : 0.0;
+}
+void mul(const double* a, const double* b, double* r) {
+  double t[16];
+  for (int i = 0; i < 4; ++i)
+    for (int j = 0; j < 4; ++j) {
+      double acc = 0.0;
+      for (int k = 0; k < 4; ++k) acc += a[4 * i + k] * b[4 * k + j];
+      t[4 * i + j] = acc;
+    }
+  std::memcpy(r, t, sizeof(t));
+}
+// Eigen::Transform<double,3,Affine>::inverse(): linear part by the closed-form 3x3 inverse, translation = -inv(L) t
+void inverseAffine(const double* T, double* r) {
+  const double a = T[0], b = T[1], c = T[2], d = T[4], e = T[5], f = T[6], g = T[8], h = T[9], k = T[10];
+  const double c00 = e * k - f * h, c01 = c * h - b * k, c02 = b * f - c * e;
+  const double c10 = f * g - d * k, c11 = a * k - c * g, c12 = c * d - a * f;
+  const double c20 = d * h - e * g, c21 = b * g - a * h, c22 = a * e - b * d;
+  const double det = a * c00 + b * c10 + c * c20, inv = 1.0 / det;
+  const double L[9] = {c00 * inv, c01 * inv, c02 * inv, c10 * inv, c11 * inv, c12 * inv, c20 * inv, c21 * inv, c22 * inv};
+  identity(r);
+  for (int i = 0; i < 3; ++i) {
+    for (int j = 0; j < 3; ++j) r[4 * i + j] = L[3 * i + j];
+    r[4 * i + 3] = -(L[3 * i] * T[3] + L[3 * i + 1] * T[7] + L[3 * i + 2] * T[11]);
+  }
+}
+
+b200reg_crop_spec at(const b200reg_crop_spec& s, const double* T) {   // CroppingVolume::setPose: only the translation matters
+  b200reg_crop_spec o = s;
+  o.center[0] = T ? T[3] : 0.0;
+  o.center[1] = T ? T[7] : 0.0;
+  o.center[2] = T ? T[11] : 0.0;
+  return o;
+}
+
+}  // namespace
+
+Mapper::Mapper(b200reg_ctx* ctx, const MapperParams& params) : ctx_(ctx), params_(params) {
+  identity(mapToRangeSensor_);
+  identity(mapToRangeSensorPrev_);
+  identity(lastInsertion_);
+  identity(odomPrev_);
+  if (b200reg_map_create(ctx_, params_.mapVoxelSize, &map_) != B200REG_OK) error_ = b200reg_last_error(ctx_);
+  if (b200reg_icp_create(ctx_, &params_.icp, &icp_) != B200REG_OK) error_ = b200reg_last_error(ctx_);
+}
+
+Mapper::~Mapper() {
+  if (reading_) b200reg_cloud_free(ctx_, reading_);
+  if (icp_) b200reg_icp_destroy(icp_);
+  if (map_) b200reg_map_destroy(ctx_, map_);
+}
+
+void Mapper::setMapToRangeSensor(const double T[16]) {
+  std::memcpy(mapToRangeSensor_, T, sizeof(mapToRangeSensor_));
+  std::memcpy(mapToRangeSensorPrev_, T, sizeof(mapToRangeSensorPrev_));
+}
+
+// ScanToMapIcp::processForScanMatchingAndMerging (ScanToMapRegistration.cpp:36-69)
+bool Mapper::process(const double* xyz, const double* normals, int64_t n, Processed* out) {
+  // wide crop: mapBuilderCropper_->crop(in) — that cropper instance never gets a pose, i.e. it sits at the identity (:30-37)
+  std::vector<double> cx(3 * (size_t)n + 3), cn(normals ? 3 * (size_t)n + 3 : 0);
+  int64_t m = 0;
+  const b200reg_crop_spec wide = at(params_.mapBuilderCropper, nullptr);
+  if (b200reg_crop_f64(ctx_, &wide, xyz, normals, n, cx.data(), normals ? cn.data() : nullptr, &m) != B200REG_OK) { error_ = b200reg_last_error(ctx_); return false; }
+  // o3d_slam::voxelize (helpers.cpp:108-115): no-op for voxel <= 0
+  out->mergeXyz.assign(3 * (size_t)m + 3, 0.0);
+  out->mergeNrm.assign(normals ? 3 * (size_t)m + 3 : 0, 0.0);
+  int64_t v = m;
+  if (params_.scanVoxelSize > 0.0 && m > 0) {
+    if (b200reg_voxel_down_sample_f64(ctx_, params_.scanVoxelSize, cx.data(), normals ? cn.data() : nullptr, m, out->mergeXyz.data(),
+                                      normals ? out->mergeNrm.data() : nullptr, &v) != B200REG_OK) { error_ = b200reg_last_error(ctx_); return false; }
+  } else {
+    std::memcpy(out->mergeXyz.data(), cx.data(), sizeof(double) * 3 * (size_t)m);
+    if (normals) std::memcpy(out->mergeNrm.data(), cn.data(), sizeof(double) * 3 * (size_t)m);
+  }
+  out->mergeXyz.resize(3 * (size_t)v);
+  if (v == 0) { error_ = "ScanToMapIcp::wideCropped cropped size is zero"; return false; }   // assert_gt (:66)
+  // estimateNormalsOrCovariancesIfNeeded (CloudRegistration.cpp:62-75): only when the cloud has no normals;
+  // EstimateNormals(Hybrid(radius, knn)) + NormalizeNormals + OrientNormalsTowardsCameraLocation(origin)
+  if (!normals) {
+    b200reg_cloud* c = nullptr;
+    if (b200reg_cloud_upload_f64(ctx_, out->mergeXyz.data(), nullptr, v, &c) != B200REG_OK) { error_ = b200reg_last_error(ctx_); return false; }
+    const float origin[3] = {0.f, 0.f, 0.f};
+    int32_t degenerate = 0;
+    int code = b200reg_surface_normals(ctx_, c, params_.normalsKnn, (float)params_.normalsRadius, 0.f, origin, nullptr, nullptr, nullptr, &degenerate);
+    std::vector<float> feat(4 * (size_t)v), nf(3 * (size_t)v);
+    if (code == B200REG_OK) code = b200reg_cloud_download_f32(ctx_, c, feat.data(), 4, nf.data());
+    b200reg_cloud_free(ctx_, c);
+    if (code != B200REG_OK) { error_ = b200reg_last_error(ctx_); return false; }
+    out->mergeNrm.assign(3 * (size_t)v, 0.0);
+    for (size_t i = 0; i < 3 * (size_t)v; ++i) out->mergeNrm[i] = (double)nf[i];
+  } else {
+    out->mergeNrm.resize(3 * (size_t)v);
+  }
+  // narrow crop at the identity pose (:62-63)
+  out->matchXyz.assign(3 * (size_t)v + 3, 0.0);
+  out->matchNrm.assign(3 * (size_t)v + 3, 0.0);
+  int64_t k = 0;
+  const b200reg_crop_spec narrow = at(params_.scanMatcherCropper, nullptr);
+  if (b200reg_crop_f64(ctx_, &narrow, out->mergeXyz.data(), out->mergeNrm.data(), v, out->matchXyz.data(), out->matchNrm.data(), &k) != B200REG_OK) {
+    error_ = b200reg_last_error(ctx_);
+    return false;
+  }
+  out->matchXyz.resize(3 * (size_t)k);
+  out->matchNrm.resize(3 * (size_t)k);
+  if (k == 0) { error_ = "ScanToMapIcp::narrow cropped size is zero"; return false; }   // assert_gt (:65)
+  return true;
+}
+
+// Submap::insertScan (Submap.cpp:39-96) without carving: transform, append, re-voxelise inside the map-builder volume at the pose
+bool Mapper::insert(const Processed& p) {
+  const b200reg_crop_spec vol = at(params_.mapBuilderCropper, mapToRangeSensor_);
+  if (b200reg_map_insert(ctx_, map_, p.mergeXyz.data(), p.mergeNrm.data(), (int64_t)(p.mergeXyz.size() / 3), mapToRangeSensor_, &vol) != B200REG_OK) {
+    error_ = b200reg_last_error(ctx_);
+    return false;
+  }
+  return true;
+}
+
+bool Mapper::addRangeMeasurement(const double* xyz, const double* normals, int64_t n, double time, const double odom[16]) {
+  stats_ = MapperStepStats();
+  error_.clear();
+  Processed processed;
+  // ---- first scan (Mapper.cpp:179-193)
+  if (b200reg_map_size(map_) == 0) {
+    std::memcpy(mapToRangeSensorPrev_, mapToRangeSensor_, sizeof(mapToRangeSensor_));
+    if (!process(xyz, normals, n, &processed)) return false;
+    if (!insert(processed)) return false;
+    std::memcpy(odomPrev_, odom, sizeof(odomPrev_));   // (the reference reads its odometry buffer at the previous scan's stamp)
+    haveOdomPrev_ = true;
+    stats_.inserted = 1;
+    stats_.mergePoints = (int64_t)(processed.mergeXyz.size() / 3);
+    stats_.mapPoints = b200reg_map_size(map_);
+    return true;
+  }
+  // ---- scan-to-map initial guess: previous refined pose * odometry motion (:265-281)
+  double estimate[16];
+  std::memcpy(estimate, mapToRangeSensorPrev_, sizeof(estimate));
+  if (haveOdomPrev_) {
+    double inv[16], motion[16];
+    inverseAffine(odomPrev_, inv);
+    mul(inv, odom, motion);
+    mul(mapToRangeSensorPrev_, motion, estimate);
+  }
+  // ---- scan processing and the fp64 -> fp32 conversion (:307-309)
+  if (!process(xyz, normals, n, &processed)) return false;
+  const int64_t nRead = (int64_t)(processed.matchXyz.size() / 3);
+  stats_.readingPoints = nRead;
+  stats_.mergePoints = (int64_t)(processed.mergeXyz.size() / 3);
+  if (reading_) { b200reg_cloud_free(ctx_, reading_); reading_ = nullptr; }
+  if (b200reg_cloud_upload_f64(ctx_, processed.matchXyz.data(), processed.matchNrm.data(), nRead, &reading_) != B200REG_OK) {
+    error_ = b200reg_last_error(ctx_);
+    return false;
+  }
+  float guess[16];
+  for (int i = 0; i < 16; ++i) guess[i] = (float)estimate[i];
+  // ---- map patch around the PREVIOUS pose (:328)
+  const b200reg_crop_spec patchVol = at(params_.scanMatcherCropper, mapToRangeSensor_);
+  b200reg_cloud* patch = nullptr;
+  if (b200reg_map_crop(ctx_, map_, &patchVol, &patch) != B200REG_OK) { error_ = b200reg_last_error(ctx_); return false; }
+  stats_.patchPoints = b200reg_cloud_size(patch);
+  if (stats_.patchPoints == 0) {   // mapPatch->IsEmpty() -> return false (:330-333)
+    b200reg_cloud_free(ctx_, patch);
+    error_ = "map patch size is zero";
+    return false;
+  }
+  // ---- reference refresh every referenceCloudSettingPeriod seconds of sensor time (:345-367)
+  float corrected[16];
+  std::memcpy(corrected, guess, sizeof(corrected));
+  bool failed = false;
+  if (!referenceSet_ || (time - lastReferenceInit_) >= params_.referenceCloudSettingPeriod) {
+    lastReferenceInit_ = time;
+    const int code = b200reg_icp_set_reference(icp_, patch);
+    if (code != B200REG_OK) {   // initReference throws inside the try block -> the estimate is kept (:420-422)
+      error_ = b200reg_last_error(ctx_);
+      stats_.icpStatus = code;
+      failed = true;
+    } else {
+      referenceSet_ = true;
+      stats_.referenceRefreshed = 1;
+    }
+  }
+  b200reg_cloud_free(ctx_, patch);
+  // ---- icp_.compute(reading, {}, guess, false) (:388-393); any runtime_error leaves the initial guess (:420-422)
+  if (!failed) {
+    b200reg_icp_stats st;
+    float T[16];
+    const int code = b200reg_icp_register(icp_, reading_, guess, T, &st);
+    stats_.icpStatus = code;
+    stats_.iterations = st.iterations;
+    if (code == B200REG_OK) std::memcpy(corrected, T, sizeof(corrected));
+    else error_ = b200reg_last_error(ctx_);
+  }
+  for (int i = 0; i < 16; ++i) mapToRangeSensor_[i] = (double)corrected[i];   // cast back to fp64 (:435)
+  // ---- insertion gate (:483-489)
+  double inv[16], motion[16];
+  inverseAffine(lastInsertion_, inv);
+  mul(inv, mapToRangeSensor_, motion);
+  const double moved = std::sqrt(motion[3] * motion[3] + motion[7] * motion[7] + motion[11] * motion[11]);
+  if (!(moved < params_.minMovementBetweenMappingSteps)) {
+    if (!insert(processed)) return false;
+    std::memcpy(lastInsertion_, mapToRangeSensor_, sizeof(lastInsertion_));
+    stats_.inserted = 1;
+  }
+  std::memcpy(mapToRangeSensorPrev_, mapToRangeSensor_, sizeof(mapToRangeSensor_));
+  std::memcpy(odomPrev_, odom, sizeof(odomPrev_));
+  stats_.mapPoints = b200reg_map_size(map_);
+  return true;
+}
+
+}  // namespace b200

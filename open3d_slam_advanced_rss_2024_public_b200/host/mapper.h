@@ -1,0 +1,87 @@
+// host/mapper.h — the scan-to-map step of open3d_slam's Mapper, as a thin host driver over the C ABI.
+//
+// Mirrors the control flow of o3d_slam::Mapper::addRangeMeasurement
+// (open3d_slam_rsl/open3d_slam/open3d_slam/src/Mapper.cpp:168-504) for one active submap:
+//   first scan        -> preprocess + insert                                             Mapper.cpp:179-193
+//   estimate          =  mapToRangeSensorPrev * (odomPrev^-1 * odomNow)                  :265-281
+//   processed         =  ScanToMapIcp::processForScanMatchingAndMerging(rawScan)         ScanToMapRegistration.cpp:36-69
+//                        (map-builder crop at the identity pose -> o3d_slam::voxelize -> normals if needed -> narrow crop)
+//   reading           =  open3dToPointmatcher(processed.match)  fp64 -> fp32             Mapper.cpp:307-309
+//   mapPatch          =  cropSubmap(activeSubmap, mapToRangeSensor_)  (PREVIOUS pose)     :328, ScanToMapRegistration.cpp:90-96
+//   every `referenceCloudSettingPeriod` seconds of SENSOR time: icp.initReference(mapPatch)       :345-367
+//   corrected         =  icp.compute(reading, {}, estimate, false); a runtime_error keeps the estimate  :388-422
+//   insert only if the sensor moved >= minMovementBetweenMappingSteps since the last insertion     :483-489
+//                        Submap::insertScan: transform, append, re-voxelise inside the cropping volume  Submap.cpp:39-96
+// Out of this driver: space carving, submap switching, the odometry time buffer (the caller hands the
+// odometry pose of each scan), RandomDownSample (ratio 1 only — the reference itself requires that for reproducibility,
+// ScanToMapRegistration.cpp:43), the initial-map mode, motion compensation.
+#pragma once
+#include <cstdint>
+#include <string>
+#include <vector>
+
+#include "../../include/b200reg.h"
+
+namespace b200 {
+
+struct MapperParams {
+  // scan processing (ScanToMapRegistration.cpp:36-69; param_*.lua: map_builder.cropper, scan_to_map_registration.scan_processing)
+  b200reg_crop_spec mapBuilderCropper{};    // wide crop of the raw scan, applied at the IDENTITY pose (its pose is never set there)
+  double scanVoxelSize = 0.1;               // o3d_slam::voxelize(scanProcessing_.voxelSize_), <= 0: off (helpers.cpp:109-111)
+  b200reg_crop_spec scanMatcherCropper{};   // narrow crop of the processed scan (identity pose) and of the map (previous pose)
+  int normalsKnn = 20;                      // CloudRegistration.cpp:62-75: EstimateNormals(Hybrid(radius, knn)) when the scan has none
+  double normalsRadius = 1.0;
+  // map (Submap.cpp:39-96; map_builder.*)
+  double mapVoxelSize = 0.15;
+  double minMovementBetweenMappingSteps = 0.0;   // Mapper.cpp:483-485
+  double referenceCloudSettingPeriod = 2.0;      // seconds of sensor time, Mapper.cpp:345-349
+  // ICP chain (param/icp.yaml)
+  b200reg_icp_config icp{};
+};
+
+struct MapperStepStats {
+  int32_t iterations = 0;
+  int32_t icpStatus = 0;          // b200reg status of the registration (non-zero: the estimate was kept, Mapper.cpp:420-422)
+  int32_t referenceRefreshed = 0;
+  int32_t inserted = 0;
+  int64_t readingPoints = 0, mergePoints = 0, patchPoints = 0, mapPoints = 0;
+};
+
+class Mapper {
+ public:
+  Mapper(b200reg_ctx* ctx, const MapperParams& params);
+  ~Mapper();
+  Mapper(const Mapper&) = delete;
+  Mapper& operator=(const Mapper&) = delete;
+
+  // Mapper::setMapToRangeSensor(Initial) (Mapper.cpp:133-166): pose of the sensor in the map before the first scan
+  void setMapToRangeSensor(const double T[16]);
+  // rawScan: n x 3 fp64 points (+ optional normals) in the sensor frame; time: seconds; odomToRangeSensor: row-major 4x4 of
+  // the external odometry at `time`.  Returns false where the reference returns false (empty map patch, failed initReference).
+  bool addRangeMeasurement(const double* xyz, const double* normals, int64_t n, double time, const double odomToRangeSensor[16]);
+
+  const double* mapToRangeSensor() const { return mapToRangeSensor_; }
+  b200reg_map* map() { return map_; }
+  const MapperStepStats& lastStats() const { return stats_; }
+  const std::string& lastError() const { return error_; }
+
+ private:
+  struct Processed {   // ProcessedScans (ScanToMapRegistration.hpp): match_ (narrow) and merge_ (wide), fp64 host clouds
+    std::vector<double> mergeXyz, mergeNrm, matchXyz, matchNrm;
+  };
+  bool process(const double* xyz, const double* normals, int64_t n, Processed* out);
+  bool insert(const Processed& p);
+
+  b200reg_ctx* ctx_;
+  MapperParams params_;
+  b200reg_map* map_ = nullptr;
+  b200reg_icp* icp_ = nullptr;
+  b200reg_cloud* reading_ = nullptr;   // reused device cloud of the reading (streaming upload)
+  double mapToRangeSensor_[16], mapToRangeSensorPrev_[16], lastInsertion_[16], odomPrev_[16];
+  bool haveOdomPrev_ = false, referenceSet_ = false;
+  double lastReferenceInit_ = 0.0;
+  MapperStepStats stats_;
+  std::string error_;
+};
+
+}  // namespace b200

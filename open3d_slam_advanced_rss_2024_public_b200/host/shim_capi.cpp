@@ -184,3 +184,53 @@ int b200pm_apply_filter(const char* name, const char* params_kv /* "k=v\n..." */
 }
 
 }  // extern "C"
+
+// ---- open3d_slam Mapper driver (host/mapper.h) ----------------------------------------------------------------------
+#include "mapper.h"
+
+extern "C" {
+
+typedef struct b200map_params {   // flat mirror of b200::MapperParams for ctypes
+  b200reg_crop_spec map_builder_cropper;
+  b200reg_crop_spec scan_matcher_cropper;
+  double scan_voxel_size, normals_radius, map_voxel_size, min_movement, reference_period;
+  int32_t normals_knn, pad;
+  b200reg_icp_config icp;
+} b200map_params;
+
+typedef struct b200map_stats {
+  int32_t iterations, icp_status, reference_refreshed, inserted;
+  int64_t reading_points, merge_points, patch_points, map_points;
+} b200map_stats;
+
+void* b200map_create(b200reg_ctx* ctx, const b200map_params* p) {
+  if (!ctx || !p) return nullptr;
+  b200::MapperParams mp;
+  mp.mapBuilderCropper = p->map_builder_cropper;
+  mp.scanMatcherCropper = p->scan_matcher_cropper;
+  mp.scanVoxelSize = p->scan_voxel_size;
+  mp.normalsKnn = p->normals_knn;
+  mp.normalsRadius = p->normals_radius;
+  mp.mapVoxelSize = p->map_voxel_size;
+  mp.minMovementBetweenMappingSteps = p->min_movement;
+  mp.referenceCloudSettingPeriod = p->reference_period;
+  mp.icp = p->icp;
+  return new b200::Mapper(ctx, mp);
+}
+void b200map_destroy(void* m) { delete (b200::Mapper*)m; }
+void b200map_set_pose(void* m, const double T[16]) { ((b200::Mapper*)m)->setMapToRangeSensor(T); }
+int32_t b200map_add_range_measurement(void* m, const double* xyz, const double* normals, int64_t n, double time, const double odom[16],
+                                      double pose_out[16], b200map_stats* stats, char* err, int32_t err_cap) {
+  b200::Mapper* mp = (b200::Mapper*)m;
+  const bool ok = mp->addRangeMeasurement(xyz, normals, n, time, odom);
+  std::memcpy(pose_out, mp->mapToRangeSensor(), sizeof(double) * 16);
+  if (stats) {
+    const b200::MapperStepStats& s = mp->lastStats();
+    *stats = b200map_stats{s.iterations, s.icpStatus, s.referenceRefreshed, s.inserted, s.readingPoints, s.mergePoints, s.patchPoints, s.mapPoints};
+  }
+  setMsg(err, err_cap, mp->lastError());
+  return ok ? 1 : 0;
+}
+b200reg_map* b200map_map(void* m) { return ((b200::Mapper*)m)->map(); }
+
+}  // extern "C"

@@ -1,0 +1,86 @@
+"""ctypes window onto the C++ scan-to-map Mapper driver (host/mapper.h — the control flow of o3d_slam::Mapper::addRangeMeasurement,
+open3d_slam/src/Mapper.cpp:168-504, over the C ABI).  Used by the mapping-loop tests and the config #3 harness."""
+import ctypes as C
+
+import numpy as np
+
+from . import capi, pm_shim
+
+
+class MapperParams(C.Structure):
+    _fields_ = [("map_builder_cropper", capi.CropSpec), ("scan_matcher_cropper", capi.CropSpec), ("scan_voxel_size", C.c_double),
+                ("normals_radius", C.c_double), ("map_voxel_size", C.c_double), ("min_movement", C.c_double),
+                ("reference_period", C.c_double), ("normals_knn", C.c_int32), ("pad", C.c_int32), ("icp", capi.IcpConfig)]
+
+
+class MapperStats(C.Structure):
+    _fields_ = [("iterations", C.c_int32), ("icp_status", C.c_int32), ("reference_refreshed", C.c_int32), ("inserted", C.c_int32),
+                ("reading_points", C.c_int64), ("merge_points", C.c_int64), ("patch_points", C.c_int64), ("map_points", C.c_int64)]
+
+
+def _lib():
+    L = pm_shim.lib()
+    if not getattr(L, "_b200map_ready", False):
+        L.b200map_create.restype = C.c_void_p
+        L.b200map_create.argtypes = [C.c_void_p, C.POINTER(MapperParams)]
+        L.b200map_destroy.argtypes = [C.c_void_p]
+        L.b200map_set_pose.argtypes = [C.c_void_p, C.c_void_p]
+        L.b200map_add_range_measurement.restype = C.c_int32
+        L.b200map_add_range_measurement.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_double, C.c_void_p, C.c_void_p,
+                                                    C.POINTER(MapperStats), C.c_char_p, C.c_int32]
+        L.b200map_map.restype = C.c_void_p
+        L.b200map_map.argtypes = [C.c_void_p]
+        L._b200map_ready = True
+    return L
+
+
+class Mapper:
+    """One active submap, no carving: see host/mapper.h for what is mirrored and what is left out."""
+
+    def __init__(self, ctx, map_builder_cropper, scan_matcher_cropper, icp_cfg, scan_voxel_size=0.1, normals_knn=20, normals_radius=1.0,
+                 map_voxel_size=0.15, min_movement=0.0, reference_period=2.0):
+        self.ctx = ctx
+        self.params = MapperParams(map_builder_cropper=map_builder_cropper, scan_matcher_cropper=scan_matcher_cropper,
+                                   scan_voxel_size=scan_voxel_size, normals_radius=normals_radius, map_voxel_size=map_voxel_size,
+                                   min_movement=min_movement, reference_period=reference_period, normals_knn=normals_knn, pad=0, icp=icp_cfg)
+        self.h = _lib().b200map_create(ctx.h, C.byref(self.params))
+        if not self.h:
+            raise RuntimeError("b200map_create failed")
+
+    def set_pose(self, T):
+        T = np.ascontiguousarray(T, dtype=np.float64).reshape(16)
+        _lib().b200map_set_pose(self.h, T.ctypes.data_as(C.c_void_p))
+
+    def add_range_measurement(self, xyz, time, odom, normals=None):
+        xyz = np.ascontiguousarray(xyz, dtype=np.float64)
+        nrm = None if normals is None else np.ascontiguousarray(normals, dtype=np.float64)
+        odom = np.ascontiguousarray(odom, dtype=np.float64).reshape(16)
+        pose = np.zeros(16, dtype=np.float64)
+        st = MapperStats()
+        err = C.create_string_buffer(1024)
+        ok = _lib().b200map_add_range_measurement(self.h, xyz.ctypes.data_as(C.c_void_p), None if nrm is None else nrm.ctypes.data_as(C.c_void_p),
+                                                  xyz.shape[0], float(time), odom.ctypes.data_as(C.c_void_p), pose.ctypes.data_as(C.c_void_p),
+                                                  C.byref(st), err, len(err))
+        return bool(ok), pose.reshape(4, 4), st, err.value.decode("utf-8", "replace")
+
+    def map_points(self):
+        """Download the resident map (fp64 points and normals)."""
+        mh = _lib().b200map_map(self.h)
+        n = int(capi.lib().b200reg_map_size(mh))
+        xyz = np.zeros((n, 3), dtype=np.float64)
+        nrm = np.zeros((n, 3), dtype=np.float64) if capi.lib().b200reg_map_has_normals(mh) else None
+        self.ctx.check(capi.lib().b200reg_map_download(self.ctx.h, mh, xyz.ctypes.data_as(C.c_void_p),
+                                                       None if nrm is None else nrm.ctypes.data_as(C.c_void_p)))
+        return xyz, nrm
+
+    def close(self):
+        if self.h:
+            _lib().b200map_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            if self.ctx.h:
+                self.close()
+        except Exception:
+            pass

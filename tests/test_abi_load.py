@@ -74,3 +74,11 @@ def test_solve_point_to_plane_host_side(oracle):
     T, x = capi.solve_point_to_plane(o["A"], o["b"], xs.astype(np.float64).mean(0), rf.astype(np.float64).mean(0))
     E = np.eye(4); E[2, 3] = 1
     assert np.allclose(T, E, atol=1e-6) and np.allclose(o["T"], E, atol=1e-6)
+
+
+def test_mapper_driver_symbols_are_exported():
+    """libb200pm.so carries the open3d_slam Mapper driver (host/mapper.h) behind b200map_* (no compute without a GPU)."""
+    from open3d_slam_advanced_rss_2024_public_b200 import mapper
+    L = mapper._lib()
+    for name in ("b200map_create", "b200map_destroy", "b200map_set_pose", "b200map_add_range_measurement", "b200map_map"):
+        assert hasattr(L, name)

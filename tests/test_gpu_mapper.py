@@ -1,0 +1,174 @@
+"""Scan-to-map mapping loop (BASELINE config #3 shape at a size the oracle finishes in seconds): the C++ Mapper driver over
+the C ABI (host/mapper.h, mirror of o3d_slam::Mapper::addRangeMeasurement, Mapper.cpp:168-504) against the same control flow
+composed from the CPU oracle's pieces.  Bars: processed-scan / map sizes equal at every step (voxel and crop membership is
+bit-exact), poses within 1e-4 m / 1e-4 rad of the oracle trajectory (normals come from two fp32 implementations whose
+eigen-solvers differ in the last bits), trajectory error vs ground truth bounded."""
+import numpy as np
+import pytest
+
+import scenes
+
+pytestmark = pytest.mark.gpu
+
+
+def trajectory(n, step=0.25):
+    poses = []
+    for i in range(n):
+        s = i * step
+        yaw = 0.35 * np.sin(0.25 * s)
+        T = scenes.rigid(scenes.rot_axis_angle(np.array([0.0, 0.0, 1.0]), yaw), np.array([-6.0 + s, 1.5 * np.sin(0.3 * s), 1.6]))
+        poses.append(T)
+    return poses
+
+
+def drifting_odometry(poses, seed):
+    """external odometry = truth + random-walk drift"""
+    rng = np.random.default_rng(seed)
+    D = np.eye(4)
+    out = []
+    for T in poses:
+        d = scenes.rigid(scenes.rot_axis_angle(rng.normal(size=3), np.deg2rad(0.05) * rng.normal()), rng.normal(size=3) * 0.004)
+        D = D @ d
+        out.append(T @ D)
+    return out
+
+
+class OracleMapper:
+    """The same control flow as host/mapper.cpp, composed from oracle calls (CPU)."""
+
+    def __init__(self, O, wide, narrow, icp_kw, scan_voxel, knn, radius, map_voxel, min_move, period):
+        self.O, self.wide, self.narrow, self.icp_kw = O, wide, narrow, icp_kw
+        self.scan_voxel, self.knn, self.radius, self.map_voxel, self.min_move, self.period = scan_voxel, knn, radius, map_voxel, min_move, period
+        self.pose = np.eye(4)
+        self.prev = np.eye(4)
+        self.last_insert = np.eye(4)
+        self.odom_prev = None
+        self.map_xyz = np.zeros((0, 3))
+        self.map_nrm = np.zeros((0, 3))
+        self.ref = None
+        self.last_ref = 0.0
+
+    def spec(self, s, T=None):
+        O = self.O
+        c = np.zeros(3) if T is None else T[:3, 3]
+        return O.crop_spec(s["kind"], c, s.get("rmin", 0.0), s.get("rmax", 0.0), s.get("zmin", 0.0), s.get("zmax", 0.0))
+
+    def process(self, xyz):
+        O = self.O
+        cx, _, _ = O.crop(self.spec(self.wide), xyz)
+        mx, _ = O.voxel_down_sample(self.scan_voxel, cx)
+        nrm = O.surface_normals(O.feat4(mx.astype(np.float32)), self.knn, max_dist=self.radius, nthreads=8,
+                                orient_origin=np.zeros(3, np.float32))["normals"].astype(np.float64)
+        nx, nn, _ = O.crop(self.spec(self.narrow), mx, nrm)
+        return mx, nrm, nx, nn
+
+    def insert(self, mx, mn):
+        O = self.O
+        tx, tn = O.transform_f64(self.pose, mx, mn)
+        allx = np.concatenate([self.map_xyz, tx])
+        alln = np.concatenate([self.map_nrm, tn])
+        self.map_xyz, self.map_nrm, _ = O.voxelize_within_volume(self.map_voxel, self.spec(self.wide, self.pose), allx, alln)
+
+    def add(self, xyz, time, odom):
+        O = self.O
+        st = dict(inserted=0, refreshed=0, iterations=0, code=0)
+        if self.map_xyz.shape[0] == 0:
+            self.prev = self.pose.copy()
+            mx, mn, _, _ = self.process(xyz)
+            self.insert(mx, mn)
+            self.odom_prev = odom.copy()
+            st.update(inserted=1, merge=mx.shape[0], map=self.map_xyz.shape[0])
+            return True, st
+        est = self.prev @ (np.linalg.inv(self.odom_prev) @ odom)
+        mx, mn, nx, nn = self.process(xyz)
+        rf, rn = O.o3d_to_pm(nx, nn)
+        px, pn, _ = O.crop(self.spec(self.narrow, self.pose), self.map_xyz, self.map_nrm)
+        if px.shape[0] == 0:
+            return False, st
+        cfg = O.icp_config(precision=O.ORC_MIXED, nthreads=8, **self.icp_kw)
+        if self.ref is None or (time - self.last_ref) >= self.period:
+            self.last_ref = time
+            pf, pnn = O.o3d_to_pm(px, pn)
+            self.ref = O.IcpReference(cfg, pf, pnn)
+            st["refreshed"] = 1
+        guess = est.astype(np.float32)
+        code, T, ist = self.ref.compute(rf, rn, guess)
+        st.update(code=code, iterations=ist.iterations, reading=rf.shape[0], merge=mx.shape[0], patch=px.shape[0])
+        self.pose = (T if code == 0 else guess).astype(np.float64)
+        moved = np.linalg.norm((np.linalg.inv(self.last_insert) @ self.pose)[:3, 3])
+        if not (moved < self.min_move):
+            self.insert(mx, mn)
+            self.last_insert = self.pose.copy()
+            st["inserted"] = 1
+        self.prev = self.pose.copy()
+        self.odom_prev = odom.copy()
+        st["map"] = self.map_xyz.shape[0]
+        return True, st
+
+
+def test_mapping_loop_matches_oracle_composition(ctx, oracle):
+    from open3d_slam_advanced_rss_2024_public_b200 import capi
+    from open3d_slam_advanced_rss_2024_public_b200.mapper import Mapper
+    O = oracle
+    scene = scenes.Scene(2001, size=(40.0, 24.0, 8.0), n_boxes=14, n_cyl=8)
+    poses = trajectory(12)
+    odom = drifting_odometry(poses, 2003)
+    wide = dict(kind=capi.CROP_MINMAX_RADIUS, rmin=1.0, rmax=30.0)
+    narrow = dict(kind=capi.CROP_MAX_RADIUS, rmax=25.0)
+    icp_kw = dict(knn=1, max_dist=0.5, trim_ratio=0.9, max_angle=1.57, max_iter=15, min_diff_rot=1e-3, min_diff_trans=1e-2, smooth_length=3)
+    kw = dict(scan_voxel=0.25, knn=10, radius=1.0, map_voxel=0.3, min_move=0.2, period=0.35)
+    om = OracleMapper(O, wide, narrow, icp_kw, **kw)
+    gm = Mapper(ctx, capi.crop_spec(wide["kind"], np.zeros(3), rmin=wide["rmin"], rmax=wide["rmax"]),
+                capi.crop_spec(narrow["kind"], np.zeros(3), rmax=narrow["rmax"]), capi.icp_config(**icp_kw),
+                scan_voxel_size=kw["scan_voxel"], normals_knn=kw["knn"], normals_radius=kw["radius"], map_voxel_size=kw["map_voxel"],
+                min_movement=kw["min_move"], reference_period=kw["period"])
+    om.pose = poses[0].copy()
+    gm.set_pose(poses[0])
+    refreshed = inserted = 0
+    for i, (T, od) in enumerate(zip(poses, odom)):
+        scan = scenes.lidar_scan(scene, T, n_beams=24, n_az=360, noise_sigma=0.01, seed=2002 + i).astype(np.float64)
+        t = 0.1 * i
+        ok_o, so = om.add(scan, t, od)
+        ok_g, pose_g, sg, err = gm.add_range_measurement(scan, t, od)
+        assert ok_o and ok_g, (i, err)
+        assert sg.merge_points == so["merge"] and sg.map_points == so["map"], (i, sg.merge_points, so)
+        assert sg.inserted == so["inserted"]
+        if i > 0:
+            assert sg.reading_points == so["reading"] and sg.patch_points == so["patch"]
+            assert sg.icp_status == so["code"] == 0 and sg.reference_refreshed == so["refreshed"]
+            assert abs(sg.iterations - so["iterations"]) <= 1, (i, sg.iterations, so["iterations"])
+            refreshed += sg.reference_refreshed
+            inserted += sg.inserted
+        assert np.abs(pose_g[:3, 3] - om.pose[:3, 3]).max() < 1e-4, (i, pose_g, om.pose)
+        assert np.linalg.norm(pose_g[:3, :3] - om.pose[:3, :3]) / np.sqrt(2) < 1e-4
+        E = np.linalg.inv(T) @ pose_g
+        assert np.abs(E[:3, 3]).max() < 0.05, (i, E)          # stays on the true trajectory despite the drifting odometry
+    assert 2 <= refreshed < len(poses) - 1 and inserted >= 5   # both the stale-reference and the skip-insertion branches ran
+    mx, mn = gm.map_points()
+    assert mx.shape[0] == om.map_xyz.shape[0]
+    # pass-through points keep their order, voxel means follow in ascending key order in both implementations
+    assert np.abs(mx - om.map_xyz).max() < 2e-4
+    gm.close()
+
+
+def test_voxel_down_sample_o3d_convention(ctx, oracle):
+    """o3d_slam::voxelize -> Open3D VoxelDownSample (a17): membership and emission order bit-exact, means bit-exact."""
+    rng = np.random.default_rng(5)
+    xyz = rng.uniform(-20, 20, (60_000, 3))
+    nrm = rng.normal(size=(60_000, 3))
+    nrm[::97] = np.nan
+    for v in (0.1, 0.35, 2.0):
+        gx, gn = ctx.voxel_down_sample(v, xyz, nrm)
+        ox, on = oracle.voxel_down_sample(v, xyz, nrm)
+        assert gx.shape == ox.shape
+        assert np.array_equal(gx, ox) and np.array_equal(np.nan_to_num(gn), np.nan_to_num(on))
+    gx, gn = ctx.voxel_down_sample(0.5, xyz)          # no normals
+    ox, _ = oracle.voxel_down_sample(0.5, xyz)
+    assert gn is None and np.array_equal(gx, ox)
+    gx2, _ = ctx.voxel_down_sample(0.5, gx)           # idempotent on membership count (means move inside their voxels)
+    assert gx2.shape[0] <= gx.shape[0]
+    from open3d_slam_advanced_rss_2024_public_b200 import capi
+    with pytest.raises(capi.InvalidParameter):
+        ctx.voxel_down_sample(0.0, xyz)
+    e, _ = ctx.voxel_down_sample(0.5, np.zeros((0, 3)))
+    assert e.shape[0] == 0
