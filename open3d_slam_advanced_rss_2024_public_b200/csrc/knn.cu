@@ -331,12 +331,15 @@ __device__ __forceinline__ void knn1Query(const float4* __restrict__ pts, const 
     float bound = best.d();   // group-wide pruning bound (starts at maxDist^2); lane-local bests are merged after each ring
     while (__any_sync(FULL, need)) {
       if (need) {
-        const int w = 2 * r + 1, nrows = w * w;
+        // the shell's (y,z) rows, clipped to the grid (a query far outside it starts at a huge ring: never enumerate (2r+1)^2)
+        const int y0 = max(ay.c - r, 0), z0 = max(az.c - r, 0);
+        const int wy = max(min(ay.c + r, g.ny - 1) - y0 + 1, 0), wz = max(min(az.c + r, g.nz - 1) - z0 + 1, 0);
+        const int nrows = wy * wz;
         for (int t0 = 0; t0 < nrows; t0 += G) {   // one round = G rows, one per lane; the group stays converged
           const int t = t0 + l;
-          const int dy = t % w - r, dz = t / w - r;
-          const int iy = ay.c + dy, iz = az.c + dz;
-          if (t < nrows && (unsigned)iy < (unsigned)g.ny && (unsigned)iz < (unsigned)g.nz) {
+          const int iy = y0 + t % max(wy, 1), iz = z0 + t / max(wy, 1);
+          const int dy = iy - ay.c, dz = iz - az.c;
+          if (t < nrows) {
             const float rowLb = lb3(0.f, axisGap(ay, iy, g.cell, g.slack), axisGap(az, iz, g.cell, g.slack));
             if (!(rowLb > bound)) {
               const bool shellRow = (abs(dz) == r) || (abs(dy) == r);
@@ -498,6 +501,195 @@ __global__ void __launch_bounds__(256, 6) knn1LoopKernel(const IcpDevParams* __r
   flushVisits(visits, farQ, &sVisits, &sFarQ, &sTicket, visitCounter, sHist, gHist);
 }
 
+// ---- 2 <= k <= 32 (SurfaceNormal's self-kNN, k-NN matchers): W lanes per query, W = 8 / 16 / 32 >= k ------------------
+// The running result is a sorted list DISTRIBUTED over the group: lane j holds the j-th best packed (d2, index) key and
+// its sorted position.  A contiguous point range is tested W candidates at a time (one coalesced float4 load per lane);
+// candidates that beat the current k-th key are found with one ballot and inserted one by one with a shuffle-up
+// (O(1) per insertion for the whole group, ~k ln(candidates / k) insertions per query).  Cells are visited like the k = 1
+// kernel: the 3x3x3 neighbourhood as 9 rows whose directory entries are fetched in one round, then whole shells, every
+// row and shell pruned by its exact fp32 lower bound against the k-th distance (maxDist^2 while the list is not full).
+// queries == nullptr: the index's own points are the queries, taken in SORTED order (neighbouring groups share cells;
+// results are written at the original index) — the self-kNN of SurfaceNormal.cpp:170-188.
+template <int W>
+struct KnnList {
+  unsigned long long key, kth;   // this lane's entry; the group's k-th entry
+  int pos;
+  unsigned gmask;
+  int l, kLane;
+  __device__ __forceinline__ float kthD() const { return __uint_as_float((unsigned)(kth >> 32)); }
+  __device__ __forceinline__ void insert(unsigned long long ck, int cp) {
+    const unsigned long long upK = __shfl_up_sync(gmask, key, 1, W);
+    const int upP = __shfl_up_sync(gmask, pos, 1, W);
+    if (key > ck) {
+      const bool take = (l == 0) || (upK < ck);
+      key = take ? ck : upK;
+      pos = take ? cp : upP;
+    }
+    kth = __shfl_sync(gmask, key, kLane, W);
+  }
+};
+
+template <int W, bool SELFCHK>
+__device__ __forceinline__ void scanList(const float4* __restrict__ pts, uint32_t s, uint32_t e, const float3 q, int selfId, KnnList<W>& L,
+                                         unsigned& visits) {
+  if (s >= e) return;
+  const int gbase = (threadIdx.x & 31) & (32 - W);
+  float4 p = ldPoint(pts + min(s + (uint32_t)L.l, e - 1));
+  for (uint32_t j0 = s; j0 < e; j0 += W) {
+    const uint32_t j = j0 + L.l;
+    const float4 pn = ldPoint(pts + min(j + W, e - 1));   // next chunk in flight while this one is inserted
+    const int id = __float_as_int(p.w);
+    const bool ok = (j < e) && !(SELFCHK && id == selfId);
+    const unsigned long long key = packKey(dist2_rn(q.x, q.y, q.z, p.x, p.y, p.z), id);
+    visits += ok ? 1u : 0u;
+    unsigned m = __ballot_sync(L.gmask, ok && key < L.kth);
+    if (W < 32) m = (m >> gbase) & ((1u << (W & 31)) - 1u);
+    while (m) {
+      const int b = __ffs(m) - 1;
+      m &= m - 1u;
+      const unsigned long long ck = __shfl_sync(L.gmask, key, b, W);
+      const int cp = __shfl_sync(L.gmask, (int)j, b, W);
+      if (ck < L.kth) L.insert(ck, cp);
+    }
+    p = pn;
+  }
+}
+
+template <int W, bool SELFCHK>
+__global__ void __launch_bounds__(256) knnListKernel(const float4* __restrict__ pts, const uint32_t* __restrict__ cellStart, GridDesc g,
+                                                     const float4* __restrict__ queries, int64_t n, int hasT, Rigid12 T, int k, float maxd2,
+                                                     int* __restrict__ outIds, float* __restrict__ outD2, int* __restrict__ outPos,
+                                                     unsigned long long* __restrict__ visitCounter) {
+  constexpr int NT = (9 + W - 1) / W;   // near rows per lane
+  const int lane = threadIdx.x & 31, l = lane & (W - 1), gbase = lane & (32 - W);
+  const unsigned gmask = (W == 32) ? 0xffffffffu : (((1u << (W & 31)) - 1u) << gbase);
+  const int64_t slot = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) / W;
+  unsigned visits = 0;
+  if (slot < n) {
+    float4 q4;
+    int64_t qi = slot;
+    if (queries) q4 = queries[slot];
+    else { q4 = pts[slot]; qi = (int64_t)__float_as_int(q4.w); q4.w = 1.f; }
+    float3 q = make_float3(q4.x, q4.y, q4.z);
+    if (hasT) q = xformPoint(T, q4.x, q4.y, q4.z, q4.w);
+    const bool finite = (fabsf(q.x) <= FLT_MAX) && (fabsf(q.y) <= FLT_MAX) && (fabsf(q.z) <= FLT_MAX);
+    const int selfId = (int)qi;
+    const float lim = 1.0e9f;
+    const AxisGeom ax{q.x, g.ox, finite ? (int)floorf(fminf(fmaxf(__fmul_rn(__fsub_rn(q.x, g.ox), g.inv_cell), -lim), lim)) : 0};
+    const AxisGeom ay{q.y, g.oy, finite ? (int)floorf(fminf(fmaxf(__fmul_rn(__fsub_rn(q.y, g.oy), g.inv_cell), -lim), lim)) : 0};
+    const AxisGeom az{q.z, g.oz, finite ? (int)floorf(fminf(fmaxf(__fmul_rn(__fsub_rn(q.z, g.oz), g.inv_cell), -lim), lim)) : 0};
+    const unsigned long long initKey = packKey(maxd2, 0);   // an entry must beat (maxDist^2, 0): d2 < maxDist^2 strictly
+    KnnList<W> L{initKey, initKey, -1, gmask, l, k - 1};
+
+    // ---- rings 0 and 1: nine (y,z) rows [cx-1, cx+1], directory entries fetched in one round
+    uint32_t sR[NT], eR[NT];
+    float lbR[NT];
+#pragma unroll
+    for (int t = 0; t < NT; ++t) {
+      sR[t] = 0; eR[t] = 0; lbR[t] = CUDART_INF_F;
+      const int ri = l + t * W;
+      const int xa = max(ax.c - 1, 0), xb = min(ax.c + 1, g.nx - 1);
+      const int iy = ay.c + (ri % 3) - 1, iz = az.c + (ri / 3) - 1;
+      if (finite && ri < 9 && xa <= xb && (unsigned)iy < (unsigned)g.ny && (unsigned)iz < (unsigned)g.nz) {
+        const uint32_t base = (uint32_t)g.nx * ((uint32_t)iy + (uint32_t)g.ny * (uint32_t)iz);
+        sR[t] = cellStart[base + xa];
+        eR[t] = cellStart[base + xb + 1];
+        lbR[t] = lb3(0.f, axisGap(ay, iy, g.cell, g.slack), axisGap(az, iz, g.cell, g.slack));
+      }
+    }
+    scanList<W, SELFCHK>(pts, __shfl_sync(gmask, sR[0], 4, W), __shfl_sync(gmask, eR[0], 4, W), q, selfId, L, visits);   // centre row first
+#pragma unroll
+    for (int t = 0; t < NT; ++t) {
+      unsigned m = __ballot_sync(gmask, eR[t] > sR[t] && (l + t * W) != 4 && !(lbR[t] > L.kthD()));
+      if (W < 32) m = (m >> gbase) & ((1u << (W & 31)) - 1u);
+      while (m) {
+        const int b = __ffs(m) - 1;
+        m &= m - 1u;
+        const uint32_t s = __shfl_sync(gmask, sR[t], b, W), e = __shfl_sync(gmask, eR[t], b, W);
+        const float lb = __shfl_sync(gmask, lbR[t], b, W);
+        if (!(lb > L.kthD())) scanList<W, SELFCHK>(pts, s, e, q, selfId, L, visits);
+      }
+    }
+
+    // ---- rings >= 2: one round = W rows of the shell, one per lane (bounds, x reach, directory), then scanned by the group
+    bool need = finite && !(L.kthD() < g.ring2Safe);
+    int r = 2, rEnd = 0;
+    if (need) {
+      const int r0 = max(max(max(-ax.c, ax.c - (g.nx - 1)), max(-ay.c, ay.c - (g.ny - 1))), max(max(-az.c, az.c - (g.nz - 1)), 0));
+      rEnd = max(max(max(ax.c, g.nx - 1 - ax.c), max(ay.c, g.ny - 1 - ay.c)), max(az.c, g.nz - 1 - az.c));
+      r = max(2, r0);
+      need = r <= rEnd && !(ringLowerBound(ax, ay, az, r, g.cell, g.slack) > L.kthD());
+    }
+    while (need) {
+      const int y0 = max(ay.c - r, 0), z0 = max(az.c - r, 0);   // shell rows clipped to the grid
+      const int wy = max(min(ay.c + r, g.ny - 1) - y0 + 1, 0), wz = max(min(az.c + r, g.nz - 1) - z0 + 1, 0);
+      const int nrows = wy * wz;
+      for (int t0 = 0; t0 < nrows; t0 += W) {
+        const int t = t0 + l;
+        const int iy = y0 + t % max(wy, 1), iz = z0 + t / max(wy, 1);
+        const int dy = iy - ay.c, dz = iz - az.c;
+        uint32_t s0 = 0, e0 = 0, s1 = 0, e1 = 0;
+        float rowLb = CUDART_INF_F;
+        if (t < nrows) {
+          rowLb = lb3(0.f, axisGap(ay, iy, g.cell, g.slack), axisGap(az, iz, g.cell, g.slack));
+          const float bound = L.kthD();
+          if (!(rowLb > bound)) {
+            int xlo = 0, xhi = g.nx - 1;
+            if (bound < CUDART_INF_F) {
+              const float reach = __fadd_rn(sqrtf(fmaxf(__fsub_rn(bound, rowLb), 0.f)), g.slack);
+              xlo = cellOfClamped(__fsub_rn(__fsub_rn(q.x, reach), g.slack), g.ox, g.inv_cell, g.nx);
+              xhi = cellOfClamped(__fadd_rn(__fadd_rn(q.x, reach), g.slack), g.ox, g.inv_cell, g.nx);
+            }
+            const uint32_t rowBase = (uint32_t)g.nx * ((uint32_t)iy + (uint32_t)g.ny * (uint32_t)iz);
+            if ((abs(dz) == r) || (abs(dy) == r)) {   // shell row: the whole x range
+              const int xa = max(ax.c - r, xlo), xb = min(ax.c + r, xhi);
+              if (xa <= xb) { s0 = cellStart[rowBase + xa]; e0 = cellStart[rowBase + xb + 1]; }
+            } else {                                   // interior row: its two end cells
+              const int xl = ax.c - r, xr = ax.c + r;
+              if (xl >= xlo && xl <= xhi) { s0 = cellStart[rowBase + xl]; e0 = cellStart[rowBase + xl + 1]; }
+              if (xr >= xlo && xr <= xhi) { s1 = cellStart[rowBase + xr]; e1 = cellStart[rowBase + xr + 1]; }
+            }
+          }
+        }
+        unsigned m = __ballot_sync(gmask, e0 > s0 || e1 > s1);
+        if (W < 32) m = (m >> gbase) & ((1u << (W & 31)) - 1u);
+        while (m) {
+          const int b = __ffs(m) - 1;
+          m &= m - 1u;
+          const float lb = __shfl_sync(gmask, rowLb, b, W);
+          const uint32_t a0 = __shfl_sync(gmask, s0, b, W), b0 = __shfl_sync(gmask, e0, b, W);
+          const uint32_t a1 = __shfl_sync(gmask, s1, b, W), b1 = __shfl_sync(gmask, e1, b, W);
+          if (!(lb > L.kthD())) {
+            scanList<W, SELFCHK>(pts, a0, b0, q, selfId, L, visits);
+            scanList<W, SELFCHK>(pts, a1, b1, q, selfId, L, visits);
+          }
+        }
+      }
+      ++r;
+      need = r <= rEnd && !(ringLowerBound(ax, ay, az, r, g.cell, g.slack) > L.kthD());
+    }
+    if (l < k) {
+      const bool found = L.key != initKey;
+      const int64_t o = (int64_t)k * qi + l;
+      outIds[o] = found ? (int)(unsigned)L.key : -1;
+      outD2[o] = found ? __uint_as_float((unsigned)(L.key >> 32)) : CUDART_INF_F;
+      outPos[o] = found ? L.pos : -1;
+    }
+  }
+  for (int o = 16; o > 0; o >>= 1) visits += __shfl_xor_sync(0xffffffffu, visits, o);
+  if ((threadIdx.x & 31) == 0 && visits) atomicAdd(visitCounter, (unsigned long long)visits);
+}
+
+template <int W>
+void launchKnnList(b200reg_ctx* ctx, const b200reg_index* ix, const float4* q, int64_t n, int hasT, const Rigid12& T, int k, float maxd2,
+                   int allowSelf, int* ids, float* d2, int* pos, unsigned long long* visits) {
+  const int blocks = divUp(n * W, 256);
+  if (allowSelf)
+    knnListKernel<W, false><<<blocks, 256, 0, ctx->stream>>>(ix->pts, ix->cellStart, ix->g, q, n, hasT, T, k, maxd2, ids, d2, pos, visits);
+  else
+    knnListKernel<W, true><<<blocks, 256, 0, ctx->stream>>>(ix->pts, ix->cellStart, ix->g, q, n, hasT, T, k, maxd2, ids, d2, pos, visits);
+}
+
 template <int G>
 void launchKnn1(b200reg_ctx* ctx, const b200reg_index* ix, const float4* q, int64_t n, int hasT, const Rigid12& T, float maxd2, int allowSelf, int* ids, float* d2, int* pos, unsigned long long* visits) {
   const int blocks = divUp(n * G, 256);
@@ -522,6 +714,7 @@ int launchKnn1Loop(b200reg_ctx* ctx, const IcpDevParams* P, const IcpDevState* S
 }
 
 // Device-side entry shared with icp.cu / normals.cu.  Results land in ctx->matchIds / matchD2 / matchPos (k*n entries);
+// queries == nullptr (2 <= k <= 32 and the list kernel only): the index's own points, n == index size.
 // the touched-point counter is dstate[0] (unsigned long long), accumulated.
 int runKnn(b200reg_ctx* ctx, const b200reg_index* ix, const float4* queries, int64_t n, const float* T, int k, float maxDist, int allowSelf) {
   if (k < 1 || k > 64) return setErr(ctx, B200REG_E_INVALID_PARAM, "knn: k = %d outside the supported range [1, 64]", k);
@@ -530,6 +723,7 @@ int runKnn(b200reg_ctx* ctx, const b200reg_index* ix, const float4* queries, int
   TRY(ensureBuf(ctx, ctx->matchD2, sizeof(float) * (size_t)k * n));
   TRY(ensureBuf(ctx, ctx->matchPos, sizeof(int) * (size_t)k * n));
   if (n == 0) return B200REG_OK;
+  if (!queries && (k < 2 || k > 32 || ctx->knnLanes == 1 || n != ix->m)) return setErr(ctx, B200REG_E_INVALID_PARAM, "knn: self mode needs 2 <= k <= 32");
   Rigid12 R;
   memset(&R, 0, sizeof(R));
   if (T) memcpy(R.m, T, sizeof(R.m));
@@ -543,6 +737,9 @@ int runKnn(b200reg_ctx* ctx, const b200reg_index* ix, const float4* queries, int
   if (k == 1 && (ctx->knnLanes == 8 || ctx->knnLanes == 0)) launchKnn1<8>(ctx, ix, queries, n, hasT, R, maxd2, allowSelf, ids, d2, pos, visits);
   else if (k == 1 && ctx->knnLanes == 4) launchKnn1<4>(ctx, ix, queries, n, hasT, R, maxd2, allowSelf, ids, d2, pos, visits);
   else if (k == 1) launchKnn<1>(ctx, ix, queries, n, hasT, R, k, maxd2, allowSelf, ids, d2, pos, visits);
+  else if (k <= 8 && ctx->knnLanes != 1) launchKnnList<8>(ctx, ix, queries, n, hasT, R, k, maxd2, allowSelf, ids, d2, pos, visits);
+  else if (k <= 16 && ctx->knnLanes != 1) launchKnnList<16>(ctx, ix, queries, n, hasT, R, k, maxd2, allowSelf, ids, d2, pos, visits);
+  else if (k <= 32 && ctx->knnLanes != 1) launchKnnList<32>(ctx, ix, queries, n, hasT, R, k, maxd2, allowSelf, ids, d2, pos, visits);
   else if (k <= 4) launchKnn<4>(ctx, ix, queries, n, hasT, R, k, maxd2, allowSelf, ids, d2, pos, visits);
   else if (k <= 8) launchKnn<8>(ctx, ix, queries, n, hasT, R, k, maxd2, allowSelf, ids, d2, pos, visits);
   else if (k <= 16) launchKnn<16>(ctx, ix, queries, n, hasT, R, k, maxd2, allowSelf, ids, d2, pos, visits);

@@ -187,7 +187,9 @@ extern "C" int32_t b200reg_surface_normals(b200reg_ctx* ctx, b200reg_cloud* inou
   const float zero[3] = {0.f, 0.f, 0.f};
   b200reg_index* ix = nullptr;
   TRY(buildIndex(ctx, inout, zero, mn, mx, 0.f, &ix));
-  int st = runKnn(ctx, ix, inout->xyz, n, nullptr, knn, max_dist, 1);
+  // the list kernel walks the cloud in the index's sorted order (null queries); the one-thread kernel takes it as it lies
+  const float4* qs = (ctx->knnLanes == 1 || knn > 32) ? inout->xyz : nullptr;
+  int st = runKnn(ctx, ix, qs, n, nullptr, knn, max_dist, 1);
   if (st != B200REG_OK) { b200reg_index_free(ctx, ix); return st; }
   if (!inout->nrm) {
     cudaError_t e = cudaMalloc(&inout->nrm, sizeof(float4) * (size_t)inout->cap);

@@ -2,6 +2,7 @@
 // (Mapper.cpp:323,435).
 #include "mapper.h"
 
+#include <chrono>
 #include <cmath>
 #include <cstring>
 
@@ -44,6 +45,15 @@ b200reg_crop_spec at(const b200reg_crop_spec& s, const double* T) {   // Croppin
   return o;
 }
 
+struct StageClock {   // adds the wall time since construction / the last lap to one slot of MapperStepStats::stageMs
+  std::chrono::steady_clock::time_point t0 = std::chrono::steady_clock::now();
+  void lap(double* slot) {
+    const auto t1 = std::chrono::steady_clock::now();
+    *slot += std::chrono::duration<double, std::milli>(t1 - t0).count();
+    t0 = t1;
+  }
+};
+
 }  // namespace
 
 Mapper::Mapper(b200reg_ctx* ctx, const MapperParams& params) : ctx_(ctx), params_(params) {
@@ -69,10 +79,14 @@ void Mapper::setMapToRangeSensor(const double T[16]) {
 // ScanToMapIcp::processForScanMatchingAndMerging (ScanToMapRegistration.cpp:36-69)
 bool Mapper::process(const double* xyz, const double* normals, int64_t n, Processed* out) {
   // wide crop: mapBuilderCropper_->crop(in) — that cropper instance never gets a pose, i.e. it sits at the identity (:30-37)
+  const auto t0 = std::chrono::steady_clock::now();
   std::vector<double> cx(3 * (size_t)n + 3), cn(normals ? 3 * (size_t)n + 3 : 0);
   int64_t m = 0;
   const b200reg_crop_spec wide = at(params_.mapBuilderCropper, nullptr);
   if (b200reg_crop_f64(ctx_, &wide, xyz, normals, n, cx.data(), normals ? cn.data() : nullptr, &m) != B200REG_OK) { error_ = b200reg_last_error(ctx_); return false; }
+  StageClock clk;
+  clk.t0 = t0;
+  clk.lap(&stats_.stageMs[MapperStepStats::kWideCrop]);
   // o3d_slam::voxelize (helpers.cpp:108-115): no-op for voxel <= 0
   out->mergeXyz.assign(3 * (size_t)m + 3, 0.0);
   out->mergeNrm.assign(normals ? 3 * (size_t)m + 3 : 0, 0.0);
@@ -86,6 +100,7 @@ bool Mapper::process(const double* xyz, const double* normals, int64_t n, Proces
   }
   out->mergeXyz.resize(3 * (size_t)v);
   if (v == 0) { error_ = "ScanToMapIcp::wideCropped cropped size is zero"; return false; }   // assert_gt (:66)
+  clk.lap(&stats_.stageMs[MapperStepStats::kVoxelize]);
   // estimateNormalsOrCovariancesIfNeeded (CloudRegistration.cpp:62-75): only when the cloud has no normals;
   // EstimateNormals(Hybrid(radius, knn)) + NormalizeNormals + OrientNormalsTowardsCameraLocation(origin)
   if (!normals) {
@@ -103,6 +118,7 @@ bool Mapper::process(const double* xyz, const double* normals, int64_t n, Proces
   } else {
     out->mergeNrm.resize(3 * (size_t)v);
   }
+  clk.lap(&stats_.stageMs[MapperStepStats::kNormals]);
   // narrow crop at the identity pose (:62-63)
   out->matchXyz.assign(3 * (size_t)v + 3, 0.0);
   out->matchNrm.assign(3 * (size_t)v + 3, 0.0);
@@ -115,16 +131,19 @@ bool Mapper::process(const double* xyz, const double* normals, int64_t n, Proces
   out->matchXyz.resize(3 * (size_t)k);
   out->matchNrm.resize(3 * (size_t)k);
   if (k == 0) { error_ = "ScanToMapIcp::narrow cropped size is zero"; return false; }   // assert_gt (:65)
+  clk.lap(&stats_.stageMs[MapperStepStats::kNarrowCrop]);
   return true;
 }
 
 // Submap::insertScan (Submap.cpp:39-96) without carving: transform, append, re-voxelise inside the map-builder volume at the pose
 bool Mapper::insert(const Processed& p) {
+  StageClock clk;
   const b200reg_crop_spec vol = at(params_.mapBuilderCropper, mapToRangeSensor_);
   if (b200reg_map_insert(ctx_, map_, p.mergeXyz.data(), p.mergeNrm.data(), (int64_t)(p.mergeXyz.size() / 3), mapToRangeSensor_, &vol) != B200REG_OK) {
     error_ = b200reg_last_error(ctx_);
     return false;
   }
+  clk.lap(&stats_.stageMs[MapperStepStats::kInsert]);
   return true;
 }
 
@@ -158,11 +177,13 @@ bool Mapper::addRangeMeasurement(const double* xyz, const double* normals, int64
   const int64_t nRead = (int64_t)(processed.matchXyz.size() / 3);
   stats_.readingPoints = nRead;
   stats_.mergePoints = (int64_t)(processed.mergeXyz.size() / 3);
+  StageClock clk;
   if (reading_) { b200reg_cloud_free(ctx_, reading_); reading_ = nullptr; }
   if (b200reg_cloud_upload_f64(ctx_, processed.matchXyz.data(), processed.matchNrm.data(), nRead, &reading_) != B200REG_OK) {
     error_ = b200reg_last_error(ctx_);
     return false;
   }
+  clk.lap(&stats_.stageMs[MapperStepStats::kUpload]);
   float guess[16];
   for (int i = 0; i < 16; ++i) guess[i] = (float)estimate[i];
   // ---- map patch around the PREVIOUS pose (:328)
@@ -175,6 +196,7 @@ bool Mapper::addRangeMeasurement(const double* xyz, const double* normals, int64
     error_ = "map patch size is zero";
     return false;
   }
+  clk.lap(&stats_.stageMs[MapperStepStats::kPatch]);
   // ---- reference refresh every referenceCloudSettingPeriod seconds of sensor time (:345-367)
   float corrected[16];
   std::memcpy(corrected, guess, sizeof(corrected));
@@ -192,6 +214,7 @@ bool Mapper::addRangeMeasurement(const double* xyz, const double* normals, int64
     }
   }
   b200reg_cloud_free(ctx_, patch);
+  clk.lap(&stats_.stageMs[MapperStepStats::kReference]);
   // ---- icp_.compute(reading, {}, guess, false) (:388-393); any runtime_error leaves the initial guess (:420-422)
   if (!failed) {
     b200reg_icp_stats st;
@@ -202,6 +225,7 @@ bool Mapper::addRangeMeasurement(const double* xyz, const double* normals, int64
     if (code == B200REG_OK) std::memcpy(corrected, T, sizeof(corrected));
     else error_ = b200reg_last_error(ctx_);
   }
+  clk.lap(&stats_.stageMs[MapperStepStats::kRegister]);
   for (int i = 0; i < 16; ++i) mapToRangeSensor_[i] = (double)corrected[i];   // cast back to fp64 (:435)
   // ---- insertion gate (:483-489)
   double inv[16], motion[16];

@@ -45,6 +45,10 @@ struct MapperStepStats {
   int32_t referenceRefreshed = 0;
   int32_t inserted = 0;
   int64_t readingPoints = 0, mergePoints = 0, patchPoints = 0, mapPoints = 0;
+  // host wall time per stage (every stage ends in a synchronising call): wide crop, voxelise, normals, narrow crop,
+  // reading upload, map-patch crop, initReference, registration, insertion
+  enum { kWideCrop, kVoxelize, kNormals, kNarrowCrop, kUpload, kPatch, kReference, kRegister, kInsert, kStages };
+  double stageMs[kStages] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
 };
 
 class Mapper {

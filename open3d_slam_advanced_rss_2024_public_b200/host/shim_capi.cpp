@@ -201,6 +201,7 @@ typedef struct b200map_params {   // flat mirror of b200::MapperParams for ctype
 typedef struct b200map_stats {
   int32_t iterations, icp_status, reference_refreshed, inserted;
   int64_t reading_points, merge_points, patch_points, map_points;
+  double stage_ms[9];   // MapperStepStats::stageMs
 } b200map_stats;
 
 void* b200map_create(b200reg_ctx* ctx, const b200map_params* p) {
@@ -226,7 +227,8 @@ int32_t b200map_add_range_measurement(void* m, const double* xyz, const double* 
   std::memcpy(pose_out, mp->mapToRangeSensor(), sizeof(double) * 16);
   if (stats) {
     const b200::MapperStepStats& s = mp->lastStats();
-    *stats = b200map_stats{s.iterations, s.icpStatus, s.referenceRefreshed, s.inserted, s.readingPoints, s.mergePoints, s.patchPoints, s.mapPoints};
+    *stats = b200map_stats{s.iterations, s.icpStatus, s.referenceRefreshed, s.inserted, s.readingPoints, s.mergePoints, s.patchPoints, s.mapPoints, {}};
+    for (int i = 0; i < b200::MapperStepStats::kStages; ++i) stats->stage_ms[i] = s.stageMs[i];
   }
   setMsg(err, err_cap, mp->lastError());
   return ok ? 1 : 0;

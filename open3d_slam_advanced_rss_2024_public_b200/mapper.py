@@ -15,7 +15,10 @@ class MapperParams(C.Structure):
 
 class MapperStats(C.Structure):
     _fields_ = [("iterations", C.c_int32), ("icp_status", C.c_int32), ("reference_refreshed", C.c_int32), ("inserted", C.c_int32),
-                ("reading_points", C.c_int64), ("merge_points", C.c_int64), ("patch_points", C.c_int64), ("map_points", C.c_int64)]
+                ("reading_points", C.c_int64), ("merge_points", C.c_int64), ("patch_points", C.c_int64), ("map_points", C.c_int64),
+                ("stage_ms", C.c_double * 9)]
+
+    STAGES = ("wide_crop", "voxelize", "normals", "narrow_crop", "upload", "patch_crop", "init_reference", "register", "insert")
 
 
 def _lib():

@@ -122,6 +122,46 @@ def test_knn_synthetic_scan_vs_map(ctx, oracle):
     assert np.array_equal(d2_g.view(np.uint32), d2_o.view(np.uint32))
 
 
+@pytest.mark.parametrize("k", [2, 8, 9, 16, 17, 32])
+def test_knn_list_kernel_equals_one_thread_kernel_and_oracle(ctx, oracle, k):
+    """The W-lanes-per-query list kernel (2 <= k <= 32) against the one-thread kernel (B200REG_KNN_LANES=1) and the oracle k-d tree on a raw
+    LiDAR scan (density varies by orders of magnitude: crowded cells and many-ring walks), queries outside the grid, k > reachable points."""
+    import os
+    from open3d_slam_advanced_rss_2024_public_b200 import capi
+    c = scenes.config2(m=150_000, n_beams=32, n_az=512)
+    ref = oracle.feat4(np.concatenate([c["scan"], c["map_xyz"][:30_000]]))
+    rng = np.random.default_rng(k)
+    far = (rng.random((64, 3)) * 400 - 200).astype(np.float32)                       # mostly outside the grid
+    q = oracle.feat4(np.concatenate([c["scan"][::7] + rng.normal(0, 0.05, (c["scan"][::7].shape[0], 3)).astype(np.float32), far]))
+    os.environ["B200REG_KNN_LANES"] = "1"
+    try:
+        ctx1 = capi.Context(0)
+    finally:
+        del os.environ["B200REG_KNN_LANES"]
+    tree = oracle.KdTree(ref)
+    for md, allow in ((np.inf, True), (0.8, True), (0.15, False)):
+        ids_l, d2_l, vis = ctx.knn(ctx.build_index(ctx.upload(ref)), ctx.upload(q), k=k, max_dist=md, allow_self=allow)
+        ids_1, d2_1, _ = ctx1.knn(ctx1.build_index(ctx1.upload(ref)), ctx1.upload(q), k=k, max_dist=md, allow_self=allow)
+        assert np.array_equal(ids_l, ids_1), (k, md)
+        assert np.array_equal(d2_l.view(np.uint32), d2_1.view(np.uint32))
+        ids_o, d2_o, _ = tree.knn(q, k=k, max_dist=md, allow_self=allow, nthreads=8)
+        assert np.array_equal(ids_l, ids_o), (k, md)
+        assert np.array_equal(d2_l.view(np.uint32), d2_o.view(np.uint32))
+        assert vis > 0
+    # fewer points than k: padding (-1, inf) after the real neighbours
+    tiny = oracle.feat4(random_cloud(max(k - 1, 1), 77))
+    ids_t, d2_t, _ = ctx.knn(ctx.build_index(ctx.upload(tiny)), ctx.upload(q[:100]), k=k)
+    ids_o, d2_o = oracle.knn_brute(tiny, q[:100], k=k)
+    assert np.array_equal(ids_t, ids_o) and np.array_equal(d2_t.view(np.uint32), d2_o.view(np.uint32))
+    assert (ids_t[:, -1] == -1).all()
+    # a one-point reference far from the queries: the search starts at a ring ~1e6 cells out (k = 1 group kernel and list kernel)
+    one = oracle.feat4(random_cloud(1, 78))
+    for kk in (1, k):
+        ids_t, d2_t, _ = ctx.knn(ctx.build_index(ctx.upload(one)), ctx.upload(q[:100]), k=kk)
+        ids_o, d2_o = oracle.knn_brute(one, q[:100], k=kk)
+        assert np.array_equal(ids_t, ids_o) and np.array_equal(d2_t.view(np.uint32), d2_o.view(np.uint32))
+
+
 def test_knn_empty_and_errors(ctx, oracle, golden):
     from open3d_slam_advanced_rss_2024_public_b200 import capi
     ref = ctx.upload(oracle.feat4(golden["car"]["ref_xyz"][:100]))
