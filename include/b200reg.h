@@ -41,6 +41,7 @@ typedef struct b200reg_ctx b200reg_ctx;
 typedef struct b200reg_cloud b200reg_cloud;   /* device-resident DataPoints mirror: float4 xyz(+pad), float4 normal */
 typedef struct b200reg_index b200reg_index;   /* radix-sorted voxel-grid index over a (centred) reference cloud    */
 typedef struct b200reg_map b200reg_map;       /* resident fp64 voxel map (open3d_slam Submap::mapCloud_)           */
+typedef struct b200reg_cloud64 b200reg_cloud64; /* device-resident open3d::geometry::PointCloud mirror: fp64 xyz (+ normals) */
 
 /* ---- context ------------------------------------------------------------------------------------------------ */
 int32_t b200reg_abi_version(void);
@@ -236,6 +237,28 @@ int32_t b200reg_crop_f64(b200reg_ctx* ctx, const b200reg_crop_spec* volume, cons
  * min_bound - voxel/2; output in ascending (x,y,z) key order.  xyz_out / nrm_out: room for n points. */
 int32_t b200reg_voxel_down_sample_f64(b200reg_ctx* ctx, double voxel_size, const double* xyz, const double* nrm, int64_t n,
                                       double* xyz_out, double* nrm_out, int64_t* n_out);
+
+/* ---- the scan-processing chain on device-resident fp64 clouds: ScanToMapIcp::processForScanMatchingAndMerging
+ *      (open3d_slam/src/ScanToMapRegistration.cpp:36-69) without a host round trip between its steps.  Every `out` parameter is
+ *      in/out: *out == NULL creates a cloud, otherwise the existing cloud's storage is reused (grown when too small). --------- */
+int32_t b200reg_cloud64_upload(b200reg_ctx* ctx, const double* xyz, const double* nrm, int64_t n, b200reg_cloud64** out);
+int32_t b200reg_cloud64_download(b200reg_ctx* ctx, const b200reg_cloud64* cloud, double* xyz, double* nrm);
+int64_t b200reg_cloud64_size(const b200reg_cloud64* cloud);
+int32_t b200reg_cloud64_has_normals(const b200reg_cloud64* cloud);
+void    b200reg_cloud64_free(b200reg_ctx* ctx, b200reg_cloud64* cloud);
+/* CroppingVolume::crop (croppers.cpp:76-106), order preserving */
+int32_t b200reg_cloud64_crop(b200reg_ctx* ctx, const b200reg_crop_spec* volume, const b200reg_cloud64* in, b200reg_cloud64** out);
+/* o3d_slam::voxelize (helpers.cpp:108-115), same convention as b200reg_voxel_down_sample_f64 */
+int32_t b200reg_cloud64_voxel_down_sample(b200reg_ctx* ctx, double voxel_size, const b200reg_cloud64* in, b200reg_cloud64** out);
+/* estimateNormalsOrCovariancesIfNeeded (open3d_slam/src/CloudRegistration.cpp:62-75): normals from the knn nearest neighbours within
+ * `radius`, oriented toward `origin` (nullable = no orientation); arithmetic of b200reg_surface_normals on the fp32 copy */
+int32_t b200reg_cloud64_estimate_normals(b200reg_ctx* ctx, b200reg_cloud64* inout, int32_t knn, double radius, const double origin[3],
+                                         int32_t* degenerate_count);
+/* open3dToPointmatcher (open3d_conversions.cpp:57-118): fp64 -> the fp32 DataPoints mirror (asynchronous on the ctx stream) */
+int32_t b200reg_cloud64_to_f32(b200reg_ctx* ctx, const b200reg_cloud64* in, b200reg_cloud** out);
+/* Submap::insertScan (Submap.cpp:39-96) with the scan already on the device */
+int32_t b200reg_map_insert_cloud64(b200reg_ctx* ctx, b200reg_map* map, const b200reg_cloud64* scan, const double T_map_scan[16],
+                                   const b200reg_crop_spec* volume);
 
 #ifdef __cplusplus
 }

@@ -130,6 +130,16 @@ SYMBOLS = {
     "b200reg_map_download": (C.c_int32, [_VP, _VP, _VP, _VP]),
     "b200reg_voxel_down_sample_f64": (C.c_int32, [_VP, C.c_double, _VP, _VP, C.c_int64, _VP, _VP, C.POINTER(C.c_int64)]),
     "b200reg_crop_f64": (C.c_int32, [_VP, C.POINTER(CropSpec), _VP, _VP, C.c_int64, _VP, _VP, C.POINTER(C.c_int64)]),
+    "b200reg_cloud64_upload": (C.c_int32, [_VP, _VP, _VP, C.c_int64, C.POINTER(_VP)]),
+    "b200reg_cloud64_download": (C.c_int32, [_VP, _VP, _VP, _VP]),
+    "b200reg_cloud64_size": (C.c_int64, [_VP]),
+    "b200reg_cloud64_has_normals": (C.c_int32, [_VP]),
+    "b200reg_cloud64_free": (None, [_VP, _VP]),
+    "b200reg_cloud64_crop": (C.c_int32, [_VP, C.POINTER(CropSpec), _VP, C.POINTER(_VP)]),
+    "b200reg_cloud64_voxel_down_sample": (C.c_int32, [_VP, C.c_double, _VP, C.POINTER(_VP)]),
+    "b200reg_cloud64_estimate_normals": (C.c_int32, [_VP, _VP, C.c_int32, C.c_double, _VP, C.POINTER(C.c_int32)]),
+    "b200reg_cloud64_to_f32": (C.c_int32, [_VP, _VP, C.POINTER(_VP)]),
+    "b200reg_map_insert_cloud64": (C.c_int32, [_VP, _VP, _VP, _VP, C.POINTER(CropSpec)]),
 }
 
 
@@ -476,6 +486,71 @@ def register_batch(ctx, cfg, refs, readings, T_init):
     return To.reshape(n, 4, 4), list(stats)[:n], status[:n]
 
 
+class Cloud64:
+    """Device-resident fp64 cloud (the open3d::geometry::PointCloud mirror): the scan-processing chain of
+    ScanToMapRegistration.cpp:36-69 without host round trips.  Every step returns a new Cloud64, or refills `out` when given."""
+
+    def __init__(self, ctx, h=None):
+        self.ctx = ctx
+        self.h = h if h is not None else _VP()
+
+    @classmethod
+    def upload(cls, ctx, xyz, nrm=None, out=None):
+        xyz, nrm = _f64(xyz), _f64(nrm)
+        c = out if out is not None else cls(ctx)
+        ctx.check(lib().b200reg_cloud64_upload(ctx.h, _p(xyz), _p(nrm), xyz.shape[0], C.byref(c.h)))
+        return c
+
+    @property
+    def size(self):
+        return int(lib().b200reg_cloud64_size(self.h)) if self.h else 0
+
+    @property
+    def has_normals(self):
+        return bool(lib().b200reg_cloud64_has_normals(self.h)) if self.h else False
+
+    def download(self):
+        n = self.size
+        xyz = np.empty((n, 3), dtype=np.float64)
+        nrm = np.empty((n, 3), dtype=np.float64) if self.has_normals else None
+        self.ctx.check(lib().b200reg_cloud64_download(self.ctx.h, self.h, _p(xyz), _p(nrm)))
+        return xyz, nrm
+
+    def crop(self, volume, out=None):
+        c = out if out is not None else Cloud64(self.ctx)
+        self.ctx.check(lib().b200reg_cloud64_crop(self.ctx.h, C.byref(volume), self.h, C.byref(c.h)))
+        return c
+
+    def voxel_down_sample(self, voxel, out=None):
+        c = out if out is not None else Cloud64(self.ctx)
+        self.ctx.check(lib().b200reg_cloud64_voxel_down_sample(self.ctx.h, float(voxel), self.h, C.byref(c.h)))
+        return c
+
+    def estimate_normals(self, knn, radius, origin=None):
+        o = None if origin is None else _f64(origin)
+        deg = C.c_int32(0)
+        self.ctx.check(lib().b200reg_cloud64_estimate_normals(self.ctx.h, self.h, int(knn), float(radius), _p(o), C.byref(deg)))
+        return deg.value
+
+    def to_f32(self, out=None):
+        """open3dToPointmatcher: the fp32 DataPoints mirror (a capi.Cloud)."""
+        c = out if out is not None else Cloud(self.ctx, _VP())
+        self.ctx.check(lib().b200reg_cloud64_to_f32(self.ctx.h, self.h, C.byref(c.h)))
+        return c
+
+    def free(self):
+        if self.h:
+            lib().b200reg_cloud64_free(self.ctx.h, self.h)
+            self.h = _VP()
+
+    def __del__(self):
+        try:
+            if self.ctx.h:
+                self.free()
+        except Exception:
+            pass
+
+
 class VoxelMap:
     """Resident fp64 voxel map (open3d_slam Submap::mapCloud_ + insertScan + cropSubmap)."""
 
@@ -492,6 +567,10 @@ class VoxelMap:
         xyz, nrm = _f64(scan_xyz), _f64(scan_nrm)
         T = _f64(T_map_scan).reshape(16)
         self.ctx.check(lib().b200reg_map_insert(self.ctx.h, self.h, _p(xyz), _p(nrm), xyz.shape[0], _p(T), C.byref(volume)))
+
+    def insert_cloud64(self, scan, T_map_scan, volume):
+        T = _f64(T_map_scan).reshape(16)
+        self.ctx.check(lib().b200reg_map_insert_cloud64(self.ctx.h, self.h, scan.h, _p(T), C.byref(volume)))
 
     def crop(self, volume):
         h = _VP()

@@ -17,12 +17,12 @@ int ensureBuf(b200reg_ctx* ctx, DevBuf& b, size_t bytes) {
   if (bytes <= b.cap) return B200REG_OK;
   if (b.p) {
     CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
-    CUDA_TRY(ctx, cudaFree(b.p));
+    CUDA_TRY(ctx, devFree(ctx, b.p));
     b.p = nullptr;
     b.cap = 0;
   }
   size_t want = bytes + bytes / 4 + 256;
-  CUDA_TRY(ctx, cudaMalloc(&b.p, want));
+  CUDA_TRY(ctx, devAlloc(ctx, &b.p, want));
   b.cap = want;
   return B200REG_OK;
 }
@@ -119,7 +119,14 @@ int32_t b200reg_ctx_create(int32_t device, b200reg_ctx** out) {
   cudaEventCreate(&ctx->ev1);
   cudaEventCreate(&ctx->tev0);
   cudaEventCreate(&ctx->tev1);
-  if (cudaMalloc(&ctx->dstate, DSTATE_BYTES) != cudaSuccess) { delete ctx; return B200REG_E_OOM; }
+  {   // keep freed blocks in the pool instead of returning them to the driver at every synchronisation
+    cudaMemPool_t pool;
+    if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) {
+      unsigned long long keep = ~0ull;
+      cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+    }
+  }
+  if (devAlloc(ctx, &ctx->dstate, DSTATE_BYTES) != cudaSuccess) { delete ctx; return B200REG_E_OOM; }
   cudaMemsetAsync(ctx->dstate, 0, DSTATE_BYTES, ctx->stream);
   if (ensurePinned(ctx, 1 << 16) != B200REG_OK) { delete ctx; return B200REG_E_OOM; }
   const char* s3 = getenv("B200REG_SELECT_3PASS");
@@ -185,9 +192,10 @@ void b200reg_ctx_destroy(b200reg_ctx* ctx) {
   DevBuf* bufs[] = {&ctx->keys0, &ctx->keys1, &ctx->vals0, &ctx->vals1, &ctx->cubtmp, &ctx->misc, &ctx->partials,
                     &ctx->matchIds, &ctx->matchD2, &ctx->matchPos, &ctx->flags, &ctx->flush, &ctx->cand};
   for (DevBuf* b : bufs)
-    if (b->p) cudaFree(b->p);
+    if (b->p) devFree(ctx, b->p);
   if (ctx->pinned) cudaFreeHost(ctx->pinned);
-  if (ctx->dstate) cudaFree(ctx->dstate);
+  if (ctx->dstate) devFree(ctx, ctx->dstate);
+  cudaStreamSynchronize(ctx->stream);
   cudaEventDestroy(ctx->ev0);
   cudaEventDestroy(ctx->ev1);
   cudaEventDestroy(ctx->tev0);
@@ -236,10 +244,10 @@ static int allocCloud(b200reg_ctx* ctx, int64_t n, bool normals, b200reg_cloud**
   b200reg_cloud* c = new b200reg_cloud();
   c->n = n;
   c->cap = n > 0 ? n : 1;
-  cudaError_t e = cudaMalloc(&c->xyz, sizeof(float4) * (size_t)c->cap);
-  if (e == cudaSuccess && normals) e = cudaMalloc(&c->nrm, sizeof(float4) * (size_t)c->cap);
+  cudaError_t e = devAlloc(ctx, &c->xyz, sizeof(float4) * (size_t)c->cap);
+  if (e == cudaSuccess && normals) e = devAlloc(ctx, &c->nrm, sizeof(float4) * (size_t)c->cap);
   if (e != cudaSuccess) {
-    if (c->xyz) cudaFree(c->xyz);
+    if (c->xyz) devFree(ctx, c->xyz);
     delete c;
     return setErr(ctx, B200REG_E_OOM, "cloud allocation of %lld points failed: %s", (long long)n, cudaGetErrorString(e));
   }
@@ -284,14 +292,14 @@ int32_t b200reg_cloud_update_f32(b200reg_ctx* ctx, b200reg_cloud* c, const float
     CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
     const int64_t cap = n > c->cap ? n : c->cap;
     float4 *nx = nullptr, *nn = nullptr;
-    cudaError_t e = cudaMalloc(&nx, sizeof(float4) * (size_t)cap);
-    if (e == cudaSuccess && (normals || c->nrm)) e = cudaMalloc(&nn, sizeof(float4) * (size_t)cap);
+    cudaError_t e = devAlloc(ctx, &nx, sizeof(float4) * (size_t)cap);
+    if (e == cudaSuccess && (normals || c->nrm)) e = devAlloc(ctx, &nn, sizeof(float4) * (size_t)cap);
     if (e != cudaSuccess) {
-      if (nx) cudaFree(nx);
+      if (nx) devFree(ctx, nx);
       return setErr(ctx, B200REG_E_OOM, "cloud_update_f32: allocation of %lld points failed: %s", (long long)cap, cudaGetErrorString(e));
     }
-    if (c->xyz) cudaFree(c->xyz);
-    if (c->nrm) cudaFree(c->nrm);
+    if (c->xyz) devFree(ctx, c->xyz);
+    if (c->nrm) devFree(ctx, c->nrm);
     c->xyz = nx; c->nrm = nn; c->cap = cap;
   }
   c->n = n;
@@ -356,8 +364,8 @@ int32_t b200reg_cloud_has_normals(const b200reg_cloud* cloud) { return (cloud &&
 void b200reg_cloud_free(b200reg_ctx* ctx, b200reg_cloud* cloud) {
   if (!cloud) return;
   if (ctx) { cudaSetDevice(ctx->device); cudaStreamSynchronize(ctx->stream); }
-  if (cloud->xyz) cudaFree(cloud->xyz);
-  if (cloud->nrm) cudaFree(cloud->nrm);
+  if (cloud->xyz) devFree(ctx, cloud->xyz);
+  if (cloud->nrm) devFree(ctx, cloud->nrm);
   delete cloud;
 }
 

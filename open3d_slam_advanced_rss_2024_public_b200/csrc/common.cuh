@@ -43,6 +43,18 @@ struct b200reg_ctx {
   void* dstate = nullptr;   // small device state block (select state, counters)
 };
 
+// Device memory comes from the device's stream-ordered pool (release threshold raised in b200reg_ctx_create so freed blocks stay
+// cached): clouds, indices and growing scratch are allocated and freed on the ctx stream without a device-wide synchronisation.
+// Objects belong to the ctx that created them.
+template <class T>
+inline cudaError_t devAlloc(b200reg_ctx* ctx, T** p, size_t bytes) {
+  return cudaMallocAsync((void**)p, bytes > 0 ? bytes : 1, ctx->stream);
+}
+inline cudaError_t devFree(b200reg_ctx* ctx, void* p) {
+  if (!p) return cudaSuccess;
+  return ctx ? cudaFreeAsync(p, ctx->stream) : cudaFree(p);
+}
+
 struct b200reg_cloud {
   int64_t n = 0;
   int64_t cap = 0;

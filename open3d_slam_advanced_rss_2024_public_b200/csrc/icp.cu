@@ -701,7 +701,7 @@ int32_t b200reg_icp_create(b200reg_ctx* ctx, const b200reg_icp_config* cfg, b200
   icp->cfg = *cfg;
   CUDA_TRY(ctx, cudaSetDevice(ctx->device));
   static_assert(sizeof(IcpDevParams) <= LOOP_STATE_OFF - LOOP_PARAMS_OFF, "loop block layout");
-  if (cudaMalloc(&icp->dBlock, LOOP_STATE_OFF + sizeof(IcpDevState)) != cudaSuccess) {
+  if (devAlloc(icp->ctx, &icp->dBlock, LOOP_STATE_OFF + sizeof(IcpDevState)) != cudaSuccess) {
     delete icp;
     return setErr(ctx, B200REG_E_OOM, "icp_create: allocation failed");
   }
@@ -717,11 +717,11 @@ void b200reg_icp_destroy(b200reg_icp* icp) {
   cudaSetDevice(ctx->device);
   cudaStreamSynchronize(ctx->stream);
   if (icp->index) b200reg_index_free(ctx, icp->index);
-  if (icp->reading.p) cudaFree(icp->reading.p);
-  if (icp->readingNrm.p) cudaFree(icp->readingNrm.p);
+  if (icp->reading.p) devFree(icp->ctx, icp->reading.p);
+  if (icp->readingNrm.p) devFree(icp->ctx, icp->readingNrm.p);
   if (icp->exec) cudaGraphExecDestroy(icp->exec);
   if (icp->graph) cudaGraphDestroy(icp->graph);
-  if (icp->dBlock) cudaFree(icp->dBlock);
+  if (icp->dBlock) devFree(icp->ctx, icp->dBlock);
   delete icp;
 }
 

@@ -151,9 +151,9 @@ int buildIndex(b200reg_ctx* ctx, const b200reg_cloud* ref, const float mean[3], 
   }
   const size_t numCells = (size_t)g.nx * g.ny * g.nz;
 
-  cudaError_t e = cudaMalloc(&ix->pts, sizeof(float4) * (size_t)m);
-  if (e == cudaSuccess && ref->nrm) e = cudaMalloc(&ix->nrm, sizeof(float4) * (size_t)m);
-  if (e == cudaSuccess) e = cudaMalloc(&ix->cellStart, sizeof(uint32_t) * (numCells + 1));
+  cudaError_t e = devAlloc(ctx, &ix->pts, sizeof(float4) * (size_t)m);
+  if (e == cudaSuccess && ref->nrm) e = devAlloc(ctx, &ix->nrm, sizeof(float4) * (size_t)m);
+  if (e == cudaSuccess) e = devAlloc(ctx, &ix->cellStart, sizeof(uint32_t) * (numCells + 1));
   if (e != cudaSuccess) {
     b200reg_index_free(ctx, ix);
     return setErr(ctx, B200REG_E_OOM, "index_build: allocation failed (%zu cells, %lld points): %s", numCells, (long long)m, cudaGetErrorString(e));
@@ -210,9 +210,9 @@ int32_t b200reg_index_build(b200reg_ctx* ctx, const b200reg_cloud* ref, float ce
 void b200reg_index_free(b200reg_ctx* ctx, b200reg_index* index) {
   if (!index) return;
   if (ctx) { cudaSetDevice(ctx->device); cudaStreamSynchronize(ctx->stream); }
-  if (index->pts) cudaFree(index->pts);
-  if (index->nrm) cudaFree(index->nrm);
-  if (index->cellStart) cudaFree(index->cellStart);
+  if (index->pts) devFree(ctx, index->pts);
+  if (index->nrm) devFree(ctx, index->nrm);
+  if (index->cellStart) devFree(ctx, index->cellStart);
   delete index;
 }
 

@@ -29,6 +29,15 @@ struct b200reg_map {
   bool hasNormals = false;
 };
 
+// device-resident mirror of an open3d::geometry::PointCloud (fp64 points + optional normals): what travels between the
+// scan-processing steps of ScanToMapRegistration.cpp:36-69 without touching the host
+struct b200reg_cloud64 {
+  int64_t n = 0, cap = 0;
+  double* xyz = nullptr;
+  double* nrm = nullptr;   // allocated with xyz; valid iff hasNormals
+  bool hasNormals = false;
+};
+
 namespace {
 
 typedef unsigned long long u64;
@@ -207,12 +216,12 @@ int mapReserve(b200reg_ctx* ctx, b200reg_map* map, int64_t want) {
   if (want <= map->cap) return B200REG_OK;
   const int64_t cap = want + want / 2 + 1024;
   double* nx = nullptr; double* nn = nullptr; double* nx2 = nullptr; double* nn2 = nullptr;
-  cudaError_t e = cudaMalloc(&nx, sizeof(double) * 3 * (size_t)cap);
-  if (e == cudaSuccess) e = cudaMalloc(&nn, sizeof(double) * 3 * (size_t)cap);
-  if (e == cudaSuccess) e = cudaMalloc(&nx2, sizeof(double) * 3 * (size_t)cap);
-  if (e == cudaSuccess) e = cudaMalloc(&nn2, sizeof(double) * 3 * (size_t)cap);
+  cudaError_t e = devAlloc(ctx, &nx, sizeof(double) * 3 * (size_t)cap);
+  if (e == cudaSuccess) e = devAlloc(ctx, &nn, sizeof(double) * 3 * (size_t)cap);
+  if (e == cudaSuccess) e = devAlloc(ctx, &nx2, sizeof(double) * 3 * (size_t)cap);
+  if (e == cudaSuccess) e = devAlloc(ctx, &nn2, sizeof(double) * 3 * (size_t)cap);
   if (e != cudaSuccess) {
-    cudaFree(nx); cudaFree(nn); cudaFree(nx2); cudaFree(nn2);
+    devFree(ctx, nx); devFree(ctx, nn); devFree(ctx, nx2); devFree(ctx, nn2);
     return setErr(ctx, B200REG_E_OOM, "map: cannot reserve %lld points: %s", (long long)cap, cudaGetErrorString(e));
   }
   if (map->n > 0) {
@@ -220,7 +229,7 @@ int mapReserve(b200reg_ctx* ctx, b200reg_map* map, int64_t want) {
     CUDA_TRY(ctx, cudaMemcpyAsync(nn, map->nrm, sizeof(double) * 3 * (size_t)map->n, cudaMemcpyDeviceToDevice, ctx->stream));
   }
   CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
-  cudaFree(map->xyz); cudaFree(map->nrm); cudaFree(map->xyz2); cudaFree(map->nrm2);
+  devFree(ctx, map->xyz); devFree(ctx, map->nrm); devFree(ctx, map->xyz2); devFree(ctx, map->nrm2);
   map->xyz = nx; map->nrm = nn; map->xyz2 = nx2; map->nrm2 = nn2;
   map->cap = cap;
   return B200REG_OK;
@@ -281,6 +290,125 @@ int revoxelize(b200reg_ctx* ctx, double voxel, const b200reg_crop_spec& spec, co
   return B200REG_OK;
 }
 
+int cloud64Reserve(b200reg_ctx* ctx, b200reg_cloud64* c, int64_t want) {
+  if (want <= c->cap) return B200REG_OK;
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  devFree(ctx, c->xyz); devFree(ctx, c->nrm);
+  c->xyz = c->nrm = nullptr;
+  c->cap = 0;
+  const int64_t cap = want + want / 4 + 1024;
+  cudaError_t e = devAlloc(ctx, &c->xyz, sizeof(double) * 3 * (size_t)cap);
+  if (e == cudaSuccess) e = devAlloc(ctx, &c->nrm, sizeof(double) * 3 * (size_t)cap);
+  if (e != cudaSuccess) { devFree(ctx, c->xyz); c->xyz = nullptr; return setErr(ctx, B200REG_E_OOM, "cloud64: cannot reserve %lld points: %s", (long long)cap, cudaGetErrorString(e)); }
+  c->cap = cap;
+  return B200REG_OK;
+}
+
+// *out == nullptr: a new cloud; otherwise its storage is reused (grown when too small)
+int cloud64Out(b200reg_ctx* ctx, b200reg_cloud64** out, int64_t want) {
+  if (!*out) *out = new b200reg_cloud64();
+  (*out)->n = 0;
+  return cloud64Reserve(ctx, *out, want);
+}
+
+// CroppingVolume::crop (croppers.cpp:76-106) on device arrays: order-preserving compaction; synchronises for the count
+int cropDevice(b200reg_ctx* ctx, const b200reg_crop_spec& spec, const double* dIn, const double* dInN, int64_t n, double* dOut, double* dOutN,
+               int64_t* m) {
+  TRY(ensureBuf(ctx, ctx->flags, 2 * sizeof(unsigned) * (size_t)n + 64));
+  unsigned* flag = (unsigned*)ctx->flags.p;
+  unsigned* off = flag + n;
+  classifyKernel<<<divUp(n, 256), 256, 0, ctx->stream>>>(dIn, n, spec, 0.0, flag, nullptr, nullptr, nullptr);
+  LAUNCH_CHECK(ctx);
+  TRY(scanFlags(ctx, flag, off, n));
+  scatterSelectedKernel<<<divUp(n, 256), 256, 0, ctx->stream>>>(flag, off, n, dIn, dInN, dOut, dOutN);
+  LAUNCH_CHECK(ctx);
+  return scanTotal(ctx, flag, off, n, m);
+}
+
+// Open3D v0.15.1 PointCloud::VoxelDownSample on device arrays (see b200reg_voxel_down_sample_f64); synchronises twice
+int voxelDownDevice(b200reg_ctx* ctx, double voxel, const double* dIn, const double* dInN, int64_t n, double* dOut, double* dOutN, int64_t* nVox) {
+  const size_t u4 = sizeof(unsigned) * (size_t)n, k8 = sizeof(u64) * (size_t)n;
+  TRY(ensureBuf(ctx, ctx->flags, 2 * u4 + 64));
+  unsigned* head = (unsigned*)ctx->flags.p;
+  unsigned* headOff = head + n;
+  TRY(ensureBuf(ctx, ctx->keys0, k8));
+  TRY(ensureBuf(ctx, ctx->keys1, k8));
+  TRY(ensureBuf(ctx, ctx->vals0, u4));
+  TRY(ensureBuf(ctx, ctx->vals1, u4));
+  const int mb = (int)fmin((double)(2 * ctx->sm_count), (double)divUp(n, 256));
+  TRY(ensureBuf(ctx, ctx->partials, sizeof(double) * 3 * (size_t)mb));
+  minBoundKernel<<<mb, 256, 0, ctx->stream>>>(dIn, n, (double*)ctx->partials.p);
+  LAUNCH_CHECK(ctx);
+  TRY(ensurePinned(ctx, sizeof(double) * 3 * (size_t)mb + 64));
+  CUDA_TRY(ctx, cudaMemcpyAsync(ctx->pinned, ctx->partials.p, sizeof(double) * 3 * (size_t)mb, cudaMemcpyDeviceToHost, ctx->stream));
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  double mn[3] = {INFINITY, INFINITY, INFINITY};
+  for (int b = 0; b < mb; ++b) for (int d = 0; d < 3; ++d) mn[d] = fmin(mn[d], ((const double*)ctx->pinned)[3 * b + d]);
+  for (int d = 0; d < 3; ++d) mn[d] = mn[d] - voxel * 0.5;
+  int* dErr = (int*)((char*)ctx->dstate + 32768 + 64);
+  CUDA_TRY(ctx, cudaMemsetAsync(dErr, 0, sizeof(int), ctx->stream));
+  o3dKeyKernel<<<divUp(n, 256), 256, 0, ctx->stream>>>(dIn, n, mn[0], mn[1], mn[2], voxel, (u64*)ctx->keys0.p, (unsigned*)ctx->vals0.p, dErr);
+  LAUNCH_CHECK(ctx);
+  cub::DoubleBuffer<u64> dk((u64*)ctx->keys0.p, (u64*)ctx->keys1.p);
+  cub::DoubleBuffer<unsigned> dv((unsigned*)ctx->vals0.p, (unsigned*)ctx->vals1.p);
+  size_t tmp = 0;
+  CUDA_TRY(ctx, cub::DeviceRadixSort::SortPairs(nullptr, tmp, dk, dv, (int)n, 0, 63, ctx->stream));
+  TRY(ensureBuf(ctx, ctx->cubtmp, tmp));
+  tmp = ctx->cubtmp.cap;
+  CUDA_TRY(ctx, cub::DeviceRadixSort::SortPairs(ctx->cubtmp.p, tmp, dk, dv, (int)n, 0, 63, ctx->stream));
+  ctx->launches += 9;
+  headFlagKernel<<<divUp(n, 256), 256, 0, ctx->stream>>>(dk.Current(), n, head);
+  LAUNCH_CHECK(ctx);
+  TRY(scanFlags(ctx, head, headOff, n));
+  voxelReduceKernel<<<divUp(n, 256), 256, 0, ctx->stream>>>(dk.Current(), dv.Current(), head, headOff, n, dIn, dInN, 0, dOut, dOutN, 0);
+  LAUNCH_CHECK(ctx);
+  CUDA_TRY(ctx, cudaMemcpyAsync((int*)ctx->pinned + 8, dErr, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+  TRY(scanTotal(ctx, head, headOff, n, nVox));
+  if (((const int*)ctx->pinned)[8]) return setErr(ctx, B200REG_E_INVALID_PARAM, "voxel_down_sample: voxel size too small for the cloud extent (index beyond 2^21)");
+  return B200REG_OK;
+}
+
+// Submap::insertScan on a scan already in device memory (dIn / dInN may live in ctx->misc: it is reused only after the sync)
+int mapInsertDevice(b200reg_ctx* ctx, b200reg_map* map, const double* dIn, const double* dInN, int64_t n, const double T_map_scan[16],
+                    const b200reg_crop_spec& volume) {
+  const int64_t total = map->n + n;
+  if (total >= (int64_t)0x7fffffff) return setErr(ctx, B200REG_E_INVALID_PARAM, "map_insert: map too large");
+  TRY(mapReserve(ctx, map, total));
+  // `mapCloud_ += transformedCloud` (Submap.cpp:84): Open3D keeps normals only if both sides have them
+  const bool normals = (map->n == 0 || map->hasNormals) && dInN != nullptr;
+  double* dT = (double*)((char*)ctx->dstate + 40960);
+  CUDA_TRY(ctx, cudaMemcpyAsync(dT, T_map_scan, sizeof(double) * 16, cudaMemcpyHostToDevice, ctx->stream));
+  transformF64Kernel<<<divUp(n, 256), 256, 0, ctx->stream>>>(dIn, normals ? dInN : nullptr, n, dT, map->xyz + 3 * (size_t)map->n,
+                                                             normals ? map->nrm + 3 * (size_t)map->n : nullptr);
+  LAUNCH_CHECK(ctx);
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));   // T_map_scan (host) and the caller's staging may be reused
+  map->hasNormals = normals;
+  if (!(map->voxel > 0.0)) {   // voxel_size <= 0: plain append (helpers.cpp:121-124)
+    map->n = total;
+    return B200REG_OK;
+  }
+  int64_t newSize = 0;
+  TRY(revoxelize(ctx, map->voxel, volume, map->xyz, normals ? map->nrm : nullptr, total, map->xyz2, normals ? map->nrm2 : nullptr, &newSize));
+  double* t = map->xyz; map->xyz = map->xyz2; map->xyz2 = t;
+  t = map->nrm; map->nrm = map->nrm2; map->nrm2 = t;
+  map->n = newSize;
+  return B200REG_OK;
+}
+
+// open3dToPointmatcher (open3d_conversions.cpp:57-118) and back: fp64 SoA-of-3 <-> float4 clouds
+__global__ void toF32Kernel(const double* __restrict__ xyz, const double* __restrict__ nrm, int64_t n, float4* __restrict__ oxyz, float4* __restrict__ onrm) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  oxyz[i] = make_float4((float)xyz[3 * i], (float)xyz[3 * i + 1], (float)xyz[3 * i + 2], 1.f);
+  if (nrm && onrm) onrm[i] = make_float4((float)nrm[3 * i], (float)nrm[3 * i + 1], (float)nrm[3 * i + 2], 0.f);
+}
+__global__ void normalsToF64Kernel(const float4* __restrict__ nrm, int64_t n, double* __restrict__ out) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const float4 v = nrm[i];
+  out[3 * i] = (double)v.x; out[3 * i + 1] = (double)v.y; out[3 * i + 2] = (double)v.z;
+}
+
 }  // namespace
 
 extern "C" {
@@ -296,7 +424,7 @@ int32_t b200reg_map_create(b200reg_ctx* ctx, double voxel_size, b200reg_map** ou
 void b200reg_map_destroy(b200reg_ctx* ctx, b200reg_map* map) {
   if (!map) return;
   if (ctx) { cudaSetDevice(ctx->device); cudaStreamSynchronize(ctx->stream); }
-  cudaFree(map->xyz); cudaFree(map->nrm); cudaFree(map->xyz2); cudaFree(map->nrm2);
+  devFree(ctx, map->xyz); devFree(ctx, map->nrm); devFree(ctx, map->xyz2); devFree(ctx, map->nrm2);
   delete map;
 }
 
@@ -308,34 +436,22 @@ int32_t b200reg_map_insert(b200reg_ctx* ctx, b200reg_map* map, const double* sca
   if (!ctx || !map || n < 0 || (n > 0 && !scan_xyz) || !T_map_scan || !volume) return setErr(ctx, B200REG_E_INVALID_PARAM, "map_insert: bad arguments");
   if (n == 0) return B200REG_OK;
   CUDA_TRY(ctx, cudaSetDevice(ctx->device));
-  const int64_t total = map->n + n;
-  if (total >= (int64_t)0x7fffffff) return setErr(ctx, B200REG_E_INVALID_PARAM, "map_insert: map too large");
-  TRY(mapReserve(ctx, map, total));
-  // `mapCloud_ += transformedCloud` (Submap.cpp:84): Open3D keeps normals only if both sides have them
-  const bool normals = (map->n == 0 || map->hasNormals) && scan_nrm != nullptr;
   const size_t fb = sizeof(double) * 3 * (size_t)n;
   TRY(ensureBuf(ctx, ctx->misc, 2 * fb + 256));
   double* dIn = (double*)ctx->misc.p;
   double* dInN = scan_nrm ? dIn + 3 * (size_t)n : nullptr;
-  double* dT = (double*)((char*)ctx->dstate + 40960);
   CUDA_TRY(ctx, cudaMemcpyAsync(dIn, scan_xyz, fb, cudaMemcpyHostToDevice, ctx->stream));
   if (scan_nrm) CUDA_TRY(ctx, cudaMemcpyAsync(dInN, scan_nrm, fb, cudaMemcpyHostToDevice, ctx->stream));
-  CUDA_TRY(ctx, cudaMemcpyAsync(dT, T_map_scan, sizeof(double) * 16, cudaMemcpyHostToDevice, ctx->stream));
-  transformF64Kernel<<<divUp(n, 256), 256, 0, ctx->stream>>>(dIn, normals ? dInN : nullptr, n, dT, map->xyz + 3 * (size_t)map->n,
-                                                             normals ? map->nrm + 3 * (size_t)map->n : nullptr);
-  LAUNCH_CHECK(ctx);
-  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));   // host scan buffers may be reused; misc is reused below
-  map->hasNormals = normals;
-  if (!(map->voxel > 0.0)) {   // voxel_size <= 0: plain append (helpers.cpp:121-124)
-    map->n = total;
-    return B200REG_OK;
-  }
-  int64_t newSize = 0;
-  TRY(revoxelize(ctx, map->voxel, *volume, map->xyz, normals ? map->nrm : nullptr, total, map->xyz2, normals ? map->nrm2 : nullptr, &newSize));
-  double* t = map->xyz; map->xyz = map->xyz2; map->xyz2 = t;
-  t = map->nrm; map->nrm = map->nrm2; map->nrm2 = t;
-  map->n = newSize;
-  return B200REG_OK;
+  // (the core synchronises after the transform, before misc is reused by the re-voxelisation)
+  return mapInsertDevice(ctx, map, dIn, dInN, n, T_map_scan, *volume);
+}
+
+int32_t b200reg_map_insert_cloud64(b200reg_ctx* ctx, b200reg_map* map, const b200reg_cloud64* scan, const double T_map_scan[16],
+                                   const b200reg_crop_spec* volume) {
+  if (!ctx || !map || !scan || !T_map_scan || !volume) return setErr(ctx, B200REG_E_INVALID_PARAM, "map_insert_cloud64: bad arguments");
+  if (scan->n == 0) return B200REG_OK;
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  return mapInsertDevice(ctx, map, scan->xyz, scan->hasNormals ? scan->nrm : nullptr, scan->n, T_map_scan, *volume);
 }
 
 int32_t b200reg_map_crop(b200reg_ctx* ctx, const b200reg_map* map, const b200reg_crop_spec* volume, b200reg_cloud** out) {
@@ -356,9 +472,9 @@ int32_t b200reg_map_crop(b200reg_ctx* ctx, const b200reg_map* map, const b200reg
   b200reg_cloud* c = new b200reg_cloud();
   c->n = m;
   c->cap = m > 0 ? m : 1;
-  cudaError_t e = cudaMalloc(&c->xyz, sizeof(float4) * (size_t)c->cap);
-  if (e == cudaSuccess && map->hasNormals) e = cudaMalloc(&c->nrm, sizeof(float4) * (size_t)c->cap);
-  if (e != cudaSuccess) { cudaFree(c->xyz); delete c; return setErr(ctx, B200REG_E_OOM, "map_crop: %s", cudaGetErrorString(e)); }
+  cudaError_t e = devAlloc(ctx, &c->xyz, sizeof(float4) * (size_t)c->cap);
+  if (e == cudaSuccess && map->hasNormals) e = devAlloc(ctx, &c->nrm, sizeof(float4) * (size_t)c->cap);
+  if (e != cudaSuccess) { devFree(ctx, c->xyz); delete c; return setErr(ctx, B200REG_E_OOM, "map_crop: %s", cudaGetErrorString(e)); }
   if (m > 0) {
     scatterSelectedF32Kernel<<<divUp(n, 256), 256, 0, ctx->stream>>>(flag, off, n, map->xyz, map->hasNormals ? map->nrm : nullptr, c->xyz, c->nrm);
     LAUNCH_CHECK(ctx);
@@ -392,18 +508,10 @@ int32_t b200reg_crop_f64(b200reg_ctx* ctx, const b200reg_crop_spec* volume, cons
   double* dInN = dIn + 3 * (size_t)n;
   double* dOut = dInN + 3 * (size_t)n;
   double* dOutN = dOut + 3 * (size_t)n;
-  TRY(ensureBuf(ctx, ctx->flags, 2 * sizeof(unsigned) * (size_t)n + 64));
-  unsigned* flag = (unsigned*)ctx->flags.p;
-  unsigned* off = flag + n;
   CUDA_TRY(ctx, cudaMemcpyAsync(dIn, xyz, fb, cudaMemcpyHostToDevice, ctx->stream));
   if (nrm) CUDA_TRY(ctx, cudaMemcpyAsync(dInN, nrm, fb, cudaMemcpyHostToDevice, ctx->stream));
-  classifyKernel<<<divUp(n, 256), 256, 0, ctx->stream>>>(dIn, n, *volume, 0.0, flag, nullptr, nullptr, nullptr);
-  LAUNCH_CHECK(ctx);
-  TRY(scanFlags(ctx, flag, off, n));
-  scatterSelectedKernel<<<divUp(n, 256), 256, 0, ctx->stream>>>(flag, off, n, dIn, nrm ? dInN : nullptr, dOut, dOutN);
-  LAUNCH_CHECK(ctx);
   int64_t m = 0;
-  TRY(scanTotal(ctx, flag, off, n, &m));
+  TRY(cropDevice(ctx, *volume, dIn, nrm ? dInN : nullptr, n, dOut, dOutN, &m));
   if (m > 0 && xyz_out) CUDA_TRY(ctx, cudaMemcpyAsync(xyz_out, dOut, sizeof(double) * 3 * (size_t)m, cudaMemcpyDeviceToHost, ctx->stream));
   if (m > 0 && nrm && nrm_out) CUDA_TRY(ctx, cudaMemcpyAsync(nrm_out, dOutN, sizeof(double) * 3 * (size_t)m, cudaMemcpyDeviceToHost, ctx->stream));
   CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
@@ -422,58 +530,145 @@ int32_t b200reg_voxel_down_sample_f64(b200reg_ctx* ctx, double voxel, const doub
   if (n == 0) return B200REG_OK;
   if (n >= (int64_t)0x7fffffff) return setErr(ctx, B200REG_E_INVALID_PARAM, "voxel_down_sample: too many points");
   CUDA_TRY(ctx, cudaSetDevice(ctx->device));
-  const size_t fb = sizeof(double) * 3 * (size_t)n, u4 = sizeof(unsigned) * (size_t)n, k8 = sizeof(u64) * (size_t)n;
+  const size_t fb = sizeof(double) * 3 * (size_t)n;
   TRY(ensureBuf(ctx, ctx->misc, 4 * fb + 64));
   double* dIn = (double*)ctx->misc.p;
   double* dInN = dIn + 3 * (size_t)n;
   double* dOut = dInN + 3 * (size_t)n;
   double* dOutN = dOut + 3 * (size_t)n;
-  TRY(ensureBuf(ctx, ctx->flags, 2 * u4 + 64));
-  unsigned* head = (unsigned*)ctx->flags.p;
-  unsigned* headOff = head + n;
-  TRY(ensureBuf(ctx, ctx->keys0, k8));
-  TRY(ensureBuf(ctx, ctx->keys1, k8));
-  TRY(ensureBuf(ctx, ctx->vals0, u4));
-  TRY(ensureBuf(ctx, ctx->vals1, u4));
   CUDA_TRY(ctx, cudaMemcpyAsync(dIn, xyz, fb, cudaMemcpyHostToDevice, ctx->stream));
   if (nrm) CUDA_TRY(ctx, cudaMemcpyAsync(dInN, nrm, fb, cudaMemcpyHostToDevice, ctx->stream));
-  const int mb = (int)fmin((double)(2 * ctx->sm_count), (double)divUp(n, 256));
-  TRY(ensureBuf(ctx, ctx->partials, sizeof(double) * 3 * (size_t)mb));
-  minBoundKernel<<<mb, 256, 0, ctx->stream>>>(dIn, n, (double*)ctx->partials.p);
-  LAUNCH_CHECK(ctx);
-  TRY(ensurePinned(ctx, sizeof(double) * 3 * (size_t)mb + 64));
-  CUDA_TRY(ctx, cudaMemcpyAsync(ctx->pinned, ctx->partials.p, sizeof(double) * 3 * (size_t)mb, cudaMemcpyDeviceToHost, ctx->stream));
-  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
-  double mn[3] = {INFINITY, INFINITY, INFINITY};
-  for (int b = 0; b < mb; ++b) for (int d = 0; d < 3; ++d) mn[d] = fmin(mn[d], ((const double*)ctx->pinned)[3 * b + d]);
-  for (int d = 0; d < 3; ++d) mn[d] = mn[d] - voxel * 0.5;
-  int* dErr = (int*)((char*)ctx->dstate + 32768 + 64);
-  CUDA_TRY(ctx, cudaMemsetAsync(dErr, 0, sizeof(int), ctx->stream));
-  o3dKeyKernel<<<divUp(n, 256), 256, 0, ctx->stream>>>(dIn, n, mn[0], mn[1], mn[2], voxel, (u64*)ctx->keys0.p, (unsigned*)ctx->vals0.p, dErr);
-  LAUNCH_CHECK(ctx);
-  cub::DoubleBuffer<u64> dk((u64*)ctx->keys0.p, (u64*)ctx->keys1.p);
-  cub::DoubleBuffer<unsigned> dv((unsigned*)ctx->vals0.p, (unsigned*)ctx->vals1.p);
-  size_t tmp = 0;
-  CUDA_TRY(ctx, cub::DeviceRadixSort::SortPairs(nullptr, tmp, dk, dv, (int)n, 0, 63, ctx->stream));
-  TRY(ensureBuf(ctx, ctx->cubtmp, tmp));
-  tmp = ctx->cubtmp.cap;
-  CUDA_TRY(ctx, cub::DeviceRadixSort::SortPairs(ctx->cubtmp.p, tmp, dk, dv, (int)n, 0, 63, ctx->stream));
-  ctx->launches += 9;
-  headFlagKernel<<<divUp(n, 256), 256, 0, ctx->stream>>>(dk.Current(), n, head);
-  LAUNCH_CHECK(ctx);
-  TRY(scanFlags(ctx, head, headOff, n));
-  voxelReduceKernel<<<divUp(n, 256), 256, 0, ctx->stream>>>(dk.Current(), dv.Current(), head, headOff, n, dIn, nrm ? dInN : nullptr, 0, dOut,
-                                                             nrm ? dOutN : nullptr, 0);
-  LAUNCH_CHECK(ctx);
   int64_t nVox = 0;
-  TRY(scanTotal(ctx, head, headOff, n, &nVox));
-  CUDA_TRY(ctx, cudaMemcpyAsync(ctx->pinned, dErr, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+  TRY(voxelDownDevice(ctx, voxel, dIn, nrm ? dInN : nullptr, n, dOut, nrm ? dOutN : nullptr, &nVox));
   CUDA_TRY(ctx, cudaMemcpyAsync(xyz_out, dOut, sizeof(double) * 3 * (size_t)nVox, cudaMemcpyDeviceToHost, ctx->stream));
   if (nrm && nrm_out) CUDA_TRY(ctx, cudaMemcpyAsync(nrm_out, dOutN, sizeof(double) * 3 * (size_t)nVox, cudaMemcpyDeviceToHost, ctx->stream));
   CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
-  if (*(const int*)ctx->pinned) return setErr(ctx, B200REG_E_INVALID_PARAM, "voxel_down_sample: voxel size too small for the cloud extent (index beyond 2^21)");
   *n_out = nVox;
   return B200REG_OK;
 }
 
+// ---- the same steps on device-resident fp64 clouds (no host round trip between them) ------------------------------------
+int32_t b200reg_cloud64_upload(b200reg_ctx* ctx, const double* xyz, const double* nrm, int64_t n, b200reg_cloud64** out) {
+  if (!ctx || !out || n < 0 || (n > 0 && !xyz)) return setErr(ctx, B200REG_E_INVALID_PARAM, "cloud64_upload: bad arguments");
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  TRY(cloud64Out(ctx, out, n));
+  b200reg_cloud64* c = *out;
+  if (n > 0) {
+    CUDA_TRY(ctx, cudaMemcpyAsync(c->xyz, xyz, sizeof(double) * 3 * (size_t)n, cudaMemcpyHostToDevice, ctx->stream));
+    if (nrm) CUDA_TRY(ctx, cudaMemcpyAsync(c->nrm, nrm, sizeof(double) * 3 * (size_t)n, cudaMemcpyHostToDevice, ctx->stream));
+    CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));   // pageable host memory may be reused by the caller
+  }
+  c->n = n;
+  c->hasNormals = nrm != nullptr;
+  return B200REG_OK;
+}
+
+int32_t b200reg_cloud64_download(b200reg_ctx* ctx, const b200reg_cloud64* c, double* xyz, double* nrm) {
+  if (!ctx || !c) return setErr(ctx, B200REG_E_INVALID_PARAM, "cloud64_download: bad arguments");
+  if (nrm && !c->hasNormals) return setErr(ctx, B200REG_E_INVALID_FIELD, "cloud64 has no normals");
+  if (c->n == 0) return B200REG_OK;
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  if (xyz) CUDA_TRY(ctx, cudaMemcpyAsync(xyz, c->xyz, sizeof(double) * 3 * (size_t)c->n, cudaMemcpyDeviceToHost, ctx->stream));
+  if (nrm) CUDA_TRY(ctx, cudaMemcpyAsync(nrm, c->nrm, sizeof(double) * 3 * (size_t)c->n, cudaMemcpyDeviceToHost, ctx->stream));
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  return B200REG_OK;
+}
+
+int64_t b200reg_cloud64_size(const b200reg_cloud64* c) { return c ? c->n : 0; }
+int32_t b200reg_cloud64_has_normals(const b200reg_cloud64* c) { return (c && c->hasNormals) ? 1 : 0; }
+
+void b200reg_cloud64_free(b200reg_ctx* ctx, b200reg_cloud64* c) {
+  if (!c) return;
+  if (ctx) { cudaSetDevice(ctx->device); cudaStreamSynchronize(ctx->stream); }
+  devFree(ctx, c->xyz); devFree(ctx, c->nrm);
+  delete c;
+}
+
+int32_t b200reg_cloud64_crop(b200reg_ctx* ctx, const b200reg_crop_spec* volume, const b200reg_cloud64* in, b200reg_cloud64** out) {
+  if (!ctx || !volume || !in || !out || *out == in) return setErr(ctx, B200REG_E_INVALID_PARAM, "cloud64_crop: bad arguments");
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  TRY(cloud64Out(ctx, out, in->n));
+  b200reg_cloud64* c = *out;
+  c->hasNormals = in->hasNormals;
+  if (in->n == 0) return B200REG_OK;
+  int64_t m = 0;
+  TRY(cropDevice(ctx, *volume, in->xyz, in->hasNormals ? in->nrm : nullptr, in->n, c->xyz, c->nrm, &m));
+  c->n = m;
+  return B200REG_OK;
+}
+
+int32_t b200reg_cloud64_voxel_down_sample(b200reg_ctx* ctx, double voxel, const b200reg_cloud64* in, b200reg_cloud64** out) {
+  if (!ctx || !in || !out || *out == in) return setErr(ctx, B200REG_E_INVALID_PARAM, "cloud64_voxel_down_sample: bad arguments");
+  if (!(voxel > 0.0)) return setErr(ctx, B200REG_E_INVALID_PARAM, "voxel_down_sample: voxel_size <= 0");
+  if (in->n >= (int64_t)0x7fffffff) return setErr(ctx, B200REG_E_INVALID_PARAM, "voxel_down_sample: too many points");
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  TRY(cloud64Out(ctx, out, in->n));
+  b200reg_cloud64* c = *out;
+  c->hasNormals = in->hasNormals;
+  if (in->n == 0) return B200REG_OK;
+  int64_t nVox = 0;
+  TRY(voxelDownDevice(ctx, voxel, in->xyz, in->hasNormals ? in->nrm : nullptr, in->n, c->xyz, in->hasNormals ? c->nrm : nullptr, &nVox));
+  c->n = nVox;
+  return B200REG_OK;
+}
+
+int32_t b200reg_cloud64_to_f32(b200reg_ctx* ctx, const b200reg_cloud64* in, b200reg_cloud** out) {
+  if (!ctx || !in || !out) return setErr(ctx, B200REG_E_INVALID_PARAM, "cloud64_to_f32: bad arguments");
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  const bool fresh = (*out == nullptr);
+  b200reg_cloud* c = fresh ? new b200reg_cloud() : *out;
+  if (c->cap < in->n || c->cap == 0 || (in->hasNormals && !c->nrm)) {
+    CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+    devFree(ctx, c->xyz); devFree(ctx, c->nrm);
+    c->xyz = c->nrm = nullptr;
+    c->n = 0;
+    c->cap = in->n + in->n / 4 + 1024;
+    cudaError_t e = devAlloc(ctx, &c->xyz, sizeof(float4) * (size_t)c->cap);
+    if (e == cudaSuccess) e = devAlloc(ctx, &c->nrm, sizeof(float4) * (size_t)c->cap);
+    if (e != cudaSuccess) {
+      devFree(ctx, c->xyz);
+      c->xyz = nullptr;
+      c->cap = 0;
+      if (fresh) delete c;
+      return setErr(ctx, B200REG_E_OOM, "cloud64_to_f32: %s", cudaGetErrorString(e));
+    }
+  }
+  if (!in->hasNormals && c->nrm) {   // DataPoints without a normals descriptor
+    CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+    devFree(ctx, c->nrm);
+    c->nrm = nullptr;
+  }
+  c->n = in->n;
+  *out = c;
+  if (in->n > 0) {
+    toF32Kernel<<<divUp(in->n, 256), 256, 0, ctx->stream>>>(in->xyz, in->hasNormals ? in->nrm : nullptr, in->n, c->xyz, c->nrm);
+    LAUNCH_CHECK(ctx);
+  }
+  return B200REG_OK;
+}
+
+// estimateNormalsOrCovariancesIfNeeded (CloudRegistration.cpp:62-75): fp32 copy of the points -> SurfaceNormal kernels (kNN,
+// covariance, eigenvector, orientation toward `origin`) -> fp64 normals of the cloud.  Same arithmetic as
+// b200reg_cloud_upload_f64 + b200reg_surface_normals + a host widening of the result.
+int32_t b200reg_cloud64_estimate_normals(b200reg_ctx* ctx, b200reg_cloud64* inout, int32_t knn, double radius, const double origin[3],
+                                         int32_t* degenerate_count) {
+  if (!ctx || !inout) return setErr(ctx, B200REG_E_INVALID_PARAM, "cloud64_estimate_normals: bad arguments");
+  if (degenerate_count) *degenerate_count = 0;
+  if (inout->n == 0) return B200REG_OK;
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  b200reg_cloud* tmp = nullptr;
+  inout->hasNormals = false;
+  TRY(b200reg_cloud64_to_f32(ctx, inout, &tmp));
+  float o[3] = {0.f, 0.f, 0.f};
+  if (origin) for (int d = 0; d < 3; ++d) o[d] = (float)origin[d];
+  int code = b200reg_surface_normals(ctx, tmp, knn, (float)radius, 0.f, origin ? o : nullptr, nullptr, nullptr, nullptr, degenerate_count);
+  if (code == B200REG_OK) {
+    normalsToF64Kernel<<<divUp(inout->n, 256), 256, 0, ctx->stream>>>(tmp->nrm, inout->n, inout->nrm);
+    ctx->launches++;
+    if (cudaGetLastError() != cudaSuccess) code = setErr(ctx, B200REG_E_CUDA, "cloud64_estimate_normals: launch failed");
+    else inout->hasNormals = true;
+  }
+  b200reg_cloud_free(ctx, tmp);
+  return code;
+}
 }  // extern "C"

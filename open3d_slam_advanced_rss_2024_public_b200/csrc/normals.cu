@@ -192,7 +192,7 @@ extern "C" int32_t b200reg_surface_normals(b200reg_ctx* ctx, b200reg_cloud* inou
   int st = runKnn(ctx, ix, qs, n, nullptr, knn, max_dist, 1);
   if (st != B200REG_OK) { b200reg_index_free(ctx, ix); return st; }
   if (!inout->nrm) {
-    cudaError_t e = cudaMalloc(&inout->nrm, sizeof(float4) * (size_t)inout->cap);
+    cudaError_t e = devAlloc(ctx, &inout->nrm, sizeof(float4) * (size_t)inout->cap);
     if (e != cudaSuccess) { b200reg_index_free(ctx, ix); return setErr(ctx, B200REG_E_OOM, "surface_normals: %s", cudaGetErrorString(e)); }
   }
   const size_t extra = sizeof(float) * (size_t)n * 7 + 64;

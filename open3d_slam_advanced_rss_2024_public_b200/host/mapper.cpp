@@ -5,6 +5,7 @@
 #include <chrono>
 #include <cmath>
 #include <cstring>
+#include <utility>
 
 namespace b200 {
 namespace {
@@ -67,6 +68,10 @@ Mapper::Mapper(b200reg_ctx* ctx, const MapperParams& params) : ctx_(ctx), params
 
 Mapper::~Mapper() {
   if (reading_) b200reg_cloud_free(ctx_, reading_);
+  b200reg_cloud64_free(ctx_, raw_);
+  b200reg_cloud64_free(ctx_, cropped_);
+  b200reg_cloud64_free(ctx_, merge_);
+  b200reg_cloud64_free(ctx_, match_);
   if (icp_) b200reg_icp_destroy(icp_);
   if (map_) b200reg_map_destroy(ctx_, map_);
 }
@@ -76,70 +81,46 @@ void Mapper::setMapToRangeSensor(const double T[16]) {
   std::memcpy(mapToRangeSensorPrev_, T, sizeof(mapToRangeSensorPrev_));
 }
 
-// ScanToMapIcp::processForScanMatchingAndMerging (ScanToMapRegistration.cpp:36-69)
-bool Mapper::process(const double* xyz, const double* normals, int64_t n, Processed* out) {
-  // wide crop: mapBuilderCropper_->crop(in) — that cropper instance never gets a pose, i.e. it sits at the identity (:30-37)
-  const auto t0 = std::chrono::steady_clock::now();
-  std::vector<double> cx(3 * (size_t)n + 3), cn(normals ? 3 * (size_t)n + 3 : 0);
-  int64_t m = 0;
-  const b200reg_crop_spec wide = at(params_.mapBuilderCropper, nullptr);
-  if (b200reg_crop_f64(ctx_, &wide, xyz, normals, n, cx.data(), normals ? cn.data() : nullptr, &m) != B200REG_OK) { error_ = b200reg_last_error(ctx_); return false; }
+// ScanToMapIcp::processForScanMatchingAndMerging (ScanToMapRegistration.cpp:36-69), every step on the device: the raw scan is
+// the only host -> device copy of a mapping step
+bool Mapper::process(const double* xyz, const double* normals, int64_t n) {
   StageClock clk;
-  clk.t0 = t0;
+  auto fail = [&]() { error_ = b200reg_last_error(ctx_); return false; };
+  if (b200reg_cloud64_upload(ctx_, xyz, normals, n, &raw_) != B200REG_OK) return fail();
+  // wide crop: mapBuilderCropper_->crop(in) — that cropper instance never gets a pose, i.e. it sits at the identity (:30-37)
+  const b200reg_crop_spec wide = at(params_.mapBuilderCropper, nullptr);
+  if (b200reg_cloud64_crop(ctx_, &wide, raw_, &cropped_) != B200REG_OK) return fail();
   clk.lap(&stats_.stageMs[MapperStepStats::kWideCrop]);
   // o3d_slam::voxelize (helpers.cpp:108-115): no-op for voxel <= 0
-  out->mergeXyz.assign(3 * (size_t)m + 3, 0.0);
-  out->mergeNrm.assign(normals ? 3 * (size_t)m + 3 : 0, 0.0);
-  int64_t v = m;
-  if (params_.scanVoxelSize > 0.0 && m > 0) {
-    if (b200reg_voxel_down_sample_f64(ctx_, params_.scanVoxelSize, cx.data(), normals ? cn.data() : nullptr, m, out->mergeXyz.data(),
-                                      normals ? out->mergeNrm.data() : nullptr, &v) != B200REG_OK) { error_ = b200reg_last_error(ctx_); return false; }
+  if (params_.scanVoxelSize > 0.0 && b200reg_cloud64_size(cropped_) > 0) {
+    if (b200reg_cloud64_voxel_down_sample(ctx_, params_.scanVoxelSize, cropped_, &merge_) != B200REG_OK) return fail();
   } else {
-    std::memcpy(out->mergeXyz.data(), cx.data(), sizeof(double) * 3 * (size_t)m);
-    if (normals) std::memcpy(out->mergeNrm.data(), cn.data(), sizeof(double) * 3 * (size_t)m);
+    std::swap(cropped_, merge_);
+    if (!merge_) { error_ = "ScanToMapIcp::wideCropped cropped size is zero"; return false; }
   }
-  out->mergeXyz.resize(3 * (size_t)v);
-  if (v == 0) { error_ = "ScanToMapIcp::wideCropped cropped size is zero"; return false; }   // assert_gt (:66)
+  if (b200reg_cloud64_size(merge_) == 0) { error_ = "ScanToMapIcp::wideCropped cropped size is zero"; return false; }   // assert_gt (:66)
   clk.lap(&stats_.stageMs[MapperStepStats::kVoxelize]);
   // estimateNormalsOrCovariancesIfNeeded (CloudRegistration.cpp:62-75): only when the cloud has no normals;
   // EstimateNormals(Hybrid(radius, knn)) + NormalizeNormals + OrientNormalsTowardsCameraLocation(origin)
-  if (!normals) {
-    b200reg_cloud* c = nullptr;
-    if (b200reg_cloud_upload_f64(ctx_, out->mergeXyz.data(), nullptr, v, &c) != B200REG_OK) { error_ = b200reg_last_error(ctx_); return false; }
-    const float origin[3] = {0.f, 0.f, 0.f};
+  if (!b200reg_cloud64_has_normals(merge_)) {
+    const double origin[3] = {0.0, 0.0, 0.0};
     int32_t degenerate = 0;
-    int code = b200reg_surface_normals(ctx_, c, params_.normalsKnn, (float)params_.normalsRadius, 0.f, origin, nullptr, nullptr, nullptr, &degenerate);
-    std::vector<float> feat(4 * (size_t)v), nf(3 * (size_t)v);
-    if (code == B200REG_OK) code = b200reg_cloud_download_f32(ctx_, c, feat.data(), 4, nf.data());
-    b200reg_cloud_free(ctx_, c);
-    if (code != B200REG_OK) { error_ = b200reg_last_error(ctx_); return false; }
-    out->mergeNrm.assign(3 * (size_t)v, 0.0);
-    for (size_t i = 0; i < 3 * (size_t)v; ++i) out->mergeNrm[i] = (double)nf[i];
-  } else {
-    out->mergeNrm.resize(3 * (size_t)v);
+    if (b200reg_cloud64_estimate_normals(ctx_, merge_, params_.normalsKnn, params_.normalsRadius, origin, &degenerate) != B200REG_OK) return fail();
   }
   clk.lap(&stats_.stageMs[MapperStepStats::kNormals]);
   // narrow crop at the identity pose (:62-63)
-  out->matchXyz.assign(3 * (size_t)v + 3, 0.0);
-  out->matchNrm.assign(3 * (size_t)v + 3, 0.0);
-  int64_t k = 0;
   const b200reg_crop_spec narrow = at(params_.scanMatcherCropper, nullptr);
-  if (b200reg_crop_f64(ctx_, &narrow, out->mergeXyz.data(), out->mergeNrm.data(), v, out->matchXyz.data(), out->matchNrm.data(), &k) != B200REG_OK) {
-    error_ = b200reg_last_error(ctx_);
-    return false;
-  }
-  out->matchXyz.resize(3 * (size_t)k);
-  out->matchNrm.resize(3 * (size_t)k);
-  if (k == 0) { error_ = "ScanToMapIcp::narrow cropped size is zero"; return false; }   // assert_gt (:65)
+  if (b200reg_cloud64_crop(ctx_, &narrow, merge_, &match_) != B200REG_OK) return fail();
+  if (b200reg_cloud64_size(match_) == 0) { error_ = "ScanToMapIcp::narrow cropped size is zero"; return false; }   // assert_gt (:65)
   clk.lap(&stats_.stageMs[MapperStepStats::kNarrowCrop]);
   return true;
 }
 
 // Submap::insertScan (Submap.cpp:39-96) without carving: transform, append, re-voxelise inside the map-builder volume at the pose
-bool Mapper::insert(const Processed& p) {
+bool Mapper::insert() {
   StageClock clk;
   const b200reg_crop_spec vol = at(params_.mapBuilderCropper, mapToRangeSensor_);
-  if (b200reg_map_insert(ctx_, map_, p.mergeXyz.data(), p.mergeNrm.data(), (int64_t)(p.mergeXyz.size() / 3), mapToRangeSensor_, &vol) != B200REG_OK) {
+  if (b200reg_map_insert_cloud64(ctx_, map_, merge_, mapToRangeSensor_, &vol) != B200REG_OK) {
     error_ = b200reg_last_error(ctx_);
     return false;
   }
@@ -150,16 +131,15 @@ bool Mapper::insert(const Processed& p) {
 bool Mapper::addRangeMeasurement(const double* xyz, const double* normals, int64_t n, double time, const double odom[16]) {
   stats_ = MapperStepStats();
   error_.clear();
-  Processed processed;
   // ---- first scan (Mapper.cpp:179-193)
   if (b200reg_map_size(map_) == 0) {
     std::memcpy(mapToRangeSensorPrev_, mapToRangeSensor_, sizeof(mapToRangeSensor_));
-    if (!process(xyz, normals, n, &processed)) return false;
-    if (!insert(processed)) return false;
+    if (!process(xyz, normals, n)) return false;
+    if (!insert()) return false;
     std::memcpy(odomPrev_, odom, sizeof(odomPrev_));   // (the reference reads its odometry buffer at the previous scan's stamp)
     haveOdomPrev_ = true;
     stats_.inserted = 1;
-    stats_.mergePoints = (int64_t)(processed.mergeXyz.size() / 3);
+    stats_.mergePoints = b200reg_cloud64_size(merge_);
     stats_.mapPoints = b200reg_map_size(map_);
     return true;
   }
@@ -173,13 +153,11 @@ bool Mapper::addRangeMeasurement(const double* xyz, const double* normals, int64
     mul(mapToRangeSensorPrev_, motion, estimate);
   }
   // ---- scan processing and the fp64 -> fp32 conversion (:307-309)
-  if (!process(xyz, normals, n, &processed)) return false;
-  const int64_t nRead = (int64_t)(processed.matchXyz.size() / 3);
-  stats_.readingPoints = nRead;
-  stats_.mergePoints = (int64_t)(processed.mergeXyz.size() / 3);
+  if (!process(xyz, normals, n)) return false;
+  stats_.readingPoints = b200reg_cloud64_size(match_);
+  stats_.mergePoints = b200reg_cloud64_size(merge_);
   StageClock clk;
-  if (reading_) { b200reg_cloud_free(ctx_, reading_); reading_ = nullptr; }
-  if (b200reg_cloud_upload_f64(ctx_, processed.matchXyz.data(), processed.matchNrm.data(), nRead, &reading_) != B200REG_OK) {
+  if (b200reg_cloud64_to_f32(ctx_, match_, &reading_) != B200REG_OK) {   // open3dToPointmatcher, device to device
     error_ = b200reg_last_error(ctx_);
     return false;
   }
@@ -233,7 +211,7 @@ bool Mapper::addRangeMeasurement(const double* xyz, const double* normals, int64
   mul(inv, mapToRangeSensor_, motion);
   const double moved = std::sqrt(motion[3] * motion[3] + motion[7] * motion[7] + motion[11] * motion[11]);
   if (!(moved < params_.minMovementBetweenMappingSteps)) {
-    if (!insert(processed)) return false;
+    if (!insert()) return false;
     std::memcpy(lastInsertion_, mapToRangeSensor_, sizeof(lastInsertion_));
     stats_.inserted = 1;
   }

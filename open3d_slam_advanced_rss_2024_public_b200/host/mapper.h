@@ -70,17 +70,16 @@ class Mapper {
   const std::string& lastError() const { return error_; }
 
  private:
-  struct Processed {   // ProcessedScans (ScanToMapRegistration.hpp): match_ (narrow) and merge_ (wide), fp64 host clouds
-    std::vector<double> mergeXyz, mergeNrm, matchXyz, matchNrm;
-  };
-  bool process(const double* xyz, const double* normals, int64_t n, Processed* out);
-  bool insert(const Processed& p);
+  // ProcessedScans (ScanToMapRegistration.hpp): merge_ (wide) and match_ (narrow), device-resident fp64 clouds reused scan after scan
+  bool process(const double* xyz, const double* normals, int64_t n);
+  bool insert();
 
   b200reg_ctx* ctx_;
   MapperParams params_;
   b200reg_map* map_ = nullptr;
   b200reg_icp* icp_ = nullptr;
-  b200reg_cloud* reading_ = nullptr;   // reused device cloud of the reading (streaming upload)
+  b200reg_cloud* reading_ = nullptr;   // fp32 DataPoints mirror of match_ (open3dToPointmatcher on the device)
+  b200reg_cloud64 *raw_ = nullptr, *cropped_ = nullptr, *merge_ = nullptr, *match_ = nullptr;
   double mapToRangeSensor_[16], mapToRangeSensorPrev_[16], lastInsertion_[16], odomPrev_[16];
   bool haveOdomPrev_ = false, referenceSet_ = false;
   double lastReferenceInit_ = 0.0;

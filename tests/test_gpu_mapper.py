@@ -172,3 +172,56 @@ def test_voxel_down_sample_o3d_convention(ctx, oracle):
         ctx.voxel_down_sample(0.0, xyz)
     e, _ = ctx.voxel_down_sample(0.5, np.zeros((0, 3)))
     assert e.shape[0] == 0
+
+
+def test_cloud64_chain_equals_host_array_chain(ctx):
+    """The device-resident scan-processing chain (b200reg_cloud64_*) gives bit-identical clouds to the host-array entry points it
+    shares its kernels with (crop_f64 -> voxel_down_sample_f64 -> upload_f64 + surface_normals -> crop_f64 -> upload_f64), and the
+    map built from it equals the map built from host arrays."""
+    from open3d_slam_advanced_rss_2024_public_b200 import capi
+    scene = scenes.Scene(31, size=(60.0, 40.0, 8.0), n_boxes=25, n_cyl=15)
+    T = scenes.rigid(scenes.rot_axis_angle(np.array([0.0, 0.0, 1.0]), 0.2), np.array([1.0, -2.0, 1.7]))
+    scan = scenes.lidar_scan(scene, T, n_beams=48, n_az=600, noise_sigma=0.01, seed=5).astype(np.float64)
+    wide = capi.crop_spec(capi.CROP_MINMAX_RADIUS, np.zeros(3), rmin=1.5, rmax=40.0)
+    narrow = capi.crop_spec(capi.CROP_MAX_RADIUS, np.zeros(3), rmax=25.0)
+    # host-array chain
+    cx, _ = ctx.crop_f64(wide, scan)
+    vx, _ = ctx.voxel_down_sample(0.12, cx)
+    c32 = ctx.upload(vx)
+    c32.surface_normals(12, max_dist=0.8, orient_origin=np.zeros(3, np.float32))
+    _, n32 = c32.download()
+    vn = n32.astype(np.float64)
+    mx, mn = ctx.crop_f64(narrow, vx, vn)
+    # device chain, with storage reuse on a second pass (first pass on a smaller cloud so every buffer has to grow)
+    raw = crop = merge = match = None
+    for pts in (scan[:5000], scan):
+        raw = capi.Cloud64.upload(ctx, pts, out=raw)
+        crop = raw.crop(wide, out=crop)
+        merge = crop.voxel_down_sample(0.12, out=merge)
+        assert not merge.has_normals
+        merge.estimate_normals(12, 0.8, origin=np.zeros(3))
+        match = merge.crop(narrow, out=match)
+    dx, dn = merge.download()
+    assert np.array_equal(dx, vx) and np.array_equal(dn, vn)
+    qx, qn = match.download()
+    assert np.array_equal(qx, mx) and np.array_equal(qn, mn)
+    f, fn = match.to_f32().download()
+    assert np.array_equal(f[:, :3], mx.astype(np.float32)) and (f[:, 3] == 1).all() and np.array_equal(fn, mn.astype(np.float32))
+    # a cloud with normals keeps them through crop and voxelisation; without normals to_f32 has none
+    withn = capi.Cloud64.upload(ctx, vx, vn)
+    hx, hn = ctx.voxel_down_sample(0.3, vx, vn)
+    gx, gn = withn.voxel_down_sample(0.3).download()
+    assert np.array_equal(gx, hx) and np.array_equal(gn, hn)
+    assert not capi.Cloud64.upload(ctx, vx).to_f32().has_normals
+    # map insertion from the device cloud == from host arrays
+    vol = capi.crop_spec(capi.CROP_MAX_RADIUS, T[:3, 3], rmax=40.0)
+    ma, mb = capi.VoxelMap(ctx, 0.2), capi.VoxelMap(ctx, 0.2)
+    for Tm in (T, T @ scenes.rigid(np.eye(3), np.array([0.3, 0.1, 0.0]))):
+        ma.insert(vx, vn, Tm, vol)
+        mb.insert_cloud64(merge, Tm, vol)
+    xa, na = ma.download()
+    xb, nb = mb.download()
+    assert np.array_equal(xa, xb) and np.array_equal(na, nb)
+    # empty results and reuse of an emptied cloud
+    none = merge.crop(capi.crop_spec(capi.CROP_MAX_RADIUS, np.array([1e4, 0, 0]), rmax=1.0), out=match)
+    assert none.size == 0 and none.download()[0].shape == (0, 3)
