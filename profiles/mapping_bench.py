@@ -58,3 +58,22 @@ for tag, sel in (("reference refreshed", 1), ("reference kept", 0)):
     if len(rows):
         print(f"stages, {tag} ({len(rows)} scans), median ms: " + ", ".join(f"{n} {x:.2f}" for n, x in zip(MapperStats.STAGES, np.median(rows, axis=0)))
               + f" | sum {np.median(rows, axis=0).sum():.2f}")
+
+# ---- CPU arm: the same control flow composed from the oracle's pieces (tests/test_gpu_mapper.py::OracleMapper), first N scans
+n_cpu = int(sys.argv[2]) if len(sys.argv) > 2 else 0
+if n_cpu > 0:
+    from oracle import oracle_py as O  # noqa: E402  (profiles/ is measurement code: the oracle is the timed CPU baseline here)
+    from test_gpu_mapper import OracleMapper  # noqa: E402
+    O.lib()
+    om = OracleMapper(O, dict(kind=capi.CROP_MINMAX_RADIUS, rmin=2.0, rmax=80.0), dict(kind=capi.CROP_MAX_RADIUS, rmax=80.0),
+                      dict(knn=1, max_dist=0.5, trim_ratio=0.9, max_angle=1.57, max_iter=15, min_diff_rot=1e-3, min_diff_trans=1e-2, smooth_length=3),
+                      scan_voxel=0.1, knn=20, radius=1.0, map_voxel=0.15, min_move=0.0, period=2.0)
+    om.pose = poses[0].copy()
+    tc = []
+    for i in range(min(n_cpu, n_scans)):
+        t0 = time.perf_counter()
+        ok, st = om.add(scans[i], 0.1 * i, odom[i])
+        tc.append(time.perf_counter() - t0)
+        assert ok
+    tc = np.array(tc[1:])
+    print(f"CPU oracle composition (8 threads in kNN / normals / ICP), {len(tc)} scans: {1.0 / tc.mean():.2f} scans/s (mean {tc.mean()*1e3:.0f} ms)")
