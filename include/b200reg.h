@@ -224,6 +224,16 @@ int32_t b200reg_map_has_normals(const b200reg_map* map);
  * `volume` (helpers.cpp:117-192).  scan_xyz / scan_nrm: HOST fp64 arrays (nrm nullable). */
 int32_t b200reg_map_insert(b200reg_ctx* ctx, b200reg_map* map, const double* scan_xyz, const double* scan_nrm, int64_t n,
                            const double T_map_scan[16], const b200reg_crop_spec* volume);
+/* Space carving on the resident map: Submap::carve (open3d_slam/src/Submap.cpp:130-144) -> getIdxsOfCarvedPoints
+ * (helpers.cpp:245-281): the raw scan (HOST fp64, sensor frame) is moved into the map frame, every ray is sampled every
+ * voxel_size from the sensor up to max(voxel_size, min(length - truncation_distance, max_raytracing_length)), and every map point
+ * inside `volume` that shares a voxel with a sample is deleted unless the map has normals and |ray . normal| <=
+ * min_dot_product_with_normal.  The surviving points keep their order.  removed (nullable): number of deleted points. */
+typedef struct b200reg_carve_params {   /* SpaceCarvingParameters (Parameters.hpp:88-95) */
+  double voxel_size, max_raytracing_length, truncation_distance, min_dot_product_with_normal;
+} b200reg_carve_params;
+int32_t b200reg_map_carve(b200reg_ctx* ctx, b200reg_map* map, const double* scan_xyz, int64_t n, const double T_map_scan[16],
+                          const b200reg_crop_spec* volume, const b200reg_carve_params* params, int64_t* removed);
 /* ScanToMapRegistration::cropSubmap (open3d_slam/src/ScanToMapRegistration.cpp:90-96) + open3dToPointmatcher:
  * order-preserving crop of the resident map into a float cloud ready for b200reg_icp_set_reference. */
 int32_t b200reg_map_crop(b200reg_ctx* ctx, const b200reg_map* map, const b200reg_crop_spec* volume, b200reg_cloud** out);
@@ -259,6 +269,9 @@ int32_t b200reg_cloud64_to_f32(b200reg_ctx* ctx, const b200reg_cloud64* in, b200
 /* Submap::insertScan (Submap.cpp:39-96) with the scan already on the device */
 int32_t b200reg_map_insert_cloud64(b200reg_ctx* ctx, b200reg_map* map, const b200reg_cloud64* scan, const double T_map_scan[16],
                                    const b200reg_crop_spec* volume);
+/* b200reg_map_carve with the raw scan already on the device */
+int32_t b200reg_map_carve_cloud64(b200reg_ctx* ctx, b200reg_map* map, const b200reg_cloud64* scan, const double T_map_scan[16],
+                                  const b200reg_crop_spec* volume, const b200reg_carve_params* params, int64_t* removed);
 
 #ifdef __cplusplus
 }

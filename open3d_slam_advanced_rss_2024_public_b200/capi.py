@@ -58,6 +58,12 @@ class StepStats(C.Structure):
                 ("mean_reading", C.c_double * 3), ("mean_reference", C.c_double * 3)]
 
 
+class CarveParams(C.Structure):
+    """SpaceCarvingParameters (Parameters.hpp:88-95)"""
+    _fields_ = [("voxel_size", C.c_double), ("max_raytracing_length", C.c_double), ("truncation_distance", C.c_double),
+                ("min_dot_product_with_normal", C.c_double)]
+
+
 class IcpConfig(C.Structure):
     _fields_ = [("knn", C.c_int32), ("max_dist", C.c_float), ("epsilon", C.c_float), ("trim_ratio", C.c_float),
                 ("max_angle", C.c_float), ("force2D", C.c_int32), ("force4DOF", C.c_int32), ("max_iter", C.c_int32),
@@ -140,6 +146,8 @@ SYMBOLS = {
     "b200reg_cloud64_estimate_normals": (C.c_int32, [_VP, _VP, C.c_int32, C.c_double, _VP, C.POINTER(C.c_int32)]),
     "b200reg_cloud64_to_f32": (C.c_int32, [_VP, _VP, C.POINTER(_VP)]),
     "b200reg_map_insert_cloud64": (C.c_int32, [_VP, _VP, _VP, _VP, C.POINTER(CropSpec)]),
+    "b200reg_map_carve": (C.c_int32, [_VP, _VP, _VP, C.c_int64, _VP, C.POINTER(CropSpec), C.POINTER(CarveParams), C.POINTER(C.c_int64)]),
+    "b200reg_map_carve_cloud64": (C.c_int32, [_VP, _VP, _VP, _VP, C.POINTER(CropSpec), C.POINTER(CarveParams), C.POINTER(C.c_int64)]),
 }
 
 
@@ -567,6 +575,18 @@ class VoxelMap:
         xyz, nrm = _f64(scan_xyz), _f64(scan_nrm)
         T = _f64(T_map_scan).reshape(16)
         self.ctx.check(lib().b200reg_map_insert(self.ctx.h, self.h, _p(xyz), _p(nrm), xyz.shape[0], _p(T), C.byref(volume)))
+
+    def carve(self, scan, T_map_scan, volume, voxel_size=0.1, max_raytracing_length=20.0, truncation_distance=0.1, min_dot=0.5):
+        """Space carving (Submap::carve): scan = raw scan in the sensor frame, host fp64 array or a Cloud64.  Returns the removed count."""
+        T = _f64(T_map_scan).reshape(16)
+        cp = CarveParams(voxel_size, max_raytracing_length, truncation_distance, min_dot)
+        removed = C.c_int64(0)
+        if isinstance(scan, Cloud64):
+            self.ctx.check(lib().b200reg_map_carve_cloud64(self.ctx.h, self.h, scan.h, _p(T), C.byref(volume), C.byref(cp), C.byref(removed)))
+        else:
+            xyz = _f64(scan)
+            self.ctx.check(lib().b200reg_map_carve(self.ctx.h, self.h, _p(xyz), xyz.shape[0], _p(T), C.byref(volume), C.byref(cp), C.byref(removed)))
+        return removed.value
 
     def insert_cloud64(self, scan, T_map_scan, volume):
         T = _f64(T_map_scan).reshape(16)

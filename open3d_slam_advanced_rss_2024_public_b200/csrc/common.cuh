@@ -36,6 +36,7 @@ struct b200reg_ctx {
   int trace = 0;             // b200reg_ctx_set_trace: stamp kernel starts of the device-resident loop
   int select3 = 0;           // env B200REG_SELECT_3PASS=1: three-launch radix select inside the graph loop too (A/B)
   int hostLoop = 0;          // env B200REG_HOST_LOOP=1: keep the ICP iterate loop on the host (A/B against the graph loop)
+  int knnSeed = 1;           // env B200REG_KNN_SEED=0: do not seed the k = 1 match with the previous iteration's matches (A/B)
   int knnLanes = 0;          // lanes per query of the k = 1 match kernel: 0 automatic (8; the loop switches to 4 once far queries are rare),
                              // 8, 4, or 1 (the general kernel) forced by env B200REG_KNN_LANES for A/B runs
   void* pinned = nullptr;   // pinned host staging for small D2H results
@@ -108,7 +109,8 @@ struct IcpDevParams {   // written by the host once per registration
   int useTrim, useAngle, force2D, force4DOF;
   int maxIter, smoothLength;
   float minDiffRot, minDiffTrans, boundRot, boundTrans;
-  int lanesForced;             // 0: chosen per iteration from the far-query count
+  int lanesForced;
+  int seedOn;             // 0: chosen per iteration from the far-query count
   // fused trimmed-distance selection (nullable = filter off): the match kernel histograms the top 11 bits of d2 into fhist0
   unsigned* fhist0;            // 2048 bins, zero between iterations
   unsigned* fhist1;            // 2048 bins

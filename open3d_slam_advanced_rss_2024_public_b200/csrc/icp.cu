@@ -7,7 +7,8 @@
 #include "icp_kernels.cuh"
 
 int launchKnn1Loop(b200reg_ctx* ctx, const IcpDevParams* P, const IcpDevState* S, unsigned long long* counters, int blocks);
-int runKnn(b200reg_ctx* ctx, const b200reg_index* ix, const float4* queries, int64_t n, const float* T, int k, float maxDist, int allowSelf);
+int runKnn(b200reg_ctx* ctx, const b200reg_index* ix, const float4* queries, int64_t n, const float* T, int k, float maxDist, int allowSelf,
+           int seeded);
 int cloudStats(b200reg_ctx* ctx, const b200reg_cloud* c, double sum[3], float mn[3], float mx[3]);
 int buildIndex(b200reg_ctx* ctx, const b200reg_cloud* ref, const float mean[3], const float bbMin[3], const float bbMax[3], float cell,
                b200reg_index** out);
@@ -44,9 +45,9 @@ struct HostStep {   // what one iteration brings back over PCIe: NUM_MOM doubles
 
 // device part of one iteration: match -> select -> reduce -> async D2H into pinned memory (no sync here)
 int enqueueStep(b200reg_ctx* ctx, const b200reg_index* ix, const float4* reading, const float4* readingNrm, int64_t n, const float* T,
-                int k, float maxDist, float trimRatio, float maxAngle, int force2D) {
+                int k, float maxDist, float trimRatio, float maxAngle, int force2D, int seeded = 0) {
   if (!ix->nrm) return setErr(ctx, B200REG_E_INVALID_FIELD, "PointToPlaneErrorMinimizer: reference cloud has no 'normals' descriptor");
-  TRY(runKnn(ctx, ix, reading, n, T, k, maxDist, 1));
+  TRY(runKnn(ctx, ix, reading, n, T, k, maxDist, 1, (seeded && k == 1) ? 1 : 0));
   const int64_t total = n * k;
   SelState* st = selState(ctx);
   const bool useTrim = trimRatio > 0.f;
@@ -825,6 +826,7 @@ int32_t b200reg_icp_register(b200reg_icp* icp, const b200reg_cloud* reading, con
       hP->cand = (unsigned*)ctx->cand.p;
     }
     hP->lanesForced = (ctx->knnLanes == 4 || ctx->knnLanes == 8) ? ctx->knnLanes : 0;
+    hP->seedOn = ctx->knnSeed;
     hP->trace = ctx->trace ? (unsigned long long*)((char*)ctx->dstate + DSTATE_TRACE_OFF) : nullptr;
     if (ctx->trace) CUDA_TRY(ctx, cudaMemsetAsync((char*)ctx->dstate + DSTATE_TRACE_OFF, 0, sizeof(unsigned long long), ctx->stream));
     memset(hS, 0, sizeof(*hS));
@@ -871,7 +873,7 @@ int32_t b200reg_icp_register(b200reg_icp* icp, const b200reg_cloud* reading, con
   while (iterate) {
     if (!rigidOk(T_iter)) { status = setErr(ctx, B200REG_E_TRANSFORM, "RigidTransformation: Error, rotation matrix is not orthogonal."); break; }
     status = enqueueStep(ctx, icp->index, (const float4*)icp->reading.p, needNrm ? (const float4*)icp->readingNrm.p : nullptr, n, T_iter,
-                         cfg.knn, cfg.max_dist, cfg.trim_ratio, cfg.max_angle, cfg.force2D);
+                         cfg.knn, cfg.max_dist, cfg.trim_ratio, cfg.max_angle, cfg.force2D, st.iterations > 0 ? 1 : 0);
     if (status != B200REG_OK) break;
     cudaError_t e = cudaStreamSynchronize(ctx->stream);
     if (e != cudaSuccess) { status = setErr(ctx, B200REG_E_CUDA, "ICP iteration failed: %s", cudaGetErrorString(e)); break; }

@@ -239,8 +239,8 @@ __device__ __forceinline__ float ringLowerBound(const AxisGeom& ax, const AxisGe
 template <int G, bool SELFCHK>
 __device__ __forceinline__ void knn1Query(const float4* __restrict__ pts, const uint32_t* __restrict__ cellStart, const GridDesc& g,
                                           const float4* __restrict__ queries, int64_t n, int64_t qi, int hasT, const Rigid12& T, float maxd2,
-                                          int* __restrict__ outIds, float* __restrict__ outD2, int* __restrict__ outPos, unsigned& visits, unsigned& farQ,
-                                          unsigned* __restrict__ sHist) {
+                                          int* __restrict__ outIds, float* __restrict__ outD2, int* outPos, unsigned& visits, unsigned& farQ,
+                                          unsigned* __restrict__ sHist, const int* seedPos) {
   constexpr unsigned FULL = 0xffffffffu;
   constexpr int NR = 8 / G;   // non-centre rows owned by each lane
   const int lane = threadIdx.x & 31, l = lane & (G - 1), gbase = lane & (32 - G);
@@ -258,14 +258,28 @@ __device__ __forceinline__ void knn1Query(const float4* __restrict__ pts, const 
   // a candidate must beat (maxDist^2, index 0): d2 < maxDist^2 strictly, any index (NaN patterns sort above +inf and never win)
   const unsigned long long initKey = packKey(maxd2, 0);
   Best1 best{initKey, -1};
+  // Seed (iterations >= 2 of a registration): the point this query matched in the previous iteration, re-measured under the new
+  // transform.  It is an ordinary candidate (same key, same tie rule), so the result is unchanged — but the search starts with a
+  // bound that is usually the answer itself: rows beyond it are never fetched and the x range of the others shrinks to 1-2 cells.
+  if (seedPos && finite) {
+    const int sp = seedPos[qi];
+    if (sp >= 0) test1<SELFCHK>(ldPoint(pts + sp), (uint32_t)sp, q, selfId, best, visits);
+  }
+  const float bound0 = best.d();   // group-uniform; maxDist^2 without a seed
+  const bool tight = bound0 < g.ring2Safe;   // the bound lies inside the 3x3x3 neighbourhood: clip before fetching
 
-  // ---- rings 0 and 1: nine (y,z) rows, each the contiguous x range [cx-1, cx+1]
+  // ---- rings 0 and 1: nine (y,z) rows, each the contiguous x range [cx-1, cx+1] (clipped to the bound's reach when tight)
   uint32_t sC = 0, eC = 0, sL[NR], eL[NR];
   float lbL[NR];
 #pragma unroll
   for (int t = 0; t < NR; ++t) { sL[t] = 0; eL[t] = 0; lbL[t] = CUDART_INF_F; }
   {
-    const int xa = max(ax.c - 1, 0), xb = min(ax.c + 1, g.nx - 1);
+    int xa = max(ax.c - 1, 0), xb = min(ax.c + 1, g.nx - 1);
+    if (tight) {   // no point with d2 <= bound0 lies outside the cells of q.x -+ (sqrt(bound0) + slack): same argument as the shell walk below
+      const float reach = __fadd_rn(sqrtf(bound0), g.slack);
+      xa = max(xa, cellOfClamped(__fsub_rn(__fsub_rn(q.x, reach), g.slack), g.ox, g.inv_cell, g.nx));
+      xb = min(xb, cellOfClamped(__fadd_rn(__fadd_rn(q.x, reach), g.slack), g.ox, g.inv_cell, g.nx));
+    }
     if (finite && xa <= xb) {
       if ((unsigned)ay.c < (unsigned)g.ny && (unsigned)az.c < (unsigned)g.nz) {
         const uint32_t base = (uint32_t)g.nx * ((uint32_t)ay.c + (uint32_t)g.ny * (uint32_t)az.c);
@@ -278,10 +292,13 @@ __device__ __forceinline__ void knn1Query(const float4* __restrict__ pts, const 
         const int ri = rr + (rr >= 4 ? 1 : 0);
         const int iy = ay.c + (ri % 3) - 1, iz = az.c + (ri / 3) - 1;
         if ((unsigned)iy < (unsigned)g.ny && (unsigned)iz < (unsigned)g.nz) {
-          const uint32_t base = (uint32_t)g.nx * ((uint32_t)iy + (uint32_t)g.ny * (uint32_t)iz);
-          sL[t] = cellStart[base + xa];
-          eL[t] = cellStart[base + xb + 1];
-          lbL[t] = lb3(0.f, axisGap(ay, iy, g.cell, g.slack), axisGap(az, iz, g.cell, g.slack));
+          const float lb = lb3(0.f, axisGap(ay, iy, g.cell, g.slack), axisGap(az, iz, g.cell, g.slack));
+          if (!(lb > bound0)) {
+            const uint32_t base = (uint32_t)g.nx * ((uint32_t)iy + (uint32_t)g.ny * (uint32_t)iz);
+            sL[t] = cellStart[base + xa];
+            eL[t] = cellStart[base + xb + 1];
+            lbL[t] = lb;
+          }
         }
       }
     }
@@ -442,15 +459,15 @@ __device__ __forceinline__ void flushVisits(unsigned visits, unsigned farQ, unsi
 template <int G, bool SELFCHK>
 __global__ void __launch_bounds__(256) knn1GroupKernel(const float4* __restrict__ pts, const uint32_t* __restrict__ cellStart, GridDesc g,
                                                        const float4* __restrict__ queries, int64_t n, int hasT, Rigid12 T, float maxd2,
-                                                       int* __restrict__ outIds, float* __restrict__ outD2, int* __restrict__ outPos,
-                                                       unsigned long long* __restrict__ visitCounter) {
+                                                       int* __restrict__ outIds, float* __restrict__ outD2, int* outPos,
+                                                       unsigned long long* __restrict__ visitCounter, const int* seedPos) {
   constexpr int LOG2G = (G == 8) ? 3 : 2;
   __shared__ unsigned sVisits, sFarQ, sTicket;
   if (threadIdx.x == 0) { sVisits = 0; sFarQ = 0; sTicket = 0; }
   __syncthreads();   // all warps are at the start here: nobody waits on a straggler
   unsigned visits = 0, farQ = 0;
   const int64_t qi = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> LOG2G;
-  knn1Query<G, SELFCHK>(pts, cellStart, g, queries, n, qi, hasT, T, maxd2, outIds, outD2, outPos, visits, farQ, nullptr);
+  knn1Query<G, SELFCHK>(pts, cellStart, g, queries, n, qi, hasT, T, maxd2, outIds, outD2, outPos, visits, farQ, nullptr, seedPos);
   flushVisits(visits, farQ, &sVisits, &sFarQ, &sTicket, visitCounter);
 }
 
@@ -470,6 +487,7 @@ __device__ __forceinline__ void knn1LoopBody(const IcpDevParams* __restrict__ P,
   int* ids = P->ids;
   float* d2 = P->d2;
   int* pos = P->pos;
+  const int* seed = (P->seedOn && S->iterations > 0) ? P->pos : nullptr;   // the previous iteration's matches (same reference)
   Rigid12 T;
 #pragma unroll
   for (int j = 0; j < 12; ++j) T.m[j] = S->T[j];
@@ -477,7 +495,7 @@ __device__ __forceinline__ void knn1LoopBody(const IcpDevParams* __restrict__ P,
   const int64_t first = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> LOG2G;
   const int64_t blockFirst = ((int64_t)blockIdx.x * blockDim.x) >> LOG2G;
   for (int64_t base = 0; blockFirst + base < n; base += groupsPerGrid)   // trip count uniform over the block
-    knn1Query<G, false>(pts, cellStart, g, queries, n, first + base, 1, T, maxd2, ids, d2, pos, visits, farQ, sHist);
+    knn1Query<G, false>(pts, cellStart, g, queries, n, first + base, 1, T, maxd2, ids, d2, pos, visits, farQ, sHist, seed);
 }
 
 // S->lanes (written by the loop's tail from the previous iteration's far-query count) picks the decomposition: 8 lanes per
@@ -691,12 +709,12 @@ void launchKnnList(b200reg_ctx* ctx, const b200reg_index* ix, const float4* q, i
 }
 
 template <int G>
-void launchKnn1(b200reg_ctx* ctx, const b200reg_index* ix, const float4* q, int64_t n, int hasT, const Rigid12& T, float maxd2, int allowSelf, int* ids, float* d2, int* pos, unsigned long long* visits) {
+void launchKnn1(b200reg_ctx* ctx, const b200reg_index* ix, const float4* q, int64_t n, int hasT, const Rigid12& T, float maxd2, int allowSelf, int* ids, float* d2, int* pos, unsigned long long* visits, const int* seed) {
   const int blocks = divUp(n * G, 256);
   if (allowSelf)
-    knn1GroupKernel<G, false><<<blocks, 256, 0, ctx->stream>>>(ix->pts, ix->cellStart, ix->g, q, n, hasT, T, maxd2, ids, d2, pos, visits);
+    knn1GroupKernel<G, false><<<blocks, 256, 0, ctx->stream>>>(ix->pts, ix->cellStart, ix->g, q, n, hasT, T, maxd2, ids, d2, pos, visits, seed);
   else
-    knn1GroupKernel<G, true><<<blocks, 256, 0, ctx->stream>>>(ix->pts, ix->cellStart, ix->g, q, n, hasT, T, maxd2, ids, d2, pos, visits);
+    knn1GroupKernel<G, true><<<blocks, 256, 0, ctx->stream>>>(ix->pts, ix->cellStart, ix->g, q, n, hasT, T, maxd2, ids, d2, pos, visits, seed);
 }
 
 template <int K>
@@ -716,7 +734,10 @@ int launchKnn1Loop(b200reg_ctx* ctx, const IcpDevParams* P, const IcpDevState* S
 // Device-side entry shared with icp.cu / normals.cu.  Results land in ctx->matchIds / matchD2 / matchPos (k*n entries);
 // queries == nullptr (2 <= k <= 32 and the list kernel only): the index's own points, n == index size.
 // the touched-point counter is dstate[0] (unsigned long long), accumulated.
-int runKnn(b200reg_ctx* ctx, const b200reg_index* ix, const float4* queries, int64_t n, const float* T, int k, float maxDist, int allowSelf) {
+// seeded != 0 (k = 1 only): ctx->matchPos still holds the previous iteration's matches of the SAME queries against the SAME index;
+// they are re-measured and used as the starting bound (knn1Query).
+int runKnn(b200reg_ctx* ctx, const b200reg_index* ix, const float4* queries, int64_t n, const float* T, int k, float maxDist, int allowSelf,
+           int seeded) {
   if (k < 1 || k > 64) return setErr(ctx, B200REG_E_INVALID_PARAM, "knn: k = %d outside the supported range [1, 64]", k);
   if (!(maxDist >= 0.f)) return setErr(ctx, B200REG_E_INVALID_PARAM, "knn: maxDist must be >= 0");
   TRY(ensureBuf(ctx, ctx->matchIds, sizeof(int) * (size_t)k * n));
@@ -734,8 +755,9 @@ int runKnn(b200reg_ctx* ctx, const b200reg_index* ix, const float4* queries, int
   unsigned long long* visits = (unsigned long long*)ctx->dstate;
   const int hasT = T ? 1 : 0;
   profBegin(ctx);
-  if (k == 1 && (ctx->knnLanes == 8 || ctx->knnLanes == 0)) launchKnn1<8>(ctx, ix, queries, n, hasT, R, maxd2, allowSelf, ids, d2, pos, visits);
-  else if (k == 1 && ctx->knnLanes == 4) launchKnn1<4>(ctx, ix, queries, n, hasT, R, maxd2, allowSelf, ids, d2, pos, visits);
+  const int* seed = (seeded && ctx->knnSeed) ? pos : nullptr;
+  if (k == 1 && (ctx->knnLanes == 8 || ctx->knnLanes == 0)) launchKnn1<8>(ctx, ix, queries, n, hasT, R, maxd2, allowSelf, ids, d2, pos, visits, seed);
+  else if (k == 1 && ctx->knnLanes == 4) launchKnn1<4>(ctx, ix, queries, n, hasT, R, maxd2, allowSelf, ids, d2, pos, visits, seed);
   else if (k == 1) launchKnn<1>(ctx, ix, queries, n, hasT, R, k, maxd2, allowSelf, ids, d2, pos, visits);
   else if (k <= 8 && ctx->knnLanes != 1) launchKnnList<8>(ctx, ix, queries, n, hasT, R, k, maxd2, allowSelf, ids, d2, pos, visits);
   else if (k <= 16 && ctx->knnLanes != 1) launchKnnList<16>(ctx, ix, queries, n, hasT, R, k, maxd2, allowSelf, ids, d2, pos, visits);
@@ -758,7 +780,7 @@ extern "C" int32_t b200reg_knn(b200reg_ctx* ctx, const b200reg_index* index, con
   CUDA_TRY(ctx, cudaSetDevice(ctx->device));
   const int64_t n = query->n;
   CUDA_TRY(ctx, cudaMemsetAsync(ctx->dstate, 0, sizeof(unsigned long long), ctx->stream));
-  TRY(runKnn(ctx, index, query->xyz, n, T, k, max_dist, allow_self));
+  TRY(runKnn(ctx, index, query->xyz, n, T, k, max_dist, allow_self, 0));
   if (ids_out && n) CUDA_TRY(ctx, cudaMemcpyAsync(ids_out, ctx->matchIds.p, sizeof(int) * (size_t)k * n, cudaMemcpyDeviceToHost, ctx->stream));
   if (d2_out && n) CUDA_TRY(ctx, cudaMemcpyAsync(d2_out, ctx->matchD2.p, sizeof(float) * (size_t)k * n, cudaMemcpyDeviceToHost, ctx->stream));
   CUDA_TRY(ctx, cudaMemcpyAsync(ctx->pinned, ctx->dstate, sizeof(unsigned long long), cudaMemcpyDeviceToHost, ctx->stream));

@@ -395,6 +395,119 @@ int mapInsertDevice(b200reg_ctx* ctx, b200reg_map* map, const double* dIn, const
   return B200REG_OK;
 }
 
+__global__ void fillKernel(unsigned* __restrict__ a, int64_t n, unsigned v) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) a[i] = v;
+}
+
+// getIdxsOfCarvedPoints (helpers.cpp:245-281), one thread per scan ray.  The VoxelMap over the map points is the sorted
+// (key, index) table; a sampled position looks its voxel up by binary search.  Consecutive samples that fall into the same
+// voxel are looked up once (the reference inserts the same ids into a set again).  Removal = keep[id] <- 0 (idempotent).
+__global__ void carveRayKernel(const double* __restrict__ scan, int64_t n, double sx, double sy, double sz, const u64* __restrict__ skeys,
+                               const unsigned* __restrict__ svals, int64_t m, const double* __restrict__ nrm, double inv, double step,
+                               double maxRay, double trunc, double minDot, unsigned* __restrict__ keep) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const double d0 = scan[3 * i] - sx, d1 = scan[3 * i + 1] - sy, d2 = scan[3 * i + 2] - sz;
+  const double length = sqrt((d0 * d0 + d1 * d1) + d2 * d2);
+  const double dx = d0 / length, dy = d1 / length, dz = d2 / length;
+  const double lim = fmin(length - trunc, maxRay);          // std::min(length - truncation, maxRaytracingLength)
+  const double maxPath = (step < lim) ? lim : step;         // std::max(voxelSize, .)
+  double distance = 0.0;
+  u64 prev = ~0ull;
+  while (distance < maxPath) {
+    const double fx = floor((distance * dx + sx) * inv), fy = floor((distance * dy + sy) * inv), fz = floor((distance * dz + sz) * inv);
+    const double kl = 1048575.0;
+    if (fabs(fx) <= kl && fabs(fy) <= kl && fabs(fz) <= kl) {
+      const u64 key = ((u64)((long long)fx + 1048576ll) << 42) | ((u64)((long long)fy + 1048576ll) << 21) | (u64)((long long)fz + 1048576ll);
+      if (key != prev) {
+        prev = key;
+        int64_t lo = 0, hi = m;
+        while (lo < hi) {
+          const int64_t mid = (lo + hi) >> 1;
+          if (skeys[mid] < key) lo = mid + 1; else hi = mid;
+        }
+        for (int64_t t = lo; t < m && skeys[t] == key; ++t) {
+          const unsigned id = svals[t];
+          bool rm = true;
+          if (nrm) {
+            double nx = nrm[3 * (size_t)id], ny = nrm[3 * (size_t)id + 1], nz = nrm[3 * (size_t)id + 2];
+            const double n2 = (nx * nx + ny * ny) + nz * nz;
+            if (n2 > 0.0) { const double nn = sqrt(n2); nx /= nn; ny /= nn; nz /= nn; }   // Eigen normalized()
+            rm = fabs((dx * nx + dy * ny) + dz * nz) > minDot;
+          }
+          if (rm) keep[id] = 0u;
+        }
+      }
+    }
+    distance += step;
+  }
+}
+
+// Submap::carve (Submap.cpp:130-144) on the resident map; dScan: the raw scan in the sensor frame, device memory
+int carveDevice(b200reg_ctx* ctx, b200reg_map* map, const double* dScan, int64_t n, const double T_map_scan[16], const b200reg_crop_spec& volume,
+                const b200reg_carve_params& cp, int64_t* removed) {
+  *removed = 0;
+  const int64_t N = map->n;
+  if (N == 0 || n == 0) return B200REG_OK;
+  if (!(cp.voxel_size > 0.0)) return setErr(ctx, B200REG_E_INVALID_PARAM, "carve: voxel_size must be > 0");
+  const size_t u4 = sizeof(unsigned) * (size_t)N, k8 = sizeof(u64) * (size_t)N;
+  TRY(ensureBuf(ctx, ctx->flags, 4 * u4 + 64));
+  unsigned* inFlag = (unsigned*)ctx->flags.p;
+  unsigned* inOff = inFlag + N;
+  unsigned* keep = inOff + N;
+  unsigned* keepOff = keep + N;
+  TRY(ensureBuf(ctx, ctx->keys0, k8));
+  TRY(ensureBuf(ctx, ctx->keys1, k8));
+  TRY(ensureBuf(ctx, ctx->vals0, u4));
+  TRY(ensureBuf(ctx, ctx->vals1, u4));
+  TRY(ensureBuf(ctx, ctx->misc, k8 + sizeof(double) * 3 * (size_t)n + 64));
+  u64* keysAll = (u64*)ctx->misc.p;
+  double* dScanT = (double*)((char*)ctx->misc.p + ((k8 + 63) & ~(size_t)63));
+  double* dT = (double*)((char*)ctx->dstate + 40960);
+  int* dErr = (int*)((char*)ctx->dstate + 32768 + 64);
+  CUDA_TRY(ctx, cudaMemcpyAsync(dT, T_map_scan, sizeof(double) * 16, cudaMemcpyHostToDevice, ctx->stream));
+  CUDA_TRY(ctx, cudaMemsetAsync(dErr, 0, sizeof(int), ctx->stream));
+  transformF64Kernel<<<divUp(n, 256), 256, 0, ctx->stream>>>(dScan, nullptr, n, dT, dScanT, nullptr);   // o3d_slam::transform(mapToRangeSensor, rawScan)
+  LAUNCH_CHECK(ctx);
+  classifyKernel<<<divUp(N, 256), 256, 0, ctx->stream>>>(map->xyz, N, volume, 1.0 / cp.voxel_size, inFlag, nullptr, keysAll, dErr);   // getIndicesWithinVolume + getKey
+  LAUNCH_CHECK(ctx);
+  TRY(scanFlags(ctx, inFlag, inOff, N));
+  int64_t nIn = 0;
+  CUDA_TRY(ctx, cudaMemcpyAsync((int*)ctx->pinned + 8, dErr, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+  TRY(scanTotal(ctx, inFlag, inOff, N, &nIn));   // synchronises (T_map_scan may be reused by the caller)
+  if (((const int*)ctx->pinned)[8]) return setErr(ctx, B200REG_E_INVALID_PARAM, "carve: voxel index outside +-2^20 (voxel size too small for the map extent)");
+  if (nIn == 0) return B200REG_OK;
+  compactPairsKernel<<<divUp(N, 256), 256, 0, ctx->stream>>>(inFlag, inOff, keysAll, N, (u64*)ctx->keys0.p, (unsigned*)ctx->vals0.p);
+  LAUNCH_CHECK(ctx);
+  cub::DoubleBuffer<u64> dk((u64*)ctx->keys0.p, (u64*)ctx->keys1.p);
+  cub::DoubleBuffer<unsigned> dv((unsigned*)ctx->vals0.p, (unsigned*)ctx->vals1.p);
+  size_t tmp = 0;
+  CUDA_TRY(ctx, cub::DeviceRadixSort::SortPairs(nullptr, tmp, dk, dv, (int)nIn, 0, 63, ctx->stream));
+  TRY(ensureBuf(ctx, ctx->cubtmp, tmp));
+  tmp = ctx->cubtmp.cap;
+  CUDA_TRY(ctx, cub::DeviceRadixSort::SortPairs(ctx->cubtmp.p, tmp, dk, dv, (int)nIn, 0, 63, ctx->stream));
+  ctx->launches += 9;
+  fillKernel<<<divUp(N, 256), 256, 0, ctx->stream>>>(keep, N, 1u);
+  LAUNCH_CHECK(ctx);
+  carveRayKernel<<<divUp(n, 128), 128, 0, ctx->stream>>>(dScanT, n, T_map_scan[3], T_map_scan[7], T_map_scan[11], dk.Current(), dv.Current(), nIn,
+                                                         map->hasNormals ? map->nrm : nullptr, 1.0 / cp.voxel_size, cp.voxel_size,
+                                                         cp.max_raytracing_length, cp.truncation_distance, cp.min_dot_product_with_normal, keep);
+  LAUNCH_CHECK(ctx);
+  TRY(scanFlags(ctx, keep, keepOff, N));
+  int64_t kept = 0;
+  TRY(scanTotal(ctx, keep, keepOff, N, &kept));
+  if (kept == N) return B200REG_OK;   // removeByIds: nothing to remove (helpers.cpp:230-233)
+  scatterSelectedKernel<<<divUp(N, 256), 256, 0, ctx->stream>>>(keep, keepOff, N, map->xyz, map->hasNormals ? map->nrm : nullptr, map->xyz2,
+                                                                 map->hasNormals ? map->nrm2 : nullptr);
+  LAUNCH_CHECK(ctx);
+  double* t = map->xyz; map->xyz = map->xyz2; map->xyz2 = t;
+  t = map->nrm; map->nrm = map->nrm2; map->nrm2 = t;
+  map->n = kept;
+  *removed = N - kept;
+  return B200REG_OK;
+}
+
 // open3dToPointmatcher (open3d_conversions.cpp:57-118) and back: fp64 SoA-of-3 <-> float4 clouds
 __global__ void toF32Kernel(const double* __restrict__ xyz, const double* __restrict__ nrm, int64_t n, float4* __restrict__ oxyz, float4* __restrict__ onrm) {
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -452,6 +565,35 @@ int32_t b200reg_map_insert_cloud64(b200reg_ctx* ctx, b200reg_map* map, const b20
   if (scan->n == 0) return B200REG_OK;
   CUDA_TRY(ctx, cudaSetDevice(ctx->device));
   return mapInsertDevice(ctx, map, scan->xyz, scan->hasNormals ? scan->nrm : nullptr, scan->n, T_map_scan, *volume);
+}
+
+int32_t b200reg_map_carve(b200reg_ctx* ctx, b200reg_map* map, const double* scan_xyz, int64_t n, const double T_map_scan[16],
+                          const b200reg_crop_spec* volume, const b200reg_carve_params* params, int64_t* removed) {
+  if (!ctx || !map || n < 0 || (n > 0 && !scan_xyz) || !T_map_scan || !volume || !params) return setErr(ctx, B200REG_E_INVALID_PARAM, "map_carve: bad arguments");
+  int64_t r = 0;
+  if (removed) *removed = 0;
+  if (n == 0 || map->n == 0) return B200REG_OK;
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  double* dIn = nullptr;
+  CUDA_TRY(ctx, devAlloc(ctx, &dIn, sizeof(double) * 3 * (size_t)n));
+  cudaError_t e = cudaMemcpyAsync(dIn, scan_xyz, sizeof(double) * 3 * (size_t)n, cudaMemcpyHostToDevice, ctx->stream);
+  int code = (e == cudaSuccess) ? carveDevice(ctx, map, dIn, n, T_map_scan, *volume, *params, &r) : setErr(ctx, B200REG_E_CUDA, "map_carve: %s", cudaGetErrorString(e));
+  cudaStreamSynchronize(ctx->stream);   // the host scan may be reused
+  devFree(ctx, dIn);
+  if (removed) *removed = r;
+  return code;
+}
+
+int32_t b200reg_map_carve_cloud64(b200reg_ctx* ctx, b200reg_map* map, const b200reg_cloud64* scan, const double T_map_scan[16],
+                                  const b200reg_crop_spec* volume, const b200reg_carve_params* params, int64_t* removed) {
+  if (!ctx || !map || !scan || !T_map_scan || !volume || !params) return setErr(ctx, B200REG_E_INVALID_PARAM, "map_carve_cloud64: bad arguments");
+  int64_t r = 0;
+  if (removed) *removed = 0;
+  if (scan->n == 0 || map->n == 0) return B200REG_OK;
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  const int code = carveDevice(ctx, map, scan->xyz, scan->n, T_map_scan, *volume, *params, &r);
+  if (removed) *removed = r;
+  return code;
 }
 
 int32_t b200reg_map_crop(b200reg_ctx* ctx, const b200reg_map* map, const b200reg_crop_spec* volume, b200reg_cloud** out) {

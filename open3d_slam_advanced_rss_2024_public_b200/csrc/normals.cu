@@ -9,7 +9,8 @@
 
 #include "common.cuh"
 
-int runKnn(b200reg_ctx* ctx, const b200reg_index* ix, const float4* queries, int64_t n, const float* T, int k, float maxDist, int allowSelf);
+int runKnn(b200reg_ctx* ctx, const b200reg_index* ix, const float4* queries, int64_t n, const float* T, int k, float maxDist, int allowSelf,
+           int seeded);
 int cloudStats(b200reg_ctx* ctx, const b200reg_cloud* c, double sum[3], float mn[3], float mx[3]);
 int buildIndex(b200reg_ctx* ctx, const b200reg_cloud* ref, const float mean[3], const float bbMin[3], const float bbMax[3], float cell,
                b200reg_index** out);
@@ -189,7 +190,7 @@ extern "C" int32_t b200reg_surface_normals(b200reg_ctx* ctx, b200reg_cloud* inou
   TRY(buildIndex(ctx, inout, zero, mn, mx, 0.f, &ix));
   // the list kernel walks the cloud in the index's sorted order (null queries); the one-thread kernel takes it as it lies
   const float4* qs = (ctx->knnLanes == 1 || knn > 32) ? inout->xyz : nullptr;
-  int st = runKnn(ctx, ix, qs, n, nullptr, knn, max_dist, 1);
+  int st = runKnn(ctx, ix, qs, n, nullptr, knn, max_dist, 1, 0);
   if (st != B200REG_OK) { b200reg_index_free(ctx, ix); return st; }
   if (!inout->nrm) {
     cudaError_t e = devAlloc(ctx, &inout->nrm, sizeof(float4) * (size_t)inout->cap);

@@ -62,6 +62,7 @@ Mapper::Mapper(b200reg_ctx* ctx, const MapperParams& params) : ctx_(ctx), params
   identity(mapToRangeSensorPrev_);
   identity(lastInsertion_);
   identity(odomPrev_);
+  identity(cropperPose_);
   if (b200reg_map_create(ctx_, params_.mapVoxelSize, &map_) != B200REG_OK) error_ = b200reg_last_error(ctx_);
   if (b200reg_icp_create(ctx_, &params_.icp, &icp_) != B200REG_OK) error_ = b200reg_last_error(ctx_);
 }
@@ -119,11 +120,23 @@ bool Mapper::process(const double* xyz, const double* normals, int64_t n) {
 // Submap::insertScan (Submap.cpp:39-96) without carving: transform, append, re-voxelise inside the map-builder volume at the pose
 bool Mapper::insert() {
   StageClock clk;
+  // carve(rawScan, mapToRangeSensor, *mapBuilderCropper_, carving_, &mapCloud_) (Submap.cpp:56-60,130-144): every N-th inserted scan,
+  // with the cropper still at the pose of the previous insertion
+  if (params_.carvingEnabled && b200reg_map_size(map_) > 0 && params_.carveSpaceEveryNscans > 0 &&
+      nScansInsertedMap_ % params_.carveSpaceEveryNscans == 0) {
+    const b200reg_crop_spec carveVol = at(params_.mapBuilderCropper, cropperPose_);
+    if (b200reg_map_carve_cloud64(ctx_, map_, raw_, mapToRangeSensor_, &carveVol, &params_.carving, &stats_.carvedPoints) != B200REG_OK) {
+      error_ = b200reg_last_error(ctx_);
+      return false;
+    }
+  }
   const b200reg_crop_spec vol = at(params_.mapBuilderCropper, mapToRangeSensor_);
   if (b200reg_map_insert_cloud64(ctx_, map_, merge_, mapToRangeSensor_, &vol) != B200REG_OK) {
     error_ = b200reg_last_error(ctx_);
     return false;
   }
+  std::memcpy(cropperPose_, mapToRangeSensor_, sizeof(cropperPose_));   // mapBuilderCropper_->setPose(mapToRangeSensor) (Submap.cpp:86)
+  ++nScansInsertedMap_;
   clk.lap(&stats_.stageMs[MapperStepStats::kInsert]);
   return true;
 }

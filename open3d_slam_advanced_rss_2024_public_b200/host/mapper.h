@@ -12,7 +12,7 @@
 //   corrected         =  icp.compute(reading, {}, estimate, false); a runtime_error keeps the estimate  :388-422
 //   insert only if the sensor moved >= minMovementBetweenMappingSteps since the last insertion     :483-489
 //                        Submap::insertScan: transform, append, re-voxelise inside the cropping volume  Submap.cpp:39-96
-// Out of this driver: space carving, submap switching, the odometry time buffer (the caller hands the
+// Out of this driver: submap switching, the odometry time buffer (the caller hands the
 // odometry pose of each scan), RandomDownSample (ratio 1 only — the reference itself requires that for reproducibility,
 // ScanToMapRegistration.cpp:43), the initial-map mode, motion compensation.
 #pragma once
@@ -35,6 +35,10 @@ struct MapperParams {
   double mapVoxelSize = 0.15;
   double minMovementBetweenMappingSteps = 0.0;   // Mapper.cpp:483-485
   double referenceCloudSettingPeriod = 2.0;      // seconds of sensor time, Mapper.cpp:345-349
+  // space carving (Submap.cpp:56-60,130-144; map_builder.space_carving.*): off by default like Parameters.hpp:181
+  bool carvingEnabled = false;
+  int carveSpaceEveryNscans = 10;
+  b200reg_carve_params carving{0.1, 20.0, 0.1, 0.5};
   // ICP chain (param/icp.yaml)
   b200reg_icp_config icp{};
 };
@@ -44,7 +48,7 @@ struct MapperStepStats {
   int32_t icpStatus = 0;          // b200reg status of the registration (non-zero: the estimate was kept, Mapper.cpp:420-422)
   int32_t referenceRefreshed = 0;
   int32_t inserted = 0;
-  int64_t readingPoints = 0, mergePoints = 0, patchPoints = 0, mapPoints = 0;
+  int64_t readingPoints = 0, mergePoints = 0, patchPoints = 0, mapPoints = 0, carvedPoints = 0;
   // host wall time per stage (every stage ends in a synchronising call): wide crop, voxelise, normals, narrow crop,
   // reading upload, map-patch crop, initReference, registration, insertion
   enum { kWideCrop, kVoxelize, kNormals, kNarrowCrop, kUpload, kPatch, kReference, kRegister, kInsert, kStages };
@@ -81,6 +85,8 @@ class Mapper {
   b200reg_cloud* reading_ = nullptr;   // fp32 DataPoints mirror of match_ (open3dToPointmatcher on the device)
   b200reg_cloud64 *raw_ = nullptr, *cropped_ = nullptr, *merge_ = nullptr, *match_ = nullptr;
   double mapToRangeSensor_[16], mapToRangeSensorPrev_[16], lastInsertion_[16], odomPrev_[16];
+  double cropperPose_[16];             // mapBuilderCropper_'s pose: set AFTER each insertion (Submap.cpp:86), so carving sees the previous one
+  int64_t nScansInsertedMap_ = 0;
   bool haveOdomPrev_ = false, referenceSet_ = false;
   double lastReferenceInit_ = 0.0;
   MapperStepStats stats_;

@@ -196,12 +196,15 @@ typedef struct b200map_params {   // flat mirror of b200::MapperParams for ctype
   double scan_voxel_size, normals_radius, map_voxel_size, min_movement, reference_period;
   int32_t normals_knn, pad;
   b200reg_icp_config icp;
+  int32_t carving_enabled, carve_every;
+  b200reg_carve_params carving;
 } b200map_params;
 
 typedef struct b200map_stats {
   int32_t iterations, icp_status, reference_refreshed, inserted;
   int64_t reading_points, merge_points, patch_points, map_points;
   double stage_ms[9];   // MapperStepStats::stageMs
+  int64_t carved_points;
 } b200map_stats;
 
 void* b200map_create(b200reg_ctx* ctx, const b200map_params* p) {
@@ -216,6 +219,9 @@ void* b200map_create(b200reg_ctx* ctx, const b200map_params* p) {
   mp.minMovementBetweenMappingSteps = p->min_movement;
   mp.referenceCloudSettingPeriod = p->reference_period;
   mp.icp = p->icp;
+  mp.carvingEnabled = p->carving_enabled != 0;
+  mp.carveSpaceEveryNscans = p->carve_every;
+  mp.carving = p->carving;
   return new b200::Mapper(ctx, mp);
 }
 void b200map_destroy(void* m) { delete (b200::Mapper*)m; }
@@ -229,6 +235,7 @@ int32_t b200map_add_range_measurement(void* m, const double* xyz, const double* 
     const b200::MapperStepStats& s = mp->lastStats();
     *stats = b200map_stats{s.iterations, s.icpStatus, s.referenceRefreshed, s.inserted, s.readingPoints, s.mergePoints, s.patchPoints, s.mapPoints, {}};
     for (int i = 0; i < b200::MapperStepStats::kStages; ++i) stats->stage_ms[i] = s.stageMs[i];
+    stats->carved_points = s.carvedPoints;
   }
   setMsg(err, err_cap, mp->lastError());
   return ok ? 1 : 0;

@@ -10,13 +10,14 @@ from . import capi, pm_shim
 class MapperParams(C.Structure):
     _fields_ = [("map_builder_cropper", capi.CropSpec), ("scan_matcher_cropper", capi.CropSpec), ("scan_voxel_size", C.c_double),
                 ("normals_radius", C.c_double), ("map_voxel_size", C.c_double), ("min_movement", C.c_double),
-                ("reference_period", C.c_double), ("normals_knn", C.c_int32), ("pad", C.c_int32), ("icp", capi.IcpConfig)]
+                ("reference_period", C.c_double), ("normals_knn", C.c_int32), ("pad", C.c_int32), ("icp", capi.IcpConfig),
+                ("carving_enabled", C.c_int32), ("carve_every", C.c_int32), ("carving", capi.CarveParams)]
 
 
 class MapperStats(C.Structure):
     _fields_ = [("iterations", C.c_int32), ("icp_status", C.c_int32), ("reference_refreshed", C.c_int32), ("inserted", C.c_int32),
                 ("reading_points", C.c_int64), ("merge_points", C.c_int64), ("patch_points", C.c_int64), ("map_points", C.c_int64),
-                ("stage_ms", C.c_double * 9)]
+                ("stage_ms", C.c_double * 9), ("carved_points", C.c_int64)]
 
     STAGES = ("wide_crop", "voxelize", "normals", "narrow_crop", "upload", "patch_crop", "init_reference", "register", "insert")
 
@@ -41,11 +42,14 @@ class Mapper:
     """One active submap, no carving: see host/mapper.h for what is mirrored and what is left out."""
 
     def __init__(self, ctx, map_builder_cropper, scan_matcher_cropper, icp_cfg, scan_voxel_size=0.1, normals_knn=20, normals_radius=1.0,
-                 map_voxel_size=0.15, min_movement=0.0, reference_period=2.0):
+                 map_voxel_size=0.15, min_movement=0.0, reference_period=2.0, carving=None, carve_every=10):
+        """carving: None (off, the reference's default) or a capi.CarveParams."""
         self.ctx = ctx
         self.params = MapperParams(map_builder_cropper=map_builder_cropper, scan_matcher_cropper=scan_matcher_cropper,
                                    scan_voxel_size=scan_voxel_size, normals_radius=normals_radius, map_voxel_size=map_voxel_size,
-                                   min_movement=min_movement, reference_period=reference_period, normals_knn=normals_knn, pad=0, icp=icp_cfg)
+                                   min_movement=min_movement, reference_period=reference_period, normals_knn=normals_knn, pad=0, icp=icp_cfg,
+                                   carving_enabled=0 if carving is None else 1, carve_every=carve_every,
+                                   carving=carving if carving is not None else capi.CarveParams(0.1, 20.0, 0.1, 0.5))
         self.h = _lib().b200map_create(ctx.h, C.byref(self.params))
         if not self.h:
             raise RuntimeError("b200map_create failed")

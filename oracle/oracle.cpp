@@ -1340,4 +1340,54 @@ void orc_o3d_to_pm(const double* xyz, const double* nrm, int64_t n, float* feat4
   }
 }
 
+// Space carving on the map cloud: Submap::carve (src/Submap.cpp:130-144) -> getIdxsOfCarvedPoints (src/helpers.cpp:245-281).
+// The map points inside `spec` are binned into a VoxelMap with key = int(floor(p * (1/voxel))) (Voxel.cpp:122-128,
+// VoxelHashMap.hpp:48-51,127); every scan ray (scan already in the map frame) is sampled at distance = 0, step, 2 step, ...
+// < max(voxel, min(length - truncation, maxRaytracingLength)) with `distance += stepSize` accumulation (:254-277); every map
+// point in a sampled voxel is removed if the cloud has no normals or |direction . normal.normalized()| > minDot (:264-269).
+// Output: remove_mask[i] = 1 for removed map points (the reference's unordered id set + SelectByIndex(invert) keeps the rest in
+// order, helpers.cpp:230-236).  Returns the number of removed points.
+int64_t orc_carve(const double* scan_xyz, int64_t n_scan, const double sensor[3], const double* map_xyz, const double* map_nrm,
+                  int64_t n_map, const orc_crop_spec* spec, double voxel, double max_ray_length, double truncation, double min_dot,
+                  uint8_t* remove_mask) {
+  const double inv = 1.0 / voxel;
+  std::map<Key, std::vector<int64_t>> vox;
+  for (int64_t i = 0; i < n_map; ++i) {
+    remove_mask[i] = 0;
+    const double* p = map_xyz + 3 * i;
+    if (!withinVolume(*spec, p)) continue;   // cropper.getIndicesWithinVolume(*map) (Submap.cpp:138)
+    vox[Key((int)std::floor(p[0] * inv), (int)std::floor(p[1] * inv), (int)std::floor(p[2] * inv))].push_back(i);
+  }
+  for (int64_t i = 0; i < n_scan; ++i) {
+    const double* p = scan_xyz + 3 * i;
+    const double d0 = p[0] - sensor[0], d1 = p[1] - sensor[1], d2 = p[2] - sensor[2];
+    const double length = std::sqrt((d0 * d0 + d1 * d1) + d2 * d2);
+    const double dir[3] = {d0 / length, d1 / length, d2 / length};
+    const double maxPath = std::max(voxel, std::min(length - truncation, max_ray_length));
+    double distance = 0.0;
+    while (distance < maxPath) {
+      const double c[3] = {distance * dir[0] + sensor[0], distance * dir[1] + sensor[1], distance * dir[2] + sensor[2]};
+      const auto it = vox.find(Key((int)std::floor(c[0] * inv), (int)std::floor(c[1] * inv), (int)std::floor(c[2] * inv)));
+      if (it != vox.end()) {
+        for (const int64_t id : it->second) {
+          bool rm = true;
+          if (map_nrm) {
+            const double* a = map_nrm + 3 * id;
+            const double n2 = (a[0] * a[0] + a[1] * a[1]) + a[2] * a[2];   // Eigen normalized(): v / sqrt(squaredNorm) when > 0
+            double nx = a[0], ny = a[1], nz = a[2];
+            if (n2 > 0.0) { const double nn = std::sqrt(n2); nx /= nn; ny /= nn; nz /= nn; }
+            rm = std::fabs((dir[0] * nx + dir[1] * ny) + dir[2] * nz) > min_dot;
+          }
+          if (rm) remove_mask[id] = 1;
+        }
+      }
+      distance += voxel;
+    }
+  }
+  int64_t removed = 0;
+  for (int64_t i = 0; i < n_map; ++i) removed += remove_mask[i];
+  return removed;
+}
+
+
 }  // extern "C"

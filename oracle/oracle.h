@@ -118,6 +118,9 @@ void    orc_transform_f64(const double T[16], const double* xyz, const double* n
 int64_t orc_voxelize_within_volume(double voxel, const orc_crop_spec* spec, const double* xyz, const double* nrm, int64_t n,
                                    double* xyz_out, double* nrm_out, int64_t* n_passthrough);   /* helpers.cpp:117-192; output = pass-through, then voxels in ascending (x,y,z) key order */
 int64_t orc_voxel_down_sample(double voxel, const double* xyz, const double* nrm, int64_t n, double* xyz_out, double* nrm_out); /* Open3D v0.15.1 VoxelDownSample, ascending key order */
+int64_t orc_carve(const double* scan_xyz, int64_t n_scan, const double sensor[3], const double* map_xyz, const double* map_nrm,
+                  int64_t n_map, const orc_crop_spec* spec, double voxel, double max_ray_length, double truncation, double min_dot,
+                  uint8_t* remove_mask);   /* Submap.cpp:130-144 + helpers.cpp:245-281; scan already in the map frame */
 void    orc_o3d_to_pm(const double* xyz, const double* nrm, int64_t n, float* feat4, float* nrm3);   /* open3d_conversions.cpp:57-118 */
 
 #ifdef __cplusplus

@@ -301,6 +301,18 @@ def voxelize_within_volume(voxel, spec, xyz, nrm=None):
     return xo[:m], (None if no is None else no[:m]), npass.value
 
 
+def carve(scan_xyz, sensor, map_xyz, map_nrm, spec, voxel=0.1, max_ray_length=20.0, truncation=0.1, min_dot=0.5):
+    """Space carving (Submap.cpp:130-144, helpers.cpp:245-281): boolean mask of the map points to remove; scan in the map frame."""
+    scan_xyz, map_xyz, map_nrm, sensor = _f64(scan_xyz), _f64(map_xyz), _f64(map_nrm), _f64(sensor)
+    mask = np.zeros(map_xyz.shape[0], dtype=np.uint8)
+    lib().orc_carve.restype = C.c_int64
+    lib().orc_carve.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_double, C.c_double,
+                                C.c_double, C.c_double, C.c_void_p]
+    lib().orc_carve(_p(scan_xyz), scan_xyz.shape[0], _p(sensor), _p(map_xyz), _p(map_nrm), map_xyz.shape[0], C.byref(spec), voxel,
+                    max_ray_length, truncation, min_dot, _p(mask))
+    return mask.astype(bool)
+
+
 def voxel_down_sample(voxel, xyz, nrm=None):
     xyz, nrm = _f64(xyz), _f64(nrm)
     xo = np.empty_like(xyz)

@@ -212,3 +212,56 @@ def test_map_insert_without_normals_and_upload_f64(ctx, oracle):
     f_o, _ = oracle.o3d_to_pm(xyz)
     f_g, _ = ctx.upload(xyz).download()
     assert np.array_equal(f_g.view(np.uint32), f_o.view(np.uint32))
+
+
+@pytest.mark.parametrize("with_normals", [True, False])
+def test_map_carve_matches_oracle(ctx, oracle, with_normals):
+    """Space carving on the resident map (Submap::carve -> getIdxsOfCarvedPoints): a map built from two scans, with a block of
+    'ghost' points dropped into free space, carved by a third scan through b200reg_map_carve (host scan) and
+    b200reg_map_carve_cloud64 (device scan): the surviving map must equal the oracle's mask applied to the same map, bit for bit
+    and in order; carving twice with the same scan removes nothing new."""
+    from open3d_slam_advanced_rss_2024_public_b200 import capi
+    sc = scenes.Scene(91, size=(40.0, 30.0, 6.0), n_boxes=10, n_cyl=6, keepout=[[10 + i, 12.0] for i in range(6)])
+    voxel = 0.15
+    rng = np.random.default_rng(9)
+    maps = []
+    for mode in ("host", "cloud64"):
+        m = capi.VoxelMap(ctx, voxel)
+        for i in range(2):
+            pose = scenes.rigid(scenes.rot_axis_angle([0, 0, 1], 0.3 * i), [10.0 + 1.5 * i, 12.0, 1.5])
+            scan = scenes.lidar_scan(sc, pose, 32, 256, 0.01, seed=300 + i)
+            c32 = ctx.upload(scan.astype(np.float64))
+            c32.surface_normals(10, max_dist=1.0, orient_origin=np.zeros(3, np.float32))
+            sn = c32.download()[1].astype(np.float64) if with_normals else None
+            _, sg = _spec_pair(oracle, 0, pose[:3, 3], rmax=25.0)
+            m.insert(scan, sn, pose, sg)
+        ghost = np.array([13.0, 12.5, 1.0]) + np.random.default_rng(10).uniform(-0.4, 0.4, (400, 3))   # a departed object in free space
+        gn = np.tile([-1.0, 0.0, 0.0], (400, 1)) if with_normals else None
+        _, far_vol = _spec_pair(oracle, 0, [1e3, 0, 0], rmax=1.0)                                          # nothing inside: plain append + no re-voxelisation
+        m.insert(ghost, gn, np.eye(4), far_vol)
+        before_x, before_n = m.download()
+        pose = scenes.rigid(scenes.rot_axis_angle([0, 0, 1], 0.1), [11.0, 12.2, 1.5])
+        raw = scenes.lidar_scan(sc, pose, 32, 256, 0.01, seed=310).astype(np.float64)
+        so, sg = _spec_pair(oracle, 0, [10.5, 12.0, 1.5], rmax=12.0)                                        # cropper still at the previous insertion's pose
+        kw = dict(voxel_size=0.1, max_raytracing_length=15.0, truncation_distance=0.2, min_dot=0.4)
+        removed = m.carve(raw if mode == "host" else capi.Cloud64.upload(ctx, raw), pose, sg, **kw)
+        tx, _ = oracle.transform_f64(pose, raw, None)
+        mask = oracle.carve(tx, pose[:3, 3], before_x, before_n, so, voxel=0.1, max_ray_length=15.0, truncation=0.2, min_dot=0.4)
+        after_x, after_n = m.download()
+        assert removed == int(mask.sum()) and removed > 100, (mode, removed, int(mask.sum()))
+        assert np.array_equal(after_x, before_x[~mask])
+        if with_normals:
+            assert np.array_equal(after_n, before_n[~mask])
+        ghost_rows = (np.abs(before_x - np.array([13.0, 12.5, 1.0])) <= 0.4).all(axis=1)
+        assert mask[ghost_rows].mean() > 0.5                      # most of the departed object is gone
+        assert m.carve(raw, pose, sg, **kw) == 0                   # idempotent
+        maps.append(after_x)
+        m.close()
+    assert np.array_equal(maps[0], maps[1])
+    # parameter check and empty inputs
+    m = capi.VoxelMap(ctx, voxel)
+    assert m.carve(raw, pose, sg) == 0                             # empty map: nothing to do (Submap.cpp:132)
+    m.insert(raw[:100], None, pose, sg)
+    assert m.carve(np.zeros((0, 3)), pose, sg) == 0
+    with pytest.raises(capi.InvalidParameter):
+        m.carve(raw, pose, sg, voxel_size=0.0)

@@ -36,8 +36,9 @@ def drifting_odometry(poses, seed):
 class OracleMapper:
     """The same control flow as host/mapper.cpp, composed from oracle calls (CPU)."""
 
-    def __init__(self, O, wide, narrow, icp_kw, scan_voxel, knn, radius, map_voxel, min_move, period):
+    def __init__(self, O, wide, narrow, icp_kw, scan_voxel, knn, radius, map_voxel, min_move, period, carving=None, carve_every=10):
         self.O, self.wide, self.narrow, self.icp_kw = O, wide, narrow, icp_kw
+        self.carving, self.carve_every, self.n_inserted, self.cropper_pose, self.carved = carving, carve_every, 0, None, 0
         self.scan_voxel, self.knn, self.radius, self.map_voxel, self.min_move, self.period = scan_voxel, knn, radius, map_voxel, min_move, period
         self.pose = np.eye(4)
         self.prev = np.eye(4)
@@ -64,6 +65,13 @@ class OracleMapper:
 
     def insert(self, mx, mn):
         O = self.O
+        self.carved = 0
+        if self.carving is not None and self.map_xyz.shape[0] > 0 and self.n_inserted % self.carve_every == 0:   # Submap.cpp:56-60,130-144
+            sx, _ = O.transform_f64(self.pose, self.raw, None)
+            mask = O.carve(sx, self.pose[:3, 3], self.map_xyz, self.map_nrm, self.spec(self.wide, self.cropper_pose), **self.carving)
+            self.map_xyz, self.map_nrm, self.carved = self.map_xyz[~mask], self.map_nrm[~mask], int(mask.sum())
+        self.cropper_pose = self.pose.copy()
+        self.n_inserted += 1
         tx, tn = O.transform_f64(self.pose, mx, mn)
         allx = np.concatenate([self.map_xyz, tx])
         alln = np.concatenate([self.map_nrm, tn])
@@ -71,6 +79,7 @@ class OracleMapper:
 
     def add(self, xyz, time, odom):
         O = self.O
+        self.raw = xyz
         st = dict(inserted=0, refreshed=0, iterations=0, code=0)
         if self.map_xyz.shape[0] == 0:
             self.prev = self.pose.copy()
@@ -225,3 +234,44 @@ def test_cloud64_chain_equals_host_array_chain(ctx):
     # empty results and reuse of an emptied cloud
     none = merge.crop(capi.crop_spec(capi.CROP_MAX_RADIUS, np.array([1e4, 0, 0]), rmax=1.0), out=match)
     assert none.size == 0 and none.download()[0].shape == (0, 3)
+
+
+def test_mapping_loop_with_space_carving(ctx, oracle):
+    """The mapping loop with carving every 2nd inserted scan (param_replay.lua enables it): a block of ghost points is planted into
+    both maps' first scan; carved counts, map sizes and poses must follow the oracle composition step by step."""
+    from open3d_slam_advanced_rss_2024_public_b200 import capi
+    from open3d_slam_advanced_rss_2024_public_b200.mapper import Mapper
+    O = oracle
+    scene = scenes.Scene(2001, size=(40.0, 24.0, 8.0), n_boxes=14, n_cyl=8)
+    poses = trajectory(9)
+    odom = drifting_odometry(poses, 2004)
+    wide = dict(kind=capi.CROP_MINMAX_RADIUS, rmin=1.0, rmax=30.0)
+    narrow = dict(kind=capi.CROP_MAX_RADIUS, rmax=25.0)
+    icp_kw = dict(knn=1, max_dist=0.5, trim_ratio=0.9, max_angle=1.57, max_iter=15, min_diff_rot=1e-3, min_diff_trans=1e-2, smooth_length=3)
+    kw = dict(scan_voxel=0.25, knn=10, radius=1.0, map_voxel=0.3, min_move=0.0, period=0.35)
+    carve_o = dict(voxel=0.3, max_ray_length=12.0, truncation=0.3, min_dot=0.3)
+    om = OracleMapper(O, wide, narrow, icp_kw, carving=carve_o, carve_every=2, **kw)
+    gm = Mapper(ctx, capi.crop_spec(wide["kind"], np.zeros(3), rmin=wide["rmin"], rmax=wide["rmax"]),
+                capi.crop_spec(narrow["kind"], np.zeros(3), rmax=narrow["rmax"]), capi.icp_config(**icp_kw),
+                scan_voxel_size=kw["scan_voxel"], normals_knn=kw["knn"], normals_radius=kw["radius"], map_voxel_size=kw["map_voxel"],
+                min_movement=kw["min_move"], reference_period=kw["period"], carving=capi.CarveParams(0.3, 12.0, 0.3, 0.3), carve_every=2)
+    om.pose = poses[0].copy()
+    gm.set_pose(poses[0])
+    total_carved = 0
+    for i, (T, od) in enumerate(zip(poses, odom)):
+        scan = scenes.lidar_scan(scene, T, n_beams=32, n_az=360, noise_sigma=0.01, seed=700 + i).astype(np.float64)
+        if i == 0:   # a parked object 3 m ahead of the first pose that is gone afterwards (sensor-frame points)
+            obj = np.array([3.0, 0.0, -0.6]) + np.random.default_rng(1).uniform(-0.5, 0.5, (600, 3)) * np.array([0.1, 1.0, 1.0])
+            scan = np.concatenate([scan, obj])
+        ok_o, st_o = om.add(scan, 0.1 * i, od)
+        ok_g, pose_g, st_g, err = gm.add_range_measurement(scan, 0.1 * i, od)
+        assert ok_o and ok_g, err
+        assert st_g.carved_points == om.carved, (i, st_g.carved_points, om.carved)
+        assert st_g.map_points == st_o["map"], (i, st_g.map_points, st_o["map"])
+        total_carved += om.carved
+        d = np.linalg.inv(om.pose) @ pose_g
+        assert np.abs(d[:3, 3]).max() < 1e-4 and np.linalg.norm(d[:3, :3] - np.eye(3)) < 1e-4, i
+    assert total_carved > 20
+    gx, _ = gm.map_points()
+    assert gx.shape[0] == om.map_xyz.shape[0] and np.abs(gx - om.map_xyz).max() < 2e-4
+    gm.close()

@@ -266,3 +266,55 @@ def test_transform_and_determinant_check(oracle):
     bad[:3, :3] *= 1.01
     st, _, _ = oracle.transform(bad, pts)
     assert st == -2      # TransformationError (TransformationsImpl.cpp:74)
+
+
+def test_space_carving_known_answers(oracle):
+    """orc_carve against hand-derived answers for getIdxsOfCarvedPoints (helpers.cpp:245-281): a wall the rays end on (kept: rays
+    stop truncation_distance short of it), a ghost plane in free space facing the sensor (removed), a ghost plane seen edge-on
+    (|ray . normal| <= minDot: kept), points outside the carving volume (never touched), and a map without normals (everything
+    a ray passes through goes)."""
+    O = oracle
+    yy, zz = np.meshgrid(np.arange(-1.0, 1.0001, 0.05), np.arange(-1.0, 1.0001, 0.05), indexing="ij")
+    plane = lambda x: np.stack([np.full(yy.size, x), yy.ravel(), zz.ravel()], axis=1)  # noqa: E731
+    wall, ghost, edge, outside = plane(5.0), plane(2.03), plane(3.03), plane(2.53) + np.array([0.0, 30.0, 0.0])
+    nrm = np.concatenate([np.tile([-1.0, 0, 0], (len(wall), 1)), np.tile([-1.0, 0, 0], (len(ghost), 1)), np.tile([0, 0, 1.0], (len(edge), 1)),
+                          np.tile([-1.0, 0, 0], (len(outside), 1))])
+    map_xyz = np.concatenate([wall, ghost, edge, outside])
+    scan = np.concatenate([wall, plane(2.53) + np.array([0.0, 30.0, 0.0]) * 0 + np.array([2.47, 30.0, 0.0])])   # rays to the wall and toward `outside`
+    sensor = np.zeros(3)
+    vol = O.crop_spec(O.CROP_MAX_RADIUS, sensor, rmax=10.0)
+    m = O.carve(scan, sensor, map_xyz, nrm, vol, voxel=0.1, max_ray_length=20.0, truncation=0.1, min_dot=0.5)
+    a, b, c = len(wall), len(wall) + len(ghost), len(wall) + len(ghost) + len(edge)
+    fan = lambda pts, x: (np.abs(pts[:, 1]) <= 0.85 * x / 5.0) & (np.abs(pts[:, 2]) <= 0.85 * x / 5.0)      # well inside the ray fan  # noqa: E731
+    off = lambda pts, x: (np.abs(pts[:, 1]) >= 1.25 * x / 5.0) | (np.abs(pts[:, 2]) >= 1.25 * x / 5.0)      # clearly outside it  # noqa: E731
+    assert not m[:a].any()                                   # the surface the rays end on survives
+    assert m[a:b][fan(ghost, 2.0)].all() and not m[a:b][off(ghost, 2.1)].any()   # free-space ghost facing the sensor: carved where rays pass
+    assert not m[b:c].any()                                  # edge-on surface: |dir . n| = |dir_z| <= 0.28 < 0.5
+    assert not m[c:].any()                                   # outside the cropping volume (30 m away > rmax 10)
+    m2 = O.carve(scan, sensor, map_xyz, None, vol, voxel=0.1)   # no normals: everything a ray passes through goes
+    assert m2[a:b][fan(ghost, 2.0)].all() and m2[b:c][fan(edge, 3.0)].all() and not m2[:a].any() and not m2[c:].any()
+    # ray length: maximalPathTraveled = max(voxel, min(length - truncation, maxRaytracingLength)) — a 1 m cap stops before the ghost
+    assert not O.carve(scan, sensor, map_xyz, nrm, vol, voxel=0.1, max_ray_length=1.0).any()
+    # brute-force restatement in numpy (fp64, same sampling) on a random case
+    rng = np.random.default_rng(3)
+    mp = rng.uniform(-4, 4, (3000, 3)); mn = rng.normal(size=(3000, 3))
+    sc = rng.uniform(-6, 6, (200, 3)); s0 = np.array([0.3, -0.2, 0.1])
+    vol2 = O.crop_spec(O.CROP_MAX_RADIUS, s0, rmax=5.0)
+    got = O.carve(sc, s0, mp, mn, vol2, voxel=0.25, max_ray_length=4.0, truncation=0.2, min_dot=0.3)
+    inside = np.linalg.norm(mp - s0, axis=1) <= 5.0
+    keys = {}
+    for i in np.nonzero(inside)[0]:
+        keys.setdefault(tuple(np.floor(mp[i] * (1.0 / 0.25)).astype(int)), []).append(i)
+    want = np.zeros(3000, dtype=bool)
+    for p in sc:
+        d = p - s0
+        L = np.sqrt((d[0] * d[0] + d[1] * d[1]) + d[2] * d[2])
+        u = d / L
+        dist, mx = 0.0, max(0.25, min(L - 0.2, 4.0))
+        while dist < mx:
+            for i in keys.get(tuple(np.floor((dist * u + s0) * (1.0 / 0.25)).astype(int)), []):
+                n = mn[i] / np.sqrt((mn[i][0] * mn[i][0] + mn[i][1] * mn[i][1]) + mn[i][2] * mn[i][2])
+                if abs((u[0] * n[0] + u[1] * n[1]) + u[2] * n[2]) > 0.3:
+                    want[i] = True
+            dist += 0.25
+    assert np.array_equal(got, want) and want.sum() > 20
