@@ -34,9 +34,10 @@ scans = [scenes.lidar_scan(scene, T, n_beams=128, n_az=1024, noise_sigma=0.01, s
 ctx = capi.Context(0)
 icp = capi.icp_config(knn=1, max_dist=0.5, trim_ratio=0.9, max_angle=1.57, max_iter=15, min_diff_rot=1e-3, min_diff_trans=1e-2, smooth_length=3)
 m = Mapper(ctx, capi.crop_spec(capi.CROP_MINMAX_RADIUS, np.zeros(3), rmin=2.0, rmax=80.0), capi.crop_spec(capi.CROP_MAX_RADIUS, np.zeros(3), rmax=80.0),
-           icp, scan_voxel_size=0.1, normals_knn=20, normals_radius=1.0, map_voxel_size=0.15, min_movement=0.0, reference_period=2.0)
+           icp, scan_voxel_size=0.1, normals_knn=20, normals_radius=1.0, map_voxel_size=0.15, min_movement=0.0, reference_period=2.0,
+           carving=capi.CarveParams(0.1, 20.0, 0.1, 0.5) if os.environ.get("B200MAP_CARVE") else None, carve_every=10)
 m.set_pose(poses[0])
-ts, its, errs, stages = [], [], [], []
+ts, its, errs, stages, carved = [], [], [], [], []
 for i, (sc, od, T) in enumerate(zip(scans, odom, poses)):
     ctx.sync()
     t0 = time.perf_counter()
@@ -45,6 +46,8 @@ for i, (sc, od, T) in enumerate(zip(scans, odom, poses)):
     assert ok, err
     its.append(st.iterations)
     stages.append((st.reference_refreshed, list(st.stage_ms)))
+    if st.carved_points or (os.environ.get("B200MAP_CARVE") and i % 10 == 0 and i > 0):
+        carved.append((i, st.carved_points, ts[-1] * 1e3 if ts else 0.0))
     errs.append(np.abs((np.linalg.inv(T) @ pose)[:3, 3]).max())
     if i in (1, n_scans - 1):
         print(f"scan {i}: {ts[-1]*1e3:.2f} ms, reading {st.reading_points}, merge {st.merge_points}, patch {st.patch_points}, map {st.map_points}, "
@@ -77,3 +80,6 @@ if n_cpu > 0:
         assert ok
     tc = np.array(tc[1:])
     print(f"CPU oracle composition (8 threads in kNN / normals / ICP), {len(tc)} scans: {1.0 / tc.mean():.2f} scans/s (mean {tc.mean()*1e3:.0f} ms)")
+if carved:
+    print("space carving (every 10th inserted scan; raw 131 072-ray scan, 0.1 m steps up to 20 m): " +
+          ", ".join(f"scan {i}: {c} points carved" for i, c, _ in carved))
