@@ -126,6 +126,12 @@ int32_t b200reg_icp_step(b200reg_ctx* ctx, const b200reg_index* index, const b20
  *      classes call when a chain mixes CPU and CUDA modules --------------------------------------------------------- */
 /* TrimmedDistOutlierFilter::compute (OutlierFiltersImpl.cpp:140-147): tau = quantile of the finite d2, w = (d2 <= tau) */
 int32_t b200reg_trimmed_dist(b200reg_ctx* ctx, const float* d2, int64_t count, float ratio, float* tau_out, float* w_out);
+/* MaxDistOutlierFilter / MinDistOutlierFilter / MedianDistOutlierFilter::compute (OutlierFiltersImpl.cpp:64-125) on the squared
+ * distances of a Matches object: w = (d2 <= maxDist^2), (d2 >= minDist^2), (d2 <= factor * median(d2)) with the median taken by
+ * the same exact radix select as the trimmed filter (Matches::getDistsQuantile(0.5)).  param = maxDist | minDist | factor;
+ * limit_out (nullable) = the threshold that was applied. */
+enum { B200REG_OUTLIER_MAX_DIST = 0, B200REG_OUTLIER_MIN_DIST = 1, B200REG_OUTLIER_MEDIAN_DIST = 2 };
+int32_t b200reg_dist_outlier(b200reg_ctx* ctx, int32_t kind, const float* d2, int64_t count, float param, float* limit_out, float* w_out);
 /* SurfaceNormalOutlierFilter::compute (OutlierFiltersImpl.cpp:236-281); normals 3 floats per point, nullable = filter off */
 int32_t b200reg_surface_normal_outlier(b200reg_ctx* ctx, const float* normals_reading, const float* normals_reference,
                                        int64_t n_reference, const int32_t* ids, int32_t k, int64_t n, float max_angle, float* w_out);

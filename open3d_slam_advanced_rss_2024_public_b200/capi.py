@@ -115,6 +115,7 @@ SYMBOLS = {
     "b200reg_knn": (C.c_int32, [_VP, _VP, _VP, _VP, C.c_int32, C.c_float, C.c_float, C.c_int32, _VP, _VP, C.POINTER(C.c_uint64)]),
     "b200reg_icp_step": (C.c_int32, [_VP, _VP, _VP, _VP, C.c_int32, C.c_float, C.c_float, C.c_float, C.c_int32, _VP, _VP, C.POINTER(StepStats)]),
     "b200reg_trimmed_dist": (C.c_int32, [_VP, _VP, C.c_int64, C.c_float, C.POINTER(C.c_float), _VP]),
+    "b200reg_dist_outlier": (C.c_int32, [_VP, C.c_int32, _VP, C.c_int64, C.c_float, C.POINTER(C.c_float), _VP]),
     "b200reg_surface_normal_outlier": (C.c_int32, [_VP, _VP, _VP, C.c_int64, _VP, C.c_int32, C.c_int64, C.c_float, _VP]),
     "b200reg_point_to_plane": (C.c_int32, [_VP, _VP, _VP, _VP, _VP, _VP, C.c_int32, C.c_int32, _VP, _VP, C.POINTER(StepStats)]),
     "b200reg_solve_point_to_plane": (C.c_int32, [_VP, _VP, _VP, _VP, C.c_int32, C.c_int32, _VP, _VP]),
@@ -331,6 +332,14 @@ class Context:
         m = C.c_int64(0)
         self.check(lib().b200reg_voxel_down_sample_f64(self.h, float(voxel), _p(xyz), _p(nrm), xyz.shape[0], _p(xo), _p(no), C.byref(m)))
         return xo[:m.value], (None if no is None else no[:m.value])
+
+    def dist_outlier(self, kind, d2, param):
+        """MaxDist (0) / MinDist (1) / MedianDist (2) outlier weights on squared distances; returns (limit, weights)."""
+        d2 = _f32(d2)
+        w = np.empty(d2.shape, dtype=np.float32)
+        lim = C.c_float(0)
+        self.check(lib().b200reg_dist_outlier(self.h, int(kind), _p(d2), d2.size, float(param), C.byref(lim), _p(w)))
+        return lim.value, w
 
     def crop_f64(self, spec, xyz, nrm=None):
         xyz, nrm = _f64(xyz), _f64(nrm)

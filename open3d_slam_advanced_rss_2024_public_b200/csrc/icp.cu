@@ -952,6 +952,18 @@ __global__ void trimWeightsKernel(const float* __restrict__ d2, int64_t count, c
   w[i] = (d2[i] <= __uint_as_float(st->tauBits)) ? 1.f : 0.f;   // OutlierFiltersImpl.cpp:146
 }
 
+// MaxDist / MinDist / MedianDist weights: w = (d2 <= limit) or (d2 >= limit) (OutlierFiltersImpl.cpp:74-81,95-102,116-125);
+// scaleByTau: limit = fl(limit * tau) with tau the quantile the select kernels left in `st` (MedianDist: factor * median)
+__global__ void distWeightsKernel(const float* __restrict__ d2, int64_t count, float limit, int greater, const SelState* __restrict__ st,
+                                  int scaleByTau, float* __restrict__ w, float* __restrict__ limitOut) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (scaleByTau) limit = __fmul_rn(limit, __uint_as_float(st->tauBits));
+  if (i == 0 && limitOut) *limitOut = limit;
+  if (i >= count) return;
+  const float d = d2[i];
+  w[i] = (greater ? (d >= limit) : (d <= limit)) ? 1.f : 0.f;
+}
+
 // SurfaceNormalOutlierFilter::compute (OutlierFiltersImpl.cpp:236-281) on explicit arrays (normals: 3 floats per point)
 __global__ void normalGateKernel(const float* __restrict__ nRead, const float* __restrict__ nRef, const int* __restrict__ ids, int k,
                                  int64_t total, float eps, float* __restrict__ w) {
@@ -989,6 +1001,40 @@ int32_t b200reg_trimmed_dist(b200reg_ctx* ctx, const float* d2, int64_t count, f
   CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
   if (h->error) return setErr(ctx, B200REG_E_NOT_CONVERGED, "No matches available for computing distance quantiles");
   if (tau_out) memcpy(tau_out, &h->tauBits, sizeof(float));
+  return B200REG_OK;
+}
+
+int32_t b200reg_dist_outlier(b200reg_ctx* ctx, int32_t kind, const float* d2, int64_t count, float param, float* limit_out, float* w_out) {
+  if (!ctx || count < 0 || (count > 0 && (!d2 || !w_out)) || kind < B200REG_OUTLIER_MAX_DIST || kind > B200REG_OUTLIER_MEDIAN_DIST)
+    return setErr(ctx, B200REG_E_INVALID_PARAM, "dist_outlier: bad arguments");
+  // parameter bounds of the CPU twins (OutlierFiltersImpl.h:46-49,64-67,83-86)
+  if (kind == B200REG_OUTLIER_MEDIAN_DIST && !(param >= 0.0000001f)) return setErr(ctx, B200REG_E_INVALID_PARAM, "MedianDistOutlierFilter: factor must be >= 1e-7");
+  if (kind != B200REG_OUTLIER_MEDIAN_DIST && !(param >= 0.0000001f)) return setErr(ctx, B200REG_E_INVALID_PARAM, "%s: distance must be >= 1e-7", kind == B200REG_OUTLIER_MAX_DIST ? "MaxDistOutlierFilter" : "MinDistOutlierFilter");
+  if (kind == B200REG_OUTLIER_MEDIAN_DIST && count == 0) return setErr(ctx, B200REG_E_NOT_CONVERGED, "No matches available for computing distance quantiles");
+  if (limit_out) *limit_out = 0.f;
+  if (count == 0) return B200REG_OK;
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  TRY(ensureBuf(ctx, ctx->matchD2, sizeof(float) * (size_t)count));
+  TRY(ensureBuf(ctx, ctx->misc, sizeof(float) * (size_t)count + 64));
+  float* dd = (float*)ctx->matchD2.p;
+  float* dw = (float*)ctx->misc.p;
+  float* dLimit = dw + count;
+  CUDA_TRY(ctx, cudaMemcpyAsync(dd, d2, sizeof(float) * (size_t)count, cudaMemcpyHostToDevice, ctx->stream));
+  SelState* st = selState(ctx);
+  const bool median = kind == B200REG_OUTLIER_MEDIAN_DIST;
+  if (median) TRY(launchSelect(ctx, dd, count, 0.5f, nullptr));   // input.getDistsQuantile(0.5)
+  // pow(maxDist, 2) is evaluated in double and rounded once to T = float: the same value as the fp32 product
+  const float limit = median ? param : param * param;
+  distWeightsKernel<<<divUp(count, 256), 256, 0, ctx->stream>>>(dd, count, limit, kind == B200REG_OUTLIER_MIN_DIST ? 1 : 0, st, median ? 1 : 0, dw, dLimit);
+  LAUNCH_CHECK(ctx);
+  SelState* h = (SelState*)ctx->pinned;
+  float* hLimit = (float*)((char*)ctx->pinned + 1024);
+  CUDA_TRY(ctx, cudaMemcpyAsync(h, st, sizeof(SelState), cudaMemcpyDeviceToHost, ctx->stream));
+  CUDA_TRY(ctx, cudaMemcpyAsync(hLimit, dLimit, sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+  CUDA_TRY(ctx, cudaMemcpyAsync(w_out, dw, sizeof(float) * (size_t)count, cudaMemcpyDeviceToHost, ctx->stream));
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  if (median && h->error) return setErr(ctx, B200REG_E_NOT_CONVERGED, "No matches available for computing distance quantiles");
+  if (limit_out) *limit_out = *hLimit;
   return B200REG_OK;
 }
 

@@ -226,6 +226,31 @@ PM::OutlierWeights CudaTrimmedDistOutlierFilter::compute(const PM::DataPoints&, 
   return w;
 }
 
+CudaDistOutlierFilterBase::CudaDistOutlierFilterBase(const std::string& name, const PM::ParametersDoc& doc, const PM::Parameters& params, int kind_, const char* key)
+    : PM::OutlierFilter(name, doc, params), kind(kind_), param(get<float>(key)), device(get<int>("device")) {}
+PM::OutlierWeights CudaDistOutlierFilterBase::compute(const PM::DataPoints&, const PM::DataPoints&, const PM::Matches& input) {
+  b200reg_ctx* ctx = contextFor(device);
+  PM::OutlierWeights w(input.dists.rows(), input.dists.cols());
+  check(ctx, b200reg_dist_outlier(ctx, kind, input.dists.data(), (int64_t)input.dists.d.size(), param, nullptr, w.data()));
+  return w;
+}
+const PM::ParametersDoc CudaMaxDistOutlierFilter::availableParameters() {   // OutlierFiltersImpl.h:46-49
+  return {{"maxDist", "threshold distance (Euclidean norm)", "1", "0.0000001", "inf", &P::Comp<float>}, {"device", "CUDA device ordinal", "0", "0", "1023", &P::Comp<int>}};
+}
+CudaMaxDistOutlierFilter::CudaMaxDistOutlierFilter(const PM::Parameters& params)
+    : CudaDistOutlierFilterBase("CudaMaxDistOutlierFilter", availableParameters(), params, B200REG_OUTLIER_MAX_DIST, "maxDist") {}
+const PM::ParametersDoc CudaMinDistOutlierFilter::availableParameters() {   // OutlierFiltersImpl.h:64-67
+  return {{"minDist", "threshold distance (Euclidean norm)", "1", "0.0000001", "inf", &P::Comp<float>}, {"device", "CUDA device ordinal", "0", "0", "1023", &P::Comp<int>}};
+}
+CudaMinDistOutlierFilter::CudaMinDistOutlierFilter(const PM::Parameters& params)
+    : CudaDistOutlierFilterBase("CudaMinDistOutlierFilter", availableParameters(), params, B200REG_OUTLIER_MIN_DIST, "minDist") {}
+const PM::ParametersDoc CudaMedianDistOutlierFilter::availableParameters() {   // OutlierFiltersImpl.h:83-86
+  return {{"factor", "points farther away factor * median will be considered outliers.", "3", "0.0000001", "inf", &P::Comp<float>},
+          {"device", "CUDA device ordinal", "0", "0", "1023", &P::Comp<int>}};
+}
+CudaMedianDistOutlierFilter::CudaMedianDistOutlierFilter(const PM::Parameters& params)
+    : CudaDistOutlierFilterBase("CudaMedianDistOutlierFilter", availableParameters(), params, B200REG_OUTLIER_MEDIAN_DIST, "factor") {}
+
 const PM::ParametersDoc CudaSurfaceNormalOutlierFilter::availableParameters() {
   return {{"maxAngle", "Maximum authorised angle between the 2 surface normals (in radian)", "1.57", "0.0", "3.1416", &P::Comp<float>},
           {"device", "CUDA device ordinal", "0", "0", "1023", &P::Comp<int>}};
@@ -290,6 +315,9 @@ void registerCudaModules(PM& pm) {
   ADD_TO_REGISTRAR(Matcher, CudaKDTreeMatcher, CudaKDTreeMatcher)
   ADD_TO_REGISTRAR(OutlierFilter, CudaTrimmedDistOutlierFilter, CudaTrimmedDistOutlierFilter)
   ADD_TO_REGISTRAR(OutlierFilter, CudaSurfaceNormalOutlierFilter, CudaSurfaceNormalOutlierFilter)
+  ADD_TO_REGISTRAR(OutlierFilter, CudaMaxDistOutlierFilter, CudaMaxDistOutlierFilter)
+  ADD_TO_REGISTRAR(OutlierFilter, CudaMinDistOutlierFilter, CudaMinDistOutlierFilter)
+  ADD_TO_REGISTRAR(OutlierFilter, CudaMedianDistOutlierFilter, CudaMedianDistOutlierFilter)
   ADD_TO_REGISTRAR(ErrorMinimizer, CudaPointToPlaneErrorMinimizer, CudaPointToPlaneErrorMinimizer)
 }
 

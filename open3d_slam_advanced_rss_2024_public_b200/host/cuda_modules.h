@@ -67,6 +67,30 @@ struct CudaTrimmedDistOutlierFilter : public PM::OutlierFilter {   // twin: Outl
   PM::OutlierWeights compute(const PM::DataPoints& filteredReading, const PM::DataPoints& filteredReference, const PM::Matches& input) override;
 };
 
+// MaxDist / MinDist / MedianDist twins (OutlierFiltersImpl.h:40-104): one device kernel behind all three (b200reg_dist_outlier)
+struct CudaDistOutlierFilterBase : public PM::OutlierFilter {
+  const int kind;      // B200REG_OUTLIER_*
+  const float param;   // maxDist | minDist | factor
+  const int device;
+  CudaDistOutlierFilterBase(const std::string& name, const PM::ParametersDoc& doc, const PM::Parameters& params, int kind, const char* key);
+  PM::OutlierWeights compute(const PM::DataPoints& filteredReading, const PM::DataPoints& filteredReference, const PM::Matches& input) override;
+};
+struct CudaMaxDistOutlierFilter : public CudaDistOutlierFilterBase {
+  static const std::string description() { return "This filter considers as outlier links whose norms are above a fix threshold."; }
+  static const PM::ParametersDoc availableParameters();
+  explicit CudaMaxDistOutlierFilter(const PM::Parameters& params = PM::Parameters());
+};
+struct CudaMinDistOutlierFilter : public CudaDistOutlierFilterBase {
+  static const std::string description() { return "This filter considers as outlier links whose norms are below a threshold."; }
+  static const PM::ParametersDoc availableParameters();
+  explicit CudaMinDistOutlierFilter(const PM::Parameters& params = PM::Parameters());
+};
+struct CudaMedianDistOutlierFilter : public CudaDistOutlierFilterBase {
+  static const std::string description() { return "This filter considers as outlier links whose norms are above the median link norms times a factor."; }
+  static const PM::ParametersDoc availableParameters();
+  explicit CudaMedianDistOutlierFilter(const PM::Parameters& params = PM::Parameters());
+};
+
 struct CudaSurfaceNormalOutlierFilter : public PM::OutlierFilter {   // twin: OutlierFiltersImpl.h:176-192
   static const std::string description() { return "Hard rejection threshold using the angle between the surface normal vectors of the reading and the reference."; }
   static const PM::ParametersDoc availableParameters();

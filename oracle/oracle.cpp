@@ -337,6 +337,24 @@ int distsQuantile(const float* d2, int64_t count, float quantile, float* out) {
 extern "C" {
 
 // TrimmedDistOutlierFilter::compute (OutlierFiltersImpl.cpp:140-147): w = (d2 <= limit)
+// MaxDist / MinDist / MedianDist outlier filters (OutlierFiltersImpl.cpp:64-125): kind 0 w = (d2 <= fl(maxDist^2)), kind 1
+// w = (d2 >= fl(minDist^2)) — pow(x, 2) on T = float is evaluated in double and rounded once, i.e. the fp32 product —, kind 2
+// w = (d2 <= fl(factor * getDistsQuantile(0.5))).
+int32_t orc_dist_outlier(int32_t kind, const float* d2, int64_t count, float param, float* limit_out, float* w_out) {
+  float limit = 0.f;
+  if (kind == 2) {
+    float median = 0.f;
+    const int st = distsQuantile(d2, count, 0.5f, &median);
+    if (st != ORC_OK) return st;
+    limit = param * median;
+  } else {
+    limit = (float)std::pow((double)param, 2);
+  }
+  for (int64_t i = 0; i < count; ++i) w_out[i] = ((kind == 1) ? (d2[i] >= limit) : (d2[i] <= limit)) ? 1.f : 0.f;
+  if (limit_out) *limit_out = limit;
+  return ORC_OK;
+}
+
 int32_t orc_trimmed_dist(const float* d2, int64_t count, float ratio, float* tau_out, float* w_out) {
   float tau = 0.f;
   const int st = distsQuantile(d2, count, ratio, &tau);

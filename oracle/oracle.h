@@ -72,6 +72,7 @@ uint64_t orc_knn_brute(const float* ref, int32_t rstride, int64_t m, const float
 int32_t orc_transform(const float T[16], float* feat, int32_t stride, float* normals, int64_t n);
 
 /* ---- outlier filters ---- */
+int32_t orc_dist_outlier(int32_t kind, const float* d2, int64_t count, float param, float* limit_out, float* w_out);   /* OutlierFiltersImpl.cpp:64-125 */
 int32_t orc_trimmed_dist(const float* d2, int64_t count, float ratio, float* tau_out, float* w_out);   /* OutlierFiltersImpl.cpp:140-147, Matches.cpp:61-87 */
 void    orc_surface_normal_outlier(const float* nrm_read, const float* nrm_ref, const int32_t* ids, int32_t k, int64_t n,
                                    float max_angle, float* w_out);                                     /* OutlierFiltersImpl.cpp:226-281 */

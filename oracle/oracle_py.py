@@ -63,6 +63,7 @@ def lib():
         L.orc_transform.argtypes = [C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_int64]
         L.orc_trimmed_dist.restype = C.c_int32
         L.orc_trimmed_dist.argtypes = [C.c_void_p, C.c_int64, C.c_float, C.c_void_p, C.c_void_p]
+        L.orc_dist_outlier.argtypes = [C.c_int32, C.c_void_p, C.c_int64, C.c_float, C.c_void_p, C.c_void_p]
         L.orc_surface_normal_outlier.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int64, C.c_float, C.c_void_p]
         L.orc_no_filter_weights.argtypes = [C.c_void_p, C.c_int64, C.c_void_p]
         L.orc_point_to_plane.restype = C.c_int32
@@ -157,6 +158,15 @@ def trimmed_dist(d2, ratio):
     w = np.empty(d2.shape, dtype=np.float32)
     st = lib().orc_trimmed_dist(_p(d2), d2.size, ratio, C.byref(tau), _p(w))
     return st, tau.value, w
+
+
+def dist_outlier(kind, d2, param):
+    """MaxDist (0) / MinDist (1) / MedianDist (2) outlier filters: returns (status, limit, weights)."""
+    d2 = _f32(d2)
+    lim = C.c_float(0)
+    w = np.empty(d2.shape, dtype=np.float32)
+    st = lib().orc_dist_outlier(int(kind), _p(d2), d2.size, float(param), C.byref(lim), _p(w))
+    return st, lim.value, w
 
 
 def surface_normal_outlier(nrm_read, nrm_ref, ids, max_angle):

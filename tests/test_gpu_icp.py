@@ -220,6 +220,39 @@ def test_icp_step_matches_oracle(ctx, oracle, golden, k, trim, angle):
     assert_same_T(Tg, o["T"], 1e-6, 1e-6)
 
 
+@pytest.mark.parametrize("kind,param", [(0, 0.35), (0, 2.0), (1, 0.35), (2, 3.0), (2, 0.5), (2, 1.0)])
+def test_distance_outlier_filters_match_oracle(ctx, oracle, kind, param):
+    """MaxDist / MinDist / MedianDist (b200reg_dist_outlier) against the oracle: limit and weights bit-exact, incl. +inf padding,
+    exact ties at the limit and the median's float-multiply rank."""
+    from open3d_slam_advanced_rss_2024_public_b200 import capi
+    rng = np.random.default_rng(17 + kind)
+    for n in (1, 7, 1000, 131072):
+        d2 = (rng.random(n).astype(np.float32) ** 2) * np.float32(1.5)
+        d2[rng.random(n) < 0.1] = np.inf
+        if n > 10:
+            d2[:5] = np.float32(param) * np.float32(param)          # values exactly at a MaxDist / MinDist limit
+            d2[5:9] = d2[9]                                          # ties
+        if not np.isfinite(d2).any():
+            d2[0] = 0.25
+        st, lim_o, w_o = oracle.dist_outlier(kind, d2, param)
+        lim_g, w_g = ctx.dist_outlier(kind, d2, param)
+        assert st == 0 and np.float32(lim_g).view(np.uint32) == np.float32(lim_o).view(np.uint32), (n, lim_g, lim_o)
+        assert np.array_equal(w_g, w_o), n
+    # k > 1 shaped input (n x k matrix) is just a longer array
+    d2 = rng.random((500, 3)).astype(np.float32)
+    assert np.array_equal(ctx.dist_outlier(kind, d2, param)[1], oracle.dist_outlier(kind, d2, param)[2])
+    # errors of the CPU twins: parameter bounds -> InvalidParameter; a median without any finite match -> ConvergenceError
+    with pytest.raises(capi.InvalidParameter):
+        ctx.dist_outlier(kind, d2, 0.0)
+    if kind == 2:
+        with pytest.raises(capi.ConvergenceError):
+            ctx.dist_outlier(2, np.full(16, np.inf, dtype=np.float32), 3.0)
+        with pytest.raises(capi.ConvergenceError):
+            ctx.dist_outlier(2, np.zeros(0, dtype=np.float32), 3.0)
+    else:
+        assert ctx.dist_outlier(kind, np.zeros(0, dtype=np.float32), 1.0)[1].size == 0
+
+
 def test_trimmed_quantile_rank_semantics(ctx, oracle):
     # n = 131072, ratio 0.8 -> rank 104857 (float multiply + truncation, SURVEY 9.2); heavy ties at the limit
     rng = np.random.default_rng(1)

@@ -318,3 +318,19 @@ def test_space_carving_known_answers(oracle):
                     want[i] = True
             dist += 0.25
     assert np.array_equal(got, want) and want.sum() > 20
+
+
+def test_distance_outlier_filters_known_answers(oracle):
+    """MaxDist / MinDist / MedianDist (OutlierFiltersImpl.cpp:64-125) on squared distances, incl. the +inf padding of missing matches:
+    inf <= limit is false, inf >= limit is true; the median is getDistsQuantile(0.5) = the element of rank uint(float(n_finite) * 0.5)."""
+    d2 = np.array([0.04, 0.25, np.inf, 1.0, 0.0, 4.0, 9.0, 0.09], dtype=np.float32)
+    st, lim, w = oracle.dist_outlier(0, d2, 0.5)
+    assert st == 0 and lim == np.float32(0.25) and w.tolist() == [1, 1, 0, 0, 1, 0, 0, 1]          # the boundary value is kept (<=)
+    st, lim, w = oracle.dist_outlier(1, d2, 0.5)
+    assert st == 0 and w.tolist() == [0, 1, 1, 1, 0, 1, 1, 0]
+    st, lim, w = oracle.dist_outlier(2, d2, 3.0)
+    finite = np.sort(d2[np.isfinite(d2)])                                                           # 7 finite values, rank uint(7 * 0.5) = 3
+    assert st == 0 and lim == np.float32(3.0) * finite[3] and w.tolist() == [1, 1, 0, 0, 1, 0, 0, 1]
+    assert oracle.dist_outlier(2, np.full(4, np.inf, dtype=np.float32), 3.0)[0] != 0                # no finite match: ConvergenceError
+    x = np.float32(0.3)                                                                             # pow(float, 2) in double, rounded once
+    assert oracle.dist_outlier(0, d2, float(x))[1] == np.float32(np.float64(x) ** 2) == x * x

@@ -41,7 +41,8 @@ def shim():
 def test_cuda_modules_are_registered_by_name(shim):
     assert {"CudaVoxelGridDataPointsFilter", "CudaSurfaceNormalDataPointsFilter"} <= set(shim.list_modules("DataPointsFilter"))
     assert "CudaKDTreeMatcher" in shim.list_modules("Matcher")
-    assert {"CudaTrimmedDistOutlierFilter", "CudaSurfaceNormalOutlierFilter"} <= set(shim.list_modules("OutlierFilter"))
+    assert {"CudaTrimmedDistOutlierFilter", "CudaSurfaceNormalOutlierFilter", "CudaMaxDistOutlierFilter", "CudaMinDistOutlierFilter",
+            "CudaMedianDistOutlierFilter"} <= set(shim.list_modules("OutlierFilter"))
     assert "CudaPointToPlaneErrorMinimizer" in shim.list_modules("ErrorMinimizer")
     assert {"CounterTransformationChecker", "DifferentialTransformationChecker", "BoundTransformationChecker"} <= set(shim.list_modules("TransformationChecker"))
 
@@ -53,6 +54,9 @@ def test_parameter_tables_match_the_cpu_twins(shim):
     assert p["knn"] == ("1", "1", "2147483647") and p["epsilon"] == ("0", "0", "inf") and p["searchType"] == ("1", "0", "2") and p["maxDist"] == ("inf", "0", "inf")
     assert shim.module_parameters("OutlierFilter", "CudaTrimmedDistOutlierFilter")["ratio"] == ("0.85", "0.0000001", "1.0")
     assert shim.module_parameters("OutlierFilter", "CudaSurfaceNormalOutlierFilter")["maxAngle"][0] == "1.57"
+    assert shim.module_parameters("OutlierFilter", "CudaMaxDistOutlierFilter")["maxDist"] == ("1", "0.0000001", "inf")      # OutlierFiltersImpl.h:46-49
+    assert shim.module_parameters("OutlierFilter", "CudaMinDistOutlierFilter")["minDist"] == ("1", "0.0000001", "inf")      # :64-67
+    assert shim.module_parameters("OutlierFilter", "CudaMedianDistOutlierFilter")["factor"] == ("3", "0.0000001", "inf")    # :83-86
     p = shim.module_parameters("ErrorMinimizer", "CudaPointToPlaneErrorMinimizer")
     assert p["force2D"] == ("0", "0", "1") and p["force4DOF"] == ("0", "0", "1")
     p = shim.module_parameters("DataPointsFilter", "CudaVoxelGridDataPointsFilter")
@@ -229,3 +233,25 @@ def test_chain_errors_surface_as_runtime_errors(shim, oracle, golden):
             icp(q, ref, None, None, None, force_generic=generic)
     with pytest.raises(shim.PmError, match="empty"):                # ICP.cpp:357-359
         icp(np.zeros((0, 4), dtype=np.float32), ref, None, None, rn)
+
+
+@pytest.mark.gpu
+def test_chain_with_distance_outlier_filters(shim, oracle, golden):
+    """A chain that adds the MaxDist / MedianDist twins runs in the generic lane (module by module).  With limits that reject
+    nothing beyond what the trimmed filter already rejects, weights multiply to the same set and the result equals the plain chain;
+    a tighter MaxDist than the matcher's radius shrinks the kept set."""
+    car = golden["car"]
+    ref, rn, q = oracle.feat4(car["ref_xyz"]), car["ref_normals"], oracle.feat4(car["data_xyz"])
+    qn = oracle.surface_normals(q, 10, nthreads=8, orient_origin=[0, 0, 0])["normals"]
+    base = to_cuda(yaml_text("open3d_slam_icp.yaml"))
+    T0, s0 = shim.ICP(base)(q, ref, None, qn, rn, force_generic=True)
+    loose = base.replace("outlierFilters:\n", "outlierFilters:\n  - CudaMaxDistOutlierFilter:\n      maxDist: 100.0\n  - CudaMedianDistOutlierFilter:\n      factor: 1000000.0\n", 1)
+    assert loose != base
+    T1, s1 = shim.ICP(loose)(q, ref, None, qn, rn)
+    assert not s1["fast_lane"] and s1["iterations"] == s0["iterations"]
+    _assert_same_T(T1, T0, 1e-6)
+    tight = base.replace("outlierFilters:\n", "outlierFilters:\n  - CudaMaxDistOutlierFilter:\n      maxDist: 0.3\n", 1)
+    T2, s2 = shim.ICP(tight)(q, ref, None, qn, rn)
+    assert not s2["fast_lane"] and s2["overlap"] < s0["overlap"] and np.isfinite(T2).all()
+    with pytest.raises(shim.InvalidParameter):
+        shim.ICP(base.replace("outlierFilters:\n", "outlierFilters:\n  - CudaMedianDistOutlierFilter:\n      factor: 0\n", 1))
