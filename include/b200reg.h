@@ -19,6 +19,7 @@
  */
 #ifndef B200REG_H
 #define B200REG_H
+#include <stddef.h>
 #include <stdint.h>
 #ifdef __cplusplus
 extern "C" {
@@ -278,6 +279,22 @@ int32_t b200reg_map_insert_cloud64(b200reg_ctx* ctx, b200reg_map* map, const b20
 /* b200reg_map_carve with the raw scan already on the device */
 int32_t b200reg_map_carve_cloud64(b200reg_ctx* ctx, b200reg_map* map, const b200reg_cloud64* scan, const double T_map_scan[16],
                                   const b200reg_crop_spec* volume, const b200reg_carve_params* params, int64_t* removed);
+
+/* ---- sensor_msgs/PointCloud2 bytes straight to device clouds: replaces
+ *      RosPointCloud2Deserializer<float>::deserialize (pointmatcher_ros/src/RosPointCloud2Deserializer.cpp:9-38,213-232; features
+ *      x y z pad = 1 and the "normals" descriptor) and open3d_conversions::rosToOpen3d (open3d_conversions.cpp:203-244).  Both read
+ *      fields through PointCloud2ConstIterator<float>: value i = the 4 bytes at data + i * point_step + offset as a host-order float,
+ *      whatever the declared datatype; row_step and is_bigendian are not consulted.  Offsets < 0 = field absent (normals are taken
+ *      only when all three are present); x, y, z are required.  *out is in/out like the cloud64 entry points. ------------------- */
+typedef struct b200reg_pc2_layout {
+  uint32_t width, height, point_step;
+  int32_t off_x, off_y, off_z;
+  int32_t off_normal_x, off_normal_y, off_normal_z;
+} b200reg_pc2_layout;
+int32_t b200reg_cloud_from_pointcloud2(b200reg_ctx* ctx, const uint8_t* data, size_t data_bytes, const b200reg_pc2_layout* layout,
+                                       b200reg_cloud** out);
+int32_t b200reg_cloud64_from_pointcloud2(b200reg_ctx* ctx, const uint8_t* data, size_t data_bytes, const b200reg_pc2_layout* layout,
+                                         b200reg_cloud64** out);
 
 #ifdef __cplusplus
 }

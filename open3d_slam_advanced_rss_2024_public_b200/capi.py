@@ -64,6 +64,18 @@ class CarveParams(C.Structure):
                 ("min_dot_product_with_normal", C.c_double)]
 
 
+class Pc2Layout(C.Structure):
+    """The parts of sensor_msgs/PointCloud2 the deserialisers read (byte offsets of FLOAT32 fields; < 0 = absent)."""
+    _fields_ = [("width", C.c_uint32), ("height", C.c_uint32), ("point_step", C.c_uint32), ("off_x", C.c_int32), ("off_y", C.c_int32),
+                ("off_z", C.c_int32), ("off_normal_x", C.c_int32), ("off_normal_y", C.c_int32), ("off_normal_z", C.c_int32)]
+
+
+def pc2_layout(width, height, point_step, fields):
+    """fields: {name: byte offset} as in sensor_msgs/PointField."""
+    g = lambda k: int(fields.get(k, -1))  # noqa: E731
+    return Pc2Layout(width, height, point_step, g("x"), g("y"), g("z"), g("normal_x"), g("normal_y"), g("normal_z"))
+
+
 class IcpConfig(C.Structure):
     _fields_ = [("knn", C.c_int32), ("max_dist", C.c_float), ("epsilon", C.c_float), ("trim_ratio", C.c_float),
                 ("max_angle", C.c_float), ("force2D", C.c_int32), ("force4DOF", C.c_int32), ("max_iter", C.c_int32),
@@ -147,6 +159,8 @@ SYMBOLS = {
     "b200reg_cloud64_estimate_normals": (C.c_int32, [_VP, _VP, C.c_int32, C.c_double, _VP, C.POINTER(C.c_int32)]),
     "b200reg_cloud64_to_f32": (C.c_int32, [_VP, _VP, C.POINTER(_VP)]),
     "b200reg_map_insert_cloud64": (C.c_int32, [_VP, _VP, _VP, _VP, C.POINTER(CropSpec)]),
+    "b200reg_cloud_from_pointcloud2": (C.c_int32, [_VP, _VP, C.c_size_t, C.POINTER(Pc2Layout), C.POINTER(_VP)]),
+    "b200reg_cloud64_from_pointcloud2": (C.c_int32, [_VP, _VP, C.c_size_t, C.POINTER(Pc2Layout), C.POINTER(_VP)]),
     "b200reg_map_carve": (C.c_int32, [_VP, _VP, _VP, C.c_int64, _VP, C.POINTER(CropSpec), C.POINTER(CarveParams), C.POINTER(C.c_int64)]),
     "b200reg_map_carve_cloud64": (C.c_int32, [_VP, _VP, _VP, _VP, C.POINTER(CropSpec), C.POINTER(CarveParams), C.POINTER(C.c_int64)]),
 }
@@ -276,6 +290,20 @@ class Context:
             h = _VP()
             self.check(lib().b200reg_cloud_upload_f32(self.h, _p(feat), feat.shape[1], _p(nrm), feat.shape[0], C.byref(h)))
         return Cloud(self, h)
+
+    def cloud_from_pointcloud2(self, data, layout, out=None):
+        """RosPointCloud2Deserializer<float>::deserialize on the device: message bytes -> fp32 cloud (x y z pad, normals)."""
+        data = np.ascontiguousarray(np.frombuffer(data, dtype=np.uint8) if not isinstance(data, np.ndarray) else data.view(np.uint8).reshape(-1))
+        c = out if out is not None else Cloud(self, _VP())
+        self.check(lib().b200reg_cloud_from_pointcloud2(self.h, _p(data) if data.size else None, data.size, C.byref(layout), C.byref(c.h)))
+        return c
+
+    def cloud64_from_pointcloud2(self, data, layout, out=None):
+        """open3d_conversions::rosToOpen3d on the device: message bytes -> fp64 cloud (points, normals)."""
+        data = np.ascontiguousarray(np.frombuffer(data, dtype=np.uint8) if not isinstance(data, np.ndarray) else data.view(np.uint8).reshape(-1))
+        c = out if out is not None else Cloud64(self)
+        self.check(lib().b200reg_cloud64_from_pointcloud2(self.h, _p(data) if data.size else None, data.size, C.byref(layout), C.byref(c.h)))
+        return c
 
     def build_index(self, cloud, cell=0.0):
         h = _VP()

@@ -522,6 +522,64 @@ __global__ void normalsToF64Kernel(const float4* __restrict__ nrm, int64_t n, do
   out[3 * i] = (double)v.x; out[3 * i + 1] = (double)v.y; out[3 * i + 2] = (double)v.z;
 }
 
+
+// sensor_msgs/PointCloud2 bytes -> device clouds.  Both reference deserialisers read the fields through
+// sensor_msgs::PointCloud2ConstIterator<float>: point i's value is the 4 bytes at data + i * point_step + field.offset taken as a
+// host-order float, whatever datatype the field declares; row_step and is_bigendian are not consulted.
+__device__ __forceinline__ float pc2Float(const unsigned char* __restrict__ p, int aligned) {
+  if (aligned) return *reinterpret_cast<const float*>(p);
+  const unsigned v = (unsigned)p[0] | ((unsigned)p[1] << 8) | ((unsigned)p[2] << 16) | ((unsigned)p[3] << 24);
+  return __uint_as_float(v);
+}
+struct Pc2Dev {
+  unsigned step;
+  int ox, oy, oz, onx, ony, onz, aligned;
+};
+// RosPointCloud2Deserializer<float>::deserialize (RosPointCloud2Deserializer.cpp:9-38,213-232): features x y z pad = 1, "normals"
+__global__ void pc2ToF32Kernel(const unsigned char* __restrict__ data, int64_t n, Pc2Dev L, float4* __restrict__ xyz, float4* __restrict__ nrm) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const unsigned char* p = data + (size_t)i * L.step;
+  xyz[i] = make_float4(pc2Float(p + L.ox, L.aligned), pc2Float(p + L.oy, L.aligned), pc2Float(p + L.oz, L.aligned), 1.f);
+  if (nrm) nrm[i] = make_float4(pc2Float(p + L.onx, L.aligned), pc2Float(p + L.ony, L.aligned), pc2Float(p + L.onz, L.aligned), 0.f);
+}
+// open3d_conversions::rosToOpen3d (open3d_conversions.cpp:203-244): Vector3d(float x, float y, float z), normals likewise
+__global__ void pc2ToF64Kernel(const unsigned char* __restrict__ data, int64_t n, Pc2Dev L, double* __restrict__ xyz, double* __restrict__ nrm) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const unsigned char* p = data + (size_t)i * L.step;
+  xyz[3 * i] = (double)pc2Float(p + L.ox, L.aligned);
+  xyz[3 * i + 1] = (double)pc2Float(p + L.oy, L.aligned);
+  xyz[3 * i + 2] = (double)pc2Float(p + L.oz, L.aligned);
+  if (nrm) {
+    nrm[3 * i] = (double)pc2Float(p + L.onx, L.aligned);
+    nrm[3 * i + 1] = (double)pc2Float(p + L.ony, L.aligned);
+    nrm[3 * i + 2] = (double)pc2Float(p + L.onz, L.aligned);
+  }
+}
+
+// validates the layout, uploads the message bytes into ctx->misc; *n = width * height, *hasN = all three normal fields present
+int pc2Stage(b200reg_ctx* ctx, const uint8_t* data, size_t bytes, const b200reg_pc2_layout* L, Pc2Dev* dev, int64_t* n, bool* hasN) {
+  *n = (int64_t)L->width * (int64_t)L->height;
+  if (*n >= (int64_t)0x7fffffff) return setErr(ctx, B200REG_E_INVALID_PARAM, "pointcloud2: too many points");
+  *hasN = L->off_normal_x >= 0 && L->off_normal_y >= 0 && L->off_normal_z >= 0;
+  const int offs[6] = {L->off_x, L->off_y, L->off_z, L->off_normal_x, L->off_normal_y, L->off_normal_z};
+  if (L->off_x < 0 || L->off_y < 0 || L->off_z < 0)   // the iterator throws "Field x does not exist" (point_cloud2_iterator.h)
+    return setErr(ctx, B200REG_E_INVALID_FIELD, "pointcloud2: fields x, y, z are required (3-D clouds)");
+  int aligned = (L->point_step % 4 == 0) ? 1 : 0;
+  for (int k = 0; k < (*hasN ? 6 : 3); ++k) {
+    if ((uint32_t)offs[k] + 4u > L->point_step) return setErr(ctx, B200REG_E_INVALID_PARAM, "pointcloud2: field offset %d beyond point_step %u", offs[k], L->point_step);
+    if (offs[k] % 4 != 0) aligned = 0;
+  }
+  if (*n > 0 && (!data || bytes < (size_t)*n * L->point_step)) return setErr(ctx, B200REG_E_INVALID_PARAM, "pointcloud2: data holds %zu bytes, width * height * point_step = %zu", bytes, (size_t)*n * L->point_step);
+  *dev = Pc2Dev{L->point_step, offs[0], offs[1], offs[2], offs[3], offs[4], offs[5], aligned};
+  if (*n == 0) return B200REG_OK;
+  const size_t need = (size_t)*n * L->point_step;
+  TRY(ensureBuf(ctx, ctx->misc, need + 64));
+  CUDA_TRY(ctx, cudaMemcpyAsync(ctx->misc.p, data, need, cudaMemcpyHostToDevice, ctx->stream));
+  return B200REG_OK;
+}
+
 }  // namespace
 
 extern "C" {
@@ -813,4 +871,60 @@ int32_t b200reg_cloud64_estimate_normals(b200reg_ctx* ctx, b200reg_cloud64* inou
   b200reg_cloud_free(ctx, tmp);
   return code;
 }
+int32_t b200reg_cloud_from_pointcloud2(b200reg_ctx* ctx, const uint8_t* data, size_t data_bytes, const b200reg_pc2_layout* layout,
+                                       b200reg_cloud** out) {
+  if (!ctx || !layout || !out) return setErr(ctx, B200REG_E_INVALID_PARAM, "cloud_from_pointcloud2: bad arguments");
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  Pc2Dev dev;
+  int64_t n = 0;
+  bool hasN = false;
+  TRY(pc2Stage(ctx, data, data_bytes, layout, &dev, &n, &hasN));
+  const bool fresh = (*out == nullptr);
+  b200reg_cloud* c = fresh ? new b200reg_cloud() : *out;
+  if (c->cap < n || c->cap == 0 || (hasN && !c->nrm)) {
+    devFree(ctx, c->xyz); devFree(ctx, c->nrm);
+    c->xyz = c->nrm = nullptr;
+    c->n = 0;
+    c->cap = n + n / 4 + 1024;
+    cudaError_t e = devAlloc(ctx, &c->xyz, sizeof(float4) * (size_t)c->cap);
+    if (e == cudaSuccess && hasN) e = devAlloc(ctx, &c->nrm, sizeof(float4) * (size_t)c->cap);
+    if (e != cudaSuccess) {
+      devFree(ctx, c->xyz);
+      c->xyz = nullptr;
+      c->cap = 0;
+      if (fresh) delete c;
+      return setErr(ctx, B200REG_E_OOM, "cloud_from_pointcloud2: %s", cudaGetErrorString(e));
+    }
+  }
+  if (!hasN && c->nrm) { devFree(ctx, c->nrm); c->nrm = nullptr; }
+  c->n = n;
+  *out = c;
+  if (n > 0) {
+    pc2ToF32Kernel<<<divUp(n, 256), 256, 0, ctx->stream>>>((const unsigned char*)ctx->misc.p, n, dev, c->xyz, hasN ? c->nrm : nullptr);
+    LAUNCH_CHECK(ctx);
+    CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));   // the message buffer may be reused by the caller
+  }
+  return B200REG_OK;
+}
+
+int32_t b200reg_cloud64_from_pointcloud2(b200reg_ctx* ctx, const uint8_t* data, size_t data_bytes, const b200reg_pc2_layout* layout,
+                                         b200reg_cloud64** out) {
+  if (!ctx || !layout || !out) return setErr(ctx, B200REG_E_INVALID_PARAM, "cloud64_from_pointcloud2: bad arguments");
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  Pc2Dev dev;
+  int64_t n = 0;
+  bool hasN = false;
+  TRY(pc2Stage(ctx, data, data_bytes, layout, &dev, &n, &hasN));
+  TRY(cloud64Out(ctx, out, n));
+  b200reg_cloud64* c = *out;
+  c->hasNormals = hasN;
+  c->n = n;
+  if (n > 0) {
+    pc2ToF64Kernel<<<divUp(n, 256), 256, 0, ctx->stream>>>((const unsigned char*)ctx->misc.p, n, dev, c->xyz, hasN ? c->nrm : nullptr);
+    LAUNCH_CHECK(ctx);
+    CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  }
+  return B200REG_OK;
+}
+
 }  // extern "C"

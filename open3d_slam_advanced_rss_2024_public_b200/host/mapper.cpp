@@ -84,10 +84,9 @@ void Mapper::setMapToRangeSensor(const double T[16]) {
 
 // ScanToMapIcp::processForScanMatchingAndMerging (ScanToMapRegistration.cpp:36-69), every step on the device: the raw scan is
 // the only host -> device copy of a mapping step
-bool Mapper::process(const double* xyz, const double* normals, int64_t n) {
+bool Mapper::process() {
   StageClock clk;
   auto fail = [&]() { error_ = b200reg_last_error(ctx_); return false; };
-  if (b200reg_cloud64_upload(ctx_, xyz, normals, n, &raw_) != B200REG_OK) return fail();
   // wide crop: mapBuilderCropper_->crop(in) — that cropper instance never gets a pose, i.e. it sits at the identity (:30-37)
   const b200reg_crop_spec wide = at(params_.mapBuilderCropper, nullptr);
   if (b200reg_cloud64_crop(ctx_, &wide, raw_, &cropped_) != B200REG_OK) return fail();
@@ -144,10 +143,26 @@ bool Mapper::insert() {
 bool Mapper::addRangeMeasurement(const double* xyz, const double* normals, int64_t n, double time, const double odom[16]) {
   stats_ = MapperStepStats();
   error_.clear();
+  StageClock clk;
+  if (b200reg_cloud64_upload(ctx_, xyz, normals, n, &raw_) != B200REG_OK) { error_ = b200reg_last_error(ctx_); return false; }
+  clk.lap(&stats_.stageMs[MapperStepStats::kWideCrop]);   // (the upload is booked with the first stage)
+  return step(time, odom);
+}
+
+bool Mapper::addRangeMeasurementPointCloud2(const uint8_t* data, size_t bytes, const b200reg_pc2_layout& layout, double time, const double odom[16]) {
+  stats_ = MapperStepStats();
+  error_.clear();
+  StageClock clk;
+  if (b200reg_cloud64_from_pointcloud2(ctx_, data, bytes, &layout, &raw_) != B200REG_OK) { error_ = b200reg_last_error(ctx_); return false; }
+  clk.lap(&stats_.stageMs[MapperStepStats::kWideCrop]);
+  return step(time, odom);
+}
+
+bool Mapper::step(double time, const double odom[16]) {
   // ---- first scan (Mapper.cpp:179-193)
   if (b200reg_map_size(map_) == 0) {
     std::memcpy(mapToRangeSensorPrev_, mapToRangeSensor_, sizeof(mapToRangeSensor_));
-    if (!process(xyz, normals, n)) return false;
+    if (!process()) return false;
     if (!insert()) return false;
     std::memcpy(odomPrev_, odom, sizeof(odomPrev_));   // (the reference reads its odometry buffer at the previous scan's stamp)
     haveOdomPrev_ = true;
@@ -166,7 +181,7 @@ bool Mapper::addRangeMeasurement(const double* xyz, const double* normals, int64
     mul(mapToRangeSensorPrev_, motion, estimate);
   }
   // ---- scan processing and the fp64 -> fp32 conversion (:307-309)
-  if (!process(xyz, normals, n)) return false;
+  if (!process()) return false;
   stats_.readingPoints = b200reg_cloud64_size(match_);
   stats_.mergePoints = b200reg_cloud64_size(merge_);
   StageClock clk;

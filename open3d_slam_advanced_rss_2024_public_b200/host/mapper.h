@@ -68,6 +68,11 @@ class Mapper {
   // the external odometry at `time`.  Returns false where the reference returns false (empty map patch, failed initReference).
   bool addRangeMeasurement(const double* xyz, const double* normals, int64_t n, double time, const double odomToRangeSensor[16]);
 
+  // the same step fed with the sensor_msgs/PointCloud2 bytes of the scan (SlamWrapperRos's rosToOpen3d + addRangeScan path,
+  // open3d_conversions.cpp:203-244): the message is deserialised on the device, nothing else crosses PCIe
+  bool addRangeMeasurementPointCloud2(const uint8_t* data, size_t bytes, const b200reg_pc2_layout& layout, double time,
+                                      const double odomToRangeSensor[16]);
+
   const double* mapToRangeSensor() const { return mapToRangeSensor_; }
   b200reg_map* map() { return map_; }
   const MapperStepStats& lastStats() const { return stats_; }
@@ -75,7 +80,8 @@ class Mapper {
 
  private:
   // ProcessedScans (ScanToMapRegistration.hpp): merge_ (wide) and match_ (narrow), device-resident fp64 clouds reused scan after scan
-  bool process(const double* xyz, const double* normals, int64_t n);
+  bool process();   // raw_ -> merge_ / match_
+  bool step(double time, const double odomToRangeSensor[16]);
   bool insert();
 
   b200reg_ctx* ctx_;

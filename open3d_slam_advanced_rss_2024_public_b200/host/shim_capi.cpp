@@ -240,6 +240,20 @@ int32_t b200map_add_range_measurement(void* m, const double* xyz, const double* 
   setMsg(err, err_cap, mp->lastError());
   return ok ? 1 : 0;
 }
+int32_t b200map_add_pointcloud2(void* m, const uint8_t* data, size_t bytes, const b200reg_pc2_layout* layout, double time, const double odom[16],
+                                double pose_out[16], b200map_stats* stats, char* err, int32_t err_cap) {
+  b200::Mapper* mp = (b200::Mapper*)m;
+  const bool ok = layout && mp->addRangeMeasurementPointCloud2(data, bytes, *layout, time, odom);
+  std::memcpy(pose_out, mp->mapToRangeSensor(), sizeof(double) * 16);
+  if (stats) {
+    const b200::MapperStepStats& s = mp->lastStats();
+    *stats = b200map_stats{s.iterations, s.icpStatus, s.referenceRefreshed, s.inserted, s.readingPoints, s.mergePoints, s.patchPoints, s.mapPoints, {}};
+    for (int i = 0; i < b200::MapperStepStats::kStages; ++i) stats->stage_ms[i] = s.stageMs[i];
+    stats->carved_points = s.carvedPoints;
+  }
+  setMsg(err, err_cap, mp->lastError());
+  return ok ? 1 : 0;
+}
 b200reg_map* b200map_map(void* m) { return ((b200::Mapper*)m)->map(); }
 
 }  // extern "C"

@@ -32,6 +32,9 @@ def _lib():
         L.b200map_add_range_measurement.restype = C.c_int32
         L.b200map_add_range_measurement.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_double, C.c_void_p, C.c_void_p,
                                                     C.POINTER(MapperStats), C.c_char_p, C.c_int32]
+        L.b200map_add_pointcloud2.restype = C.c_int32
+        L.b200map_add_pointcloud2.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.POINTER(capi.Pc2Layout), C.c_double, C.c_void_p, C.c_void_p,
+                                              C.POINTER(MapperStats), C.c_char_p, C.c_int32]
         L.b200map_map.restype = C.c_void_p
         L.b200map_map.argtypes = [C.c_void_p]
         L._b200map_ready = True
@@ -68,6 +71,17 @@ class Mapper:
         ok = _lib().b200map_add_range_measurement(self.h, xyz.ctypes.data_as(C.c_void_p), None if nrm is None else nrm.ctypes.data_as(C.c_void_p),
                                                   xyz.shape[0], float(time), odom.ctypes.data_as(C.c_void_p), pose.ctypes.data_as(C.c_void_p),
                                                   C.byref(st), err, len(err))
+        return bool(ok), pose.reshape(4, 4), st, err.value.decode("utf-8", "replace")
+
+    def add_pointcloud2(self, data, layout, time, odom):
+        """The same step fed with the bytes of a sensor_msgs/PointCloud2 (layout: capi.pc2_layout)."""
+        data = np.ascontiguousarray(np.frombuffer(data, dtype=np.uint8) if not isinstance(data, np.ndarray) else data.view(np.uint8).reshape(-1))
+        odom = np.ascontiguousarray(odom, dtype=np.float64).reshape(16)
+        pose = np.zeros(16, dtype=np.float64)
+        st = MapperStats()
+        err = C.create_string_buffer(1024)
+        ok = _lib().b200map_add_pointcloud2(self.h, data.ctypes.data_as(C.c_void_p), data.size, C.byref(layout), float(time),
+                                            odom.ctypes.data_as(C.c_void_p), pose.ctypes.data_as(C.c_void_p), C.byref(st), err, len(err))
         return bool(ok), pose.reshape(4, 4), st, err.value.decode("utf-8", "replace")
 
     def map_points(self):

@@ -1408,4 +1408,25 @@ int64_t orc_carve(const double* scan_xyz, int64_t n_scan, const double sensor[3]
 }
 
 
+// sensor_msgs/PointCloud2 -> clouds.  RosPointCloud2Deserializer<float>::deserialize (pointmatcher_ros/src/
+// RosPointCloud2Deserializer.cpp:9-38,113-143,213-232) and open3d_conversions::rosToOpen3d (open3d_conversions.cpp:203-244) both
+// walk the message with sensor_msgs::PointCloud2ConstIterator<float>: element i of a field = the 4 bytes at
+// data + i * point_step + offset read as a float (no datatype conversion, row_step unused).  offs = {x, y, z, normal_x, normal_y,
+// normal_z}; the normals are taken when all three offsets are >= 0.  feat4 (nullable): x y z 1; xyz64 (nullable): doubles.
+int32_t orc_pointcloud2(const uint8_t* data, int64_t n, uint32_t point_step, const int32_t offs[6], float* feat4, float* nrm3,
+                        double* xyz64, double* nrm64) {
+  const bool hasN = offs[3] >= 0 && offs[4] >= 0 && offs[5] >= 0;
+  if (offs[0] < 0 || offs[1] < 0 || offs[2] < 0) return ORC_E_FIELD;
+  for (int64_t i = 0; i < n; ++i) {
+    const uint8_t* p = data + (size_t)i * point_step;
+    float v[6] = {0, 0, 0, 0, 0, 0};
+    for (int k = 0; k < (hasN ? 6 : 3); ++k) std::memcpy(&v[k], p + offs[k], 4);
+    if (feat4) { feat4[4 * i] = v[0]; feat4[4 * i + 1] = v[1]; feat4[4 * i + 2] = v[2]; feat4[4 * i + 3] = 1.f; }
+    if (xyz64) for (int d = 0; d < 3; ++d) xyz64[3 * i + d] = (double)v[d];
+    if (hasN && nrm3) for (int d = 0; d < 3; ++d) nrm3[3 * i + d] = v[3 + d];
+    if (hasN && nrm64) for (int d = 0; d < 3; ++d) nrm64[3 * i + d] = (double)v[3 + d];
+  }
+  return ORC_OK;
+}
+
 }  // extern "C"

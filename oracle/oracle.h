@@ -122,6 +122,8 @@ int64_t orc_voxel_down_sample(double voxel, const double* xyz, const double* nrm
 int64_t orc_carve(const double* scan_xyz, int64_t n_scan, const double sensor[3], const double* map_xyz, const double* map_nrm,
                   int64_t n_map, const orc_crop_spec* spec, double voxel, double max_ray_length, double truncation, double min_dot,
                   uint8_t* remove_mask);   /* Submap.cpp:130-144 + helpers.cpp:245-281; scan already in the map frame */
+int32_t orc_pointcloud2(const uint8_t* data, int64_t n, uint32_t point_step, const int32_t offs[6], float* feat4, float* nrm3,
+                        double* xyz64, double* nrm64);   /* RosPointCloud2Deserializer.cpp:9-38,113-143,213-232; open3d_conversions.cpp:203-244 */
 void    orc_o3d_to_pm(const double* xyz, const double* nrm, int64_t n, float* feat4, float* nrm3);   /* open3d_conversions.cpp:57-118 */
 
 #ifdef __cplusplus

@@ -323,6 +323,19 @@ def carve(scan_xyz, sensor, map_xyz, map_nrm, spec, voxel=0.1, max_ray_length=20
     return mask.astype(bool)
 
 
+def pointcloud2(data, n, point_step, fields):
+    """PointCloud2 bytes -> (feat4 f32, normals f32 | None, xyz f64, normals f64 | None); fields = {name: byte offset}."""
+    data = np.ascontiguousarray(np.frombuffer(data, dtype=np.uint8) if not isinstance(data, np.ndarray) else data.view(np.uint8).reshape(-1))
+    offs = np.array([fields.get(k, -1) for k in ("x", "y", "z", "normal_x", "normal_y", "normal_z")], dtype=np.int32)
+    has_n = bool((offs[3:] >= 0).all())
+    f4, x64 = np.zeros((n, 4), dtype=np.float32), np.zeros((n, 3), dtype=np.float64)
+    n3 = np.zeros((n, 3), dtype=np.float32) if has_n else None
+    n64 = np.zeros((n, 3), dtype=np.float64) if has_n else None
+    lib().orc_pointcloud2.argtypes = [C.c_void_p, C.c_int64, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+    st = lib().orc_pointcloud2(_p(data), n, point_step, _p(offs), _p(f4), _p(n3), _p(x64), _p(n64))
+    return st, f4, n3, x64, n64
+
+
 def voxel_down_sample(voxel, xyz, nrm=None):
     xyz, nrm = _f64(xyz), _f64(nrm)
     xo = np.empty_like(xyz)

@@ -265,3 +265,34 @@ def test_map_carve_matches_oracle(ctx, oracle, with_normals):
     assert m.carve(np.zeros((0, 3)), pose, sg) == 0
     with pytest.raises(capi.InvalidParameter):
         m.carve(raw, pose, sg, voxel_size=0.0)
+
+
+@pytest.mark.parametrize("fields,step", [({"x": 0, "y": 4, "z": 8}, 12), ({"x": 0, "y": 4, "z": 8, "normal_x": 12, "normal_y": 16, "normal_z": 20}, 24),
+                                         ({"x": 0, "y": 4, "z": 8, "normal_x": 16, "normal_y": 20, "normal_z": 24}, 48),
+                                         ({"z": 1, "x": 9, "y": 5, "normal_x": 13, "normal_y": 17}, 23)])
+def test_pointcloud2_to_device_clouds(ctx, oracle, fields, step):
+    """sensor_msgs/PointCloud2 bytes -> fp32 cloud (RosPointCloud2Deserializer) and fp64 cloud (rosToOpen3d) on the device, bit for
+    bit against the oracle, incl. NaN returns, unaligned records, storage reuse, empty messages and the error cases."""
+    from open3d_slam_advanced_rss_2024_public_b200 import capi
+    from test_oracle_golden import _pc2_message
+    c32 = c64 = None
+    for n, (w, h) in ((64, (64, 1)), (131072, (1024, 128))):          # second pass reuses and grows the clouds
+        data, _ = _pc2_message(n, fields, step, 5 + n)
+        st, f4, n3, x64, n64 = oracle.pointcloud2(data, n, step, fields)
+        L = capi.pc2_layout(w, h, step, fields)
+        c32 = ctx.cloud_from_pointcloud2(data, L, out=c32)
+        g4, gn = c32.download()
+        assert np.array_equal(g4.view(np.uint32), f4.view(np.uint32))
+        assert (gn is None) == (n3 is None) and (gn is None or np.array_equal(gn.view(np.uint32), n3.view(np.uint32)))
+        c64 = ctx.cloud64_from_pointcloud2(data, L, out=c64)
+        gx, gn64 = c64.download()
+        assert np.array_equal(gx.view(np.uint64), x64.view(np.uint64))
+        assert (gn64 is None) == (n64 is None) and (gn64 is None or np.array_equal(gn64, n64))
+    assert ctx.cloud_from_pointcloud2(np.zeros(0, np.uint8), capi.pc2_layout(0, 0, step, fields)).size == 0
+    assert ctx.cloud64_from_pointcloud2(np.zeros(0, np.uint8), capi.pc2_layout(0, 1, step, fields)).size == 0
+    with pytest.raises(capi.InvalidField):
+        ctx.cloud_from_pointcloud2(data, capi.pc2_layout(w, h, step, {"x": 0, "y": 4}))
+    with pytest.raises(capi.InvalidParameter):
+        ctx.cloud_from_pointcloud2(data[:-1], L)                        # buffer shorter than width * height * point_step
+    with pytest.raises(capi.InvalidParameter):
+        ctx.cloud64_from_pointcloud2(data, capi.pc2_layout(w, h, step, dict(fields, x=step - 2)))

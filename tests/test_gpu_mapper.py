@@ -275,3 +275,36 @@ def test_mapping_loop_with_space_carving(ctx, oracle):
     gx, _ = gm.map_points()
     assert gx.shape[0] == om.map_xyz.shape[0] and np.abs(gx - om.map_xyz).max() < 2e-4
     gm.close()
+
+
+def test_mapper_pointcloud2_entry_equals_array_entry(ctx):
+    """Feeding the mapping step with sensor_msgs/PointCloud2 bytes (an Ouster-like 48-byte record, x y z as FLOAT32) gives exactly the
+    poses, counts and map of feeding it the same points as an fp64 array (rosToOpen3d widens the floats exactly)."""
+    from open3d_slam_advanced_rss_2024_public_b200 import capi
+    from open3d_slam_advanced_rss_2024_public_b200.mapper import Mapper
+    scene = scenes.Scene(2001, size=(40.0, 24.0, 8.0), n_boxes=14, n_cyl=8)
+    poses = trajectory(5)
+    odom = drifting_odometry(poses, 2005)
+    icp = capi.icp_config(knn=1, max_dist=0.5, trim_ratio=0.9, max_angle=1.57, max_iter=15, min_diff_rot=1e-3, min_diff_trans=1e-2, smooth_length=3)
+    mk = lambda: Mapper(ctx, capi.crop_spec(capi.CROP_MINMAX_RADIUS, np.zeros(3), rmin=1.0, rmax=30.0),  # noqa: E731
+                        capi.crop_spec(capi.CROP_MAX_RADIUS, np.zeros(3), rmax=25.0), icp, scan_voxel_size=0.25, normals_knn=10,
+                        normals_radius=1.0, map_voxel_size=0.3, min_movement=0.0, reference_period=0.25)
+    ma, mb = mk(), mk()
+    ma.set_pose(poses[0]); mb.set_pose(poses[0])
+    fields, step = {"x": 0, "y": 4, "z": 8}, 48
+    for i, (T, od) in enumerate(zip(poses, odom)):
+        scan = scenes.lidar_scan(scene, T, n_beams=32, n_az=360, noise_sigma=0.01, seed=900 + i).astype(np.float32)
+        n = scan.shape[0]
+        buf = np.random.default_rng(i).integers(0, 256, size=(n, step), dtype=np.uint8)
+        buf[:, :12] = scan.view(np.uint8).reshape(n, 12)
+        ok_a, pose_a, st_a, err_a = ma.add_range_measurement(scan.astype(np.float64), 0.1 * i, od)
+        ok_b, pose_b, st_b, err_b = mb.add_pointcloud2(buf.reshape(-1), capi.pc2_layout(n, 1, step, fields), 0.1 * i, od)
+        assert ok_a and ok_b, (err_a, err_b)
+        assert np.array_equal(pose_a, pose_b), i
+        assert (st_a.iterations, st_a.reading_points, st_a.merge_points, st_a.map_points) == (st_b.iterations, st_b.reading_points, st_b.merge_points, st_b.map_points)
+    xa, na = ma.map_points()
+    xb, nb = mb.map_points()
+    assert np.array_equal(xa, xb) and np.array_equal(na, nb)
+    ok, _, _, err = mb.add_pointcloud2(buf.reshape(-1)[:100], capi.pc2_layout(n, 1, step, fields), 1.0, odom[-1])
+    assert not ok and "point_step" in err
+    ma.close(); mb.close()

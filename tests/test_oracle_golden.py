@@ -334,3 +334,40 @@ def test_distance_outlier_filters_known_answers(oracle):
     assert oracle.dist_outlier(2, np.full(4, np.inf, dtype=np.float32), 3.0)[0] != 0                # no finite match: ConvergenceError
     x = np.float32(0.3)                                                                             # pow(float, 2) in double, rounded once
     assert oracle.dist_outlier(0, d2, float(x))[1] == np.float32(np.float64(x) ** 2) == x * x
+
+
+def _pc2_message(n, fields, point_step, seed, dtype_override=None):
+    """A sensor_msgs/PointCloud2 data buffer: `fields` = {name: byte offset}; every listed field holds a FLOAT32; the rest of each
+    point record is random bytes (intensity, ring, time ... of a real driver)."""
+    rng = np.random.default_rng(seed)
+    buf = rng.integers(0, 256, size=(n, point_step), dtype=np.uint8)
+    vals = {}
+    for name, off in fields.items():
+        v = rng.normal(size=n).astype(np.float32) * 20
+        if name == "x" and n > 3:
+            v[3] = np.nan          # invalid returns stay in the cloud (is_dense = false)
+        vals[name] = v
+        buf[:, off:off + 4] = v.view(np.uint8).reshape(n, 4)
+    return buf.reshape(-1), vals
+
+
+@pytest.mark.parametrize("fields,step", [({"x": 0, "y": 4, "z": 8}, 12), ({"x": 0, "y": 4, "z": 8, "normal_x": 12, "normal_y": 16, "normal_z": 20}, 24),
+                                         ({"x": 0, "y": 4, "z": 8, "normal_x": 16, "normal_y": 20, "normal_z": 24}, 48),
+                                         ({"z": 1, "x": 9, "y": 5, "normal_x": 13, "normal_y": 17}, 23)])
+def test_pointcloud2_deserialisation_layouts(oracle, fields, step):
+    """orc_pointcloud2 against numpy on the layouts of RosPointCloud2DeserializerTest.cpp:195-399 (points; points + normals) plus an
+    Ouster-like 48-byte record and a packed, unaligned one: value = bytes at i * point_step + offset as float32; features get
+    pad = 1; normals only when all three fields exist; the fp64 side is the exact widening of the floats."""
+    n = 257
+    data, vals = _pc2_message(n, fields, step, 11)
+    st, f4, n3, x64, n64 = oracle.pointcloud2(data, n, step, fields)
+    assert st == 0
+    want = np.stack([vals["x"], vals["y"], vals["z"]], axis=1)
+    assert np.array_equal(f4[:, :3].view(np.uint32), want.view(np.uint32)) and (f4[:, 3] == 1).all()
+    assert np.array_equal(x64, want.astype(np.float64), equal_nan=True)
+    if "normal_z" in fields:
+        wn = np.stack([vals["normal_x"], vals["normal_y"], vals["normal_z"]], axis=1)
+        assert np.array_equal(n3, wn) and np.array_equal(n64, wn.astype(np.float64))
+    else:
+        assert n3 is None and n64 is None
+    assert oracle.pointcloud2(data, n, step, {"x": 0, "y": 4})[0] != 0   # "Field z does not exist"
