@@ -296,6 +296,22 @@ int32_t b200reg_cloud_from_pointcloud2(b200reg_ctx* ctx, const uint8_t* data, si
 int32_t b200reg_cloud64_from_pointcloud2(b200reg_ctx* ctx, const uint8_t* data, size_t data_bytes, const b200reg_pc2_layout* layout,
                                          b200reg_cloud64** out);
 
+/* ---- loop-closure support operations around b200reg_icp_register_batch --------------------------------- */
+/* computeIndicesOfOverlappingPoints (open3d_slam/src/helpers.cpp:320-345; call site PlaceRecognition.cpp:100-106): source is moved
+ * by T (PointCloud::Transform), both clouds are binned with key = floor(p / voxel_size); a point is in the overlap when its voxel
+ * holds >= min_points_per_voxel source AND target points.  idx_*_out (HOST, room for the cloud's size, nullable): ascending point
+ * indices (the reference emits them in unordered_map order — a set either way). */
+int32_t b200reg_overlap_indices(b200reg_ctx* ctx, const b200reg_cloud64* source, const b200reg_cloud64* target,
+                                const double T_source_to_target[16], double voxel_size, int64_t min_points_per_voxel,
+                                int64_t* idx_source_out, int64_t* n_source_out, int64_t* idx_target_out, int64_t* n_target_out);
+/* open3d::pipelines::registration::GetInformationMatrixFromPointClouds (Open3D v0.15.1, external; call sites
+ * PlaceRecognition.cpp:148-149, constraint_builders.cpp:71-72): every source point moved by T takes its nearest target point
+ * within max_correspondence_distance (the path's fp32 k = 1 search); info_out = sum over correspondences of G^T G with
+ * G = [-[q]x | I] of the matched TARGET point q, 6x6 row-major, unknown order (rotation, translation), accumulated in fp64. */
+int32_t b200reg_information_matrix(b200reg_ctx* ctx, const b200reg_cloud64* source, const b200reg_cloud64* target,
+                                   double max_correspondence_distance, const double T_source_to_target[16], double info_out[36],
+                                   int64_t* n_correspondences);
+
 #ifdef __cplusplus
 }
 #endif

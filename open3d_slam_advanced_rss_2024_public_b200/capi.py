@@ -161,6 +161,8 @@ SYMBOLS = {
     "b200reg_map_insert_cloud64": (C.c_int32, [_VP, _VP, _VP, _VP, C.POINTER(CropSpec)]),
     "b200reg_cloud_from_pointcloud2": (C.c_int32, [_VP, _VP, C.c_size_t, C.POINTER(Pc2Layout), C.POINTER(_VP)]),
     "b200reg_cloud64_from_pointcloud2": (C.c_int32, [_VP, _VP, C.c_size_t, C.POINTER(Pc2Layout), C.POINTER(_VP)]),
+    "b200reg_overlap_indices": (C.c_int32, [_VP, _VP, _VP, _VP, C.c_double, C.c_int64, _VP, C.POINTER(C.c_int64), _VP, C.POINTER(C.c_int64)]),
+    "b200reg_information_matrix": (C.c_int32, [_VP, _VP, _VP, C.c_double, _VP, _VP, C.POINTER(C.c_int64)]),
     "b200reg_map_carve": (C.c_int32, [_VP, _VP, _VP, C.c_int64, _VP, C.POINTER(CropSpec), C.POINTER(CarveParams), C.POINTER(C.c_int64)]),
     "b200reg_map_carve_cloud64": (C.c_int32, [_VP, _VP, _VP, _VP, C.POINTER(CropSpec), C.POINTER(CarveParams), C.POINTER(C.c_int64)]),
 }
@@ -304,6 +306,23 @@ class Context:
         c = out if out is not None else Cloud64(self)
         self.check(lib().b200reg_cloud64_from_pointcloud2(self.h, _p(data) if data.size else None, data.size, C.byref(layout), C.byref(c.h)))
         return c
+
+    def overlap_indices(self, source, target, T_source_to_target, voxel_size, min_points_per_voxel=1):
+        """computeIndicesOfOverlappingPoints on two Cloud64: ascending indices (source, target) of the points in shared voxels."""
+        T = _f64(T_source_to_target).reshape(16)
+        si, ti = np.empty(source.size, dtype=np.int64), np.empty(target.size, dtype=np.int64)
+        ns, nt = C.c_int64(0), C.c_int64(0)
+        self.check(lib().b200reg_overlap_indices(self.h, source.h, target.h, _p(T), float(voxel_size), int(min_points_per_voxel),
+                                                 _p(si), C.byref(ns), _p(ti), C.byref(nt)))
+        return si[:ns.value], ti[:nt.value]
+
+    def information_matrix(self, source, target, max_correspondence_distance, T_source_to_target):
+        """GetInformationMatrixFromPointClouds on two Cloud64: (6 x 6 fp64, number of correspondences)."""
+        T = _f64(T_source_to_target).reshape(16)
+        info = np.zeros(36, dtype=np.float64)
+        nc = C.c_int64(0)
+        self.check(lib().b200reg_information_matrix(self.h, source.h, target.h, float(max_correspondence_distance), _p(T), _p(info), C.byref(nc)))
+        return info.reshape(6, 6), nc.value
 
     def build_index(self, cloud, cell=0.0):
         h = _VP()

@@ -71,6 +71,15 @@ struct GridDesc {
   int nx, ny, nz;
 };
 
+// device-resident mirror of an open3d::geometry::PointCloud (fp64 points + optional normals): what travels between the
+// scan-processing steps of ScanToMapRegistration.cpp:36-69 without touching the host
+struct b200reg_cloud64 {
+  int64_t n = 0, cap = 0;
+  double* xyz = nullptr;
+  double* nrm = nullptr;   // allocated with xyz; valid iff hasNormals
+  bool hasNormals = false;
+};
+
 struct b200reg_index {
   int64_t m = 0;
   float4* pts = nullptr;       // sorted by cell: x y z (centred) + original index bits in .w

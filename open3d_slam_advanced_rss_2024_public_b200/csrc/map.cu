@@ -29,15 +29,6 @@ struct b200reg_map {
   bool hasNormals = false;
 };
 
-// device-resident mirror of an open3d::geometry::PointCloud (fp64 points + optional normals): what travels between the
-// scan-processing steps of ScanToMapRegistration.cpp:36-69 without touching the host
-struct b200reg_cloud64 {
-  int64_t n = 0, cap = 0;
-  double* xyz = nullptr;
-  double* nrm = nullptr;   // allocated with xyz; valid iff hasNormals
-  bool hasNormals = false;
-};
-
 namespace {
 
 typedef unsigned long long u64;

@@ -1429,4 +1429,64 @@ int32_t orc_pointcloud2(const uint8_t* data, int64_t n, uint32_t point_step, con
   return ORC_OK;
 }
 
+// computeIndicesOfOverlappingPoints (open3d_slam/src/helpers.cpp:320-345): masks of the source / target points whose voxel
+// (key = int(floor(p * (1/voxel))), source moved by Open3D's PointCloud::Transform first) holds >= min_pts points of BOTH clouds.
+void orc_overlap(const double* src, int64_t n_src, const double* tgt, int64_t n_tgt, const double T[16], double voxel, int64_t min_pts,
+                 uint8_t* src_mask, uint8_t* tgt_mask) {
+  const double inv = 1.0 / voxel;
+  std::map<Key, std::pair<std::vector<int64_t>, std::vector<int64_t>>> vox;
+  for (int64_t i = 0; i < n_tgt; ++i) {
+    const double* p = tgt + 3 * i;
+    vox[Key((int)std::floor(p[0] * inv), (int)std::floor(p[1] * inv), (int)std::floor(p[2] * inv))].second.push_back(i);
+    tgt_mask[i] = 0;
+  }
+  for (int64_t i = 0; i < n_src; ++i) {
+    const double* p = src + 3 * i;
+    double q[4];
+    for (int r = 0; r < 4; ++r) q[r] = ((T[4 * r + 0] * p[0] + T[4 * r + 1] * p[1]) + T[4 * r + 2] * p[2]) + T[4 * r + 3] * 1.0;
+    const double x = q[0] / q[3], y = q[1] / q[3], z = q[2] / q[3];
+    vox[Key((int)std::floor(x * inv), (int)std::floor(y * inv), (int)std::floor(z * inv))].first.push_back(i);
+    src_mask[i] = 0;
+  }
+  for (const auto& kv : vox) {
+    if ((int64_t)kv.second.first.size() >= min_pts && (int64_t)kv.second.second.size() >= min_pts) {
+      for (int64_t i : kv.second.first) src_mask[i] = 1;
+      for (int64_t i : kv.second.second) tgt_mask[i] = 1;
+    }
+  }
+}
+
+// GetInformationMatrixFromPointClouds (Open3D v0.15.1 pipelines/registration/Registration.cpp, external): source moved by T,
+// nearest target point within max_dist (d2 < r2, fp64 brute force here), GTG += G_r^T G_r for the three rows
+// [0 z -y 1 0 0], [-z 0 x 0 1 0], [y -x 0 0 0 1] of the matched TARGET point.  Returns the number of correspondences.
+int64_t orc_information_matrix(const double* src, int64_t n_src, const double* tgt, int64_t n_tgt, double max_dist, const double T[16],
+                               double info[36]) {
+  for (int i = 0; i < 36; ++i) info[i] = 0.0;
+  std::vector<int64_t> match((size_t)n_src, -1);
+#pragma omp parallel for schedule(static)
+  for (int64_t i = 0; i < n_src; ++i) {
+    const double* p = src + 3 * i;
+    double q[4];
+    for (int r = 0; r < 4; ++r) q[r] = ((T[4 * r + 0] * p[0] + T[4 * r + 1] * p[1]) + T[4 * r + 2] * p[2]) + T[4 * r + 3] * 1.0;
+    const double x = q[0] / q[3], y = q[1] / q[3], z = q[2] / q[3];
+    double best = max_dist * max_dist;
+    for (int64_t j = 0; j < n_tgt; ++j) {
+      const double dx = x - tgt[3 * j], dy = y - tgt[3 * j + 1], dz = z - tgt[3 * j + 2];
+      const double d2 = (dx * dx + dy * dy) + dz * dz;
+      if (d2 < best) { best = d2; match[(size_t)i] = j; }
+    }
+  }
+  int64_t count = 0;
+  for (int64_t i = 0; i < n_src; ++i) {
+    if (match[(size_t)i] < 0) continue;
+    ++count;
+    const double* t = tgt + 3 * match[(size_t)i];
+    const double rows[3][6] = {{0, t[2], -t[1], 1, 0, 0}, {-t[2], 0, t[0], 0, 1, 0}, {t[1], -t[0], 0, 0, 0, 1}};
+    for (int r = 0; r < 3; ++r)
+      for (int a = 0; a < 6; ++a)
+        for (int b = 0; b < 6; ++b) info[6 * a + b] += rows[r][a] * rows[r][b];
+  }
+  return count;
+}
+
 }  // extern "C"

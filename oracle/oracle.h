@@ -124,6 +124,10 @@ int64_t orc_carve(const double* scan_xyz, int64_t n_scan, const double sensor[3]
                   uint8_t* remove_mask);   /* Submap.cpp:130-144 + helpers.cpp:245-281; scan already in the map frame */
 int32_t orc_pointcloud2(const uint8_t* data, int64_t n, uint32_t point_step, const int32_t offs[6], float* feat4, float* nrm3,
                         double* xyz64, double* nrm64);   /* RosPointCloud2Deserializer.cpp:9-38,113-143,213-232; open3d_conversions.cpp:203-244 */
+void    orc_overlap(const double* src, int64_t n_src, const double* tgt, int64_t n_tgt, const double T[16], double voxel, int64_t min_pts,
+                    uint8_t* src_mask, uint8_t* tgt_mask);   /* helpers.cpp:320-345 */
+int64_t orc_information_matrix(const double* src, int64_t n_src, const double* tgt, int64_t n_tgt, double max_dist, const double T[16],
+                               double info[36]);   /* Open3D v0.15.1 GetInformationMatrixFromPointClouds (external) */
 void    orc_o3d_to_pm(const double* xyz, const double* nrm, int64_t n, float* feat4, float* nrm3);   /* open3d_conversions.cpp:57-118 */
 
 #ifdef __cplusplus

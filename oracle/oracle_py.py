@@ -336,6 +336,26 @@ def pointcloud2(data, n, point_step, fields):
     return st, f4, n3, x64, n64
 
 
+def overlap(src, tgt, T, voxel, min_pts=1):
+    """computeIndicesOfOverlappingPoints: ascending indices (source, target)."""
+    src, tgt, T = _f64(src), _f64(tgt), _f64(T).reshape(16)
+    sm, tm = np.zeros(src.shape[0], dtype=np.uint8), np.zeros(tgt.shape[0], dtype=np.uint8)
+    lib().orc_overlap.restype = None
+    lib().orc_overlap.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_void_p, C.c_double, C.c_int64, C.c_void_p, C.c_void_p]
+    lib().orc_overlap(_p(src), src.shape[0], _p(tgt), tgt.shape[0], _p(T), voxel, min_pts, _p(sm), _p(tm))
+    return np.nonzero(sm)[0], np.nonzero(tm)[0]
+
+
+def information_matrix(src, tgt, max_dist, T):
+    """GetInformationMatrixFromPointClouds (fp64 brute-force correspondences): (6 x 6, count)."""
+    src, tgt, T = _f64(src), _f64(tgt), _f64(T).reshape(16)
+    info = np.zeros(36, dtype=np.float64)
+    lib().orc_information_matrix.restype = C.c_int64
+    lib().orc_information_matrix.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_double, C.c_void_p, C.c_void_p]
+    cnt = lib().orc_information_matrix(_p(src), src.shape[0], _p(tgt), tgt.shape[0], max_dist, _p(T), _p(info))
+    return info.reshape(6, 6), int(cnt)
+
+
 def voxel_down_sample(voxel, xyz, nrm=None):
     xyz, nrm = _f64(xyz), _f64(nrm)
     xo = np.empty_like(xyz)

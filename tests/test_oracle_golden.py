@@ -371,3 +371,40 @@ def test_pointcloud2_deserialisation_layouts(oracle, fields, step):
     else:
         assert n3 is None and n64 is None
     assert oracle.pointcloud2(data, n, step, {"x": 0, "y": 4})[0] != 0   # "Field z does not exist"
+
+
+def test_loop_closure_support_ops_known_answers(oracle):
+    """computeIndicesOfOverlappingPoints (helpers.cpp:320-345) and GetInformationMatrixFromPointClouds (Open3D v0.15.1) on cases with
+    hand-derived answers."""
+    O = oracle
+    # two unit-spaced rows of points; voxel 1.0: target occupies voxels x = 0..4, source (after a +2.5 shift) voxels 2..6
+    tgt = np.array([[i + 0.5, 0.5, 0.5] for i in range(5)] + [[0.6, 0.5, 0.5]])        # voxel 0 holds two target points
+    src = np.array([[i + 0.5 - 2.5 + 2.0, 0.5, 0.5] for i in range(5)])                 # x = 0, 1, 2, 3, 4 before the shift
+    T = np.eye(4); T[0, 3] = 2.5                                                          # -> 2.5 .. 6.5: voxels 2..6
+    si, ti = O.overlap(src, tgt, T, 1.0, 1)
+    assert si.tolist() == [0, 1, 2] and ti.tolist() == [2, 3, 4]                          # shared voxels 2, 3, 4
+    si, ti = O.overlap(src, tgt, np.eye(4), 1.0, 2)                                       # min 2 points per voxel on BOTH sides: none
+    assert si.size == 0 and ti.size == 0
+    si, ti = O.overlap(np.concatenate([src, src[:1] + 0.1]), tgt, np.eye(4), 1.0, 2)      # source x = 0 and 0.1 share voxel 0 with 0.5, 0.6
+    assert si.tolist() == [0, 5] and ti.tolist() == [0, 5]
+    # information matrix: one correspondence at q = (1, 2, 3): G^T G with G = [-[q]x | I]
+    info, cnt = O.information_matrix(np.array([[1.0, 2.0, 3.05]]), np.array([[1.0, 2.0, 3.0], [9.0, 9.0, 9.0]]), 0.1, np.eye(4))
+    q = np.array([1.0, 2.0, 3.0])
+    qx = np.array([[0, -q[2], q[1]], [q[2], 0, -q[0]], [-q[1], q[0], 0]])
+    G = np.hstack([-qx, np.eye(3)])
+    assert cnt == 1 and np.allclose(info, G.T @ G, rtol=0, atol=1e-12)
+    assert O.information_matrix(np.array([[1.0, 2.0, 3.2]]), np.array([[1.0, 2.0, 3.0]]), 0.1, np.eye(4))[1] == 0   # beyond the radius
+    # many points: equals the numpy restatement (correspondence = nearest target within the radius, d2 < r2)
+    rng = np.random.default_rng(4)
+    tg = rng.uniform(-5, 5, (400, 3)); sr = tg[rng.permutation(400)[:300]] + rng.normal(0, 0.02, (300, 3))
+    Tm = np.eye(4); Tm[:3, 3] = [0.01, -0.02, 0.005]
+    info, cnt = O.information_matrix(sr, tg, 0.05, Tm)
+    moved = sr + Tm[:3, 3]
+    d = np.linalg.norm(moved[:, None] - tg[None], axis=2)
+    j = d.argmin(axis=1); ok = d.min(axis=1) < 0.05
+    want = np.zeros((6, 6))
+    for t in tg[j[ok]]:
+        tx = np.array([[0, -t[2], t[1]], [t[2], 0, -t[0]], [-t[1], t[0], 0]])
+        Gm = np.hstack([-tx, np.eye(3)])
+        want += Gm.T @ Gm
+    assert cnt == int(ok.sum()) and cnt > 100 and np.allclose(info, want, rtol=1e-12)
