@@ -28,7 +28,7 @@ sys.path.insert(0, os.path.join(ROOT, "tests"))
 B_KNN1 = 536          # algorithmic bytes per k=1 query   (SURVEY 8d / BASELINE.md §5)
 B_ITER = 600          # algorithmic bytes per reading point per ICP iteration
 B_BUILD = 156         # algorithmic bytes per reference point for the index build
-NCU_TRAFFIC_BYTES = 35_330_000   # dram__bytes_read + write per match launch, mean of the 5 launches of one registration (profiles/r1/ncu_full_knn1_r1g.txt)
+NCU_TRAFFIC_BYTES = 32_980_000   # dram__bytes_read + write per match launch, mean of the 5 launches of one registration (profiles/r1/ncu_full_knn1_r1h.txt)
 ICP_KW = dict(knn=1, max_dist=1.0, trim_ratio=0.8, max_iter=40, min_diff_rot=1e-3, min_diff_trans=1e-2, smooth_length=3)
 
 
@@ -306,7 +306,7 @@ def main():
                    "wall_s_timed_region": wall_s, "result_gather_ms": gather_ms,
                    "parallelism": f"{world} independent registration streams, one per GPU (replicas; pair i -> rank i mod G), one NCCL all_gather of the results"},
         "knn_queries_per_s": n / (knn_t * 1e-3), "knn_visits_per_query": visits / n,
-        "roofline": {"bound": "hbm", "kernel": "knn1GroupKernel<8> (k = 1 match; knn1LoopKernel is the same body inside the graph loop)",
+        "roofline": {"bound": "hbm", "kernel": "knn1GroupKernel<8 | 4> (k = 1 match, lanes per query chosen per iteration as in the graph loop, where knn1LoopKernel is the same body)",
                      "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "traffic": NCU_TRAFFIC_BYTES, "peak_source": peak_src, "algorithmic_bytes_per_launch": B_KNN1 * n, "avg_launch_ms": knn_t,
                      "launch_ms_by_iteration": [float(x) for x in per_launch.mean(0)],

@@ -40,7 +40,7 @@ int launchSelect(b200reg_ctx* ctx, const float* d2, int64_t count, float ratio, 
 struct HostStep {   // what one iteration brings back over PCIe: NUM_MOM doubles + the select state + the visit counter
   double mom[NUM_MOM];
   SelState sel;
-  unsigned long long visits;
+  unsigned long long visits, far;   // dstate[0], dstate[1]: touched points, queries the 3x3x3 neighbourhood could not settle
 };
 
 // device part of one iteration: match -> select -> reduce -> async D2H into pinned memory (no sync here)
@@ -77,7 +77,7 @@ int enqueueStep(b200reg_ctx* ctx, const b200reg_index* ix, const float4* reading
   HostStep* h = (HostStep*)ctx->pinned;
   CUDA_TRY(ctx, cudaMemcpyAsync(h->mom, resultPtr(ctx), sizeof(double) * NUM_MOM, cudaMemcpyDeviceToHost, ctx->stream));
   CUDA_TRY(ctx, cudaMemcpyAsync(&h->sel, st, sizeof(SelState), cudaMemcpyDeviceToHost, ctx->stream));
-  CUDA_TRY(ctx, cudaMemcpyAsync(&h->visits, ctx->dstate, sizeof(unsigned long long), cudaMemcpyDeviceToHost, ctx->stream));
+  CUDA_TRY(ctx, cudaMemcpyAsync(&h->visits, ctx->dstate, 2 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, ctx->stream));
   return B200REG_OK;
 }
 
@@ -866,20 +866,27 @@ int32_t b200reg_icp_register(b200reg_icp* icp, const b200reg_cloud* reading, con
   const CheckerCfg ccfg{cfg.max_iter, cfg.smooth_length, cfg.min_diff_rot, cfg.min_diff_trans, cfg.bound_rot, cfg.bound_trans};
   CheckerState chk;
   checkersInit(chk, T_iter);
-  CUDA_TRY(ctx, cudaMemsetAsync(ctx->dstate, 0, sizeof(unsigned long long), ctx->stream));
+  CUDA_TRY(ctx, cudaMemsetAsync(ctx->dstate, 0, 2 * sizeof(unsigned long long), ctx->stream));
   CUDA_TRY(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
   int status = B200REG_OK;
   const HostStep* h = (const HostStep*)ctx->pinned;
+  unsigned long long farPrev = 0;
+  const int lanesCfg = ctx->knnLanes;
+  int lanesAuto = 8;   // the tail kernel's rule (icpTailKernel): 4 lanes per query once < 1/16 of the queries needed rings >= 2
   while (iterate) {
     if (!rigidOk(T_iter)) { status = setErr(ctx, B200REG_E_TRANSFORM, "RigidTransformation: Error, rotation matrix is not orthogonal."); break; }
+    if (lanesCfg == 0 && cfg.knn == 1) ctx->knnLanes = lanesAuto;
     status = enqueueStep(ctx, icp->index, (const float4*)icp->reading.p, needNrm ? (const float4*)icp->readingNrm.p : nullptr, n, T_iter,
                          cfg.knn, cfg.max_dist, cfg.trim_ratio, cfg.max_angle, cfg.force2D, st.iterations > 0 ? 1 : 0);
+    ctx->knnLanes = lanesCfg;
     if (status != B200REG_OK) break;
     cudaError_t e = cudaStreamSynchronize(ctx->stream);
     if (e != cudaSuccess) { status = setErr(ctx, B200REG_E_CUDA, "ICP iteration failed: %s", cudaGetErrorString(e)); break; }
     if (cfg.trim_ratio > 0.f && h->sel.error) { status = setErr(ctx, B200REG_E_NOT_CONVERGED, "No matches available for computing distance quantiles"); break; }
     if (h->mom[M_CNT] < 1.0) { status = setErr(ctx, B200REG_E_NOT_CONVERGED, "ErrorMnimizer: no point to minimize"); break; }
     st.kept_last = (int64_t)h->mom[M_CNT];
+    lanesAuto = ((h->far - farPrev) * 16ull < (unsigned long long)n) ? 4 : 8;
+    farPrev = h->far;
     st.point_used_ratio = (float)h->mom[M_CNT] / (float)total;
     st.overlap_ratio = st.point_used_ratio;
     st.last_tau = (cfg.trim_ratio > 0.f) ? *(const float*)&h->sel.tauBits : INFINITY;

@@ -487,7 +487,9 @@ __device__ __forceinline__ void knn1LoopBody(const IcpDevParams* __restrict__ P,
   int* ids = P->ids;
   float* d2 = P->d2;
   int* pos = P->pos;
-  const int* seed = (P->seedOn && S->iterations > 0) ? P->pos : nullptr;   // the previous iteration's matches (same reference)
+  // the previous iteration's matches (same reference) seed the search once far queries are rare (the 4-lane regime): while many
+  // queries still move by more than a cell per iteration the seed's extra dependent load costs more than its bound saves
+  const int* seed = (P->seedOn && S->iterations > 0 && G == 4) ? P->pos : nullptr;
   Rigid12 T;
 #pragma unroll
   for (int j = 0; j < 12; ++j) T.m[j] = S->T[j];
@@ -755,7 +757,7 @@ int runKnn(b200reg_ctx* ctx, const b200reg_index* ix, const float4* queries, int
   unsigned long long* visits = (unsigned long long*)ctx->dstate;
   const int hasT = T ? 1 : 0;
   profBegin(ctx);
-  const int* seed = (seeded && ctx->knnSeed) ? pos : nullptr;
+  const int* seed = (seeded && ctx->knnSeed && ctx->knnLanes == 4) ? pos : nullptr;   // as in knn1LoopBody: only in the 4-lane regime
   if (k == 1 && (ctx->knnLanes == 8 || ctx->knnLanes == 0)) launchKnn1<8>(ctx, ix, queries, n, hasT, R, maxd2, allowSelf, ids, d2, pos, visits, seed);
   else if (k == 1 && ctx->knnLanes == 4) launchKnn1<4>(ctx, ix, queries, n, hasT, R, maxd2, allowSelf, ids, d2, pos, visits, seed);
   else if (k == 1) launchKnn<1>(ctx, ix, queries, n, hasT, R, k, maxd2, allowSelf, ids, d2, pos, visits);
