@@ -133,6 +133,11 @@ int32_t b200reg_trimmed_dist(b200reg_ctx* ctx, const float* d2, int64_t count, f
  * limit_out (nullable) = the threshold that was applied. */
 enum { B200REG_OUTLIER_MAX_DIST = 0, B200REG_OUTLIER_MIN_DIST = 1, B200REG_OUTLIER_MEDIAN_DIST = 2 };
 int32_t b200reg_dist_outlier(b200reg_ctx* ctx, int32_t kind, const float* d2, int64_t count, float param, float* limit_out, float* w_out);
+/* VarTrimmedDistOutlierFilter::compute (OutlierFiltersImpl.cpp:166-220): the inlier ratio that minimises FRMS(f) =
+ * cumsum(sorted d2)[f] / f / (f / N)^(2 lambda) over [minRatio, maxRatio) (sorted = finite d2 > 0; the fp32 running sum is
+ * taken in the reference's order), then limit = getDistsQuantile(ratio), w = (d2 <= limit).  ratio_out / tau_out / w_out nullable. */
+int32_t b200reg_var_trimmed_dist(b200reg_ctx* ctx, const float* d2, int64_t count, float min_ratio, float max_ratio, float lambda,
+                                 float* ratio_out, float* tau_out, float* w_out);
 /* SurfaceNormalOutlierFilter::compute (OutlierFiltersImpl.cpp:236-281); normals 3 floats per point, nullable = filter off */
 int32_t b200reg_surface_normal_outlier(b200reg_ctx* ctx, const float* normals_reading, const float* normals_reference,
                                        int64_t n_reference, const int32_t* ids, int32_t k, int64_t n, float max_angle, float* w_out);
@@ -141,6 +146,19 @@ int32_t b200reg_surface_normal_outlier(b200reg_ctx* ctx, const float* normals_re
 int32_t b200reg_point_to_plane(b200reg_ctx* ctx, const b200reg_cloud* reading, const b200reg_cloud* reference, const int32_t* ids,
                                const float* d2, const float* w, int32_t k, int32_t force2D, double A_out[36], double b_out[6],
                                b200reg_step_stats* stats);
+
+/* PointToPointErrorMinimizer::compute (ErrorMinimizers/PointToPoint.cpp:55-94) on explicit matches and OutlierWeights (k*n each,
+ * HOST): weighted means, 3x3 cross-covariance of the centred pairs (fp64 on the device), SVD on the host, reflection fix,
+ * T_out = [U V^T | meanReference - R meanReading] rounded to fp32.  stats nullable. */
+int32_t b200reg_point_to_point(b200reg_ctx* ctx, const b200reg_cloud* reading, const b200reg_cloud* reference, const int32_t* ids,
+                               const float* d2, const float* w, int32_t k, float T_out[16], b200reg_step_stats* stats);
+/* PointToPlaneWithCovErrorMinimizer::estimateCovariance (ErrorMinimizers/PointToPlaneWithCov.cpp:70-160): covariance of the step
+ * transform T (the one b200reg_solve_point_to_plane returned for the same pairs) from the pairs centred on mean_reading /
+ * mean_reference (b200reg_step_stats of b200reg_point_to_plane) — the state PointToPlane.cpp:263-268 leaves the ErrorElements in.
+ * cov_out: 6x6 row-major, sensor_std_dev^2 * H^-1 (D D^T) H^-1. */
+int32_t b200reg_point_to_plane_covariance(b200reg_ctx* ctx, const b200reg_cloud* reading, const b200reg_cloud* reference, const int32_t* ids,
+                                          const float* d2, const float* w, int32_t k, const double mean_reading[3],
+                                          const double mean_reference[3], const float T[16], float sensor_std_dev, double cov_out[36]);
 
 /* PointToPlaneErrorMinimizer::compute tail (PointToPlane.cpp:185-368): solve (LLT, rank-reduced minimum norm when
  * singular), Rodrigues, un-centre.  Host arithmetic in fp64; T_out = the 4x4 step transform rounded to fp32. */
@@ -207,6 +225,23 @@ int32_t b200reg_icp_reference_mean(const b200reg_icp* icp, float mean_out[3]);
  * when average_descriptors != 0, else the first point's are kept. */
 int32_t b200reg_voxelgrid(b200reg_ctx* ctx, b200reg_cloud* inout, float vx, float vy, float vz, int32_t use_centroid,
                           int32_t average_descriptors);
+/* The compacting filters: MaxDistDataPointsFilter (MaxDist.cpp:62-105: keep norm < |maxDist|, or feature(dim) < maxDist),
+ * MinDistDataPointsFilter (MinDist.cpp:62-101, the same with >), BoundingBoxDataPointsFilter (BoundingBox.cpp:66-95, strict
+ * bounds, removeInside) and RandomSamplingDataPointsFilter (RandomSampling.cpp:60-100: draw i of std::minstd_rand(seed) against
+ * prob, at most floor(n * prob) + 1 points; the reference seeds from std::random_device, here the seed is the caller's).
+ * Order of the kept points is preserved; normals travel with their points. */
+enum { B200REG_FILTER_MAX_DIST = 0, B200REG_FILTER_MIN_DIST = 1, B200REG_FILTER_BOUNDING_BOX = 2, B200REG_FILTER_RANDOM_SAMPLING = 3 };
+typedef struct b200reg_filter_params {
+  int32_t kind;
+  int32_t dim;            /* MaxDist / MinDist: -1 radius, 0 x, 1 y, 2 z                         */
+  float   dist;           /* maxDist | minDist                                                   */
+  float   box[6];         /* xMin xMax yMin yMax zMin zMax                                       */
+  int32_t remove_inside;
+  int32_t random_method;  /* randomSamplingMethod: 0 direct RNG, 1 uniform_real_distribution     */
+  double  prob;
+  uint64_t seed;
+} b200reg_filter_params;
+int32_t b200reg_cloud_filter(b200reg_ctx* ctx, b200reg_cloud* inout, const b200reg_filter_params* params);
 /* SurfaceNormalDataPointsFilter::inPlaceFilter (DataPointsFilters/SurfaceNormal.cpp:83-330).  Writes the cloud's
  * normals; optional HOST outputs (nullable): densities[n], eig_values[3n] ascending, lin_plan_curv[3n].
  * orient_origin (nullable float[3]): flip normals toward that point (CloudRegistration.cpp:71-74 usage). */

@@ -64,6 +64,15 @@ class CarveParams(C.Structure):
                 ("min_dot_product_with_normal", C.c_double)]
 
 
+class FilterParams(C.Structure):
+    """b200reg_filter_params: MaxDist / MinDist / BoundingBox / RandomSampling DataPointsFilters"""
+    _fields_ = [("kind", C.c_int32), ("dim", C.c_int32), ("dist", C.c_float), ("box", C.c_float * 6), ("remove_inside", C.c_int32),
+                ("random_method", C.c_int32), ("prob", C.c_double), ("seed", C.c_uint64)]
+
+
+FILTER_MAX_DIST, FILTER_MIN_DIST, FILTER_BOUNDING_BOX, FILTER_RANDOM_SAMPLING = 0, 1, 2, 3
+
+
 class Pc2Layout(C.Structure):
     """The parts of sensor_msgs/PointCloud2 the deserialisers read (byte offsets of FLOAT32 fields; < 0 = absent)."""
     _fields_ = [("width", C.c_uint32), ("height", C.c_uint32), ("point_step", C.c_uint32), ("off_x", C.c_int32), ("off_y", C.c_int32),
@@ -163,6 +172,10 @@ SYMBOLS = {
     "b200reg_cloud64_from_pointcloud2": (C.c_int32, [_VP, _VP, C.c_size_t, C.POINTER(Pc2Layout), C.POINTER(_VP)]),
     "b200reg_overlap_indices": (C.c_int32, [_VP, _VP, _VP, _VP, C.c_double, C.c_int64, _VP, C.POINTER(C.c_int64), _VP, C.POINTER(C.c_int64)]),
     "b200reg_information_matrix": (C.c_int32, [_VP, _VP, _VP, C.c_double, _VP, _VP, C.POINTER(C.c_int64)]),
+    "b200reg_var_trimmed_dist": (C.c_int32, [_VP, _VP, C.c_int64, C.c_float, C.c_float, C.c_float, C.POINTER(C.c_float), C.POINTER(C.c_float), _VP]),
+    "b200reg_point_to_point": (C.c_int32, [_VP, _VP, _VP, _VP, _VP, _VP, C.c_int32, _VP, C.POINTER(StepStats)]),
+    "b200reg_point_to_plane_covariance": (C.c_int32, [_VP, _VP, _VP, _VP, _VP, _VP, C.c_int32, _VP, _VP, _VP, C.c_float, _VP]),
+    "b200reg_cloud_filter": (C.c_int32, [_VP, _VP, C.POINTER(FilterParams)]),
     "b200reg_map_carve": (C.c_int32, [_VP, _VP, _VP, C.c_int64, _VP, C.POINTER(CropSpec), C.POINTER(CarveParams), C.POINTER(C.c_int64)]),
     "b200reg_map_carve_cloud64": (C.c_int32, [_VP, _VP, _VP, _VP, C.POINTER(CropSpec), C.POINTER(CarveParams), C.POINTER(C.c_int64)]),
 }
@@ -388,6 +401,36 @@ class Context:
         self.check(lib().b200reg_dist_outlier(self.h, int(kind), _p(d2), d2.size, float(param), C.byref(lim), _p(w)))
         return lim.value, w
 
+    def var_trimmed_dist(self, d2, min_ratio, max_ratio, lam):
+        """VarTrimmedDistOutlierFilter on squared distances; returns (optimised ratio, limit, weights)."""
+        d2 = _f32(d2)
+        w = np.empty(d2.shape, dtype=np.float32)
+        ratio, tau = C.c_float(0), C.c_float(0)
+        self.check(lib().b200reg_var_trimmed_dist(self.h, _p(d2), d2.size, float(min_ratio), float(max_ratio), float(lam), C.byref(ratio),
+                                                  C.byref(tau), _p(w)))
+        return ratio.value, tau.value, w
+
+    def point_to_point(self, reading, reference, ids, d2, w):
+        """PointToPointErrorMinimizer::compute on explicit matches / weights; returns (T 4x4 float32, StepStats)."""
+        ids = np.ascontiguousarray(ids, dtype=np.int32)
+        d2, w = _f32(d2), _f32(w)
+        k = ids.size // max(reading.size, 1)
+        T = np.zeros((4, 4), dtype=np.float32)
+        st = StepStats()
+        self.check(lib().b200reg_point_to_point(self.h, reading.h, reference.h, _p(ids), _p(d2), _p(w), k, _p(T), C.byref(st)))
+        return T, st
+
+    def point_to_plane_covariance(self, reading, reference, ids, d2, w, mean_reading, mean_reference, T, sensor_std_dev):
+        """PointToPlaneWithCovErrorMinimizer::estimateCovariance for the step transform T; returns the 6x6 covariance."""
+        ids = np.ascontiguousarray(ids, dtype=np.int32)
+        d2, w, T = _f32(d2), _f32(w), _f32(T)
+        mr, ms = _f64(mean_reading), _f64(mean_reference)
+        k = ids.size // max(reading.size, 1)
+        cov = np.zeros((6, 6), dtype=np.float64)
+        self.check(lib().b200reg_point_to_plane_covariance(self.h, reading.h, reference.h, _p(ids), _p(d2), _p(w), k, _p(mr), _p(ms), _p(T),
+                                                           float(sensor_std_dev), _p(cov)))
+        return cov
+
     def crop_f64(self, spec, xyz, nrm=None):
         xyz, nrm = _f64(xyz), _f64(nrm)
         xo = np.empty_like(xyz)
@@ -438,6 +481,13 @@ class Cloud:
     def transform(self, T):
         T = _f32(T).reshape(16)
         self.ctx.check(lib().b200reg_cloud_transform(self.ctx.h, self.h, _p(T)))
+
+    def filter(self, kind, dim=-1, dist=1.0, box=(-1, 1, -1, 1, -1, 1), remove_inside=True, random_method=0, prob=0.75, seed=1):
+        """MaxDist / MinDist / BoundingBox / RandomSampling DataPointsFilter, in place (order preserving)."""
+        P = FilterParams(kind=int(kind), dim=int(dim), dist=float(dist), box=(C.c_float * 6)(*[float(b) for b in box]),
+                         remove_inside=int(remove_inside), random_method=int(random_method), prob=float(prob), seed=int(seed))
+        self.ctx.check(lib().b200reg_cloud_filter(self.ctx.h, self.h, C.byref(P)))
+        return self
 
     def voxelgrid(self, vx, vy, vz, use_centroid=True, average_descriptors=True):
         self.ctx.check(lib().b200reg_voxelgrid(self.ctx.h, self.h, vx, vy, vz, int(use_centroid), int(average_descriptors)))

@@ -3,6 +3,7 @@
 // re-thrown as the libpointmatcher exception types callers already catch (Mapper.cpp:420 catches std::runtime_error).
 #include "cuda_modules.h"
 
+#include <cstring>
 #include <map>
 #include <mutex>
 #include <thread>
@@ -277,8 +278,15 @@ const PM::ParametersDoc CudaPointToPlaneErrorMinimizer::availableParameters() {
 CudaPointToPlaneErrorMinimizer::CudaPointToPlaneErrorMinimizer(const PM::Parameters& params)
     : PM::ErrorMinimizer("CudaPointToPlaneErrorMinimizer", availableParameters(), params), force2D(get<bool>("force2D")), force4DOF(get<bool>("force4DOF")),
       device(get<int>("device")) {}
+CudaPointToPlaneErrorMinimizer::CudaPointToPlaneErrorMinimizer(const std::string& name, const PM::ParametersDoc& doc, const PM::Parameters& params)
+    : PM::ErrorMinimizer(name, doc, params), force2D(get<bool>("force2D")), force4DOF(get<bool>("force4DOF")), device(get<int>("device")) {}
 PM::TransformationParameters CudaPointToPlaneErrorMinimizer::compute(const PM::DataPoints& filteredReading, const PM::DataPoints& filteredReference,
                                                                      const PM::OutlierWeights& outlierWeights, const PM::Matches& matches) {
+  return computeOnDevice(filteredReading, filteredReference, outlierWeights, matches, 0.f, nullptr);
+}
+PM::TransformationParameters CudaPointToPlaneErrorMinimizer::computeOnDevice(const PM::DataPoints& filteredReading, const PM::DataPoints& filteredReference,
+                                                                             const PM::OutlierWeights& outlierWeights, const PM::Matches& matches,
+                                                                             float sensorStdDev, PM::Matrix* covariance) {
   b200reg_ctx* ctx = contextFor(device);
   if (!filteredReference.descriptorExists("normals")) throw PM::DataPoints::InvalidField("Field normals not found");   // PointToPlane.cpp:115
   CloudGuard gr(ctx), gf(ctx);
@@ -294,7 +302,143 @@ PM::TransformationParameters CudaPointToPlaneErrorMinimizer::compute(const PM::D
   b200reg_solve_point_to_plane(A, b, st.mean_reading, st.mean_reference, force2D ? 1 : 0, force4DOF ? 1 : 0, T, nullptr);
   PM::TransformationParameters out(4, 4);
   for (int i = 0; i < 4; ++i) for (int j = 0; j < 4; ++j) out(i, j) = T[4 * i + j];
+  if (covariance) {   // PointToPlaneWithCov.cpp:62-66: estimateCovariance(mPts, out) on the centred ErrorElements
+    double cov[36];
+    check(ctx, b200reg_point_to_plane_covariance(ctx, gr.c, gf.c, matches.ids.data(), matches.dists.data(), outlierWeights.data(),
+                                                 (int32_t)matches.ids.rows(), st.mean_reading, st.mean_reference, T, sensorStdDev, cov));
+    *covariance = PM::Matrix(6, 6);
+    for (int i = 0; i < 6; ++i) for (int j = 0; j < 6; ++j) (*covariance)(i, j) = (float)cov[6 * i + j];
+  }
   return out;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// CudaPointToPlaneWithCovErrorMinimizer, CudaPointToPointErrorMinimizer, CudaVarTrimmedDistOutlierFilter
+// ---------------------------------------------------------------------------------------------------------------
+const PM::ParametersDoc CudaPointToPlaneWithCovErrorMinimizer::availableParameters() {   // PointToPlaneWithCov.h:70-76 (+ the base's force4DOF)
+  return {{"force2D", "If set to true(1), the minimization will be force to give a solution in 2D (i.e., on the XY-plane) even with 3D inputs.", "0", "0", "1", &P::Comp<bool>},
+          {"force4DOF", "If set to true(1), the minimization will optimize only yaw and translation, pitch and roll will follow the prior.", "0", "0", "1", &P::Comp<bool>},
+          {"sensorStdDev", "sensor standard deviation", "0.01", "0.", "inf", &P::Comp<float>},
+          {"device", "CUDA device ordinal", "0", "0", "1023", &P::Comp<int>}};
+}
+CudaPointToPlaneWithCovErrorMinimizer::CudaPointToPlaneWithCovErrorMinimizer(const PM::Parameters& params)
+    : CudaPointToPlaneErrorMinimizer("CudaPointToPlaneWithCovErrorMinimizer", availableParameters(), params), sensorStdDev(get<float>("sensorStdDev")) {}
+PM::TransformationParameters CudaPointToPlaneWithCovErrorMinimizer::compute(const PM::DataPoints& filteredReading, const PM::DataPoints& filteredReference,
+                                                                            const PM::OutlierWeights& outlierWeights, const PM::Matches& matches) {
+  return computeOnDevice(filteredReading, filteredReference, outlierWeights, matches, sensorStdDev, &covMatrix);
+}
+
+const PM::ParametersDoc CudaPointToPointErrorMinimizer::availableParameters() { return {{"device", "CUDA device ordinal", "0", "0", "1023", &P::Comp<int>}}; }
+CudaPointToPointErrorMinimizer::CudaPointToPointErrorMinimizer(const PM::Parameters& params)
+    : PM::ErrorMinimizer("CudaPointToPointErrorMinimizer", availableParameters(), params), device(get<int>("device")) {}
+PM::TransformationParameters CudaPointToPointErrorMinimizer::compute(const PM::DataPoints& filteredReading, const PM::DataPoints& filteredReference,
+                                                                     const PM::OutlierWeights& outlierWeights, const PM::Matches& matches) {
+  if (filteredReading.features.rows() != 4) throw PM::InvalidParameter("CudaPointToPointErrorMinimizer: only 3D clouds (4 x N features) are supported");
+  b200reg_ctx* ctx = contextFor(device);
+  CloudGuard gr(ctx), gf(ctx);
+  upload(ctx, filteredReading, false, gr);
+  upload(ctx, filteredReference, false, gf);
+  float T[16];
+  b200reg_step_stats st;
+  check(ctx, b200reg_point_to_point(ctx, gr.c, gf.c, matches.ids.data(), matches.dists.data(), outlierWeights.data(), (int32_t)matches.ids.rows(), T, &st));
+  this->pointUsedRatio = st.point_used_ratio;
+  this->weightedPointUsedRatio = st.weighted_point_used_ratio;
+  PM::TransformationParameters out(4, 4);
+  for (int i = 0; i < 4; ++i) for (int j = 0; j < 4; ++j) out(i, j) = T[4 * i + j];
+  return out;
+}
+
+const PM::ParametersDoc CudaVarTrimmedDistOutlierFilter::availableParameters() {   // OutlierFiltersImpl.h:153-159
+  return {{"minRatio", "min ratio", "0.05", "0.0000001", "1", &P::Comp<float>},
+          {"maxRatio", "max ratio", "0.99", "0.0000001", "1", &P::Comp<float>},
+          {"lambda", "lambda (part of the term that balance the rmsd: 1/ratio^lambda", "2.35"},
+          {"device", "CUDA device ordinal", "0", "0", "1023", &P::Comp<int>}};
+}
+CudaVarTrimmedDistOutlierFilter::CudaVarTrimmedDistOutlierFilter(const PM::Parameters& params)
+    : PM::OutlierFilter("CudaVarTrimmedDistOutlierFilter", availableParameters(), params), minRatio(get<float>("minRatio")), maxRatio(get<float>("maxRatio")),
+      lambda(get<float>("lambda")), device(get<int>("device")) {
+  if (minRatio >= maxRatio)   // OutlierFiltersImpl.cpp:160-163
+    throw PM::InvalidParameter("VarTrimmedDistOutlierFilter: minRatio (" + std::to_string(minRatio) + ") should be smaller than maxRatio (" + std::to_string(maxRatio) + ")");
+}
+PM::OutlierWeights CudaVarTrimmedDistOutlierFilter::compute(const PM::DataPoints&, const PM::DataPoints&, const PM::Matches& input) {
+  b200reg_ctx* ctx = contextFor(device);
+  PM::OutlierWeights w(input.dists.rows(), input.dists.cols());
+  check(ctx, b200reg_var_trimmed_dist(ctx, input.dists.data(), (int64_t)input.dists.d.size(), minRatio, maxRatio, lambda, nullptr, nullptr, w.data()));
+  return w;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// the compacting DataPointsFilters
+// ---------------------------------------------------------------------------------------------------------------
+CudaCompactingFilterBase::CudaCompactingFilterBase(const std::string& name, const PM::ParametersDoc& doc, const PM::Parameters& params)
+    : PM::DataPointsFilter(name, doc, params), device(get<int>("device")) { std::memset(&fp, 0, sizeof(fp)); }
+PM::DataPoints CudaCompactingFilterBase::filter(const PM::DataPoints& input) { PM::DataPoints o(input); inPlaceFilter(o); return o; }
+void CudaCompactingFilterBase::inPlaceFilter(PM::DataPoints& cloud) {
+  if (cloud.features.rows() != 4) throw PM::InvalidParameter(className + ": only 3D clouds (4 x N features) are supported");
+  for (auto& l : cloud.descriptorLabels)
+    if (l.text != "normals") throw PM::DataPoints::InvalidField(className + ": descriptor '" + l.text + "' is not carried on the device (only 'normals')");
+  if (cloud.times.rows() != 0) throw PM::DataPoints::InvalidField(className + ": times are not carried on the device");
+  b200reg_ctx* ctx = contextFor(device);
+  CloudGuard g(ctx);
+  upload(ctx, cloud, true, g);
+  check(ctx, b200reg_cloud_filter(ctx, g.c, &fp));
+  const int64_t m = b200reg_cloud_size(g.c);
+  const bool hasN = cloud.descriptorExists("normals");
+  std::vector<float> nrm(hasN ? 3 * (size_t)m : 0);
+  cloud.conservativeResize(m);
+  check(ctx, b200reg_cloud_download_f32(ctx, g.c, cloud.features.data(), 4, hasN ? nrm.data() : nullptr));
+  if (hasN) {
+    const int row = cloud.getDescriptorStartingRow("normals");
+    for (int64_t c = 0; c < m; ++c) for (int r = 0; r < 3; ++r) cloud.descriptors(row + r, c) = nrm[3 * c + r];
+  }
+}
+const PM::ParametersDoc CudaMaxDistDataPointsFilter::availableParameters() {   // MaxDist.h:57-62
+  return {{"dim", "dimension on which the filter will be applied. x=0, y=1, z=2, radius=-1", "-1", "-1", "2", &P::Comp<int>},
+          {"maxDist", "maximum distance authorized. If dim is set to -1 (radius), the absolute value of minDist will be used. All points beyond that will be filtered.", "1", "-inf", "inf", &P::Comp<float>},
+          {"device", "CUDA device ordinal", "0", "0", "1023", &P::Comp<int>}};
+}
+CudaMaxDistDataPointsFilter::CudaMaxDistDataPointsFilter(const PM::Parameters& params)
+    : CudaCompactingFilterBase("CudaMaxDistDataPointsFilter", availableParameters(), params) {
+  fp.kind = B200REG_FILTER_MAX_DIST; fp.dim = get<int>("dim"); fp.dist = get<float>("maxDist");
+}
+const PM::ParametersDoc CudaMinDistDataPointsFilter::availableParameters() {   // MinDist.h:57-62
+  return {{"dim", "dimension on which the filter will be applied. x=0, y=1, z=2, radius=-1", "-1", "-1", "2", &P::Comp<int>},
+          {"minDist", "minimum value authorized. If dim is set to -1 (radius), the absolute value of minDist will be used. All points before that will be filtered.", "1", "-inf", "inf", &P::Comp<float>},
+          {"device", "CUDA device ordinal", "0", "0", "1023", &P::Comp<int>}};
+}
+CudaMinDistDataPointsFilter::CudaMinDistDataPointsFilter(const PM::Parameters& params)
+    : CudaCompactingFilterBase("CudaMinDistDataPointsFilter", availableParameters(), params) {
+  fp.kind = B200REG_FILTER_MIN_DIST; fp.dim = get<int>("dim"); fp.dist = get<float>("minDist");
+}
+const PM::ParametersDoc CudaBoundingBoxDataPointsFilter::availableParameters() {   // BoundingBox.h:58-68
+  return {{"xMin", "minimum value on x-axis defining one side of the bounding box", "-1", "-inf", "inf", &P::Comp<float>},
+          {"xMax", "maximum value on x-axis defining one side of the bounding box", "1", "-inf", "inf", &P::Comp<float>},
+          {"yMin", "minimum value on y-axis defining one side of the bounding box", "-1", "-inf", "inf", &P::Comp<float>},
+          {"yMax", "maximum value on y-axis defining one side of the bounding box", "1", "-inf", "inf", &P::Comp<float>},
+          {"zMin", "minimum value on z-axis defining one side of the bounding box", "-1", "-inf", "inf", &P::Comp<float>},
+          {"zMax", "maximum value on z-axis defining one side of the bounding box", "1", "-inf", "inf", &P::Comp<float>},
+          {"removeInside", "If set to true (1), remove points inside the bounding box; else (0), remove points outside the bounding box", "1", "0", "1", P::Comp<bool>},
+          {"device", "CUDA device ordinal", "0", "0", "1023", &P::Comp<int>}};
+}
+CudaBoundingBoxDataPointsFilter::CudaBoundingBoxDataPointsFilter(const PM::Parameters& params)
+    : CudaCompactingFilterBase("CudaBoundingBoxDataPointsFilter", availableParameters(), params) {
+  fp.kind = B200REG_FILTER_BOUNDING_BOX;
+  const char* keys[6] = {"xMin", "xMax", "yMin", "yMax", "zMin", "zMax"};
+  for (int i = 0; i < 6; ++i) fp.box[i] = get<float>(keys[i]);
+  fp.remove_inside = get<bool>("removeInside") ? 1 : 0;
+}
+const PM::ParametersDoc CudaRandomSamplingDataPointsFilter::availableParameters() {   // RandomSampling.h:59-64 (+ seed: the CPU twin draws it from std::random_device)
+  return {{"prob", "Probability to keep a point, one over decimation factor ", "0.75", "0", "1", &P::Comp<double>},
+          {"randomSamplingMethod", "Random sampling method: Direct RNG (0) (fastest), Uniform (1) (more accurate but slower)", "0", "0", "1", &P::Comp<int>},
+          {"seed", "seed of the std::minstd_rand sequence the points are drawn against", "1", "0", "2147483646", &P::Comp<int64_t>},
+          {"device", "CUDA device ordinal", "0", "0", "1023", &P::Comp<int>}};
+}
+CudaRandomSamplingDataPointsFilter::CudaRandomSamplingDataPointsFilter(const PM::Parameters& params)
+    : CudaCompactingFilterBase("CudaRandomSamplingDataPointsFilter", availableParameters(), params) {
+  fp.kind = B200REG_FILTER_RANDOM_SAMPLING;
+  fp.prob = get<double>("prob");
+  fp.random_method = get<int>("randomSamplingMethod");
+  fp.seed = (uint64_t)get<int64_t>("seed");
 }
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -319,6 +463,13 @@ void registerCudaModules(PM& pm) {
   ADD_TO_REGISTRAR(OutlierFilter, CudaMinDistOutlierFilter, CudaMinDistOutlierFilter)
   ADD_TO_REGISTRAR(OutlierFilter, CudaMedianDistOutlierFilter, CudaMedianDistOutlierFilter)
   ADD_TO_REGISTRAR(ErrorMinimizer, CudaPointToPlaneErrorMinimizer, CudaPointToPlaneErrorMinimizer)
+  ADD_TO_REGISTRAR(ErrorMinimizer, CudaPointToPlaneWithCovErrorMinimizer, CudaPointToPlaneWithCovErrorMinimizer)
+  ADD_TO_REGISTRAR(ErrorMinimizer, CudaPointToPointErrorMinimizer, CudaPointToPointErrorMinimizer)
+  ADD_TO_REGISTRAR(OutlierFilter, CudaVarTrimmedDistOutlierFilter, CudaVarTrimmedDistOutlierFilter)
+  ADD_TO_REGISTRAR(DataPointsFilter, CudaMaxDistDataPointsFilter, CudaMaxDistDataPointsFilter)
+  ADD_TO_REGISTRAR(DataPointsFilter, CudaMinDistDataPointsFilter, CudaMinDistDataPointsFilter)
+  ADD_TO_REGISTRAR(DataPointsFilter, CudaBoundingBoxDataPointsFilter, CudaBoundingBoxDataPointsFilter)
+  ADD_TO_REGISTRAR(DataPointsFilter, CudaRandomSamplingDataPointsFilter, CudaRandomSamplingDataPointsFilter)
 }
 
 }  // namespace b200

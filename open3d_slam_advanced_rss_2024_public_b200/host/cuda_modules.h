@@ -91,6 +91,15 @@ struct CudaMedianDistOutlierFilter : public CudaDistOutlierFilterBase {
   explicit CudaMedianDistOutlierFilter(const PM::Parameters& params = PM::Parameters());
 };
 
+struct CudaVarTrimmedDistOutlierFilter : public PM::OutlierFilter {   // twin: OutlierFiltersImpl.h:147-173
+  static const std::string description() { return "Hard rejection threshold using quantile and variable ratio. Based on \\cite{Phillips2007VarTrimmed}."; }
+  static const PM::ParametersDoc availableParameters();
+  const float minRatio, maxRatio, lambda;
+  const int device;
+  explicit CudaVarTrimmedDistOutlierFilter(const PM::Parameters& params = PM::Parameters());
+  PM::OutlierWeights compute(const PM::DataPoints& filteredReading, const PM::DataPoints& filteredReference, const PM::Matches& input) override;
+};
+
 struct CudaSurfaceNormalOutlierFilter : public PM::OutlierFilter {   // twin: OutlierFiltersImpl.h:176-192
   static const std::string description() { return "Hard rejection threshold using the angle between the surface normal vectors of the reading and the reference."; }
   static const PM::ParametersDoc availableParameters();
@@ -106,8 +115,64 @@ struct CudaPointToPlaneErrorMinimizer : public PM::ErrorMinimizer {   // twin: E
   const bool force2D, force4DOF;
   const int device;
   explicit CudaPointToPlaneErrorMinimizer(const PM::Parameters& params = PM::Parameters());
+  CudaPointToPlaneErrorMinimizer(const std::string& name, const PM::ParametersDoc& doc, const PM::Parameters& params);   // for the WithCov child
   PM::TransformationParameters compute(const PM::DataPoints& filteredReading, const PM::DataPoints& filteredReference,
                                        const PM::OutlierWeights& outlierWeights, const PM::Matches& matches) override;
+ protected:
+  // compute() with the pieces the covariance needs left on the device / returned: step transform, matched means
+  PM::TransformationParameters computeOnDevice(const PM::DataPoints& filteredReading, const PM::DataPoints& filteredReference,
+                                               const PM::OutlierWeights& outlierWeights, const PM::Matches& matches, float sensorStdDev,
+                                               PM::Matrix* covariance);
+};
+
+struct CudaPointToPointErrorMinimizer : public PM::ErrorMinimizer {   // twin: ErrorMinimizers/PointToPoint.h:45-62
+  static const std::string description() { return "Point-to-point error. Based on SVD decomposition. Per \\cite{Besl1992Point2Point}."; }
+  static const PM::ParametersDoc availableParameters();
+  const int device;
+  explicit CudaPointToPointErrorMinimizer(const PM::Parameters& params = PM::Parameters());
+  PM::TransformationParameters compute(const PM::DataPoints& filteredReading, const PM::DataPoints& filteredReference,
+                                       const PM::OutlierWeights& outlierWeights, const PM::Matches& matches) override;
+};
+
+struct CudaPointToPlaneWithCovErrorMinimizer : public CudaPointToPlaneErrorMinimizer {   // twin: ErrorMinimizers/PointToPlaneWithCov.h:46-85
+  static const std::string description() { return "Point-to-plane error (or point-to-line in 2D). Based on \\cite{Chen1991Point2Plane}. Covariance estimation based on \\cite{Censi2007ICPCovariance}."; }
+  static const PM::ParametersDoc availableParameters();
+  const float sensorStdDev;
+  PM::Matrix covMatrix;
+  explicit CudaPointToPlaneWithCovErrorMinimizer(const PM::Parameters& params = PM::Parameters());
+  PM::TransformationParameters compute(const PM::DataPoints& filteredReading, const PM::DataPoints& filteredReference,
+                                       const PM::OutlierWeights& outlierWeights, const PM::Matches& matches) override;
+  PM::Matrix getCovariance() const override { return covMatrix; }
+};
+
+// MaxDist / MinDist / BoundingBox / RandomSampling twins (DataPointsFilters/{MaxDist,MinDist,BoundingBox,RandomSampling}.h): one predicate
+// kernel + an order-preserving compaction behind all four (b200reg_cloud_filter)
+struct CudaCompactingFilterBase : public PM::DataPointsFilter {
+  b200reg_filter_params fp;
+  const int device;
+  CudaCompactingFilterBase(const std::string& name, const PM::ParametersDoc& doc, const PM::Parameters& params);
+  PM::DataPoints filter(const PM::DataPoints& input) override;
+  void inPlaceFilter(PM::DataPoints& cloud) override;
+};
+struct CudaMaxDistDataPointsFilter : public CudaCompactingFilterBase {
+  static const std::string description() { return "Subsampling. Filter points beyond a maximum distance measured on a specific axis. If dim is set to -1, points are filtered based on a maximum radius."; }
+  static const PM::ParametersDoc availableParameters();
+  explicit CudaMaxDistDataPointsFilter(const PM::Parameters& params = PM::Parameters());
+};
+struct CudaMinDistDataPointsFilter : public CudaCompactingFilterBase {
+  static const std::string description() { return "Subsampling. Filter points before a minimum distance measured on a specific axis. If dim is set to -1, points are filtered based on a minimum radius."; }
+  static const PM::ParametersDoc availableParameters();
+  explicit CudaMinDistDataPointsFilter(const PM::Parameters& params = PM::Parameters());
+};
+struct CudaBoundingBoxDataPointsFilter : public CudaCompactingFilterBase {
+  static const std::string description() { return "Subsampling. Remove points laying in a bounding box which is axis aligned."; }
+  static const PM::ParametersDoc availableParameters();
+  explicit CudaBoundingBoxDataPointsFilter(const PM::Parameters& params = PM::Parameters());
+};
+struct CudaRandomSamplingDataPointsFilter : public CudaCompactingFilterBase {
+  static const std::string description() { return "Subsampling. This filter reduces the size of the point cloud by randomly dropping points. Based on \\cite{Masuda1996Random}"; }
+  static const PM::ParametersDoc availableParameters();
+  explicit CudaRandomSamplingDataPointsFilter(const PM::Parameters& params = PM::Parameters());
 };
 
 }  // namespace b200

@@ -539,6 +539,7 @@ bool PointMatcher<T>::ICP::fastLaneEligible() const {
   using namespace b200;
   if (!dynamic_cast<CudaKDTreeMatcher*>(this->matcher.get())) return false;
   if (!dynamic_cast<CudaPointToPlaneErrorMinimizer*>(this->errorMinimizer.get())) return false;
+  if (dynamic_cast<CudaPointToPlaneWithCovErrorMinimizer*>(this->errorMinimizer.get())) return false;   // its covariance is a per-module product
   if (!this->readingStepDataPointsFilters.empty()) return false;
   int nTrim = 0, nAngle = 0, nCnt = 0, nDiff = 0, nBound = 0;
   for (auto& f : this->outlierFilters) {

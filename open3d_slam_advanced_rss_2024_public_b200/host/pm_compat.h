@@ -265,6 +265,7 @@ struct PointMatcher {
     T getPointUsedRatio() const { return pointUsedRatio; }
     T getWeightedPointUsedRatio() const { return weightedPointUsedRatio; }
     virtual T getOverlap() const { return weightedPointUsedRatio; }   // PointToPlane.cpp:477-481 fallback
+    virtual Matrix getCovariance() const { return Matrix(6, 6, T(0)); }   // ErrorMinimizer.cpp:264-270: zero unless a child redefines it
   };
   struct TransformationChecker : public Parametrizable {
     TransformationChecker() {}

@@ -1490,3 +1490,276 @@ int64_t orc_information_matrix(const double* src, int64_t n_src, const double* t
 }
 
 }  // extern "C"
+
+// ================================================================================================================
+// VarTrimmedDistOutlierFilter, PointToPointErrorMinimizer, PointToPlaneWithCov covariance and the
+// compacting DataPointsFilters
+// ================================================================================================================
+#include <random>
+
+// VarTrimmedDistOutlierFilter::optimizeInlierRatio (OutlierFiltersImpl.cpp:178-220), then compute (:166-175).
+// The window [minEl, maxEl) is cut at the number of valid distances: beyond it the reference reads vector capacity that
+// std::partial_sum never wrote (undefined behaviour).  pow(ratio, lambda) is the fp64 pow rounded once to float.
+extern "C" int32_t orc_var_trimmed_dist(const float* d2, int64_t count, float min_ratio, float max_ratio, float lambda, float* ratio_out,
+                                        float* tau_out, float* w_out) {
+  if (!(min_ratio < max_ratio)) return ORC_E_PARAM;     // :160-163
+  std::vector<float> sorted;
+  sorted.reserve((size_t)count);
+  for (int64_t i = 0; i < count; ++i)
+    if (d2[i] != kInf && d2[i] > 0.f) sorted.push_back(d2[i]);   // :189-192
+  if (sorted.empty()) return ORC_E_CONVERGENCE;                   // :193-194
+  std::sort(sorted.begin(), sorted.end());
+  std::vector<float> cum(sorted.size());
+  {
+    volatile float run = 0.f;   // std::partial_sum on float: one rounded add per element, in order
+    for (size_t i = 0; i < sorted.size(); ++i) { run = run + sorted[i]; cum[i] = run; }
+  }
+  const int points_nbr = (int)count;
+  const int minEl = (int)std::floor(min_ratio * points_nbr), maxEl = (int)std::floor(max_ratio * points_nbr);   // :200-201
+  const int end = std::min<int64_t>(maxEl, (int64_t)sorted.size());
+  int minIndex = -1;
+  float best = kInf;
+  for (int e = std::max(minEl, 0); e < end; ++e) {
+    const float id = (float)(e + 1);                                   // LinSpaced(.., minEl + 1, maxEl)
+    volatile float ratio = id / (float)points_nbr;                     // :208
+    volatile float deno = (float)std::pow((double)ratio, (double)lambda);   // :209
+    volatile float invId = 1.f / id, invD = 1.f / deno;
+    volatile float a = cum[e] * invId, b = invD * invD;
+    const float frms = a * b;                                          // :211
+    if (frms < best) { best = frms; minIndex = e - minEl; }            // minCoeff: first minimum
+  }
+  if (minIndex < 0) return ORC_E_CONVERGENCE;
+  const float ratio = (float)(minIndex + minEl) / (float)points_nbr;   // :214
+  if (ratio_out) *ratio_out = ratio;
+  if (!tau_out && !w_out) return ORC_OK;
+  return orc_trimmed_dist(d2, count, ratio, tau_out, w_out);           // :172-173
+}
+
+namespace {
+
+// 3x3 SVD through the symmetric eigen-decomposition of M^T M (fp64): M = U diag(s) V^T, s descending
+void svd3ViaEig(const double M[9], double U[3][3], double s[3], double V[3][3]) {
+  double MtM[9];
+  for (int i = 0; i < 3; ++i)
+    for (int j = 0; j < 3; ++j) MtM[3 * i + j] = M[i] * M[j] + M[3 + i] * M[3 + j] + M[6 + i] * M[6 + j];
+  double val[3], vec[3][3];
+  symEig3(MtM, val, vec);   // ascending
+  for (int c = 0; c < 3; ++c) {
+    const int src = 2 - c;
+    s[c] = std::sqrt(std::max(val[src], 0.0));
+    for (int r = 0; r < 3; ++r) V[r][c] = vec[r][src];
+  }
+  for (int c = 0; c < 2; ++c) {
+    double u[3];
+    for (int r = 0; r < 3; ++r) u[r] = M[3 * r] * V[0][c] + M[3 * r + 1] * V[1][c] + M[3 * r + 2] * V[2][c];
+    if (c == 1) {   // re-orthogonalise against the first column
+      const double d = u[0] * U[0][0] + u[1] * U[1][0] + u[2] * U[2][0];
+      for (int r = 0; r < 3; ++r) u[r] -= d * U[r][0];
+    }
+    const double nn = std::sqrt(u[0] * u[0] + u[1] * u[1] + u[2] * u[2]);
+    for (int r = 0; r < 3; ++r) U[r][c] = u[r] / nn;
+  }
+  // third column: M v3 / s3 when s3 is well above round-off, else the cross product (sign fixed later by the reflection test)
+  double u3[3] = {U[1][0] * U[2][1] - U[2][0] * U[1][1], U[2][0] * U[0][1] - U[0][0] * U[2][1], U[0][0] * U[1][1] - U[1][0] * U[0][1]};
+  double mv[3];
+  for (int r = 0; r < 3; ++r) mv[r] = M[3 * r] * V[0][2] + M[3 * r + 1] * V[1][2] + M[3 * r + 2] * V[2][2];
+  const double sgn = (mv[0] * u3[0] + mv[1] * u3[1] + mv[2] * u3[2]) < 0.0 ? -1.0 : 1.0;
+  for (int r = 0; r < 3; ++r) U[r][2] = sgn * u3[r];
+}
+
+template <typename S>
+int pointToPoint(const float* readFeat, int rstride, int64_t n, const float* refFeat, int fstride, const int32_t* ids, const float* d2,
+                 const float* w, int k, float T_out[16], int* kept_out) {
+  std::vector<Pair> pairs;
+  for (int64_t i = 0; i < n; ++i)
+    for (int j = 0; j < k; ++j) {
+      const int64_t o = (int64_t)k * i + j;
+      if (d2[o] == kInf) continue;                                   // ErrorMinimizer.cpp:103-106
+      if (w[o] != 0.f) pairs.push_back({i, ids[o], w[o]});           // :108
+    }
+  if (kept_out) *kept_out = (int)pairs.size();
+  if (pairs.empty()) return ORC_E_CONVERGENCE;
+  S wsum = 0, mp[3] = {0, 0, 0}, mq[3] = {0, 0, 0};
+  for (const Pair& p : pairs) {                                      // PointToPoint.cpp:62-67
+    wsum += (S)p.w;
+    for (int d = 0; d < 3; ++d) {
+      mp[d] += (S)readFeat[p.read * rstride + d] * (S)p.w;
+      mq[d] += (S)refFeat[(int64_t)p.ref * fstride + d] * (S)p.w;
+    }
+  }
+  const S inv = S(1) / wsum;
+  for (int d = 0; d < 3; ++d) { mp[d] *= inv; mq[d] *= inv; }
+  S C[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+  for (const Pair& p : pairs)                                        // :70-77  m = ref_c * diag(w) * read_c^T
+    for (int i = 0; i < 3; ++i)
+      for (int j = 0; j < 3; ++j)
+        C[3 * i + j] += ((S)refFeat[(int64_t)p.ref * fstride + i] - mq[i]) * (S)p.w * ((S)readFeat[p.read * rstride + j] - mp[j]);
+  double M[9], U[3][3], s[3], V[3][3], R[3][3];
+  for (int i = 0; i < 9; ++i) M[i] = (double)C[i];
+  svd3ViaEig(M, U, s, V);
+  auto mul = [&]() {
+    for (int i = 0; i < 3; ++i)
+      for (int j = 0; j < 3; ++j) R[i][j] = U[i][0] * V[j][0] + U[i][1] * V[j][1] + U[i][2] * V[j][2];
+  };
+  mul();
+  const double det = R[0][0] * (R[1][1] * R[2][2] - R[1][2] * R[2][1]) - R[0][1] * (R[1][0] * R[2][2] - R[1][2] * R[2][0]) +
+                     R[0][2] * (R[1][0] * R[2][1] - R[1][1] * R[2][0]);
+  if (det < 0.0) {                                                   // :80-85
+    for (int r = 0; r < 3; ++r) V[r][2] = -V[r][2];
+    mul();
+  }
+  for (int i = 0; i < 3; ++i) {
+    for (int j = 0; j < 3; ++j) T_out[4 * i + j] = (float)R[i][j];
+    T_out[4 * i + 3] = (float)((double)mq[i] - (R[i][0] * (double)mp[0] + R[i][1] * (double)mp[1] + R[i][2] * (double)mp[2]));   // :86
+  }
+  T_out[12] = T_out[13] = T_out[14] = 0.f;
+  T_out[15] = 1.f;
+  return ORC_OK;
+}
+
+}  // namespace
+
+extern "C" int32_t orc_point_to_point(const float* read_feat, int32_t rstride, int64_t n, const float* ref_feat, int32_t fstride,
+                                      const int32_t* ids, const float* d2, const float* w, int32_t k, int32_t precision, float T_out[16],
+                                      int32_t* kept_out) {
+  int kept = 0;
+  const int st = precision == ORC_REF32 ? pointToPoint<float>(read_feat, rstride, n, ref_feat, fstride, ids, d2, w, k, T_out, &kept)
+                                        : pointToPoint<double>(read_feat, rstride, n, ref_feat, fstride, ids, d2, w, k, T_out, &kept);
+  if (kept_out) *kept_out = kept;
+  return st;
+}
+
+namespace {
+
+// PointToPlaneWithCovErrorMinimizer::estimateCovariance (PointToPlaneWithCov.cpp:70-160) over the ErrorElements as
+// PointToPlaneErrorMinimizer::compute leaves them: mean-centred in place (PointToPlane.cpp:263-268)
+template <typename S>
+int p2planeCovariance(const float* readFeat, int rstride, int64_t n, const float* refFeat, int fstride, const float* refNormals,
+                      const int32_t* ids, const float* d2, const float* w, int k, const float T[16], float sensorStdDev, double cov[36]) {
+  if (!refNormals) {                                                 // :91-92
+    for (int i = 0; i < 36; ++i) cov[i] = (i % 7 == 0) ? (double)std::numeric_limits<float>::max() : 0.0;
+    return ORC_OK;
+  }
+  std::vector<Pair> pairs;
+  for (int64_t i = 0; i < n; ++i)
+    for (int j = 0; j < k; ++j) {
+      const int64_t o = (int64_t)k * i + j;
+      if (d2[o] == kInf) continue;
+      if (w[o] != 0.f) pairs.push_back({i, ids[o], w[o]});
+    }
+  if (pairs.empty()) return ORC_E_CONVERGENCE;
+  const S K = (S)pairs.size();
+  S mp[3] = {0, 0, 0}, mq[3] = {0, 0, 0};
+  for (const Pair& p : pairs)
+    for (int d = 0; d < 3; ++d) { mp[d] += (S)readFeat[p.read * rstride + d]; mq[d] += (S)refFeat[(int64_t)p.ref * fstride + d]; }
+  for (int d = 0; d < 3; ++d) { mp[d] /= K; mq[d] /= K; }
+  const S beta = -std::asin((S)T[8]);                                // :94-99
+  const S alpha = std::atan2((S)T[9], (S)T[10]);
+  const S gamma = std::atan2((S)T[4] / std::cos(beta), (S)T[0] / std::cos(beta));
+  const S tx = (S)T[3], ty = (S)T[7], tz = (S)T[11];
+  std::vector<S> H(36, S(0)), C(36, S(0));
+  for (const Pair& p : pairs) {
+    S r[3], q[3], nn[3];
+    for (int d = 0; d < 3; ++d) {
+      r[d] = (S)readFeat[p.read * rstride + d] - mp[d];
+      q[d] = (S)refFeat[(int64_t)p.ref * fstride + d] - mq[d];
+      nn[d] = (S)refNormals[3 * (int64_t)p.ref + d];
+    }
+    const S rr = std::sqrt(r[0] * r[0] + r[1] * r[1] + r[2] * r[2]), fr = std::sqrt(q[0] * q[0] + q[1] * q[1] + q[2] * q[2]);   // :113-116
+    const S rd[3] = {r[0] / rr, r[1] / rr, r[2] / rr}, fd[3] = {q[0] / fr, q[1] / fr, q[2] / fr};
+    const S na = nn[2] * rd[1] - nn[1] * rd[2], nb = nn[0] * rd[2] - nn[2] * rd[0], ng = nn[1] * rd[0] - nn[0] * rd[1];         // :118-120
+    S E = nn[0] * (r[0] - gamma * r[1] + beta * r[2] + tx - q[0]);                                                            // :122-124
+    E += nn[1] * (gamma * r[0] + r[1] - alpha * r[2] + ty - q[1]);
+    E += nn[2] * (-beta * r[0] + alpha * r[1] + r[2] + tz - q[2]);
+    S Nr = nn[0] * (rd[0] - gamma * rd[1] + beta * rd[2]);                                                                    // :126-128
+    Nr += nn[1] * (gamma * rd[0] + rd[1] - alpha * rd[2]);
+    Nr += nn[2] * (-beta * rd[0] + alpha * rd[1] + rd[2]);
+    const S Nf = -(nn[0] * fd[0] + nn[1] * fd[1] + nn[2] * fd[2]);                                                            // :130
+    const S v[6] = {nn[0], nn[1], nn[2], rr * na, rr * nb, rr * ng};                                                          // :133
+    const S g = E + rr * Nr;
+    const S a[6] = {nn[0] * Nr, nn[1] * Nr, nn[2] * Nr, na * g, nb * g, ng * g};                                              // :137
+    const S b[6] = {nn[0] * Nf, nn[1] * Nf, nn[2] * Nf, fr * na * Nf, fr * nb * Nf, fr * ng * Nf};                            // :141
+    for (int i = 0; i < 6; ++i)
+      for (int j = 0; j < 6; ++j) { H[6 * i + j] += v[i] * v[j]; C[6 * i + j] += a[i] * a[j] + b[i] * b[j]; }                 // :135, :148-150
+  }
+  // inverse of J_hessian by solving H X = I column by column (fp64 LLT-free Gauss with partial pivoting)
+  double A[6][12];
+  for (int i = 0; i < 6; ++i)
+    for (int j = 0; j < 6; ++j) { A[i][j] = (double)H[6 * i + j]; A[i][6 + j] = i == j ? 1.0 : 0.0; }
+  for (int c = 0; c < 6; ++c) {
+    int piv = c;
+    for (int r2 = c + 1; r2 < 6; ++r2) if (std::fabs(A[r2][c]) > std::fabs(A[piv][c])) piv = r2;
+    if (!(std::fabs(A[piv][c]) > 0.0)) { for (int i = 0; i < 36; ++i) cov[i] = std::nan(""); return ORC_OK; }
+    for (int j = 0; j < 12; ++j) std::swap(A[c][j], A[piv][j]);
+    const double pv = A[c][c];
+    for (int j = 0; j < 12; ++j) A[c][j] /= pv;
+    for (int r2 = 0; r2 < 6; ++r2) {
+      if (r2 == c) continue;
+      const double f = A[r2][c];
+      for (int j = 0; j < 12; ++j) A[r2][j] -= f * A[c][j];
+    }
+  }
+  double t1[36];
+  for (int i = 0; i < 6; ++i)
+    for (int j = 0; j < 6; ++j) { double s = 0; for (int l = 0; l < 6; ++l) s += A[i][6 + l] * (double)C[6 * l + j]; t1[6 * i + j] = s; }
+  const double s2 = (double)sensorStdDev * (double)sensorStdDev;     // :156
+  for (int i = 0; i < 6; ++i)
+    for (int j = 0; j < 6; ++j) { double s = 0; for (int l = 0; l < 6; ++l) s += t1[6 * i + l] * A[l][6 + j]; cov[6 * i + j] = s2 * s; }
+  return ORC_OK;
+}
+
+}  // namespace
+
+extern "C" int32_t orc_point_to_plane_covariance(const float* read_feat, int32_t rstride, int64_t n, const float* ref_feat, int32_t fstride,
+                                                 const float* ref_normals, const int32_t* ids, const float* d2, const float* w, int32_t k,
+                                                 int32_t precision, const float T[16], float sensor_std_dev, double cov_out[36]) {
+  return precision == ORC_REF32
+             ? p2planeCovariance<float>(read_feat, rstride, n, ref_feat, fstride, ref_normals, ids, d2, w, k, T, sensor_std_dev, cov_out)
+             : p2planeCovariance<double>(read_feat, rstride, n, ref_feat, fstride, ref_normals, ids, d2, w, k, T, sensor_std_dev, cov_out);
+}
+
+// MaxDist.cpp:62-105, MinDist.cpp:62-101, BoundingBox.cpp:66-95, RandomSampling.cpp:60-100 on a 3-D cloud: keep[i] in {0, 1},
+// returns the number kept.  kind / fields as b200reg_filter_params (include/b200reg.h).
+extern "C" int64_t orc_cloud_filter(const float* feat, int32_t stride, int64_t n, int32_t kind, int32_t dim, float dist, const float box[6],
+                                    int32_t remove_inside, int32_t random_method, double prob, uint64_t seed, uint8_t* keep) {
+  int64_t j = 0;
+  if (kind == 3) {
+    std::minstd_rand gen((std::minstd_rand::result_type)seed);       // RandomSampling.cpp:64-65 with a caller-supplied seed
+    std::vector<float> rnd((size_t)n);
+    if (random_method == 1) {
+      std::uniform_real_distribution<float> distribution(0, 1);      // :76-77
+      for (int64_t i = 0; i < n; ++i) rnd[i] = distribution(gen);
+    } else {
+      const float range = static_cast<float>(gen.max() - gen.min()); // :71-72
+      for (int64_t i = 0; i < n; ++i) rnd[i] = static_cast<float>(gen() / range);
+    }
+    const size_t nbPointsOut = (size_t)((double)(size_t)n * prob);   // :88
+    for (int64_t i = 0; i < n; ++i) keep[i] = 0;
+    for (int64_t i = 0; i < n && (size_t)j <= nbPointsOut; ++i)      // :92
+      if (rnd[i] < prob) { keep[i] = 1; ++j; }
+    return j;
+  }
+  for (int64_t i = 0; i < n; ++i) {
+    const float* p = feat + i * stride;
+    bool k2;
+    if (kind == 2) {
+      const bool in = (p[0] > box[0] && p[0] < box[1]) && (p[1] > box[2] && p[1] < box[3]) && (p[2] > box[4] && p[2] < box[5]);
+      k2 = remove_inside ? !in : in;
+    } else {
+      float v, lim = dist;
+      if (dim == -1) {
+        volatile float xx = p[0] * p[0], yy = p[1] * p[1], zz = p[2] * p[2];
+        volatile float s = xx + yy;
+        s = s + zz;
+        v = std::sqrt((float)s);
+        lim = std::fabs(lim);
+      } else {
+        v = p[dim];
+      }
+      k2 = kind == 0 ? (v < lim) : (v > lim);
+    }
+    keep[i] = k2 ? 1 : 0;
+    j += k2;
+  }
+  return j;
+}

@@ -130,6 +130,20 @@ int64_t orc_information_matrix(const double* src, int64_t n_src, const double* t
                                double info[36]);   /* Open3D v0.15.1 GetInformationMatrixFromPointClouds (external) */
 void    orc_o3d_to_pm(const double* xyz, const double* nrm, int64_t n, float* feat4, float* nrm3);   /* open3d_conversions.cpp:57-118 */
 
+/* ---- SURVEY 8f rank 3 modules ---- */
+int32_t orc_var_trimmed_dist(const float* d2, int64_t count, float min_ratio, float max_ratio, float lambda, float* ratio_out, float* tau_out,
+                             float* w_out);   /* OutlierFiltersImpl.cpp:152-220 */
+int32_t orc_point_to_point(const float* read_feat, int32_t rstride, int64_t n, const float* ref_feat, int32_t fstride, const int32_t* ids,
+                           const float* d2, const float* w, int32_t k, int32_t precision, float T_out[16],
+                           int32_t* kept_out);   /* ErrorMinimizers/PointToPoint.cpp:55-94 */
+int32_t orc_point_to_plane_covariance(const float* read_feat, int32_t rstride, int64_t n, const float* ref_feat, int32_t fstride,
+                                      const float* ref_normals, const int32_t* ids, const float* d2, const float* w, int32_t k,
+                                      int32_t precision, const float T[16], float sensor_std_dev,
+                                      double cov_out[36]);   /* ErrorMinimizers/PointToPlaneWithCov.cpp:70-160 */
+int64_t orc_cloud_filter(const float* feat, int32_t stride, int64_t n, int32_t kind, int32_t dim, float dist, const float box[6],
+                         int32_t remove_inside, int32_t random_method, double prob, uint64_t seed,
+                         uint8_t* keep);   /* DataPointsFilters/MaxDist.cpp, MinDist.cpp, BoundingBox.cpp, RandomSampling.cpp */
+
 #ifdef __cplusplus
 }
 #endif

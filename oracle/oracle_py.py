@@ -13,6 +13,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 _LIB = None
 
 ORC_REF32, ORC_MIXED = 0, 1
+ORC_OK, ORC_E_CONVERGENCE, ORC_E_TRANSFORM, ORC_E_PARAM, ORC_E_EMPTY, ORC_E_FIELD = 0, -1, -2, -3, -4, -5
 CROP_MAX_RADIUS, CROP_MIN_RADIUS, CROP_MINMAX_RADIUS, CROP_CYLINDER = 0, 1, 2, 3
 
 
@@ -371,3 +372,63 @@ def o3d_to_pm(xyz, nrm=None):
     nn = None if nrm is None else np.empty((n, 3), dtype=np.float32)
     lib().orc_o3d_to_pm(_p(xyz), _p(nrm), n, _p(f), _p(nn))
     return f, nn
+
+
+def var_trimmed_dist(d2, min_ratio, max_ratio, lam):
+    """VarTrimmedDistOutlierFilter: returns (status, optimised ratio, limit, weights)."""
+    d2 = _f32(d2)
+    ratio, tau = C.c_float(0), C.c_float(0)
+    w = np.empty(d2.shape, dtype=np.float32)
+    L = lib()
+    L.orc_var_trimmed_dist.argtypes = [C.c_void_p, C.c_int64, C.c_float, C.c_float, C.c_float, C.c_void_p, C.c_void_p, C.c_void_p]
+    st = L.orc_var_trimmed_dist(_p(d2), d2.size, min_ratio, max_ratio, lam, C.byref(ratio), C.byref(tau), _p(w))
+    return st, ratio.value, tau.value, w
+
+
+def point_to_point(read_feat, ref_feat, ids, d2, w, precision=ORC_MIXED):
+    """PointToPointErrorMinimizer::compute on explicit matches / weights: returns (status, T 4x4 float32, kept)."""
+    read_feat, ref_feat = _f32(read_feat), _f32(ref_feat)
+    ids = np.ascontiguousarray(ids, dtype=np.int32)
+    d2, w = _f32(d2), _f32(w)
+    n, k = ids.shape
+    T = np.zeros((4, 4), dtype=np.float32)
+    kept = C.c_int32(0)
+    L = lib()
+    L.orc_point_to_point.argtypes = [C.c_void_p, C.c_int32, C.c_int64, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32,
+                                     C.c_int32, C.c_void_p, C.c_void_p]
+    st = L.orc_point_to_point(_p(read_feat), read_feat.shape[1], n, _p(ref_feat), ref_feat.shape[1], _p(ids), _p(d2), _p(w), k, precision,
+                              _p(T), C.byref(kept))
+    return st, T, kept.value
+
+
+def point_to_plane_covariance(read_feat, ref_feat, ref_normals, ids, d2, w, T, sensor_std_dev, precision=ORC_MIXED):
+    """PointToPlaneWithCovErrorMinimizer::estimateCovariance: returns (status, 6x6 float64)."""
+    read_feat, ref_feat, ref_normals = _f32(read_feat), _f32(ref_feat), _f32(ref_normals)
+    ids = np.ascontiguousarray(ids, dtype=np.int32)
+    d2, w, T = _f32(d2), _f32(w), _f32(T)
+    n, k = ids.shape
+    cov = np.zeros((6, 6), dtype=np.float64)
+    L = lib()
+    L.orc_point_to_plane_covariance.argtypes = [C.c_void_p, C.c_int32, C.c_int64, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p,
+                                                C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_float, C.c_void_p]
+    st = L.orc_point_to_plane_covariance(_p(read_feat), read_feat.shape[1], n, _p(ref_feat), ref_feat.shape[1], _p(ref_normals), _p(ids),
+                                         _p(d2), _p(w), k, precision, _p(T), sensor_std_dev, _p(cov))
+    return st, cov
+
+
+FILTER_MAX_DIST, FILTER_MIN_DIST, FILTER_BOUNDING_BOX, FILTER_RANDOM_SAMPLING = 0, 1, 2, 3
+
+
+def cloud_filter(feat, kind, dim=-1, dist=1.0, box=(-1, 1, -1, 1, -1, 1), remove_inside=True, random_method=0, prob=0.75, seed=1):
+    """MaxDist / MinDist / BoundingBox / RandomSampling DataPointsFilters: returns the boolean keep mask."""
+    feat = _f32(feat)
+    n = feat.shape[0]
+    keep = np.zeros(n, dtype=np.uint8)
+    b = np.asarray(box, dtype=np.float32)
+    L = lib()
+    L.orc_cloud_filter.restype = C.c_int64
+    L.orc_cloud_filter.argtypes = [C.c_void_p, C.c_int32, C.c_int64, C.c_int32, C.c_int32, C.c_float, C.c_void_p, C.c_int32, C.c_int32,
+                                   C.c_double, C.c_uint64, C.c_void_p]
+    cnt = L.orc_cloud_filter(_p(feat), feat.shape[1], n, kind, dim, dist, _p(b), int(remove_inside), random_method, prob, seed, _p(keep))
+    assert cnt == int(keep.sum())
+    return keep.astype(bool)

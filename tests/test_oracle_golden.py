@@ -408,3 +408,140 @@ def test_loop_closure_support_ops_known_answers(oracle):
         Gm = np.hstack([-tx, np.eye(3)])
         want += Gm.T @ Gm
     assert cnt == int(ok.sum()) and cnt > 100 and np.allclose(info, want, rtol=1e-12)
+
+
+def test_var_trimmed_dist_reference_known_answers(oracle):
+    """utest/ui/Outliers.cpp:126-151 (VarTrimmedDistOutlierFilterParameters): dists 4 5 5 5 5, minRatio 1e-7, maxRatio 1."""
+    O = oracle
+    d2 = np.array([4, 5, 5, 5, 5], dtype=np.float32)
+    st, ratio, tau, w = O.var_trimmed_dist(d2, 0.0000001, 1.0, 0.0)      # lambda 0: everything but the minimum is rejected
+    assert st == 0 and w.tolist() == [1, 0, 0, 0, 0] and ratio == 0.0 and tau == 4.0
+    st, ratio, tau, w = O.var_trimmed_dist(d2, 0.0000001, 1.0, 1.0)      # lambda 1: all kept
+    assert st == 0 and w.tolist() == [1, 1, 1, 1, 1] and ratio == np.float32(0.8)
+    assert O.var_trimmed_dist(d2, 0.8, 0.6, 1.0)[0] == O.ORC_E_PARAM                      # minRatio >= maxRatio (:160-163)
+    assert O.var_trimmed_dist(np.array([np.inf, 0.0], np.float32), 0.1, 0.9, 1.0)[0] == O.ORC_E_CONVERGENCE   # no valid match (:193)
+    # numpy restatement (float32 cumulative sum in order, FRMS, first argmin) on a contaminated distribution
+    rng = np.random.default_rng(5)
+    d2 = np.concatenate([rng.random(700) ** 2 * 0.01, rng.random(300) * 4 + 1]).astype(np.float32)
+    rng.shuffle(d2)
+    d2[::50] = np.inf
+    d2[7] = 0.0
+    prev = 0.0
+    for lam in (0.5, 0.95, 2.0):
+        st, ratio, tau, w = O.var_trimmed_dist(d2, 0.05, 0.99, lam)
+        srt = np.sort(d2[np.isfinite(d2) & (d2 > 0)])
+        cum = np.cumsum(srt, dtype=np.float32)
+        n = d2.size
+        lo, hi = int(np.floor(np.float32(0.05) * n)), min(int(np.floor(np.float32(0.99) * n)), srt.size)
+        ids = np.arange(lo + 1, hi + 1, dtype=np.float32)
+        deno = ((ids / np.float32(n)).astype(np.float64) ** lam).astype(np.float32)
+        frms = (cum[lo:hi] * (np.float32(1) / ids)) * ((np.float32(1) / deno) * (np.float32(1) / deno))
+        want = np.float32(int(frms.argmin()) + lo) / np.float32(n)
+        assert st == 0 and ratio == want, (lam, ratio, want)
+        assert ratio >= prev                                                              # a larger lambda rewards a larger inlier set
+        prev = ratio
+        st2, tau2, w2 = O.trimmed_dist(d2, ratio)
+        assert tau == tau2 and np.array_equal(w, w2)
+
+
+def test_point_to_point_minimizer_known_answers(oracle):
+    """PointToPoint.cpp:55-94: exact pairs under a known rigid transform are recovered; a mirrored set yields a rotation (the
+    reflection branch :80-85); weights and invalid matches act as in ErrorElements."""
+    O = oracle
+    rng = np.random.default_rng(6)
+    p = rng.uniform(-5, 5, (200, 3))
+    T = scenes.rigid(scenes.rot_axis_angle([0.3, -0.2, 1.0], np.deg2rad(25.0)), [0.7, -1.2, 0.4])
+    q = p @ T[:3, :3].T + T[:3, 3]
+    ids = np.arange(200, dtype=np.int32).reshape(-1, 1)
+    d2 = np.ones((200, 1), np.float32)
+    w = np.ones((200, 1), np.float32)
+    for prec in (O.ORC_REF32, O.ORC_MIXED):
+        st, To, kept = O.point_to_point(O.feat4(p), O.feat4(q), ids, d2, w, prec)
+        assert st == 0 and kept == 200 and np.abs(To - T).max() < (2e-5 if prec == O.ORC_REF32 else 2e-6)
+    # invalid matches and zero weights drop out: corrupt those pairs, the answer must not move
+    q2 = q.copy(); q2[:20] += 3.0
+    d2b = d2.copy(); d2b[:10] = np.inf
+    wb = w.copy(); wb[10:20] = 0.0
+    st, To, kept = O.point_to_point(O.feat4(p), O.feat4(q2), ids, d2b, wb)
+    assert st == 0 and kept == 180 and np.abs(To - T).max() < 2e-6
+    # fractional weights: equals the numpy weighted Kabsch
+    wf = rng.random((200, 1)).astype(np.float32) + 0.1
+    qn = q + rng.normal(0, 0.05, q.shape)
+    st, To, _ = O.point_to_point(O.feat4(p), O.feat4(qn), ids, d2, wf)
+    pf, qf = O.feat4(p)[:, :3].astype(np.float64), O.feat4(qn)[:, :3].astype(np.float64)
+    ww = wf[:, 0].astype(np.float64)
+    mp, mq = (pf * ww[:, None]).sum(0) / ww.sum(), (qf * ww[:, None]).sum(0) / ww.sum()
+    U, _, Vt = np.linalg.svd(((qf - mq) * ww[:, None]).T @ (pf - mp))
+    R = U @ Vt
+    assert np.linalg.det(R) > 0 and np.abs(To[:3, :3] - R).max() < 2e-6 and np.abs(To[:3, 3] - (mq - R @ mp)).max() < 2e-6
+    # a mirrored copy: U V^T is a reflection, the minimiser must still answer with a proper rotation
+    qm = p * np.array([1.0, 1.0, -1.0])
+    st, To, _ = O.point_to_point(O.feat4(p), O.feat4(qm), ids, d2, w)
+    assert st == 0 and abs(np.linalg.det(To[:3, :3].astype(np.float64)) - 1.0) < 1e-5
+    assert O.point_to_point(O.feat4(p), O.feat4(q), ids, d2, np.zeros_like(w))[0] == O.ORC_E_CONVERGENCE
+
+
+def test_point_to_plane_covariance_equals_numpy_restatement(oracle):
+    """PointToPlaneWithCov.cpp:70-160 written with numpy arrays, against the oracle's loop (fp64 lane), plus the no-normals answer."""
+    O = oracle
+    rng = np.random.default_rng(7)
+    n = 500
+    p = rng.uniform(-8, 8, (n, 3)); q = p + rng.normal(0, 0.02, (n, 3))
+    nr = rng.normal(size=(n, 3)); nr /= np.linalg.norm(nr, axis=1, keepdims=True)
+    ids = rng.permutation(n).astype(np.int32).reshape(-1, 1)
+    d2 = np.ones((n, 1), np.float32); d2[::17] = np.inf
+    w = np.ones((n, 1), np.float32); w[::13] = 0
+    T = scenes.rigid(scenes.rot_axis_angle([0.2, 0.5, 1.0], np.deg2rad(0.8)), [0.01, -0.02, 0.015]).astype(np.float32)
+    pf, qf, nf = O.feat4(p), O.feat4(q), nr.astype(np.float32)
+    st, cov = O.point_to_plane_covariance(pf, qf, nf, ids, d2, w, T, 0.05)
+    keep = np.isfinite(d2[:, 0]) & (w[:, 0] != 0)
+    r = pf[keep, :3].astype(np.float64); s = qf[ids[keep, 0], :3].astype(np.float64); nn = nf[ids[keep, 0]].astype(np.float64)
+    r -= r.mean(0); s -= s.mean(0)
+    Td = T.astype(np.float64)
+    beta = -np.arcsin(Td[2, 0]); alpha = np.arctan2(Td[2, 1], Td[2, 2]); gamma = np.arctan2(Td[1, 0] / np.cos(beta), Td[0, 0] / np.cos(beta))
+    t = Td[:3, 3]
+    rr = np.linalg.norm(r, axis=1); fr = np.linalg.norm(s, axis=1)
+    rd = r / rr[:, None]; fd = s / fr[:, None]
+    nabg = np.stack([nn[:, 2] * rd[:, 1] - nn[:, 1] * rd[:, 2], nn[:, 0] * rd[:, 2] - nn[:, 2] * rd[:, 0], nn[:, 1] * rd[:, 0] - nn[:, 0] * rd[:, 1]], 1)
+    Rlin = np.array([[1, -gamma, beta], [gamma, 1, -alpha], [-beta, alpha, 1]])
+    E = (nn * (r @ Rlin.T + t - s)).sum(1)
+    Nr = (nn * (rd @ Rlin.T)).sum(1)
+    Nf = -(nn * fd).sum(1)
+    V = np.hstack([nn, rr[:, None] * nabg])
+    A = np.hstack([nn * Nr[:, None], nabg * (E + rr * Nr)[:, None]])
+    B = np.hstack([nn * Nf[:, None], nabg * (fr * Nf)[:, None]])
+    Hi = np.linalg.inv(V.T @ V)
+    want = float(np.float32(0.05)) ** 2 * Hi @ (A.T @ A + B.T @ B) @ Hi                           # sensorStdDev is a float parameter
+    assert st == 0 and np.allclose(cov, want, rtol=1e-8, atol=1e-18)
+    assert np.allclose(cov, cov.T, rtol=1e-9, atol=1e-20) and (np.linalg.eigvalsh(cov) > -1e-18).all()
+    st, cov32 = O.point_to_plane_covariance(pf, qf, nf, ids, d2, w, T, 0.05, O.ORC_REF32)        # the reference's fp32 lane
+    assert st == 0 and np.allclose(cov32, want, rtol=5e-2, atol=1e-12)
+    st, none = O.point_to_plane_covariance(pf, qf, None, ids, d2, w, T, 0.05)                    # :91-92
+    assert st == 0 and np.array_equal(none, np.eye(6) * np.finfo(np.float32).max)
+
+
+def test_compacting_filters_known_answers(oracle):
+    """MaxDist / MinDist / BoundingBox / RandomSampling DataPointsFilters (DataPointsFilters/*.cpp) on small clouds."""
+    O = oracle
+    pts = np.array([[0, 0, 0], [1, 0, 0], [0, 2, 0], [0, 0, 3], [1, 1, 1], [-2, -2, -2], [3, 4, 0]], dtype=np.float32)
+    f = O.feat4(pts)
+    assert O.cloud_filter(f, O.FILTER_MAX_DIST, dim=-1, dist=-2.0).tolist() == [True, True, False, False, True, False, False]   # |maxDist|, strict
+    assert O.cloud_filter(f, O.FILTER_MAX_DIST, dim=1, dist=2.0).tolist() == [True, True, False, True, True, True, False]
+    assert O.cloud_filter(f, O.FILTER_MIN_DIST, dim=-1, dist=2.0).tolist() == [False, False, False, True, False, True, True]
+    assert O.cloud_filter(f, O.FILTER_MIN_DIST, dim=2, dist=-1.0).tolist() == [True, True, True, True, True, False, True]
+    box = (-0.5, 1.5, -0.5, 1.5, -0.5, 1.5)
+    assert O.cloud_filter(f, O.FILTER_BOUNDING_BOX, box=box, remove_inside=True).tolist() == [False, False, True, True, False, True, True]
+    assert O.cloud_filter(f, O.FILTER_BOUNDING_BOX, box=box, remove_inside=False).tolist() == [True, True, False, False, True, False, False]
+    assert O.cloud_filter(f, O.FILTER_BOUNDING_BOX, box=(0, 1, -1, 1, -1, 1), remove_inside=False).tolist() == [False] * 7     # strict bounds
+    # RandomSampling: minstd_rand(seed) draws against prob, at most floor(n * prob) + 1 points, deterministic per seed
+    big = O.feat4(np.random.default_rng(8).uniform(-1, 1, (20000, 3)))
+    for method in (0, 1):
+        k1 = O.cloud_filter(big, O.FILTER_RANDOM_SAMPLING, prob=0.3, seed=42, random_method=method)
+        k2 = O.cloud_filter(big, O.FILTER_RANDOM_SAMPLING, prob=0.3, seed=42, random_method=method)
+        k3 = O.cloud_filter(big, O.FILTER_RANDOM_SAMPLING, prob=0.3, seed=43, random_method=method)
+        assert np.array_equal(k1, k2) and not np.array_equal(k1, k3)
+        assert abs(k1.mean() - 0.3) < 0.015 and k1.sum() <= int(20000 * 0.3) + 1
+    # the first draws of minstd_rand(1): 48271, 182605794 -> / 2^31
+    k = O.cloud_filter(big[:2], O.FILTER_RANDOM_SAMPLING, prob=0.05, seed=1)
+    assert k.tolist() == [True, False]     # 48271 / 2^31 = 2.2e-5 < 0.05 ; 182605794 / 2^31 = 0.085 > 0.05
+    assert O.cloud_filter(big, O.FILTER_RANDOM_SAMPLING, prob=1.0, seed=3).all() and not O.cloud_filter(big, O.FILTER_RANDOM_SAMPLING, prob=0.0, seed=3).any()

@@ -43,7 +43,10 @@ def test_cuda_modules_are_registered_by_name(shim):
     assert "CudaKDTreeMatcher" in shim.list_modules("Matcher")
     assert {"CudaTrimmedDistOutlierFilter", "CudaSurfaceNormalOutlierFilter", "CudaMaxDistOutlierFilter", "CudaMinDistOutlierFilter",
             "CudaMedianDistOutlierFilter"} <= set(shim.list_modules("OutlierFilter"))
-    assert "CudaPointToPlaneErrorMinimizer" in shim.list_modules("ErrorMinimizer")
+    assert {"CudaPointToPlaneErrorMinimizer", "CudaPointToPlaneWithCovErrorMinimizer", "CudaPointToPointErrorMinimizer"} <= set(shim.list_modules("ErrorMinimizer"))
+    assert "CudaVarTrimmedDistOutlierFilter" in shim.list_modules("OutlierFilter")
+    assert {"CudaMaxDistDataPointsFilter", "CudaMinDistDataPointsFilter", "CudaBoundingBoxDataPointsFilter",
+            "CudaRandomSamplingDataPointsFilter"} <= set(shim.list_modules("DataPointsFilter"))
     assert {"CounterTransformationChecker", "DifferentialTransformationChecker", "BoundTransformationChecker"} <= set(shim.list_modules("TransformationChecker"))
 
 
@@ -63,6 +66,18 @@ def test_parameter_tables_match_the_cpu_twins(shim):
     assert p["vSizeX"] == ("1.0", "0.001", "+inf") and p["useCentroid"][0] == "1" and p["averageExistingDescriptors"][0] == "1"
     p = shim.module_parameters("DataPointsFilter", "CudaSurfaceNormalDataPointsFilter")
     assert p["knn"] == ("5", "3", "2147483647") and p["keepNormals"][0] == "1" and p["keepSurfaceDescriptors"][0] == "1" and p["keepDensities"][0] == "0"
+    p = shim.module_parameters("OutlierFilter", "CudaVarTrimmedDistOutlierFilter")                                           # OutlierFiltersImpl.h:153-159
+    assert p["minRatio"] == ("0.05", "0.0000001", "1") and p["maxRatio"] == ("0.99", "0.0000001", "1") and p["lambda"][0] == "2.35"
+    p = shim.module_parameters("ErrorMinimizer", "CudaPointToPlaneWithCovErrorMinimizer")                                   # PointToPlaneWithCov.h:70-76
+    assert p["force2D"] == ("0", "0", "1") and p["sensorStdDev"] == ("0.01", "0.", "inf")
+    assert set(shim.module_parameters("ErrorMinimizer", "CudaPointToPointErrorMinimizer")) == {"device"}                    # PointToPoint.h: no parameters
+    assert shim.module_parameters("DataPointsFilter", "CudaMaxDistDataPointsFilter")["maxDist"] == ("1", "-inf", "inf")     # MaxDist.h:57-62
+    p = shim.module_parameters("DataPointsFilter", "CudaMinDistDataPointsFilter")                                           # MinDist.h:57-62
+    assert p["dim"] == ("-1", "-1", "2") and p["minDist"] == ("1", "-inf", "inf")
+    p = shim.module_parameters("DataPointsFilter", "CudaBoundingBoxDataPointsFilter")                                       # BoundingBox.h:58-68
+    assert p["xMin"] == ("-1", "-inf", "inf") and p["zMax"] == ("1", "-inf", "inf") and p["removeInside"] == ("1", "0", "1")
+    p = shim.module_parameters("DataPointsFilter", "CudaRandomSamplingDataPointsFilter")                                    # RandomSampling.h:59-64
+    assert p["prob"] == ("0.75", "0", "1") and p["randomSamplingMethod"] == ("0", "0", "1")
     p = shim.module_parameters("TransformationChecker", "DifferentialTransformationChecker")
     assert p["minDiffRotErr"][0] == "0.001" and p["smoothLength"][0] == "3"
     assert shim.module_parameters("TransformationChecker", "CounterTransformationChecker")["maxIterationCount"][0] == "40"
@@ -255,3 +270,74 @@ def test_chain_with_distance_outlier_filters(shim, oracle, golden):
     assert not s2["fast_lane"] and s2["overlap"] < s0["overlap"] and np.isfinite(T2).all()
     with pytest.raises(shim.InvalidParameter):
         shim.ICP(base.replace("outlierFilters:\n", "outlierFilters:\n  - CudaMedianDistOutlierFilter:\n      factor: 0\n", 1))
+
+
+@pytest.mark.gpu
+def test_compacting_filters_by_name_match_oracle(shim, oracle, golden):
+    """utest/ui/DataFilters.cpp shapes (MaxDistDataPointsFilter, MinDistDataPointsFilter, BoundingBoxDataPointsFilter,
+    RandomSamplingDataPointsFilter tests): created through the registrar with string parameters, membership against the oracle."""
+    pts = oracle.feat4(golden["car"]["data_xyz"])
+    cases = [("CudaMaxDistDataPointsFilter", {"dim": -1, "maxDist": 7.0}, dict(kind=0, dim=-1, dist=7.0)),
+             ("CudaMaxDistDataPointsFilter", {"dim": 0, "maxDist": 0.5}, dict(kind=0, dim=0, dist=0.5)),
+             ("CudaMinDistDataPointsFilter", {"dim": -1, "minDist": 5.0}, dict(kind=1, dim=-1, dist=5.0)),
+             ("CudaMinDistDataPointsFilter", {"dim": 2, "minDist": 0.2}, dict(kind=1, dim=2, dist=0.2)),
+             ("CudaBoundingBoxDataPointsFilter", {"xMin": -5.5, "xMax": 6.5, "yMin": -10, "yMax": 8, "zMin": -1, "zMax": 3, "removeInside": 1},
+              dict(kind=2, box=(-5.5, 6.5, -10, 8, -1, 3), remove_inside=True)),
+             ("CudaBoundingBoxDataPointsFilter", {"xMin": -5.5, "xMax": 6.5, "yMin": -10, "yMax": 8, "zMin": -1, "zMax": 3, "removeInside": 0},
+              dict(kind=2, box=(-5.5, 6.5, -10, 8, -1, 3), remove_inside=False)),
+             ("CudaRandomSamplingDataPointsFilter", {"prob": 0.5, "seed": 77}, dict(kind=3, prob=0.5, seed=77)),
+             ("CudaRandomSamplingDataPointsFilter", {"prob": 0.25, "seed": 78, "randomSamplingMethod": 1}, dict(kind=3, prob=0.25, seed=78, random_method=1))]
+    for name, params, okw in cases:
+        f, _, _ = shim.apply_filter(name, params, pts)
+        keep = oracle.cloud_filter(pts, **okw)
+        assert 0 < keep.sum() < pts.shape[0], name
+        assert np.array_equal(f[:, :3], pts[keep, :3]), (name, params)
+    with pytest.raises(shim.InvalidParameter):
+        shim.apply_filter("CudaMaxDistDataPointsFilter", {"dim": 3}, pts)                     # dim bound of the parameter table
+    with pytest.raises(shim.InvalidParameter):
+        shim.apply_filter("CudaRandomSamplingDataPointsFilter", {"prob": 1.5}, pts)
+
+
+@pytest.mark.gpu
+def test_chains_with_point_to_point_var_trimmed_and_covariance(shim, oracle, golden):
+    """utest/ui/ErrorMinimizers.cpp / Outliers.cpp shapes (validate3dTransformation with the default chain and one module swapped):
+    PointToPoint + VarTrimmedDist reach validT3d like the reference's own tests require; PointToPlaneWithCov returns the transform
+    of the plain point-to-plane chain."""
+    car = golden["car"]
+    ref, rn, q = oracle.feat4(car["ref_xyz"]), car["ref_normals"], oracle.feat4(car["data_xyz"])
+    base = """matcher:
+  CudaKDTreeMatcher:
+    knn: 1
+outlierFilters:
+  - OUTLIER
+errorMinimizer:
+  MINIMIZER
+transformationCheckers:
+  - CounterTransformationChecker:
+      maxIterationCount: 40
+  - DifferentialTransformationChecker:
+      minDiffRotErr: 0.001
+      minDiffTransErr: 0.01
+      smoothLength: 3
+inspector:
+  NullInspector
+logger:
+  NullLogger
+"""
+    V = golden["T"]["validT3d"]
+    trimmed = "CudaTrimmedDistOutlierFilter:\n      ratio: 0.85"
+    vart = "CudaVarTrimmedDistOutlierFilter:\n      minRatio: 0.60\n      maxRatio: 0.80\n      lambda: 0.9"     # Outliers.cpp:113-123
+    T_pp, s_pp = shim.ICP(base.replace("OUTLIER", trimmed).replace("MINIMIZER", "CudaPointToPointErrorMinimizer"))(q, ref, None, None, rn)
+    T_vt, s_vt = shim.ICP(base.replace("OUTLIER", vart).replace("MINIMIZER", "CudaPointToPointErrorMinimizer"))(q, ref, None, None, rn)
+    T_pl, s_pl = shim.ICP(base.replace("OUTLIER", trimmed).replace("MINIMIZER", "CudaPointToPlaneErrorMinimizer"))(q, ref, None, None, rn)
+    T_cv, s_cv = shim.ICP(base.replace("OUTLIER", trimmed).replace("MINIMIZER", "CudaPointToPlaneWithCovErrorMinimizer:\n    sensorStdDev: 0.02"))(q, ref, None, None, rn)
+    for T, s in ((T_pp, s_pp), (T_vt, s_vt), (T_pl, s_pl), (T_cv, s_cv)):
+        assert np.isfinite(T).all() and not (s is not s_pl and s["fast_lane"])
+        # validate3dTransformation (utest/utest.cpp): translation norm within 0.1 ... of validT3d
+        assert abs(np.linalg.norm(V[:3, 3]) - np.linalg.norm(T[:3, 3])) < 0.1
+        R = T[:3, :3].astype(np.float64) @ V[:3, :3].T
+        assert np.degrees(np.arccos(np.clip((np.trace(R) - 1) / 2, -1, 1))) < 6.0
+    assert s_cv["iterations"] == s_pl["iterations"]
+    _assert_same_T(T_cv, T_pl, 1e-6)
+    with pytest.raises(shim.InvalidParameter):
+        shim.ICP(base.replace("OUTLIER", "CudaVarTrimmedDistOutlierFilter:\n      minRatio: 0.9\n      maxRatio: 0.5").replace("MINIMIZER", "CudaPointToPointErrorMinimizer"))
