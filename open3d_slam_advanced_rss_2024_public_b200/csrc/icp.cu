@@ -568,7 +568,7 @@ namespace {
 // --fmad=false), so both loops take the same decisions.
 __global__ void __launch_bounds__(32) icpTailKernel(const IcpDevParams* __restrict__ P, IcpDevState* __restrict__ S,
                                                     const double* __restrict__ result, const SelState* __restrict__ st,
-                                                    const unsigned long long* __restrict__ visitCounter,
+                                                    unsigned long long* __restrict__ visitCounter,
                                                     cudaGraphConditionalHandle handle) {
   if (threadIdx.x != 0) return;
   traceStamp(P->trace, 6);
@@ -609,6 +609,7 @@ __global__ void __launch_bounds__(32) icpTailKernel(const IcpDevParams* __restri
   S->tau = p.useTrim ? __uint_as_float(tauBits) : CUDART_INF_F;
   S->visits = visits;
   S->farPrev = farNow;
+  visitCounter[2] = 0ull;   // the match kernel's work counter (knn1LoopBody), for the next iteration
   S->lanes = p.lanesForced ? p.lanesForced : (((farNow - farPrev) * 16ull < (unsigned long long)p.n) ? 4 : 8);
   S->errKind = err;
   S->errA = errv[0]; S->errB = errv[1]; S->errC = errv[2]; S->errD = errv[3];
@@ -635,7 +636,7 @@ int buildLoopGraph(b200reg_icp* icp) {
   bool capturing = false;
   const bool useTrim = icp->cfg.trim_ratio > 0.f;
   SelState* st = selState(ctx);
-  const int knnBlocks = 24 * ctx->sm_count, redBlocks = 2 * ctx->sm_count;
+  const int knnBlocks = 6 * ctx->sm_count /* the resident grid of knn1LoopKernel: its warps pull work from a counter */, redBlocks = 2 * ctx->sm_count;
   if (ensureBuf(ctx, ctx->partials, sizeof(double) * NUM_MOM * (size_t)redBlocks) != B200REG_OK) return -1;
   {
     cudaGraphConditionalHandle handle;
@@ -664,7 +665,7 @@ int buildLoopGraph(b200reg_icp* icp) {
     ReduceParams RP;
     memset(&RP, 0, sizeof(RP));
     reduceKernel<<<redBlocks, 256, 0, ctx->stream>>>(RP, st, nullptr, &st->ticket[3], resultPtr(ctx), icp->dP, icp->dS);
-    icpTailKernel<<<1, 32, 0, ctx->stream>>>(icp->dP, icp->dS, resultPtr(ctx), st, (const unsigned long long*)icp->dBlock, handle);
+    icpTailKernel<<<1, 32, 0, ctx->stream>>>(icp->dP, icp->dS, resultPtr(ctx), st, (unsigned long long*)icp->dBlock, handle);
     nodes += 2;
     GRAPH_TRY(cudaGetLastError());
     capturing = false;

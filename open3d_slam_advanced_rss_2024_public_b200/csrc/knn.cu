@@ -332,34 +332,47 @@ __device__ __forceinline__ void knn1Query(const float4* __restrict__ pts, const 
     groupMin<G>(best);
   }
 
-  // ---- rings >= 2: the (y,z) rows of each shell are dealt to the G lanes.  Any point of a ring >= 2 is farther than
-  // sqrt(ring2Safe) (one whole cell minus the fp32 assignment slack), so a closer best ends the search here.
+  // ---- beyond the 3x3x3 neighbourhood: rings in the (y,z) plane only.  Ring r = the rows with max(|dy|, |dz|) == r; along x a row is
+  // ONE contiguous range of the directory, [xlo, xhi] = the cells a point with d2 <= bound can lie in (two loads, whatever its length),
+  // so a shell costs 8 r row look-ups instead of the 8 r rows + 2 (2r - 1)^2 end cells of a cubic shell.  Rings 0 and 1 are the nine
+  // rows of the first stage again, now beyond x = cx -+ 1 (two ranges per row).  A point found anywhere tightens bound, which prunes
+  // later rows (rowLb > bound) and shortens their x range; the walk ends at the first ring whose nearest face is farther than the best.
   {
-    int r = 2, rEnd = 0;
-    bool need = finite && !(best.d() < g.ring2Safe);
-    if (need) {
-      const int r0 = max(max(max(-ax.c, ax.c - (g.nx - 1)), max(-ay.c, ay.c - (g.ny - 1))), max(max(-az.c, az.c - (g.nz - 1)), 0));
-      rEnd = max(max(max(ax.c, g.nx - 1 - ax.c), max(ay.c, g.ny - 1 - ay.c)), max(az.c, g.nz - 1 - az.c));
-      r = max(2, r0);
-      need = r <= rEnd && !(ringLowerBound(ax, ay, az, r, g.cell, g.slack) > best.d());
+    const bool need0 = finite && !(best.d() < g.ring2Safe);   // any point outside the 3x3x3 cells is farther than sqrt(ring2Safe)
+    int r = 0, rEnd = -1;
+    if (need0) {
+      r = max(max(max(-ay.c, ay.c - (g.ny - 1)), max(-az.c, az.c - (g.nz - 1))), 0);   // first ring with a row inside the grid
+      rEnd = max(max(ay.c, g.ny - 1 - ay.c), max(az.c, g.nz - 1 - az.c));
     }
+    auto ringLb2 = [&](int rr) {
+      const float f = fminf(fminf(axisGap(ay, ay.c - rr, g.cell, g.slack), axisGap(ay, ay.c + rr, g.cell, g.slack)),
+                            fminf(axisGap(az, az.c - rr, g.cell, g.slack), axisGap(az, az.c + rr, g.cell, g.slack)));
+      return lb3(0.f, 0.f, f);
+    };
+    bool need = need0 && r <= rEnd && !(ringLb2(r) > best.d());
     if (need && l == 0) ++farQ;   // statistic: queries the 3x3x3 neighbourhood could not settle (drives the lanes-per-query choice)
     const unsigned gmask = ((1u << G) - 1u) << gbase;
     float bound = best.d();   // group-wide pruning bound (starts at maxDist^2); lane-local bests are merged after each ring
     while (__any_sync(FULL, need)) {
       if (need) {
-        // the shell's (y,z) rows, clipped to the grid (a query far outside it starts at a huge ring: never enumerate (2r+1)^2)
-        const int y0 = max(ay.c - r, 0), z0 = max(az.c - r, 0);
-        const int wy = max(min(ay.c + r, g.ny - 1) - y0 + 1, 0), wz = max(min(az.c + r, g.nz - 1) - z0 + 1, 0);
-        const int nrows = wy * wz;
+        // the ring's rows inside the grid: sides z = cz -+ r over y in [ya, yb], sides y = cy -+ r over z in [za, zb]
+        const int ya = max(ay.c - r, 0), yb = min(ay.c + r, g.ny - 1), za = max(az.c - r + 1, 0), zb = min(az.c + r - 1, g.nz - 1);
+        const int wy = max(yb - ya + 1, 0), wz = max(zb - za + 1, 0);
+        const int nA = ((unsigned)(az.c - r) < (unsigned)g.nz) ? wy : 0;
+        const int nB = (r > 0 && (unsigned)(az.c + r) < (unsigned)g.nz) ? wy : 0;
+        const int nC = (r > 0 && (unsigned)(ay.c - r) < (unsigned)g.ny) ? wz : 0;
+        const int nD = (r > 0 && (unsigned)(ay.c + r) < (unsigned)g.ny) ? wz : 0;
+        const int nrows = nA + nB + nC + nD;
         for (int t0 = 0; t0 < nrows; t0 += G) {   // one round = G rows, one per lane; the group stays converged
-          const int t = t0 + l;
-          const int iy = y0 + t % max(wy, 1), iz = z0 + t / max(wy, 1);
-          const int dy = iy - ay.c, dz = iz - az.c;
+          int t = t0 + l;
           if (t < nrows) {
+            int iy, iz;
+            if (t < nA) { iy = ya + t; iz = az.c - r; }
+            else if ((t -= nA) < nB) { iy = ya + t; iz = az.c + r; }
+            else if ((t -= nB) < nC) { iy = ay.c - r; iz = za + t; }
+            else { iy = ay.c + r; iz = za + (t - nC); }
             const float rowLb = lb3(0.f, axisGap(ay, iy, g.cell, g.slack), axisGap(az, iz, g.cell, g.slack));
             if (!(rowLb > bound)) {
-              const bool shellRow = (abs(dz) == r) || (abs(dy) == r);
               // x cells a better point of this row can lie in: the index build's own (monotone) cell function applied to
               // q.x -+ reach, reach = sqrt(bound - rowLb) + slack  =>  no point with d2 <= bound falls outside [xlo, xhi]
               int xlo = 0, xhi = g.nx - 1;
@@ -371,15 +384,10 @@ __device__ __forceinline__ void knn1Query(const float4* __restrict__ pts, const 
               const uint32_t rowBase = (uint32_t)g.nx * ((uint32_t)iy + (uint32_t)g.ny * (uint32_t)iz);
 #pragma unroll 1
               for (int seg = 0; seg < 2; ++seg) {
-                int xa, xb;
-                if (shellRow) {
-                  if (seg == 1) break;
-                  xa = ax.c - r; xb = ax.c + r;
-                } else {   // interior row of the shell: only its two end cells
-                  xa = xb = (seg == 0) ? ax.c - r : ax.c + r;
-                }
-                xa = max(xa, xlo);
-                xb = min(xb, xhi);
+                int xa = xlo, xb = xhi;
+                if (r <= 1) {   // cells cx - 1 .. cx + 1 of these rows were the first stage's
+                  if (seg == 0) xb = min(xb, ax.c - 2); else xa = max(xa, ax.c + 2);
+                } else if (seg == 1) break;
                 if (xa > xb) continue;
                 const uint32_t s = cellStart[rowBase + xa], e = cellStart[rowBase + xb + 1];
                 for (uint32_t j = s; j < e; j += 4) {   // four independent loads in flight per lane (this loop is latency bound)
@@ -402,7 +410,7 @@ __device__ __forceinline__ void knn1Query(const float4* __restrict__ pts, const 
       groupMin<G>(best);
       if (need) {
         ++r;
-        need = r <= rEnd && !(ringLowerBound(ax, ay, az, r, g.cell, g.slack) > best.d());
+        need = r <= rEnd && !(ringLb2(r) > best.d());
       }
     }
   }
@@ -476,8 +484,10 @@ __global__ void __launch_bounds__(256) knn1GroupKernel(const float4* __restrict_
 // instantiated CUDA graph serves every reading size and reference.
 template <int G>
 __device__ __forceinline__ void knn1LoopBody(const IcpDevParams* __restrict__ P, const IcpDevState* __restrict__ S, unsigned& visits,
-                                             unsigned& farQ, unsigned* __restrict__ sHist) {
+                                             unsigned& farQ, unsigned* __restrict__ sHist, unsigned long long* __restrict__ work) {
   constexpr int LOG2G = (G == 8) ? 3 : 2;
+  constexpr int QPW = 32 >> LOG2G;   // queries of one warp-wide call
+  constexpr int CHUNK = QPW;         // queries a warp takes from the work counter at a time
   const GridDesc g = P->g;
   const float4* pts = P->pts;
   const uint32_t* cellStart = P->cellStart;
@@ -493,11 +503,19 @@ __device__ __forceinline__ void knn1LoopBody(const IcpDevParams* __restrict__ P,
   Rigid12 T;
 #pragma unroll
   for (int j = 0; j < 12; ++j) T.m[j] = S->T[j];
-  const int64_t groupsPerGrid = ((int64_t)gridDim.x * blockDim.x) >> LOG2G;
-  const int64_t first = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> LOG2G;
-  const int64_t blockFirst = ((int64_t)blockIdx.x * blockDim.x) >> LOG2G;
-  for (int64_t base = 0; blockFirst + base < n; base += groupsPerGrid)   // trip count uniform over the block
-    knn1Query<G, false>(pts, cellStart, g, queries, n, first + base, 1, T, maxd2, ids, d2, pos, visits, farQ, sHist, seed);
+  // Query cost varies by an order of magnitude (a query far from the map walks rings, and such queries come in runs: the scan is in
+  // sensor order), so the warps of the resident grid take chunks of 32 consecutive queries from a counter instead of a fixed stride:
+  // no warp idles while another still has a run of far queries ahead of it.  The loop's tail resets the counter.
+  const int lane = threadIdx.x & 31;
+  for (;;) {
+    long long base = 0;
+    if (lane == 0) base = (long long)atomicAdd(work, (unsigned long long)CHUNK);
+    base = __shfl_sync(0xffffffffu, base, 0);
+    if (base >= n) break;
+#pragma unroll 1
+    for (int sub = 0; sub < CHUNK; sub += QPW)
+      knn1Query<G, false>(pts, cellStart, g, queries, n, base + sub + (lane >> LOG2G), 1, T, maxd2, ids, d2, pos, visits, farQ, sHist, seed);
+  }
 }
 
 // S->lanes (written by the loop's tail from the previous iteration's far-query count) picks the decomposition: 8 lanes per
@@ -516,8 +534,8 @@ __global__ void __launch_bounds__(256, 6) knn1LoopKernel(const IcpDevParams* __r
   __syncthreads();
   traceStamp(P->trace, 1);
   unsigned visits = 0, farQ = 0;
-  if (S->lanes == 4) knn1LoopBody<4>(P, S, visits, farQ, sHist);
-  else knn1LoopBody<8>(P, S, visits, farQ, sHist);
+  if (S->lanes == 4) knn1LoopBody<4>(P, S, visits, farQ, sHist, visitCounter + 2);
+  else knn1LoopBody<8>(P, S, visits, farQ, sHist, visitCounter + 2);
   flushVisits(visits, farQ, &sVisits, &sFarQ, &sTicket, visitCounter, sHist, gHist);
 }
 
