@@ -1088,7 +1088,9 @@ void symEig3(const double Cin[9], double val[3], double vec[3][3]) {
     if (off == 0.0) break;
     for (int p = 0; p < 3; ++p)
       for (int q = p + 1; q < 3; ++q) {
-        if (a[p][q] == 0.0) continue;
+        // converged pair: an off-diagonal below 2^-70 of its diagonals rotates by an angle no fp64 result can see; without this
+        // the residue left by each rotation never reaches exactly 0 and most matrices run all 64 sweeps
+        if (fabs(a[p][q]) <= 8.470329472543003e-22 * (fabs(a[p][p]) + fabs(a[q][q]))) { a[p][q] = 0.0; a[q][p] = 0.0; continue; }
         const double theta = (a[q][q] - a[p][p]) / (2.0 * a[p][q]);
         const double t = ((theta >= 0) ? 1.0 : -1.0) / (std::fabs(theta) + std::sqrt(theta * theta + 1.0));
         const double c = 1.0 / std::sqrt(t * t + 1.0), s = t * c;
