@@ -142,6 +142,12 @@ struct IcpDevState {    // initialised by the host, advanced by icpTailKernel ev
 };
 #define ICP_STATE_HEAD_BYTES offsetof(IcpDevState, chk)
 
+// resident blocks per SM of the k = 1 match kernels (knn.cu): 4 x 256 threads leave 64 registers per thread — no spills; 5, 6 and 8
+// blocks (48 / 40 / 32 registers, 140-460 B of spills) and 2-3 blocks (80-119 registers) all measured slower (profiles/r1_notes.md)
+#ifndef KNN1_LOOP_MINB
+#define KNN1_LOOP_MINB 4
+#endif
+
 #define DSTATE_BYTES 131072      /* ctx->dstate; [32768, 49152) is scratch of normals.cu / map.cu */
 #define DSTATE_TRACE_OFF 16384   /* 1 + 2047 x uint64 inside ctx->dstate */
 #define DSTATE_FH0_OFF 65536     /* fused select: pass-0 histogram, 2048 x uint32 */

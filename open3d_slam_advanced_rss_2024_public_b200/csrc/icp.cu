@@ -636,7 +636,7 @@ int buildLoopGraph(b200reg_icp* icp) {
   bool capturing = false;
   const bool useTrim = icp->cfg.trim_ratio > 0.f;
   SelState* st = selState(ctx);
-  const int knnBlocks = 6 * ctx->sm_count /* the resident grid of knn1LoopKernel: its warps pull work from a counter */, redBlocks = 2 * ctx->sm_count;
+  const int knnBlocks = KNN1_LOOP_MINB * ctx->sm_count /* the resident grid of knn1LoopKernel: its warps pull work from a counter */, redBlocks = 2 * ctx->sm_count;
   if (ensureBuf(ctx, ctx->partials, sizeof(double) * NUM_MOM * (size_t)redBlocks) != B200REG_OK) return -1;
   {
     cudaGraphConditionalHandle handle;

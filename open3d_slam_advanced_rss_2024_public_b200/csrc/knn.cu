@@ -8,6 +8,7 @@
 // are (after subtracting GridDesc::slack) never larger than the true per-axis separation, so by monotonicity of
 // round-to-nearest the bound never exceeds the computed d2 of any point in the cell.  Cells whose bound equals the
 // current k-th distance are still visited (a tie with a smaller index may hide there).
+#include <algorithm>
 #include <cfloat>
 #include <cmath>
 
@@ -464,18 +465,29 @@ __device__ __forceinline__ void flushVisits(unsigned visits, unsigned farQ, unsi
   }
 }
 
+// Stand-alone match (b200reg_knn, the host-driven loop): like knn1LoopKernel a resident grid (KNN1_MINB blocks per SM) whose warps
+// take 32/G queries per grab from `work` (zeroed by the launcher) — query cost varies by an order of magnitude and far queries come
+// in runs, so no warp idles behind one.
 template <int G, bool SELFCHK>
-__global__ void __launch_bounds__(256) knn1GroupKernel(const float4* __restrict__ pts, const uint32_t* __restrict__ cellStart, GridDesc g,
-                                                       const float4* __restrict__ queries, int64_t n, int hasT, Rigid12 T, float maxd2,
-                                                       int* __restrict__ outIds, float* __restrict__ outD2, int* outPos,
-                                                       unsigned long long* __restrict__ visitCounter, const int* seedPos) {
+__global__ void __launch_bounds__(256, KNN1_LOOP_MINB) knn1GroupKernel(const float4* __restrict__ pts, const uint32_t* __restrict__ cellStart, GridDesc g,
+                                                                       const float4* __restrict__ queries, int64_t n, int hasT, Rigid12 T, float maxd2,
+                                                                       int* __restrict__ outIds, float* __restrict__ outD2, int* outPos,
+                                                                       unsigned long long* __restrict__ visitCounter, const int* seedPos,
+                                                                       unsigned long long* __restrict__ work) {
   constexpr int LOG2G = (G == 8) ? 3 : 2;
+  constexpr int QPW = 32 >> LOG2G;   // queries of one warp-wide call
   __shared__ unsigned sVisits, sFarQ, sTicket;
   if (threadIdx.x == 0) { sVisits = 0; sFarQ = 0; sTicket = 0; }
   __syncthreads();   // all warps are at the start here: nobody waits on a straggler
   unsigned visits = 0, farQ = 0;
-  const int64_t qi = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> LOG2G;
-  knn1Query<G, SELFCHK>(pts, cellStart, g, queries, n, qi, hasT, T, maxd2, outIds, outD2, outPos, visits, farQ, nullptr, seedPos);
+  const int lane = threadIdx.x & 31;
+  for (;;) {
+    long long base = 0;
+    if (lane == 0) base = (long long)atomicAdd(work, (unsigned long long)QPW);
+    base = __shfl_sync(0xffffffffu, base, 0);
+    if (base >= n) break;
+    knn1Query<G, SELFCHK>(pts, cellStart, g, queries, n, base + (lane >> LOG2G), hasT, T, maxd2, outIds, outD2, outPos, visits, farQ, nullptr, seedPos);
+  }
   flushVisits(visits, farQ, &sVisits, &sFarQ, &sTicket, visitCounter);
 }
 
@@ -520,7 +532,7 @@ __device__ __forceinline__ void knn1LoopBody(const IcpDevParams* __restrict__ P,
 
 // S->lanes (written by the loop's tail from the previous iteration's far-query count) picks the decomposition: 8 lanes per
 // query while many queries need rings >= 2 (the first iterations of a badly aligned scan), 4 once they are rare.
-__global__ void __launch_bounds__(256, 6) knn1LoopKernel(const IcpDevParams* __restrict__ P, const IcpDevState* __restrict__ S,
+__global__ void __launch_bounds__(256, KNN1_LOOP_MINB) knn1LoopKernel(const IcpDevParams* __restrict__ P, const IcpDevState* __restrict__ S,
                                                          unsigned long long* __restrict__ visitCounter) {
   __shared__ unsigned sVisits, sFarQ, sTicket;
   __shared__ unsigned sHistBuf[2050];   // pass-0 histogram of the block's d2 + touched bin range
@@ -730,11 +742,12 @@ void launchKnnList(b200reg_ctx* ctx, const b200reg_index* ix, const float4* q, i
 
 template <int G>
 void launchKnn1(b200reg_ctx* ctx, const b200reg_index* ix, const float4* q, int64_t n, int hasT, const Rigid12& T, float maxd2, int allowSelf, int* ids, float* d2, int* pos, unsigned long long* visits, const int* seed) {
-  const int blocks = divUp(n * G, 256);
+  const int blocks = (int)std::min<int64_t>(divUp(n * G, 256), (int64_t)KNN1_LOOP_MINB * ctx->sm_count);   // resident grid
+  unsigned long long* work = visits + 2;   // dstate[2], zeroed by runKnn
   if (allowSelf)
-    knn1GroupKernel<G, false><<<blocks, 256, 0, ctx->stream>>>(ix->pts, ix->cellStart, ix->g, q, n, hasT, T, maxd2, ids, d2, pos, visits, seed);
+    knn1GroupKernel<G, false><<<blocks, 256, 0, ctx->stream>>>(ix->pts, ix->cellStart, ix->g, q, n, hasT, T, maxd2, ids, d2, pos, visits, seed, work);
   else
-    knn1GroupKernel<G, true><<<blocks, 256, 0, ctx->stream>>>(ix->pts, ix->cellStart, ix->g, q, n, hasT, T, maxd2, ids, d2, pos, visits, seed);
+    knn1GroupKernel<G, true><<<blocks, 256, 0, ctx->stream>>>(ix->pts, ix->cellStart, ix->g, q, n, hasT, T, maxd2, ids, d2, pos, visits, seed, work);
 }
 
 template <int K>
@@ -774,6 +787,7 @@ int runKnn(b200reg_ctx* ctx, const b200reg_index* ix, const float4* queries, int
   int* pos = (int*)ctx->matchPos.p;
   unsigned long long* visits = (unsigned long long*)ctx->dstate;
   const int hasT = T ? 1 : 0;
+  if (k == 1 && ctx->knnLanes != 1) CUDA_TRY(ctx, cudaMemsetAsync(visits + 2, 0, sizeof(unsigned long long), ctx->stream));   // work counter of knn1GroupKernel
   profBegin(ctx);
   const int* seed = (seeded && ctx->knnSeed && ctx->knnLanes == 4) ? pos : nullptr;   // as in knn1LoopBody: only in the 4-lane regime
   if (k == 1 && (ctx->knnLanes == 8 || ctx->knnLanes == 0)) launchKnn1<8>(ctx, ix, queries, n, hasT, R, maxd2, allowSelf, ids, d2, pos, visits, seed);
