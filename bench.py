@@ -28,7 +28,7 @@ sys.path.insert(0, os.path.join(ROOT, "tests"))
 B_KNN1 = 536          # algorithmic bytes per k=1 query   (SURVEY 8d / BASELINE.md §5)
 B_ITER = 600          # algorithmic bytes per reading point per ICP iteration
 B_BUILD = 156         # algorithmic bytes per reference point for the index build
-NCU_TRAFFIC_BYTES = 32_980_000   # dram__bytes_read + write per match launch, mean of the 5 launches of one registration (profiles/r1/ncu_full_knn1_r1h.txt)
+NCU_TRAFFIC_BYTES = 33_190_000   # dram__bytes_read + write per match launch, mean of the 5 launches of one registration (profiles/r1/ncu_full_knn1_hostloop_r1j.txt)
 ICP_KW = dict(knn=1, max_dist=1.0, trim_ratio=0.8, max_iter=40, min_diff_rot=1e-3, min_diff_trans=1e-2, smooth_length=3)
 
 
