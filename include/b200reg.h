@@ -25,7 +25,7 @@
 extern "C" {
 #endif
 
-#define B200REG_ABI_VERSION 1
+#define B200REG_ABI_VERSION 2
 
 enum {
   B200REG_OK = 0,
@@ -87,7 +87,9 @@ void    b200reg_cloud_free(b200reg_ctx* ctx, b200reg_cloud* cloud);
 int32_t b200reg_cloud_transform(b200reg_ctx* ctx, b200reg_cloud* inout, const float T[16]);
 
 /* ---- KDTreeMatcher::init (MatchersImpl.cpp:109-114) -> index build; KDTreeMatcher::findClosests (:117-132) -> knn ---- */
-/* cell <= 0 : automatic cell size.  The index copies what it needs; `ref` may be freed afterwards. */
+/* cell <= 0 : automatic cell size.  The index copies what it needs; `ref` may be freed afterwards.  The directory holds at most
+ * max(8 x points, 65536) cells (<= 2^30): a smaller requested cell is grown by factors of 1.26 until the grid fits (the search stays
+ * exact for any cell size).  Non-finite coordinates in `ref` -> B200REG_E_INVALID_PARAM. */
 int32_t b200reg_index_build(b200reg_ctx* ctx, const b200reg_cloud* ref, float cell, b200reg_index** out);
 void    b200reg_index_free(b200reg_ctx* ctx, b200reg_index* index);
 int64_t b200reg_index_size(const b200reg_index* index);
@@ -175,14 +177,20 @@ typedef struct b200reg_icp_config {
   float   max_angle;      /* SurfaceNormalOutlierFilter maxAngle; < 0 absent                          */
   int32_t force2D;        /* PointToPlane.h:74                                                       */
   int32_t force4DOF;      /* PointToPlane.h:75                                                       */
-  int32_t max_iter;       /* CounterTransformationChecker maxIterationCount; <= 0 absent             */
+  int32_t max_iter;       /* CounterTransformationChecker maxIterationCount; < 0 absent (0 stops after the first
+                             iteration, exactly like 1: counter >= limit, TransformationCheckersImpl.cpp:70)       */
   float   min_diff_rot;   /* DifferentialTransformationChecker (TransformationCheckersImpl.h:88-93)  */
   float   min_diff_trans;
   int32_t smooth_length;  /* < 0 : checker absent                                                    */
   float   bound_rot;      /* BoundTransformationChecker; < 0 absent                                  */
   float   bound_trans;
   float   cell;           /* index cell size for b200reg_icp_set_reference; <= 0 automatic           */
+  int32_t checker_order[3]; /* order the chain lists its checkers in (B200REG_CHECKER_*, 0 ends the list): the reference
+                             evaluates them in that order and Counter's MaxNumIterationsReached throw skips the ones
+                             behind it (ICP.cpp:437-446).  All 0 = Differential, Bound, Counter.  Whatever the
+                             configuration, the loop gives up with B200REG_E_NOT_CONVERGED after 10000 iterations.    */
 } b200reg_icp_config;
+enum { B200REG_CHECKER_COUNTER = 1, B200REG_CHECKER_DIFFERENTIAL = 2, B200REG_CHECKER_BOUND = 3 };
 
 typedef struct b200reg_icp_stats {   /* the reference's Inspector stat names (ICP.cpp:282-284,391-393,452-456) */
   int32_t iterations;                 /* IterationsCount                 */
@@ -203,16 +211,42 @@ typedef struct b200reg_icp_stats {   /* the reference's Inspector stat names (IC
 typedef struct b200reg_icp b200reg_icp;   /* PointMatcher<float>::ICP with the CUDA chain inside */
 int32_t b200reg_icp_create(b200reg_ctx* ctx, const b200reg_icp_config* cfg, b200reg_icp** out);
 void    b200reg_icp_destroy(b200reg_icp* icp);
-/* ICP::initReference (ICP.cpp:293-328): mean, centring, index build.  Keeps its own copy of what it needs. */
+/* ICP::initReference (ICP.cpp:293-328): mean, centring, index build.  Keeps its own copy of what it needs.  The work is only
+ * ENQUEUED on the ctx stream (mean, bounding box and grid are derived on the device): the call does not wait for the GPU, and a
+ * reference with non-finite coordinates is reported (B200REG_E_INVALID_PARAM) by the next call that needs the result —
+ * b200reg_icp_register, b200reg_icp_reference_mean or b200reg_index_cell(b200reg_icp_index(icp)). */
 int32_t b200reg_icp_set_reference(b200reg_icp* icp, const b200reg_cloud* reference);
 /* ICP::compute(reading, <empty>, T_init, initializeMatcher=false) (ICP.cpp:258-290 + 332-468), as Mapper.cpp:391-393 calls it */
 int32_t b200reg_icp_register(b200reg_icp* icp, const b200reg_cloud* reading, const float T_init[16], float T_out[16],
                              b200reg_icp_stats* stats);
-/* n independent registrations on this ctx's device: pair i = initReference(refs[i]) + compute(readings[i], T_init + 16 i)
- * -> T_out + 16 i (the loop-closure refinement loop, open3d_slam/src/PlaceRecognition.cpp:71-174).  One call per
- * GPU; sharding pairs over GPUs and gathering the results is the caller's (batch.py: pair i -> rank i mod G, one all_gather).
- * stats / status: arrays of n, nullable.  With `status` the call returns OK and reports per-pair codes (a failed pair
- * keeps T_out = T_init); without it the first failure code is returned. */
+/* ---- batched registration: n independent pairs, pair i = initReference(refs[i]) + compute(readings[i], T_init + 16 i) -> T_out + 16 i
+ *      (the loop-closure refinement loop, open3d_slam/src/PlaceRecognition.cpp:71-174).  A batch object owns `lanes`
+ *      independent lanes on the ctx's device (stream, scratch, ICP object with its instantiated loop graph, reusable clouds); pair i
+ *      runs on lane i mod lanes and up to `lanes` pairs are in flight at once — uploads, index build, reading preparation, the
+ *      device-resident loop and the read-back of one pair are enqueued without a host wait, and the kernels of different lanes
+ *      interleave on the device.  Every pair's result is bit-identical to b200reg_icp_set_reference + b200reg_icp_register.
+ *      lanes <= 0: default (4, or env B200REG_BATCH_LANES).  The configuration must have knn == 1.
+ *      stats / status: arrays of n, nullable.  With `status` the call returns OK and reports per-pair codes (a failed pair keeps
+ *      T_out = T_init, what Mapper.cpp:420-428 falls back to); without it the first failure code is returned.
+ *      One batch per (thread, device); sharding pairs over GPUs and gathering the results: b200reg_multi_* below. */
+typedef struct b200reg_batch b200reg_batch;
+int32_t b200reg_batch_create(b200reg_ctx* ctx, const b200reg_icp_config* cfg, int32_t lanes, b200reg_batch** out);
+void    b200reg_batch_destroy(b200reg_batch* batch);
+int32_t b200reg_batch_lanes(const b200reg_batch* batch);
+/* clouds already on the device (created on `ctx`) */
+int32_t b200reg_batch_register(b200reg_batch* batch, int32_t n, const b200reg_cloud* const* refs, const b200reg_cloud* const* readings,
+                               const float* T_init, float* T_out, b200reg_icp_stats* stats, int32_t* status);
+/* HOST clouds (layout of b200reg_cloud_upload_f32; normals nullable for readings, required for references): the uploads are part of
+ * the pipeline.  The buffers must stay valid until the call returns; pinned memory lets the copies overlap the other lanes' kernels. */
+typedef struct b200reg_host_cloud {
+  const float* feat;
+  int32_t feat_stride;
+  const float* normals;
+  int64_t n;
+} b200reg_host_cloud;
+int32_t b200reg_batch_register_host(b200reg_batch* batch, int32_t n, const b200reg_host_cloud* refs, const b200reg_host_cloud* readings,
+                                    const float* T_init, float* T_out, b200reg_icp_stats* stats, int32_t* status);
+/* one-shot form of b200reg_batch_register: a batch object with the default number of lanes for the duration of the call */
 int32_t b200reg_icp_register_batch(b200reg_ctx* ctx, const b200reg_icp_config* cfg, int32_t n, const b200reg_cloud* const* refs,
                                    const b200reg_cloud* const* readings, const float* T_init, float* T_out, b200reg_icp_stats* stats,
                                    int32_t* status);

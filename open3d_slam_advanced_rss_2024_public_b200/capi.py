@@ -89,7 +89,15 @@ class IcpConfig(C.Structure):
     _fields_ = [("knn", C.c_int32), ("max_dist", C.c_float), ("epsilon", C.c_float), ("trim_ratio", C.c_float),
                 ("max_angle", C.c_float), ("force2D", C.c_int32), ("force4DOF", C.c_int32), ("max_iter", C.c_int32),
                 ("min_diff_rot", C.c_float), ("min_diff_trans", C.c_float), ("smooth_length", C.c_int32),
-                ("bound_rot", C.c_float), ("bound_trans", C.c_float), ("cell", C.c_float)]
+                ("bound_rot", C.c_float), ("bound_trans", C.c_float), ("cell", C.c_float), ("checker_order", C.c_int32 * 3)]
+
+
+CHECKER_COUNTER, CHECKER_DIFFERENTIAL, CHECKER_BOUND = 1, 2, 3
+
+
+class HostCloud(C.Structure):
+    """b200reg_host_cloud: a cloud in host memory (layout of b200reg_cloud_upload_f32)."""
+    _fields_ = [("feat", C.c_void_p), ("feat_stride", C.c_int32), ("normals", C.c_void_p), ("n", C.c_int64)]
 
 
 class IcpStats(C.Structure):
@@ -145,6 +153,11 @@ SYMBOLS = {
     "b200reg_icp_set_reference": (C.c_int32, [_VP, _VP]),
     "b200reg_icp_register": (C.c_int32, [_VP, _VP, _VP, _VP, C.POINTER(IcpStats)]),
     "b200reg_icp_register_batch": (C.c_int32, [_VP, C.POINTER(IcpConfig), C.c_int32, _VP, _VP, _VP, _VP, _VP, _VP]),
+    "b200reg_batch_create": (C.c_int32, [_VP, C.POINTER(IcpConfig), C.c_int32, C.POINTER(_VP)]),
+    "b200reg_batch_destroy": (None, [_VP]),
+    "b200reg_batch_lanes": (C.c_int32, [_VP]),
+    "b200reg_batch_register": (C.c_int32, [_VP, C.c_int32, _VP, _VP, _VP, _VP, _VP, _VP]),
+    "b200reg_batch_register_host": (C.c_int32, [_VP, C.c_int32, _VP, _VP, _VP, _VP, _VP, _VP]),
     "b200reg_icp_index": (_VP, [_VP]),
     "b200reg_icp_reference_mean": (C.c_int32, [_VP, _VP]),
     "b200reg_voxelgrid": (C.c_int32, [_VP, _VP, C.c_float, C.c_float, C.c_float, C.c_int32, C.c_int32]),
@@ -224,6 +237,8 @@ def icp_config(**kw):
     for k, v in kw.items():
         if not hasattr(c, k):
             raise AttributeError(k)
+        if k == "checker_order":
+            v = (C.c_int32 * 3)(*(list(v) + [0, 0, 0])[:3])
         setattr(c, k, v)
     return c
 
@@ -598,6 +613,66 @@ def register_batch(ctx, cfg, refs, readings, T_init):
     ctx.check(lib().b200reg_icp_register_batch(ctx.h, C.byref(cfg), n, C.cast(rh, _VP), C.cast(qh, _VP), _p(Ti), _p(To), C.cast(stats, _VP),
                                                _p(status)))
     return To.reshape(n, 4, 4), list(stats)[:n], status[:n]
+
+
+class Batch:
+    """b200reg_batch: `lanes` registrations in flight on the ctx's device (pair i -> lane i mod lanes)."""
+
+    def __init__(self, ctx, cfg=None, lanes=0, **kw):
+        self.ctx = ctx
+        self.cfg = cfg if cfg is not None else icp_config(**kw)
+        self.h = _VP()
+        ctx.check(lib().b200reg_batch_create(ctx.h, C.byref(self.cfg), int(lanes), C.byref(self.h)))
+
+    @property
+    def lanes(self):
+        return int(lib().b200reg_batch_lanes(self.h))
+
+    def _out(self, n, T_init):
+        Ti = np.ascontiguousarray(np.asarray(T_init, dtype=np.float32).reshape(n, 16))
+        return Ti, np.zeros((n, 16), dtype=np.float32), (IcpStats * max(n, 1))(), np.zeros(max(n, 1), dtype=np.int32)
+
+    def register(self, refs, readings, T_init):
+        """refs / readings: lists of device Clouds of this ctx.  Returns (T n x 4 x 4, [IcpStats], status int32[n])."""
+        n = len(refs)
+        assert len(readings) == n
+        Ti, To, stats, status = self._out(n, T_init)
+        rh = (_VP * max(n, 1))(*[c.h.value if isinstance(c.h, _VP) else c.h for c in refs])
+        qh = (_VP * max(n, 1))(*[c.h.value if isinstance(c.h, _VP) else c.h for c in readings])
+        self.ctx.check(lib().b200reg_batch_register(self.h, n, C.cast(rh, _VP), C.cast(qh, _VP), _p(Ti), _p(To), C.cast(stats, _VP), _p(status)))
+        return To.reshape(n, 4, 4), list(stats)[:n], status[:n]
+
+    @staticmethod
+    def host_clouds(items):
+        """items: [(feat N x stride float32 C-contiguous, normals N x 3 float32 or None)] -> (HostCloud array, keep-alive list)."""
+        arr = (HostCloud * max(len(items), 1))()
+        keep = []
+        for i, (feat, nrm) in enumerate(items):
+            assert feat.dtype == np.float32 and feat.flags.c_contiguous and (nrm is None or (nrm.dtype == np.float32 and nrm.flags.c_contiguous))
+            keep.append((feat, nrm))
+            arr[i] = HostCloud(feat.ctypes.data, feat.shape[1], None if nrm is None else nrm.ctypes.data, feat.shape[0])
+        return arr, keep
+
+    def register_host(self, refs, readings, T_init):
+        """refs / readings: HostCloud arrays from host_clouds() (keep the numpy arrays alive).  The uploads are part of the pipeline."""
+        n = len(refs) if not isinstance(refs, tuple) else len(refs[1])
+        ra = refs[0] if isinstance(refs, tuple) else refs
+        qa = readings[0] if isinstance(readings, tuple) else readings
+        Ti, To, stats, status = self._out(n, T_init)
+        self.ctx.check(lib().b200reg_batch_register_host(self.h, n, C.cast(ra, _VP), C.cast(qa, _VP), _p(Ti), _p(To), C.cast(stats, _VP), _p(status)))
+        return To.reshape(n, 4, 4), list(stats)[:n], status[:n]
+
+    def close(self):
+        if self.h:
+            lib().b200reg_batch_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            if self.ctx.h:
+                self.close()
+        except Exception:
+            pass
 
 
 class Cloud64:

@@ -27,6 +27,23 @@ int ensureBuf(b200reg_ctx* ctx, DevBuf& b, size_t bytes) {
   return B200REG_OK;
 }
 
+// pinned 128-byte slots for the index headers (index.cu): handed out from 64-slot chunks that live as long as the ctx
+IndexHeader* acquireHeaderSlot(b200reg_ctx* ctx) {
+  static_assert(sizeof(IndexHeader) <= 128, "header slot size");
+  if (ctx->hdrFree.empty()) {
+    void* chunk = nullptr;
+    if (cudaMallocHost(&chunk, 64 * 128) != cudaSuccess) return nullptr;
+    ctx->hdrChunks.push_back(chunk);
+    for (int i = 63; i >= 0; --i) ctx->hdrFree.push_back((IndexHeader*)((char*)chunk + 128 * i));
+  }
+  IndexHeader* s = ctx->hdrFree.back();
+  ctx->hdrFree.pop_back();
+  return s;
+}
+void releaseHeaderSlot(b200reg_ctx* ctx, IndexHeader* slot) {
+  if (ctx && slot) ctx->hdrFree.push_back(slot);
+}
+
 void profBegin(b200reg_ctx* ctx) {
   if (ctx->profile && ctx->profCount < B200_PROF_MAX) cudaEventRecord(ctx->profEv[2 * ctx->profCount], ctx->stream);
 }
@@ -196,6 +213,7 @@ void b200reg_ctx_destroy(b200reg_ctx* ctx) {
   for (DevBuf* b : bufs)
     if (b->p) devFree(ctx, b->p);
   if (ctx->pinned) cudaFreeHost(ctx->pinned);
+  for (void* c : ctx->hdrChunks) cudaFreeHost(c);
   if (ctx->dstate) devFree(ctx, ctx->dstate);
   cudaStreamSynchronize(ctx->stream);
   cudaEventDestroy(ctx->ev0);
@@ -295,7 +313,7 @@ int32_t b200reg_cloud_update_f32(b200reg_ctx* ctx, b200reg_cloud* c, const float
     const int64_t cap = n > c->cap ? n : c->cap;
     float4 *nx = nullptr, *nn = nullptr;
     cudaError_t e = devAlloc(ctx, &nx, sizeof(float4) * (size_t)cap);
-    if (e == cudaSuccess && (normals || c->nrm)) e = devAlloc(ctx, &nn, sizeof(float4) * (size_t)cap);
+    if (e == cudaSuccess && normals) e = devAlloc(ctx, &nn, sizeof(float4) * (size_t)cap);
     if (e != cudaSuccess) {
       if (nx) devFree(ctx, nx);
       return setErr(ctx, B200REG_E_OOM, "cloud_update_f32: allocation of %lld points failed: %s", (long long)cap, cudaGetErrorString(e));
@@ -305,6 +323,10 @@ int32_t b200reg_cloud_update_f32(b200reg_ctx* ctx, b200reg_cloud* c, const float
     c->xyz = nx; c->nrm = nn; c->cap = cap;
   }
   c->n = n;
+  if (!normals && c->nrm) {   // the new content has no 'normals' descriptor: the previous scan's must not survive (stream-ordered free)
+    CUDA_TRY(ctx, devFree(ctx, c->nrm));
+    c->nrm = nullptr;
+  }
   if (n == 0) return B200REG_OK;
   const size_t fb = sizeof(float) * (size_t)n * feat_stride, nb = normals ? sizeof(float) * 3 * (size_t)n : 0;
   if (feat_stride == 4 && !normals) {

@@ -3,10 +3,12 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <algorithm>
 #include <cstdarg>
 #include <cstddef>
 #include <cstdio>
 #include <cstring>
+#include <vector>
 
 #include <math_constants.h>
 
@@ -20,6 +22,7 @@ struct DevBuf {   // growable device scratch (never shrinks; freed with the ctx)
   size_t cap = 0;
 };
 
+struct IndexHeader;
 struct b200reg_ctx {
   int device = 0;
   cudaStream_t stream = nullptr;
@@ -42,6 +45,9 @@ struct b200reg_ctx {
   void* pinned = nullptr;   // pinned host staging for small D2H results
   size_t pinned_cap = 0;
   void* dstate = nullptr;   // small device state block (select state, counters)
+  // pinned slots the index builds copy their device-derived headers into (index.cu); chunks are freed with the ctx
+  std::vector<void*> hdrChunks;
+  std::vector<IndexHeader*> hdrFree;
 };
 
 // Device memory comes from the device's stream-ordered pool (release threshold raised in b200reg_ctx_create so freed blocks stay
@@ -80,15 +86,36 @@ struct b200reg_cloud64 {
   bool hasNormals = false;
 };
 
+// What the index build derives ON THE DEVICE from the cloud (index.cu gridKernel): the kernels read it from HBM through
+// b200reg_index::dHdr, the host gets an asynchronous copy (hHdr) it waits for only when it needs a value.
+struct IndexHeader {
+  GridDesc g;
+  float mean[3];            // subtracted reference mean (0 if built un-centred)
+  float bbMin[3], bbMax[3]; // bbox of the cloud as given
+  double sum[3];            // fp64 coordinate sums
+  long long m;
+  unsigned numCells;
+  int status;               // 0 ok, 1 non-finite coordinates in the cloud
+};
+
 struct b200reg_index {
   int64_t m = 0;
   float4* pts = nullptr;       // sorted by cell: x y z (centred) + original index bits in .w
   float4* nrm = nullptr;       // sorted normals (nullable)
-  uint32_t* cellStart = nullptr;   // numCells + 1
-  GridDesc g{};
-  float mean[3] = {0, 0, 0};   // subtracted reference mean (0 if built un-centred)
-  double build_ms = 0;
+  uint32_t* dirBase = nullptr; // allocation of the directory: 3 pad words, then cellStart[numCells + 1] (so that the counts, cellStart + 1, are 16-byte aligned)
+  uint32_t* cellStart = nullptr;   // numCells + 1 entries (numCells <= cellCap)
+  uint32_t cellCap = 0;
+  IndexHeader* dHdr = nullptr;     // device
+  IndexHeader* hHdr = nullptr;     // pinned host copy, valid once hdrReady has completed
+  cudaEvent_t hdrReady = nullptr;
+  bool hdrFetched = false;
 };
+// host view of the header (waits once for the build's asynchronous copy); nullptr + ctx error if the build failed on the device
+const IndexHeader* indexHeader(b200reg_ctx* ctx, const b200reg_index* ix);
+// enqueue the build of an index over `ref` on the ctx stream (centre != 0: after subtracting the cloud's mean); no host wait
+int buildIndex(b200reg_ctx* ctx, const b200reg_cloud* ref, int centre, float cell, b200reg_index** out);
+IndexHeader* acquireHeaderSlot(b200reg_ctx* ctx);
+void releaseHeaderSlot(b200reg_ctx* ctx, IndexHeader* slot);
 
 // ---- device-resident registration loop (CUDA-graph while node, icp.cu): everything a kernel of the loop body needs is read
 // from these two blocks in HBM, so ONE instantiated graph serves every reading size, reference and configuration.
@@ -101,12 +128,12 @@ struct CheckerState {   // Counter / Differential / Bound checkers (Transformati
   float q0[4], t0[3];
   int pad;
 };
-enum { ICPERR_NONE = 0, ICPERR_ROT_NAN, ICPERR_TRANS_NAN, ICPERR_BOUND, ICPERR_NO_QUANTILE, ICPERR_NO_POINTS, ICPERR_NOT_RIGID };
+enum { ICPERR_NONE = 0, ICPERR_ROT_NAN, ICPERR_TRANS_NAN, ICPERR_BOUND, ICPERR_NO_QUANTILE, ICPERR_NO_POINTS, ICPERR_NOT_RIGID, ICPERR_ITER_CAP };
 struct IcpDevParams {   // written by the host once per registration
   const float4* pts;
   const float4* nrm;
   const uint32_t* cellStart;
-  GridDesc g;
+  const GridDesc* gp;     // the index header's grid (device-derived, index.cu)
   const float4* reading;
   const float4* readingNrm;
   long long n;
@@ -118,6 +145,7 @@ struct IcpDevParams {   // written by the host once per registration
   int useTrim, useAngle, force2D, force4DOF;
   int maxIter, smoothLength;
   float minDiffRot, minDiffTrans, boundRot, boundTrans;
+  int checkerOrder[3];
   int lanesForced;
   int seedOn;             // 0: chosen per iteration from the far-query count
   // fused trimmed-distance selection (nullable = filter off): the match kernel histograms the top 11 bits of d2 into fhist0
@@ -166,6 +194,8 @@ __device__ __forceinline__ void traceStamp(unsigned long long* trace, unsigned t
 }
 #endif
 int setErr(b200reg_ctx* ctx, int code, const char* fmt, ...);
+// mean sums and bbox of a cloud on the HOST (one synchronisation; voxelgrid.cu — the index build derives its own on the device)
+int cloudStats(b200reg_ctx* ctx, const b200reg_cloud* c, double sum[3], float mn[3], float mx[3]);
 int ensureBuf(b200reg_ctx* ctx, DevBuf& b, size_t bytes);
 int ensurePinned(b200reg_ctx* ctx, size_t bytes);
 // event bracket around the match kernel while profiling is on (no-ops otherwise)

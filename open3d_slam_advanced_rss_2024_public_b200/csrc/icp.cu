@@ -9,9 +9,6 @@
 int launchKnn1Loop(b200reg_ctx* ctx, const IcpDevParams* P, const IcpDevState* S, unsigned long long* counters, int blocks);
 int runKnn(b200reg_ctx* ctx, const b200reg_index* ix, const float4* queries, int64_t n, const float* T, int k, float maxDist, int allowSelf,
            int seeded);
-int cloudStats(b200reg_ctx* ctx, const b200reg_cloud* c, double sum[3], float mn[3], float mx[3]);
-int buildIndex(b200reg_ctx* ctx, const b200reg_cloud* ref, const float mean[3], const float bbMin[3], const float bbMax[3], float cell,
-               b200reg_index** out);
 
 namespace {
 
@@ -339,9 +336,12 @@ __host__ __device__ float quatDist(const float a[4], const float b[4]) {   // Qu
 // Counter / Differential / Bound checkers (TransformationCheckersImpl.cpp:58-225) on a POD state, shared by the host-driven
 // loop and the device-resident one (icpTailKernel).
 struct CheckerCfg {
-  int maxIter, smoothLength;
-  float minDiffRot, minDiffTrans, boundRot, boundTrans;
+  int maxIter, smoothLength;   // maxIter < 0: no Counter; smoothLength < 0: no Differential
+  float minDiffRot, minDiffTrans, boundRot, boundTrans;   // boundRot < 0: no Bound
+  int order[3];                // evaluation order (B200REG_CHECKER_*; 0 ends the list); all 0 = Differential, Bound, Counter
 };
+// no configuration may spin the device forever (a chain without checkers loops forever in the reference, ICP.cpp:399)
+#define ICP_HARD_ITERATION_CAP 10000
 __host__ __device__ void checkersPush(CheckerState& c, const float* T) {
   const int slot = c.count % CHK_HIST;
   quatOf(T, c.rot[slot]);
@@ -355,39 +355,44 @@ __host__ __device__ void checkersInit(CheckerState& c, const float* T) {
   quatOf(T, c.q0);
   c.t0[0] = T[3]; c.t0[1] = T[7]; c.t0[2] = T[11];
 }
-// returns ICPERR_*; may clear `iterate` / set `maxIter`; err[] = the values the reference puts in its message
+// returns ICPERR_*; may clear `iterate` / set `maxIter`; err[] = the values the reference puts in its message.  The checkers run
+// in the chain's order (ICP.cpp:437-446): Counter's MaxNumIterationsReached is a throw, so the checkers listed after it are
+// skipped on the iteration it fires (TransformationCheckersImpl.cpp:66-77).
 __host__ __device__ int checkersCheck(const CheckerCfg& cfg, CheckerState& c, const float* T, bool& iterate, bool& maxIter, float err[4]) {
-  if (cfg.smoothLength >= 0) {
-    checkersPush(c, T);
-    const int sl = cfg.smoothLength, cnt = c.count;
-    float cv0 = 0.f, cv1 = 0.f;
-    if (cnt > sl) {
-      for (int i = cnt - 1; sl > 0 && i >= cnt - sl; --i) {
-        const int a = i % CHK_HIST, b = (i - 1) % CHK_HIST;
-        cv0 += fabsf(quatDist(c.rot[a], c.rot[b]));
-        const float dx = c.tr[a][0] - c.tr[b][0], dy = c.tr[a][1] - c.tr[b][1], dz = c.tr[a][2] - c.tr[b][2];
-        cv1 += fabsf(sqrtf(dx * dx + dy * dy + dz * dz));
+  const bool legacy = cfg.order[0] == 0;
+  for (int slot = 0; slot < 3; ++slot) {
+    const int kind = legacy ? (slot == 0 ? B200REG_CHECKER_DIFFERENTIAL : slot == 1 ? B200REG_CHECKER_BOUND : B200REG_CHECKER_COUNTER) : cfg.order[slot];
+    if (kind == 0) break;
+    if (kind == B200REG_CHECKER_DIFFERENTIAL && cfg.smoothLength >= 0) {
+      checkersPush(c, T);
+      const int sl = cfg.smoothLength, cnt = c.count;
+      float cv0 = 0.f, cv1 = 0.f;
+      if (cnt > sl) {
+        for (int i = cnt - 1; sl > 0 && i >= cnt - sl; --i) {
+          const int a = i % CHK_HIST, b = (i - 1) % CHK_HIST;
+          cv0 += fabsf(quatDist(c.rot[a], c.rot[b]));
+          const float dx = c.tr[a][0] - c.tr[b][0], dy = c.tr[a][1] - c.tr[b][1], dz = c.tr[a][2] - c.tr[b][2];
+          cv1 += fabsf(sqrtf(dx * dx + dy * dy + dz * dz));
+        }
+        cv0 /= (float)sl; cv1 /= (float)sl;
+        if (cv0 < cfg.minDiffRot && cv1 < cfg.minDiffTrans) iterate = false;
       }
-      cv0 /= (float)sl; cv1 /= (float)sl;
-      if (cv0 < cfg.minDiffRot && cv1 < cfg.minDiffTrans) iterate = false;
+      if (cv0 != cv0) return ICPERR_ROT_NAN;
+      if (cv1 != cv1) return ICPERR_TRANS_NAN;
+    } else if (kind == B200REG_CHECKER_BOUND && cfg.boundRot >= 0.f) {
+      float q[4];
+      quatOf(T, q);
+      const float r = quatDist(q, c.q0);
+      const float dx = T[3] - c.t0[0], dy = T[7] - c.t0[1], dz = T[11] - c.t0[2];
+      const float t = sqrtf(dx * dx + dy * dy + dz * dz);
+      if (r > cfg.boundRot || t > cfg.boundTrans) {
+        err[0] = r; err[1] = cfg.boundRot; err[2] = t; err[3] = cfg.boundTrans;
+        return ICPERR_BOUND;
+      }
+    } else if (kind == B200REG_CHECKER_COUNTER && cfg.maxIter >= 0) {
+      ++c.counter;   // maxIterationCount 0 stops after the first iteration, like 1 (counter >= limit, :70)
+      if (c.counter >= cfg.maxIter) { iterate = false; maxIter = true; return ICPERR_NONE; }   // MaxNumIterationsReached, caught at ICP.cpp:441-445
     }
-    if (cv0 != cv0) return ICPERR_ROT_NAN;
-    if (cv1 != cv1) return ICPERR_TRANS_NAN;
-  }
-  if (cfg.boundRot >= 0.f) {
-    float q[4];
-    quatOf(T, q);
-    const float r = quatDist(q, c.q0);
-    const float dx = T[3] - c.t0[0], dy = T[7] - c.t0[1], dz = T[11] - c.t0[2];
-    const float t = sqrtf(dx * dx + dy * dy + dz * dz);
-    if (r > cfg.boundRot || t > cfg.boundTrans) {
-      err[0] = r; err[1] = cfg.boundRot; err[2] = t; err[3] = cfg.boundTrans;
-      return ICPERR_BOUND;
-    }
-  }
-  if (cfg.maxIter > 0) {
-    ++c.counter;
-    if (c.counter >= cfg.maxIter) { iterate = false; maxIter = true; }   // MaxNumIterationsReached, caught at ICP.cpp:441-445
   }
   return ICPERR_NONE;
 }
@@ -401,6 +406,7 @@ int icpErrToStatus(b200reg_ctx* ctx, int kind, const float err[4]) {
     case ICPERR_NO_QUANTILE: return setErr(ctx, B200REG_E_NOT_CONVERGED, "No matches available for computing distance quantiles");
     case ICPERR_NO_POINTS: return setErr(ctx, B200REG_E_NOT_CONVERGED, "ErrorMnimizer: no point to minimize");
     case ICPERR_NOT_RIGID: return setErr(ctx, B200REG_E_TRANSFORM, "RigidTransformation: Error, rotation matrix is not orthogonal.");
+    case ICPERR_ITER_CAP: return setErr(ctx, B200REG_E_NOT_CONVERGED, "ICP: no transformation checker stopped the loop within %d iterations", ICP_HARD_ITERATION_CAP);
   }
   return setErr(ctx, B200REG_E_CUDA, "ICP: unknown device error %d", kind);
 }
@@ -416,7 +422,6 @@ struct b200reg_icp {
   b200reg_ctx* ctx = nullptr;
   b200reg_icp_config cfg{};
   b200reg_index* index = nullptr;   // over the centred, (un)filtered reference — `referenceFiltered` + the matcher
-  float mean[3] = {0, 0, 0};        // T_refIn_refMean translation
   double refPrepS = 0;
   DevBuf reading, readingNrm;       // `reading` of ICP.cpp:352-375 (in the refMean frame)
   // device-resident iterate loop (k = 1): a CUDA graph whose body is a `while` conditional node
@@ -427,6 +432,12 @@ struct b200reg_icp {
   cudaGraphExec_t exec = nullptr;
   int graphState = 0;               // 0 not built yet, 1 ready, -1 unavailable (host-driven loop is used)
   int graphNodes = 0;               // kernels per iteration of the body
+  // a registration enqueued on the ctx stream and not yet collected (icpEnqueue / icpFinish): the batch lanes keep one in flight each
+  bool pending = false;
+  float pendTinit[16];
+  int64_t pendN = 0;
+  double pendT1 = 0;
+  b200reg_icp_stats pendStats{};
 };
 
 extern "C" {
@@ -543,13 +554,23 @@ int32_t b200reg_icp_step(b200reg_ctx* ctx, const b200reg_index* index, const b20
 // =================================================================================================================
 namespace {
 
-__global__ void prepReadingKernel(const float4* __restrict__ xyz, const float4* __restrict__ nrm, int64_t n, Rigid12 T, float t30, float t31,
-                                  float t32, float t33, float4* __restrict__ oxyz, float4* __restrict__ onrm) {
+// reading <- T_refMean_readMean * reading with T_refMean_readMean = T_refIn_refMean^-1 * T_init (ICP.cpp:363-375; meanReading is
+// forced to 0 in this fork).  The reference mean is read from the index header the build left in HBM, so the host never waits
+// for it; every thread forms the 4x4 product with the host's own mul4 (same rounded operations, this file is --fmad=false).
+struct Mat16 { float m[16]; };
+__global__ void prepReadingKernel(const float4* __restrict__ xyz, const float4* __restrict__ nrm, int64_t n, Mat16 Tinit,
+                                  const IndexHeader* __restrict__ hdr, float4* __restrict__ oxyz, float4* __restrict__ onrm) {
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
+  const float TrefInv[16] = {1, 0, 0, -hdr->mean[0], 0, 1, 0, -hdr->mean[1], 0, 0, 1, -hdr->mean[2], 0, 0, 0, 1};
+  float Tpre[16];
+  mul4(TrefInv, Tinit.m, Tpre);
+  Rigid12 T;
+#pragma unroll
+  for (int j = 0; j < 12; ++j) T.m[j] = Tpre[j];
   const float4 p = xyz[i];
   const float3 r = xformPoint(T, p.x, p.y, p.z, p.w);
-  const float w = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(t30, p.x), __fmul_rn(t31, p.y)), __fmul_rn(t32, p.z)), __fmul_rn(t33, p.w));
+  const float w = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(Tpre[12], p.x), __fmul_rn(Tpre[13], p.y)), __fmul_rn(Tpre[14], p.z)), __fmul_rn(Tpre[15], p.w));
   oxyz[i] = make_float4(r.x, r.y, r.z, w);
   if (nrm) {
     const float4 q = nrm[i];
@@ -598,9 +619,12 @@ __global__ void __launch_bounds__(32) icpTailKernel(const IcpDevParams* __restri
     mul4(Tstep, Told, Tnew);   // T_iter = T_step * T_iter (ICP.cpp:433)
 #pragma unroll
     for (int i = 0; i < 16; ++i) S->T[i] = Tnew[i];
-    const CheckerCfg ccfg{p.maxIter, p.smoothLength, p.minDiffRot, p.minDiffTrans, p.boundRot, p.boundTrans};
+    const CheckerCfg ccfg{p.maxIter, p.smoothLength, p.minDiffRot, p.minDiffTrans, p.boundRot, p.boundTrans,
+                          {p.checkerOrder[0], p.checkerOrder[1], p.checkerOrder[2]}};
     err = checkersCheck(ccfg, S->chk, Tnew, iterate, maxIter, errv);
-    S->iterations = S->iterations + 1;
+    const int its = S->iterations + 1;
+    S->iterations = its;
+    if (err == ICPERR_NONE && iterate && its >= ICP_HARD_ITERATION_CAP) err = ICPERR_ITER_CAP;
     if (err == ICPERR_NONE && iterate && !rigidOk(Tnew)) err = ICPERR_NOT_RIGID;   // the next iteration's RigidTransformation check
   }
   if (err != ICPERR_NONE) iterate = false;
@@ -727,21 +751,18 @@ void b200reg_icp_destroy(b200reg_icp* icp) {
   delete icp;
 }
 
-// ICP::initReference (ICP.cpp:293-328): mean of the reference, centring, matcher->init.
+// ICP::initReference (ICP.cpp:293-328): mean of the reference, centring, matcher->init.  Enqueue only: mean, bbox and grid are
+// derived on the device (index.cu), the host never waits.  A reference with non-finite coordinates is reported by the first call
+// that needs the result (b200reg_icp_register, b200reg_icp_reference_mean, b200reg_icp_index).
 int32_t b200reg_icp_set_reference(b200reg_icp* icp, const b200reg_cloud* reference) {
   if (!icp || !reference) return B200REG_E_INVALID_PARAM;
   b200reg_ctx* ctx = icp->ctx;
   const double t0 = nowSec();
+  if (icp->pending) return setErr(ctx, B200REG_E_INVALID_PARAM, "icp_set_reference: a registration is still in flight on this object");
   if (icp->index) { b200reg_index_free(ctx, icp->index); icp->index = nullptr; }   // matcherIsInitialized = false
   if (reference->n == 0) return setErr(ctx, B200REG_E_NO_POINTS, "initReference: reference cloud is empty");   // :295-298
   CUDA_TRY(ctx, cudaSetDevice(ctx->device));
-  double sum[3];
-  float mn[3], mx[3];
-  TRY(cloudStats(ctx, reference, sum, mn, mx));
-  // meanReference = features.rowwise().mean() (:313): fp64 sum rounded once to fp32 (contract)
-  for (int d = 0; d < 3; ++d) icp->mean[d] = (float)(sum[d] / (double)reference->n);
-  TRY(buildIndex(ctx, reference, icp->mean, mn, mx, icp->cfg.cell, &icp->index));
-  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  TRY(buildIndex(ctx, reference, 1, icp->cfg.cell, &icp->index));
   icp->refPrepS = nowSec() - t0;
   return B200REG_OK;
 }
@@ -750,18 +771,200 @@ const b200reg_index* b200reg_icp_index(const b200reg_icp* icp) { return icp ? ic
 
 int32_t b200reg_icp_reference_mean(const b200reg_icp* icp, float mean_out[3]) {
   if (!icp || !mean_out) return B200REG_E_INVALID_PARAM;
-  for (int d = 0; d < 3; ++d) mean_out[d] = icp->mean[d];
+  for (int d = 0; d < 3; ++d) mean_out[d] = 0.f;
+  if (!icp->index) return B200REG_OK;
+  const IndexHeader* h = indexHeader(icp->ctx, icp->index);
+  if (!h) return B200REG_E_INVALID_PARAM;
+  for (int d = 0; d < 3; ++d) mean_out[d] = h->mean[d];
   return B200REG_OK;
 }
+
+}  // extern "C"
+
+namespace {
+
+// T_refMean_readMean = T_refIn_refMean^-1 * T_init (meanReading forced to 0 in this fork, ICP.cpp:363-373), on the host
+void preTransform(const float mean[3], const float T_init[16], float Tpre[16]) {
+  const float TrefInv[16] = {1, 0, 0, -mean[0], 0, 1, 0, -mean[1], 0, 0, 1, -mean[2], 0, 0, 0, 1};
+  mul4(TrefInv, T_init, Tpre);
+}
+
+// RigidTransformation::checkParameters on T_refMean_readMean (ICP.cpp:375).  With a last row of (0 0 0 1) its rotation block is
+// T_init's, entry for entry, so the usual case needs no reference mean — and therefore no wait for the index build.
+int checkPreTransform(b200reg_icp* icp, const float T_init[16]) {
+  b200reg_ctx* ctx = icp->ctx;
+  bool ok;
+  if (T_init[12] == 0.f && T_init[13] == 0.f && T_init[14] == 0.f && T_init[15] == 1.f) ok = rigidOk(T_init);
+  else {
+    const IndexHeader* h = indexHeader(ctx, icp->index);
+    if (!h) return B200REG_E_INVALID_PARAM;
+    float Tpre[16];
+    preTransform(h->mean, T_init, Tpre);
+    ok = rigidOk(Tpre);
+  }
+  return ok ? B200REG_OK : setErr(ctx, B200REG_E_TRANSFORM, "RigidTransformation: Error, rotation matrix is not orthogonal.");
+}
+
+int enqueuePrepReading(b200reg_icp* icp, const b200reg_cloud* reading, const float T_init[16], bool needNrm) {
+  b200reg_ctx* ctx = icp->ctx;
+  const int64_t n = reading->n;
+  TRY(ensureBuf(ctx, icp->reading, sizeof(float4) * (size_t)n));
+  if (needNrm) TRY(ensureBuf(ctx, icp->readingNrm, sizeof(float4) * (size_t)n));
+  Mat16 Ti;
+  memcpy(Ti.m, T_init, sizeof(Ti.m));
+  prepReadingKernel<<<divUp(n, 256), 256, 0, ctx->stream>>>(reading->xyz, needNrm ? reading->nrm : nullptr, n, Ti, icp->index->dHdr,
+                                                            (float4*)icp->reading.p, (float4*)icp->readingNrm.p);
+  LAUNCH_CHECK(ctx);
+  return B200REG_OK;
+}
+
+// icpCorrected_T_refIn_readIn = T_refIn_refMean * (T_iter * T_refMean_readMean) * I   (ICP.cpp:459-465)
+int composeResult(b200reg_icp* icp, const float T_iter[16], const float T_init[16], float T_out[16]) {
+  const IndexHeader* h = indexHeader(icp->ctx, icp->index);
+  if (!h) return B200REG_E_INVALID_PARAM;
+  float Tpre[16], tmp[16];
+  preTransform(h->mean, T_init, Tpre);
+  const float Tref[16] = {1, 0, 0, h->mean[0], 0, 1, 0, h->mean[1], 0, 0, 1, h->mean[2], 0, 0, 0, 1};
+  mul4(T_iter, Tpre, tmp);
+  mul4(Tref, tmp, T_out);
+  return B200REG_OK;
+}
+
+inline bool wantGraphLoop(const b200reg_icp* icp) { return icp->cfg.knn == 1 && !icp->ctx->profile && !icp->ctx->hostLoop; }
+
+// First half of a registration through the device-resident loop: everything up to the read-back of the final state is enqueued
+// on the ctx stream; nothing waits.  The host image of the loop block and the result slot live in the ctx's pinned staging, so
+// ONE registration per ctx can be in flight (the batch lanes own a ctx each).
+int icpEnqueue(b200reg_icp* icp, const b200reg_cloud* reading, const float T_init[16]) {
+  b200reg_ctx* ctx = icp->ctx;
+  const b200reg_icp_config& cfg = icp->cfg;
+  b200reg_icp_stats& st = icp->pendStats;
+  memset(&st, 0, sizeof(st));
+  if (icp->pending) return setErr(ctx, B200REG_E_INVALID_PARAM, "icp_register: a registration is still in flight on this object");
+  if (!icp->index) return setErr(ctx, B200REG_E_NO_POINTS, "ICP: matcher not initialised (empty reference)");
+  if (!icp->index->nrm) return setErr(ctx, B200REG_E_INVALID_FIELD, "PointToPlaneErrorMinimizer: reference cloud has no 'normals' descriptor");
+  const int64_t n = reading->n;
+  st.reference_point_count = icp->index->m;
+  st.reading_point_count = n;
+  st.reference_preprocessing_s = icp->refPrepS;
+  if (n == 0) return setErr(ctx, B200REG_E_NO_POINTS, "The reading point cloud is empty.");   // ICP.cpp:357-359
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  const double t0 = nowSec();
+  TRY(checkPreTransform(icp, T_init));
+  const bool needNrm = reading->nrm && cfg.max_angle >= 0.f;
+  TRY(enqueuePrepReading(icp, reading, T_init, needNrm));
+  st.reading_preprocessing_s = nowSec() - t0;
+  icp->pendT1 = nowSec();
+  const float T_iter[16] = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1};
+  TRY(ensureBuf(ctx, ctx->matchIds, sizeof(int) * (size_t)n));
+  TRY(ensureBuf(ctx, ctx->matchD2, sizeof(float) * (size_t)n));
+  TRY(ensureBuf(ctx, ctx->matchPos, sizeof(int) * (size_t)n));
+  char* pin = (char*)ctx->pinned;
+  char* hBlock = pin + 8192;   // host image of the loop block
+  IcpDevParams* hP = (IcpDevParams*)(hBlock + LOOP_PARAMS_OFF);
+  IcpDevState* hS = (IcpDevState*)(hBlock + LOOP_STATE_OFF);
+  IcpDevState* hR = (IcpDevState*)(pin + 16384);
+  memset(hBlock, 0, LOOP_PARAMS_OFF);   // visit / far counters
+  memset(hP, 0, sizeof(*hP));
+  hP->pts = icp->index->pts; hP->nrm = icp->index->nrm; hP->cellStart = icp->index->cellStart; hP->gp = &icp->index->dHdr->g;
+  hP->reading = (const float4*)icp->reading.p;
+  hP->readingNrm = needNrm ? (const float4*)icp->readingNrm.p : nullptr;
+  hP->n = n;
+  hP->ids = (int*)ctx->matchIds.p; hP->d2 = (float*)ctx->matchD2.p; hP->pos = (int*)ctx->matchPos.p;
+  hP->partials = (double*)ctx->partials.p;
+  hP->maxd2 = cfg.max_dist * cfg.max_dist;
+  hP->trimRatio = cfg.trim_ratio;
+  hP->cosAngle = cosf(cfg.max_angle);
+  hP->useTrim = cfg.trim_ratio > 0.f ? 1 : 0;
+  hP->useAngle = cfg.max_angle >= 0.f ? 1 : 0;
+  hP->force2D = cfg.force2D; hP->force4DOF = cfg.force4DOF;
+  hP->maxIter = cfg.max_iter; hP->smoothLength = cfg.smooth_length;
+  hP->minDiffRot = cfg.min_diff_rot; hP->minDiffTrans = cfg.min_diff_trans;
+  hP->boundRot = cfg.bound_rot; hP->boundTrans = cfg.bound_trans;
+  for (int j = 0; j < 3; ++j) hP->checkerOrder[j] = cfg.checker_order[j];
+  if (cfg.trim_ratio > 0.f && !ctx->select3) {
+    TRY(ensureBuf(ctx, ctx->cand, sizeof(unsigned) * (size_t)n));
+    hP->fhist0 = (unsigned*)((char*)ctx->dstate + DSTATE_FH0_OFF);
+    hP->fhist1 = (unsigned*)((char*)ctx->dstate + DSTATE_FH1_OFF);
+    hP->fcnt = (unsigned*)((char*)ctx->dstate + DSTATE_FCNT_OFF);
+    hP->cand = (unsigned*)ctx->cand.p;
+  }
+  hP->lanesForced = (ctx->knnLanes == 4 || ctx->knnLanes == 8) ? ctx->knnLanes : 0;
+  hP->seedOn = ctx->knnSeed;
+  hP->trace = ctx->trace ? (unsigned long long*)((char*)ctx->dstate + DSTATE_TRACE_OFF) : nullptr;
+  if (ctx->trace) CUDA_TRY(ctx, cudaMemsetAsync((char*)ctx->dstate + DSTATE_TRACE_OFF, 0, sizeof(unsigned long long), ctx->stream));
+  memset(hS, 0, sizeof(*hS));
+  memcpy(hS->T, T_iter, sizeof(T_iter));
+  hS->iterate = 1;
+  hS->lanes = (ctx->knnLanes == 4) ? 4 : 8;
+  checkersInit(hS->chk, T_iter);
+  // counters + parameters + the part of the state the loop reads before writing it (head, checker counters, first ring slot)
+  CUDA_TRY(ctx, cudaMemcpyAsync(icp->dBlock, hBlock, LOOP_STATE_OFF + sizeof(IcpDevState), cudaMemcpyHostToDevice, ctx->stream));
+  CUDA_TRY(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
+  CUDA_TRY(ctx, cudaGraphLaunch(icp->exec, ctx->stream));
+  CUDA_TRY(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
+  CUDA_TRY(ctx, cudaMemcpyAsync(hR, icp->dS, ICP_STATE_HEAD_BYTES, cudaMemcpyDeviceToHost, ctx->stream));
+  memcpy(icp->pendTinit, T_init, sizeof(icp->pendTinit));
+  icp->pendN = n;
+  icp->pending = true;
+  return B200REG_OK;
+}
+
+// Second half: wait for the stream, read the 144-byte head of the final state, compose the result.
+int icpFinish(b200reg_icp* icp, float T_out[16], b200reg_icp_stats* stats) {
+  b200reg_ctx* ctx = icp->ctx;
+  b200reg_icp_stats& st = icp->pendStats;
+  auto done = [&](int code) { if (stats) *stats = st; return code; };
+  if (!icp->pending) return done(setErr(ctx, B200REG_E_INVALID_PARAM, "icp_register: nothing in flight"));
+  icp->pending = false;
+  const cudaError_t e = cudaStreamSynchronize(ctx->stream);
+  if (e != cudaSuccess) return done(setErr(ctx, B200REG_E_CUDA, "ICP loop failed: %s", cudaGetErrorString(e)));
+  const IcpDevState* hR = (const IcpDevState*)((char*)ctx->pinned + 16384);
+  const double total = (double)icp->pendN * icp->cfg.knn;
+  float gms = 0;
+  cudaEventElapsedTime(&gms, ctx->ev0, ctx->ev1);
+  st.device_ms = gms;
+  st.iterations = hR->iterations;
+  st.max_iterations_reached = hR->maxIterReached;
+  st.points_touched = hR->visits;
+  st.kept_last = (int64_t)hR->kept;
+  st.point_used_ratio = (float)hR->kept / (float)total;
+  st.overlap_ratio = st.point_used_ratio;
+  st.last_tau = hR->tau;
+  st.convergence_s = nowSec() - icp->pendT1;
+  // kernels of the graph: (iterations that ran the full body) x nodes; an iteration that failed early still ran them all
+  ctx->launches += (uint64_t)icp->graphNodes * (uint64_t)(hR->iterations + ((hR->errKind == ICPERR_NO_QUANTILE || hR->errKind == ICPERR_NO_POINTS) ? 1 : 0));
+  if (!indexHeader(ctx, icp->index)) return done(B200REG_E_INVALID_PARAM);   // non-finite reference: the loop ran on a dummy grid
+  const float errv[4] = {hR->errA, hR->errB, hR->errC, hR->errD};
+  const int gstatus = icpErrToStatus(ctx, hR->errKind, errv);
+  if (gstatus != B200REG_OK) return done(gstatus);
+  return done(composeResult(icp, hR->T, icp->pendTinit, T_out));
+}
+
+}  // namespace
+
+extern "C" {
 
 int32_t b200reg_icp_register(b200reg_icp* icp, const b200reg_cloud* reading, const float T_init[16], float T_out[16],
                              b200reg_icp_stats* stats) {
   if (!icp || !reading || !T_init || !T_out) return B200REG_E_INVALID_PARAM;
   b200reg_ctx* ctx = icp->ctx;
   const b200reg_icp_config& cfg = icp->cfg;
+  // ---- device-resident loop: the whole iterate loop is ONE graph launch; the host comes back for the final state only
+  if (wantGraphLoop(icp) && icp->graphState == 0) {
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    icp->graphState = (buildLoopGraph(icp) == 0) ? 1 : -1;
+  }
+  if (wantGraphLoop(icp) && icp->graphState == 1) {
+    const int code = icpEnqueue(icp, reading, T_init);
+    if (code != B200REG_OK) { if (stats) *stats = icp->pendStats; return code; }
+    return icpFinish(icp, T_out, stats);
+  }
+  // ---- host-driven loop (k > 1 chains, profiling, A/B): one synchronisation per iteration
   b200reg_icp_stats st;
   memset(&st, 0, sizeof(st));
   auto done = [&](int code) { if (stats) *stats = st; return code; };
+  if (icp->pending) return done(setErr(ctx, B200REG_E_INVALID_PARAM, "icp_register: a registration is still in flight on this object"));
   if (!icp->index) return done(setErr(ctx, B200REG_E_NO_POINTS, "ICP: matcher not initialised (empty reference)"));
   if (!icp->index->nrm) return done(setErr(ctx, B200REG_E_INVALID_FIELD, "PointToPlaneErrorMinimizer: reference cloud has no 'normals' descriptor"));
   const int64_t n = reading->n;
@@ -771,100 +974,18 @@ int32_t b200reg_icp_register(b200reg_icp* icp, const b200reg_cloud* reading, con
   if (n == 0) return done(setErr(ctx, B200REG_E_NO_POINTS, "The reading point cloud is empty."));   // ICP.cpp:357-359
   CUDA_TRY(ctx, cudaSetDevice(ctx->device));
   const double t0 = nowSec();
-  // T_refMean_readMean = T_refIn_refMean^-1 * T_init (meanReading forced to 0 in this fork, ICP.cpp:363-373)
-  float TrefInv[16] = {1, 0, 0, -icp->mean[0], 0, 1, 0, -icp->mean[1], 0, 0, 1, -icp->mean[2], 0, 0, 0, 1};
-  float Tpre[16];
-  mul4(TrefInv, T_init, Tpre);
-  if (!rigidOk(Tpre)) return done(setErr(ctx, B200REG_E_TRANSFORM, "RigidTransformation: Error, rotation matrix is not orthogonal."));
+  if (!indexHeader(ctx, icp->index)) return done(B200REG_E_INVALID_PARAM);
+  { const int c = checkPreTransform(icp, T_init); if (c != B200REG_OK) return done(c); }
   const bool needNrm = reading->nrm && cfg.max_angle >= 0.f;
-  TRY(ensureBuf(ctx, icp->reading, sizeof(float4) * (size_t)n));
-  if (needNrm) TRY(ensureBuf(ctx, icp->readingNrm, sizeof(float4) * (size_t)n));
-  Rigid12 Rp;
-  memcpy(Rp.m, Tpre, sizeof(Rp.m));
-  prepReadingKernel<<<divUp(n, 256), 256, 0, ctx->stream>>>(reading->xyz, needNrm ? reading->nrm : nullptr, n, Rp, Tpre[12], Tpre[13], Tpre[14],
-                                                            Tpre[15], (float4*)icp->reading.p, (float4*)icp->readingNrm.p);
-  LAUNCH_CHECK(ctx);
+  { const int c = enqueuePrepReading(icp, reading, T_init, needNrm); if (c != B200REG_OK) return done(c); }
   st.reading_preprocessing_s = nowSec() - t0;
 
   const double t1 = nowSec();
   float T_iter[16] = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1};
   bool iterate = true, maxIter = false;
   const double total = (double)n * cfg.knn;
-  // ---- device-resident loop: the whole iterate loop is ONE graph launch; the host comes back for the final state only
-  const bool wantGraph = cfg.knn == 1 && !ctx->profile && !ctx->hostLoop;
-  if (wantGraph && icp->graphState == 0) icp->graphState = (buildLoopGraph(icp) == 0) ? 1 : -1;
-  if (wantGraph && icp->graphState == 1) {
-    TRY(ensureBuf(ctx, ctx->matchIds, sizeof(int) * (size_t)n));
-    TRY(ensureBuf(ctx, ctx->matchD2, sizeof(float) * (size_t)n));
-    TRY(ensureBuf(ctx, ctx->matchPos, sizeof(int) * (size_t)n));
-    char* pin = (char*)ctx->pinned;
-    char* hBlock = pin + 8192;   // host image of the loop block
-    IcpDevParams* hP = (IcpDevParams*)(hBlock + LOOP_PARAMS_OFF);
-    IcpDevState* hS = (IcpDevState*)(hBlock + LOOP_STATE_OFF);
-    IcpDevState* hR = (IcpDevState*)(pin + 16384);
-    memset(hBlock, 0, LOOP_PARAMS_OFF);   // visit / far counters
-    memset(hP, 0, sizeof(*hP));
-    hP->pts = icp->index->pts; hP->nrm = icp->index->nrm; hP->cellStart = icp->index->cellStart; hP->g = icp->index->g;
-    hP->reading = (const float4*)icp->reading.p;
-    hP->readingNrm = needNrm ? (const float4*)icp->readingNrm.p : nullptr;
-    hP->n = n;
-    hP->ids = (int*)ctx->matchIds.p; hP->d2 = (float*)ctx->matchD2.p; hP->pos = (int*)ctx->matchPos.p;
-    hP->partials = (double*)ctx->partials.p;
-    hP->maxd2 = cfg.max_dist * cfg.max_dist;
-    hP->trimRatio = cfg.trim_ratio;
-    hP->cosAngle = cosf(cfg.max_angle);
-    hP->useTrim = cfg.trim_ratio > 0.f ? 1 : 0;
-    hP->useAngle = cfg.max_angle >= 0.f ? 1 : 0;
-    hP->force2D = cfg.force2D; hP->force4DOF = cfg.force4DOF;
-    hP->maxIter = cfg.max_iter; hP->smoothLength = cfg.smooth_length;
-    hP->minDiffRot = cfg.min_diff_rot; hP->minDiffTrans = cfg.min_diff_trans;
-    hP->boundRot = cfg.bound_rot; hP->boundTrans = cfg.bound_trans;
-    if (cfg.trim_ratio > 0.f && !ctx->select3) {
-      TRY(ensureBuf(ctx, ctx->cand, sizeof(unsigned) * (size_t)n));
-      hP->fhist0 = (unsigned*)((char*)ctx->dstate + DSTATE_FH0_OFF);
-      hP->fhist1 = (unsigned*)((char*)ctx->dstate + DSTATE_FH1_OFF);
-      hP->fcnt = (unsigned*)((char*)ctx->dstate + DSTATE_FCNT_OFF);
-      hP->cand = (unsigned*)ctx->cand.p;
-    }
-    hP->lanesForced = (ctx->knnLanes == 4 || ctx->knnLanes == 8) ? ctx->knnLanes : 0;
-    hP->seedOn = ctx->knnSeed;
-    hP->trace = ctx->trace ? (unsigned long long*)((char*)ctx->dstate + DSTATE_TRACE_OFF) : nullptr;
-    if (ctx->trace) CUDA_TRY(ctx, cudaMemsetAsync((char*)ctx->dstate + DSTATE_TRACE_OFF, 0, sizeof(unsigned long long), ctx->stream));
-    memset(hS, 0, sizeof(*hS));
-    memcpy(hS->T, T_iter, sizeof(T_iter));
-    hS->iterate = 1;
-    hS->lanes = (ctx->knnLanes == 4) ? 4 : 8;
-    checkersInit(hS->chk, T_iter);
-    // counters + parameters + the part of the state the loop reads before writing it (head, checker counters, first ring slot)
-    CUDA_TRY(ctx, cudaMemcpyAsync(icp->dBlock, hBlock, LOOP_STATE_OFF + sizeof(IcpDevState), cudaMemcpyHostToDevice, ctx->stream));
-    CUDA_TRY(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
-    CUDA_TRY(ctx, cudaGraphLaunch(icp->exec, ctx->stream));
-    CUDA_TRY(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
-    CUDA_TRY(ctx, cudaMemcpyAsync(hR, icp->dS, ICP_STATE_HEAD_BYTES, cudaMemcpyDeviceToHost, ctx->stream));
-    CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
-    float gms = 0;
-    cudaEventElapsedTime(&gms, ctx->ev0, ctx->ev1);
-    st.device_ms = gms;
-    st.iterations = hR->iterations;
-    st.max_iterations_reached = hR->maxIterReached;
-    st.points_touched = hR->visits;
-    st.kept_last = (int64_t)hR->kept;
-    st.point_used_ratio = (float)hR->kept / (float)total;
-    st.overlap_ratio = st.point_used_ratio;
-    st.last_tau = hR->tau;
-    st.convergence_s = nowSec() - t1;
-    // kernels of the graph: (iterations that ran the full body) x nodes; an iteration that failed early still ran them all
-    ctx->launches += (uint64_t)icp->graphNodes * (uint64_t)(hR->iterations + ((hR->errKind == ICPERR_NO_QUANTILE || hR->errKind == ICPERR_NO_POINTS) ? 1 : 0));
-    const float errv[4] = {hR->errA, hR->errB, hR->errC, hR->errD};
-    const int gstatus = icpErrToStatus(ctx, hR->errKind, errv);
-    if (gstatus != B200REG_OK) return done(gstatus);
-    float Tref[16] = {1, 0, 0, icp->mean[0], 0, 1, 0, icp->mean[1], 0, 0, 1, icp->mean[2], 0, 0, 0, 1};
-    float tmp[16];
-    mul4(hR->T, Tpre, tmp);
-    mul4(Tref, tmp, T_out);
-    return done(B200REG_OK);
-  }
-  const CheckerCfg ccfg{cfg.max_iter, cfg.smooth_length, cfg.min_diff_rot, cfg.min_diff_trans, cfg.bound_rot, cfg.bound_trans};
+  const CheckerCfg ccfg{cfg.max_iter, cfg.smooth_length, cfg.min_diff_rot, cfg.min_diff_trans, cfg.bound_rot, cfg.bound_trans,
+                        {cfg.checker_order[0], cfg.checker_order[1], cfg.checker_order[2]}};
   CheckerState chk;
   checkersInit(chk, T_iter);
   CUDA_TRY(ctx, cudaMemsetAsync(ctx->dstate, 0, 2 * sizeof(unsigned long long), ctx->stream));
@@ -900,6 +1021,7 @@ int32_t b200reg_icp_register(b200reg_icp* icp, const b200reg_cloud* reading, con
     status = icpErrToStatus(ctx, checkersCheck(ccfg, chk, T_iter, iterate, maxIter, errv), errv);
     ++st.iterations;
     if (status != B200REG_OK) break;
+    if (iterate && st.iterations >= ICP_HARD_ITERATION_CAP) { status = icpErrToStatus(ctx, ICPERR_ITER_CAP, errv); break; }
   }
   cudaEventRecord(ctx->ev1, ctx->stream);
   cudaEventSynchronize(ctx->ev1);
@@ -910,40 +1032,184 @@ int32_t b200reg_icp_register(b200reg_icp* icp, const b200reg_cloud* reading, con
   st.max_iterations_reached = maxIter ? 1 : 0;
   st.convergence_s = nowSec() - t1;
   if (status != B200REG_OK) return done(status);
-  // icpCorrected_T_refIn_readIn = T_refIn_refMean * (T_iter * T_refMean_readMean) * I   (ICP.cpp:459-465)
-  float Tref[16] = {1, 0, 0, icp->mean[0], 0, 1, 0, icp->mean[1], 0, 0, 1, icp->mean[2], 0, 0, 0, 1};
-  float tmp[16];
-  mul4(T_iter, Tpre, tmp);
-  mul4(Tref, tmp, T_out);
-  return done(B200REG_OK);
+  return done(composeResult(icp, T_iter, T_init, T_out));
 }
 
-// Batch of independent registrations on this ctx's device (loop-closure candidate refinement, PlaceRecognition.cpp:71-174:
-// independent iterations of a `for` loop).  Pair i: initReference(refs[i]) + compute(readings[i], T_init[i]).
-// A failing pair does not stop the batch: its status is recorded and its T_out is T_init (what Mapper.cpp:420-428 falls
-// back to when ICP throws).
+}  // extern "C"
+
+// =================================================================================================================
+// b200reg_batch — independent registrations kept in flight on ONE device (loop-closure candidate refinement,
+// PlaceRecognition.cpp:71-174: independent iterations of a `for` loop).  A single registration leaves the machine
+// under half full during the match and nearly idle during select / reduce / solve (profiles/r1_summary.md), so the batch owns
+// `lanes` independent lanes — each a ctx (stream, scratch, pinned staging), an ICP object (loop block + instantiated while-graph)
+// and two reusable device clouds — and deals pair i to lane i mod lanes.  Everything a pair needs (uploads, index build, reading
+// preparation, the device-resident loop, the read-back of the 144-byte result) is ENQUEUED on the lane's stream without a host
+// wait; the host collects a lane's result only when it needs that lane for the next pair.  The kernels of different lanes
+// interleave on the device: while one lane solves its 6x6 system another lane's match kernel has the SMs.
+// Results are those of the serial path, bit for bit: a lane runs exactly the code b200reg_icp_register runs.
+// =================================================================================================================
+#define BATCH_MAX_LANES 16
+struct b200reg_batch {
+  b200reg_ctx* parent = nullptr;
+  b200reg_icp_config cfg{};
+  int lanes = 0;
+  cudaEvent_t parentReady = nullptr;   // the parent stream's position when a batch call starts (its clouds may still be in flight)
+  struct Lane {
+    b200reg_ctx* ctx = nullptr;
+    b200reg_icp* icp = nullptr;
+    b200reg_cloud* ref = nullptr;       // reusable device clouds of the host-buffer entry point
+    b200reg_cloud* reading = nullptr;
+    int32_t inFlight = -1;              // pair index
+  } lane[BATCH_MAX_LANES];
+};
+
+namespace {
+
+int batchCollect(b200reg_batch* B, b200reg_batch::Lane& L, const float* T_init, float* T_out, b200reg_icp_stats* stats, int32_t* status, int* first) {
+  const int32_t i = L.inFlight;
+  if (i < 0) return B200REG_OK;
+  L.inFlight = -1;
+  b200reg_icp_stats st;
+  const int code = icpFinish(L.icp, T_out + 16 * (size_t)i, &st);
+  if (code != B200REG_OK) {
+    memcpy(T_out + 16 * (size_t)i, T_init + 16 * (size_t)i, 16 * sizeof(float));   // what Mapper.cpp:420-428 falls back to when ICP throws
+    if (*first == B200REG_OK) { *first = code; setErr(B->parent, code, "pair %d: %s", (int)i, L.ctx->err); }
+  }
+  B->parent->launches += L.ctx->launches;
+  L.ctx->launches = 0;
+  if (stats) stats[i] = st;
+  if (status) status[i] = code;
+  return code;
+}
+
+void batchFail(b200reg_batch* B, b200reg_batch::Lane& L, int32_t i, int code, const float* T_init, float* T_out, b200reg_icp_stats* stats,
+               int32_t* status, int* first) {
+  memcpy(T_out + 16 * (size_t)i, T_init + 16 * (size_t)i, 16 * sizeof(float));
+  if (*first == B200REG_OK) { *first = code; setErr(B->parent, code, "pair %d: %s", (int)i, L.ctx->err); }
+  if (stats) { stats[i] = L.icp->pendStats; }
+  if (status) status[i] = code;
+}
+
+// the loop of both batch entry points; `fetch` brings pair i's clouds to the lane (device pointers or uploads)
+template <class Fetch>
+int batchRun(b200reg_batch* B, int32_t n, const float* T_init, float* T_out, b200reg_icp_stats* stats, int32_t* status, Fetch fetch) {
+  b200reg_ctx* P = B->parent;
+  CUDA_TRY(P, cudaSetDevice(P->device));
+  CUDA_TRY(P, cudaEventRecord(B->parentReady, P->stream));
+  for (int l = 0; l < B->lanes; ++l) CUDA_TRY(P, cudaStreamWaitEvent(B->lane[l].ctx->stream, B->parentReady, 0));
+  int first = B200REG_OK;
+  for (int32_t i = 0; i < n; ++i) {
+    b200reg_batch::Lane& L = B->lane[i % B->lanes];
+    batchCollect(B, L, T_init, T_out, stats, status, &first);
+    const b200reg_cloud *ref = nullptr, *reading = nullptr;
+    memset(&L.icp->pendStats, 0, sizeof(L.icp->pendStats));
+    int code = fetch(L, i, &ref, &reading);
+    if (code == B200REG_OK) code = b200reg_icp_set_reference(L.icp, ref);
+    if (code == B200REG_OK) code = icpEnqueue(L.icp, reading, T_init + 16 * (size_t)i);
+    if (code == B200REG_OK) L.inFlight = i;
+    else batchFail(B, L, i, code, T_init, T_out, stats, status, &first);
+  }
+  for (int l = 0; l < B->lanes; ++l) batchCollect(B, B->lane[l], T_init, T_out, stats, status, &first);
+  return status ? B200REG_OK : first;   // with a status array the per-pair codes are the result
+}
+
+}  // namespace
+
+extern "C" {
+
+int32_t b200reg_batch_create(b200reg_ctx* ctx, const b200reg_icp_config* cfg, int32_t lanes, b200reg_batch** out) {
+  if (!ctx || !cfg || !out) return setErr(ctx, B200REG_E_INVALID_PARAM, "batch_create: bad arguments");
+  *out = nullptr;
+  if (cfg->knn != 1) return setErr(ctx, B200REG_E_INVALID_PARAM, "batch_create: the batched lanes run the device-resident loop (knn = 1)");
+  if (lanes <= 0) {
+    const char* env = getenv("B200REG_BATCH_LANES");
+    lanes = env ? atoi(env) : 0;
+    if (lanes <= 0) lanes = 4;
+  }
+  if (lanes > BATCH_MAX_LANES) lanes = BATCH_MAX_LANES;
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  b200reg_batch* B = new b200reg_batch();
+  B->parent = ctx;
+  B->cfg = *cfg;
+  B->lanes = lanes;
+  int code = B200REG_OK;
+  if (cudaEventCreateWithFlags(&B->parentReady, cudaEventDisableTiming) != cudaSuccess) code = setErr(ctx, B200REG_E_CUDA, "batch_create: event");
+  for (int l = 0; l < lanes && code == B200REG_OK; ++l) {
+    b200reg_batch::Lane& L = B->lane[l];
+    code = b200reg_ctx_create(ctx->device, &L.ctx);
+    if (code != B200REG_OK) { setErr(ctx, code, "batch_create: lane context"); break; }
+    L.ctx->profile = 0; L.ctx->hostLoop = 0;   // lanes always run the graph loop
+    code = b200reg_icp_create(L.ctx, cfg, &L.icp);
+    if (code != B200REG_OK) { setErr(ctx, code, "batch_create: %s", L.ctx->err); break; }
+    L.icp->graphState = (buildLoopGraph(L.icp) == 0) ? 1 : -1;
+    if (L.icp->graphState != 1) code = setErr(ctx, B200REG_E_CUDA, "batch_create: the device-resident loop (conditional graph nodes) is unavailable");
+  }
+  if (code != B200REG_OK) { b200reg_batch_destroy(B); return code; }
+  *out = B;
+  return B200REG_OK;
+}
+
+void b200reg_batch_destroy(b200reg_batch* B) {
+  if (!B) return;
+  cudaSetDevice(B->parent->device);
+  for (int l = 0; l < B->lanes; ++l) {
+    b200reg_batch::Lane& L = B->lane[l];
+    if (!L.ctx) continue;
+    cudaStreamSynchronize(L.ctx->stream);
+    if (L.icp) { L.icp->pending = false; b200reg_icp_destroy(L.icp); }
+    if (L.ref) b200reg_cloud_free(L.ctx, L.ref);
+    if (L.reading) b200reg_cloud_free(L.ctx, L.reading);
+    b200reg_ctx_destroy(L.ctx);
+  }
+  if (B->parentReady) cudaEventDestroy(B->parentReady);
+  delete B;
+}
+
+int32_t b200reg_batch_lanes(const b200reg_batch* B) { return B ? B->lanes : 0; }
+
+int32_t b200reg_batch_register(b200reg_batch* B, int32_t n, const b200reg_cloud* const* refs, const b200reg_cloud* const* readings,
+                               const float* T_init, float* T_out, b200reg_icp_stats* stats, int32_t* status) {
+  if (!B) return B200REG_E_INVALID_PARAM;
+  if (n < 0 || (n > 0 && (!refs || !readings || !T_init || !T_out))) return setErr(B->parent, B200REG_E_INVALID_PARAM, "batch_register: bad arguments");
+  return batchRun(B, n, T_init, T_out, stats, status, [&](b200reg_batch::Lane& L, int32_t i, const b200reg_cloud** ref, const b200reg_cloud** reading) {
+    if (!refs[i] || !readings[i]) return setErr(L.ctx, B200REG_E_INVALID_PARAM, "batch_register: null cloud");
+    *ref = refs[i];
+    *reading = readings[i];
+    return (int)B200REG_OK;
+  });
+}
+
+int32_t b200reg_batch_register_host(b200reg_batch* B, int32_t n, const b200reg_host_cloud* refs, const b200reg_host_cloud* readings,
+                                    const float* T_init, float* T_out, b200reg_icp_stats* stats, int32_t* status) {
+  if (!B) return B200REG_E_INVALID_PARAM;
+  if (n < 0 || (n > 0 && (!refs || !readings || !T_init || !T_out))) return setErr(B->parent, B200REG_E_INVALID_PARAM, "batch_register_host: bad arguments");
+  return batchRun(B, n, T_init, T_out, stats, status, [&](b200reg_batch::Lane& L, int32_t i, const b200reg_cloud** ref, const b200reg_cloud** reading) {
+    const b200reg_host_cloud &hr = refs[i], &hq = readings[i];
+    // asynchronous uploads on the lane's stream (pinned host memory overlaps with the other lanes' kernels; pageable memory is
+    // staged by the runtime and only the staging copy blocks this thread)
+    int code = L.ref ? b200reg_cloud_update_f32(L.ctx, L.ref, hr.feat, hr.feat_stride, hr.normals, hr.n, 1)
+                     : b200reg_cloud_upload_f32(L.ctx, hr.feat, hr.feat_stride, hr.normals, hr.n, &L.ref);
+    if (code != B200REG_OK) return code;
+    code = L.reading ? b200reg_cloud_update_f32(L.ctx, L.reading, hq.feat, hq.feat_stride, hq.normals, hq.n, 1)
+                     : b200reg_cloud_upload_f32(L.ctx, hq.feat, hq.feat_stride, hq.normals, hq.n, &L.reading);
+    if (code != B200REG_OK) return code;
+    *ref = L.ref;
+    *reading = L.reading;
+    return (int)B200REG_OK;
+  });
+}
+
+// One-shot form: a batch object with the default number of lanes for the duration of the call.
 int32_t b200reg_icp_register_batch(b200reg_ctx* ctx, const b200reg_icp_config* cfg, int32_t n, const b200reg_cloud* const* refs,
                                    const b200reg_cloud* const* readings, const float* T_init, float* T_out, b200reg_icp_stats* stats,
                                    int32_t* status) {
   if (!ctx || !cfg || n < 0 || (n > 0 && (!refs || !readings || !T_init || !T_out)))
     return setErr(ctx, B200REG_E_INVALID_PARAM, "icp_register_batch: bad arguments");
-  b200reg_icp* icp = nullptr;
-  TRY(b200reg_icp_create(ctx, cfg, &icp));
-  int first = B200REG_OK;
-  for (int32_t i = 0; i < n; ++i) {
-    int code = (refs[i] && readings[i]) ? b200reg_icp_set_reference(icp, refs[i]) : B200REG_E_INVALID_PARAM;
-    b200reg_icp_stats st;
-    memset(&st, 0, sizeof(st));
-    if (code == B200REG_OK) code = b200reg_icp_register(icp, readings[i], T_init + 16 * (size_t)i, T_out + 16 * (size_t)i, &st);
-    if (code != B200REG_OK) {
-      memcpy(T_out + 16 * (size_t)i, T_init + 16 * (size_t)i, 16 * sizeof(float));
-      if (first == B200REG_OK) first = code;
-    }
-    if (stats) stats[i] = st;
-    if (status) status[i] = code;
-  }
-  b200reg_icp_destroy(icp);
-  return status ? B200REG_OK : first;   // with a status array the per-pair codes are the result
+  b200reg_batch* B = nullptr;
+  TRY(b200reg_batch_create(ctx, cfg, n < 4 ? (n > 0 ? n : 1) : 0, &B));
+  const int code = b200reg_batch_register(B, n, refs, readings, T_init, T_out, stats, status);
+  b200reg_batch_destroy(B);
+  return code;
 }
 
 }  // extern "C"

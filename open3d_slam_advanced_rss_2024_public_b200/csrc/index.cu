@@ -1,13 +1,23 @@
-// csrc/index.cu — KDTreeMatcher::init replacement (MatchersImpl.cpp:109-114): a radix-sorted voxel-grid index.
+// csrc/index.cu — KDTreeMatcher::init replacement (MatchersImpl.cpp:109-114): a counting-sorted voxel-grid index, built
+// without a host round trip.
 //
 // Layout in HBM: the (centred) reference is re-ordered by linear cell id (x fastest) into
 //   pts[M]  float4 = (x, y, z, original index as int bits)   — one 16 B coalesced load yields position AND id
 //   nrm[M]  float4 = reference normals in the same order
 //   cellStart[numCells + 1] uint32                           — CSR directory; x-adjacent cells are contiguous ranges
-// Build = stats (mean + bbox, fp64 sums) -> key/count -> 32-bit radix sort of (cell, index) -> exclusive scan -> gather.
-#include <cub/device/device_radix_sort.cuh>
-#include <cub/device/device_scan.cuh>
-
+//   hdr     IndexHeader (device)                             — grid geometry + mean, derived ON THE DEVICE from the cloud's bbox
+//
+// Build (all on the ctx stream, nothing waits on the host):
+//   statsKernel      fp64 coordinate sums + bbox per block                                   16 B/pt read
+//   gridKernel       one block: mean (fp64 sum rounded once to fp32, ICP.cpp:313), bbox of the centred cloud, cell size, grid
+//   zeroDirKernel    directory + scan tile states
+//   countKernel      cell of fl(p - mean) (ICP.cpp:320); rank of the point inside its cell = the value the atomic returns   16 B/pt read, 4 B/pt written
+//   scanDirKernel    single-pass inclusive scan of the counts (decoupled look-back), length read from the header        8 B/cell
+//   scatterKernel    pts[cellStart[cell] + rank] = (centred point, index), normals alike                               36 B/pt read, 32 B/pt written
+// The order of the points INSIDE a cell is the arrival order of the atomics; nothing downstream depends on it: every search
+// resolves ties by (d2, original index) and the reductions run in reading order (knn.cu, icp_kernels.cuh).
+// The host learns the grid (for b200reg_index_cell, error reporting) from an asynchronous copy of the header, waited for only
+// when somebody asks.
 #include <cfloat>
 #include <cmath>
 
@@ -55,38 +65,236 @@ __global__ void statsKernel(const float4* __restrict__ xyz, int64_t n, StatsPart
   }
 }
 
+// One block: block partials -> mean, bbox of the centred cloud, cell size, grid dimensions (what the host used to do between two
+// synchronisations).  The partials are added in block order by one thread per quantity, so the mean is the same whatever ran
+// beside this kernel.  Non-finite coordinates (a LiDAR driver's +-inf "no return") leave status = 1 and a 1-cell grid, so the
+// kernels behind this one run harmlessly and the host reports InvalidParameter when it reads the header.
+#define GRID_MAX_PARTIALS 768
+__global__ void __launch_bounds__(256) gridKernel(const StatsPartial* __restrict__ partials, int blocks, long long m, int centre, float userCell,
+                                                  unsigned capCells, IndexHeader* __restrict__ hdr) {
+  __shared__ StatsPartial sp[GRID_MAX_PARTIALS];
+  __shared__ double sSum[3];
+  __shared__ float sMn[3], sMx[3];
+  for (int b = threadIdx.x; b < blocks; b += blockDim.x) sp[b] = partials[b];
+  __syncthreads();
+  if (threadIdx.x < 3) {
+    double s = 0;
+    for (int b = 0; b < blocks; ++b) s += (threadIdx.x == 0) ? sp[b].sx : (threadIdx.x == 1) ? sp[b].sy : sp[b].sz;
+    sSum[threadIdx.x] = s;
+  } else if (threadIdx.x >= 32 && threadIdx.x < 35) {
+    const int d = threadIdx.x - 32;
+    float a = FLT_MAX, z = -FLT_MAX;
+    for (int b = 0; b < blocks; ++b) {
+      a = fminf(a, d == 0 ? sp[b].mnx : d == 1 ? sp[b].mny : sp[b].mnz);
+      z = fmaxf(z, d == 0 ? sp[b].mxx : d == 1 ? sp[b].mxy : sp[b].mxz);
+    }
+    sMn[d] = a; sMx[d] = z;
+  }
+  __syncthreads();
+  if (threadIdx.x != 0) return;
+  IndexHeader h;
+  h.m = m;
+  bool finite = true;
+  for (int d = 0; d < 3; ++d) {
+    h.sum[d] = sSum[d];
+    h.bbMin[d] = sMn[d]; h.bbMax[d] = sMx[d];
+    // meanReference = features.rowwise().mean() (ICP.cpp:313): fp64 sum rounded once to fp32 (contract)
+    h.mean[d] = centre ? (float)(sSum[d] / (double)m) : 0.f;
+    finite = finite && (fabs(sSum[d]) <= DBL_MAX) && (fabsf(sMn[d]) <= FLT_MAX) && (fabsf(sMx[d]) <= FLT_MAX);
+  }
+  h.status = finite ? 0 : 1;
+  GridDesc& g = h.g;
+  if (!finite) {
+    for (int d = 0; d < 3; ++d) h.mean[d] = 0.f;
+    g.ox = g.oy = g.oz = 0.f; g.cell = 1.f; g.inv_cell = 1.f; g.slack = 0.f; g.ring2Safe = 0.f; g.nx = g.ny = g.nz = 1;
+    h.numCells = 1;
+    *hdr = h;
+    return;
+  }
+  // bbox of the centred cloud: fl(min - mean) .. fl(max - mean) (fp32 subtraction is monotone)
+  float lo[3], hi[3], ext[3];
+  float maxAbs = 0.f;
+  for (int d = 0; d < 3; ++d) {
+    lo[d] = h.bbMin[d] - h.mean[d];
+    hi[d] = h.bbMax[d] - h.mean[d];
+    ext[d] = fmaxf(hi[d] - lo[d], 1e-6f);
+    maxAbs = fmaxf(maxAbs, fmaxf(fabsf(lo[d]), fabsf(hi[d])));
+  }
+  float cell = userCell;
+  const float emax = fmaxf(ext[0], fmaxf(ext[1], ext[2]));
+  if (!(cell > 0.f) || !(cell <= FLT_MAX)) {   // automatic: ~2.5 x the mean spacing of points spread over the bbox surface
+    const double area = 2.0 * ((double)ext[0] * ext[1] + (double)ext[1] * ext[2] + (double)ext[0] * ext[2]);
+    cell = (float)(2.5 * sqrt(area / (double)m));
+    cell = fmaxf(cell, emax * 1e-4f);
+  }
+  cell = fmaxf(cell, emax * 1e-6f);   // a user cell far below the extent would overflow the int cell coordinates
+  for (int it = 0; it < 400; ++it) {   // keep the directory inside its allocation (capCells, chosen by the host from m alone)
+    const double nc = (floor((double)(ext[0] / cell)) + 1) * (floor((double)(ext[1] / cell)) + 1) * (floor((double)(ext[2] / cell)) + 1);
+    if (nc <= (double)capCells) break;
+    cell *= 1.26f;
+  }
+  g.ox = lo[0]; g.oy = lo[1]; g.oz = lo[2];
+  g.cell = cell;
+  g.inv_cell = 1.0f / cell;
+  g.nx = (int)floorf(ext[0] / cell) + 1;
+  g.ny = (int)floorf(ext[1] / cell) + 1;
+  g.nz = (int)floorf(ext[2] / cell) + 1;
+  // slack >= error of fl((p-o)*inv) cell assignment + error of evaluating cell bounds in fp32 (see knn.cu)
+  g.slack = 16.f * 1.1920929e-7f * (maxAbs + emax + cell);
+  {   // (cell - 4 slack)^2 with a 1 % margin, rounded toward zero: a point >= 2 cells away cannot have a smaller fp32 d2
+    const double c = (double)cell - 4.0 * (double)g.slack;
+    g.ring2Safe = (c > 0.0) ? nextafterf((float)(0.99 * c * c), 0.f) : 0.f;
+  }
+  h.numCells = (unsigned)g.nx * (unsigned)g.ny * (unsigned)g.nz;
+  *hdr = h;
+}
+
+// ---- directory: counts -> inclusive scan, single pass ------------------------------------------------------------------------
+#define SCAN_THREADS 256
+#define SCAN_ITEMS 16
+#define SCAN_TILE (SCAN_THREADS * SCAN_ITEMS)
+// tile state: bits [63:62] = 0 empty, 1 aggregate of this tile only, 2 inclusive prefix; bits [31:0] = value (< 2^31)
+#define TS_AGG (1ull << 62)
+#define TS_INC (2ull << 62)
+
+// Directory allocation: dirBase = [3 pad words | cellStart[0] | counts of cells 0 .. numCells-1 | padding to a whole scan tile];
+// cellStart = dirBase + 3, so the counts (cellStart + 1 = dirBase + 4) are 16-byte aligned for the scan's vector accesses.
+// zeroes dirBase[0 .. 4 + numCells) (rounded up to 16 bytes), the tile states of the scan and its tile counter
+__global__ void zeroDirKernel(const IndexHeader* __restrict__ hdr, uint32_t* __restrict__ dirBase, unsigned long long* __restrict__ tileState,
+                              unsigned* __restrict__ tileCounter) {
+  const unsigned numCells = hdr->numCells;
+  const size_t quads = ((size_t)numCells + 4 + 3) / 4;   // dirBase is 16-byte aligned (pool allocation) and padded
+  const size_t stride = (size_t)gridDim.x * blockDim.x, t0 = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  uint4* d4 = reinterpret_cast<uint4*>(dirBase);
+  for (size_t i = t0; i < quads; i += stride) d4[i] = make_uint4(0u, 0u, 0u, 0u);
+  const size_t tiles = ((size_t)numCells + SCAN_TILE - 1) / SCAN_TILE;
+  for (size_t i = t0; i < tiles; i += stride) tileState[i] = 0ull;
+  if (t0 == 0) *tileCounter = 0u;
+}
+
 __device__ __forceinline__ int cellCoord(float p, float o, float inv, int nmax) {
   const int c = (int)floorf(__fmul_rn(__fsub_rn(p, o), inv));
   return min(max(c, 0), nmax - 1);
 }
-
-// centred point = fl(p - mean) exactly as ICP.cpp:320 does; key = linear cell (x fastest)
-__global__ void keyKernel(const float4* __restrict__ xyz, int64_t n, float mx, float my, float mz, GridDesc g,
-                          uint32_t* __restrict__ keys, uint32_t* __restrict__ vals, uint32_t* __restrict__ counts) {
-  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
-  const float4 p = xyz[i];
-  const float x = __fsub_rn(p.x, mx), y = __fsub_rn(p.y, my), z = __fsub_rn(p.z, mz);
+__device__ __forceinline__ uint32_t cellKeyOf(const float4 p, const float mx, const float my, const float mz, const GridDesc& g, float& x, float& y,
+                                              float& z) {
+  // centred point = fl(p - mean) exactly as ICP.cpp:320 does; key = linear cell (x fastest)
+  x = __fsub_rn(p.x, mx); y = __fsub_rn(p.y, my); z = __fsub_rn(p.z, mz);
   const int cx = cellCoord(x, g.ox, g.inv_cell, g.nx), cy = cellCoord(y, g.oy, g.inv_cell, g.ny), cz = cellCoord(z, g.oz, g.inv_cell, g.nz);
-  const uint32_t key = (uint32_t)cx + (uint32_t)g.nx * ((uint32_t)cy + (uint32_t)g.ny * (uint32_t)cz);
-  keys[i] = key;
-  vals[i] = (uint32_t)i;
-  atomicAdd(&counts[key], 1u);
+  return (uint32_t)cx + (uint32_t)g.nx * ((uint32_t)cy + (uint32_t)g.ny * (uint32_t)cz);
 }
 
-__global__ void gatherKernel(const float4* __restrict__ xyz, const float4* __restrict__ nrm, const uint32_t* __restrict__ vals,
-                             int64_t n, float mx, float my, float mz, float4* __restrict__ pts, float4* __restrict__ outN) {
-  const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (j >= n) return;
-  const uint32_t i = vals[j];
-  const float4 p = xyz[i];
-  pts[j] = make_float4(__fsub_rn(p.x, mx), __fsub_rn(p.y, my), __fsub_rn(p.z, mz), __int_as_float((int)i));
-  if (nrm) outN[j] = nrm[i];
+__global__ void __launch_bounds__(256) countKernel(const float4* __restrict__ xyz, int64_t n, const IndexHeader* __restrict__ hdr,
+                                                   uint32_t* __restrict__ cellStart, uint32_t* __restrict__ rank) {
+  const GridDesc g = hdr->g;
+  const float mx = hdr->mean[0], my = hdr->mean[1], mz = hdr->mean[2];
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    float x, y, z;
+    const uint32_t key = cellKeyOf(xyz[i], mx, my, mz, g, x, y, z);
+    rank[i] = atomicAdd(&cellStart[key + 1], 1u);   // counts live one slot up: the scan turns them into the next cell's start
+  }
+}
+
+// Inclusive scan of the counts, cellStart[1 .. numCells], in place (cellStart[0] stays 0): afterwards cellStart[c] = first sorted
+// position of cell c and cellStart[numCells] = m.  One pass over the directory: tiles are handed out by a counter (so a tile's predecessors are always
+// running or done), each publishes its aggregate, then looks back over its predecessors' states a warp at a time.
+__global__ void __launch_bounds__(SCAN_THREADS) scanDirKernel(const IndexHeader* __restrict__ hdr, uint32_t* __restrict__ cellStart,
+                                                              unsigned long long* __restrict__ tileState, unsigned* __restrict__ tileCounter) {
+  const unsigned numCells = hdr->numCells;
+  const unsigned tiles = (numCells + SCAN_TILE - 1) / SCAN_TILE;
+  uint32_t* __restrict__ data = cellStart + 1;   // 16-byte aligned (zeroDirKernel)
+  __shared__ unsigned sTile, sWarp[SCAN_THREADS / 32], sPrefix;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  for (;;) {
+    __syncthreads();   // sTile / sPrefix / sWarp of the previous round are no longer read
+    if (threadIdx.x == 0) sTile = atomicAdd(tileCounter, 1u);
+    __syncthreads();
+    const unsigned tile = sTile;
+    if (tile >= tiles) return;
+    const size_t base = (size_t)tile * SCAN_TILE + (size_t)threadIdx.x * SCAN_ITEMS;
+    unsigned v[SCAN_ITEMS];
+    // each thread owns SCAN_ITEMS consecutive words (64 B: two full sectors), fetched as four 16-byte loads; the allocation is
+    // padded to a whole tile, words beyond numCells are ignored
+#pragma unroll
+    for (int j = 0; j < SCAN_ITEMS / 4; ++j) {
+      const uint4 q = __ldcg(reinterpret_cast<const uint4*>(data + base) + j);
+      v[4 * j] = q.x; v[4 * j + 1] = q.y; v[4 * j + 2] = q.z; v[4 * j + 3] = q.w;
+    }
+#pragma unroll
+    for (int j = 0; j < SCAN_ITEMS; ++j) if (base + j >= numCells) v[j] = 0u;
+    unsigned sum = 0;
+#pragma unroll
+    for (int j = 0; j < SCAN_ITEMS; ++j) { sum += v[j]; v[j] = sum; }   // thread-local inclusive
+    unsigned incl = sum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const unsigned t = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl += t;
+    }
+    if (lane == 31) sWarp[warp] = incl;
+    __syncthreads();
+    unsigned warpOff = 0, tileSum = 0;
+#pragma unroll
+    for (int w = 0; w < SCAN_THREADS / 32; ++w) {
+      const unsigned s = sWarp[w];
+      if (w < warp) warpOff += s;
+      tileSum += s;
+    }
+    if (warp == 0) {   // publish, then look back
+      if (lane == 0) {
+        __threadfence();
+        atomicExch(&tileState[tile], (tile == 0 ? TS_INC : TS_AGG) | (unsigned long long)tileSum);
+      }
+      unsigned prefix = 0;
+      if (tile > 0) {
+        int look = (int)tile - 1;
+        for (;;) {
+          const int idx = look - lane;
+          unsigned long long s = TS_INC;   // lanes before tile 0 behave like an inclusive prefix of 0
+          if (idx >= 0) {
+            do { s = *((volatile unsigned long long*)&tileState[idx]); } while ((s >> 62) == 0ull);
+          }
+          const unsigned incMask = __ballot_sync(0xffffffffu, (s >> 62) == 2ull);
+          const int firstInc = incMask ? (__ffs(incMask) - 1) : 32;   // nearest predecessor holding an inclusive prefix
+          unsigned contrib = (lane <= firstInc) ? (unsigned)s : 0u;
+#pragma unroll
+          for (int o = 16; o > 0; o >>= 1) contrib += __shfl_xor_sync(0xffffffffu, contrib, o);
+          prefix += contrib;
+          if (incMask) break;
+          look -= 32;
+        }
+        if (lane == 0) {
+          __threadfence();
+          atomicExch(&tileState[tile], TS_INC | (unsigned long long)(prefix + tileSum));
+        }
+      }
+      if (lane == 0) sPrefix = prefix;
+    }
+    __syncthreads();
+    const unsigned off = sPrefix + warpOff + (incl - sum);
+#pragma unroll
+    for (int j = 0; j < SCAN_ITEMS / 4; ++j)   // words beyond numCells land in the allocation's padding
+      reinterpret_cast<uint4*>(data + base)[j] = make_uint4(v[4 * j] + off, v[4 * j + 1] + off, v[4 * j + 2] + off, v[4 * j + 3] + off);
+  }
+}
+
+__global__ void __launch_bounds__(256) scatterKernel(const float4* __restrict__ xyz, const float4* __restrict__ nrm, int64_t n,
+                                                     const IndexHeader* __restrict__ hdr, const uint32_t* __restrict__ cellStart,
+                                                     const uint32_t* __restrict__ rank, float4* __restrict__ pts, float4* __restrict__ outN) {
+  const GridDesc g = hdr->g;
+  const float mx = hdr->mean[0], my = hdr->mean[1], mz = hdr->mean[2];
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    float x, y, z;
+    const uint32_t key = cellKeyOf(xyz[i], mx, my, mz, g, x, y, z);
+    const uint32_t j = cellStart[key] + rank[i];
+    pts[j] = make_float4(x, y, z, __int_as_float((int)i));
+    if (nrm) outN[j] = nrm[i];
+  }
 }
 
 }  // namespace
 
-// shared with icp.cu: mean (fp64 sum rounded once to fp32) and bbox of a cloud
+// shared with voxelgrid.cu: mean sums and bbox of a cloud on the HOST (one synchronisation; the index build does not use this)
 int cloudStats(b200reg_ctx* ctx, const b200reg_cloud* c, double sum[3], float mn[3], float mx[3]) {
   const int blocks = (int)fmin((double)(4 * ctx->sm_count), (double)divUp(c->n, 256));
   TRY(ensureBuf(ctx, ctx->partials, sizeof(StatsPartial) * (size_t)blocks));
@@ -107,83 +315,87 @@ int cloudStats(b200reg_ctx* ctx, const b200reg_cloud* c, double sum[3], float mn
   return B200REG_OK;
 }
 
-// Build the index over `ref` after subtracting `mean` (pass zeros for an un-centred index).
-int buildIndex(b200reg_ctx* ctx, const b200reg_cloud* ref, const float mean[3], const float bbMin[3], const float bbMax[3], float cell,
-               b200reg_index** out) {
+static void indexRelease(b200reg_ctx* ctx, b200reg_index* ix) {
+  if (!ix) return;
+  if (ix->hdrReady) {
+    cudaEventSynchronize(ix->hdrReady);   // the header copy targets ix->hHdr: it must have landed before the slot is reused
+    cudaEventDestroy(ix->hdrReady);
+  }
+  if (ix->hHdr) releaseHeaderSlot(ctx, ix->hHdr);
+  if (ix->pts) devFree(ctx, ix->pts);
+  if (ix->nrm) devFree(ctx, ix->nrm);
+  if (ix->dirBase) devFree(ctx, ix->dirBase);
+  if (ix->dHdr) devFree(ctx, ix->dHdr);
+  delete ix;
+}
+
+// Enqueue the build of an index over `ref` (centre != 0: after subtracting the cloud's mean, ICP.cpp:313-320).  Nothing here
+// waits for the device; `ref` must stay alive until the stream has passed this point (stream-ordered frees on the same ctx do).
+int buildIndex(b200reg_ctx* ctx, const b200reg_cloud* ref, int centre, float cell, b200reg_index** out) {
   const int64_t m = ref->n;
+  *out = nullptr;
   if (m <= 0) return setErr(ctx, B200REG_E_NO_POINTS, "index_build: reference cloud is empty");
   if (m >= (int64_t)0x7fffffff) return setErr(ctx, B200REG_E_INVALID_PARAM, "index_build: more than 2^31-1 points");
   b200reg_index* ix = new b200reg_index();
   ix->m = m;
-  for (int d = 0; d < 3; ++d) ix->mean[d] = mean[d];
-  // bbox of the centred cloud: fl(min - mean) .. fl(max - mean) (fp32 subtraction is monotone)
-  float lo[3], hi[3], ext[3];
-  float maxAbs = 0.f;
-  for (int d = 0; d < 3; ++d) {
-    lo[d] = bbMin[d] - mean[d];
-    hi[d] = bbMax[d] - mean[d];
-    ext[d] = fmaxf(hi[d] - lo[d], 1e-6f);
-    maxAbs = fmaxf(maxAbs, fmaxf(fabsf(lo[d]), fabsf(hi[d])));
-  }
-  if (!(cell > 0.f)) {   // automatic: ~2.5 x the mean spacing of points spread over the bbox surface
-    const double area = 2.0 * ((double)ext[0] * ext[1] + (double)ext[1] * ext[2] + (double)ext[0] * ext[2]);
-    cell = (float)(2.5 * sqrt(area / (double)m));
-    const float emax = fmaxf(ext[0], fmaxf(ext[1], ext[2]));
-    cell = fmaxf(cell, emax * 1e-4f);
-  }
-  for (;;) {   // keep the directory below 2^30 cells
-    const double nc = (floor(ext[0] / cell) + 1) * (floor(ext[1] / cell) + 1) * (floor(ext[2] / cell) + 1);
-    if (nc <= (double)(1u << 30)) break;
-    cell *= 1.26f;
-  }
-  GridDesc& g = ix->g;
-  g.ox = lo[0]; g.oy = lo[1]; g.oz = lo[2];
-  g.cell = cell;
-  g.inv_cell = 1.0f / cell;
-  g.nx = (int)floorf(ext[0] / cell) + 1;
-  g.ny = (int)floorf(ext[1] / cell) + 1;
-  g.nz = (int)floorf(ext[2] / cell) + 1;
-  // slack >= error of fl((p-o)*inv) cell assignment + error of evaluating cell bounds in fp32 (see knn.cu)
-  g.slack = 16.f * 1.1920929e-7f * (maxAbs + fmaxf(ext[0], fmaxf(ext[1], ext[2])) + cell);
-  {   // (cell - 4 slack)^2 with a 1 % margin, rounded toward zero: a point >= 2 cells away cannot have a smaller fp32 d2
-    const double c = (double)cell - 4.0 * (double)g.slack;
-    g.ring2Safe = (c > 0.0) ? nextafterf((float)(0.99 * c * c), 0.f) : 0.f;
-  }
-  const size_t numCells = (size_t)g.nx * g.ny * g.nz;
-
-  cudaError_t e = devAlloc(ctx, &ix->pts, sizeof(float4) * (size_t)m);
+  // directory capacity from m alone (the host does not know the bbox): 8 cells per point, at least 2^16, at most 2^30; the
+  // device grows the cell until the grid fits (the automatic cell gives ~4 cells per point on surface-like clouds)
+  const uint64_t cap = std::min<uint64_t>(std::max<uint64_t>(8ull * (uint64_t)m, 1ull << 16), 1ull << 30);
+  ix->cellCap = (uint32_t)cap;
+  const size_t tilesCap = (cap + SCAN_TILE - 1) / SCAN_TILE;
+  const int sblocks = (int)fmin((double)(4 * ctx->sm_count), (double)divUp(m, 256));
+  static_assert(4 * B200_SM_COUNT <= GRID_MAX_PARTIALS, "gridKernel stages the block partials in shared memory");
+  int st = B200REG_OK;
+  cudaError_t e = cudaSuccess;
+  auto fail = [&](int code) { indexRelease(ctx, ix); return code; };
+  if (sblocks > GRID_MAX_PARTIALS) return fail(setErr(ctx, B200REG_E_INVALID_PARAM, "index_build: device with more than %d SMs", GRID_MAX_PARTIALS / 4));
+  e = devAlloc(ctx, &ix->pts, sizeof(float4) * (size_t)m);
   if (e == cudaSuccess && ref->nrm) e = devAlloc(ctx, &ix->nrm, sizeof(float4) * (size_t)m);
-  if (e == cudaSuccess) e = devAlloc(ctx, &ix->cellStart, sizeof(uint32_t) * (numCells + 1));
-  if (e != cudaSuccess) {
-    b200reg_index_free(ctx, ix);
-    return setErr(ctx, B200REG_E_OOM, "index_build: allocation failed (%zu cells, %lld points): %s", numCells, (long long)m, cudaGetErrorString(e));
-  }
-  TRY(ensureBuf(ctx, ctx->keys0, sizeof(uint32_t) * (size_t)m));
-  TRY(ensureBuf(ctx, ctx->keys1, sizeof(uint32_t) * (size_t)m));
-  TRY(ensureBuf(ctx, ctx->vals0, sizeof(uint32_t) * (size_t)m));
-  TRY(ensureBuf(ctx, ctx->vals1, sizeof(uint32_t) * (size_t)m));
-  uint32_t* counts = ix->cellStart;   // counted in place, then scanned in place
-  CUDA_TRY(ctx, cudaMemsetAsync(counts, 0, sizeof(uint32_t) * (numCells + 1), ctx->stream));
-  keyKernel<<<divUp(m, 256), 256, 0, ctx->stream>>>(ref->xyz, m, mean[0], mean[1], mean[2], g, (uint32_t*)ctx->keys0.p,
-                                                    (uint32_t*)ctx->vals0.p, counts);
-  LAUNCH_CHECK(ctx);
-  int endBit = 1;
-  while (endBit < 32 && ((size_t)1 << endBit) < numCells) ++endBit;
-  cub::DoubleBuffer<uint32_t> dk((uint32_t*)ctx->keys0.p, (uint32_t*)ctx->keys1.p), dv((uint32_t*)ctx->vals0.p, (uint32_t*)ctx->vals1.p);
-  size_t tmpSort = 0, tmpScan = 0;
-  CUDA_TRY(ctx, cub::DeviceRadixSort::SortPairs(nullptr, tmpSort, dk, dv, (int)m, 0, endBit, ctx->stream));
-  CUDA_TRY(ctx, cub::DeviceScan::ExclusiveSum(nullptr, tmpScan, counts, counts, (int64_t)(numCells + 1), ctx->stream));
-  TRY(ensureBuf(ctx, ctx->cubtmp, tmpSort > tmpScan ? tmpSort : tmpScan));
-  size_t tmpBytes = ctx->cubtmp.cap;
-  CUDA_TRY(ctx, cub::DeviceRadixSort::SortPairs(ctx->cubtmp.p, tmpBytes, dk, dv, (int)m, 0, endBit, ctx->stream));
-  ctx->launches += (uint64_t)((endBit + 7) / 8 + 2);
-  tmpBytes = ctx->cubtmp.cap;
-  CUDA_TRY(ctx, cub::DeviceScan::ExclusiveSum(ctx->cubtmp.p, tmpBytes, counts, counts, (int64_t)(numCells + 1), ctx->stream));
-  ctx->launches += 2;
-  gatherKernel<<<divUp(m, 256), 256, 0, ctx->stream>>>(ref->xyz, ref->nrm, dv.Current(), m, mean[0], mean[1], mean[2], ix->pts, ix->nrm);
-  LAUNCH_CHECK(ctx);
+  if (e == cudaSuccess) e = devAlloc(ctx, &ix->dirBase, sizeof(uint32_t) * ((size_t)tilesCap * SCAN_TILE + 8));
+  ix->cellStart = ix->dirBase ? ix->dirBase + 3 : nullptr;
+  if (e == cudaSuccess) e = devAlloc(ctx, &ix->dHdr, sizeof(IndexHeader));
+  if (e == cudaSuccess) e = cudaEventCreateWithFlags(&ix->hdrReady, cudaEventDisableTiming);
+  if (e != cudaSuccess)
+    return fail(setErr(ctx, B200REG_E_OOM, "index_build: allocation failed (%llu directory cells, %lld points): %s", (unsigned long long)cap, (long long)m, cudaGetErrorString(e)));
+  ix->hHdr = acquireHeaderSlot(ctx);
+  if (!ix->hHdr) return fail(setErr(ctx, B200REG_E_OOM, "index_build: no pinned header slot"));
+  if ((st = ensureBuf(ctx, ctx->partials, sizeof(StatsPartial) * (size_t)sblocks)) != B200REG_OK) return fail(st);
+  if ((st = ensureBuf(ctx, ctx->keys0, sizeof(uint32_t) * (size_t)m)) != B200REG_OK) return fail(st);
+  if ((st = ensureBuf(ctx, ctx->cubtmp, sizeof(unsigned long long) * tilesCap + 64)) != B200REG_OK) return fail(st);
+  unsigned long long* tileState = (unsigned long long*)ctx->cubtmp.p;
+  unsigned* tileCounter = (unsigned*)((char*)ctx->cubtmp.p + sizeof(unsigned long long) * tilesCap);
+  uint32_t* rank = (uint32_t*)ctx->keys0.p;
+  const int wide = 8 * ctx->sm_count;   // grid of the streaming passes: 8 blocks of 256 threads per SM
+  const int pblocks = (int)std::min<int64_t>(divUp(m, 256), wide);
+  statsKernel<<<sblocks, 256, 0, ctx->stream>>>(ref->xyz, m, (StatsPartial*)ctx->partials.p);
+  gridKernel<<<1, 256, 0, ctx->stream>>>((const StatsPartial*)ctx->partials.p, sblocks, (long long)m, centre, cell, ix->cellCap, ix->dHdr);
+  zeroDirKernel<<<(int)std::min<uint64_t>(wide, (cap / 4 + 255) / 256), 256, 0, ctx->stream>>>(ix->dHdr, ix->dirBase, tileState, tileCounter);
+  countKernel<<<pblocks, 256, 0, ctx->stream>>>(ref->xyz, m, ix->dHdr, ix->cellStart, rank);
+  scanDirKernel<<<(int)std::min<uint64_t>(4 * ctx->sm_count, tilesCap), SCAN_THREADS, 0, ctx->stream>>>(ix->dHdr, ix->cellStart, tileState, tileCounter);
+  scatterKernel<<<pblocks, 256, 0, ctx->stream>>>(ref->xyz, ref->nrm, m, ix->dHdr, ix->cellStart, rank, ix->pts, ix->nrm);
+  ctx->launches += 6;
+  e = cudaGetLastError();
+  if (e == cudaSuccess) e = cudaMemcpyAsync(ix->hHdr, ix->dHdr, sizeof(IndexHeader), cudaMemcpyDeviceToHost, ctx->stream);
+  if (e == cudaSuccess) e = cudaEventRecord(ix->hdrReady, ctx->stream);
+  if (e != cudaSuccess) return fail(setErr(ctx, B200REG_E_CUDA, "index_build: %s", cudaGetErrorString(e)));
   *out = ix;
   return B200REG_OK;
+}
+
+// Host view of the header: waits (once) for the asynchronous copy enqueued by the build.  Returns nullptr with the ctx error set
+// when the build failed on the device (non-finite coordinates).
+const IndexHeader* indexHeader(b200reg_ctx* ctx, const b200reg_index* cix) {
+  b200reg_index* ix = const_cast<b200reg_index*>(cix);
+  if (!ix->hdrFetched) {
+    const cudaError_t e = cudaEventSynchronize(ix->hdrReady);
+    if (e != cudaSuccess) { setErr(ctx, B200REG_E_CUDA, "index_build failed: %s", cudaGetErrorString(e)); return nullptr; }
+    ix->hdrFetched = true;
+  }
+  if (ix->hHdr->status != 0) {
+    setErr(ctx, B200REG_E_INVALID_PARAM, "index_build: non-finite coordinates in the reference cloud");
+    return nullptr;
+  }
+  return ix->hHdr;
 }
 
 extern "C" {
@@ -193,30 +405,27 @@ int32_t b200reg_index_build(b200reg_ctx* ctx, const b200reg_cloud* ref, float ce
   *out = nullptr;
   if (ref->n <= 0) return setErr(ctx, B200REG_E_NO_POINTS, "index_build: reference cloud is empty");
   CUDA_TRY(ctx, cudaSetDevice(ctx->device));
-  CUDA_TRY(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
-  double sum[3];
-  float mn[3], mx[3];
-  TRY(cloudStats(ctx, ref, sum, mn, mx));
-  const float zero[3] = {0.f, 0.f, 0.f};
-  TRY(buildIndex(ctx, ref, zero, mn, mx, cell, out));
-  CUDA_TRY(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
-  CUDA_TRY(ctx, cudaEventSynchronize(ctx->ev1));
-  float ms = 0;
-  cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1);
-  (*out)->build_ms = ms;
+  b200reg_index* ix = nullptr;
+  TRY(buildIndex(ctx, ref, 0, cell, &ix));
+  if (!indexHeader(ctx, ix)) {   // this entry point reports device-side failures at once
+    indexRelease(ctx, ix);
+    return B200REG_E_INVALID_PARAM;
+  }
+  *out = ix;
   return B200REG_OK;
 }
 
 void b200reg_index_free(b200reg_ctx* ctx, b200reg_index* index) {
   if (!index) return;
-  if (ctx) { cudaSetDevice(ctx->device); cudaStreamSynchronize(ctx->stream); }
-  if (index->pts) devFree(ctx, index->pts);
-  if (index->nrm) devFree(ctx, index->nrm);
-  if (index->cellStart) devFree(ctx, index->cellStart);
-  delete index;
+  if (ctx) cudaSetDevice(ctx->device);
+  indexRelease(ctx, index);   // stream-ordered frees: kernels already enqueued on the ctx stream keep their memory
 }
 
 int64_t b200reg_index_size(const b200reg_index* index) { return index ? index->m : 0; }
-float b200reg_index_cell(const b200reg_index* index) { return index ? index->g.cell : 0.f; }
+float b200reg_index_cell(const b200reg_index* index) {
+  if (!index) return 0.f;
+  const IndexHeader* h = indexHeader(nullptr, index);
+  return h ? h->g.cell : 0.f;
+}
 
 }  // extern "C"

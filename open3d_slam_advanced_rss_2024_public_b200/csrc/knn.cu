@@ -80,11 +80,12 @@ __device__ __forceinline__ float lb3(float gx, float gy, float gz) {
 }
 
 template <int K>
-__global__ void __launch_bounds__(128) knnKernel(const float4* __restrict__ pts, const uint32_t* __restrict__ cellStart, GridDesc g,
+__global__ void __launch_bounds__(128) knnKernel(const float4* __restrict__ pts, const uint32_t* __restrict__ cellStart, const GridDesc* __restrict__ gp,
                                                  const float4* __restrict__ queries, int64_t n, int hasT, Rigid12 T, int k, float maxd2,
                                                  int allowSelf, int* __restrict__ outIds, float* __restrict__ outD2,
                                                  int* __restrict__ outPos, unsigned long long* __restrict__ visitCounter) {
   const int64_t qi = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const GridDesc g = *gp;   // device-derived grid (index.cu)
   unsigned visits = 0;
   if (qi < n) {
     const float4 q4 = queries[qi];
@@ -469,7 +470,7 @@ __device__ __forceinline__ void flushVisits(unsigned visits, unsigned farQ, unsi
 // take 32/G queries per grab from `work` (zeroed by the launcher) — query cost varies by an order of magnitude and far queries come
 // in runs, so no warp idles behind one.
 template <int G, bool SELFCHK>
-__global__ void __launch_bounds__(256, KNN1_LOOP_MINB) knn1GroupKernel(const float4* __restrict__ pts, const uint32_t* __restrict__ cellStart, GridDesc g,
+__global__ void __launch_bounds__(256, KNN1_LOOP_MINB) knn1GroupKernel(const float4* __restrict__ pts, const uint32_t* __restrict__ cellStart, const GridDesc* __restrict__ gp,
                                                                        const float4* __restrict__ queries, int64_t n, int hasT, Rigid12 T, float maxd2,
                                                                        int* __restrict__ outIds, float* __restrict__ outD2, int* outPos,
                                                                        unsigned long long* __restrict__ visitCounter, const int* seedPos,
@@ -477,6 +478,7 @@ __global__ void __launch_bounds__(256, KNN1_LOOP_MINB) knn1GroupKernel(const flo
   constexpr int LOG2G = (G == 8) ? 3 : 2;
   constexpr int QPW = 32 >> LOG2G;   // queries of one warp-wide call
   __shared__ unsigned sVisits, sFarQ, sTicket;
+  const GridDesc g = *gp;   // device-derived grid (index.cu)
   if (threadIdx.x == 0) { sVisits = 0; sFarQ = 0; sTicket = 0; }
   __syncthreads();   // all warps are at the start here: nobody waits on a straggler
   unsigned visits = 0, farQ = 0;
@@ -500,7 +502,7 @@ __device__ __forceinline__ void knn1LoopBody(const IcpDevParams* __restrict__ P,
   constexpr int LOG2G = (G == 8) ? 3 : 2;
   constexpr int QPW = 32 >> LOG2G;   // queries of one warp-wide call
   constexpr int CHUNK = QPW;         // queries a warp takes from the work counter at a time
-  const GridDesc g = P->g;
+  const GridDesc g = *P->gp;
   const float4* pts = P->pts;
   const uint32_t* cellStart = P->cellStart;
   const float4* queries = P->reading;
@@ -606,7 +608,7 @@ __device__ __forceinline__ void scanList(const float4* __restrict__ pts, uint32_
 }
 
 template <int W, bool SELFCHK>
-__global__ void __launch_bounds__(256) knnListKernel(const float4* __restrict__ pts, const uint32_t* __restrict__ cellStart, GridDesc g,
+__global__ void __launch_bounds__(256) knnListKernel(const float4* __restrict__ pts, const uint32_t* __restrict__ cellStart, const GridDesc* __restrict__ gp,
                                                      const float4* __restrict__ queries, int64_t n, int hasT, Rigid12 T, int k, float maxd2,
                                                      int* __restrict__ outIds, float* __restrict__ outD2, int* __restrict__ outPos,
                                                      unsigned long long* __restrict__ visitCounter) {
@@ -614,6 +616,7 @@ __global__ void __launch_bounds__(256) knnListKernel(const float4* __restrict__ 
   const int lane = threadIdx.x & 31, l = lane & (W - 1), gbase = lane & (32 - W);
   const unsigned gmask = (W == 32) ? 0xffffffffu : (((1u << (W & 31)) - 1u) << gbase);
   const int64_t slot = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) / W;
+  const GridDesc g = *gp;   // device-derived grid (index.cu)
   unsigned visits = 0;
   if (slot < n) {
     float4 q4;
@@ -735,9 +738,9 @@ void launchKnnList(b200reg_ctx* ctx, const b200reg_index* ix, const float4* q, i
                    int allowSelf, int* ids, float* d2, int* pos, unsigned long long* visits) {
   const int blocks = divUp(n * W, 256);
   if (allowSelf)
-    knnListKernel<W, false><<<blocks, 256, 0, ctx->stream>>>(ix->pts, ix->cellStart, ix->g, q, n, hasT, T, k, maxd2, ids, d2, pos, visits);
+    knnListKernel<W, false><<<blocks, 256, 0, ctx->stream>>>(ix->pts, ix->cellStart, &ix->dHdr->g, q, n, hasT, T, k, maxd2, ids, d2, pos, visits);
   else
-    knnListKernel<W, true><<<blocks, 256, 0, ctx->stream>>>(ix->pts, ix->cellStart, ix->g, q, n, hasT, T, k, maxd2, ids, d2, pos, visits);
+    knnListKernel<W, true><<<blocks, 256, 0, ctx->stream>>>(ix->pts, ix->cellStart, &ix->dHdr->g, q, n, hasT, T, k, maxd2, ids, d2, pos, visits);
 }
 
 template <int G>
@@ -745,15 +748,15 @@ void launchKnn1(b200reg_ctx* ctx, const b200reg_index* ix, const float4* q, int6
   const int blocks = (int)std::min<int64_t>(divUp(n * G, 256), (int64_t)KNN1_LOOP_MINB * ctx->sm_count);   // resident grid
   unsigned long long* work = visits + 2;   // dstate[2], zeroed by runKnn
   if (allowSelf)
-    knn1GroupKernel<G, false><<<blocks, 256, 0, ctx->stream>>>(ix->pts, ix->cellStart, ix->g, q, n, hasT, T, maxd2, ids, d2, pos, visits, seed, work);
+    knn1GroupKernel<G, false><<<blocks, 256, 0, ctx->stream>>>(ix->pts, ix->cellStart, &ix->dHdr->g, q, n, hasT, T, maxd2, ids, d2, pos, visits, seed, work);
   else
-    knn1GroupKernel<G, true><<<blocks, 256, 0, ctx->stream>>>(ix->pts, ix->cellStart, ix->g, q, n, hasT, T, maxd2, ids, d2, pos, visits, seed, work);
+    knn1GroupKernel<G, true><<<blocks, 256, 0, ctx->stream>>>(ix->pts, ix->cellStart, &ix->dHdr->g, q, n, hasT, T, maxd2, ids, d2, pos, visits, seed, work);
 }
 
 template <int K>
 void launchKnn(b200reg_ctx* ctx, const b200reg_index* ix, const float4* q, int64_t n, int hasT, const Rigid12& T, int k, float maxd2,
                int allowSelf, int* ids, float* d2, int* pos, unsigned long long* visits) {
-  knnKernel<K><<<divUp(n, 128), 128, 0, ctx->stream>>>(ix->pts, ix->cellStart, ix->g, q, n, hasT, T, k, maxd2, allowSelf, ids, d2, pos, visits);
+  knnKernel<K><<<divUp(n, 128), 128, 0, ctx->stream>>>(ix->pts, ix->cellStart, &ix->dHdr->g, q, n, hasT, T, k, maxd2, allowSelf, ids, d2, pos, visits);
 }
 
 }  // namespace

@@ -15,9 +15,6 @@
 
 int runKnn(b200reg_ctx* ctx, const b200reg_index* ix, const float4* queries, int64_t n, const float* T, int k, float maxDist, int allowSelf,
            int seeded);
-int cloudStats(b200reg_ctx* ctx, const b200reg_cloud* c, double sum[3], float mn[3], float mx[3]);
-int buildIndex(b200reg_ctx* ctx, const b200reg_cloud* ref, const float mean[3], const float bbMin[3], const float bbMax[3], float cell,
-               b200reg_index** out);
 
 namespace {
 
@@ -230,11 +227,7 @@ extern "C" int32_t b200reg_information_matrix(b200reg_ctx* ctx, const b200reg_cl
   toF32MovedKernel<<<divUp(nS, 256), 256, 0, ctx->stream>>>(source->xyz, nS, dT, src.xyz);
   toF32MovedKernel<<<divUp(nT, 256), 256, 0, ctx->stream>>>(target->xyz, nT, nullptr, tgt.xyz);
   ctx->launches += 2;
-  double sum[3];
-  float mn[3], mx[3];
-  int code = cloudStats(ctx, &tgt, sum, mn, mx);
-  const float zero[3] = {0.f, 0.f, 0.f};
-  if (code == B200REG_OK) code = buildIndex(ctx, &tgt, zero, mn, mx, 0.f, &ix);
+  int code = buildIndex(ctx, &tgt, 0, 0.f, &ix);
   // KDTreeFlann::SearchHybrid(point, max_correspondence_distance, 1): the nearest target point with d2 < r^2
   if (code == B200REG_OK) code = runKnn(ctx, ix, src.xyz, nS, nullptr, 1, (float)max_correspondence_distance, 1, 0);
   const int blocks = (int)fmin((double)(2 * ctx->sm_count), (double)divUp(nS, 256));
@@ -245,8 +238,10 @@ extern "C" int32_t b200reg_information_matrix(b200reg_ctx* ctx, const b200reg_cl
   ctx->launches++;
   cudaMemcpyAsync(ctx->pinned, ctx->partials.p, sizeof(double) * INFO_MOM * (size_t)blocks, cudaMemcpyDeviceToHost, ctx->stream);
   e = cudaStreamSynchronize(ctx->stream);
+  const bool indexOk = (e != cudaSuccess) || indexHeader(ctx, ix) != nullptr;
   cleanup();
   if (e != cudaSuccess) return setErr(ctx, B200REG_E_CUDA, "information_matrix: %s", cudaGetErrorString(e));
+  if (!indexOk) return setErr(ctx, B200REG_E_INVALID_PARAM, "information_matrix: non-finite coordinates in the target cloud");
   double m[INFO_MOM] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
   const double* h = (const double*)ctx->pinned;
   for (int b = 0; b < blocks; ++b)

@@ -11,9 +11,6 @@
 
 int runKnn(b200reg_ctx* ctx, const b200reg_index* ix, const float4* queries, int64_t n, const float* T, int k, float maxDist, int allowSelf,
            int seeded);
-int cloudStats(b200reg_ctx* ctx, const b200reg_cloud* c, double sum[3], float mn[3], float mx[3]);
-int buildIndex(b200reg_ctx* ctx, const b200reg_cloud* ref, const float mean[3], const float bbMin[3], const float bbMax[3], float cell,
-               b200reg_index** out);
 
 namespace {
 
@@ -184,12 +181,8 @@ extern "C" int32_t b200reg_surface_normals(b200reg_ctx* ctx, b200reg_cloud* inou
   if (n == 0) return B200REG_OK;
   CUDA_TRY(ctx, cudaSetDevice(ctx->device));
   // own matcher over the cloud itself (SurfaceNormal.cpp:170-179): un-centred index
-  double sum[3];
-  float mn[3], mx[3];
-  TRY(cloudStats(ctx, inout, sum, mn, mx));
-  const float zero[3] = {0.f, 0.f, 0.f};
   b200reg_index* ix = nullptr;
-  TRY(buildIndex(ctx, inout, zero, mn, mx, 0.f, &ix));
+  TRY(buildIndex(ctx, inout, 0, 0.f, &ix));
   // the list kernel walks the cloud in the index's sorted order (null queries); the one-thread kernel takes it as it lies
   const float4* qs = (ctx->knnLanes == 1 || knn > 32) ? inout->xyz : nullptr;
   int st = runKnn(ctx, ix, qs, n, nullptr, knn, max_dist, 1, 0);
@@ -216,8 +209,10 @@ extern "C" int32_t b200reg_surface_normals(b200reg_ctx* ctx, b200reg_cloud* inou
   if (e == cudaSuccess && lin_plan_curv_out) e = cudaMemcpyAsync(lin_plan_curv_out, dLpc, sizeof(float) * 3 * (size_t)n, cudaMemcpyDeviceToHost, ctx->stream);
   if (e == cudaSuccess) e = cudaMemcpyAsync(ctx->pinned, dDeg, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream);
   if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+  const bool indexOk = (e != cudaSuccess) || indexHeader(ctx, ix) != nullptr;   // non-finite coordinates: the header carries the verdict
   b200reg_index_free(ctx, ix);
   if (e != cudaSuccess) return setErr(ctx, B200REG_E_CUDA, "surface_normals: %s", cudaGetErrorString(e));
+  if (!indexOk) return setErr(ctx, B200REG_E_INVALID_PARAM, "SurfaceNormalDataPointsFilter: non-finite coordinates in the cloud");
   if (degenerate_count) *degenerate_count = *(const int*)ctx->pinned;
   return B200REG_OK;
 }

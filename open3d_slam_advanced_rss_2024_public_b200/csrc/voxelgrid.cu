@@ -12,7 +12,6 @@
 
 #include "common.cuh"
 
-int cloudStats(b200reg_ctx* ctx, const b200reg_cloud* c, double sum[3], float mn[3], float mx[3]);
 
 namespace {
 

@@ -596,17 +596,19 @@ bool PointMatcher<T>::ICP::initReference(const DataPoints& referenceIn) {   // I
     fi->ctx = contextFor(km->device);
     b200reg_icp_config& c = fi->cfg;
     c.knn = km->knn; c.max_dist = km->maxDist; c.epsilon = km->epsilon; c.cell = km->cell;
-    c.trim_ratio = -1.f; c.max_angle = -1.f; c.max_iter = 0; c.smooth_length = -1; c.bound_rot = -1.f; c.bound_trans = -1.f;
+    c.trim_ratio = -1.f; c.max_angle = -1.f; c.max_iter = -1; c.smooth_length = -1; c.bound_rot = -1.f; c.bound_trans = -1.f;
     for (auto& f : this->outlierFilters) {
       if (auto* t = dynamic_cast<CudaTrimmedDistOutlierFilter*>(f.get())) c.trim_ratio = t->ratio;
       if (auto* a = dynamic_cast<CudaSurfaceNormalOutlierFilter*>(f.get())) c.max_angle = a->maxAngle;
     }
     auto* em = static_cast<CudaPointToPlaneErrorMinimizer*>(this->errorMinimizer.get());
     c.force2D = em->force2D; c.force4DOF = em->force4DOF;
+    int slot = 0;   // the device loop evaluates the checkers in the chain's order (ICP.cpp:437-446)
+    c.checker_order[0] = c.checker_order[1] = c.checker_order[2] = 0;
     for (auto& ch : this->transformationCheckers) {
-      if (auto* x = dynamic_cast<CounterTransformationChecker*>(ch.get())) c.max_iter = (int)x->maxIterationCount;
-      if (auto* x = dynamic_cast<DifferentialTransformationChecker*>(ch.get())) { c.min_diff_rot = x->minDiffRotErr; c.min_diff_trans = x->minDiffTransErr; c.smooth_length = (int)x->smoothLength; }
-      if (auto* x = dynamic_cast<BoundTransformationChecker*>(ch.get())) { c.bound_rot = x->maxRotationNorm; c.bound_trans = x->maxTranslationNorm; }
+      if (auto* x = dynamic_cast<CounterTransformationChecker*>(ch.get())) { c.max_iter = (int)std::min<unsigned>(x->maxIterationCount, 2147483647u); c.checker_order[slot++] = B200REG_CHECKER_COUNTER; }
+      if (auto* x = dynamic_cast<DifferentialTransformationChecker*>(ch.get())) { c.min_diff_rot = x->minDiffRotErr; c.min_diff_trans = x->minDiffTransErr; c.smooth_length = (int)x->smoothLength; c.checker_order[slot++] = B200REG_CHECKER_DIFFERENTIAL; }
+      if (auto* x = dynamic_cast<BoundTransformationChecker*>(ch.get())) { c.bound_rot = x->maxRotationNorm; c.bound_trans = x->maxTranslationNorm; c.checker_order[slot++] = B200REG_CHECKER_BOUND; }
     }
     int32_t st = b200reg_icp_create(fi->ctx, &c, &fi->icp);
     if (st != B200REG_OK) throwStatus(fi->ctx, st);

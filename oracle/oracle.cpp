@@ -825,7 +825,7 @@ struct Checkers {
       const float tr = std::sqrt(dx * dx + dy * dy + dz * dz);
       if (rot > cfg.bound_rot || tr > cfg.bound_trans) status = ORC_E_CONVERGENCE;
     }
-    if (cfg.max_iter > 0 && status == ORC_OK) {          // Counter::check :64-76 (throws, caught at ICP.cpp:441-445)
+    if (cfg.max_iter >= 0 && status == ORC_OK) {          // Counter::check :64-76 (throws, caught at ICP.cpp:441-445)
       ++counter;
       if (counter >= cfg.max_iter) { iterate = false; maxIterReached = true; }
     }

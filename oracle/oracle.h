@@ -34,7 +34,7 @@ typedef struct orc_icp_config {
   float   max_angle;      /* SurfaceNormalOutlierFilter maxAngle; < 0 : filter absent */
   int32_t force2D;        /* PointToPlane.h:74 */
   int32_t force4DOF;      /* PointToPlane.h:75 */
-  int32_t max_iter;       /* CounterTransformationChecker; <= 0 : absent */
+  int32_t max_iter;       /* CounterTransformationChecker; < 0 : absent (0 stops after the first iteration, like 1) */
   float   min_diff_rot;   /* DifferentialTransformationChecker */
   float   min_diff_trans;
   int32_t smooth_length;  /* < 0 : checker absent */

@@ -23,7 +23,7 @@ def test_header_symbols_are_exported_and_bound():
     for s in syms:
         assert hasattr(L, s), f"libb200reg.so does not export {s}"
     assert sorted(capi.SYMBOLS) == syms, set(capi.SYMBOLS) ^ set(syms)
-    assert capi.lib().b200reg_abi_version() == 1
+    assert capi.lib().b200reg_abi_version() == 2
 
 
 def test_no_cpu_fallback_without_gpu():

@@ -1,0 +1,286 @@
+"""GPU parity tests added in round 2: the lanes of the batched registration, the device-derived index (no host round trip),
+the checker semantics the advisor flagged, and the BASELINE configurations at their FULL sizes.
+
+Everything goes through the C ABI (ctypes) and is compared with the CPU oracle on the same seeded inputs; bars:
+bit-exact for indices / distances / counts / tau, 1e-5 m / 1e-5 rad for transforms (north star)."""
+import numpy as np
+import pytest
+
+import scenes
+
+pytestmark = pytest.mark.gpu
+
+TOL_T, TOL_R = 1e-5, 1e-5
+
+
+def rot_angle(Ra, Rb):
+    c = (np.trace(Ra.astype(np.float64).T @ Rb.astype(np.float64)) - 1.0) / 2.0
+    return float(np.arccos(np.clip(c, -1.0, 1.0)))
+
+
+def assert_same_T(Ta, Tb, tol_t=TOL_T, tol_r=TOL_R):
+    dt = float(np.abs(Ta[:3, 3].astype(np.float64) - Tb[:3, 3].astype(np.float64)).max())
+    dr = float(np.linalg.norm(Ta[:3, :3].astype(np.float64) - Tb[:3, :3].astype(np.float64)) / np.sqrt(2.0))
+    assert dt <= tol_t and dr <= tol_r, (dt, dr)
+
+
+def _pairs(oracle, n_pairs, seed0, m=40_000, beams=16, az=256):
+    out = []
+    for i in range(n_pairs):
+        c = scenes.config2(m=m + 3_000 * i, n_beams=beams, n_az=az + 16 * i, scene_seed=seed0 + i, size=(60.0, 60.0, 8.0), n_boxes=20, n_cyl=12)
+        out.append(dict(ref=oracle.feat4(c["map_xyz"]), rn=np.ascontiguousarray(c["map_nrm"], dtype=np.float32), q=oracle.feat4(c["scan"]),
+                        Ti=c["T_init"].astype(np.float32)))
+    return out
+
+
+@pytest.mark.parametrize("lanes", [1, 2, 3, 4])
+def test_batch_lanes_bit_identical_to_serial(ctx, oracle, lanes):
+    """b200reg_batch with R lanes in flight: every pair's transform, iteration count, tau and kept count are those of the
+    stand-alone b200reg_icp_set_reference + b200reg_icp_register, bit for bit — for device clouds and for host clouds
+    (uploads inside the pipeline) — and equal the oracle.  A failing pair in the middle keeps T_init and its status."""
+    from open3d_slam_advanced_rss_2024_public_b200 import capi
+    kw = dict(knn=1, max_dist=1.0, trim_ratio=0.8, max_iter=40)
+    P = _pairs(oracle, 7, 4100)
+    far = np.eye(4, dtype=np.float32)
+    far[:3, 3] = 1000.0
+    P.insert(3, dict(ref=P[0]["ref"], rn=P[0]["rn"], q=P[0]["q"], Ti=far))   # no point within maxDist: ConvergenceError
+    serial = []
+    for p in P:
+        icp = capi.ICP(ctx, **kw)
+        icp.set_reference(ctx.upload(p["ref"], p["rn"]))
+        try:
+            T, st = icp.register(ctx.upload(p["q"]), p["Ti"])
+            serial.append((T, st.iterations, st.last_tau, st.kept_last, 0))
+        except capi.ConvergenceError:
+            serial.append((p["Ti"], 0, 0.0, 0, capi.E_NOT_CONVERGED))
+        icp.close()
+    assert [s[4] for s in serial] == [0, 0, 0, capi.E_NOT_CONVERGED, 0, 0, 0, 0]
+    b = capi.Batch(ctx, lanes=lanes, **kw)
+    assert b.lanes == lanes
+    refs = [ctx.upload(p["ref"], p["rn"]) for p in P]
+    reads = [ctx.upload(p["q"]) for p in P]
+    Tis = np.stack([p["Ti"] for p in P])
+    for rep in range(2):   # the second call reuses the lanes' graphs, clouds and scratch
+        T, stats, status = b.register(refs, reads, Tis)
+        Th, stats_h, status_h = b.register_host(b.host_clouds([(p["ref"], p["rn"]) for p in P]), b.host_clouds([(p["q"], None) for p in P]), Tis)
+        for i, s in enumerate(serial):
+            assert status[i] == s[4] and status_h[i] == s[4]
+            assert np.array_equal(T[i], s[0]) and np.array_equal(Th[i], s[0]), i
+            if s[4] == 0:
+                assert stats[i].iterations == s[1] == stats_h[i].iterations
+                assert np.float32(stats[i].last_tau).tobytes() == np.float32(s[2]).tobytes() == np.float32(stats_h[i].last_tau).tobytes()
+                assert stats[i].kept_last == s[3] == stats_h[i].kept_last
+    b.close()
+    for i in (0, 5):
+        p = P[i]
+        code, T_o, st_o = oracle.icp(oracle.icp_config(precision=oracle.ORC_MIXED, nthreads=8, **kw), p["ref"], p["rn"], p["q"], None, p["Ti"])
+        assert code == 0 and st_o.iterations == serial[i][1]
+        assert_same_T(serial[i][0], T_o)
+    # the one-shot form (temporary batch object)
+    T1, _, status1 = capi.register_batch(ctx, capi.icp_config(**kw), refs, reads, Tis)
+    assert all(np.array_equal(T1[i], serial[i][0]) for i in range(len(P))) and list(status1) == [s[4] for s in serial]
+
+
+def test_batch_empty_and_errors(ctx, oracle):
+    from open3d_slam_advanced_rss_2024_public_b200 import capi
+    kw = dict(knn=1, max_dist=1.0, trim_ratio=0.8, max_iter=40)
+    b = capi.Batch(ctx, lanes=2, **kw)
+    T, stats, status = b.register([], [], np.zeros((0, 4, 4), np.float32))
+    assert T.shape == (0, 4, 4)
+    p = _pairs(oracle, 1, 4200)[0]
+    empty = ctx.upload(np.zeros((0, 4), np.float32))
+    T, stats, status = b.register([ctx.upload(p["ref"], p["rn"]), empty, ctx.upload(p["ref"])], [empty, ctx.upload(p["q"]), ctx.upload(p["q"])],
+                                  np.stack([p["Ti"]] * 3))
+    assert list(status) == [capi.E_NO_POINTS, capi.E_NO_POINTS, capi.E_INVALID_FIELD]   # empty reading / empty reference / no normals
+    assert all(np.array_equal(T[i], p["Ti"]) for i in range(3))
+    b.close()
+    with pytest.raises(capi.InvalidParameter):
+        capi.Batch(ctx, lanes=2, knn=3)
+
+
+def test_index_nonfinite_reference_is_an_error_not_a_hang(ctx, oracle):
+    """a +-inf coordinate (a LiDAR 'no return') used to spin buildIndex forever; now the device-derived header
+    carries a status and every entry point that needs the index reports InvalidParameter."""
+    from open3d_slam_advanced_rss_2024_public_b200 import capi
+    p = _pairs(oracle, 1, 4300)[0]
+    for bad in (np.inf, -np.inf, np.nan):
+        ref = p["ref"].copy()
+        ref[1234, 1] = bad
+        with pytest.raises(capi.InvalidParameter):
+            ctx.build_index(ctx.upload(ref, p["rn"]))
+        icp = capi.ICP(ctx, knn=1, max_dist=1.0, trim_ratio=0.8)
+        icp.set_reference(ctx.upload(ref, p["rn"]))     # enqueue only: the error surfaces at the first call that needs the result
+        with pytest.raises(capi.InvalidParameter):
+            icp.register(ctx.upload(p["q"]), p["Ti"])
+        icp.close()
+        c = ctx.upload(ref)
+        with pytest.raises(capi.InvalidParameter):
+            c.surface_normals(10, max_dist=1.0)
+    # the context is still healthy
+    ix = ctx.build_index(ctx.upload(p["ref"], p["rn"]))
+    assert ix.size == p["ref"].shape[0] and ix.cell > 0
+
+
+@pytest.mark.parametrize("cell", [1e-5, 1e-3, 0.02])
+def test_index_directory_cap_grows_the_cell_results_unchanged(ctx, oracle, golden, cell):
+    """A requested cell that would need more directory cells than max(8 M, 65536) is grown on the device; the search is exact for
+    any cell, so ids and distances still equal the oracle's k-d tree."""
+    car = golden["car"]
+    ref, q = oracle.feat4(car["ref_xyz"]), oracle.feat4(car["data_xyz"])
+    ix = ctx.build_index(ctx.upload(ref), cell=cell)
+    assert ix.cell > cell
+    ids_g, d2_g, _ = ctx.knn(ix, ctx.upload(q), k=3, max_dist=0.7)
+    ids_o, d2_o, _ = oracle.KdTree(ref).knn(q, k=3, max_dist=0.7, nthreads=4)
+    assert np.array_equal(ids_g, ids_o) and np.array_equal(d2_g.view(np.uint32), d2_o.view(np.uint32))
+
+
+def test_max_iteration_count_zero_and_absent(ctx, oracle):
+    """maxIterationCount 0 is legal in the reference and stops after ONE iteration (counter >= limit); negative = no
+    Counter checker.  Device loop, host loop and oracle agree."""
+    from open3d_slam_advanced_rss_2024_public_b200 import capi
+    p = _pairs(oracle, 1, 4400)[0]
+    ref, q = ctx.upload(p["ref"], p["rn"]), ctx.upload(p["q"])
+    for mi, want in ((0, 1), (1, 1), (2, 2)):
+        kw = dict(knn=1, max_dist=1.0, trim_ratio=0.8, max_iter=mi, smooth_length=-1)
+        icp = capi.ICP(ctx, **kw)
+        icp.set_reference(ref)
+        T, st = icp.register(q, p["Ti"])
+        assert st.iterations == want and st.max_iterations_reached == 1
+        code, T_o, st_o = oracle.icp(oracle.icp_config(precision=oracle.ORC_MIXED, nthreads=4, **kw), p["ref"], p["rn"], p["q"], None, p["Ti"])
+        assert code == 0 and st_o.iterations == want
+        assert_same_T(T, T_o)
+        ctx.set_profiling(True)      # host-driven loop
+        T_h, st_h = icp.register(q, p["Ti"])
+        ctx.set_profiling(False)
+        ctx.profile_read()
+        assert st_h.iterations == want and np.abs(T_h - T).max() <= 2e-6
+        icp.close()
+    kw = dict(knn=1, max_dist=1.0, trim_ratio=0.8, max_iter=-1, smooth_length=3, min_diff_rot=1e-3, min_diff_trans=1e-2)
+    icp = capi.ICP(ctx, **kw)
+    icp.set_reference(ref)
+    T, st = icp.register(q, p["Ti"])
+    code, T_o, st_o = oracle.icp(oracle.icp_config(precision=oracle.ORC_MIXED, nthreads=4, **kw), p["ref"], p["rn"], p["q"], None, p["Ti"])
+    assert code == 0 and st.iterations == st_o.iterations and st.max_iterations_reached == 0
+    assert_same_T(T, T_o)
+    icp.close()
+
+
+def test_checker_order_counter_first_skips_bound(ctx, oracle):
+    """the reference evaluates the checkers in chain order and Counter's throw skips the ones behind it
+    (ICP.cpp:437-446).  With Counter first, the last allowed iteration returns normally even where Bound would trip."""
+    from open3d_slam_advanced_rss_2024_public_b200 import capi
+    p = _pairs(oracle, 1, 4500)[0]
+    ref, q = ctx.upload(p["ref"], p["rn"]), ctx.upload(p["q"])
+    base = dict(knn=1, max_dist=1.0, trim_ratio=0.8, max_iter=1, smooth_length=-1, bound_rot=1e-9, bound_trans=1e-9)
+    icp = capi.ICP(ctx, checker_order=[capi.CHECKER_COUNTER, capi.CHECKER_BOUND], **base)
+    icp.set_reference(ref)
+    T, st = icp.register(q, p["Ti"])
+    assert st.iterations == 1 and st.max_iterations_reached == 1
+    icp.close()
+    for order in ([capi.CHECKER_BOUND, capi.CHECKER_COUNTER], [0, 0, 0]):
+        icp = capi.ICP(ctx, checker_order=order, **base)
+        icp.set_reference(ref)
+        with pytest.raises(capi.ConvergenceError, match="limit out of bounds"):
+            icp.register(q, p["Ti"])
+        ctx.set_profiling(True)
+        with pytest.raises(capi.ConvergenceError, match="limit out of bounds"):
+            icp.register(q, p["Ti"])
+        ctx.set_profiling(False)
+        ctx.profile_read()
+        icp.close()
+
+
+def test_cloud_update_without_normals_drops_the_old_ones(ctx, oracle):
+    """b200reg_cloud_update_f32(normals = NULL) on a cloud that had normals must not leave the previous scan's in place
+    (the SurfaceNormal outlier gate would run against stale data; the reference skips the filter without the descriptor)."""
+    from open3d_slam_advanced_rss_2024_public_b200 import capi
+    p = _pairs(oracle, 1, 4600)[0]
+    kw = dict(knn=1, max_dist=1.0, trim_ratio=0.8, max_angle=0.5, max_iter=40)
+    icp = capi.ICP(ctx, **kw)
+    icp.set_reference(ctx.upload(p["ref"], p["rn"]))
+    T_plain, st_plain = icp.register(ctx.upload(p["q"]), p["Ti"])
+    rng = np.random.default_rng(5)
+    junk = rng.normal(size=(p["q"].shape[0], 3)).astype(np.float32)
+    junk /= np.linalg.norm(junk, axis=1, keepdims=True)
+    c = ctx.upload(p["q"], junk)
+    assert c.has_normals
+    c.update(p["q"])                     # same points, no normals
+    assert not c.has_normals
+    T_upd, st_upd = icp.register(c, p["Ti"])
+    assert np.array_equal(T_upd, T_plain) and st_upd.iterations == st_plain.iterations
+    icp.close()
+
+
+# ---------------------------------------------------------------------------------------------------------------------------
+# BASELINE configurations at full size
+# ---------------------------------------------------------------------------------------------------------------------------
+@pytest.fixture(scope="module")
+def config2_full():
+    return scenes.config2()      # 5 000 000-point map, 128 x 1024 scan: ~8 s of numpy
+
+
+def test_config2_full_size_matches_oracle(ctx, oracle, config2_full):
+    """BASELINE config #2 at 5 M x 131 072 (the bench workload): iteration count, kept pairs and tau bit pattern equal the oracle's
+    mixed-precision lane, the transform within 1e-5 m / 1e-5 rad; batch lanes and host loop give the same answer."""
+    from open3d_slam_advanced_rss_2024_public_b200 import capi
+    c = config2_full
+    ref, rn, q = oracle.feat4(c["map_xyz"]), c["map_nrm"].astype(np.float32), oracle.feat4(c["scan"])
+    Ti = c["T_init"].astype(np.float32)
+    kw = dict(knn=1, max_dist=1.0, trim_ratio=0.8, max_iter=40, min_diff_rot=1e-3, min_diff_trans=1e-2, smooth_length=3)
+    icp = capi.ICP(ctx, **kw)
+    cref, cq = ctx.upload(ref, rn), ctx.upload(q)
+    icp.set_reference(cref)
+    T_g, st = icp.register(cq, Ti)
+    code, T_o, st_o = oracle.icp(oracle.icp_config(precision=oracle.ORC_MIXED, nthreads=16, **kw), ref, rn, q, None, Ti)
+    assert code == 0
+    assert st.iterations == st_o.iterations
+    assert st.kept_last == st_o.kept_last
+    assert np.float32(st.last_tau).tobytes() == np.float32(st_o.last_tau).tobytes()
+    assert_same_T(T_g, T_o)
+    E = np.linalg.inv(c["T_true"]) @ T_g.astype(np.float64)
+    assert np.abs(E[:3, 3]).max() < 0.01 and rot_angle(np.eye(3), E[:3, :3]) < 1e-3   # and it is the right pose
+    b = capi.Batch(ctx, lanes=2, **kw)
+    Tb, sb, status = b.register([cref, cref, cref], [cq, cq, cq], np.stack([Ti] * 3))
+    assert not status.any() and all(np.array_equal(Tb[i], T_g) for i in range(3))
+    b.close()
+    icp.close()
+
+
+def test_config2_full_size_knn_sample_bit_exact(ctx, oracle, config2_full):
+    """k = 1 and k = 20 against the 5 M-point map: ids and d2 bit patterns of every scan point equal the oracle's k-d tree."""
+    c = config2_full
+    ref, q = oracle.feat4(c["map_xyz"]), oracle.feat4((c["scan"] @ c["T_init"][:3, :3].T + c["T_init"][:3, 3]))
+    ix = ctx.build_index(ctx.upload(ref))
+    tree = oracle.KdTree(ref)
+    for k, md, sub in ((1, 1.0, 1), (20, 1.0, 16)):
+        qq = q[::sub]
+        ids_g, d2_g, _ = ctx.knn(ix, ctx.upload(qq), k=k, max_dist=md)
+        ids_o, d2_o, _ = tree.knn(qq, k=k, max_dist=md, nthreads=16)
+        assert np.array_equal(ids_g, ids_o)
+        assert np.array_equal(d2_g.view(np.uint32), d2_o.view(np.uint32))
+
+
+def test_config5_large_map_sampled_brute_force(ctx, oracle):
+    """BASELINE config #5 shape at 8 M points (the 50 M run is profiles/config5_stress.py): a sample of scan queries is compared bit
+    for bit with BRUTE FORCE over the whole map (no tree, no grid: independent of both search structures), map points queried
+    against their own index return themselves at distance 0, and k = 20 rows of the sample equal brute force too."""
+    m = 8_000_000
+    side = float(np.sqrt(m / 50e6) * 420.0)
+    scene = scenes.Scene(5001, size=(side, side, 12.0), n_boxes=int(400 * m / 50e6) + 20, n_cyl=int(300 * m / 50e6) + 10)
+    map_xyz, _ = scene.make_map(m, 5002)
+    ref = oracle.feat4(map_xyz)
+    T_true = scenes.rigid(scenes.rot_axis_angle([0, 0, 1], 0.3), [side * 0.4, side * 0.5, 1.8])
+    scan = scenes.lidar_scan(scene, T_true, 64, 512, 0.01, 5100)
+    q = oracle.feat4(scan @ T_true[:3, :3].T + T_true[:3, 3])
+    ix = ctx.build_index(ctx.upload(ref))
+    rng = np.random.default_rng(7)
+    sel = rng.choice(q.shape[0], 256, replace=False)
+    qs = q[sel]
+    for k in (1, 20):
+        ids_g, d2_g, _ = ctx.knn(ix, ctx.upload(qs), k=k, max_dist=1.0)
+        ids_b, d2_b = oracle.knn_brute(ref, qs, k=k, max_dist=1.0)
+        assert np.array_equal(ids_g, ids_b)
+        assert np.array_equal(d2_g.view(np.uint32), d2_b.view(np.uint32))
+    own = rng.choice(m, 200_000, replace=False)
+    ids_g, d2_g, _ = ctx.knn(ix, ctx.upload(ref[own]), k=1, max_dist=0.5)
+    assert np.array_equal(ids_g[:, 0], own.astype(np.int32)) and not d2_g.any()
