@@ -233,11 +233,14 @@ typedef struct b200reg_batch b200reg_batch;
 int32_t b200reg_batch_create(b200reg_ctx* ctx, const b200reg_icp_config* cfg, int32_t lanes, b200reg_batch** out);
 void    b200reg_batch_destroy(b200reg_batch* batch);
 int32_t b200reg_batch_lanes(const b200reg_batch* batch);
-/* clouds already on the device (created on `ctx`) */
+/* ICP::initReference ONCE for the whole batch: every pair whose reference is not given (refs == NULL below) registers its reading
+ * against this index — many scans, or many initial guesses of one scan, against one map (re-localisation, multi-sequence mapping). */
+int32_t b200reg_batch_set_reference(b200reg_batch* batch, const b200reg_cloud* reference);
+/* clouds already on the device (created on `ctx`); refs == NULL: the reference of b200reg_batch_set_reference for every pair */
 int32_t b200reg_batch_register(b200reg_batch* batch, int32_t n, const b200reg_cloud* const* refs, const b200reg_cloud* const* readings,
                                const float* T_init, float* T_out, b200reg_icp_stats* stats, int32_t* status);
-/* HOST clouds (layout of b200reg_cloud_upload_f32; normals nullable for readings, required for references): the uploads are part of
- * the pipeline.  The buffers must stay valid until the call returns; pinned memory lets the copies overlap the other lanes' kernels. */
+/* HOST clouds (layout of b200reg_cloud_upload_f32; normals nullable for readings, required for references; refs == NULL as above):
+ * the uploads are part of the pipeline.  The buffers must stay valid until the call returns; pinned memory lets the copies overlap the other lanes' kernels. */
 typedef struct b200reg_host_cloud {
   const float* feat;
   int32_t feat_stride;

@@ -156,6 +156,7 @@ SYMBOLS = {
     "b200reg_batch_create": (C.c_int32, [_VP, C.POINTER(IcpConfig), C.c_int32, C.POINTER(_VP)]),
     "b200reg_batch_destroy": (None, [_VP]),
     "b200reg_batch_lanes": (C.c_int32, [_VP]),
+    "b200reg_batch_set_reference": (C.c_int32, [_VP, _VP]),
     "b200reg_batch_register": (C.c_int32, [_VP, C.c_int32, _VP, _VP, _VP, _VP, _VP, _VP]),
     "b200reg_batch_register_host": (C.c_int32, [_VP, C.c_int32, _VP, _VP, _VP, _VP, _VP, _VP]),
     "b200reg_icp_index": (_VP, [_VP]),
@@ -632,14 +633,19 @@ class Batch:
         Ti = np.ascontiguousarray(np.asarray(T_init, dtype=np.float32).reshape(n, 16))
         return Ti, np.zeros((n, 16), dtype=np.float32), (IcpStats * max(n, 1))(), np.zeros(max(n, 1), dtype=np.int32)
 
+    def set_reference(self, cloud):
+        """One reference for every pair registered with refs=None."""
+        self.ctx.check(lib().b200reg_batch_set_reference(self.h, cloud.h))
+
     def register(self, refs, readings, T_init):
-        """refs / readings: lists of device Clouds of this ctx.  Returns (T n x 4 x 4, [IcpStats], status int32[n])."""
-        n = len(refs)
-        assert len(readings) == n
+        """refs / readings: lists of device Clouds of this ctx (refs=None: the shared reference).
+        Returns (T n x 4 x 4, [IcpStats], status int32[n])."""
+        n = len(readings)
+        assert refs is None or len(refs) == n
         Ti, To, stats, status = self._out(n, T_init)
-        rh = (_VP * max(n, 1))(*[c.h.value if isinstance(c.h, _VP) else c.h for c in refs])
+        rh = None if refs is None else C.cast((_VP * max(n, 1))(*[c.h.value if isinstance(c.h, _VP) else c.h for c in refs]), _VP)
         qh = (_VP * max(n, 1))(*[c.h.value if isinstance(c.h, _VP) else c.h for c in readings])
-        self.ctx.check(lib().b200reg_batch_register(self.h, n, C.cast(rh, _VP), C.cast(qh, _VP), _p(Ti), _p(To), C.cast(stats, _VP), _p(status)))
+        self.ctx.check(lib().b200reg_batch_register(self.h, n, rh, C.cast(qh, _VP), _p(Ti), _p(To), C.cast(stats, _VP), _p(status)))
         return To.reshape(n, 4, 4), list(stats)[:n], status[:n]
 
     @staticmethod
@@ -655,11 +661,12 @@ class Batch:
 
     def register_host(self, refs, readings, T_init):
         """refs / readings: HostCloud arrays from host_clouds() (keep the numpy arrays alive).  The uploads are part of the pipeline."""
-        n = len(refs) if not isinstance(refs, tuple) else len(refs[1])
+        n = len(readings[1]) if isinstance(readings, tuple) else len(readings)
         ra = refs[0] if isinstance(refs, tuple) else refs
         qa = readings[0] if isinstance(readings, tuple) else readings
         Ti, To, stats, status = self._out(n, T_init)
-        self.ctx.check(lib().b200reg_batch_register_host(self.h, n, C.cast(ra, _VP), C.cast(qa, _VP), _p(Ti), _p(To), C.cast(stats, _VP), _p(status)))
+        self.ctx.check(lib().b200reg_batch_register_host(self.h, n, None if ra is None else C.cast(ra, _VP), C.cast(qa, _VP), _p(Ti), _p(To),
+                                                         C.cast(stats, _VP), _p(status)))
         return To.reshape(n, 4, 4), list(stats)[:n], status[:n]
 
     def close(self):

@@ -100,8 +100,11 @@ struct IndexHeader {
 
 struct b200reg_index {
   int64_t m = 0;
+  int64_t mCap = 0;            // points the pts / nrm allocations hold (a recycled index keeps its storage)
   float4* pts = nullptr;       // sorted by cell: x y z (centred) + original index bits in .w
-  float4* nrm = nullptr;       // sorted normals (nullable)
+  float4* nrm = nullptr;       // sorted normals (nullable): nrmStore when the current content has normals
+  float4* nrmStore = nullptr;  // the allocation behind nrm (kept when a recycled index is rebuilt over a cloud without normals)
+  bool hasNrm = false;
   uint32_t* dirBase = nullptr; // allocation of the directory: 3 pad words, then cellStart[numCells + 1] (so that the counts, cellStart + 1, are 16-byte aligned)
   uint32_t* cellStart = nullptr;   // numCells + 1 entries (numCells <= cellCap)
   uint32_t cellCap = 0;
@@ -112,8 +115,10 @@ struct b200reg_index {
 };
 // host view of the header (waits once for the build's asynchronous copy); nullptr + ctx error if the build failed on the device
 const IndexHeader* indexHeader(b200reg_ctx* ctx, const b200reg_index* ix);
-// enqueue the build of an index over `ref` on the ctx stream (centre != 0: after subtracting the cloud's mean); no host wait
-int buildIndex(b200reg_ctx* ctx, const b200reg_cloud* ref, int centre, float cell, b200reg_index** out);
+// enqueue the build of an index over `ref` on the ctx stream (centre != 0: after subtracting the cloud's mean); no host wait.
+// recycle (nullable): an index of the SAME ctx that is no longer needed — its storage is reused when it is large enough (no
+// allocator calls on the path of a periodic rebuild), otherwise it is freed; either way the caller must forget it.
+int buildIndex(b200reg_ctx* ctx, const b200reg_cloud* ref, int centre, float cell, b200reg_index** out, b200reg_index* recycle = nullptr);
 IndexHeader* acquireHeaderSlot(b200reg_ctx* ctx);
 void releaseHeaderSlot(b200reg_ctx* ctx, IndexHeader* slot);
 

@@ -422,6 +422,7 @@ struct b200reg_icp {
   b200reg_ctx* ctx = nullptr;
   b200reg_icp_config cfg{};
   b200reg_index* index = nullptr;   // over the centred, (un)filtered reference — `referenceFiltered` + the matcher
+  bool ownsIndex = true;            // false: the index belongs to a b200reg_batch (shared by its lanes, read-only)
   double refPrepS = 0;
   DevBuf reading, readingNrm;       // `reading` of ICP.cpp:352-375 (in the refMean frame)
   // device-resident iterate loop (k = 1): a CUDA graph whose body is a `while` conditional node
@@ -742,7 +743,7 @@ void b200reg_icp_destroy(b200reg_icp* icp) {
   b200reg_ctx* ctx = icp->ctx;
   cudaSetDevice(ctx->device);
   cudaStreamSynchronize(ctx->stream);
-  if (icp->index) b200reg_index_free(ctx, icp->index);
+  if (icp->index && icp->ownsIndex) b200reg_index_free(ctx, icp->index);
   if (icp->reading.p) devFree(icp->ctx, icp->reading.p);
   if (icp->readingNrm.p) devFree(icp->ctx, icp->readingNrm.p);
   if (icp->exec) cudaGraphExecDestroy(icp->exec);
@@ -759,10 +760,15 @@ int32_t b200reg_icp_set_reference(b200reg_icp* icp, const b200reg_cloud* referen
   b200reg_ctx* ctx = icp->ctx;
   const double t0 = nowSec();
   if (icp->pending) return setErr(ctx, B200REG_E_INVALID_PARAM, "icp_set_reference: a registration is still in flight on this object");
-  if (icp->index) { b200reg_index_free(ctx, icp->index); icp->index = nullptr; }   // matcherIsInitialized = false
-  if (reference->n == 0) return setErr(ctx, B200REG_E_NO_POINTS, "initReference: reference cloud is empty");   // :295-298
+  b200reg_index* old = (icp->index && icp->ownsIndex) ? icp->index : nullptr;   // matcherIsInitialized = false
+  icp->index = nullptr;
+  icp->ownsIndex = true;
   CUDA_TRY(ctx, cudaSetDevice(ctx->device));
-  TRY(buildIndex(ctx, reference, 1, icp->cfg.cell, &icp->index));
+  if (reference->n == 0) {   // :295-298
+    if (old) b200reg_index_free(ctx, old);
+    return setErr(ctx, B200REG_E_NO_POINTS, "initReference: reference cloud is empty");
+  }
+  TRY(buildIndex(ctx, reference, 1, icp->cfg.cell, &icp->index, old));   // the previous index's storage is reused when it fits
   icp->refPrepS = nowSec() - t0;
   return B200REG_OK;
 }
@@ -1054,6 +1060,8 @@ struct b200reg_batch {
   b200reg_icp_config cfg{};
   int lanes = 0;
   cudaEvent_t parentReady = nullptr;   // the parent stream's position when a batch call starts (its clouds may still be in flight)
+  b200reg_index* shared = nullptr;     // b200reg_batch_set_reference: ONE index (built on the parent stream) every lane registers against
+  double sharedPrepS = 0;
   struct Lane {
     b200reg_ctx* ctx = nullptr;
     b200reg_icp* icp = nullptr;
@@ -1104,7 +1112,14 @@ int batchRun(b200reg_batch* B, int32_t n, const float* T_init, float* T_out, b20
     const b200reg_cloud *ref = nullptr, *reading = nullptr;
     memset(&L.icp->pendStats, 0, sizeof(L.icp->pendStats));
     int code = fetch(L, i, &ref, &reading);
-    if (code == B200REG_OK) code = b200reg_icp_set_reference(L.icp, ref);
+    if (code == B200REG_OK && ref) code = b200reg_icp_set_reference(L.icp, ref);
+    else if (code == B200REG_OK) {   // the batch's shared reference (read-only for the lanes)
+      if (L.icp->index && L.icp->ownsIndex) b200reg_index_free(L.ctx, L.icp->index);
+      L.icp->index = B->shared;
+      L.icp->ownsIndex = false;
+      L.icp->refPrepS = B->sharedPrepS;
+      if (!B->shared) code = setErr(L.ctx, B200REG_E_NO_POINTS, "ICP: matcher not initialised (b200reg_batch_set_reference was not called)");
+    }
     if (code == B200REG_OK) code = icpEnqueue(L.icp, reading, T_init + 16 * (size_t)i);
     if (code == B200REG_OK) L.inFlight = i;
     else batchFail(B, L, i, code, T_init, T_out, stats, status, &first);
@@ -1156,24 +1171,44 @@ void b200reg_batch_destroy(b200reg_batch* B) {
     b200reg_batch::Lane& L = B->lane[l];
     if (!L.ctx) continue;
     cudaStreamSynchronize(L.ctx->stream);
-    if (L.icp) { L.icp->pending = false; b200reg_icp_destroy(L.icp); }
+    if (L.icp) { L.icp->pending = false; b200reg_icp_destroy(L.icp); }   // a shared index is not the lane's to free
     if (L.ref) b200reg_cloud_free(L.ctx, L.ref);
     if (L.reading) b200reg_cloud_free(L.ctx, L.reading);
     b200reg_ctx_destroy(L.ctx);
   }
+  if (B->shared) b200reg_index_free(B->parent, B->shared);
   if (B->parentReady) cudaEventDestroy(B->parentReady);
   delete B;
 }
 
 int32_t b200reg_batch_lanes(const b200reg_batch* B) { return B ? B->lanes : 0; }
 
+// ICP::initReference once for the whole batch: the index is built on the parent stream and every lane registers its readings
+// against it (many scans / many initial guesses against one map: re-localisation, multi-sequence mapping).
+int32_t b200reg_batch_set_reference(b200reg_batch* B, const b200reg_cloud* reference) {
+  if (!B || !reference) return B200REG_E_INVALID_PARAM;
+  b200reg_ctx* P = B->parent;
+  const double t0 = nowSec();
+  CUDA_TRY(P, cudaSetDevice(P->device));
+  for (int l = 0; l < B->lanes; ++l) {   // no lane may still hold the old index
+    b200reg_batch::Lane& L = B->lane[l];
+    CUDA_TRY(P, cudaStreamSynchronize(L.ctx->stream));
+    if (L.icp->index && !L.icp->ownsIndex) L.icp->index = nullptr;
+  }
+  if (B->shared) { b200reg_index_free(P, B->shared); B->shared = nullptr; }
+  if (reference->n == 0) return setErr(P, B200REG_E_NO_POINTS, "initReference: reference cloud is empty");
+  TRY(buildIndex(P, reference, 1, B->cfg.cell, &B->shared));
+  B->sharedPrepS = nowSec() - t0;
+  return B200REG_OK;
+}
+
 int32_t b200reg_batch_register(b200reg_batch* B, int32_t n, const b200reg_cloud* const* refs, const b200reg_cloud* const* readings,
                                const float* T_init, float* T_out, b200reg_icp_stats* stats, int32_t* status) {
   if (!B) return B200REG_E_INVALID_PARAM;
-  if (n < 0 || (n > 0 && (!refs || !readings || !T_init || !T_out))) return setErr(B->parent, B200REG_E_INVALID_PARAM, "batch_register: bad arguments");
+  if (n < 0 || (n > 0 && (!readings || !T_init || !T_out))) return setErr(B->parent, B200REG_E_INVALID_PARAM, "batch_register: bad arguments");
   return batchRun(B, n, T_init, T_out, stats, status, [&](b200reg_batch::Lane& L, int32_t i, const b200reg_cloud** ref, const b200reg_cloud** reading) {
-    if (!refs[i] || !readings[i]) return setErr(L.ctx, B200REG_E_INVALID_PARAM, "batch_register: null cloud");
-    *ref = refs[i];
+    if ((refs && !refs[i]) || !readings[i]) return setErr(L.ctx, B200REG_E_INVALID_PARAM, "batch_register: null cloud");
+    *ref = refs ? refs[i] : nullptr;
     *reading = readings[i];
     return (int)B200REG_OK;
   });
@@ -1182,18 +1217,23 @@ int32_t b200reg_batch_register(b200reg_batch* B, int32_t n, const b200reg_cloud*
 int32_t b200reg_batch_register_host(b200reg_batch* B, int32_t n, const b200reg_host_cloud* refs, const b200reg_host_cloud* readings,
                                     const float* T_init, float* T_out, b200reg_icp_stats* stats, int32_t* status) {
   if (!B) return B200REG_E_INVALID_PARAM;
-  if (n < 0 || (n > 0 && (!refs || !readings || !T_init || !T_out))) return setErr(B->parent, B200REG_E_INVALID_PARAM, "batch_register_host: bad arguments");
+  if (n < 0 || (n > 0 && (!readings || !T_init || !T_out))) return setErr(B->parent, B200REG_E_INVALID_PARAM, "batch_register_host: bad arguments");
   return batchRun(B, n, T_init, T_out, stats, status, [&](b200reg_batch::Lane& L, int32_t i, const b200reg_cloud** ref, const b200reg_cloud** reading) {
-    const b200reg_host_cloud &hr = refs[i], &hq = readings[i];
+    const b200reg_host_cloud& hq = readings[i];
     // asynchronous uploads on the lane's stream (pinned host memory overlaps with the other lanes' kernels; pageable memory is
     // staged by the runtime and only the staging copy blocks this thread)
-    int code = L.ref ? b200reg_cloud_update_f32(L.ctx, L.ref, hr.feat, hr.feat_stride, hr.normals, hr.n, 1)
-                     : b200reg_cloud_upload_f32(L.ctx, hr.feat, hr.feat_stride, hr.normals, hr.n, &L.ref);
-    if (code != B200REG_OK) return code;
+    int code = B200REG_OK;
+    *ref = nullptr;
+    if (refs) {
+      const b200reg_host_cloud& hr = refs[i];
+      code = L.ref ? b200reg_cloud_update_f32(L.ctx, L.ref, hr.feat, hr.feat_stride, hr.normals, hr.n, 1)
+                   : b200reg_cloud_upload_f32(L.ctx, hr.feat, hr.feat_stride, hr.normals, hr.n, &L.ref);
+      if (code != B200REG_OK) return code;
+      *ref = L.ref;
+    }
     code = L.reading ? b200reg_cloud_update_f32(L.ctx, L.reading, hq.feat, hq.feat_stride, hq.normals, hq.n, 1)
                      : b200reg_cloud_upload_f32(L.ctx, hq.feat, hq.feat_stride, hq.normals, hq.n, &L.reading);
     if (code != B200REG_OK) return code;
-    *ref = L.ref;
     *reading = L.reading;
     return (int)B200REG_OK;
   });

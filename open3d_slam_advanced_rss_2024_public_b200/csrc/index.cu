@@ -11,9 +11,11 @@
 //   statsKernel      fp64 coordinate sums + bbox per block                                   16 B/pt read
 //   gridKernel       one block: mean (fp64 sum rounded once to fp32, ICP.cpp:313), bbox of the centred cloud, cell size, grid
 //   zeroDirKernel    directory + scan tile states
-//   countKernel      cell of fl(p - mean) (ICP.cpp:320); rank of the point inside its cell = the value the atomic returns   16 B/pt read, 4 B/pt written
+//   countKernel      cell of fl(p - mean) (ICP.cpp:320); rank of the point inside its cell = the value the atomic returns   16 B/pt read, 8 B/pt written
 //   scanDirKernel    single-pass inclusive scan of the counts (decoupled look-back), length read from the header        8 B/cell
-//   scatterKernel    pts[cellStart[cell] + rank] = (centred point, index), normals alike                               36 B/pt read, 32 B/pt written
+//   permKernel       perm[cellStart[cell] + rank] = original index (4-byte scatter into an L2-resident array)           12 B/pt read, 4 B/pt written
+//   gatherPtsKernel  pts[j] = (centred point perm[j], index): coalesced streaming writes, 16-byte gathers from an L2-resident array   20 B/pt read, 16 B/pt written
+//   gatherNrmKernel  the normals alike, in a pass of their own                                                          20 B/pt read, 16 B/pt written
 // The order of the points INSIDE a cell is the arrival order of the atomics; nothing downstream depends on it: every search
 // resolves ties by (d2, original index) and the reductions run in reading order (knn.cu, icp_kernels.cuh).
 // The host learns the grid (for b200reg_index_cell, error reporting) from an asynchronous copy of the header, waited for only
@@ -69,26 +71,30 @@ __global__ void statsKernel(const float4* __restrict__ xyz, int64_t n, StatsPart
 // synchronisations).  The partials are added in block order by one thread per quantity, so the mean is the same whatever ran
 // beside this kernel.  Non-finite coordinates (a LiDAR driver's +-inf "no return") leave status = 1 and a 1-cell grid, so the
 // kernels behind this one run harmlessly and the host reports InvalidParameter when it reads the header.
-#define GRID_MAX_PARTIALS 768
-__global__ void __launch_bounds__(256) gridKernel(const StatsPartial* __restrict__ partials, int blocks, long long m, int centre, float userCell,
+__global__ void __launch_bounds__(288) gridKernel(const StatsPartial* __restrict__ partials, int blocks, long long m, int centre, float userCell,
                                                   unsigned capCells, IndexHeader* __restrict__ hdr) {
-  __shared__ StatsPartial sp[GRID_MAX_PARTIALS];
   __shared__ double sSum[3];
   __shared__ float sMn[3], sMx[3];
-  for (int b = threadIdx.x; b < blocks; b += blockDim.x) sp[b] = partials[b];
-  __syncthreads();
-  if (threadIdx.x < 3) {
+  // nine warps, one quantity each (3 sums, 3 minima, 3 maxima): lane l adds partials l, l + 32, ... in order, then a shuffle tree —
+  // a fixed order, so the mean does not depend on what ran beside this kernel
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (warp < 3) {
     double s = 0;
-    for (int b = 0; b < blocks; ++b) s += (threadIdx.x == 0) ? sp[b].sx : (threadIdx.x == 1) ? sp[b].sy : sp[b].sz;
-    sSum[threadIdx.x] = s;
-  } else if (threadIdx.x >= 32 && threadIdx.x < 35) {
-    const int d = threadIdx.x - 32;
-    float a = FLT_MAX, z = -FLT_MAX;
-    for (int b = 0; b < blocks; ++b) {
-      a = fminf(a, d == 0 ? sp[b].mnx : d == 1 ? sp[b].mny : sp[b].mnz);
-      z = fmaxf(z, d == 0 ? sp[b].mxx : d == 1 ? sp[b].mxy : sp[b].mxz);
-    }
-    sMn[d] = a; sMx[d] = z;
+    for (int b = lane; b < blocks; b += 32) s += (warp == 0) ? partials[b].sx : (warp == 1) ? partials[b].sy : partials[b].sz;
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    if (lane == 0) sSum[warp] = s;
+  } else if (warp < 6) {
+    const int d = warp - 3;
+    float a = FLT_MAX;
+    for (int b = lane; b < blocks; b += 32) a = fminf(a, d == 0 ? partials[b].mnx : d == 1 ? partials[b].mny : partials[b].mnz);
+    for (int o = 16; o > 0; o >>= 1) a = fminf(a, __shfl_xor_sync(0xffffffffu, a, o));
+    if (lane == 0) sMn[d] = a;
+  } else {
+    const int d = warp - 6;
+    float z = -FLT_MAX;
+    for (int b = lane; b < blocks; b += 32) z = fmaxf(z, d == 0 ? partials[b].mxx : d == 1 ? partials[b].mxy : partials[b].mxz);
+    for (int o = 16; o > 0; o >>= 1) z = fmaxf(z, __shfl_xor_sync(0xffffffffu, z, o));
+    if (lane == 0) sMx[d] = z;
   }
   __syncthreads();
   if (threadIdx.x != 0) return;
@@ -185,13 +191,14 @@ __device__ __forceinline__ uint32_t cellKeyOf(const float4 p, const float mx, co
 }
 
 __global__ void __launch_bounds__(256) countKernel(const float4* __restrict__ xyz, int64_t n, const IndexHeader* __restrict__ hdr,
-                                                   uint32_t* __restrict__ cellStart, uint32_t* __restrict__ rank) {
+                                                   uint32_t* __restrict__ cellStart, uint2* __restrict__ keyRank) {
   const GridDesc g = hdr->g;
   const float mx = hdr->mean[0], my = hdr->mean[1], mz = hdr->mean[2];
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
     float x, y, z;
     const uint32_t key = cellKeyOf(xyz[i], mx, my, mz, g, x, y, z);
-    rank[i] = atomicAdd(&cellStart[key + 1], 1u);   // counts live one slot up: the scan turns them into the next cell's start
+    const uint32_t r = atomicAdd(&cellStart[key + 1], 1u);   // counts live one slot up: the scan turns them into the next cell's start
+    keyRank[i] = make_uint2(key, r);
   }
 }
 
@@ -203,7 +210,7 @@ __global__ void __launch_bounds__(SCAN_THREADS) scanDirKernel(const IndexHeader*
   const unsigned numCells = hdr->numCells;
   const unsigned tiles = (numCells + SCAN_TILE - 1) / SCAN_TILE;
   uint32_t* __restrict__ data = cellStart + 1;   // 16-byte aligned (zeroDirKernel)
-  __shared__ unsigned sTile, sWarp[SCAN_THREADS / 32], sPrefix;
+  __shared__ unsigned sTile, sWarp[SCAN_ITEMS / 4][SCAN_THREADS / 32], sPrefix;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   for (;;) {
     __syncthreads();   // sTile / sPrefix / sWarp of the previous round are no longer read
@@ -211,34 +218,46 @@ __global__ void __launch_bounds__(SCAN_THREADS) scanDirKernel(const IndexHeader*
     __syncthreads();
     const unsigned tile = sTile;
     if (tile >= tiles) return;
-    const size_t base = (size_t)tile * SCAN_TILE + (size_t)threadIdx.x * SCAN_ITEMS;
-    unsigned v[SCAN_ITEMS];
-    // each thread owns SCAN_ITEMS consecutive words (64 B: two full sectors), fetched as four 16-byte loads; the allocation is
-    // padded to a whole tile, words beyond numCells are ignored
+    // group (j, tid) = the four words at tile base + 4 (j * SCAN_THREADS + tid): consecutive threads load consecutive 16 bytes.
+    // The allocation is padded to a whole tile; words beyond numCells are ignored.
+    const size_t tbase = (size_t)tile * SCAN_TILE;
+    constexpr int NG = SCAN_ITEMS / 4;
+    uint4 q[NG];
 #pragma unroll
-    for (int j = 0; j < SCAN_ITEMS / 4; ++j) {
-      const uint4 q = __ldcg(reinterpret_cast<const uint4*>(data + base) + j);
-      v[4 * j] = q.x; v[4 * j + 1] = q.y; v[4 * j + 2] = q.z; v[4 * j + 3] = q.w;
+    for (int j = 0; j < NG; ++j) q[j] = __ldcg(reinterpret_cast<const uint4*>(data + tbase) + j * SCAN_THREADS + threadIdx.x);
+    unsigned gsum[NG], gincl[NG];
+#pragma unroll
+    for (int j = 0; j < NG; ++j) {
+      const size_t w0 = tbase + 4 * ((size_t)j * SCAN_THREADS + threadIdx.x);
+      if (w0 + 0 >= numCells) q[j].x = 0u;
+      if (w0 + 1 >= numCells) q[j].y = 0u;
+      if (w0 + 2 >= numCells) q[j].z = 0u;
+      if (w0 + 3 >= numCells) q[j].w = 0u;
+      q[j].y += q[j].x; q[j].z += q[j].y; q[j].w += q[j].z;   // inclusive inside the group
+      gsum[j] = q[j].w;
+      unsigned incl = gsum[j];
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const unsigned t = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += t;
+      }
+      gincl[j] = incl;
+      if (lane == 31) sWarp[j][warp] = incl;
     }
-#pragma unroll
-    for (int j = 0; j < SCAN_ITEMS; ++j) if (base + j >= numCells) v[j] = 0u;
-    unsigned sum = 0;
-#pragma unroll
-    for (int j = 0; j < SCAN_ITEMS; ++j) { sum += v[j]; v[j] = sum; }   // thread-local inclusive
-    unsigned incl = sum;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-      const unsigned t = __shfl_up_sync(0xffffffffu, incl, o);
-      if (lane >= o) incl += t;
-    }
-    if (lane == 31) sWarp[warp] = incl;
     __syncthreads();
-    unsigned warpOff = 0, tileSum = 0;
+    // offset of group (j, tid) inside the tile = all groups of rows j' < j + the warps before this one in row j + the lanes before
+    unsigned goff[NG], tileSum = 0;
 #pragma unroll
-    for (int w = 0; w < SCAN_THREADS / 32; ++w) {
-      const unsigned s = sWarp[w];
-      if (w < warp) warpOff += s;
-      tileSum += s;
+    for (int j = 0; j < NG; ++j) {
+      unsigned before = 0, row = 0;
+#pragma unroll
+      for (int w = 0; w < SCAN_THREADS / 32; ++w) {
+        const unsigned sw = sWarp[j][w];
+        if (w < warp) before += sw;
+        row += sw;
+      }
+      goff[j] = tileSum + before + (gincl[j] - gsum[j]);
+      tileSum += row;
     }
     if (warp == 0) {   // publish, then look back
       if (lane == 0) {
@@ -271,25 +290,46 @@ __global__ void __launch_bounds__(SCAN_THREADS) scanDirKernel(const IndexHeader*
       if (lane == 0) sPrefix = prefix;
     }
     __syncthreads();
-    const unsigned off = sPrefix + warpOff + (incl - sum);
+    const unsigned prefix = sPrefix;
 #pragma unroll
-    for (int j = 0; j < SCAN_ITEMS / 4; ++j)   // words beyond numCells land in the allocation's padding
-      reinterpret_cast<uint4*>(data + base)[j] = make_uint4(v[4 * j] + off, v[4 * j + 1] + off, v[4 * j + 2] + off, v[4 * j + 3] + off);
+    for (int j = 0; j < NG; ++j) {   // words beyond numCells land in the allocation's padding
+      const unsigned off = prefix + goff[j];
+      reinterpret_cast<uint4*>(data + tbase)[j * SCAN_THREADS + threadIdx.x] = make_uint4(q[j].x + off, q[j].y + off, q[j].z + off, q[j].w + off);
+    }
   }
 }
 
-__global__ void __launch_bounds__(256) scatterKernel(const float4* __restrict__ xyz, const float4* __restrict__ nrm, int64_t n,
-                                                     const IndexHeader* __restrict__ hdr, const uint32_t* __restrict__ cellStart,
-                                                     const uint32_t* __restrict__ rank, float4* __restrict__ pts, float4* __restrict__ outN) {
-  const GridDesc g = hdr->g;
-  const float mx = hdr->mean[0], my = hdr->mean[1], mz = hdr->mean[2];
+// perm[sorted position] = original index.  The random 4-byte writes land in a 4 M-byte array that stays in L2; scattering the
+// 32-byte payload instead was measured at 313 us for 5 M points (partial-sector writes), this + the gather below at ~180 us.
+__global__ void __launch_bounds__(256) permKernel(const uint2* __restrict__ keyRank, int64_t n, const uint32_t* __restrict__ cellStart,
+                                                  uint32_t* __restrict__ perm) {
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
-    float x, y, z;
-    const uint32_t key = cellKeyOf(xyz[i], mx, my, mz, g, x, y, z);
-    const uint32_t j = cellStart[key] + rank[i];
-    pts[j] = make_float4(x, y, z, __int_as_float((int)i));
-    if (nrm) outN[j] = nrm[i];
+    const uint2 kr = keyRank[i];
+    perm[cellStart[kr.x] + kr.y] = (uint32_t)i;
   }
+}
+
+// sorted payload: pts[j] = (fl(p - mean), original index), then the normals in a pass of their own.  One pass over both arrays
+// gathers from 32 B/pt of input — more than the L2 holds for a 5 M-point map, so half-used sectors are fetched twice; one array
+// at a time (16 B/pt, L2-resident) with the output streamed past the cache fetches every input sector once.
+__device__ __forceinline__ float4 ldGather(const float4* p) {   // keep the gathered line (its other half is some other thread's point)
+  float4 v;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
+  return v;
+}
+__global__ void __launch_bounds__(256) gatherPtsKernel(const float4* __restrict__ xyz, int64_t n, const IndexHeader* __restrict__ hdr,
+                                                       const uint32_t* __restrict__ perm, float4* __restrict__ pts) {
+  const float mx = hdr->mean[0], my = hdr->mean[1], mz = hdr->mean[2];
+  for (int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; j < n; j += (int64_t)gridDim.x * blockDim.x) {
+    const uint32_t i = __ldcs(perm + j);
+    const float4 p = ldGather(xyz + i);
+    __stcs(pts + j, make_float4(__fsub_rn(p.x, mx), __fsub_rn(p.y, my), __fsub_rn(p.z, mz), __int_as_float((int)i)));
+  }
+}
+__global__ void __launch_bounds__(256) gatherNrmKernel(const float4* __restrict__ nrm, int64_t n, const uint32_t* __restrict__ perm,
+                                                       float4* __restrict__ outN) {
+  for (int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; j < n; j += (int64_t)gridDim.x * blockDim.x)
+    __stcs(outN + j, ldGather(nrm + __ldcs(perm + j)));
 }
 
 }  // namespace
@@ -323,7 +363,7 @@ static void indexRelease(b200reg_ctx* ctx, b200reg_index* ix) {
   }
   if (ix->hHdr) releaseHeaderSlot(ctx, ix->hHdr);
   if (ix->pts) devFree(ctx, ix->pts);
-  if (ix->nrm) devFree(ctx, ix->nrm);
+  if (ix->nrmStore) devFree(ctx, ix->nrmStore);
   if (ix->dirBase) devFree(ctx, ix->dirBase);
   if (ix->dHdr) devFree(ctx, ix->dHdr);
   delete ix;
@@ -331,49 +371,65 @@ static void indexRelease(b200reg_ctx* ctx, b200reg_index* ix) {
 
 // Enqueue the build of an index over `ref` (centre != 0: after subtracting the cloud's mean, ICP.cpp:313-320).  Nothing here
 // waits for the device; `ref` must stay alive until the stream has passed this point (stream-ordered frees on the same ctx do).
-int buildIndex(b200reg_ctx* ctx, const b200reg_cloud* ref, int centre, float cell, b200reg_index** out) {
+int buildIndex(b200reg_ctx* ctx, const b200reg_cloud* ref, int centre, float cell, b200reg_index** out, b200reg_index* recycle) {
   const int64_t m = ref->n;
   *out = nullptr;
-  if (m <= 0) return setErr(ctx, B200REG_E_NO_POINTS, "index_build: reference cloud is empty");
-  if (m >= (int64_t)0x7fffffff) return setErr(ctx, B200REG_E_INVALID_PARAM, "index_build: more than 2^31-1 points");
-  b200reg_index* ix = new b200reg_index();
-  ix->m = m;
+  if (m <= 0) { indexRelease(ctx, recycle); return setErr(ctx, B200REG_E_NO_POINTS, "index_build: reference cloud is empty"); }
+  if (m >= (int64_t)0x7fffffff) { indexRelease(ctx, recycle); return setErr(ctx, B200REG_E_INVALID_PARAM, "index_build: more than 2^31-1 points"); }
   // directory capacity from m alone (the host does not know the bbox): 8 cells per point, at least 2^16, at most 2^30; the
   // device grows the cell until the grid fits (the automatic cell gives ~4 cells per point on surface-like clouds)
   const uint64_t cap = std::min<uint64_t>(std::max<uint64_t>(8ull * (uint64_t)m, 1ull << 16), 1ull << 30);
-  ix->cellCap = (uint32_t)cap;
-  const size_t tilesCap = (cap + SCAN_TILE - 1) / SCAN_TILE;
+  b200reg_index* ix = nullptr;
+  if (recycle && recycle->mCap >= m && recycle->cellCap >= cap && recycle->cellCap <= 4 * cap && (recycle->nrm || !ref->nrm)) {
+    ix = recycle;   // same stream: everything enqueued against the old content runs before the kernels below
+    if (!ix->hdrFetched) cudaEventSynchronize(ix->hdrReady);   // the old header copy must have landed before the slot is rewritten
+    ix->hdrFetched = false;
+    ix->hasNrm = ref->nrm != nullptr;
+  } else {
+    indexRelease(ctx, recycle);
+    ix = new b200reg_index();
+  }
+  ix->m = m;
+  const size_t tilesCap = ((ix == recycle ? (uint64_t)ix->cellCap : cap) + SCAN_TILE - 1) / SCAN_TILE;
   const int sblocks = (int)fmin((double)(4 * ctx->sm_count), (double)divUp(m, 256));
-  static_assert(4 * B200_SM_COUNT <= GRID_MAX_PARTIALS, "gridKernel stages the block partials in shared memory");
   int st = B200REG_OK;
   cudaError_t e = cudaSuccess;
   auto fail = [&](int code) { indexRelease(ctx, ix); return code; };
-  if (sblocks > GRID_MAX_PARTIALS) return fail(setErr(ctx, B200REG_E_INVALID_PARAM, "index_build: device with more than %d SMs", GRID_MAX_PARTIALS / 4));
-  e = devAlloc(ctx, &ix->pts, sizeof(float4) * (size_t)m);
-  if (e == cudaSuccess && ref->nrm) e = devAlloc(ctx, &ix->nrm, sizeof(float4) * (size_t)m);
-  if (e == cudaSuccess) e = devAlloc(ctx, &ix->dirBase, sizeof(uint32_t) * ((size_t)tilesCap * SCAN_TILE + 8));
-  ix->cellStart = ix->dirBase ? ix->dirBase + 3 : nullptr;
-  if (e == cudaSuccess) e = devAlloc(ctx, &ix->dHdr, sizeof(IndexHeader));
-  if (e == cudaSuccess) e = cudaEventCreateWithFlags(&ix->hdrReady, cudaEventDisableTiming);
-  if (e != cudaSuccess)
-    return fail(setErr(ctx, B200REG_E_OOM, "index_build: allocation failed (%llu directory cells, %lld points): %s", (unsigned long long)cap, (long long)m, cudaGetErrorString(e)));
-  ix->hHdr = acquireHeaderSlot(ctx);
-  if (!ix->hHdr) return fail(setErr(ctx, B200REG_E_OOM, "index_build: no pinned header slot"));
+  if (ix != recycle) {
+    ix->cellCap = (uint32_t)cap;
+    ix->mCap = m + m / 8;   // head-room: a periodically rebuilt reference (the Mapper's map patch) changes size a little every time
+    ix->hasNrm = ref->nrm != nullptr;
+    e = devAlloc(ctx, &ix->pts, sizeof(float4) * (size_t)ix->mCap);
+    if (e == cudaSuccess && ref->nrm) e = devAlloc(ctx, &ix->nrmStore, sizeof(float4) * (size_t)ix->mCap);
+    if (e == cudaSuccess) e = devAlloc(ctx, &ix->dirBase, sizeof(uint32_t) * ((size_t)tilesCap * SCAN_TILE + 8));
+    ix->cellStart = ix->dirBase ? ix->dirBase + 3 : nullptr;
+    if (e == cudaSuccess) e = devAlloc(ctx, &ix->dHdr, sizeof(IndexHeader));
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&ix->hdrReady, cudaEventDisableTiming);
+    if (e != cudaSuccess)
+      return fail(setErr(ctx, B200REG_E_OOM, "index_build: allocation failed (%llu directory cells, %lld points): %s", (unsigned long long)cap, (long long)m, cudaGetErrorString(e)));
+    ix->hHdr = acquireHeaderSlot(ctx);
+    if (!ix->hHdr) return fail(setErr(ctx, B200REG_E_OOM, "index_build: no pinned header slot"));
+  }
+  ix->nrm = ix->hasNrm ? ix->nrmStore : nullptr;
   if ((st = ensureBuf(ctx, ctx->partials, sizeof(StatsPartial) * (size_t)sblocks)) != B200REG_OK) return fail(st);
-  if ((st = ensureBuf(ctx, ctx->keys0, sizeof(uint32_t) * (size_t)m)) != B200REG_OK) return fail(st);
+  if ((st = ensureBuf(ctx, ctx->keys0, sizeof(uint2) * (size_t)m)) != B200REG_OK) return fail(st);
+  if ((st = ensureBuf(ctx, ctx->vals0, sizeof(uint32_t) * (size_t)m)) != B200REG_OK) return fail(st);
   if ((st = ensureBuf(ctx, ctx->cubtmp, sizeof(unsigned long long) * tilesCap + 64)) != B200REG_OK) return fail(st);
   unsigned long long* tileState = (unsigned long long*)ctx->cubtmp.p;
   unsigned* tileCounter = (unsigned*)((char*)ctx->cubtmp.p + sizeof(unsigned long long) * tilesCap);
-  uint32_t* rank = (uint32_t*)ctx->keys0.p;
+  uint2* keyRank = (uint2*)ctx->keys0.p;
+  uint32_t* perm = (uint32_t*)ctx->vals0.p;
   const int wide = 8 * ctx->sm_count;   // grid of the streaming passes: 8 blocks of 256 threads per SM
   const int pblocks = (int)std::min<int64_t>(divUp(m, 256), wide);
   statsKernel<<<sblocks, 256, 0, ctx->stream>>>(ref->xyz, m, (StatsPartial*)ctx->partials.p);
-  gridKernel<<<1, 256, 0, ctx->stream>>>((const StatsPartial*)ctx->partials.p, sblocks, (long long)m, centre, cell, ix->cellCap, ix->dHdr);
+  gridKernel<<<1, 288, 0, ctx->stream>>>((const StatsPartial*)ctx->partials.p, sblocks, (long long)m, centre, cell, ix->cellCap, ix->dHdr);
   zeroDirKernel<<<(int)std::min<uint64_t>(wide, (cap / 4 + 255) / 256), 256, 0, ctx->stream>>>(ix->dHdr, ix->dirBase, tileState, tileCounter);
-  countKernel<<<pblocks, 256, 0, ctx->stream>>>(ref->xyz, m, ix->dHdr, ix->cellStart, rank);
+  countKernel<<<pblocks, 256, 0, ctx->stream>>>(ref->xyz, m, ix->dHdr, ix->cellStart, keyRank);
   scanDirKernel<<<(int)std::min<uint64_t>(4 * ctx->sm_count, tilesCap), SCAN_THREADS, 0, ctx->stream>>>(ix->dHdr, ix->cellStart, tileState, tileCounter);
-  scatterKernel<<<pblocks, 256, 0, ctx->stream>>>(ref->xyz, ref->nrm, m, ix->dHdr, ix->cellStart, rank, ix->pts, ix->nrm);
-  ctx->launches += 6;
+  permKernel<<<pblocks, 256, 0, ctx->stream>>>(keyRank, m, ix->cellStart, perm);
+  gatherPtsKernel<<<pblocks, 256, 0, ctx->stream>>>(ref->xyz, m, ix->dHdr, perm, ix->pts);
+  if (ref->nrm) gatherNrmKernel<<<pblocks, 256, 0, ctx->stream>>>(ref->nrm, m, perm, ix->nrm);
+  ctx->launches += ref->nrm ? 8 : 7;
   e = cudaGetLastError();
   if (e == cudaSuccess) e = cudaMemcpyAsync(ix->hHdr, ix->dHdr, sizeof(IndexHeader), cudaMemcpyDeviceToHost, ctx->stream);
   if (e == cudaSuccess) e = cudaEventRecord(ix->hdrReady, ctx->stream);

@@ -81,6 +81,43 @@ def test_batch_lanes_bit_identical_to_serial(ctx, oracle, lanes):
     assert all(np.array_equal(T1[i], serial[i][0]) for i in range(len(P))) and list(status1) == [s[4] for s in serial]
 
 
+def test_batch_shared_reference(ctx, oracle):
+    """b200reg_batch_set_reference: ONE index, many readings / initial guesses in flight against it; every result equals the
+    stand-alone registration against the same reference bit for bit, for device and host readings, and mixing with per-pair
+    references afterwards works."""
+    from open3d_slam_advanced_rss_2024_public_b200 import capi
+    kw = dict(knn=1, max_dist=1.0, trim_ratio=0.8, max_iter=40)
+    P = _pairs(oracle, 3, 4700)
+    ref = ctx.upload(P[0]["ref"], P[0]["rn"])
+    rng = np.random.default_rng(11)
+    reads, Tis = [], []
+    for j in range(9):   # the same scan from perturbed initial guesses + sub-sampled versions of it
+        q = P[0]["q"][:: 1 + j % 3]
+        T = P[0]["Ti"].copy()
+        T[:3, 3] += rng.uniform(-0.05, 0.05, 3).astype(np.float32)
+        reads.append(np.ascontiguousarray(q)); Tis.append(T)
+    icp = capi.ICP(ctx, **kw)
+    icp.set_reference(ref)
+    serial = [icp.register(ctx.upload(q), T) for q, T in zip(reads, Tis)]
+    icp.close()
+    b = capi.Batch(ctx, lanes=3, **kw)
+    _, _, status0 = b.register(None, [ctx.upload(reads[0])], np.stack(Tis[:1]))   # no shared reference yet
+    assert list(status0) == [capi.E_NO_POINTS]
+    b.set_reference(ref)
+    T, stats, status = b.register(None, [ctx.upload(q) for q in reads], np.stack(Tis))
+    Th, stats_h, status_h = b.register_host(None, b.host_clouds([(q, None) for q in reads]), np.stack(Tis))
+    assert not status.any() and not status_h.any()
+    for j, (T_s, st_s) in enumerate(serial):
+        assert np.array_equal(T[j], T_s) and np.array_equal(Th[j], T_s)
+        assert stats[j].iterations == st_s.iterations == stats_h[j].iterations
+    # per-pair references after a shared one, then the shared one again
+    T2, _, status2 = b.register([ctx.upload(p["ref"], p["rn"]) for p in P[1:]], [ctx.upload(p["q"]) for p in P[1:]], np.stack([p["Ti"] for p in P[1:]]))
+    assert not status2.any()
+    T3, _, status3 = b.register(None, [ctx.upload(reads[0])], np.stack(Tis[:1]))
+    assert not status3.any() and np.array_equal(T3[0], serial[0][0])
+    b.close()
+
+
 def test_batch_empty_and_errors(ctx, oracle):
     from open3d_slam_advanced_rss_2024_public_b200 import capi
     kw = dict(knn=1, max_dist=1.0, trim_ratio=0.8, max_iter=40)
