@@ -253,6 +253,21 @@ int32_t b200reg_batch_register_host(b200reg_batch* batch, int32_t n, const b200r
 int32_t b200reg_icp_register_batch(b200reg_ctx* ctx, const b200reg_icp_config* cfg, int32_t n, const b200reg_cloud* const* refs,
                                    const b200reg_cloud* const* readings, const float* T_init, float* T_out, b200reg_icp_stats* stats,
                                    int32_t* status);
+/* ---- the batch sharded over the GPUs of one box from ONE process: pair i -> devices[i mod G]; every device runs its pairs
+ *      through its own b200reg_batch, driven by its own host thread; then ONE ncclAllGather of 96-byte records (4x4, status,
+ *      iterations, kept, tau, owner) over NVLink leaves every device with every pair's result, and T_out / status are read from
+ *      the gathered block.  NCCL is resolved at run time (dlopen of libnccl.so.2) and used for this gather only.
+ *      devices == NULL / n_devices == 0: every visible GPU.  On failure *out is still returned so that b200reg_multi_last_error can be
+ *      read; destroy it.  gather_ms (nullable): CUDA-event time of the all-gather on device 0. */
+typedef struct b200reg_multi b200reg_multi;
+int32_t b200reg_multi_create(const int32_t* devices, int32_t n_devices, const b200reg_icp_config* cfg, int32_t lanes, b200reg_multi** out);
+void    b200reg_multi_destroy(b200reg_multi* multi);
+int32_t b200reg_multi_devices(const b200reg_multi* multi);
+int32_t b200reg_multi_nccl_version(const b200reg_multi* multi);
+const char* b200reg_multi_last_error(const b200reg_multi* multi);
+uint64_t b200reg_multi_launch_count(const b200reg_multi* multi);
+int32_t b200reg_multi_register_host(b200reg_multi* multi, int32_t n, const b200reg_host_cloud* refs, const b200reg_host_cloud* readings,
+                                    const float* T_init, float* T_out, b200reg_icp_stats* stats, int32_t* status, float* gather_ms);
 const b200reg_index* b200reg_icp_index(const b200reg_icp* icp);
 int32_t b200reg_icp_reference_mean(const b200reg_icp* icp, float mean_out[3]);
 
@@ -285,6 +300,21 @@ int32_t b200reg_cloud_filter(b200reg_ctx* ctx, b200reg_cloud* inout, const b200r
 int32_t b200reg_surface_normals(b200reg_ctx* ctx, b200reg_cloud* inout, int32_t knn, float max_dist, float epsilon,
                                 const float* orient_origin, float* densities_out, float* eig_values_out,
                                 float* lin_plan_curv_out, int32_t* degenerate_count);
+
+/* The complete descriptor set of the filter (SurfaceNormal.cpp:126-144,247-323).  Optional HOST outputs (nullable): densities[n],
+ * eig_values[3n] ascending, eig_vectors[9n] (serializeEigVec: row-major, eigenvectors in columns, column 0 = the normal's), matched_ids
+ * [knn n] (the neighbours' indices as floats, -1 = none; ascending (d2, index)), mean_dists[n] (|point - mean of its neighbours|;
+ * numeric_limits<size_t>::max() for a degenerate point), lin_plan_curv[3n].  smooth_normals reproduces the reference's in-place
+ * sweep exactly: point i averages the already smoothed normals of its lower-index neighbours and the original normals of the others,
+ * each flipped to the side of its own original normal. */
+typedef struct b200reg_normals_options {
+  int32_t knn;
+  float   max_dist, epsilon;
+  int32_t smooth_normals;
+  const float* orient_origin;   /* nullable float[3]: flip normals toward that point before smoothing */
+  float *densities, *eig_values, *eig_vectors, *matched_ids, *mean_dists, *lin_plan_curv;
+} b200reg_normals_options;
+int32_t b200reg_surface_normals_ex(b200reg_ctx* ctx, b200reg_cloud* inout, const b200reg_normals_options* options, int32_t* degenerate_count);
 
 /* ---- open3d_slam voxel-map crop / insert (fp64) --------------------------------------------------------------------- */
 enum { B200REG_CROP_MAX_RADIUS = 0, B200REG_CROP_MIN_RADIUS = 1, B200REG_CROP_MINMAX_RADIUS = 2, B200REG_CROP_CYLINDER = 3 };

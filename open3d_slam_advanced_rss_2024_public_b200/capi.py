@@ -95,6 +95,13 @@ class IcpConfig(C.Structure):
 CHECKER_COUNTER, CHECKER_DIFFERENTIAL, CHECKER_BOUND = 1, 2, 3
 
 
+class NormalsOptions(C.Structure):
+    """b200reg_normals_options"""
+    _fields_ = [("knn", C.c_int32), ("max_dist", C.c_float), ("epsilon", C.c_float), ("smooth_normals", C.c_int32), ("orient_origin", C.c_void_p),
+                ("densities", C.c_void_p), ("eig_values", C.c_void_p), ("eig_vectors", C.c_void_p), ("matched_ids", C.c_void_p),
+                ("mean_dists", C.c_void_p), ("lin_plan_curv", C.c_void_p)]
+
+
 class HostCloud(C.Structure):
     """b200reg_host_cloud: a cloud in host memory (layout of b200reg_cloud_upload_f32)."""
     _fields_ = [("feat", C.c_void_p), ("feat_stride", C.c_int32), ("normals", C.c_void_p), ("n", C.c_int64)]
@@ -159,10 +166,18 @@ SYMBOLS = {
     "b200reg_batch_set_reference": (C.c_int32, [_VP, _VP]),
     "b200reg_batch_register": (C.c_int32, [_VP, C.c_int32, _VP, _VP, _VP, _VP, _VP, _VP]),
     "b200reg_batch_register_host": (C.c_int32, [_VP, C.c_int32, _VP, _VP, _VP, _VP, _VP, _VP]),
+    "b200reg_multi_create": (C.c_int32, [_VP, C.c_int32, C.POINTER(IcpConfig), C.c_int32, C.POINTER(_VP)]),
+    "b200reg_multi_destroy": (None, [_VP]),
+    "b200reg_multi_devices": (C.c_int32, [_VP]),
+    "b200reg_multi_nccl_version": (C.c_int32, [_VP]),
+    "b200reg_multi_last_error": (C.c_char_p, [_VP]),
+    "b200reg_multi_launch_count": (C.c_uint64, [_VP]),
+    "b200reg_multi_register_host": (C.c_int32, [_VP, C.c_int32, _VP, _VP, _VP, _VP, _VP, _VP, C.POINTER(C.c_float)]),
     "b200reg_icp_index": (_VP, [_VP]),
     "b200reg_icp_reference_mean": (C.c_int32, [_VP, _VP]),
     "b200reg_voxelgrid": (C.c_int32, [_VP, _VP, C.c_float, C.c_float, C.c_float, C.c_int32, C.c_int32]),
     "b200reg_surface_normals": (C.c_int32, [_VP, _VP, C.c_int32, C.c_float, C.c_float, _VP, _VP, _VP, _VP, C.POINTER(C.c_int32)]),
+    "b200reg_surface_normals_ex": (C.c_int32, [_VP, _VP, C.POINTER(NormalsOptions), C.POINTER(C.c_int32)]),
     "b200reg_map_create": (C.c_int32, [_VP, C.c_double, C.POINTER(_VP)]),
     "b200reg_map_destroy": (None, [_VP, _VP]),
     "b200reg_map_size": (C.c_int64, [_VP]),
@@ -508,15 +523,19 @@ class Cloud:
     def voxelgrid(self, vx, vy, vz, use_centroid=True, average_descriptors=True):
         self.ctx.check(lib().b200reg_voxelgrid(self.ctx.h, self.h, vx, vy, vz, int(use_centroid), int(average_descriptors)))
 
-    def surface_normals(self, knn, max_dist=np.inf, epsilon=0.0, orient_origin=None, keep=()):
+    def surface_normals(self, knn, max_dist=np.inf, epsilon=0.0, orient_origin=None, keep=(), smooth=False):
+        """SurfaceNormalDataPointsFilter on this cloud (writes its normals).  keep: any of densities, eig_values, eig_vectors, matched_ids,
+        mean_dists, lin_plan_curv."""
         n = self.size
         oo = None if orient_origin is None else _f32(orient_origin)
-        dens = np.empty(n, dtype=np.float32) if "densities" in keep else None
-        ev = np.empty((n, 3), dtype=np.float32) if "eig_values" in keep else None
-        lpc = np.empty((n, 3), dtype=np.float32) if "lin_plan_curv" in keep else None
+        shapes = dict(densities=(n,), eig_values=(n, 3), eig_vectors=(n, 9), matched_ids=(n, knn), mean_dists=(n,), lin_plan_curv=(n, 3))
+        out = {k: (np.empty(sh, dtype=np.float32) if k in keep else None) for k, sh in shapes.items()}
+        opt = NormalsOptions(knn=int(knn), max_dist=float(max_dist), epsilon=float(epsilon), smooth_normals=int(smooth),
+                             orient_origin=None if oo is None else oo.ctypes.data, **{k: (None if v is None else v.ctypes.data) for k, v in out.items()})
         deg = C.c_int32(0)
-        self.ctx.check(lib().b200reg_surface_normals(self.ctx.h, self.h, knn, max_dist, epsilon, _p(oo), _p(dens), _p(ev), _p(lpc), C.byref(deg)))
-        return dict(densities=dens, eig_values=ev, lin_plan_curv=lpc, degenerate=deg.value)
+        self.ctx.check(lib().b200reg_surface_normals_ex(self.ctx.h, self.h, C.byref(opt), C.byref(deg)))
+        out["degenerate"] = deg.value
+        return out
 
     def free(self):
         if self.h:
@@ -678,6 +697,59 @@ class Batch:
         try:
             if self.ctx.h:
                 self.close()
+        except Exception:
+            pass
+
+
+class Multi:
+    """b200reg_multi: one process driving every GPU of the box (one host thread + one b200reg_batch per device), pair i -> device
+    i mod G, one ncclAllGather of the results."""
+
+    def __init__(self, devices=None, cfg=None, lanes=0, **kw):
+        self.cfg = cfg if cfg is not None else icp_config(**kw)
+        self.h = _VP()
+        dv = None if not devices else (C.c_int32 * len(devices))(*devices)
+        code = lib().b200reg_multi_create(None if dv is None else C.cast(dv, _VP), 0 if dv is None else len(devices), C.byref(self.cfg), int(lanes),
+                                          C.byref(self.h))
+        if code != OK:
+            msg = lib().b200reg_multi_last_error(self.h).decode("utf-8", "replace") if self.h else "b200reg_multi_create failed (no CUDA device)"
+            self.close()
+            raise _EXC.get(code, B200RegError)(msg)
+
+    @property
+    def devices(self):
+        return int(lib().b200reg_multi_devices(self.h))
+
+    @property
+    def nccl_version(self):
+        return int(lib().b200reg_multi_nccl_version(self.h))
+
+    @property
+    def launch_count(self):
+        return int(lib().b200reg_multi_launch_count(self.h))
+
+    def register_host(self, refs, readings, T_init):
+        """refs / readings: results of Batch.host_clouds().  Returns (T n x 4 x 4, [IcpStats], status, gather_ms)."""
+        n = len(readings[1])
+        Ti = np.ascontiguousarray(np.asarray(T_init, dtype=np.float32).reshape(n, 16))
+        To = np.zeros((n, 16), dtype=np.float32)
+        stats = (IcpStats * max(n, 1))()
+        status = np.zeros(max(n, 1), dtype=np.int32)
+        gms = C.c_float(0)
+        code = lib().b200reg_multi_register_host(self.h, n, C.cast(refs[0], _VP), C.cast(readings[0], _VP), _p(Ti), _p(To), C.cast(stats, _VP), _p(status),
+                                                 C.byref(gms))
+        if code != OK:
+            raise _EXC.get(code, B200RegError)(lib().b200reg_multi_last_error(self.h).decode("utf-8", "replace"))
+        return To.reshape(n, 4, 4), list(stats)[:n], status[:n], gms.value
+
+    def close(self):
+        if self.h:
+            lib().b200reg_multi_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
         except Exception:
             pass
 

@@ -150,6 +150,8 @@ int32_t b200reg_ctx_create(int32_t device, b200reg_ctx** out) {
   ctx->select3 = (s3 && s3[0] == '1') ? 1 : 0;
   const char* hl = getenv("B200REG_HOST_LOOP");
   ctx->hostLoop = (hl && hl[0] == '1') ? 1 : 0;
+  const char* dbg = getenv("B200REG_DEBUG_SYNC");
+  ctx->debugSync = (dbg && dbg[0] == '1') ? 1 : 0;
   const char* seed = getenv("B200REG_KNN_SEED");
   ctx->knnSeed = (seed && seed[0] == '0') ? 0 : 1;
   const char* lanes = getenv("B200REG_KNN_LANES");

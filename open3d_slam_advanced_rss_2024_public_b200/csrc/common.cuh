@@ -39,6 +39,7 @@ struct b200reg_ctx {
   int trace = 0;             // b200reg_ctx_set_trace: stamp kernel starts of the device-resident loop
   int select3 = 0;           // env B200REG_SELECT_3PASS=1: three-launch radix select inside the graph loop too (A/B)
   int hostLoop = 0;          // env B200REG_HOST_LOOP=1: keep the ICP iterate loop on the host (A/B against the graph loop)
+  int debugSync = 0;         // env B200REG_DEBUG_SYNC=1: synchronise after every checked launch (fault localisation)
   int knnSeed = 1;           // env B200REG_KNN_SEED=0: do not seed the k = 1 match with the previous iteration's matches (A/B)
   int knnLanes = 0;          // lanes per query of the k = 1 match kernel: 0 automatic (8; the loop switches to 4 once far queries are rare),
                              // 8, 4, or 1 (the general kernel) forced by env B200REG_KNN_LANES for A/B runs
@@ -219,6 +220,7 @@ void profEnd(b200reg_ctx* ctx);
   do {                                     \
     (ctx)->launches++;                     \
     CUDA_TRY((ctx), cudaGetLastError());   \
+    if ((ctx)->debugSync) CUDA_TRY((ctx), cudaStreamSynchronize((ctx)->stream));   /* env B200REG_DEBUG_SYNC=1: localise a faulting kernel */ \
   } while (0)
 
 #define TRY(expr)                 \

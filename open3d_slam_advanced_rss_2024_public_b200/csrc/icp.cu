@@ -659,6 +659,9 @@ int buildLoopGraph(b200reg_icp* icp) {
   cudaGraph_t g = nullptr, body = nullptr, captured = nullptr;
   cudaGraphExec_t exec = nullptr;
   bool capturing = false;
+  const int debugSync = ctx->debugSync;
+  ctx->debugSync = 0;   // no synchronisation inside a stream capture
+  struct Restore { b200reg_ctx* c; int v; ~Restore() { c->debugSync = v; } } restore{ctx, debugSync};
   const bool useTrim = icp->cfg.trim_ratio > 0.f;
   SelState* st = selState(ctx);
   const int knnBlocks = KNN1_LOOP_MINB * ctx->sm_count /* the resident grid of knn1LoopKernel: its warps pull work from a counter */, redBlocks = 2 * ctx->sm_count;

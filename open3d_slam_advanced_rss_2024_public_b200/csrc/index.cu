@@ -380,8 +380,10 @@ int buildIndex(b200reg_ctx* ctx, const b200reg_cloud* ref, int centre, float cel
   // device grows the cell until the grid fits (the automatic cell gives ~4 cells per point on surface-like clouds)
   const uint64_t cap = std::min<uint64_t>(std::max<uint64_t>(8ull * (uint64_t)m, 1ull << 16), 1ull << 30);
   b200reg_index* ix = nullptr;
+  bool recycled = false;   // (not `ix == recycle`: a freshly allocated index may land at the address of the one just released)
   if (recycle && recycle->mCap >= m && recycle->cellCap >= cap && recycle->cellCap <= 4 * cap && (recycle->nrm || !ref->nrm)) {
     ix = recycle;   // same stream: everything enqueued against the old content runs before the kernels below
+    recycled = true;
     if (!ix->hdrFetched) cudaEventSynchronize(ix->hdrReady);   // the old header copy must have landed before the slot is rewritten
     ix->hdrFetched = false;
     ix->hasNrm = ref->nrm != nullptr;
@@ -390,12 +392,12 @@ int buildIndex(b200reg_ctx* ctx, const b200reg_cloud* ref, int centre, float cel
     ix = new b200reg_index();
   }
   ix->m = m;
-  const size_t tilesCap = ((ix == recycle ? (uint64_t)ix->cellCap : cap) + SCAN_TILE - 1) / SCAN_TILE;
+  const size_t tilesCap = ((recycled ? (uint64_t)ix->cellCap : cap) + SCAN_TILE - 1) / SCAN_TILE;
   const int sblocks = (int)fmin((double)(4 * ctx->sm_count), (double)divUp(m, 256));
   int st = B200REG_OK;
   cudaError_t e = cudaSuccess;
   auto fail = [&](int code) { indexRelease(ctx, ix); return code; };
-  if (ix != recycle) {
+  if (!recycled) {
     ix->cellCap = (uint32_t)cap;
     ix->mCap = m + m / 8;   // head-room: a periodically rebuilt reference (the Mapper's map patch) changes size a little every time
     ix->hasNrm = ref->nrm != nullptr;
@@ -421,15 +423,33 @@ int buildIndex(b200reg_ctx* ctx, const b200reg_cloud* ref, int centre, float cel
   uint32_t* perm = (uint32_t*)ctx->vals0.p;
   const int wide = 8 * ctx->sm_count;   // grid of the streaming passes: 8 blocks of 256 threads per SM
   const int pblocks = (int)std::min<int64_t>(divUp(m, 256), wide);
+#define IDX_STEP(name)                                                                                                   \
+  do {                                                                                                                   \
+    ctx->launches++;                                                                                                     \
+    if (ctx->debugSync) {                                                                                                \
+      const cudaError_t de = cudaStreamSynchronize(ctx->stream);                                                         \
+      if (de != cudaSuccess) return fail(setErr(ctx, B200REG_E_CUDA, "index_build: %s: %s", name, cudaGetErrorString(de))); \
+    }                                                                                                                    \
+  } while (0)
   statsKernel<<<sblocks, 256, 0, ctx->stream>>>(ref->xyz, m, (StatsPartial*)ctx->partials.p);
+  IDX_STEP("statsKernel");
   gridKernel<<<1, 288, 0, ctx->stream>>>((const StatsPartial*)ctx->partials.p, sblocks, (long long)m, centre, cell, ix->cellCap, ix->dHdr);
+  IDX_STEP("gridKernel");
   zeroDirKernel<<<(int)std::min<uint64_t>(wide, (cap / 4 + 255) / 256), 256, 0, ctx->stream>>>(ix->dHdr, ix->dirBase, tileState, tileCounter);
+  IDX_STEP("zeroDirKernel");
   countKernel<<<pblocks, 256, 0, ctx->stream>>>(ref->xyz, m, ix->dHdr, ix->cellStart, keyRank);
+  IDX_STEP("countKernel");
   scanDirKernel<<<(int)std::min<uint64_t>(4 * ctx->sm_count, tilesCap), SCAN_THREADS, 0, ctx->stream>>>(ix->dHdr, ix->cellStart, tileState, tileCounter);
+  IDX_STEP("scanDirKernel");
   permKernel<<<pblocks, 256, 0, ctx->stream>>>(keyRank, m, ix->cellStart, perm);
+  IDX_STEP("permKernel");
   gatherPtsKernel<<<pblocks, 256, 0, ctx->stream>>>(ref->xyz, m, ix->dHdr, perm, ix->pts);
-  if (ref->nrm) gatherNrmKernel<<<pblocks, 256, 0, ctx->stream>>>(ref->nrm, m, perm, ix->nrm);
-  ctx->launches += ref->nrm ? 8 : 7;
+  IDX_STEP("gatherPtsKernel");
+  if (ref->nrm) {
+    gatherNrmKernel<<<pblocks, 256, 0, ctx->stream>>>(ref->nrm, m, perm, ix->nrm);
+    IDX_STEP("gatherNrmKernel");
+  }
+#undef IDX_STEP
   e = cudaGetLastError();
   if (e == cudaSuccess) e = cudaMemcpyAsync(ix->hHdr, ix->dHdr, sizeof(IndexHeader), cudaMemcpyDeviceToHost, ctx->stream);
   if (e == cudaSuccess) e = cudaEventRecord(ix->hdrReady, ctx->stream);

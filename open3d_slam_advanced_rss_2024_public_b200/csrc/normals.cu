@@ -108,7 +108,8 @@ __global__ void __launch_bounds__(128) normalsKernel(const float4* __restrict__ 
                                                      const int* __restrict__ pos, const float* __restrict__ d2, int64_t n, int k,
                                                      int orient, float ox, float oy, float oz, float4* __restrict__ outN,
                                                      float* __restrict__ dens, float* __restrict__ eigv, float* __restrict__ lpc,
-                                                     int* __restrict__ degenerate) {
+                                                     float* __restrict__ eigVec, float* __restrict__ meanDist, const int* __restrict__ ids,
+                                                     float* __restrict__ matchedIds, int* __restrict__ degenerate) {
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   const int* myPos = pos + (int64_t)k * i;
@@ -156,6 +157,17 @@ __global__ void __launch_bounds__(128) normalsKernel(const float4* __restrict__ 
     dens[i] = dd;
   }
   if (eigv) { eigv[3 * i] = (float)val[0]; eigv[3 * i + 1] = (float)val[1]; eigv[3 * i + 2] = (float)val[2]; }
+  if (eigVec)   // serializeEigVec: row-major, eigenvectors in columns (utils.h:90-101; SurfaceNormal.cpp:256-257); zeros when degenerate
+    for (int r = 0; r < 3; ++r) for (int c = 0; c < 3; ++c) eigVec[9 * i + 3 * r + c] = (float)vec[r][c];
+  if (meanDist) {   // SurfaceNormal.cpp:258-268: |point - mean of the neighbours|; numeric_limits<size_t>::max() when degenerate
+    if (isDeg) meanDist[i] = 18446744073709551615.0f;
+    else {
+      const double dx = (double)p.x - mean[0], dy = (double)p.y - mean[1], dz = (double)p.z - mean[2];
+      meanDist[i] = (float)sqrt(dx * dx + dy * dy + dz * dz);
+    }
+  }
+  if (matchedIds)   // matches.ids cast to T (:294-297); -1 where there is no neighbour
+    for (int j = 0; j < k; ++j) matchedIds[(int64_t)k * i + j] = (float)ids[(int64_t)k * i + j];
   if (lpc) {   // SurfaceNormalEstimatorPCA.cpp:86-99
     float l = 0.f, pl = 0.f, cu = 0.f;
     if (!isDeg) {
@@ -168,14 +180,63 @@ __global__ void __launch_bounds__(128) normalsKernel(const float4* __restrict__ 
   }
 }
 
+// smoothNormals (SurfaceNormal.cpp:299-323).  The reference overwrites normals->col(i) inside the loop, so point i averages the
+// ALREADY SMOOTHED normals of its neighbours with a smaller index and the original normals of the others (itself included) — a
+// sequential sweep.  Reproduced exactly by a dependency-ordered pipeline: warps take points in index order from a ticket counter
+// (so every smaller index is held by a running or finished warp: no deadlock), wait for the done flags of their lower-index
+// neighbours, and read `newN` for those and `oldN` for the rest.  The fp32 sum runs in neighbour order (ascending (d2, index)),
+// the sign test is the reference's currentNormal.dot(normal) > 0 on individually rounded operations.
+__global__ void __launch_bounds__(256) smoothNormalsKernel(const float4* __restrict__ oldN, float4* newN, const int* __restrict__ ids,
+                                                           const float* __restrict__ d2, long long n, int k, unsigned long long* ticket,
+                                                           int* done) {
+  const int lane = threadIdx.x & 31;
+  for (;;) {
+    long long i = 0;
+    if (lane == 0) i = (long long)atomicAdd(ticket, 1ull);
+    i = __shfl_sync(0xffffffffu, i, 0);
+    if (i >= n) return;
+    const float4 cur = oldN[i];
+    float mx = 0.f, my = 0.f, mz = 0.f;
+    int cnt = 0;
+    for (int j0 = 0; j0 < k; j0 += 32) {
+      const int j = j0 + lane;
+      bool valid = false;
+      float cx = 0.f, cy = 0.f, cz = 0.f;
+      if (j < k && d2[(long long)k * i + j] != CUDART_INF_F) {
+        const int id = ids[(long long)k * i + j];
+        float4 nb;
+        if (id < i) {   // already smoothed in the reference's sweep
+          while (atomicAdd(&done[id], 0) == 0) __nanosleep(20);
+          __threadfence();
+          nb = __ldcg(newN + id);
+        } else nb = oldN[id];
+        const float dot = __fadd_rn(__fadd_rn(__fmul_rn(cur.x, nb.x), __fmul_rn(cur.y, nb.y)), __fmul_rn(cur.z, nb.z));
+        const float sgn = (dot > 0.f) ? 1.f : -1.f;   // mean += normal, else mean -= normal (flip)
+        cx = sgn * nb.x; cy = sgn * nb.y; cz = sgn * nb.z;
+        valid = true;
+      }
+      const unsigned vm = __ballot_sync(0xffffffffu, valid);
+      for (int jj = 0; jj < 32; ++jj) {   // neighbour order, every lane keeps the same running sum
+        const float vx = __shfl_sync(0xffffffffu, cx, jj), vy = __shfl_sync(0xffffffffu, cy, jj), vz = __shfl_sync(0xffffffffu, cz, jj);
+        if (vm & (1u << jj)) { mx = __fadd_rn(mx, vx); my = __fadd_rn(my, vy); mz = __fadd_rn(mz, vz); ++cnt; }
+      }
+    }
+    if (lane == 0) {
+      const float fn = (float)cnt;   // mean / T(n): 0 / 0 = NaN when the point has no neighbour at all, like the reference
+      newN[i] = make_float4(__fdiv_rn(mx, fn), __fdiv_rn(my, fn), __fdiv_rn(mz, fn), 0.f);
+      __threadfence();
+      atomicExch(&done[i], 1);
+    }
+  }
+}
+
 }  // namespace
 
-extern "C" int32_t b200reg_surface_normals(b200reg_ctx* ctx, b200reg_cloud* inout, int32_t knn, float max_dist, float epsilon,
-                                           const float* orient_origin, float* densities_out, float* eig_values_out,
-                                           float* lin_plan_curv_out, int32_t* degenerate_count) {
-  if (!ctx || !inout) return setErr(ctx, B200REG_E_INVALID_PARAM, "surface_normals: bad arguments");
+extern "C" int32_t b200reg_surface_normals_ex(b200reg_ctx* ctx, b200reg_cloud* inout, const b200reg_normals_options* opt, int32_t* degenerate_count) {
+  if (!ctx || !inout || !opt) return setErr(ctx, B200REG_E_INVALID_PARAM, "surface_normals: bad arguments");
+  const int32_t knn = opt->knn;
   if (knn < 3) return setErr(ctx, B200REG_E_INVALID_PARAM, "SurfaceNormalDataPointsFilter: knn must be >= 3");   // SurfaceNormal.h:69
-  if (!(epsilon >= 0.f) || !(max_dist >= 0.f)) return setErr(ctx, B200REG_E_INVALID_PARAM, "SurfaceNormalDataPointsFilter: epsilon/maxDist must be >= 0");
+  if (!(opt->epsilon >= 0.f) || !(opt->max_dist >= 0.f)) return setErr(ctx, B200REG_E_INVALID_PARAM, "SurfaceNormalDataPointsFilter: epsilon/maxDist must be >= 0");
   const int64_t n = inout->n;
   if (degenerate_count) *degenerate_count = 0;
   if (n == 0) return B200REG_OK;
@@ -185,28 +246,56 @@ extern "C" int32_t b200reg_surface_normals(b200reg_ctx* ctx, b200reg_cloud* inou
   TRY(buildIndex(ctx, inout, 0, 0.f, &ix));
   // the list kernel walks the cloud in the index's sorted order (null queries); the one-thread kernel takes it as it lies
   const float4* qs = (ctx->knnLanes == 1 || knn > 32) ? inout->xyz : nullptr;
-  int st = runKnn(ctx, ix, qs, n, nullptr, knn, max_dist, 1, 0);
+  int st = runKnn(ctx, ix, qs, n, nullptr, knn, opt->max_dist, 1, 0);
   if (st != B200REG_OK) { b200reg_index_free(ctx, ix); return st; }
   if (!inout->nrm) {
     cudaError_t e = devAlloc(ctx, &inout->nrm, sizeof(float4) * (size_t)inout->cap);
     if (e != cudaSuccess) { b200reg_index_free(ctx, ix); return setErr(ctx, B200REG_E_OOM, "surface_normals: %s", cudaGetErrorString(e)); }
   }
-  const size_t extra = sizeof(float) * (size_t)n * 7 + 64;
+  // device staging of the optional outputs: [densities n | eigValues 3n | linPlanCurv 3n | eigVectors 9n | meanDists n | matchedIds knn n]
+  const size_t extra = sizeof(float) * (size_t)n * (17 + (size_t)knn) + 64;
   st = ensureBuf(ctx, ctx->misc, extra);
   if (st != B200REG_OK) { b200reg_index_free(ctx, ix); return st; }
-  float* dDens = densities_out ? (float*)ctx->misc.p : nullptr;
-  float* dEig = eig_values_out ? (float*)ctx->misc.p + n : nullptr;
-  float* dLpc = lin_plan_curv_out ? (float*)ctx->misc.p + 4 * n : nullptr;
+  float* base = (float*)ctx->misc.p;
+  float* dDens = opt->densities ? base : nullptr;
+  float* dEig = opt->eig_values ? base + n : nullptr;
+  float* dLpc = opt->lin_plan_curv ? base + 4 * n : nullptr;
+  float* dVec = opt->eig_vectors ? base + 7 * n : nullptr;
+  float* dMd = opt->mean_dists ? base + 16 * n : nullptr;
+  float* dMi = opt->matched_ids ? base + 17 * n : nullptr;
   int* dDeg = (int*)((char*)ctx->dstate + 32768);
   cudaMemsetAsync(dDeg, 0, sizeof(int), ctx->stream);
-  const float ox = orient_origin ? orient_origin[0] : 0.f, oy = orient_origin ? orient_origin[1] : 0.f, oz = orient_origin ? orient_origin[2] : 0.f;
+  const float* oo = opt->orient_origin;
+  const float ox = oo ? oo[0] : 0.f, oy = oo ? oo[1] : 0.f, oz = oo ? oo[2] : 0.f;
   normalsKernel<<<divUp(n, 128), 128, 0, ctx->stream>>>(inout->xyz, ix->pts, (const int*)ctx->matchPos.p, (const float*)ctx->matchD2.p, n, knn,
-                                                        orient_origin ? 1 : 0, ox, oy, oz, inout->nrm, dDens, dEig, dLpc, dDeg);
+                                                        oo ? 1 : 0, ox, oy, oz, inout->nrm, dDens, dEig, dLpc, dVec, dMd, (const int*)ctx->matchIds.p, dMi, dDeg);
   ctx->launches++;
   cudaError_t e = cudaGetLastError();
-  if (e == cudaSuccess && densities_out) e = cudaMemcpyAsync(densities_out, dDens, sizeof(float) * (size_t)n, cudaMemcpyDeviceToHost, ctx->stream);
-  if (e == cudaSuccess && eig_values_out) e = cudaMemcpyAsync(eig_values_out, dEig, sizeof(float) * 3 * (size_t)n, cudaMemcpyDeviceToHost, ctx->stream);
-  if (e == cudaSuccess && lin_plan_curv_out) e = cudaMemcpyAsync(lin_plan_curv_out, dLpc, sizeof(float) * 3 * (size_t)n, cudaMemcpyDeviceToHost, ctx->stream);
+  if (e == cudaSuccess && opt->smooth_normals) {
+    // old normals -> scratch, smoothed normals -> the cloud; flags + ticket in a scratch of their own
+    e = (ensureBuf(ctx, ctx->keys1, sizeof(float4) * (size_t)n) == B200REG_OK && ensureBuf(ctx, ctx->vals1, sizeof(int) * (size_t)n + 64) == B200REG_OK)
+            ? cudaSuccess : cudaErrorMemoryAllocation;
+    if (e == cudaSuccess) e = cudaMemcpyAsync(ctx->keys1.p, inout->nrm, sizeof(float4) * (size_t)n, cudaMemcpyDeviceToDevice, ctx->stream);
+    if (e == cudaSuccess) e = cudaMemsetAsync(ctx->vals1.p, 0, sizeof(int) * (size_t)n + 64, ctx->stream);
+    if (e == cudaSuccess) {
+      int* done = (int*)ctx->vals1.p;
+      unsigned long long* ticket = (unsigned long long*)((char*)ctx->vals1.p + ((sizeof(int) * (size_t)n + 15) / 16) * 16);
+      const int blocks = (int)fmin((double)(4 * ctx->sm_count), (double)divUp(n * 32, 256));   // resident grid: waiting warps must not starve running ones
+      smoothNormalsKernel<<<blocks, 256, 0, ctx->stream>>>((const float4*)ctx->keys1.p, inout->nrm, (const int*)ctx->matchIds.p,
+                                                           (const float*)ctx->matchD2.p, (long long)n, knn, ticket, done);
+      ctx->launches++;
+      e = cudaGetLastError();
+    }
+  }
+  auto d2h = [&](float* host, const float* dev, size_t count) {
+    if (e == cudaSuccess && host) e = cudaMemcpyAsync(host, dev, sizeof(float) * count, cudaMemcpyDeviceToHost, ctx->stream);
+  };
+  d2h(opt->densities, dDens, (size_t)n);
+  d2h(opt->eig_values, dEig, 3 * (size_t)n);
+  d2h(opt->lin_plan_curv, dLpc, 3 * (size_t)n);
+  d2h(opt->eig_vectors, dVec, 9 * (size_t)n);
+  d2h(opt->mean_dists, dMd, (size_t)n);
+  d2h(opt->matched_ids, dMi, (size_t)knn * (size_t)n);
   if (e == cudaSuccess) e = cudaMemcpyAsync(ctx->pinned, dDeg, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream);
   if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
   const bool indexOk = (e != cudaSuccess) || indexHeader(ctx, ix) != nullptr;   // non-finite coordinates: the header carries the verdict
@@ -215,4 +304,14 @@ extern "C" int32_t b200reg_surface_normals(b200reg_ctx* ctx, b200reg_cloud* inou
   if (!indexOk) return setErr(ctx, B200REG_E_INVALID_PARAM, "SurfaceNormalDataPointsFilter: non-finite coordinates in the cloud");
   if (degenerate_count) *degenerate_count = *(const int*)ctx->pinned;
   return B200REG_OK;
+}
+
+extern "C" int32_t b200reg_surface_normals(b200reg_ctx* ctx, b200reg_cloud* inout, int32_t knn, float max_dist, float epsilon,
+                                           const float* orient_origin, float* densities_out, float* eig_values_out,
+                                           float* lin_plan_curv_out, int32_t* degenerate_count) {
+  b200reg_normals_options o;
+  memset(&o, 0, sizeof(o));
+  o.knn = knn; o.max_dist = max_dist; o.epsilon = epsilon; o.orient_origin = orient_origin;
+  o.densities = densities_out; o.eig_values = eig_values_out; o.lin_plan_curv = lin_plan_curv_out;
+  return b200reg_surface_normals_ex(ctx, inout, &o, degenerate_count);
 }

@@ -139,9 +139,7 @@ CudaSurfaceNormalDataPointsFilter::CudaSurfaceNormalDataPointsFilter(const PM::P
       keepEigenValues(get<bool>("keepEigenValues")), keepEigenVectors(get<bool>("keepEigenVectors")), keepMatchedIds(get<bool>("keepMatchedIds")),
       keepMeanDist(get<bool>("keepMeanDist")), keepSurfaceDescriptors(get<bool>("keepSurfaceDescriptors")), sortEigen(get<bool>("sortEigen")),
       smoothNormals(get<bool>("smoothNormals")), device(get<int>("device")) {
-  // descriptors this round's kernel does not produce are refused loudly instead of being left uninitialised
-  if (keepEigenVectors || keepMatchedIds || keepMeanDist) throw PM::InvalidParameter("CudaSurfaceNormalDataPointsFilter: keepEigenVectors / keepMatchedIds / keepMeanDist are not produced by the device kernel yet");
-  if (smoothNormals) throw PM::InvalidParameter("CudaSurfaceNormalDataPointsFilter: smoothNormals is not supported (order-dependent in the reference, SURVEY 9.5)");
+  if (smoothNormals && !keepNormals) throw PM::InvalidParameter("CudaSurfaceNormalDataPointsFilter: smoothNormals needs keepNormals (the reference dereferences an empty optional, SurfaceNormal.cpp:303)");
 }
 PM::DataPoints CudaSurfaceNormalDataPointsFilter::filter(const PM::DataPoints& input) { PM::DataPoints o(input); inPlaceFilter(o); return o; }
 void CudaSurfaceNormalDataPointsFilter::inPlaceFilter(PM::DataPoints& cloud) {
@@ -151,24 +149,38 @@ void CudaSurfaceNormalDataPointsFilter::inPlaceFilter(PM::DataPoints& cloud) {
   if ((int64_t)dsum != cloud.descriptors.rows()) throw PM::DataPoints::InvalidField("SurfaceNormalDataPointsFilter: Error, descriptor labels do not match descriptor data");
   const int64_t n = cloud.features.cols();
   // label order of the reference (SurfaceNormal.cpp:126-144); allocateDescriptor reuses / appends like DataPoints::allocateFields
-  int rowN = -1, rowD = -1, rowE = -1, rowL = -1, rowP = -1, rowC = -1;
+  int rowN = -1, rowD = -1, rowE = -1, rowL = -1, rowP = -1, rowC = -1, rowV = -1, rowI = -1, rowM = -1;
   if (keepNormals) rowN = cloud.allocateDescriptor("normals", 3);
   if (keepDensities) rowD = cloud.allocateDescriptor("densities", 1);
   if (keepEigenValues) rowE = cloud.allocateDescriptor("eigValues", 3);
+  if (keepEigenVectors) rowV = cloud.allocateDescriptor("eigVectors", 9);
+  if (keepMatchedIds) rowI = cloud.allocateDescriptor("matchedIds", (int)knn);
+  if (keepMeanDist) rowM = cloud.allocateDescriptor("meanDists", 1);
   if (keepSurfaceDescriptors) { rowL = cloud.allocateDescriptor("linearity", 1); rowP = cloud.allocateDescriptor("planarity", 1); rowC = cloud.allocateDescriptor("curvature", 1); }
   if (n == 0) return;
   b200reg_ctx* ctx = contextFor(device);
   CloudGuard g(ctx);
   check(ctx, b200reg_cloud_upload_f32(ctx, cloud.features.data(), 4, nullptr, n, &g.c));
   std::vector<float> dens(keepDensities ? (size_t)n : 0), eig(keepEigenValues ? 3 * (size_t)n : 0), lpc(keepSurfaceDescriptors ? 3 * (size_t)n : 0), nrm(3 * (size_t)n);
+  std::vector<float> vec(keepEigenVectors ? 9 * (size_t)n : 0), mid(keepMatchedIds ? (size_t)knn * (size_t)n : 0), md(keepMeanDist ? (size_t)n : 0);
   int32_t degenerate = 0;
-  check(ctx, b200reg_surface_normals(ctx, g.c, (int32_t)knn, maxDist, epsilon, nullptr, keepDensities ? dens.data() : nullptr,
-                                     keepEigenValues ? eig.data() : nullptr, keepSurfaceDescriptors ? lpc.data() : nullptr, &degenerate));
+  b200reg_normals_options opt{};
+  opt.knn = (int32_t)knn; opt.max_dist = maxDist; opt.epsilon = epsilon; opt.smooth_normals = smoothNormals ? 1 : 0;
+  opt.densities = keepDensities ? dens.data() : nullptr;
+  opt.eig_values = keepEigenValues ? eig.data() : nullptr;
+  opt.eig_vectors = keepEigenVectors ? vec.data() : nullptr;
+  opt.matched_ids = keepMatchedIds ? mid.data() : nullptr;
+  opt.mean_dists = keepMeanDist ? md.data() : nullptr;
+  opt.lin_plan_curv = keepSurfaceDescriptors ? lpc.data() : nullptr;
+  check(ctx, b200reg_surface_normals_ex(ctx, g.c, &opt, &degenerate));
   check(ctx, b200reg_cloud_download_f32(ctx, g.c, nullptr, 4, nrm.data()));
   for (int64_t c = 0; c < n; ++c) {
     if (keepNormals) for (int r = 0; r < 3; ++r) cloud.descriptors(rowN + r, c) = nrm[3 * c + r];
     if (keepDensities) cloud.descriptors(rowD, c) = dens[c];
     if (keepEigenValues) for (int r = 0; r < 3; ++r) cloud.descriptors(rowE + r, c) = eig[3 * c + r];   // ascending (documented order; sortEigen is therefore always honoured)
+    if (keepEigenVectors) for (int r = 0; r < 9; ++r) cloud.descriptors(rowV + r, c) = vec[9 * c + r];   // serializeEigVec order (utils.h:90-101)
+    if (keepMatchedIds) for (unsigned r = 0; r < knn; ++r) cloud.descriptors(rowI + (int)r, c) = mid[(size_t)knn * c + r];
+    if (keepMeanDist) cloud.descriptors(rowM, c) = md[c];
     if (keepSurfaceDescriptors) { cloud.descriptors(rowL, c) = lpc[3 * c]; cloud.descriptors(rowP, c) = lpc[3 * c + 1]; cloud.descriptors(rowC, c) = lpc[3 * c + 2]; }
   }
   (void)degenerate;

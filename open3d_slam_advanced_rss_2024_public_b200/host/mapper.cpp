@@ -131,7 +131,9 @@ bool Mapper::insert() {
   }
   const b200reg_crop_spec vol = at(params_.mapBuilderCropper, mapToRangeSensor_);
   if (b200reg_map_insert_cloud64(ctx_, map_, merge_, mapToRangeSensor_, &vol) != B200REG_OK) {
+    const std::string earlier = error_;   // a failed registration only keeps the estimate; its message must not be lost here
     error_ = b200reg_last_error(ctx_);
+    if (!earlier.empty()) error_ = earlier + " | " + error_;
     return false;
   }
   std::memcpy(cropperPose_, mapToRangeSensor_, sizeof(cropperPose_));   // mapBuilderCropper_->setPose(mapToRangeSensor) (Submap.cpp:86)

@@ -1215,6 +1215,34 @@ extern "C" int32_t orc_surface_normals(const float* feat, int32_t stride, int64_
   return ORC_OK;
 }
 
+// smoothNormals (SurfaceNormal.cpp:299-323): one sweep in index order that OVERWRITES normals->col(i) as it goes, so point i
+// averages the already smoothed normals of its neighbours with a smaller index and the original ones of the others (itself
+// included); each neighbour's normal is flipped to the side of the point's own (original) normal; T = float sums in neighbour order.
+extern "C" int32_t orc_smooth_normals(const float* feat, int32_t stride, int64_t n, int32_t knn, float max_dist, int32_t nthreads,
+                                      float* normals /* in/out, 3 per point */) {
+  if (knn < 3) return ORC_E_PARAM;
+  std::vector<int32_t> ids((size_t)knn * n);
+  std::vector<float> d2((size_t)knn * n);
+  void* tree = orc_kdtree_build(feat, stride, n);
+  orc_kdtree_knn(tree, feat, stride, n, knn, max_dist, 1, ids.data(), d2.data(), nthreads);
+  orc_kdtree_free(tree);
+  for (int64_t i = 0; i < n; ++i) {   // sequential by construction
+    const float cur[3] = {normals[3 * i], normals[3 * i + 1], normals[3 * i + 2]};
+    float mean[3] = {0.f, 0.f, 0.f};
+    int cnt = 0;
+    for (int j = 0; j < knn; ++j) {
+      if (d2[(size_t)knn * i + j] == kInf) continue;
+      const float* nb = normals + 3 * (int64_t)ids[(size_t)knn * i + j];
+      const float dot = (cur[0] * nb[0] + cur[1] * nb[1]) + cur[2] * nb[2];
+      if (dot > 0.f) { mean[0] += nb[0]; mean[1] += nb[1]; mean[2] += nb[2]; }
+      else { mean[0] -= nb[0]; mean[1] -= nb[1]; mean[2] -= nb[2]; }
+      ++cnt;
+    }
+    for (int c = 0; c < 3; ++c) normals[3 * i + c] = mean[c] / (float)cnt;
+  }
+  return ORC_OK;
+}
+
 // ================================================================================================================
 // open3d_slam side (fp64): croppers, transform, map voxelisation, Open3D VoxelDownSample, Open3D -> pointmatcher
 // citations relative to open3d_slam_rsl/open3d_slam/open3d_slam/

@@ -106,6 +106,9 @@ int32_t orc_surface_normals(const float* feat, int32_t stride, int64_t n, int32_
                             float* normals, float* densities, float* eig_values, float* eig_vectors, float* matched_ids,
                             float* mean_dists, float* lin_plan_curv, int32_t* degenerate_count);
 
+/* smoothNormals (SurfaceNormal.cpp:299-323): the in-place sequential sweep, on the normals orc_surface_normals returned */
+int32_t orc_smooth_normals(const float* feat, int32_t stride, int64_t n, int32_t knn, float max_dist, int32_t nthreads, float* normals);
+
 /* ---- open3d_slam side (fp64) ---- */
 enum { ORC_CROP_MAX_RADIUS = 0, ORC_CROP_MIN_RADIUS = 1, ORC_CROP_MINMAX_RADIUS = 2, ORC_CROP_CYLINDER = 3 };
 typedef struct orc_crop_spec {

@@ -278,6 +278,18 @@ def surface_normals(feat, knn, max_dist=np.inf, precision=ORC_MIXED, nthreads=8,
     return out
 
 
+def smooth_normals(feat, normals, knn, max_dist=np.inf, nthreads=8):
+    """smoothNormals of SurfaceNormal.cpp:299-323 (sequential in-place sweep); returns the smoothed copy."""
+    feat = _f32(feat)
+    out = np.array(normals, dtype=np.float32, order="C", copy=True)
+    L = lib()
+    L.orc_smooth_normals.restype = C.c_int32
+    L.orc_smooth_normals.argtypes = [C.c_void_p, C.c_int32, C.c_int64, C.c_int32, C.c_float, C.c_int32, C.c_void_p]
+    st = L.orc_smooth_normals(_p(feat), feat.shape[1], feat.shape[0], knn, max_dist, nthreads, _p(out))
+    assert st == 0, st
+    return out
+
+
 def crop_spec(kind, center, rmin=0.0, rmax=0.0, zmin=0.0, zmax=0.0, invert=False):
     s = CropSpec(kind=kind, invert=int(invert), rmin=rmin, rmax=rmax, zmin=zmin, zmax=zmax)
     for i in range(3):

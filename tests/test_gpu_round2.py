@@ -321,3 +321,98 @@ def test_config5_large_map_sampled_brute_force(ctx, oracle):
     own = rng.choice(m, 200_000, replace=False)
     ids_g, d2_g, _ = ctx.knn(ix, ctx.upload(ref[own]), k=1, max_dist=0.5)
     assert np.array_equal(ids_g[:, 0], own.astype(np.int32)) and not d2_g.any()
+
+
+def test_multi_gpu_host_matches_single_device_batch(ctx, oracle):
+    """b200reg_multi (one process, one host thread + batch per visible GPU, pair i -> device i mod G, ONE ncclAllGather of the
+    96-byte records): T / status come out of the gathered block and equal the single-device batch bit for bit.  On a 1-GPU box
+    G = 1 (the communicator has one rank); the 2/4/8-GPU runs are profiles/r2/config4_multi_*.json."""
+    from open3d_slam_advanced_rss_2024_public_b200 import capi
+    kw = dict(knn=1, max_dist=1.0, trim_ratio=0.8, max_iter=40)
+    P = _pairs(oracle, 5, 4800)
+    far = np.eye(4, dtype=np.float32)
+    far[:3, 3] = 1000.0
+    P.insert(2, dict(ref=P[0]["ref"], rn=P[0]["rn"], q=P[0]["q"], Ti=far))
+    Tis = np.stack([p["Ti"] for p in P])
+    b = capi.Batch(ctx, lanes=2, **kw)
+    refs_h = b.host_clouds([(p["ref"], p["rn"]) for p in P])
+    reads_h = b.host_clouds([(p["q"], None) for p in P])
+    T1, stats1, status1 = b.register_host(refs_h, reads_h, Tis)
+    b.close()
+    m = capi.Multi(None, lanes=2, **kw)      # every visible GPU
+    assert m.devices >= 1 and m.nccl_version > 0
+    for rep in range(2):
+        T, stats, status, gather_ms = m.register_host(refs_h, reads_h, Tis)
+        assert list(status) == list(status1) and status[2] == capi.E_NOT_CONVERGED
+        assert np.array_equal(T, T1) and gather_ms >= 0.0
+        assert [s.iterations for s in stats] == [s.iterations for s in stats1]
+    assert m.launch_count > 0
+    m.close()
+    m1 = capi.Multi([0], lanes=1, **kw)
+    T, _, status, _ = m1.register_host(refs_h, reads_h, Tis)
+    assert np.array_equal(T, T1)
+    m1.close()
+
+
+# ---------------------------------------------------------------------------------------------------------------------------
+# SURVEY a14: the complete descriptor set of SurfaceNormalDataPointsFilter (SurfaceNormal.cpp:126-144,247-323)
+# ---------------------------------------------------------------------------------------------------------------------------
+def _normals_cloud(seed, n=6000):
+    rng = np.random.default_rng(seed)
+    c = scenes.config2(m=n, n_beams=8, n_az=128, scene_seed=seed, size=(30.0, 30.0, 6.0), n_boxes=8, n_cyl=5)
+    x = c["map_xyz"].astype(np.float32)
+    x[:5] = x[5]                               # exact duplicates: ties resolved by index
+    iso = np.array([[200.0, 200.0, 50.0], [-300.0, 10.0, 5.0]], np.float32)   # points with no neighbour inside maxDist but themselves
+    line = np.stack([np.linspace(400, 401, 12), np.full(12, 7.0), np.full(12, 1.0)], axis=1).astype(np.float32)   # collinear: degenerate covariance
+    return np.concatenate([x, iso, line, rng.uniform(0, 30, (40, 3)).astype(np.float32)])
+
+
+@pytest.mark.parametrize("knn,max_dist", [(10, 1.0), (20, np.inf), (5, 0.4)])
+def test_surface_normals_all_descriptors_match_oracle(ctx, oracle, knn, max_dist):
+    """keepEigenVectors (9, row-major), keepMatchedIds (knn, as floats), keepMeanDist besides the round-1 outputs: matched ids are
+    bit-exact (the k-NN contract), everything else is within 1e-5 of the oracle's mixed-precision lane, degenerate points included."""
+    x = _normals_cloud(4900 + knn)
+    f = oracle.feat4(x)
+    keep = ("densities", "eig_values", "eig_vectors", "matched_ids", "mean_dists", "lin_plan_curv")
+    c = ctx.upload(f)
+    g = c.surface_normals(knn, max_dist=max_dist, keep=keep)
+    _, nrm = c.download(normals=True)
+    o = oracle.surface_normals(f, knn, max_dist=max_dist, precision=oracle.ORC_MIXED, nthreads=8, keep=("normals",) + keep)
+    assert g["degenerate"] == o["degenerate"] and g["degenerate"] > 0
+    assert np.array_equal(g["matched_ids"], o["matched_ids"])
+    assert np.array_equal(g["mean_dists"] > 1e18, o["mean_dists"] > 1e18)           # numeric_limits<size_t>::max() marks degenerate points
+    ok = o["mean_dists"] < 1e18
+    assert np.abs(g["mean_dists"][ok] - o["mean_dists"][ok]).max() <= 1e-5
+    assert np.abs(g["eig_values"] - o["eig_values"]).max() <= 1e-5 * max(1.0, float(np.abs(o["eig_values"]).max()))
+    assert np.abs(nrm - o["normals"]).max() <= 1e-5
+    # eigenvectors: same solver on both sides, so the signs agree as well; columns are unit vectors, column 0 is the normal
+    gv, ov = g["eig_vectors"].reshape(-1, 3, 3), o["eig_vectors"].reshape(-1, 3, 3)
+    # a pair of (near-)equal eigenvalues makes its eigenvectors arbitrary inside their plane: compare well-separated ones
+    ev = o["eig_values"]
+    sep = (np.abs(ev[:, 1] - ev[:, 0]) > 1e-4 * np.abs(ev[:, 2]) + 1e-12) & (np.abs(ev[:, 2] - ev[:, 1]) > 1e-4 * np.abs(ev[:, 2]) + 1e-12) & ok
+    assert sep.sum() > 0.8 * ok.sum()
+    assert np.abs(gv[sep] - ov[sep]).max() <= 2e-4
+    assert np.abs(gv[ok][:, :, 0] - nrm[ok]).max() <= 1e-6
+    assert not gv[~ok].any()
+    assert np.abs(g["densities"] - o["densities"]).max() <= 1e-5 * max(1.0, float(o["densities"].max()))
+    assert np.abs(g["lin_plan_curv"] - o["lin_plan_curv"]).max() <= 1e-4
+
+
+@pytest.mark.parametrize("knn,max_dist", [(10, 1.0), (6, 0.3)])
+def test_surface_normals_smoothing_reproduces_the_sequential_sweep(ctx, oracle, knn, max_dist):
+    """smoothNormals overwrites normals->col(i) inside the loop (SurfaceNormal.cpp:299-323): point i sees the smoothed normals of its
+    lower-index neighbours.  The device pipeline (ordered tickets + done flags) gives the sweep's result bit for bit when fed the same
+    un-smoothed normals; points whose only neighbour is themselves keep theirs, points with none become NaN like mean / 0."""
+    from open3d_slam_advanced_rss_2024_public_b200 import capi
+    x = _normals_cloud(5000 + knn, n=20000)
+    f = oracle.feat4(x)
+    c = ctx.upload(f)
+    c.surface_normals(knn, max_dist=max_dist)
+    _, raw = c.download(normals=True)
+    c2 = ctx.upload(f)
+    c2.surface_normals(knn, max_dist=max_dist, smooth=True)
+    _, sm = c2.download(normals=True)
+    want = oracle.smooth_normals(f, raw, knn, max_dist=max_dist)
+    assert np.array_equal(np.isnan(sm), np.isnan(want))
+    assert np.array_equal(sm[~np.isnan(sm)].view(np.uint32), want[~np.isnan(want)].view(np.uint32))
+    assert np.abs(sm - raw)[~np.isnan(sm)].max() > 1e-3      # and it did something
