@@ -162,6 +162,13 @@ int32_t b200reg_point_to_plane_covariance(b200reg_ctx* ctx, const b200reg_cloud*
                                           const float* d2, const float* w, int32_t k, const double mean_reading[3],
                                           const double mean_reference[3], const float T[16], float sensor_std_dev, double cov_out[36]);
 
+/* PointToPlaneErrorMinimizer::getResidualError / computeResidualError (ErrorMinimizers/PointToPlane.cpp:372-422): over the ErrorElements
+ * pairs (finite distance, non-zero weight) the sum of w ((reading - reference) . n_reference)^2, accumulated in fp64; force2D drops z.
+ * (getOverlap, :426-521: the device clouds carry no simpleSensorNoise / densities descriptors, for which the reference itself returns
+ * getWeightedPointUsedRatio() (:477-481) — b200reg_step_stats.weighted_point_used_ratio / b200reg_icp_stats.overlap_ratio.) */
+int32_t b200reg_point_to_plane_residual(b200reg_ctx* ctx, const b200reg_cloud* reading, const b200reg_cloud* reference, const int32_t* ids,
+                                        const float* d2, const float* w, int32_t k, int32_t force2D, double* residual_out, int64_t* kept_out);
+
 /* PointToPlaneErrorMinimizer::compute tail (PointToPlane.cpp:185-368): solve (LLT, rank-reduced minimum norm when
  * singular), Rodrigues, un-centre.  Host arithmetic in fp64; T_out = the 4x4 step transform rounded to fp32. */
 int32_t b200reg_solve_point_to_plane(const double A[36], const double b[6], const double mean_reading[3],

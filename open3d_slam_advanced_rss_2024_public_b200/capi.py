@@ -154,6 +154,7 @@ SYMBOLS = {
     "b200reg_dist_outlier": (C.c_int32, [_VP, C.c_int32, _VP, C.c_int64, C.c_float, C.POINTER(C.c_float), _VP]),
     "b200reg_surface_normal_outlier": (C.c_int32, [_VP, _VP, _VP, C.c_int64, _VP, C.c_int32, C.c_int64, C.c_float, _VP]),
     "b200reg_point_to_plane": (C.c_int32, [_VP, _VP, _VP, _VP, _VP, _VP, C.c_int32, C.c_int32, _VP, _VP, C.POINTER(StepStats)]),
+    "b200reg_point_to_plane_residual": (C.c_int32, [_VP, _VP, _VP, _VP, _VP, _VP, C.c_int32, C.c_int32, C.POINTER(C.c_double), C.POINTER(C.c_int64)]),
     "b200reg_solve_point_to_plane": (C.c_int32, [_VP, _VP, _VP, _VP, C.c_int32, C.c_int32, _VP, _VP]),
     "b200reg_icp_create": (C.c_int32, [_VP, C.POINTER(IcpConfig), C.POINTER(_VP)]),
     "b200reg_icp_destroy": (None, [_VP]),
@@ -414,6 +415,15 @@ class Context:
         st = StepStats()
         self.check(lib().b200reg_point_to_plane(self.h, reading.h, reference.h, _p(ids), _p(d2), _p(w), k, int(force2D), _p(A), _p(b), C.byref(st)))
         return A, b, st
+
+    def point_to_plane_residual(self, reading, reference, ids, d2, w, force2D=False):
+        """PointToPlaneErrorMinimizer::getResidualError on explicit matches / weights: (sum w ((p - q) . n)^2, kept pairs)."""
+        ids = np.ascontiguousarray(ids, dtype=np.int32)
+        d2, w = _f32(d2), _f32(w)
+        k = ids.size // max(reading.size, 1)
+        res, kept = C.c_double(0), C.c_int64(0)
+        self.check(lib().b200reg_point_to_plane_residual(self.h, reading.h, reference.h, _p(ids), _p(d2), _p(w), k, int(force2D), C.byref(res), C.byref(kept)))
+        return res.value, kept.value
 
     def voxel_down_sample(self, voxel, xyz, nrm=None):
         """o3d_slam::voxelize / Open3D VoxelDownSample on a host fp64 cloud (ascending key order)."""

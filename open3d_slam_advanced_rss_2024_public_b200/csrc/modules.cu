@@ -168,6 +168,24 @@ __global__ void __launch_bounds__(256) p2pMomentsKernel(PairArgs A, double* __re
   blockReduceStore<P2P_N>(m, partials);
 }
 
+// PointToPlaneErrorMinimizer::computeResidualError (PointToPlane.cpp:372-407): 0 sum w ((p - q) . n)^2 | 1 kept pairs.  A.alpha != 0: force2D
+constexpr int RES_N = 2;
+__global__ void __launch_bounds__(256) residualKernel(PairArgs A, double* __restrict__ partials) {
+  double m[RES_N] = {0.0, 0.0};
+  const bool twoD = A.alpha != 0.0;
+  for (int64_t o = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; o < A.total; o += (int64_t)gridDim.x * blockDim.x) {
+    double w;
+    int id;
+    if (!pairOf(A, o, w, id)) continue;
+    const float4 p = A.reading[o / A.k], q = A.refPts[id], n = A.refNrm[id];
+    double dot = ((double)p.x - (double)q.x) * (double)n.x + ((double)p.y - (double)q.y) * (double)n.y;
+    if (!twoD) dot += ((double)p.z - (double)q.z) * (double)n.z;
+    m[0] += w * (dot * dot);
+    m[1] += 1.0;
+  }
+  blockReduceStore<RES_N>(m, partials);
+}
+
 // PointToPlaneWithCov::estimateCovariance (PointToPlaneWithCov.cpp:70-160): J_hessian = sum v v^T and d2J_dZdX d2J_dZdX^T =
 // sum (a a^T + b b^T), upper triangles (21 + 21 moments) | 42 pair count.  The pairs are the mean-centred ErrorElements that
 // PointToPlaneErrorMinimizer::compute leaves behind (PointToPlane.cpp:263-268 centres mPts in place before the covariance runs).
@@ -528,6 +546,24 @@ int32_t b200reg_point_to_point(b200reg_ctx* ctx, const b200reg_cloud* reading, c
   T_out[12] = T_out[13] = T_out[14] = 0.f;
   T_out[15] = 1.f;
   if (stats) for (int d = 0; d < 3; ++d) { stats->mean_reading[d] = mp[d]; stats->mean_reference[d] = mq[d]; }
+  return B200REG_OK;
+}
+
+int32_t b200reg_point_to_plane_residual(b200reg_ctx* ctx, const b200reg_cloud* reading, const b200reg_cloud* reference, const int32_t* ids,
+                                        const float* d2, const float* w, int32_t k, int32_t force2D, double* residual_out, int64_t* kept_out) {
+  if (!ctx || !reading || !reference || !ids || !d2 || !w || !residual_out || k < 1) return setErr(ctx, B200REG_E_INVALID_PARAM, "point_to_plane_residual: bad arguments");
+  if (!reference->nrm) return setErr(ctx, B200REG_E_INVALID_FIELD, "PointToPlaneErrorMinimizer: reference cloud has no 'normals' descriptor");
+  *residual_out = 0.0;
+  if (kept_out) *kept_out = 0;
+  if (reading->n * k == 0) return B200REG_OK;
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  PairArgs A;
+  TRY(stagePairs(ctx, reading, reference, ids, d2, w, k, A));
+  A.alpha = force2D ? 1.0 : 0.0;
+  double m[RES_N];
+  TRY((reducePairs<RES_N>(ctx, residualKernel, A, m)));
+  *residual_out = m[0];
+  if (kept_out) *kept_out = (int64_t)m[1];
   return B200REG_OK;
 }
 

@@ -324,6 +324,19 @@ PM::TransformationParameters CudaPointToPlaneErrorMinimizer::computeOnDevice(con
   return out;
 }
 
+float CudaPointToPlaneErrorMinimizer::getResidualError(const PM::DataPoints& filteredReading, const PM::DataPoints& filteredReference,
+                                                       const PM::OutlierWeights& outlierWeights, const PM::Matches& matches) const {   // PointToPlane.cpp:410-422
+  b200reg_ctx* ctx = contextFor(device);
+  if (!filteredReference.descriptorExists("normals")) throw PM::DataPoints::InvalidField("Field normals not found");
+  CloudGuard gr(ctx), gf(ctx);
+  upload(ctx, filteredReading, false, gr);
+  upload(ctx, filteredReference, true, gf);
+  double res = 0.0;
+  check(ctx, b200reg_point_to_plane_residual(ctx, gr.c, gf.c, matches.ids.data(), matches.dists.data(), outlierWeights.data(), (int32_t)matches.ids.rows(),
+                                             force2D ? 1 : 0, &res, nullptr));
+  return (float)res;
+}
+
 // ---------------------------------------------------------------------------------------------------------------
 // CudaPointToPlaneWithCovErrorMinimizer, CudaPointToPointErrorMinimizer, CudaVarTrimmedDistOutlierFilter
 // ---------------------------------------------------------------------------------------------------------------

@@ -118,6 +118,11 @@ struct CudaPointToPlaneErrorMinimizer : public PM::ErrorMinimizer {   // twin: E
   CudaPointToPlaneErrorMinimizer(const std::string& name, const PM::ParametersDoc& doc, const PM::Parameters& params);   // for the WithCov child
   PM::TransformationParameters compute(const PM::DataPoints& filteredReading, const PM::DataPoints& filteredReference,
                                        const PM::OutlierWeights& outlierWeights, const PM::Matches& matches) override;
+  // PointToPlane.cpp:410-422: sum of w ((reading - reference) . n)^2 over the ErrorElements pairs, reduced on the device
+  float getResidualError(const PM::DataPoints& filteredReading, const PM::DataPoints& filteredReference, const PM::OutlierWeights& outlierWeights,
+                         const PM::Matches& matches) const override;
+  // getOverlap (PointToPlane.cpp:426-521): DataPoints reaching this module carry no simpleSensorNoise / densities descriptors on the
+  // device, the case for which the reference returns getWeightedPointUsedRatio() (:477-481) — the base class's implementation
  protected:
   // compute() with the pieces the covariance needs left on the device / returned: step transform, matched means
   PM::TransformationParameters computeOnDevice(const PM::DataPoints& filteredReading, const PM::DataPoints& filteredReference,

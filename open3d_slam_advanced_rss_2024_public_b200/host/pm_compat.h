@@ -264,7 +264,10 @@ struct PointMatcher {
                                              const OutlierWeights& outlierWeights, const Matches& matches) = 0;
     T getPointUsedRatio() const { return pointUsedRatio; }
     T getWeightedPointUsedRatio() const { return weightedPointUsedRatio; }
-    virtual T getOverlap() const { return weightedPointUsedRatio; }   // PointToPlane.cpp:477-481 fallback
+    virtual T getOverlap() const { return weightedPointUsedRatio; }   // ErrorMinimizer.cpp:258-262; PointToPlane.cpp:477-481 takes the same value without sensor-noise descriptors
+    virtual T getResidualError(const DataPoints&, const DataPoints&, const OutlierWeights&, const Matches&) const {   // ErrorMinimizer.cpp:274-278
+      return std::numeric_limits<T>::max();
+    }
     virtual Matrix getCovariance() const { return Matrix(6, 6, T(0)); }   // ErrorMinimizer.cpp:264-270: zero unless a child redefines it
   };
   struct TransformationChecker : public Parametrizable {

@@ -769,6 +769,35 @@ extern "C" int32_t orc_point_to_plane(const float* read_feat, int32_t rstride, i
   return st;
 }
 
+// PointToPlaneErrorMinimizer::getResidualError / computeResidualError (PointToPlane.cpp:372-422): over the ErrorElements pairs
+// (finite distance, non-zero weight; ErrorMinimizer.cpp:100-118), sum of w ((reading - reference) . n_reference)^2; force2D drops z.
+extern "C" int32_t orc_point_to_plane_residual(const float* read_feat, int32_t rstride, int64_t n, const float* ref_feat, int32_t fstride,
+                                               const float* ref_normals, const int32_t* ids, const float* d2, const float* w, int32_t k,
+                                               int32_t force2D, int32_t precision, double* residual_out) {
+  double accD = 0.0;
+  float accF = 0.f;
+  const int dims = force2D ? 2 : 3;
+  for (int64_t i = 0; i < n; ++i)
+    for (int j = 0; j < k; ++j) {
+      const size_t o = (size_t)k * i + j;
+      if (d2[o] == kInf || w[o] == 0.f) continue;
+      const float* r = read_feat + i * rstride;
+      const float* s = ref_feat + (int64_t)ids[o] * fstride;
+      const float* nn = ref_normals + 3 * (int64_t)ids[o];
+      if (precision == ORC_REF32) {
+        float dot = 0.f;
+        for (int c = 0; c < dims; ++c) dot += (r[c] - s[c]) * nn[c];
+        accF += w[o] * (dot * dot);
+      } else {
+        double dot = 0.0;
+        for (int c = 0; c < dims; ++c) dot += ((double)r[c] - (double)s[c]) * (double)nn[c];
+        accD += (double)w[o] * (dot * dot);
+      }
+    }
+  *residual_out = (precision == ORC_REF32) ? (double)accF : accD;
+  return ORC_OK;
+}
+
 // ================================================================================================================
 // Transformation checkers (TransformationCheckersImpl.cpp:58-225) and the ICP driver (ICP.cpp:258-468)
 // ================================================================================================================

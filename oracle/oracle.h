@@ -106,6 +106,10 @@ int32_t orc_surface_normals(const float* feat, int32_t stride, int64_t n, int32_
                             float* normals, float* densities, float* eig_values, float* eig_vectors, float* matched_ids,
                             float* mean_dists, float* lin_plan_curv, int32_t* degenerate_count);
 
+/* PointToPlaneErrorMinimizer::getResidualError (PointToPlane.cpp:372-422) */
+int32_t orc_point_to_plane_residual(const float* read_feat, int32_t rstride, int64_t n, const float* ref_feat, int32_t fstride,
+                                    const float* ref_normals, const int32_t* ids, const float* d2, const float* w, int32_t k,
+                                    int32_t force2D, int32_t precision, double* residual_out);
 /* smoothNormals (SurfaceNormal.cpp:299-323): the in-place sequential sweep, on the normals orc_surface_normals returned */
 int32_t orc_smooth_normals(const float* feat, int32_t stride, int64_t n, int32_t knn, float max_dist, int32_t nthreads, float* normals);
 

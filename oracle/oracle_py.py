@@ -278,6 +278,23 @@ def surface_normals(feat, knn, max_dist=np.inf, precision=ORC_MIXED, nthreads=8,
     return out
 
 
+def point_to_plane_residual(read_feat, ref_feat, ref_normals, ids, d2, w, force2D=False, precision=ORC_MIXED):
+    """PointToPlaneErrorMinimizer::getResidualError: sum of w ((reading - reference) . n)^2 over the kept pairs."""
+    read_feat, ref_feat, ref_normals = _f32(read_feat), _f32(ref_feat), _f32(ref_normals)
+    ids = np.ascontiguousarray(ids, dtype=np.int32)
+    d2, w = _f32(d2), _f32(w)
+    k = ids.size // max(read_feat.shape[0], 1)
+    out = C.c_double(0)
+    L = lib()
+    L.orc_point_to_plane_residual.restype = C.c_int32
+    L.orc_point_to_plane_residual.argtypes = [C.c_void_p, C.c_int32, C.c_int64, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                              C.c_int32, C.c_int32, C.c_int32, C.POINTER(C.c_double)]
+    st = L.orc_point_to_plane_residual(_p(read_feat), read_feat.shape[1], read_feat.shape[0], _p(ref_feat), ref_feat.shape[1], _p(ref_normals),
+                                       _p(ids), _p(d2), _p(w), k, int(force2D), precision, C.byref(out))
+    assert st == 0, st
+    return out.value
+
+
 def smooth_normals(feat, normals, knn, max_dist=np.inf, nthreads=8):
     """smoothNormals of SurfaceNormal.cpp:299-323 (sequential in-place sweep); returns the smoothed copy."""
     feat = _f32(feat)

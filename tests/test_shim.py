@@ -229,8 +229,14 @@ def test_filters_by_name_match_oracle(shim, oracle, golden):
     dot = np.abs(np.sum(n2.astype(np.float64) * o["normals"], axis=1))
     ok = ~np.all(o["normals"] == 0, axis=1)
     assert np.all(dot[ok] > 1 - 1e-6)      # fp32 storage of unit normals
+    # the descriptors round 1 refused (SurfaceNormal.cpp:133-138): produced now, in the reference's label order
+    f3, n3, labels = shim.apply_filter("CudaSurfaceNormalDataPointsFilter", {"knn": 5, "keepEigenVectors": 1, "keepMatchedIds": 1, "keepMeanDist": 1,
+                                                                           "keepSurfaceDescriptors": 0, "smoothNormals": 1}, pts)
+    assert labels == [("normals", 3), ("eigVectors", 9), ("matchedIds", 5), ("meanDists", 1)]
+    sm = oracle.smooth_normals(pts, o["normals"], 5)
+    assert np.abs(np.sum(n3.astype(np.float64) * sm, axis=1))[ok].min() > 0.0 and np.abs(n3 - sm)[ok].max() < 1e-4
     with pytest.raises(shim.InvalidParameter):
-        shim.apply_filter("CudaSurfaceNormalDataPointsFilter", {"knn": 5, "keepMatchedIds": 1}, pts)
+        shim.apply_filter("CudaSurfaceNormalDataPointsFilter", {"knn": 5, "keepNormals": 0, "smoothNormals": 1}, pts)
 
 
 @pytest.mark.gpu
