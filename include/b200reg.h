@@ -376,8 +376,10 @@ void    b200reg_cloud64_free(b200reg_ctx* ctx, b200reg_cloud64* cloud);
 int32_t b200reg_cloud64_crop(b200reg_ctx* ctx, const b200reg_crop_spec* volume, const b200reg_cloud64* in, b200reg_cloud64** out);
 /* o3d_slam::voxelize (helpers.cpp:108-115), same convention as b200reg_voxel_down_sample_f64 */
 int32_t b200reg_cloud64_voxel_down_sample(b200reg_ctx* ctx, double voxel_size, const b200reg_cloud64* in, b200reg_cloud64** out);
-/* estimateNormalsOrCovariancesIfNeeded (open3d_slam/src/CloudRegistration.cpp:62-75): normals from the knn nearest neighbours within
- * `radius`, oriented toward `origin` (nullable = no orientation); arithmetic of b200reg_surface_normals on the fp32 copy */
+/* estimateNormalsOrCovariancesIfNeeded (open3d_slam/src/CloudRegistration.cpp:62-75) -> Open3D EstimateNormals(Hybrid(radius, knn)) +
+ * OrientNormalsTowardsCameraLocation, in Open3D's scalar (fp64): the (up to) knn nearest points with d2 < radius^2, covariance and
+ * eigenvector from the fp64 coordinates, flipped toward `origin` (nullable = no orientation).  The fp32 index only proposes neighbour
+ * candidates (knn + 4, re-ranked in fp64).  Fewer than 3 neighbours: zero normal, counted in degenerate_count.  knn <= 32. */
 int32_t b200reg_cloud64_estimate_normals(b200reg_ctx* ctx, b200reg_cloud64* inout, int32_t knn, double radius, const double origin[3],
                                          int32_t* degenerate_count);
 /* open3dToPointmatcher (open3d_conversions.cpp:57-118): fp64 -> the fp32 DataPoints mirror (asynchronous on the ctx stream) */

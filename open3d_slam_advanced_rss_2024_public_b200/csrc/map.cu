@@ -838,9 +838,11 @@ int32_t b200reg_cloud64_to_f32(b200reg_ctx* ctx, const b200reg_cloud64* in, b200
   return B200REG_OK;
 }
 
-// estimateNormalsOrCovariancesIfNeeded (CloudRegistration.cpp:62-75): fp32 copy of the points -> SurfaceNormal kernels (kNN,
-// covariance, eigenvector, orientation toward `origin`) -> fp64 normals of the cloud.  Same arithmetic as
-// b200reg_cloud_upload_f64 + b200reg_surface_normals + a host widening of the result.
+// estimateNormalsOrCovariancesIfNeeded (CloudRegistration.cpp:62-75): Open3D's EstimateNormals + orientation toward `origin`, in fp64.
+// The fp32 copy of the points only feeds the index that proposes neighbour candidates; distances, the neighbour selection, the
+// covariance and the eigenvector are fp64 on the cloud's own coordinates (normals.cu estimateNormals64).
+int estimateNormals64(b200reg_ctx* ctx, b200reg_cloud64* cloud, const b200reg_cloud* rounded, int knn, double radius, const double* origin,
+                      int32_t* degenerate_count);
 int32_t b200reg_cloud64_estimate_normals(b200reg_ctx* ctx, b200reg_cloud64* inout, int32_t knn, double radius, const double origin[3],
                                          int32_t* degenerate_count) {
   if (!ctx || !inout) return setErr(ctx, B200REG_E_INVALID_PARAM, "cloud64_estimate_normals: bad arguments");
@@ -850,15 +852,8 @@ int32_t b200reg_cloud64_estimate_normals(b200reg_ctx* ctx, b200reg_cloud64* inou
   b200reg_cloud* tmp = nullptr;
   inout->hasNormals = false;
   TRY(b200reg_cloud64_to_f32(ctx, inout, &tmp));
-  float o[3] = {0.f, 0.f, 0.f};
-  if (origin) for (int d = 0; d < 3; ++d) o[d] = (float)origin[d];
-  int code = b200reg_surface_normals(ctx, tmp, knn, (float)radius, 0.f, origin ? o : nullptr, nullptr, nullptr, nullptr, degenerate_count);
-  if (code == B200REG_OK) {
-    normalsToF64Kernel<<<divUp(inout->n, 256), 256, 0, ctx->stream>>>(tmp->nrm, inout->n, inout->nrm);
-    ctx->launches++;
-    if (cudaGetLastError() != cudaSuccess) code = setErr(ctx, B200REG_E_CUDA, "cloud64_estimate_normals: launch failed");
-    else inout->hasNormals = true;
-  }
+  const int code = estimateNormals64(ctx, inout, tmp, knn, radius, origin, degenerate_count);
+  if (code == B200REG_OK) inout->hasNormals = true;
   b200reg_cloud_free(ctx, tmp);
   return code;
 }

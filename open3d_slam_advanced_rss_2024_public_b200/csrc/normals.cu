@@ -232,6 +232,86 @@ __global__ void __launch_bounds__(256) smoothNormalsKernel(const float4* __restr
 
 }  // namespace
 
+// ---- Open3D EstimateNormals(Hybrid(radius, knn)) + OrientNormalsTowardsCameraLocation on an fp64 cloud (CloudRegistration.cpp:62-75),
+// in Open3D's scalar.  The neighbour CANDIDATES come from the fp32 index (knn + 4 nearest of the rounded copy, radius widened by 1e-5);
+// this kernel re-measures them in fp64, keeps the (up to) knn nearest with d2 < radius^2 by (d2, index), and forms mean, covariance
+// and the eigenvector of the smallest eigenvalue from the fp64 coordinates — at 80 m an fp32 coordinate carries ~4e-6 m of rounding,
+// ~1e-4 rad of normal noise against the 1e-5 rad bar, which is why the points are not rounded first.
+#define N64_MAXC 32
+__global__ void __launch_bounds__(128) normals64Kernel(const double* __restrict__ xyz, const int* __restrict__ ids, int64_t n, int kc, int knn,
+                                                       double r2, int orient, double ox, double oy, double oz, double* __restrict__ outN,
+                                                       int* __restrict__ degenerate) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const double px = xyz[3 * i], py = xyz[3 * i + 1], pz = xyz[3 * i + 2];
+  double cd[N64_MAXC];
+  int ci[N64_MAXC];
+  int cnt = 0;
+  for (int c = 0; c < kc; ++c) {   // insertion sort by (d2, index) over at most 32 candidates
+    const int j = ids[(int64_t)kc * i + c];
+    if (j < 0) continue;
+    const double dx = px - xyz[3 * (int64_t)j], dy = py - xyz[3 * (int64_t)j + 1], dz = pz - xyz[3 * (int64_t)j + 2];
+    const double d = (dx * dx + dy * dy) + dz * dz;
+    if (!(d < r2)) continue;
+    int pos = cnt;
+    while (pos > 0 && (cd[pos - 1] > d || (cd[pos - 1] == d && ci[pos - 1] > j))) { cd[pos] = cd[pos - 1]; ci[pos] = ci[pos - 1]; --pos; }
+    cd[pos] = d; ci[pos] = j;
+    ++cnt;
+  }
+  if (cnt > knn) cnt = knn;
+  double nv[3] = {0.0, 0.0, 0.0};
+  if (cnt < 3) atomicAdd(degenerate, 1);
+  else {
+    double mean[3] = {0, 0, 0}, C[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+    for (int t = 0; t < cnt; ++t) { const int64_t j = ci[t]; mean[0] += xyz[3 * j]; mean[1] += xyz[3 * j + 1]; mean[2] += xyz[3 * j + 2]; }
+    for (int c = 0; c < 3; ++c) mean[c] /= (double)cnt;
+    for (int t = 0; t < cnt; ++t) {
+      const int64_t j = ci[t];
+      const double d[3] = {xyz[3 * j] - mean[0], xyz[3 * j + 1] - mean[1], xyz[3 * j + 2] - mean[2]};
+      for (int r = 0; r < 3; ++r) for (int c = 0; c < 3; ++c) C[3 * r + c] += d[r] * d[c];
+    }
+    for (int q = 0; q < 9; ++q) C[q] /= (double)cnt;
+    double val[3], vec[3][3];
+    symEig3(C, val, vec);
+    nv[0] = vec[0][0]; nv[1] = vec[1][0]; nv[2] = vec[2][0];
+    if (orient) {
+      const double dot = (ox - px) * nv[0] + (oy - py) * nv[1] + (oz - pz) * nv[2];
+      if (dot < 0) { nv[0] = -nv[0]; nv[1] = -nv[1]; nv[2] = -nv[2]; }
+    }
+  }
+  outN[3 * i] = nv[0]; outN[3 * i + 1] = nv[1]; outN[3 * i + 2] = nv[2];
+}
+
+// `rounded`: the fp32 copy of `cloud` (same order) the index is built over; writes cloud->nrm (fp64)
+int estimateNormals64(b200reg_ctx* ctx, b200reg_cloud64* cloud, const b200reg_cloud* rounded, int knn, double radius, const double* origin,
+                      int32_t* degenerate_count) {
+  const int64_t n = cloud->n;
+  if (knn < 3) return setErr(ctx, B200REG_E_INVALID_PARAM, "estimate_normals: knn must be >= 3");
+  if (!(radius >= 0.0)) return setErr(ctx, B200REG_E_INVALID_PARAM, "estimate_normals: radius must be >= 0");
+  const int kc = (knn + 4 <= N64_MAXC) ? knn + 4 : knn;   // beyond 28 the fp32 list is taken as it is (the one-thread kernel serves k > 32)
+  if (kc > 64) return setErr(ctx, B200REG_E_INVALID_PARAM, "estimate_normals: knn above 64 is not supported");
+  if (kc > N64_MAXC) return setErr(ctx, B200REG_E_INVALID_PARAM, "estimate_normals: knn above %d is not supported on the fp64 path", N64_MAXC);
+  b200reg_index* ix = nullptr;
+  TRY(buildIndex(ctx, rounded, 0, 0.f, &ix));
+  const float wide = (float)(radius * 1.00001 + 1e-6);
+  int st = runKnn(ctx, ix, ctx->knnLanes == 1 ? rounded->xyz : nullptr, n, nullptr, kc, wide, 1, 0);
+  if (st != B200REG_OK) { b200reg_index_free(ctx, ix); return st; }
+  int* dDeg = (int*)((char*)ctx->dstate + 32768);
+  cudaMemsetAsync(dDeg, 0, sizeof(int), ctx->stream);
+  normals64Kernel<<<divUp(n, 128), 128, 0, ctx->stream>>>(cloud->xyz, (const int*)ctx->matchIds.p, n, kc, knn, radius * radius, origin ? 1 : 0,
+                                                          origin ? origin[0] : 0.0, origin ? origin[1] : 0.0, origin ? origin[2] : 0.0, cloud->nrm, dDeg);
+  ctx->launches++;
+  cudaError_t e = cudaGetLastError();
+  if (e == cudaSuccess) e = cudaMemcpyAsync(ctx->pinned, dDeg, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+  const bool indexOk = (e != cudaSuccess) || indexHeader(ctx, ix) != nullptr;
+  b200reg_index_free(ctx, ix);
+  if (e != cudaSuccess) return setErr(ctx, B200REG_E_CUDA, "estimate_normals: %s", cudaGetErrorString(e));
+  if (!indexOk) return setErr(ctx, B200REG_E_INVALID_PARAM, "estimate_normals: non-finite coordinates in the cloud");
+  if (degenerate_count) *degenerate_count = *(const int*)ctx->pinned;
+  return B200REG_OK;
+}
+
 extern "C" int32_t b200reg_surface_normals_ex(b200reg_ctx* ctx, b200reg_cloud* inout, const b200reg_normals_options* opt, int32_t* degenerate_count) {
   if (!ctx || !inout || !opt) return setErr(ctx, B200REG_E_INVALID_PARAM, "surface_normals: bad arguments");
   const int32_t knn = opt->knn;

@@ -1272,6 +1272,69 @@ extern "C" int32_t orc_smooth_normals(const float* feat, int32_t stride, int64_t
   return ORC_OK;
 }
 
+// estimateNormalsOrCovariancesIfNeeded (open3d_slam/src/CloudRegistration.cpp:62-75) -> Open3D v0.15.1 PointCloud::EstimateNormals with
+// KDTreeSearchParamHybrid(radius, knn) + OrientNormalsTowardsCameraLocation, in Open3D's scalar (double): the (up to) knn nearest
+// points with d2 < radius^2 (the point itself included), covariance of those neighbours, eigenvector of the smallest eigenvalue,
+// flipped toward `origin`.  Fewer than 3 neighbours -> zero normal (counted as degenerate; Open3D's own value there is unpinned).
+// exact != 0: neighbours by brute force in fp64 (independent of any search structure; small clouds).  exact == 0: the knn + 4 nearest
+// of the fp32 k-d tree are re-ranked in fp64 (the same candidate rule the device uses; for clouds too large for brute force).
+extern "C" int32_t orc_estimate_normals_f64(const double* xyz, int64_t n, int32_t knn, double radius, const double* origin, int32_t exact,
+                                            int32_t nthreads, double* normals, int32_t* degenerate_count) {
+  if (knn < 3) return ORC_E_PARAM;
+  const double r2 = radius * radius;
+  std::vector<int32_t> cand;
+  int kc = 0;
+  if (!exact) {
+    kc = knn + 4;
+    std::vector<float> f((size_t)4 * n);
+    for (int64_t i = 0; i < n; ++i) { for (int c = 0; c < 3; ++c) f[4 * i + c] = (float)xyz[3 * i + c]; f[4 * i + 3] = 1.f; }
+    cand.resize((size_t)kc * n);
+    std::vector<float> d2f((size_t)kc * n);
+    void* tree = orc_kdtree_build(f.data(), 4, n);
+    orc_kdtree_knn(tree, f.data(), 4, n, kc, (float)(radius * 1.00001 + 1e-6), 1, cand.data(), d2f.data(), nthreads);
+    orc_kdtree_free(tree);
+  }
+  int degenerate = 0;
+#pragma omp parallel for schedule(dynamic, 64) num_threads(nthreads > 0 ? nthreads : 1) reduction(+ : degenerate)
+  for (int64_t i = 0; i < n; ++i) {
+    std::vector<std::pair<double, int32_t>> nb;
+    const double* p = xyz + 3 * i;
+    auto consider = [&](int32_t j) {
+      const double* q = xyz + 3 * (int64_t)j;
+      const double dx = p[0] - q[0], dy = p[1] - q[1], dz = p[2] - q[2];
+      const double d = (dx * dx + dy * dy) + dz * dz;
+      if (d < r2) nb.emplace_back(d, j);
+    };
+    if (exact) for (int64_t j = 0; j < n; ++j) consider((int32_t)j);
+    else for (int c = 0; c < kc; ++c) { const int32_t j = cand[(size_t)kc * i + c]; if (j >= 0) consider(j); }
+    std::sort(nb.begin(), nb.end());
+    if ((int)nb.size() > knn) nb.resize(knn);
+    double nv[3] = {0, 0, 0};
+    if (nb.size() < 3) ++degenerate;
+    else {
+      double mean[3] = {0, 0, 0}, C[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+      for (auto& e : nb) for (int c = 0; c < 3; ++c) mean[c] += xyz[3 * (int64_t)e.second + c];
+      for (int c = 0; c < 3; ++c) mean[c] /= (double)nb.size();
+      for (auto& e : nb) {
+        double d[3];
+        for (int c = 0; c < 3; ++c) d[c] = xyz[3 * (int64_t)e.second + c] - mean[c];
+        for (int r = 0; r < 3; ++r) for (int c = 0; c < 3; ++c) C[3 * r + c] += d[r] * d[c];
+      }
+      for (int q = 0; q < 9; ++q) C[q] /= (double)nb.size();
+      double val[3], vec[3][3];
+      symEig3(C, val, vec);
+      nv[0] = vec[0][0]; nv[1] = vec[1][0]; nv[2] = vec[2][0];
+      if (origin) {
+        const double dot = (origin[0] - p[0]) * nv[0] + (origin[1] - p[1]) * nv[1] + (origin[2] - p[2]) * nv[2];
+        if (dot < 0) for (int c = 0; c < 3; ++c) nv[c] = -nv[c];
+      }
+    }
+    for (int c = 0; c < 3; ++c) normals[3 * i + c] = nv[c];
+  }
+  if (degenerate_count) *degenerate_count = degenerate;
+  return ORC_OK;
+}
+
 // ================================================================================================================
 // open3d_slam side (fp64): croppers, transform, map voxelisation, Open3D VoxelDownSample, Open3D -> pointmatcher
 // citations relative to open3d_slam_rsl/open3d_slam/open3d_slam/

@@ -113,6 +113,10 @@ int32_t orc_point_to_plane_residual(const float* read_feat, int32_t rstride, int
 /* smoothNormals (SurfaceNormal.cpp:299-323): the in-place sequential sweep, on the normals orc_surface_normals returned */
 int32_t orc_smooth_normals(const float* feat, int32_t stride, int64_t n, int32_t knn, float max_dist, int32_t nthreads, float* normals);
 
+/* Open3D EstimateNormals(Hybrid(radius, knn)) + orientation toward `origin` (CloudRegistration.cpp:62-75), fp64 throughout */
+int32_t orc_estimate_normals_f64(const double* xyz, int64_t n, int32_t knn, double radius, const double* origin /* nullable */, int32_t exact,
+                                 int32_t nthreads, double* normals, int32_t* degenerate_count);
+
 /* ---- open3d_slam side (fp64) ---- */
 enum { ORC_CROP_MAX_RADIUS = 0, ORC_CROP_MIN_RADIUS = 1, ORC_CROP_MINMAX_RADIUS = 2, ORC_CROP_CYLINDER = 3 };
 typedef struct orc_crop_spec {

@@ -295,6 +295,22 @@ def point_to_plane_residual(read_feat, ref_feat, ref_normals, ids, d2, w, force2
     return out.value
 
 
+def estimate_normals_f64(xyz, knn, radius, origin=None, exact=None, nthreads=8):
+    """Open3D EstimateNormals(Hybrid) + OrientNormalsTowardsCameraLocation in fp64; exact=None: brute-force neighbours up to 20 000 points."""
+    xyz = _f64(xyz)
+    n = xyz.shape[0]
+    exact = (n <= 20_000) if exact is None else exact
+    out = np.zeros((n, 3), dtype=np.float64)
+    deg = C.c_int32(0)
+    oo = None if origin is None else _f64(origin)
+    L = lib()
+    L.orc_estimate_normals_f64.restype = C.c_int32
+    L.orc_estimate_normals_f64.argtypes = [C.c_void_p, C.c_int64, C.c_int32, C.c_double, C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.POINTER(C.c_int32)]
+    st = L.orc_estimate_normals_f64(_p(xyz), n, int(knn), float(radius), _p(oo), int(bool(exact)), int(nthreads), _p(out), C.byref(deg))
+    assert st == 0, st
+    return out, deg.value
+
+
 def smooth_normals(feat, normals, knn, max_dist=np.inf, nthreads=8):
     """smoothNormals of SurfaceNormal.cpp:299-323 (sequential in-place sweep); returns the smoothed copy."""
     feat = _f32(feat)
