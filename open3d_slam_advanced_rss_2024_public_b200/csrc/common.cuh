@@ -120,6 +120,9 @@ const IndexHeader* indexHeader(b200reg_ctx* ctx, const b200reg_index* ix);
 // recycle (nullable): an index of the SAME ctx that is no longer needed — its storage is reused when it is large enough (no
 // allocator calls on the path of a periodic rebuild), otherwise it is freed; either way the caller must forget it.
 int buildIndex(b200reg_ctx* ctx, const b200reg_cloud* ref, int centre, float cell, b200reg_index** out, b200reg_index* recycle = nullptr);
+// Open3D EstimateNormals on an fp64 cloud (normals.cu); `rounded` = its fp32 copy, same order
+int estimateNormals64(b200reg_ctx* ctx, b200reg_cloud64* cloud, const b200reg_cloud* rounded, int knn, double radius, const double* origin,
+                      int32_t* degenerate_count);
 IndexHeader* acquireHeaderSlot(b200reg_ctx* ctx);
 void releaseHeaderSlot(b200reg_ctx* ctx, IndexHeader* slot);
 

@@ -841,8 +841,6 @@ int32_t b200reg_cloud64_to_f32(b200reg_ctx* ctx, const b200reg_cloud64* in, b200
 // estimateNormalsOrCovariancesIfNeeded (CloudRegistration.cpp:62-75): Open3D's EstimateNormals + orientation toward `origin`, in fp64.
 // The fp32 copy of the points only feeds the index that proposes neighbour candidates; distances, the neighbour selection, the
 // covariance and the eigenvector are fp64 on the cloud's own coordinates (normals.cu estimateNormals64).
-int estimateNormals64(b200reg_ctx* ctx, b200reg_cloud64* cloud, const b200reg_cloud* rounded, int knn, double radius, const double* origin,
-                      int32_t* degenerate_count);
 int32_t b200reg_cloud64_estimate_normals(b200reg_ctx* ctx, b200reg_cloud64* inout, int32_t knn, double radius, const double origin[3],
                                          int32_t* degenerate_count) {
   if (!ctx || !inout) return setErr(ctx, B200REG_E_INVALID_PARAM, "cloud64_estimate_normals: bad arguments");
