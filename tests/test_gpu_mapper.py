@@ -218,7 +218,7 @@ def test_cloud64_chain_equals_host_array_chain(ctx, oracle):
     assert chord.max() <= 1e-5, (chord.max(), ang.max())
     # what rounding the points to fp32 first costs at these ranges (the round-1 path): above the 1e-5 rad bar
     chord32 = np.linalg.norm(n32[live].astype(np.float64) - vn[live], axis=1)
-    assert np.median(chord32) > 1e-6
+    assert (chord32 > 1e-5).any()
     vn = dn
     mx, mn = ctx.crop_f64(narrow, vx, vn)
     qx, qn = match.download()

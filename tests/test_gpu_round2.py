@@ -436,3 +436,24 @@ def test_point_to_plane_residual_matches_oracle(ctx, oracle, golden, k, force2D)
     assert abs(res_g - res_o) <= 1e-9 * max(1.0, abs(res_o))
     res32 = oracle.point_to_plane_residual(q, ref, rn, ids, d2, w, force2D=force2D, precision=oracle.ORC_REF32)
     assert abs(res_g - res32) <= 1e-3 * max(1.0, abs(res32))          # the reference's float accumulation
+
+
+def test_pointcloud2_reference_test_layouts_round_trip(ctx, oracle):
+    """SURVEY f2 / VERDICT r1 weak 3: the message layouts of the reference's own RosPointCloud2DeserializerTest.cpp:195-430 (as written by
+    pointMatcherCloudToRosMsg<float>), at the reference tests' sizes: deserialize(serialize(cloud)) == cloud, bit for bit, on the device
+    (fp32 DataPoints mirror and the fp64 open3d mirror) and in the oracle."""
+    from open3d_slam_advanced_rss_2024_public_b200 import capi
+    import pc2_reference_layouts as R
+    for k, case in enumerate(R.CASES):
+        data, fields, step, (w, h), feat, nrm = R.build(case, 700 + k)
+        L = capi.pc2_layout(w, h, step, fields)
+        c = ctx.cloud_from_pointcloud2(data, L)
+        g4, gn = c.download()
+        assert np.array_equal(g4.view(np.uint32), feat.view(np.uint32)), case[0]
+        assert (gn is None) == (nrm is None) and (gn is None or np.array_equal(gn.view(np.uint32), nrm.view(np.uint32))), case[0]
+        c64 = ctx.cloud64_from_pointcloud2(data, L)
+        gx, gn64 = c64.download()
+        assert np.array_equal(gx, feat[:, :3].astype(np.float64)) and (nrm is None or np.array_equal(gn64, nrm.astype(np.float64))), case[0]
+        if feat.shape[0] <= 10000:
+            st, f4, n3, x64, n64 = oracle.pointcloud2(data, feat.shape[0], step, fields)
+            assert np.array_equal(f4.view(np.uint32), feat.view(np.uint32)) and (nrm is None or np.array_equal(n3, nrm))

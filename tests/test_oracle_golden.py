@@ -545,3 +545,18 @@ def test_compacting_filters_known_answers(oracle):
     k = O.cloud_filter(big[:2], O.FILTER_RANDOM_SAMPLING, prob=0.05, seed=1)
     assert k.tolist() == [True, False]     # 48271 / 2^31 = 2.2e-5 < 0.05 ; 182605794 / 2^31 = 0.085 > 0.05
     assert O.cloud_filter(big, O.FILTER_RANDOM_SAMPLING, prob=1.0, seed=3).all() and not O.cloud_filter(big, O.FILTER_RANDOM_SAMPLING, prob=0.0, seed=3).any()
+
+
+def test_pointcloud2_reference_test_layouts_oracle(oracle):
+    """The oracle's deserialiser against the message layouts of the reference's RosPointCloud2DeserializerTest.cpp:195-430 (written by
+    pointMatcherCloudToRosMsg<float>, restated in pc2_reference_layouts.py): deserialize(serialize(cloud)) == cloud."""
+    import pc2_reference_layouts as R
+    for k, case in enumerate(R.CASES):
+        if case[1] > 200_000:
+            case = (case[0], 50_000) + case[2:]        # the million-point cases run at full size in the GPU suite
+        data, fields, step, wh, feat, nrm = R.build(case, 700 + k)
+        st, f4, n3, x64, n64 = oracle.pointcloud2(data, feat.shape[0], step, fields)
+        assert st == 0
+        assert np.array_equal(f4.view(np.uint32), feat.view(np.uint32)), case[0]
+        assert (n3 is None) == (nrm is None) and (nrm is None or np.array_equal(n3, nrm)), case[0]
+        assert np.array_equal(x64, feat[:, :3].astype(np.float64))
