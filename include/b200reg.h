@@ -16,6 +16,10 @@
  *     invalid = (-1, +inf).
  *   - 4x4 transforms are ROW-MAJOR float[16] / double[16] at this boundary.
  *   - there is NO CPU fallback: without a CUDA device every call fails with B200REG_E_CUDA.
+ *   - device memory comes from the device's DEFAULT stream-ordered pool (cudaMallocAsync); b200reg_ctx_create raises that pool's
+ *     release threshold to "never" so that freed blocks stay cached — a process-wide setting of the device the host application
+ *     shares (cudaMemPoolTrimTo on cudaDeviceGetDefaultMemPool gives the memory back).
+ *   - env B200REG_DEBUG_SYNC=1 synchronises after every checked kernel launch, so a faulting kernel is reported at its own call.
  */
 #ifndef B200REG_H
 #define B200REG_H
@@ -379,7 +383,7 @@ int32_t b200reg_cloud64_voxel_down_sample(b200reg_ctx* ctx, double voxel_size, c
 /* estimateNormalsOrCovariancesIfNeeded (open3d_slam/src/CloudRegistration.cpp:62-75) -> Open3D EstimateNormals(Hybrid(radius, knn)) +
  * OrientNormalsTowardsCameraLocation, in Open3D's scalar (fp64): the (up to) knn nearest points with d2 < radius^2, covariance and
  * eigenvector from the fp64 coordinates, flipped toward `origin` (nullable = no orientation).  The fp32 index only proposes neighbour
- * candidates (knn + 4, re-ranked in fp64).  Fewer than 3 neighbours: zero normal, counted in degenerate_count.  knn <= 32. */
+ * candidates (knn + 2, re-ranked in fp64).  Fewer than 3 neighbours: zero normal, counted in degenerate_count.  knn <= 32. */
 int32_t b200reg_cloud64_estimate_normals(b200reg_ctx* ctx, b200reg_cloud64* inout, int32_t knn, double radius, const double origin[3],
                                          int32_t* degenerate_count);
 /* open3dToPointmatcher (open3d_conversions.cpp:57-118): fp64 -> the fp32 DataPoints mirror (asynchronous on the ctx stream) */

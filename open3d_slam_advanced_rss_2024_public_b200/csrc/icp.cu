@@ -981,7 +981,12 @@ int32_t b200reg_icp_register(b200reg_icp* icp, const b200reg_cloud* reading, con
   st.reading_point_count = n;
   st.reference_preprocessing_s = icp->refPrepS;
   if (n == 0) return done(setErr(ctx, B200REG_E_NO_POINTS, "The reading point cloud is empty."));   // ICP.cpp:357-359
-  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+#define REG_TRY(expr)                                                                                                      \
+  do {                                                                                                                     \
+    const cudaError_t _e = (expr);                                                                                         \
+    if (_e != cudaSuccess) return done(setErr(ctx, B200REG_E_CUDA, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__, __LINE__)); \
+  } while (0)
+  REG_TRY(cudaSetDevice(ctx->device));   // (every failure leaves through done(): *stats is always written)
   const double t0 = nowSec();
   if (!indexHeader(ctx, icp->index)) return done(B200REG_E_INVALID_PARAM);
   { const int c = checkPreTransform(icp, T_init); if (c != B200REG_OK) return done(c); }
@@ -997,8 +1002,9 @@ int32_t b200reg_icp_register(b200reg_icp* icp, const b200reg_cloud* reading, con
                         {cfg.checker_order[0], cfg.checker_order[1], cfg.checker_order[2]}};
   CheckerState chk;
   checkersInit(chk, T_iter);
-  CUDA_TRY(ctx, cudaMemsetAsync(ctx->dstate, 0, 2 * sizeof(unsigned long long), ctx->stream));
-  CUDA_TRY(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
+  REG_TRY(cudaMemsetAsync(ctx->dstate, 0, 2 * sizeof(unsigned long long), ctx->stream));
+  REG_TRY(cudaEventRecord(ctx->ev0, ctx->stream));
+#undef REG_TRY
   int status = B200REG_OK;
   const HostStep* h = (const HostStep*)ctx->pinned;
   unsigned long long farPrev = 0;

@@ -81,13 +81,54 @@ __global__ void classifyKernel(const double* __restrict__ xyz, int64_t n, b200re
   }
 }
 
+// How the three voxel coordinates of a sort key are packed: x above y above z (ascending key = ascending (x, y, z), the emission
+// order), each in the bits its range needs.  shy / shx = bits of z / of y + z; total = the sort's end bit.
+struct KeyPack {
+  long long k0[3];   // subtracted from the (offset) coordinates before packing
+  int shx, shy, total;
+};
+inline int bitsFor(double span) {   // bits holding 0 .. span
+  int b = 1;
+  while (b < 21 && (double)(1ll << b) <= span) ++b;
+  return b;
+}
+
 __global__ void compactPairsKernel(const unsigned* __restrict__ inFlag, const unsigned* __restrict__ inOff, const u64* __restrict__ keys,
-                                   int64_t n, u64* __restrict__ ckeys, unsigned* __restrict__ cvals) {
+                                   int64_t n, KeyPack kp, u64* __restrict__ ckeys, unsigned* __restrict__ cvals) {
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n || !inFlag[i]) return;
   const unsigned o = inOff[i];
-  ckeys[o] = keys[i];
+  u64 key = keys[i];
+  if (kp.total < 63) {   // 3 x 21 bits -> the bits the cropping volume needs (same order: per-axis shifts keep (x, y, z) lexicographic)
+    const long long kx = (long long)(key >> 42) - kp.k0[0], ky = (long long)((key >> 21) & 0x1fffffull) - kp.k0[1], kz = (long long)(key & 0x1fffffull) - kp.k0[2];
+    key = ((u64)kx << kp.shx) | ((u64)ky << kp.shy) | (u64)kz;
+  }
+  ckeys[o] = key;
   cvals[o] = (unsigned)i;
+}
+
+// Key packing for the points inside a cropping volume: voxel coordinate c = floor(p / voxel) + 2^20 (classifyKernel) of a point inside a
+// sphere / cylinder of radius rmax around `center` lies within floor((center -+ rmax) / voxel) + 2^20, one voxel of margin on each side.
+// Unbounded volumes (inverted, min-radius) keep the 63-bit keys.
+KeyPack keyPackFor(const b200reg_crop_spec& s, double inv) {
+  KeyPack kp;
+  kp.k0[0] = kp.k0[1] = kp.k0[2] = 0;
+  kp.shx = 42; kp.shy = 21; kp.total = 63;
+  if (s.invert || s.kind == B200REG_CROP_MIN_RADIUS || !(s.rmax >= 0.0) || !(s.rmax < 1e300)) return kp;
+  double lo[3], hi[3];
+  for (int d = 0; d < 3; ++d) { lo[d] = s.center[d] - s.rmax; hi[d] = s.center[d] + s.rmax; }
+  if (s.kind == B200REG_CROP_CYLINDER) { lo[2] = s.zmin; hi[2] = s.zmax; }   // the cylinder's z range is absolute
+  int bits[3];
+  for (int d = 0; d < 3; ++d) {
+    const double a = floor(lo[d] * inv) - 1.0, b = floor(hi[d] * inv) + 1.0;
+    if (!(fabs(a) < 1048000.0) || !(fabs(b) < 1048000.0) || !(b >= a)) return kp;
+    kp.k0[d] = (long long)a + 1048576ll;
+    bits[d] = bitsFor(b - a);
+  }
+  kp.shy = bits[2];
+  kp.shx = bits[2] + bits[1];
+  kp.total = bits[0] + bits[1] + bits[2];
+  return kp;
 }
 
 __global__ void headFlagKernel(const u64* __restrict__ skeys, int64_t m, unsigned* __restrict__ head) {
@@ -148,37 +189,37 @@ __global__ void scatterSelectedF32Kernel(const unsigned* __restrict__ flag, cons
   if (nrm && onrm) onrm[o] = make_float4((float)nrm[3 * (size_t)i], (float)nrm[3 * (size_t)i + 1], (float)nrm[3 * (size_t)i + 2], 0.f);
 }
 
-// per-block minimum of the coordinates (Open3D GetMinBound)
+// per-block minimum (Open3D GetMinBound) and maximum of the coordinates: partial[6 b + 0..2] = min, [3..5] = max.  The maximum only
+// sizes the sort: with the extent known the voxel keys pack into the bits they need and the radix sort runs 4-5 passes instead of 8.
 __global__ void minBoundKernel(const double* __restrict__ xyz, int64_t n, double* __restrict__ partial) {
-  double m0 = CUDART_INF, m1 = CUDART_INF, m2 = CUDART_INF;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
-    m0 = fmin(m0, xyz[3 * i]); m1 = fmin(m1, xyz[3 * i + 1]); m2 = fmin(m2, xyz[3 * i + 2]);
-  }
-  for (int o = 16; o > 0; o >>= 1) {
-    m0 = fmin(m0, __shfl_xor_sync(0xffffffffu, m0, o));
-    m1 = fmin(m1, __shfl_xor_sync(0xffffffffu, m1, o));
-    m2 = fmin(m2, __shfl_xor_sync(0xffffffffu, m2, o));
-  }
-  __shared__ double sm[8][3];
-  if ((threadIdx.x & 31) == 0) { sm[threadIdx.x >> 5][0] = m0; sm[threadIdx.x >> 5][1] = m1; sm[threadIdx.x >> 5][2] = m2; }
+  double m[6] = {CUDART_INF, CUDART_INF, CUDART_INF, -CUDART_INF, -CUDART_INF, -CUDART_INF};
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    for (int d = 0; d < 3; ++d) { const double v = xyz[3 * i + d]; m[d] = fmin(m[d], v); m[3 + d] = fmax(m[3 + d], v); }
+  for (int o = 16; o > 0; o >>= 1)
+    for (int d = 0; d < 3; ++d) {
+      m[d] = fmin(m[d], __shfl_xor_sync(0xffffffffu, m[d], o));
+      m[3 + d] = fmax(m[3 + d], __shfl_xor_sync(0xffffffffu, m[3 + d], o));
+    }
+  __shared__ double sm[8][6];
+  if ((threadIdx.x & 31) == 0) for (int d = 0; d < 6; ++d) sm[threadIdx.x >> 5][d] = m[d];
   __syncthreads();
-  if (threadIdx.x < 3) {
+  if (threadIdx.x < 6) {
     double v = sm[0][threadIdx.x];
-    for (int w = 1; w < (int)(blockDim.x >> 5); ++w) v = fmin(v, sm[w][threadIdx.x]);
-    partial[3 * blockIdx.x + threadIdx.x] = v;
+    for (int w = 1; w < (int)(blockDim.x >> 5); ++w) v = (threadIdx.x < 3) ? fmin(v, sm[w][threadIdx.x]) : fmax(v, sm[w][threadIdx.x]);
+    partial[6 * blockIdx.x + threadIdx.x] = v;
   }
 }
 
 // Open3D VoxelDownSample key: floor((p - voxel_min_bound) / voxel), voxel_min_bound = min_bound - voxel / 2
-__global__ void o3dKeyKernel(const double* __restrict__ xyz, int64_t n, double mx, double my, double mz, double voxel, u64* __restrict__ keys,
-                             unsigned* __restrict__ vals, int* __restrict__ err) {
+__global__ void o3dKeyKernel(const double* __restrict__ xyz, int64_t n, double mx, double my, double mz, double voxel, int shx, int shy,
+                             u64* __restrict__ keys, unsigned* __restrict__ vals, int* __restrict__ err) {
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   const double fx = floor((xyz[3 * i] - mx) / voxel), fy = floor((xyz[3 * i + 1] - my) / voxel), fz = floor((xyz[3 * i + 2] - mz) / voxel);
   const double lim = 2097151.0;   // 21 bits per axis, keys are non-negative by construction
   u64 key = ~0ull >> 1;
   if (!(fx >= 0.0 && fx <= lim) || !(fy >= 0.0 && fy <= lim) || !(fz >= 0.0 && fz <= lim)) *err = 1;
-  else key = ((u64)fx << 42) | ((u64)fy << 21) | (u64)fz;
+  else key = ((u64)fx << shx) | ((u64)fy << shy) | (u64)fz;   // (a coordinate beyond its field could only come from a max bound that is not one: impossible)
   keys[i] = key;
   vals[i] = (unsigned)i;
 }
@@ -260,16 +301,17 @@ int revoxelize(b200reg_ctx* ctx, double voxel, const b200reg_crop_spec& spec, co
   LAUNCH_CHECK(ctx);
   int64_t nVox = 0;
   if (nIn > 0) {
-    compactPairsKernel<<<divUp(total, 256), 256, 0, ctx->stream>>>(inFlag, inOff, keysAll, total, (u64*)ctx->keys0.p, (unsigned*)ctx->vals0.p);
+    const KeyPack kp = keyPackFor(spec, 1.0 / voxel);
+    compactPairsKernel<<<divUp(total, 256), 256, 0, ctx->stream>>>(inFlag, inOff, keysAll, total, kp, (u64*)ctx->keys0.p, (unsigned*)ctx->vals0.p);
     LAUNCH_CHECK(ctx);
     cub::DoubleBuffer<u64> dk((u64*)ctx->keys0.p, (u64*)ctx->keys1.p);
     cub::DoubleBuffer<unsigned> dv((unsigned*)ctx->vals0.p, (unsigned*)ctx->vals1.p);
     size_t tmp = 0;
-    CUDA_TRY(ctx, cub::DeviceRadixSort::SortPairs(nullptr, tmp, dk, dv, (int)nIn, 0, 63, ctx->stream));
+    CUDA_TRY(ctx, cub::DeviceRadixSort::SortPairs(nullptr, tmp, dk, dv, (int)nIn, 0, kp.total, ctx->stream));
     TRY(ensureBuf(ctx, ctx->cubtmp, tmp));
     tmp = ctx->cubtmp.cap;
-    CUDA_TRY(ctx, cub::DeviceRadixSort::SortPairs(ctx->cubtmp.p, tmp, dk, dv, (int)nIn, 0, 63, ctx->stream));
-    ctx->launches += 9;
+    CUDA_TRY(ctx, cub::DeviceRadixSort::SortPairs(ctx->cubtmp.p, tmp, dk, dv, (int)nIn, 0, kp.total, ctx->stream));
+    ctx->launches += (uint64_t)((kp.total + 7) / 8 + 1);
     headFlagKernel<<<divUp(nIn, 256), 256, 0, ctx->stream>>>(dk.Current(), nIn, head);
     LAUNCH_CHECK(ctx);
     TRY(scanFlags(ctx, head, headOff, nIn));
@@ -327,27 +369,35 @@ int voxelDownDevice(b200reg_ctx* ctx, double voxel, const double* dIn, const dou
   TRY(ensureBuf(ctx, ctx->vals0, u4));
   TRY(ensureBuf(ctx, ctx->vals1, u4));
   const int mb = (int)fmin((double)(2 * ctx->sm_count), (double)divUp(n, 256));
-  TRY(ensureBuf(ctx, ctx->partials, sizeof(double) * 3 * (size_t)mb));
+  TRY(ensureBuf(ctx, ctx->partials, sizeof(double) * 6 * (size_t)mb));
   minBoundKernel<<<mb, 256, 0, ctx->stream>>>(dIn, n, (double*)ctx->partials.p);
   LAUNCH_CHECK(ctx);
-  TRY(ensurePinned(ctx, sizeof(double) * 3 * (size_t)mb + 64));
-  CUDA_TRY(ctx, cudaMemcpyAsync(ctx->pinned, ctx->partials.p, sizeof(double) * 3 * (size_t)mb, cudaMemcpyDeviceToHost, ctx->stream));
+  TRY(ensurePinned(ctx, sizeof(double) * 6 * (size_t)mb + 64));
+  CUDA_TRY(ctx, cudaMemcpyAsync(ctx->pinned, ctx->partials.p, sizeof(double) * 6 * (size_t)mb, cudaMemcpyDeviceToHost, ctx->stream));
   CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
-  double mn[3] = {INFINITY, INFINITY, INFINITY};
-  for (int b = 0; b < mb; ++b) for (int d = 0; d < 3; ++d) mn[d] = fmin(mn[d], ((const double*)ctx->pinned)[3 * b + d]);
+  double mn[3] = {INFINITY, INFINITY, INFINITY}, mxb[3] = {-INFINITY, -INFINITY, -INFINITY};
+  for (int b = 0; b < mb; ++b)
+    for (int d = 0; d < 3; ++d) { mn[d] = fmin(mn[d], ((const double*)ctx->pinned)[6 * b + d]); mxb[d] = fmax(mxb[d], ((const double*)ctx->pinned)[6 * b + 3 + d]); }
   for (int d = 0; d < 3; ++d) mn[d] = mn[d] - voxel * 0.5;
+  // bits per axis from the extent (one voxel of margin; a non-finite extent keeps the full 21): the sort runs over the bits in use
+  int bits[3];
+  for (int d = 0; d < 3; ++d) {
+    const double span = floor((mxb[d] - mn[d]) / voxel) + 1.0;
+    bits[d] = (span >= 0.0 && span < 2097151.0) ? bitsFor(span) : 21;
+  }
+  const int shy = bits[2], shx = bits[2] + bits[1], endBit = bits[0] + bits[1] + bits[2];
   int* dErr = (int*)((char*)ctx->dstate + 32768 + 64);
   CUDA_TRY(ctx, cudaMemsetAsync(dErr, 0, sizeof(int), ctx->stream));
-  o3dKeyKernel<<<divUp(n, 256), 256, 0, ctx->stream>>>(dIn, n, mn[0], mn[1], mn[2], voxel, (u64*)ctx->keys0.p, (unsigned*)ctx->vals0.p, dErr);
+  o3dKeyKernel<<<divUp(n, 256), 256, 0, ctx->stream>>>(dIn, n, mn[0], mn[1], mn[2], voxel, shx, shy, (u64*)ctx->keys0.p, (unsigned*)ctx->vals0.p, dErr);
   LAUNCH_CHECK(ctx);
   cub::DoubleBuffer<u64> dk((u64*)ctx->keys0.p, (u64*)ctx->keys1.p);
   cub::DoubleBuffer<unsigned> dv((unsigned*)ctx->vals0.p, (unsigned*)ctx->vals1.p);
   size_t tmp = 0;
-  CUDA_TRY(ctx, cub::DeviceRadixSort::SortPairs(nullptr, tmp, dk, dv, (int)n, 0, 63, ctx->stream));
+  CUDA_TRY(ctx, cub::DeviceRadixSort::SortPairs(nullptr, tmp, dk, dv, (int)n, 0, endBit, ctx->stream));
   TRY(ensureBuf(ctx, ctx->cubtmp, tmp));
   tmp = ctx->cubtmp.cap;
-  CUDA_TRY(ctx, cub::DeviceRadixSort::SortPairs(ctx->cubtmp.p, tmp, dk, dv, (int)n, 0, 63, ctx->stream));
-  ctx->launches += 9;
+  CUDA_TRY(ctx, cub::DeviceRadixSort::SortPairs(ctx->cubtmp.p, tmp, dk, dv, (int)n, 0, endBit, ctx->stream));
+  ctx->launches += (uint64_t)((endBit + 7) / 8 + 1);
   headFlagKernel<<<divUp(n, 256), 256, 0, ctx->stream>>>(dk.Current(), n, head);
   LAUNCH_CHECK(ctx);
   TRY(scanFlags(ctx, head, headOff, n));
@@ -469,7 +519,9 @@ int carveDevice(b200reg_ctx* ctx, b200reg_map* map, const double* dScan, int64_t
   TRY(scanTotal(ctx, inFlag, inOff, N, &nIn));   // synchronises (T_map_scan may be reused by the caller)
   if (((const int*)ctx->pinned)[8]) return setErr(ctx, B200REG_E_INVALID_PARAM, "carve: voxel index outside +-2^20 (voxel size too small for the map extent)");
   if (nIn == 0) return B200REG_OK;
-  compactPairsKernel<<<divUp(N, 256), 256, 0, ctx->stream>>>(inFlag, inOff, keysAll, N, (u64*)ctx->keys0.p, (unsigned*)ctx->vals0.p);
+  KeyPack kp63;   // the ray march looks voxels up by their 3 x 21-bit key: no re-packing here
+  kp63.k0[0] = kp63.k0[1] = kp63.k0[2] = 0; kp63.shx = 42; kp63.shy = 21; kp63.total = 63;
+  compactPairsKernel<<<divUp(N, 256), 256, 0, ctx->stream>>>(inFlag, inOff, keysAll, N, kp63, (u64*)ctx->keys0.p, (unsigned*)ctx->vals0.p);
   LAUNCH_CHECK(ctx);
   cub::DoubleBuffer<u64> dk((u64*)ctx->keys0.p, (u64*)ctx->keys1.p);
   cub::DoubleBuffer<unsigned> dv((unsigned*)ctx->vals0.p, (unsigned*)ctx->vals1.p);

@@ -233,7 +233,7 @@ __global__ void __launch_bounds__(256) smoothNormalsKernel(const float4* __restr
 }  // namespace
 
 // ---- Open3D EstimateNormals(Hybrid(radius, knn)) + OrientNormalsTowardsCameraLocation on an fp64 cloud (CloudRegistration.cpp:62-75),
-// in Open3D's scalar.  The neighbour CANDIDATES come from the fp32 index (knn + 4 nearest of the rounded copy, radius widened by 1e-5);
+// in Open3D's scalar.  The neighbour CANDIDATES come from the fp32 index (knn + 2 nearest of the rounded copy, radius widened by 1e-5);
 // this kernel re-measures them in fp64, keeps the (up to) knn nearest with d2 < radius^2 by (d2, index), and forms mean, covariance
 // and the eigenvector of the smallest eigenvalue from the fp64 coordinates — at 80 m an fp32 coordinate carries ~4e-6 m of rounding,
 // ~1e-4 rad of normal noise against the 1e-5 rad bar, which is why the points are not rounded first.
@@ -288,7 +288,7 @@ int estimateNormals64(b200reg_ctx* ctx, b200reg_cloud64* cloud, const b200reg_cl
   const int64_t n = cloud->n;
   if (knn < 3) return setErr(ctx, B200REG_E_INVALID_PARAM, "estimate_normals: knn must be >= 3");
   if (!(radius >= 0.0)) return setErr(ctx, B200REG_E_INVALID_PARAM, "estimate_normals: radius must be >= 0");
-  const int kc = (knn + 4 <= N64_MAXC) ? knn + 4 : knn;   // beyond 28 the fp32 list is taken as it is (the one-thread kernel serves k > 32)
+  const int kc = (knn + 2 <= N64_MAXC) ? knn + 2 : knn;   // two spare candidates: an fp32 / fp64 order swap at the k-th place needs a near-tie (~1e-3 of the points), two in a row ~1e-6
   if (kc > 64) return setErr(ctx, B200REG_E_INVALID_PARAM, "estimate_normals: knn above 64 is not supported");
   if (kc > N64_MAXC) return setErr(ctx, B200REG_E_INVALID_PARAM, "estimate_normals: knn above %d is not supported on the fp64 path", N64_MAXC);
   b200reg_index* ix = nullptr;

@@ -1276,7 +1276,7 @@ extern "C" int32_t orc_smooth_normals(const float* feat, int32_t stride, int64_t
 // KDTreeSearchParamHybrid(radius, knn) + OrientNormalsTowardsCameraLocation, in Open3D's scalar (double): the (up to) knn nearest
 // points with d2 < radius^2 (the point itself included), covariance of those neighbours, eigenvector of the smallest eigenvalue,
 // flipped toward `origin`.  Fewer than 3 neighbours -> zero normal (counted as degenerate; Open3D's own value there is unpinned).
-// exact != 0: neighbours by brute force in fp64 (independent of any search structure; small clouds).  exact == 0: the knn + 4 nearest
+// exact != 0: neighbours by brute force in fp64 (independent of any search structure; small clouds).  exact == 0: the knn + 2 nearest
 // of the fp32 k-d tree are re-ranked in fp64 (the same candidate rule the device uses; for clouds too large for brute force).
 extern "C" int32_t orc_estimate_normals_f64(const double* xyz, int64_t n, int32_t knn, double radius, const double* origin, int32_t exact,
                                             int32_t nthreads, double* normals, int32_t* degenerate_count) {
@@ -1285,7 +1285,7 @@ extern "C" int32_t orc_estimate_normals_f64(const double* xyz, int64_t n, int32_
   std::vector<int32_t> cand;
   int kc = 0;
   if (!exact) {
-    kc = knn + 4;
+    kc = knn + 2;
     std::vector<float> f((size_t)4 * n);
     for (int64_t i = 0; i < n; ++i) { for (int c = 0; c < 3; ++c) f[4 * i + c] = (float)xyz[3 * i + c]; f[4 * i + 3] = 1.f; }
     cand.resize((size_t)kc * n);
