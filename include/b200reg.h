@@ -372,6 +372,13 @@ int32_t b200reg_voxel_down_sample_f64(b200reg_ctx* ctx, double voxel_size, const
  *      (open3d_slam/src/ScanToMapRegistration.cpp:36-69) without a host round trip between its steps.  Every `out` parameter is
  *      in/out: *out == NULL creates a cloud, otherwise the existing cloud's storage is reused (grown when too small). --------- */
 int32_t b200reg_cloud64_upload(b200reg_ctx* ctx, const double* xyz, const double* nrm, int64_t n, b200reg_cloud64** out);
+/* Next-scan prefetch (SlamWrapper's range-scan buffer feeding Mapper::addRangeMeasurement, SlamWrapper.cpp mapping worker): the
+ * upload of b200reg_cloud64_upload enqueued on the context's copy stream, behind everything already enqueued on the compute
+ * stream, so it overlaps the kernels of the scan being processed; returns without waiting (truly asynchronous for pinned host
+ * memory).  The host buffers must stay unchanged until b200reg_cloud64_acquire, which waits for the copy and orders the compute
+ * stream behind it; every other use of a prefetched cloud before acquire is undefined. */
+int32_t b200reg_cloud64_prefetch(b200reg_ctx* ctx, const double* xyz, const double* nrm, int64_t n, b200reg_cloud64** out);
+int32_t b200reg_cloud64_acquire(b200reg_ctx* ctx, b200reg_cloud64* cloud);
 int32_t b200reg_cloud64_download(b200reg_ctx* ctx, const b200reg_cloud64* cloud, double* xyz, double* nrm);
 int64_t b200reg_cloud64_size(const b200reg_cloud64* cloud);
 int32_t b200reg_cloud64_has_normals(const b200reg_cloud64* cloud);

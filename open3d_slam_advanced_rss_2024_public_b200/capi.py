@@ -189,6 +189,8 @@ SYMBOLS = {
     "b200reg_voxel_down_sample_f64": (C.c_int32, [_VP, C.c_double, _VP, _VP, C.c_int64, _VP, _VP, C.POINTER(C.c_int64)]),
     "b200reg_crop_f64": (C.c_int32, [_VP, C.POINTER(CropSpec), _VP, _VP, C.c_int64, _VP, _VP, C.POINTER(C.c_int64)]),
     "b200reg_cloud64_upload": (C.c_int32, [_VP, _VP, _VP, C.c_int64, C.POINTER(_VP)]),
+    "b200reg_cloud64_prefetch": (C.c_int32, [_VP, _VP, _VP, C.c_int64, C.POINTER(_VP)]),
+    "b200reg_cloud64_acquire": (C.c_int32, [_VP, _VP]),
     "b200reg_cloud64_download": (C.c_int32, [_VP, _VP, _VP, _VP]),
     "b200reg_cloud64_size": (C.c_int64, [_VP]),
     "b200reg_cloud64_has_normals": (C.c_int32, [_VP]),
@@ -778,6 +780,23 @@ class Cloud64:
         c = out if out is not None else cls(ctx)
         ctx.check(lib().b200reg_cloud64_upload(ctx.h, _p(xyz), _p(nrm), xyz.shape[0], C.byref(c.h)))
         return c
+
+    @classmethod
+    def prefetch(cls, ctx, xyz, nrm=None, out=None):
+        """The upload on the copy stream (b200reg_cloud64_prefetch); xyz / nrm must be C-contiguous float64 arrays (they are kept
+        referenced until acquire()).  Call acquire() before any other use."""
+        for a in (xyz, nrm):
+            if a is not None and not (isinstance(a, np.ndarray) and a.dtype == np.float64 and a.flags.c_contiguous):
+                raise ValueError("prefetch needs C-contiguous float64 arrays")
+        c = out if out is not None else cls(ctx)
+        ctx.check(lib().b200reg_cloud64_prefetch(ctx.h, _p(xyz), _p(nrm), xyz.shape[0], C.byref(c.h)))
+        c._pending = (xyz, nrm)
+        return c
+
+    def acquire(self):
+        self.ctx.check(lib().b200reg_cloud64_acquire(self.ctx.h, self.h))
+        self._pending = None
+        return self
 
     @property
     def size(self):

@@ -222,6 +222,8 @@ void b200reg_ctx_destroy(b200reg_ctx* ctx) {
   cudaEventDestroy(ctx->ev1);
   cudaEventDestroy(ctx->tev0);
   cudaEventDestroy(ctx->tev1);
+  if (ctx->copyStream) { cudaStreamSynchronize(ctx->copyStream); cudaStreamDestroy(ctx->copyStream); }
+  if (ctx->copyFence) cudaEventDestroy(ctx->copyFence);
   cudaStreamDestroy(ctx->stream);
   delete ctx;
 }

@@ -49,6 +49,9 @@ struct b200reg_ctx {
   // pinned slots the index builds copy their device-derived headers into (index.cu); chunks are freed with the ctx
   std::vector<void*> hdrChunks;
   std::vector<IndexHeader*> hdrFree;
+  // next-scan prefetch (b200reg_cloud64_prefetch): host-to-device copies run here, ordered behind the compute stream through copyFence
+  cudaStream_t copyStream = nullptr;
+  cudaEvent_t copyFence = nullptr;
 };
 
 // Device memory comes from the device's stream-ordered pool (release threshold raised in b200reg_ctx_create so freed blocks stay
@@ -85,6 +88,8 @@ struct b200reg_cloud64 {
   double* xyz = nullptr;
   double* nrm = nullptr;   // allocated with xyz; valid iff hasNormals
   bool hasNormals = false;
+  cudaEvent_t ready = nullptr;   // b200reg_cloud64_prefetch: completion of the copy-stream upload
+  bool prefetched = false;       // an upload is in flight on the copy stream; b200reg_cloud64_acquire clears it
 };
 
 // What the index build derives ON THE DEVICE from the cloud (index.cu gridKernel): the kernels read it from HBM through

@@ -817,12 +817,52 @@ int32_t b200reg_cloud64_download(b200reg_ctx* ctx, const b200reg_cloud64* c, dou
   return B200REG_OK;
 }
 
+// Next-scan prefetch: the same upload on the ctx's COPY stream, so that it overlaps the kernels of the scan being processed
+// (a pinned host buffer makes the copy truly asynchronous).  The copy is ordered behind everything already enqueued on the
+// compute stream (which may still read *out's storage); b200reg_cloud64_acquire waits for it before the cloud is used.
+int32_t b200reg_cloud64_prefetch(b200reg_ctx* ctx, const double* xyz, const double* nrm, int64_t n, b200reg_cloud64** out) {
+  if (!ctx || !out || n < 0 || (n > 0 && !xyz)) return setErr(ctx, B200REG_E_INVALID_PARAM, "cloud64_prefetch: bad arguments");
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  if (!ctx->copyStream) {
+    CUDA_TRY(ctx, cudaStreamCreateWithFlags(&ctx->copyStream, cudaStreamNonBlocking));
+    CUDA_TRY(ctx, cudaEventCreateWithFlags(&ctx->copyFence, cudaEventDisableTiming));
+  }
+  if (*out && (*out)->prefetched) TRY(b200reg_cloud64_acquire(ctx, *out));
+  TRY(cloud64Out(ctx, out, n));
+  b200reg_cloud64* c = *out;
+  if (!c->ready) CUDA_TRY(ctx, cudaEventCreateWithFlags(&c->ready, cudaEventDisableTiming));
+  CUDA_TRY(ctx, cudaEventRecord(ctx->copyFence, ctx->stream));
+  CUDA_TRY(ctx, cudaStreamWaitEvent(ctx->copyStream, ctx->copyFence, 0));
+  if (n > 0) {
+    CUDA_TRY(ctx, cudaMemcpyAsync(c->xyz, xyz, sizeof(double) * 3 * (size_t)n, cudaMemcpyHostToDevice, ctx->copyStream));
+    if (nrm) CUDA_TRY(ctx, cudaMemcpyAsync(c->nrm, nrm, sizeof(double) * 3 * (size_t)n, cudaMemcpyHostToDevice, ctx->copyStream));
+  }
+  CUDA_TRY(ctx, cudaEventRecord(c->ready, ctx->copyStream));
+  c->n = n;
+  c->hasNormals = nrm != nullptr;
+  c->prefetched = true;
+  return B200REG_OK;
+}
+
+// The host waits for the prefetch's copy (normally long finished) and the compute stream is ordered behind it: afterwards the
+// cloud behaves like an uploaded one and the host buffer may be reused.
+int32_t b200reg_cloud64_acquire(b200reg_ctx* ctx, b200reg_cloud64* c) {
+  if (!ctx || !c) return setErr(ctx, B200REG_E_INVALID_PARAM, "cloud64_acquire: bad arguments");
+  if (!c->prefetched) return B200REG_OK;
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  CUDA_TRY(ctx, cudaEventSynchronize(c->ready));
+  CUDA_TRY(ctx, cudaStreamWaitEvent(ctx->stream, c->ready, 0));
+  c->prefetched = false;
+  return B200REG_OK;
+}
+
 int64_t b200reg_cloud64_size(const b200reg_cloud64* c) { return c ? c->n : 0; }
 int32_t b200reg_cloud64_has_normals(const b200reg_cloud64* c) { return (c && c->hasNormals) ? 1 : 0; }
 
 void b200reg_cloud64_free(b200reg_ctx* ctx, b200reg_cloud64* c) {
   if (!c) return;
   if (ctx) { cudaSetDevice(ctx->device); cudaStreamSynchronize(ctx->stream); }
+  if (c->ready) { cudaEventSynchronize(c->ready); cudaEventDestroy(c->ready); }
   devFree(ctx, c->xyz); devFree(ctx, c->nrm);
   delete c;
 }

@@ -70,6 +70,8 @@ Mapper::Mapper(b200reg_ctx* ctx, const MapperParams& params) : ctx_(ctx), params
 Mapper::~Mapper() {
   if (reading_) b200reg_cloud_free(ctx_, reading_);
   b200reg_cloud64_free(ctx_, raw_);
+  b200reg_cloud64_free(ctx_, next_[0]);
+  b200reg_cloud64_free(ctx_, next_[1]);
   b200reg_cloud64_free(ctx_, cropped_);
   b200reg_cloud64_free(ctx_, merge_);
   b200reg_cloud64_free(ctx_, match_);
@@ -146,9 +148,32 @@ bool Mapper::addRangeMeasurement(const double* xyz, const double* normals, int64
   stats_ = MapperStepStats();
   error_.clear();
   StageClock clk;
-  if (b200reg_cloud64_upload(ctx_, xyz, normals, n, &raw_) != B200REG_OK) { error_ = b200reg_last_error(ctx_); return false; }
+  int slot = -1;
+  for (int k = 0; k < 2 && !normals; ++k)
+    if (next_[k] && prefetchedPtr_[k] == xyz && prefetchedN_[k] == n) slot = k;
+  if (slot >= 0) {   // the scan prefetch() started uploading
+    prefetchedPtr_[slot] = nullptr;
+    prefetchedN_[slot] = -1;
+    std::swap(raw_, next_[slot]);
+    if (b200reg_cloud64_acquire(ctx_, raw_) != B200REG_OK) { error_ = b200reg_last_error(ctx_); return false; }
+  } else if (b200reg_cloud64_upload(ctx_, xyz, normals, n, &raw_) != B200REG_OK) {
+    error_ = b200reg_last_error(ctx_);
+    return false;
+  }
   clk.lap(&stats_.stageMs[MapperStepStats::kWideCrop]);   // (the upload is booked with the first stage)
   return step(time, odom);
+}
+
+bool Mapper::prefetch(const double* xyz, int64_t n) {
+  int slot = prefetchSlot_;
+  if (prefetchedPtr_[slot] && !prefetchedPtr_[slot ^ 1]) slot ^= 1;   // keep a pending scan when the other slot is free
+  prefetchSlot_ = slot ^ 1;
+  prefetchedPtr_[slot] = nullptr;
+  prefetchedN_[slot] = -1;
+  if (b200reg_cloud64_prefetch(ctx_, xyz, nullptr, n, &next_[slot]) != B200REG_OK) { error_ = b200reg_last_error(ctx_); return false; }
+  prefetchedPtr_[slot] = xyz;
+  prefetchedN_[slot] = n;
+  return true;
 }
 
 bool Mapper::addRangeMeasurementPointCloud2(const uint8_t* data, size_t bytes, const b200reg_pc2_layout& layout, double time, const double odom[16]) {

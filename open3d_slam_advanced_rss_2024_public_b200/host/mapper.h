@@ -73,6 +73,12 @@ class Mapper {
   bool addRangeMeasurementPointCloud2(const uint8_t* data, size_t bytes, const b200reg_pc2_layout& layout, double time,
                                       const double odomToRangeSensor[16]);
 
+  // Start uploading a coming scan on the context's copy stream (what SlamWrapper's scan buffer gives the mapping worker the
+  // chance to do): called BEFORE addRangeMeasurement of the current scan, the copy overlaps that scan's kernels.  Two scans may
+  // be pending (the current one and the next); xyz must stay unchanged until the addRangeMeasurement(xyz, nullptr, n, ...) call
+  // that consumes it.  A measurement whose arguments match no pending prefetch is uploaded as usual.
+  bool prefetch(const double* xyz, int64_t n);
+
   const double* mapToRangeSensor() const { return mapToRangeSensor_; }
   b200reg_map* map() { return map_; }
   const MapperStepStats& lastStats() const { return stats_; }
@@ -90,6 +96,10 @@ class Mapper {
   b200reg_icp* icp_ = nullptr;
   b200reg_cloud* reading_ = nullptr;   // fp32 DataPoints mirror of match_ (open3dToPointmatcher on the device)
   b200reg_cloud64 *raw_ = nullptr, *cropped_ = nullptr, *merge_ = nullptr, *match_ = nullptr;
+  b200reg_cloud64* next_[2] = {nullptr, nullptr};   // prefetched scans (one is swapped with raw_ when it is consumed)
+  const double* prefetchedPtr_[2] = {nullptr, nullptr};
+  int64_t prefetchedN_[2] = {-1, -1};
+  int prefetchSlot_ = 0;
   double mapToRangeSensor_[16], mapToRangeSensorPrev_[16], lastInsertion_[16], odomPrev_[16];
   double cropperPose_[16];             // mapBuilderCropper_'s pose: set AFTER each insertion (Submap.cpp:86), so carving sees the previous one
   int64_t nScansInsertedMap_ = 0;

@@ -254,6 +254,7 @@ int32_t b200map_add_pointcloud2(void* m, const uint8_t* data, size_t bytes, cons
   setMsg(err, err_cap, mp->lastError());
   return ok ? 1 : 0;
 }
+int32_t b200map_prefetch(void* m, const double* xyz, int64_t n) { return ((b200::Mapper*)m)->prefetch(xyz, n) ? 1 : 0; }
 b200reg_map* b200map_map(void* m) { return ((b200::Mapper*)m)->map(); }
 
 }  // extern "C"

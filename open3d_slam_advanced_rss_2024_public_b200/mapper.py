@@ -35,6 +35,8 @@ def _lib():
         L.b200map_add_pointcloud2.restype = C.c_int32
         L.b200map_add_pointcloud2.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.POINTER(capi.Pc2Layout), C.c_double, C.c_void_p, C.c_void_p,
                                               C.POINTER(MapperStats), C.c_char_p, C.c_int32]
+        L.b200map_prefetch.restype = C.c_int32
+        L.b200map_prefetch.argtypes = [C.c_void_p, C.c_void_p, C.c_int64]
         L.b200map_map.restype = C.c_void_p
         L.b200map_map.argtypes = [C.c_void_p]
         L._b200map_ready = True
@@ -72,6 +74,14 @@ class Mapper:
                                                   xyz.shape[0], float(time), odom.ctypes.data_as(C.c_void_p), pose.ctypes.data_as(C.c_void_p),
                                                   C.byref(st), err, len(err))
         return bool(ok), pose.reshape(4, 4), st, err.value.decode("utf-8", "replace")
+
+    def prefetch(self, xyz):
+        """Start uploading the NEXT scan (a C-contiguous float64 n x 3 array, ideally pinned) on the copy stream; the array must
+        stay alive and unchanged until the add_range_measurement(xyz, ...) call that passes the SAME array."""
+        if not (isinstance(xyz, np.ndarray) and xyz.dtype == np.float64 and xyz.flags.c_contiguous):
+            raise ValueError("prefetch needs a C-contiguous float64 array (the same object is passed to add_range_measurement)")
+        if not _lib().b200map_prefetch(self.h, xyz.ctypes.data_as(C.c_void_p), xyz.shape[0]):
+            raise RuntimeError("b200map_prefetch failed")
 
     def add_pointcloud2(self, data, layout, time, odom):
         """The same step fed with the bytes of a sensor_msgs/PointCloud2 (layout: capi.pc2_layout)."""

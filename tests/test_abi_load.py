@@ -80,5 +80,5 @@ def test_mapper_driver_symbols_are_exported():
     """libb200pm.so carries the open3d_slam Mapper driver (host/mapper.h) behind b200map_* (no compute without a GPU)."""
     from open3d_slam_advanced_rss_2024_public_b200 import mapper
     L = mapper._lib()
-    for name in ("b200map_create", "b200map_destroy", "b200map_set_pose", "b200map_add_range_measurement", "b200map_add_pointcloud2", "b200map_map"):
+    for name in ("b200map_create", "b200map_destroy", "b200map_set_pose", "b200map_add_range_measurement", "b200map_add_pointcloud2", "b200map_prefetch", "b200map_map"):
         assert hasattr(L, name)

@@ -317,3 +317,47 @@ def test_mapper_pointcloud2_entry_equals_array_entry(ctx):
     ok, _, _, err = mb.add_pointcloud2(buf.reshape(-1)[:100], capi.pc2_layout(n, 1, step, fields), 1.0, odom[-1])
     assert not ok and "point_step" in err
     ma.close(); mb.close()
+
+
+def test_mapper_prefetch_gives_the_same_trajectory(ctx):
+    """Mapper.prefetch (b200reg_cloud64_prefetch on the copy stream, two scans pending) changes WHEN a scan is uploaded, never what
+    the step computes: poses, counts and the final map equal the plain add_range_measurement run bit for bit — also when a
+    prefetched scan is never consumed, and when the scan sizes differ (storage of the slots is recycled and grown)."""
+    import torch
+    from open3d_slam_advanced_rss_2024_public_b200 import capi
+    from open3d_slam_advanced_rss_2024_public_b200.mapper import Mapper
+    scene = scenes.Scene(2001, size=(40.0, 24.0, 8.0), n_boxes=14, n_cyl=8)
+    poses = trajectory(7)
+    odom = drifting_odometry(poses, 2005)
+    icp = capi.icp_config(knn=1, max_dist=0.5, trim_ratio=0.9, max_angle=1.57, max_iter=15, min_diff_rot=1e-3, min_diff_trans=1e-2, smooth_length=3)
+    mk = lambda: Mapper(ctx, capi.crop_spec(capi.CROP_MINMAX_RADIUS, np.zeros(3), rmin=1.0, rmax=30.0),  # noqa: E731
+                        capi.crop_spec(capi.CROP_MAX_RADIUS, np.zeros(3), rmax=25.0), icp, scan_voxel_size=0.25, normals_knn=10,
+                        normals_radius=1.0, map_voxel_size=0.3, min_movement=0.0, reference_period=0.25)
+    scans = [scenes.lidar_scan(scene, T, n_beams=24 + 4 * (i % 3), n_az=300 + 40 * i, noise_sigma=0.01, seed=900 + i).astype(np.float64) for i, T in enumerate(poses)]
+    pinned = [torch.from_numpy(s).pin_memory().numpy() for s in scans]
+    ma, mb = mk(), mk()
+    ma.set_pose(poses[0]); mb.set_pose(poses[0])
+    mb.prefetch(pinned[0])
+    decoy = np.ascontiguousarray(scans[3][:1000])
+    for i, od in enumerate(odom):
+        if i + 1 < len(pinned):
+            mb.prefetch(pinned[i + 1])          # uploads while scan i is processed
+        if i == 4:
+            mb.prefetch(decoy)                  # a third prefetch replaces a pending one: that scan is then uploaded as usual
+        ok_a, pose_a, st_a, err_a = ma.add_range_measurement(scans[i], 0.1 * i, od)
+        ok_b, pose_b, st_b, err_b = mb.add_range_measurement(pinned[i], 0.1 * i, od)
+        assert ok_a and ok_b, (err_a, err_b)
+        assert np.array_equal(pose_a, pose_b), i
+        assert (st_a.iterations, st_a.reading_points, st_a.merge_points, st_a.map_points) == (st_b.iterations, st_b.reading_points, st_b.merge_points, st_b.map_points)
+    xa, na = ma.map_points()
+    xb, nb = mb.map_points()
+    assert np.array_equal(xa, xb) and np.array_equal(na, nb)
+    ma.close(); mb.close()
+    # the cloud-level entry points
+    c = capi.Cloud64.prefetch(ctx, pinned[2])
+    c.acquire()
+    assert np.array_equal(c.download()[0], scans[2])
+    capi.Cloud64.prefetch(ctx, pinned[1], out=c)
+    capi.Cloud64.prefetch(ctx, pinned[3], out=c)     # a second prefetch into a pending cloud waits for the first
+    assert np.array_equal(c.acquire().download()[0], scans[3])
+    c.free()
