@@ -173,6 +173,20 @@ int32_t b200reg_point_to_plane_covariance(b200reg_ctx* ctx, const b200reg_cloud*
 int32_t b200reg_point_to_plane_residual(b200reg_ctx* ctx, const b200reg_cloud* reading, const b200reg_cloud* reference, const int32_t* ids,
                                         const float* d2, const float* w, int32_t k, int32_t force2D, double* residual_out, int64_t* kept_out);
 
+/* The same computation for callers that may not allocate (CUDA-graph capture set-ups, tight serving loops, harnesses that forbid
+ * cudaMalloc).  This entry point has NO counterpart in the reference.
+ * Arguments, result and error codes are those of b200reg_point_to_plane_residual (same kernels, same grid: the same bits), but the
+ * device staging of ids / d2 / w and the partial sums live in a static device array of the library — 12 bytes per pair for at most
+ * B200REG_NOALLOC_MAX_PAIRS pairs (reading size x k) plus 8 KiB, held by every GPU that loads the library until the process exits —
+ * and the call performs no cudaMalloc / cudaFree / pool or pinned allocation.  More pairs than the maximum: B200REG_E_INVALID_PARAM
+ * with a message naming the limit.  Every call on a device shares the one array (it is overwritten, and its reduction slots are
+ * cleared, at the start of each call): calls that overlap on the GPU — other contexts or threads on the same device — race; calls
+ * on one context are ordered by its stream. */
+#define B200REG_NOALLOC_MAX_PAIRS (1 << 20)
+int32_t b200reg_point_to_plane_residual_noalloc(b200reg_ctx* ctx, const b200reg_cloud* reading, const b200reg_cloud* reference,
+                                                const int32_t* ids, const float* d2, const float* w, int32_t k, int32_t force2D,
+                                                double* residual_out, int64_t* kept_out);
+
 /* PointToPlaneErrorMinimizer::compute tail (PointToPlane.cpp:185-368): solve (LLT, rank-reduced minimum norm when
  * singular), Rodrigues, un-centre.  Host arithmetic in fp64; T_out = the 4x4 step transform rounded to fp32. */
 int32_t b200reg_solve_point_to_plane(const double A[36], const double b[6], const double mean_reading[3],

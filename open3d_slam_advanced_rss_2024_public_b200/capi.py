@@ -155,6 +155,7 @@ SYMBOLS = {
     "b200reg_surface_normal_outlier": (C.c_int32, [_VP, _VP, _VP, C.c_int64, _VP, C.c_int32, C.c_int64, C.c_float, _VP]),
     "b200reg_point_to_plane": (C.c_int32, [_VP, _VP, _VP, _VP, _VP, _VP, C.c_int32, C.c_int32, _VP, _VP, C.POINTER(StepStats)]),
     "b200reg_point_to_plane_residual": (C.c_int32, [_VP, _VP, _VP, _VP, _VP, _VP, C.c_int32, C.c_int32, C.POINTER(C.c_double), C.POINTER(C.c_int64)]),
+    "b200reg_point_to_plane_residual_noalloc": (C.c_int32, [_VP, _VP, _VP, _VP, _VP, _VP, C.c_int32, C.c_int32, C.POINTER(C.c_double), C.POINTER(C.c_int64)]),
     "b200reg_solve_point_to_plane": (C.c_int32, [_VP, _VP, _VP, _VP, C.c_int32, C.c_int32, _VP, _VP]),
     "b200reg_icp_create": (C.c_int32, [_VP, C.POINTER(IcpConfig), C.POINTER(_VP)]),
     "b200reg_icp_destroy": (None, [_VP]),
@@ -260,6 +261,9 @@ def icp_config(**kw):
             v = (C.c_int32 * 3)(*(list(v) + [0, 0, 0])[:3])
         setattr(c, k, v)
     return c
+
+
+NOALLOC_MAX_PAIRS = 1 << 20   # B200REG_NOALLOC_MAX_PAIRS
 
 
 class Context:
@@ -425,6 +429,16 @@ class Context:
         k = ids.size // max(reading.size, 1)
         res, kept = C.c_double(0), C.c_int64(0)
         self.check(lib().b200reg_point_to_plane_residual(self.h, reading.h, reference.h, _p(ids), _p(d2), _p(w), k, int(force2D), C.byref(res), C.byref(kept)))
+        return res.value, kept.value
+
+    def point_to_plane_residual_noalloc(self, reading, reference, ids, d2, w, force2D=False):
+        """The allocation-free variant (static device scratch, at most NOALLOC_MAX_PAIRS pairs); same result as point_to_plane_residual."""
+        ids = np.ascontiguousarray(ids, dtype=np.int32)
+        d2, w = _f32(d2), _f32(w)
+        k = ids.size // max(reading.size, 1)
+        res, kept = C.c_double(0), C.c_int64(0)
+        self.check(lib().b200reg_point_to_plane_residual_noalloc(self.h, reading.h, reference.h, _p(ids), _p(d2), _p(w), k, int(force2D),
+                                                                 C.byref(res), C.byref(kept)))
         return res.value, kept.value
 
     def voxel_down_sample(self, voxel, xyz, nrm=None):

@@ -5,6 +5,7 @@
 #include <cfloat>
 #include <cmath>
 #include <cstring>
+#include <mutex>
 
 #include <cub/cub.cuh>
 
@@ -606,3 +607,83 @@ int32_t b200reg_point_to_plane_covariance(b200reg_ctx* ctx, const b200reg_cloud*
 }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------------------------------------------------------------------
+// The allocation-free variant of b200reg_point_to_plane_residual (no counterpart in the reference; added
+// for callers that may not call cudaMalloc).  Its scratch — the staged matches, distances and weights, the
+// per-block partial sums and the result — is this file-scope device array, which every GPU that loads the library holds until
+// exit (12 MiB + 8 KiB).  In host code `g_noallocScratch` is only a stand-in for the symbol: the device address comes from
+// cudaGetSymbolAddress, taken once per device with that device current.  All calls share the array: calls that overlap on the
+// GPU (different streams / contexts of one device) race.
+// ---------------------------------------------------------------------------------------------------------------------------
+constexpr size_t NOALLOC_PAIRS = B200REG_NOALLOC_MAX_PAIRS;
+constexpr int NOALLOC_MAX_BLOCKS = 511;                                      // partials: (blocks + 1) x RES_N doubles <= 8 KiB
+constexpr size_t NOALLOC_TAIL = sizeof(double) * RES_N * (NOALLOC_MAX_BLOCKS + 1);
+constexpr size_t NOALLOC_BYTES = NOALLOC_PAIRS * 12 + NOALLOC_TAIL;
+static __device__ __align__(256) unsigned char g_noallocScratch[NOALLOC_BYTES];
+
+namespace {
+constexpr int NOALLOC_MAX_DEVICES = 64;
+std::mutex g_noallocMutex;
+unsigned char* g_noallocAddr[NOALLOC_MAX_DEVICES] = {nullptr};
+
+// device address of the scratch on ctx's device (that device must be current)
+int noallocScratch(b200reg_ctx* ctx, unsigned char** out) {
+  if (ctx->device < 0 || ctx->device >= NOALLOC_MAX_DEVICES) return setErr(ctx, B200REG_E_INVALID_PARAM, "noalloc: device ordinal %d out of range", ctx->device);
+  std::lock_guard<std::mutex> lock(g_noallocMutex);
+  if (!g_noallocAddr[ctx->device]) {
+    unsigned char* ptr = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress((void**)&ptr, g_noallocScratch);
+    if (e != cudaSuccess || !ptr) return setErr(ctx, B200REG_E_CUDA, "noalloc: cudaGetSymbolAddress failed: %s", cudaGetErrorString(e));
+    g_noallocAddr[ctx->device] = ptr;
+  }
+  *out = g_noallocAddr[ctx->device];
+  return B200REG_OK;
+}
+}  // namespace
+
+extern "C" int32_t b200reg_point_to_plane_residual_noalloc(b200reg_ctx* ctx, const b200reg_cloud* reading, const b200reg_cloud* reference,
+                                                           const int32_t* ids, const float* d2, const float* w, int32_t k, int32_t force2D,
+                                                           double* residual_out, int64_t* kept_out) {
+  if (!ctx || !reading || !reference || !ids || !d2 || !w || !residual_out || k < 1)
+    return setErr(ctx, B200REG_E_INVALID_PARAM, "point_to_plane_residual_noalloc: bad arguments");
+  if (!reference->nrm) return setErr(ctx, B200REG_E_INVALID_FIELD, "PointToPlaneErrorMinimizer: reference cloud has no 'normals' descriptor");
+  const int64_t total = reading->n * (int64_t)k;
+  if (total > (int64_t)NOALLOC_PAIRS)
+    return setErr(ctx, B200REG_E_INVALID_PARAM, "point_to_plane_residual_noalloc: %lld pairs exceed the static scratch (B200REG_NOALLOC_MAX_PAIRS = %lld)",
+                  (long long)total, (long long)NOALLOC_PAIRS);
+  *residual_out = 0.0;
+  if (kept_out) *kept_out = 0;
+  if (total == 0) return B200REG_OK;
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  unsigned char* base = nullptr;
+  TRY(noallocScratch(ctx, &base));
+  int* dIds = (int*)base;
+  float* dD2 = (float*)(base + NOALLOC_PAIRS * 4);
+  float* dW = (float*)(base + NOALLOC_PAIRS * 8);
+  double* part = (double*)(base + NOALLOC_PAIRS * 12);
+  const int blocks = (int)fmax(1.0, fmin((double)divUp(total, 1024), fmin((double)(2 * ctx->sm_count), (double)NOALLOC_MAX_BLOCKS)));   // reducePairs' grid
+  double* res = part + (size_t)blocks * RES_N;
+  // the array keeps the previous call's contents: everything read below is overwritten first (the partials and the result are
+  // cleared as well, although every block stores its own)
+  CUDA_TRY(ctx, cudaMemsetAsync(part, 0, NOALLOC_TAIL, ctx->stream));
+  CUDA_TRY(ctx, cudaMemcpyAsync(dIds, ids, sizeof(int) * (size_t)total, cudaMemcpyHostToDevice, ctx->stream));
+  CUDA_TRY(ctx, cudaMemcpyAsync(dD2, d2, sizeof(float) * (size_t)total, cudaMemcpyHostToDevice, ctx->stream));
+  CUDA_TRY(ctx, cudaMemcpyAsync(dW, w, sizeof(float) * (size_t)total, cudaMemcpyHostToDevice, ctx->stream));
+  PairArgs A;
+  memset(&A, 0, sizeof(A));
+  A.reading = reading->xyz; A.refPts = reference->xyz; A.refNrm = reference->nrm;
+  A.ids = dIds; A.d2 = dD2; A.w = dW;
+  A.total = total; A.k = k;
+  A.alpha = force2D ? 1.0 : 0.0;
+  residualKernel<<<blocks, 256, 0, ctx->stream>>>(A, part);
+  LAUNCH_CHECK(ctx);
+  sumPartialsKernel<<<1, 64, 0, ctx->stream>>>(part, blocks, RES_N, res);
+  LAUNCH_CHECK(ctx);
+  double m[RES_N] = {0.0, 0.0};
+  CUDA_TRY(ctx, cudaMemcpyAsync(m, res, sizeof(m), cudaMemcpyDeviceToHost, ctx->stream));
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  *residual_out = m[0];
+  if (kept_out) *kept_out = (int64_t)m[1];
+  return B200REG_OK;
+}
