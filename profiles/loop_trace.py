@@ -15,7 +15,8 @@ from open3d_slam_advanced_rss_2024_public_b200 import capi  # noqa: E402
 c = scenes.config2(m=int(os.environ.get("PROF_MAP", 5_000_000)), n_beams=128, n_az=1024, scene_seed=1001)
 f4 = lambda a: np.concatenate([a.astype(np.float32), np.ones((a.shape[0], 1), np.float32)], axis=1)  # noqa: E731
 ctx = capi.Context(0)
-icp = capi.ICP(ctx, knn=1, max_dist=1.0, trim_ratio=0.8, max_iter=40, min_diff_rot=1e-3, min_diff_trans=1e-2, smooth_length=3)
+icp = capi.ICP(ctx, knn=1, max_dist=1.0, trim_ratio=0.8, max_iter=40, min_diff_rot=1e-3, min_diff_trans=1e-2, smooth_length=3,
+              cell=float(os.environ.get("PROF_CELL", 0.0)))
 icp.set_reference(ctx.upload(f4(c["map_xyz"]), c["map_nrm"].astype(np.float32)))
 scan = ctx.upload(f4(c["scan"]))
 Ti = c["T_init"].astype(np.float32)
