@@ -218,7 +218,7 @@ def run_config2(args, rank, local_rank, world):
         icp.set_reference(cref)
         build_ms.append(ctx.timer_stop())
     build_warm = float(np.median(build_ms[2:]))
-    batch = capi.Batch(ctx, lanes=args.lanes, group=args.group, cell=args.cell, **ICP_KW)
+    batch = capi.Batch(ctx, lanes=args.lanes, cell=args.cell, **ICP_KW)
     batch.set_reference(cref)
     cscans = [ctx.upload(s) for s in w["scans"]]
     pinned = [torch.from_numpy(s).pin_memory() for s in w["scans"]]
@@ -351,8 +351,7 @@ def run_config2(args, rank, local_rank, world):
         "metric": "ICP registrations/sec (131k scan vs 5M map)", "value": value, "unit": "registrations/s", "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": config2_name(args), "step": f"{BATCH} independent registrations ({BATCH} sensor poses of the scene) in flight on {batch.lanes} lanes (group size {batch.group_size}) of a b200reg_batch against the resident map index",
-                   "lanes": batch.lanes, "group_size": batch.group_size,
+        "config": {"workload": config2_name(args), "step": f"{BATCH} independent registrations ({BATCH} sensor poses of the scene) in flight on {batch.lanes} lanes of a b200reg_batch against the resident map index",
                    "iterations": iters, "cell_m": icp.index.cell, "l2": "flushed between timed steps (256 MB memset)",
                    "build": "amortised (index resident, Mapper regime: one build per 20 scans)", "index_build_ms": build_warm,
                    "index_build_ms_cold_first": build_ms[0], "index_build_gbs": B_BUILD * m / (build_warm * 1e-3) / 1e9,
@@ -412,7 +411,6 @@ def main():
     ap.add_argument("--azimuths", type=int, default=1024)
     ap.add_argument("--cell", type=float, default=0.0)
     ap.add_argument("--lanes", type=int, default=0, help="lanes of the b200reg_batch (0: library default)")
-    ap.add_argument("--group", type=int, default=-1, help="group size of the b200reg_batch (1: plain lanes; -1: library default)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--knn-reps", type=int, default=20)
     ap.add_argument("--pairs", type=int, default=256, help="config4: submap pairs")

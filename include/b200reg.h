@@ -258,15 +258,6 @@ typedef struct b200reg_batch b200reg_batch;
 int32_t b200reg_batch_create(b200reg_ctx* ctx, const b200reg_icp_config* cfg, int32_t lanes, b200reg_batch** out);
 void    b200reg_batch_destroy(b200reg_batch* batch);
 int32_t b200reg_batch_lanes(const b200reg_batch* batch);
-/* Group mode of the same batch: lanes [g * group_size, (g + 1) * group_size) form group g, and the registrations a group has in
- * flight are advanced TOGETHER by one device-resident loop — one match / select / reduce / solve launch per iteration for the whole
- * group (members whose checkers have stopped drop out, the loop ends with the last one) — so the per-iteration launch and turnaround
- * cost is paid per group, not per pair, while the lanes of other groups prepare their pairs (uploads, index builds) underneath.
- * Results stay bit-identical to the serial path.  group_size: 1 = plain lanes, 2..16 (reduced to a divisor of lanes), < 0 = default
- * (env B200REG_BATCH_GROUP, else the library default).  b200reg_batch_create(ctx, cfg, lanes, out) = group_size -1.
- * stats[i].device_ms of a grouped pair is the duration of its group's loop. */
-int32_t b200reg_batch_create_grouped(b200reg_ctx* ctx, const b200reg_icp_config* cfg, int32_t lanes, int32_t group_size, b200reg_batch** out);
-int32_t b200reg_batch_group_size(const b200reg_batch* batch);
 /* ICP::initReference ONCE for the whole batch: every pair whose reference is not given (refs == NULL below) registers its reading
  * against this index — many scans, or many initial guesses of one scan, against one map (re-localisation, multi-sequence mapping). */
 int32_t b200reg_batch_set_reference(b200reg_batch* batch, const b200reg_cloud* reference);

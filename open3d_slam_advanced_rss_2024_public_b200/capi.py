@@ -165,8 +165,6 @@ SYMBOLS = {
     "b200reg_batch_create": (C.c_int32, [_VP, C.POINTER(IcpConfig), C.c_int32, C.POINTER(_VP)]),
     "b200reg_batch_destroy": (None, [_VP]),
     "b200reg_batch_lanes": (C.c_int32, [_VP]),
-    "b200reg_batch_create_grouped": (C.c_int32, [_VP, C.POINTER(IcpConfig), C.c_int32, C.c_int32, C.POINTER(_VP)]),
-    "b200reg_batch_group_size": (C.c_int32, [_VP]),
     "b200reg_batch_set_reference": (C.c_int32, [_VP, _VP]),
     "b200reg_batch_register": (C.c_int32, [_VP, C.c_int32, _VP, _VP, _VP, _VP, _VP, _VP]),
     "b200reg_batch_register_host": (C.c_int32, [_VP, C.c_int32, _VP, _VP, _VP, _VP, _VP, _VP]),
@@ -666,20 +664,15 @@ def register_batch(ctx, cfg, refs, readings, T_init):
 class Batch:
     """b200reg_batch: `lanes` registrations in flight on the ctx's device (pair i -> lane i mod lanes)."""
 
-    def __init__(self, ctx, cfg=None, lanes=0, group=-1, **kw):
+    def __init__(self, ctx, cfg=None, lanes=0, **kw):
         self.ctx = ctx
         self.cfg = cfg if cfg is not None else icp_config(**kw)
         self.h = _VP()
-        ctx.check(lib().b200reg_batch_create_grouped(ctx.h, C.byref(self.cfg), int(lanes), int(group), C.byref(self.h)))
+        ctx.check(lib().b200reg_batch_create(ctx.h, C.byref(self.cfg), int(lanes), C.byref(self.h)))
 
     @property
     def lanes(self):
         return int(lib().b200reg_batch_lanes(self.h))
-
-    @property
-    def group_size(self):
-        """1: plain lanes; > 1: that many registrations advanced together by one device-resident loop (b200reg_batch_create_grouped)."""
-        return int(lib().b200reg_batch_group_size(self.h))
 
     def _out(self, n, T_init):
         Ti = np.ascontiguousarray(np.asarray(T_init, dtype=np.float32).reshape(n, 16))

@@ -184,27 +184,6 @@ struct IcpDevState {    // initialised by the host, advanced by icpTailKernel ev
 };
 #define ICP_STATE_HEAD_BYTES offsetof(IcpDevState, chk)
 
-// ---- a GROUP of registrations advanced by ONE while-graph (icp.cu, b200reg_batch): every kernel of the group loop handles all
-// members that still iterate — the match kernel's resident blocks pull work from every member's counter in turn, select / reduce run
-// with the member index in blockIdx.y (same grid.x, hence the same partial sums, as a registration on its own), one tail block per
-// member — so the per-iteration launch and turnaround cost is paid once per group instead of once per registration.
-#define LOOP_GROUP_MAX 16
-struct SelState;
-struct LoopGroupSlot {
-  const IcpDevParams* P;
-  IcpDevState* S;
-  unsigned long long* counters;   // [0] visits, [1] far queries, [2] the match kernel's work counter
-  SelState* st;
-  double* result;                 // NUM_MOM moments
-};
-struct LoopGroup {
-  int count;
-  unsigned tailTicket;
-  unsigned anyActive;
-  int pad;
-  LoopGroupSlot slot[LOOP_GROUP_MAX];
-};
-
 // resident blocks per SM of the k = 1 match kernels (knn.cu): 4 x 256 threads leave 64 registers per thread — no spills; 5, 6 and 8
 // blocks (48 / 40 / 32 registers, 140-460 B of spills) and 2-3 blocks (80-119 registers) all measured slower (profiles/r1_notes.md)
 #ifndef KNN1_LOOP_MINB

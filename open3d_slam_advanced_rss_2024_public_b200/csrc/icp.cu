@@ -7,7 +7,6 @@
 #include "icp_kernels.cuh"
 
 int launchKnn1Loop(b200reg_ctx* ctx, const IcpDevParams* P, const IcpDevState* S, unsigned long long* counters, int blocks);
-int launchKnn1LoopGroup(const LoopGroup* G, int blocks, cudaStream_t stream);
 int runKnn(b200reg_ctx* ctx, const b200reg_index* ix, const float4* queries, int64_t n, const float* T, int k, float maxDist, int allowSelf,
            int seeded);
 
@@ -436,10 +435,8 @@ struct b200reg_icp {
   int graphNodes = 0;               // kernels per iteration of the body
   // a registration enqueued on the ctx stream and not yet collected (icpEnqueue / icpFinish): the batch lanes keep one in flight each
   bool pending = false;
-  bool groupMember = false;         // the loop of the pending registration runs inside a group graph (b200reg_batch): its kernels are counted there
   float pendTinit[16];
   int64_t pendN = 0;
-  int pendBodyRuns = 0;             // times the loop body ran for the registration collected last
   double pendT1 = 0;
   b200reg_icp_stats pendStats{};
 };
@@ -591,9 +588,11 @@ namespace {
 // checks, A/b from the moments, the 6x6 solve, T_iter <- T_step * T_iter, the transformation checkers, and the loop
 // condition of the graph's while node.  Same __host__ __device__ arithmetic as the host loop (this file is built with
 // --fmad=false), so both loops take the same decisions.
-__device__ __forceinline__ bool icpTailBody(const IcpDevParams* __restrict__ P, IcpDevState* __restrict__ S,
-                                            const double* __restrict__ result, const SelState* __restrict__ st,
-                                            unsigned long long* __restrict__ visitCounter) {
+__global__ void __launch_bounds__(32) icpTailKernel(const IcpDevParams* __restrict__ P, IcpDevState* __restrict__ S,
+                                                    const double* __restrict__ result, const SelState* __restrict__ st,
+                                                    unsigned long long* __restrict__ visitCounter,
+                                                    cudaGraphConditionalHandle handle) {
+  if (threadIdx.x != 0) return;
   traceStamp(P->trace, 6);
   // every global read up front and independent of the others: one memory round trip instead of a chain of them
   const IcpDevParams p = *P;
@@ -641,33 +640,8 @@ __device__ __forceinline__ bool icpTailBody(const IcpDevParams* __restrict__ P, 
   S->errA = errv[0]; S->errB = errv[1]; S->errC = errv[2]; S->errD = errv[3];
   S->maxIterReached = maxIter ? 1 : 0;
   S->iterate = iterate ? 1 : 0;
-  return iterate;
-}
-
-__global__ void __launch_bounds__(32) icpTailKernel(const IcpDevParams* __restrict__ P, IcpDevState* __restrict__ S,
-                                                    const double* __restrict__ result, const SelState* __restrict__ st,
-                                                    unsigned long long* __restrict__ visitCounter,
-                                                    cudaGraphConditionalHandle handle) {
-  if (threadIdx.x != 0) return;
-  const bool iterate = icpTailBody(P, S, result, st, visitCounter);
   cudaGraphSetConditional(handle, iterate ? 1u : 0u);
   traceStamp(P->trace, 7);   // end of the tail
-}
-
-// The tails of a group: one block (one thread) per member; the last one out tells the while node whether ANY member goes on.
-__global__ void __launch_bounds__(32) icpTailGroupKernel(LoopGroup* __restrict__ G, cudaGraphConditionalHandle handle) {
-  if (threadIdx.x != 0) return;
-  if ((int)blockIdx.x < G->count) {
-    const LoopGroupSlot sl = G->slot[blockIdx.x];
-    if (sl.S->iterate != 0 && icpTailBody(sl.P, sl.S, sl.result, sl.st, sl.counters)) atomicOr(&G->anyActive, 1u);
-  }
-  __threadfence();
-  if (atomicAdd(&G->tailTicket, 1u) == gridDim.x - 1) {
-    __threadfence();
-    const unsigned any = atomicExch(&G->anyActive, 0u);
-    G->tailTicket = 0;
-    cudaGraphSetConditional(handle, any ? 1u : 0u);
-  }
 }
 
 #define GRAPH_TRY(expr)                                                    \
@@ -870,18 +844,7 @@ inline bool wantGraphLoop(const b200reg_icp* icp) { return icp->cfg.knn == 1 && 
 // First half of a registration through the device-resident loop: everything up to the read-back of the final state is enqueued
 // on the ctx stream; nothing waits.  The host image of the loop block and the result slot live in the ctx's pinned staging, so
 // ONE registration per ctx can be in flight (the batch lanes own a ctx each).
-// read-back of the 144-byte head of the final state, enqueued behind the loop on the ctx stream
-int icpReadback(b200reg_icp* icp) {
-  b200reg_ctx* ctx = icp->ctx;
-  IcpDevState* hR = (IcpDevState*)((char*)ctx->pinned + 16384);
-  CUDA_TRY(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
-  CUDA_TRY(ctx, cudaMemcpyAsync(hR, icp->dS, ICP_STATE_HEAD_BYTES, cudaMemcpyDeviceToHost, ctx->stream));
-  return B200REG_OK;
-}
-
-// launchOwn = false: everything up to the loop is enqueued (reading preparation, the loop block); the caller launches a group graph
-// that advances this registration together with others and then calls icpReadback.
-int icpEnqueue(b200reg_icp* icp, const b200reg_cloud* reading, const float T_init[16], bool launchOwn = true) {
+int icpEnqueue(b200reg_icp* icp, const b200reg_cloud* reading, const float T_init[16]) {
   b200reg_ctx* ctx = icp->ctx;
   const b200reg_icp_config& cfg = icp->cfg;
   b200reg_icp_stats& st = icp->pendStats;
@@ -909,6 +872,7 @@ int icpEnqueue(b200reg_icp* icp, const b200reg_cloud* reading, const float T_ini
   char* hBlock = pin + 8192;   // host image of the loop block
   IcpDevParams* hP = (IcpDevParams*)(hBlock + LOOP_PARAMS_OFF);
   IcpDevState* hS = (IcpDevState*)(hBlock + LOOP_STATE_OFF);
+  IcpDevState* hR = (IcpDevState*)(pin + 16384);
   memset(hBlock, 0, LOOP_PARAMS_OFF);   // visit / far counters
   memset(hP, 0, sizeof(*hP));
   hP->pts = icp->index->pts; hP->nrm = icp->index->nrm; hP->cellStart = icp->index->cellStart; hP->gp = &icp->index->dHdr->g;
@@ -946,11 +910,9 @@ int icpEnqueue(b200reg_icp* icp, const b200reg_cloud* reading, const float T_ini
   // counters + parameters + the part of the state the loop reads before writing it (head, checker counters, first ring slot)
   CUDA_TRY(ctx, cudaMemcpyAsync(icp->dBlock, hBlock, LOOP_STATE_OFF + sizeof(IcpDevState), cudaMemcpyHostToDevice, ctx->stream));
   CUDA_TRY(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
-  if (launchOwn) {
-    CUDA_TRY(ctx, cudaGraphLaunch(icp->exec, ctx->stream));
-    TRY(icpReadback(icp));
-  }
-  icp->groupMember = !launchOwn;
+  CUDA_TRY(ctx, cudaGraphLaunch(icp->exec, ctx->stream));
+  CUDA_TRY(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
+  CUDA_TRY(ctx, cudaMemcpyAsync(hR, icp->dS, ICP_STATE_HEAD_BYTES, cudaMemcpyDeviceToHost, ctx->stream));
   memcpy(icp->pendTinit, T_init, sizeof(icp->pendTinit));
   icp->pendN = n;
   icp->pending = true;
@@ -980,9 +942,7 @@ int icpFinish(b200reg_icp* icp, float T_out[16], b200reg_icp_stats* stats) {
   st.last_tau = hR->tau;
   st.convergence_s = nowSec() - icp->pendT1;
   // kernels of the graph: (iterations that ran the full body) x nodes; an iteration that failed early still ran them all
-  if (!icp->groupMember)
-    ctx->launches += (uint64_t)icp->graphNodes * (uint64_t)(hR->iterations + ((hR->errKind == ICPERR_NO_QUANTILE || hR->errKind == ICPERR_NO_POINTS) ? 1 : 0));
-  icp->pendBodyRuns = hR->iterations + ((hR->errKind == ICPERR_NO_QUANTILE || hR->errKind == ICPERR_NO_POINTS) ? 1 : 0);
+  ctx->launches += (uint64_t)icp->graphNodes * (uint64_t)(hR->iterations + ((hR->errKind == ICPERR_NO_QUANTILE || hR->errKind == ICPERR_NO_POINTS) ? 1 : 0));
   if (!indexHeader(ctx, icp->index)) return done(B200REG_E_INVALID_PARAM);   // non-finite reference: the loop ran on a dummy grid
   const float errv[4] = {hR->errA, hR->errB, hR->errC, hR->errD};
   const int gstatus = icpErrToStatus(ctx, hR->errKind, errv);
@@ -1104,9 +1064,6 @@ int32_t b200reg_icp_register(b200reg_icp* icp, const b200reg_cloud* reading, con
 // Results are those of the serial path, bit for bit: a lane runs exactly the code b200reg_icp_register runs.
 // =================================================================================================================
 #define BATCH_MAX_LANES 16
-#ifndef BATCH_DEFAULT_GROUP
-#define BATCH_DEFAULT_GROUP 1   /* lanes mode unless asked otherwise (b200reg_batch_create_grouped, env B200REG_BATCH_GROUP) */
-#endif
 struct b200reg_batch {
   b200reg_ctx* parent = nullptr;
   b200reg_icp_config cfg{};
@@ -1120,26 +1077,7 @@ struct b200reg_batch {
     b200reg_cloud* ref = nullptr;       // reusable device clouds of the host-buffer entry point
     b200reg_cloud* reading = nullptr;
     int32_t inFlight = -1;              // pair index
-    cudaEvent_t prepared = nullptr;     // group mode: the lane's preparation (uploads, index build, loop block) is enqueued up to here
   } lane[BATCH_MAX_LANES];
-  // Group mode (groupSize > 1): lanes [g * groupSize, (g + 1) * groupSize) form group g, whose registrations are advanced together by
-  // ONE while-graph (LoopGroup, common.cuh) on the group's stream: the lanes still prepare their pairs on their own streams (uploads,
-  // index builds and reading preparation of one group overlap the loop of another), the loop's kernels are launched once per group
-  // iteration.  Every member's result is that of the serial path, bit for bit (exact search and selection, same reduction grid).
-  int groupSize = 1;
-  int groups = 0;
-  struct Group {
-    cudaStream_t stream = nullptr;
-    cudaEvent_t done = nullptr;
-    cudaGraph_t graph = nullptr;
-    cudaGraphExec_t exec = nullptr;
-    LoopGroup* dG = nullptr;            // device descriptor (parent ctx allocation)
-    LoopGroup* hG = nullptr;            // pinned image
-    int members[LOOP_GROUP_MAX];        // lanes prepared for the launch being assembled
-    int filled = 0;
-    int nodes = 0;                      // kernels per iteration of the group body
-    int launchedMembers = 0, collected = 0, maxBodyRuns = 0;   // launch accounting of the launch in flight
-  } group[BATCH_MAX_LANES];
 };
 
 namespace {
@@ -1156,101 +1094,9 @@ int batchCollect(b200reg_batch* B, b200reg_batch::Lane& L, const float* T_init, 
   }
   B->parent->launches += L.ctx->launches;
   L.ctx->launches = 0;
-  if (L.icp->groupMember) {   // the group's kernels ran max-over-members iterations, once for all of them
-    b200reg_batch::Group& G = B->group[(int)(&L - B->lane) / B->groupSize];
-    if (L.icp->pendBodyRuns > G.maxBodyRuns) G.maxBodyRuns = L.icp->pendBodyRuns;
-    if (++G.collected == G.launchedMembers) {
-      B->parent->launches += (uint64_t)G.nodes * (uint64_t)G.maxBodyRuns;
-      G.collected = G.launchedMembers = G.maxBodyRuns = 0;
-    }
-    L.icp->groupMember = false;
-  }
   if (stats) stats[i] = st;
   if (status) status[i] = code;
   return code;
-}
-
-// Build the while-graph of one group once: fixed grids (the member index is blockIdx.y / blockIdx.x of the group kernels, members
-// beyond LoopGroup::count and members whose loop has ended return at once), arguments from the group's descriptor in HBM.
-int buildGroupGraph(b200reg_batch* B, b200reg_batch::Group& G) {
-  b200reg_ctx* ctx = B->parent;
-  const char* why = "";
-  cudaError_t code = cudaSuccess;
-  cudaGraph_t g = nullptr, body = nullptr, captured = nullptr;
-  cudaGraphExec_t exec = nullptr;
-  bool capturing = false;
-  const bool useTrim = B->cfg.trim_ratio > 0.f;
-  const int gs = B->groupSize;
-  const int knnBlocks = KNN1_LOOP_MINB * ctx->sm_count, redBlocks = 2 * ctx->sm_count;   // redBlocks: as buildLoopGraph (same partial sums)
-  int selBlocks = (2 * ctx->sm_count) / gs;
-  if (selBlocks < 4) selBlocks = 4;
-  {
-    cudaGraphConditionalHandle handle;
-    cudaGraphNodeParams np = {cudaGraphNodeTypeConditional};
-    cudaGraphNode_t node;
-    GRAPH_TRY(cudaGraphCreate(&g, 0));
-    GRAPH_TRY(cudaGraphConditionalHandleCreate(&handle, g, 1, cudaGraphCondAssignDefault));
-    np.type = cudaGraphNodeTypeConditional;
-    np.conditional.handle = handle;
-    np.conditional.type = cudaGraphCondTypeWhile;
-    np.conditional.size = 1;
-    GRAPH_TRY(cudaGraphAddNode(&node, g, nullptr, 0, &np));
-    body = np.conditional.phGraph_out[0];
-    GRAPH_TRY(cudaStreamBeginCaptureToGraph(G.stream, body, nullptr, nullptr, 0, cudaStreamCaptureModeThreadLocal));
-    capturing = true;
-    launchKnn1LoopGroup(G.dG, knnBlocks, G.stream);
-    G.nodes = 1;
-    if (useTrim) { selectFusedGroupKernel<<<dim3(selBlocks, gs), SELF_THREADS, 0, G.stream>>>(G.dG); ++G.nodes; }
-    reduceGroupKernel<<<dim3(redBlocks, gs), 256, 0, G.stream>>>(G.dG);
-    icpTailGroupKernel<<<gs, 32, 0, G.stream>>>(G.dG, handle);
-    G.nodes += 2;
-    GRAPH_TRY(cudaGetLastError());
-    capturing = false;
-    GRAPH_TRY(cudaStreamEndCapture(G.stream, &captured));
-    GRAPH_TRY(cudaGraphInstantiate(&exec, g, 0));
-    G.graph = g;
-    G.exec = exec;
-    return 0;
-  }
-fail:
-  if (capturing) cudaStreamEndCapture(G.stream, &captured);
-  if (g) cudaGraphDestroy(g);
-  cudaGetLastError();
-  setErr(ctx, B200REG_E_CUDA, "batch: group loop graph unavailable (%s: %s)", why, cudaGetErrorString(code));
-  return -1;
-}
-
-// launch the group's loop over the lanes prepared so far: the group stream waits for every member's preparation, the members'
-// streams wait for the loop and read their final states back
-int batchLaunchGroup(b200reg_batch* B, b200reg_batch::Group& G) {
-  b200reg_ctx* P = B->parent;
-  if (G.filled == 0) return B200REG_OK;
-  memset(G.hG, 0, sizeof(LoopGroup));
-  G.hG->count = G.filled;
-  for (int j = 0; j < G.filled; ++j) {
-    b200reg_batch::Lane& L = B->lane[G.members[j]];
-    LoopGroupSlot& sl = G.hG->slot[j];
-    sl.P = L.icp->dP;
-    sl.S = L.icp->dS;
-    sl.counters = (unsigned long long*)L.icp->dBlock;
-    sl.st = selState(L.ctx);
-    sl.result = resultPtr(L.ctx);
-    CUDA_TRY(P, cudaEventRecord(L.prepared, L.ctx->stream));
-    CUDA_TRY(P, cudaStreamWaitEvent(G.stream, L.prepared, 0));
-  }
-  CUDA_TRY(P, cudaMemcpyAsync(G.dG, G.hG, sizeof(LoopGroup), cudaMemcpyHostToDevice, G.stream));
-  CUDA_TRY(P, cudaGraphLaunch(G.exec, G.stream));
-  CUDA_TRY(P, cudaEventRecord(G.done, G.stream));
-  for (int j = 0; j < G.filled; ++j) {
-    b200reg_batch::Lane& L = B->lane[G.members[j]];
-    CUDA_TRY(P, cudaStreamWaitEvent(L.ctx->stream, G.done, 0));
-    TRY(icpReadback(L.icp));
-  }
-  G.launchedMembers = G.filled;
-  G.collected = 0;
-  G.maxBodyRuns = 0;
-  G.filled = 0;
-  return B200REG_OK;
 }
 
 void batchFail(b200reg_batch* B, b200reg_batch::Lane& L, int32_t i, int code, const float* T_init, float* T_out, b200reg_icp_stats* stats,
@@ -1283,28 +1129,9 @@ int batchRun(b200reg_batch* B, int32_t n, const float* T_init, float* T_out, b20
       L.icp->refPrepS = B->sharedPrepS;
       if (!B->shared) code = setErr(L.ctx, B200REG_E_NO_POINTS, "ICP: matcher not initialised (b200reg_batch_set_reference was not called)");
     }
-    const bool grouped = B->groupSize > 1;
-    if (code == B200REG_OK) code = icpEnqueue(L.icp, reading, T_init + 16 * (size_t)i, !grouped);
+    if (code == B200REG_OK) code = icpEnqueue(L.icp, reading, T_init + 16 * (size_t)i);
     if (code == B200REG_OK) L.inFlight = i;
     else batchFail(B, L, i, code, T_init, T_out, stats, status, &first);
-    if (grouped) {   // the lane joins the launch its group is assembling; the group's last lane (or the last pair) launches it
-      const int l = i % B->lanes;
-      b200reg_batch::Group& G = B->group[l / B->groupSize];
-      if (code == B200REG_OK) G.members[G.filled++] = l;
-      if (l % B->groupSize == B->groupSize - 1 || i == n - 1) {
-        const int lc = batchLaunchGroup(B, G);
-        if (lc != B200REG_OK) {   // nothing of this group is in flight: its members fail with the launch's error
-          for (int j = 0; j < G.filled; ++j) {
-            b200reg_batch::Lane& M = B->lane[G.members[j]];
-            M.icp->pending = false;
-            setErr(M.ctx, lc, "%s", P->err);
-            batchFail(B, M, M.inFlight, lc, T_init, T_out, stats, status, &first);
-            M.inFlight = -1;
-          }
-          G.filled = 0;
-        }
-      }
-    }
   }
   for (int l = 0; l < B->lanes; ++l) batchCollect(B, B->lane[l], T_init, T_out, stats, status, &first);
   return status ? B200REG_OK : first;   // with a status array the per-pair codes are the result
@@ -1315,10 +1142,6 @@ int batchRun(b200reg_batch* B, int32_t n, const float* T_init, float* T_out, b20
 extern "C" {
 
 int32_t b200reg_batch_create(b200reg_ctx* ctx, const b200reg_icp_config* cfg, int32_t lanes, b200reg_batch** out) {
-  return b200reg_batch_create_grouped(ctx, cfg, lanes, -1, out);
-}
-
-int32_t b200reg_batch_create_grouped(b200reg_ctx* ctx, const b200reg_icp_config* cfg, int32_t lanes, int32_t group_size, b200reg_batch** out) {
   if (!ctx || !cfg || !out) return setErr(ctx, B200REG_E_INVALID_PARAM, "batch_create: bad arguments");
   *out = nullptr;
   if (cfg->knn != 1) return setErr(ctx, B200REG_E_INVALID_PARAM, "batch_create: the batched lanes run the device-resident loop (knn = 1)");
@@ -1328,21 +1151,11 @@ int32_t b200reg_batch_create_grouped(b200reg_ctx* ctx, const b200reg_icp_config*
     if (lanes <= 0) lanes = 4;
   }
   if (lanes > BATCH_MAX_LANES) lanes = BATCH_MAX_LANES;
-  if (group_size < 0) {   // default: env B200REG_BATCH_GROUP, else BATCH_DEFAULT_GROUP
-    const char* env = getenv("B200REG_BATCH_GROUP");
-    group_size = env ? atoi(env) : BATCH_DEFAULT_GROUP;
-  }
-  if (group_size < 1) group_size = 1;
-  if (group_size > lanes) group_size = lanes;
-  if (group_size > LOOP_GROUP_MAX) group_size = LOOP_GROUP_MAX;
-  while (lanes % group_size) --group_size;   // whole groups only
   CUDA_TRY(ctx, cudaSetDevice(ctx->device));
   b200reg_batch* B = new b200reg_batch();
   B->parent = ctx;
   B->cfg = *cfg;
   B->lanes = lanes;
-  B->groupSize = group_size;
-  B->groups = lanes / group_size;
   int code = B200REG_OK;
   if (cudaEventCreateWithFlags(&B->parentReady, cudaEventDisableTiming) != cudaSuccess) code = setErr(ctx, B200REG_E_CUDA, "batch_create: event");
   for (int l = 0; l < lanes && code == B200REG_OK; ++l) {
@@ -1354,21 +1167,6 @@ int32_t b200reg_batch_create_grouped(b200reg_ctx* ctx, const b200reg_icp_config*
     if (code != B200REG_OK) { setErr(ctx, code, "batch_create: %s", L.ctx->err); break; }
     L.icp->graphState = (buildLoopGraph(L.icp) == 0) ? 1 : -1;
     if (L.icp->graphState != 1) code = setErr(ctx, B200REG_E_CUDA, "batch_create: the device-resident loop (conditional graph nodes) is unavailable");
-    if (code == B200REG_OK && L.ctx->select3) B->groupSize = 1;   // the A/B arm of the three-launch select has no group kernels
-    if (code == B200REG_OK && cudaEventCreateWithFlags(&L.prepared, cudaEventDisableTiming) != cudaSuccess) code = setErr(ctx, B200REG_E_CUDA, "batch_create: event");
-  }
-  if (B->groupSize == 1) B->groups = 0;
-  for (int g = 0; g < B->groups && code == B200REG_OK; ++g) {
-    b200reg_batch::Group& G = B->group[g];
-    if (cudaStreamCreateWithFlags(&G.stream, cudaStreamNonBlocking) != cudaSuccess ||
-        cudaEventCreateWithFlags(&G.done, cudaEventDisableTiming) != cudaSuccess ||
-        cudaMallocHost((void**)&G.hG, sizeof(LoopGroup)) != cudaSuccess || devAlloc(ctx, &G.dG, sizeof(LoopGroup)) != cudaSuccess) {
-      code = setErr(ctx, B200REG_E_CUDA, "batch_create: group resources");
-      break;
-    }
-    if (cudaMemsetAsync(G.dG, 0, sizeof(LoopGroup), ctx->stream) != cudaSuccess || cudaStreamSynchronize(ctx->stream) != cudaSuccess ||
-        buildGroupGraph(B, G) != 0)
-      code = B200REG_E_CUDA;
   }
   if (code != B200REG_OK) { b200reg_batch_destroy(B); return code; }
   *out = B;
@@ -1385,18 +1183,7 @@ void b200reg_batch_destroy(b200reg_batch* B) {
     if (L.icp) { L.icp->pending = false; b200reg_icp_destroy(L.icp); }   // a shared index is not the lane's to free
     if (L.ref) b200reg_cloud_free(L.ctx, L.ref);
     if (L.reading) b200reg_cloud_free(L.ctx, L.reading);
-    if (L.prepared) cudaEventDestroy(L.prepared);
     b200reg_ctx_destroy(L.ctx);
-  }
-  for (int g = 0; g < BATCH_MAX_LANES; ++g) {
-    b200reg_batch::Group& G = B->group[g];
-    if (G.stream) cudaStreamSynchronize(G.stream);
-    if (G.exec) cudaGraphExecDestroy(G.exec);
-    if (G.graph) cudaGraphDestroy(G.graph);
-    if (G.dG) devFree(B->parent, G.dG);
-    if (G.hG) cudaFreeHost(G.hG);
-    if (G.done) cudaEventDestroy(G.done);
-    if (G.stream) cudaStreamDestroy(G.stream);
   }
   if (B->shared) b200reg_index_free(B->parent, B->shared);
   if (B->parentReady) cudaEventDestroy(B->parentReady);
@@ -1404,7 +1191,6 @@ void b200reg_batch_destroy(b200reg_batch* B) {
 }
 
 int32_t b200reg_batch_lanes(const b200reg_batch* B) { return B ? B->lanes : 0; }
-int32_t b200reg_batch_group_size(const b200reg_batch* B) { return B ? B->groupSize : 0; }
 
 // ICP::initReference once for the whole batch: the index is built on the parent stream and every lane registers its readings
 // against it (many scans / many initial guesses against one map: re-localisation, multi-sequence mapping).

@@ -156,7 +156,7 @@ __device__ __forceinline__ void pickBin2(unsigned c0, unsigned c1, unsigned rank
   __syncthreads();
 }
 
-__device__ __forceinline__ void selectFusedBody(const IcpDevParams* __restrict__ DP, SelState* st) {
+__global__ void __launch_bounds__(SELF_THREADS, 1) selectFusedKernel(const IcpDevParams* __restrict__ DP, SelState* st) {
   __shared__ unsigned hist[2048];
   __shared__ unsigned warpSums[40];
   __shared__ unsigned bcast[2];
@@ -235,16 +235,6 @@ __device__ __forceinline__ void selectFusedBody(const IcpDevParams* __restrict__
   g1[2 * tid] = 0; g1[2 * tid + 1] = 0;
 }
 
-__global__ void __launch_bounds__(SELF_THREADS, 1) selectFusedKernel(const IcpDevParams* __restrict__ DP, SelState* st) { selectFusedBody(DP, st); }
-
-// the same for every member of a group that still iterates: member = blockIdx.y, gridDim.x blocks each (tau does not depend on the grid)
-__global__ void __launch_bounds__(SELF_THREADS, 1) selectFusedGroupKernel(const LoopGroup* __restrict__ G) {
-  if ((int)blockIdx.y >= G->count) return;
-  const LoopGroupSlot sl = G->slot[blockIdx.y];
-  if (sl.S->iterate == 0 || !sl.P->fhist0) return;
-  selectFusedBody(sl.P, sl.st);
-}
-
 struct ReduceParams {
   const float4* reading;       // pre-iteration reading (already in the refMean frame)
   const float4* readingNrm;    // nullable
@@ -320,17 +310,18 @@ __device__ __forceinline__ bool pairKept(const ReduceParams& P, int64_t o, float
 // un-centred; the matched-mean centring of PointToPlane.cpp:263-268 is applied algebraically afterwards.
 // Reduction: 36 fp64 moments per thread -> warp shuffle -> block tree -> per-block partial -> the last block adds the
 // partials in a fixed order (deterministic for a given grid).
-// arguments of the graph-driven loop: from the device-resident blocks, T_iter from the loop state
-__device__ __forceinline__ void reduceParamsFromLoop(ReduceParams& P, const IcpDevParams* __restrict__ DP, const IcpDevState* __restrict__ DS) {
-  P.reading = DP->reading; P.readingNrm = DP->readingNrm; P.refPts = DP->pts; P.refNrm = DP->nrm;
-  P.ids = DP->ids; P.d2 = DP->d2; P.pos = DP->pos; P.n = DP->n; P.k = 1; P.hasT = 1;
+__global__ void __launch_bounds__(256, 2) reduceKernel(ReduceParams P, const SelState* __restrict__ st, double* __restrict__ partials,
+                                                    unsigned* ticket, double* __restrict__ result, const IcpDevParams* __restrict__ DP,
+                                                    const IcpDevState* __restrict__ DS) {
+  if (DP) {   // graph-driven loop: arguments from the device-resident blocks, T_iter from the loop state
+    P.reading = DP->reading; P.readingNrm = DP->readingNrm; P.refPts = DP->pts; P.refNrm = DP->nrm;
+    P.ids = DP->ids; P.d2 = DP->d2; P.pos = DP->pos; P.n = DP->n; P.k = 1; P.hasT = 1;
 #pragma unroll
-  for (int j = 0; j < 12; ++j) P.T.m[j] = DS->T[j];
-  P.useTrim = DP->useTrim; P.useAngle = DP->useAngle; P.cosAngle = DP->cosAngle; P.force2D = DP->force2D; P.w = nullptr;
-}
-
-__device__ __forceinline__ void reduceBody(const ReduceParams& P, const SelState* __restrict__ st, double* __restrict__ partials,
-                                           unsigned* ticket, double* __restrict__ result) {
+    for (int j = 0; j < 12; ++j) P.T.m[j] = DS->T[j];
+    P.useTrim = DP->useTrim; P.useAngle = DP->useAngle; P.cosAngle = DP->cosAngle; P.force2D = DP->force2D; P.w = nullptr;
+    partials = DP->partials;
+    traceStamp(DP->trace, 5);
+  }
   double m[NUM_MOM];
 #pragma unroll
   for (int j = 0; j < NUM_MOM; ++j) m[j] = 0.0;
@@ -418,26 +409,4 @@ __device__ __forceinline__ void reduceBody(const ReduceParams& P, const SelState
     result[threadIdx.x] = v;
   }
   if (threadIdx.x == 0) *ticket = 0;
-}
-
-__global__ void __launch_bounds__(256, 2) reduceKernel(ReduceParams P, const SelState* __restrict__ st, double* __restrict__ partials,
-                                                    unsigned* ticket, double* __restrict__ result, const IcpDevParams* __restrict__ DP,
-                                                    const IcpDevState* __restrict__ DS) {
-  if (DP) {
-    reduceParamsFromLoop(P, DP, DS);
-    partials = DP->partials;
-    traceStamp(DP->trace, 5);
-  }
-  reduceBody(P, st, partials, ticket, result);
-}
-
-// every member of a group that still iterates: member = blockIdx.y with the grid.x of reduceKernel, so each member's partial sums —
-// and therefore its moments — are those of a registration on its own, bit for bit
-__global__ void __launch_bounds__(256, 2) reduceGroupKernel(const LoopGroup* __restrict__ G) {
-  if ((int)blockIdx.y >= G->count) return;
-  const LoopGroupSlot sl = G->slot[blockIdx.y];
-  if (sl.S->iterate == 0) return;
-  ReduceParams P;
-  reduceParamsFromLoop(P, sl.P, sl.S);
-  reduceBody(P, sl.st, sl.P->partials, &sl.st->ticket[3], sl.result);
 }

@@ -553,37 +553,6 @@ __global__ void __launch_bounds__(256, KNN1_LOOP_MINB) knn1LoopKernel(const IcpD
   flushVisits(visits, farQ, &sVisits, &sFarQ, &sTicket, visitCounter, sHist, gHist);
 }
 
-// The match of a GROUP of registrations (LoopGroup, common.cuh) in one launch: the resident blocks visit the members one after the
-// other — block b starts at member b mod count, so at any moment the blocks are spread over all members — and on each member pull
-// chunks from that member's work counter until it runs dry, then flush the member's visit counters and pass-0 histogram.  A block
-// that finds a member's counter exhausted moves on at the cost of one atomic per warp; members whose loop has ended are skipped.
-// Per member the result is what knn1LoopKernel writes (the search is exact and every query is written once).
-__global__ void __launch_bounds__(256, KNN1_LOOP_MINB) knn1GroupLoopKernel(const LoopGroup* __restrict__ G) {
-  __shared__ unsigned sVisits, sFarQ, sTicket;
-  __shared__ unsigned sHistBuf[2050];
-  const int count = G->count;
-  for (int j = 0; j < count; ++j) {
-    const int r = (int)((j + blockIdx.x) % (unsigned)count);
-    const IcpDevParams* __restrict__ P = G->slot[r].P;
-    const IcpDevState* __restrict__ S = G->slot[r].S;
-    if (S->iterate == 0) continue;   // uniform over the block
-    unsigned* gHist = P->fhist0;
-    unsigned* sHist = gHist ? sHistBuf : nullptr;
-    __syncthreads();                 // the previous member's flush has read the shared counters
-    if (threadIdx.x == 0) { sVisits = 0; sFarQ = 0; sTicket = 0; }
-    if (sHist) {
-      for (int b = threadIdx.x; b < 2048; b += blockDim.x) sHistBuf[b] = 0;
-      if (threadIdx.x == 0) { sHistBuf[2048] = 0xffffffffu; sHistBuf[2049] = 0; }
-    }
-    __syncthreads();
-    unsigned visits = 0, farQ = 0;
-    unsigned long long* counters = G->slot[r].counters;
-    if (S->lanes == 4) knn1LoopBody<4>(P, S, visits, farQ, sHist, counters + 2);
-    else knn1LoopBody<8>(P, S, visits, farQ, sHist, counters + 2);
-    flushVisits(visits, farQ, &sVisits, &sFarQ, &sTicket, counters, sHist, gHist);
-  }
-}
-
 // ---- 2 <= k <= 32 (SurfaceNormal's self-kNN, k-NN matchers): W lanes per query, W = 8 / 16 / 32 >= k ------------------
 // The running result is a sorted list DISTRIBUTED over the group: lane j holds the j-th best packed (d2, index) key and
 // its sorted position.  A contiguous point range is tested W candidates at a time (one coalesced float4 load per lane);
@@ -795,11 +764,6 @@ void launchKnn(b200reg_ctx* ctx, const b200reg_index* ix, const float4* q, int64
 // k = 1 match of the device-resident loop; `blocks` is fixed by the caller (graph capture)
 int launchKnn1Loop(b200reg_ctx* ctx, const IcpDevParams* P, const IcpDevState* S, unsigned long long* counters, int blocks) {
   knn1LoopKernel<<<blocks, 256, 0, ctx->stream>>>(P, S, counters);
-  return B200REG_OK;
-}
-
-int launchKnn1LoopGroup(const LoopGroup* G, int blocks, cudaStream_t stream) {
-  knn1GroupLoopKernel<<<blocks, 256, 0, stream>>>(G);
   return B200REG_OK;
 }
 

@@ -84,7 +84,7 @@ def run_config4(args, rank, local_rank, world):
     # pinned host staging (what a loop-closure module that owns its submaps would keep them in)
     pin = [(torch.from_numpy(r).pin_memory(), torch.from_numpy(rn).pin_memory(), torch.from_numpy(q).pin_memory()) for r, rn, q, _ in data]
     ctx = capi.Context(local_rank)
-    batch = capi.Batch(ctx, lanes=args.lanes, group=args.group, **C4_KW)
+    batch = capi.Batch(ctx, lanes=args.lanes, **C4_KW)
     refs_h = batch.host_clouds([(p[0].numpy(), p[1].numpy()) for p in pin])
     reads_h = batch.host_clouds([(p[2].numpy(), None) for p in pin])
     Ti = np.stack([np.eye(4, dtype=np.float32)] * len(mine))
