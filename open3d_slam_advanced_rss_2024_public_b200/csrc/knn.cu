@@ -562,14 +562,18 @@ __global__ void __launch_bounds__(256, KNN1_LOOP_MINB) knn1LoopKernel(const IcpD
 // row and shell pruned by its exact fp32 lower bound against the k-th distance (maxDist^2 while the list is not full).
 // queries == nullptr: the index's own points are the queries, taken in SORTED order (neighbouring groups share cells;
 // results are written at the original index) — the self-kNN of SurfaceNormal.cpp:170-188.
-template <int W>
+// TWO (W = 32 only, 32 < k <= 64): every lane holds TWO entries — entry l of the lower half (the 32 best) and entry 32 + l of the
+// upper half; an insertion into the lower half pushes its last entry into the head of the upper half.
+template <int W, bool TWO = false>
 struct KnnList {
   unsigned long long key, kth;   // this lane's entry; the group's k-th entry
   int pos;
   unsigned gmask;
-  int l, kLane;
+  int l, kLane;                  // kLane: lane holding the k-th entry (in the upper half when TWO)
+  unsigned long long keyB;       // upper half (TWO)
+  int posB;
   __device__ __forceinline__ float kthD() const { return __uint_as_float((unsigned)(kth >> 32)); }
-  __device__ __forceinline__ void insert(unsigned long long ck, int cp) {
+  __device__ __forceinline__ static void insertInto(unsigned long long& key, int& pos, unsigned long long ck, int cp, unsigned gmask, int l) {
     const unsigned long long upK = __shfl_up_sync(gmask, key, 1, W);
     const int upP = __shfl_up_sync(gmask, pos, 1, W);
     if (key > ck) {
@@ -577,12 +581,28 @@ struct KnnList {
       key = take ? ck : upK;
       pos = take ? cp : upP;
     }
-    kth = __shfl_sync(gmask, key, kLane, W);
+  }
+  __device__ __forceinline__ void insert(unsigned long long ck, int cp) {
+    if (!TWO) {
+      insertInto(key, pos, ck, cp, gmask, l);
+      kth = __shfl_sync(gmask, key, kLane, W);
+    } else {
+      const unsigned long long lastK = __shfl_sync(gmask, key, W - 1, W);
+      const int lastP = __shfl_sync(gmask, pos, W - 1, W);
+      if (ck < lastK) {   // uniform over the group: into the lower half, whose last entry moves to the head of the upper half
+        insertInto(key, pos, ck, cp, gmask, l);
+        const unsigned long long upK = __shfl_up_sync(gmask, keyB, 1, W);
+        const int upP = __shfl_up_sync(gmask, posB, 1, W);
+        keyB = (l == 0) ? lastK : upK;
+        posB = (l == 0) ? lastP : upP;
+      } else insertInto(keyB, posB, ck, cp, gmask, l);
+      kth = __shfl_sync(gmask, keyB, kLane, W);
+    }
   }
 };
 
-template <int W, bool SELFCHK>
-__device__ __forceinline__ void scanList(const float4* __restrict__ pts, uint32_t s, uint32_t e, const float3 q, int selfId, KnnList<W>& L,
+template <int W, bool SELFCHK, bool TWO>
+__device__ __forceinline__ void scanList(const float4* __restrict__ pts, uint32_t s, uint32_t e, const float3 q, int selfId, KnnList<W, TWO>& L,
                                          unsigned& visits) {
   if (s >= e) return;
   const int gbase = (threadIdx.x & 31) & (32 - W);
@@ -607,7 +627,7 @@ __device__ __forceinline__ void scanList(const float4* __restrict__ pts, uint32_
   }
 }
 
-template <int W, bool SELFCHK>
+template <int W, bool SELFCHK, bool TWO>
 __global__ void __launch_bounds__(256) knnListKernel(const float4* __restrict__ pts, const uint32_t* __restrict__ cellStart, const GridDesc* __restrict__ gp,
                                                      const float4* __restrict__ queries, int64_t n, int hasT, Rigid12 T, int k, float maxd2,
                                                      int* __restrict__ outIds, float* __restrict__ outD2, int* __restrict__ outPos,
@@ -632,7 +652,7 @@ __global__ void __launch_bounds__(256) knnListKernel(const float4* __restrict__ 
     const AxisGeom ay{q.y, g.oy, finite ? (int)floorf(fminf(fmaxf(__fmul_rn(__fsub_rn(q.y, g.oy), g.inv_cell), -lim), lim)) : 0};
     const AxisGeom az{q.z, g.oz, finite ? (int)floorf(fminf(fmaxf(__fmul_rn(__fsub_rn(q.z, g.oz), g.inv_cell), -lim), lim)) : 0};
     const unsigned long long initKey = packKey(maxd2, 0);   // an entry must beat (maxDist^2, 0): d2 < maxDist^2 strictly
-    KnnList<W> L{initKey, initKey, -1, gmask, l, k - 1};
+    KnnList<W, TWO> L{initKey, initKey, -1, gmask, l, TWO ? k - 1 - W : k - 1, initKey, -1};
 
     // ---- rings 0 and 1: nine (y,z) rows [cx-1, cx+1], directory entries fetched in one round
     uint32_t sR[NT], eR[NT];
@@ -650,7 +670,7 @@ __global__ void __launch_bounds__(256) knnListKernel(const float4* __restrict__ 
         lbR[t] = lb3(0.f, axisGap(ay, iy, g.cell, g.slack), axisGap(az, iz, g.cell, g.slack));
       }
     }
-    scanList<W, SELFCHK>(pts, __shfl_sync(gmask, sR[0], 4, W), __shfl_sync(gmask, eR[0], 4, W), q, selfId, L, visits);   // centre row first
+    scanList<W, SELFCHK, TWO>(pts, __shfl_sync(gmask, sR[0], 4, W), __shfl_sync(gmask, eR[0], 4, W), q, selfId, L, visits);   // centre row first
 #pragma unroll
     for (int t = 0; t < NT; ++t) {
       unsigned m = __ballot_sync(gmask, eR[t] > sR[t] && (l + t * W) != 4 && !(lbR[t] > L.kthD()));
@@ -660,7 +680,7 @@ __global__ void __launch_bounds__(256) knnListKernel(const float4* __restrict__ 
         m &= m - 1u;
         const uint32_t s = __shfl_sync(gmask, sR[t], b, W), e = __shfl_sync(gmask, eR[t], b, W);
         const float lb = __shfl_sync(gmask, lbR[t], b, W);
-        if (!(lb > L.kthD())) scanList<W, SELFCHK>(pts, s, e, q, selfId, L, visits);
+        if (!(lb > L.kthD())) scanList<W, SELFCHK, TWO>(pts, s, e, q, selfId, L, visits);
       }
     }
 
@@ -713,8 +733,8 @@ __global__ void __launch_bounds__(256) knnListKernel(const float4* __restrict__ 
           const uint32_t a0 = __shfl_sync(gmask, s0, b, W), b0 = __shfl_sync(gmask, e0, b, W);
           const uint32_t a1 = __shfl_sync(gmask, s1, b, W), b1 = __shfl_sync(gmask, e1, b, W);
           if (!(lb > L.kthD())) {
-            scanList<W, SELFCHK>(pts, a0, b0, q, selfId, L, visits);
-            scanList<W, SELFCHK>(pts, a1, b1, q, selfId, L, visits);
+            scanList<W, SELFCHK, TWO>(pts, a0, b0, q, selfId, L, visits);
+            scanList<W, SELFCHK, TWO>(pts, a1, b1, q, selfId, L, visits);
           }
         }
       }
@@ -728,19 +748,26 @@ __global__ void __launch_bounds__(256) knnListKernel(const float4* __restrict__ 
       outD2[o] = found ? __uint_as_float((unsigned)(L.key >> 32)) : CUDART_INF_F;
       outPos[o] = found ? L.pos : -1;
     }
+    if (TWO && W + l < k) {
+      const bool found = L.keyB != initKey;
+      const int64_t o = (int64_t)k * qi + W + l;
+      outIds[o] = found ? (int)(unsigned)L.keyB : -1;
+      outD2[o] = found ? __uint_as_float((unsigned)(L.keyB >> 32)) : CUDART_INF_F;
+      outPos[o] = found ? L.posB : -1;
+    }
   }
   for (int o = 16; o > 0; o >>= 1) visits += __shfl_xor_sync(0xffffffffu, visits, o);
   if ((threadIdx.x & 31) == 0 && visits) atomicAdd(visitCounter, (unsigned long long)visits);
 }
 
-template <int W>
+template <int W, bool TWO = false>
 void launchKnnList(b200reg_ctx* ctx, const b200reg_index* ix, const float4* q, int64_t n, int hasT, const Rigid12& T, int k, float maxd2,
                    int allowSelf, int* ids, float* d2, int* pos, unsigned long long* visits) {
   const int blocks = divUp(n * W, 256);
   if (allowSelf)
-    knnListKernel<W, false><<<blocks, 256, 0, ctx->stream>>>(ix->pts, ix->cellStart, &ix->dHdr->g, q, n, hasT, T, k, maxd2, ids, d2, pos, visits);
+    knnListKernel<W, false, TWO><<<blocks, 256, 0, ctx->stream>>>(ix->pts, ix->cellStart, &ix->dHdr->g, q, n, hasT, T, k, maxd2, ids, d2, pos, visits);
   else
-    knnListKernel<W, true><<<blocks, 256, 0, ctx->stream>>>(ix->pts, ix->cellStart, &ix->dHdr->g, q, n, hasT, T, k, maxd2, ids, d2, pos, visits);
+    knnListKernel<W, true, TWO><<<blocks, 256, 0, ctx->stream>>>(ix->pts, ix->cellStart, &ix->dHdr->g, q, n, hasT, T, k, maxd2, ids, d2, pos, visits);
 }
 
 template <int G>
@@ -780,7 +807,7 @@ int runKnn(b200reg_ctx* ctx, const b200reg_index* ix, const float4* queries, int
   TRY(ensureBuf(ctx, ctx->matchD2, sizeof(float) * (size_t)k * n));
   TRY(ensureBuf(ctx, ctx->matchPos, sizeof(int) * (size_t)k * n));
   if (n == 0) return B200REG_OK;
-  if (!queries && (k < 2 || k > 32 || ctx->knnLanes == 1 || n != ix->m)) return setErr(ctx, B200REG_E_INVALID_PARAM, "knn: self mode needs 2 <= k <= 32");
+  if (!queries && (k < 2 || ctx->knnLanes == 1 || n != ix->m)) return setErr(ctx, B200REG_E_INVALID_PARAM, "knn: self mode needs k >= 2 and the list kernel");
   Rigid12 R;
   memset(&R, 0, sizeof(R));
   if (T) memcpy(R.m, T, sizeof(R.m));
@@ -799,11 +826,12 @@ int runKnn(b200reg_ctx* ctx, const b200reg_index* ix, const float4* queries, int
   else if (k <= 8 && ctx->knnLanes != 1) launchKnnList<8>(ctx, ix, queries, n, hasT, R, k, maxd2, allowSelf, ids, d2, pos, visits);
   else if (k <= 16 && ctx->knnLanes != 1) launchKnnList<16>(ctx, ix, queries, n, hasT, R, k, maxd2, allowSelf, ids, d2, pos, visits);
   else if (k <= 32 && ctx->knnLanes != 1) launchKnnList<32>(ctx, ix, queries, n, hasT, R, k, maxd2, allowSelf, ids, d2, pos, visits);
+  else if (k > 32 && ctx->knnLanes != 1) launchKnnList<32, true>(ctx, ix, queries, n, hasT, R, k, maxd2, allowSelf, ids, d2, pos, visits);   // two entries per lane
   else if (k <= 4) launchKnn<4>(ctx, ix, queries, n, hasT, R, k, maxd2, allowSelf, ids, d2, pos, visits);
   else if (k <= 8) launchKnn<8>(ctx, ix, queries, n, hasT, R, k, maxd2, allowSelf, ids, d2, pos, visits);
   else if (k <= 16) launchKnn<16>(ctx, ix, queries, n, hasT, R, k, maxd2, allowSelf, ids, d2, pos, visits);
   else if (k <= 32) launchKnn<32>(ctx, ix, queries, n, hasT, R, k, maxd2, allowSelf, ids, d2, pos, visits);
-  else launchKnn<64>(ctx, ix, queries, n, hasT, R, k, maxd2, allowSelf, ids, d2, pos, visits);
+  else return setErr(ctx, B200REG_E_INVALID_PARAM, "knn: the one-thread-per-query kernel (B200REG_KNN_LANES=1) holds at most 32 neighbours");
   profEnd(ctx);
   LAUNCH_CHECK(ctx);
   return B200REG_OK;

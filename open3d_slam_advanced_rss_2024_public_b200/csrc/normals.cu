@@ -325,7 +325,7 @@ extern "C" int32_t b200reg_surface_normals_ex(b200reg_ctx* ctx, b200reg_cloud* i
   b200reg_index* ix = nullptr;
   TRY(buildIndex(ctx, inout, 0, 0.f, &ix));
   // the list kernel walks the cloud in the index's sorted order (null queries); the one-thread kernel takes it as it lies
-  const float4* qs = (ctx->knnLanes == 1 || knn > 32) ? inout->xyz : nullptr;
+  const float4* qs = (ctx->knnLanes == 1) ? inout->xyz : nullptr;
   int st = runKnn(ctx, ix, qs, n, nullptr, knn, opt->max_dist, 1, 0);
   if (st != B200REG_OK) { b200reg_index_free(ctx, ix); return st; }
   if (!inout->nrm) {

@@ -122,10 +122,11 @@ def test_knn_synthetic_scan_vs_map(ctx, oracle):
     assert np.array_equal(d2_g.view(np.uint32), d2_o.view(np.uint32))
 
 
-@pytest.mark.parametrize("k", [2, 8, 9, 16, 17, 32])
+@pytest.mark.parametrize("k", [2, 8, 9, 16, 17, 32, 33, 48, 64])
 def test_knn_list_kernel_equals_one_thread_kernel_and_oracle(ctx, oracle, k):
-    """The W-lanes-per-query list kernel (2 <= k <= 32) against the one-thread kernel (B200REG_KNN_LANES=1) and the oracle k-d tree on a raw
-    LiDAR scan (density varies by orders of magnitude: crowded cells and many-ring walks), queries outside the grid, k > reachable points."""
+    """The W-lanes-per-query list kernel (2 <= k <= 32; two entries per lane for 32 < k <= 64) against the one-thread kernel
+    (B200REG_KNN_LANES=1, k <= 32) and the oracle k-d tree on a raw LiDAR scan (density varies by orders of magnitude: crowded cells and
+    many-ring walks), queries outside the grid, k > reachable points."""
     import os
     from open3d_slam_advanced_rss_2024_public_b200 import capi
     c = scenes.config2(m=150_000, n_beams=32, n_az=512)
@@ -141,9 +142,13 @@ def test_knn_list_kernel_equals_one_thread_kernel_and_oracle(ctx, oracle, k):
     tree = oracle.KdTree(ref)
     for md, allow in ((np.inf, True), (0.8, True), (0.15, False)):
         ids_l, d2_l, vis = ctx.knn(ctx.build_index(ctx.upload(ref)), ctx.upload(q), k=k, max_dist=md, allow_self=allow)
-        ids_1, d2_1, _ = ctx1.knn(ctx1.build_index(ctx1.upload(ref)), ctx1.upload(q), k=k, max_dist=md, allow_self=allow)
-        assert np.array_equal(ids_l, ids_1), (k, md)
-        assert np.array_equal(d2_l.view(np.uint32), d2_1.view(np.uint32))
+        if k <= 32:
+            ids_1, d2_1, _ = ctx1.knn(ctx1.build_index(ctx1.upload(ref)), ctx1.upload(q), k=k, max_dist=md, allow_self=allow)
+            assert np.array_equal(ids_l, ids_1), (k, md)
+            assert np.array_equal(d2_l.view(np.uint32), d2_1.view(np.uint32))
+        else:
+            with pytest.raises(capi.InvalidParameter):
+                ctx1.knn(ctx1.build_index(ctx1.upload(ref)), ctx1.upload(q), k=k, max_dist=md, allow_self=allow)
         ids_o, d2_o, _ = tree.knn(q, k=k, max_dist=md, allow_self=allow, nthreads=8)
         assert np.array_equal(ids_l, ids_o), (k, md)
         assert np.array_equal(d2_l.view(np.uint32), d2_o.view(np.uint32))

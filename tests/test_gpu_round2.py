@@ -367,7 +367,7 @@ def _normals_cloud(seed, n=6000):
     return np.concatenate([x, iso, line, rng.uniform(0, 30, (40, 3)).astype(np.float32)])
 
 
-@pytest.mark.parametrize("knn,max_dist", [(10, 1.0), (20, np.inf), (5, 0.4)])
+@pytest.mark.parametrize("knn,max_dist", [(10, 1.0), (20, np.inf), (5, 0.4), (40, 2.0)])
 def test_surface_normals_all_descriptors_match_oracle(ctx, oracle, knn, max_dist):
     """keepEigenVectors (9, row-major), keepMatchedIds (knn, as floats), keepMeanDist besides the round-1 outputs: matched ids are
     bit-exact (the k-NN contract), everything else is within 1e-5 of the oracle's mixed-precision lane, degenerate points included."""
