@@ -54,6 +54,7 @@ int32_t b200reg_ctx_create(int32_t device, b200reg_ctx** out);
 void    b200reg_ctx_destroy(b200reg_ctx* ctx);
 const char* b200reg_last_error(const b200reg_ctx* ctx);
 int32_t b200reg_ctx_sync(b200reg_ctx* ctx);
+int32_t b200reg_ctx_device(const b200reg_ctx* ctx);   /* the CUDA device ordinal the context was created on */
 /* number of kernels this ctx has launched since creation (bench.py "gpu_launches") */
 uint64_t b200reg_ctx_launch_count(const b200reg_ctx* ctx);
 

@@ -128,6 +128,7 @@ SYMBOLS = {
     "b200reg_ctx_destroy": (None, [_VP]),
     "b200reg_last_error": (C.c_char_p, [_VP]),
     "b200reg_ctx_sync": (C.c_int32, [_VP]),
+    "b200reg_ctx_device": (C.c_int32, [_VP]),
     "b200reg_ctx_launch_count": (C.c_uint64, [_VP]),
     "b200reg_ctx_timer_start": (C.c_int32, [_VP]),
     "b200reg_ctx_timer_stop": (C.c_int32, [_VP, C.POINTER(C.c_float)]),

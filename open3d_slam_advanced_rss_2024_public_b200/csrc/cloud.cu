@@ -228,6 +228,8 @@ void b200reg_ctx_destroy(b200reg_ctx* ctx) {
   delete ctx;
 }
 
+int32_t b200reg_ctx_device(const b200reg_ctx* ctx) { return ctx ? ctx->device : -1; }
+
 const char* b200reg_last_error(const b200reg_ctx* ctx) { return ctx ? ctx->err : "null context"; }
 
 int32_t b200reg_ctx_sync(b200reg_ctx* ctx) {

@@ -67,16 +67,27 @@ Mapper::Mapper(b200reg_ctx* ctx, const MapperParams& params) : ctx_(ctx), params
   if (b200reg_icp_create(ctx_, &params_.icp, &icp_) != B200REG_OK) error_ = b200reg_last_error(ctx_);
 }
 
+void Mapper::freeSet(ScanSet& s) {
+  if (s.reading) b200reg_cloud_free(ctx_, s.reading);
+  b200reg_cloud64_free(ctx_, s.raw);
+  b200reg_cloud64_free(ctx_, s.cropped);
+  b200reg_cloud64_free(ctx_, s.merge);
+  b200reg_cloud64_free(ctx_, s.match);
+  s = ScanSet();
+}
+
 Mapper::~Mapper() {
-  if (reading_) b200reg_cloud_free(ctx_, reading_);
-  b200reg_cloud64_free(ctx_, raw_);
-  b200reg_cloud64_free(ctx_, next_[0]);
-  b200reg_cloud64_free(ctx_, next_[1]);
-  b200reg_cloud64_free(ctx_, cropped_);
-  b200reg_cloud64_free(ctx_, merge_);
-  b200reg_cloud64_free(ctx_, match_);
+  if (worker_.joinable()) {
+    { std::lock_guard<std::mutex> lock(mu_); stop_ = true; }
+    cv_.notify_all();
+    worker_.join();
+  }
+  if (workerCtx_) b200reg_ctx_sync(workerCtx_);
+  freeSet(sets_[0]);
+  freeSet(sets_[1]);
   if (icp_) b200reg_icp_destroy(icp_);
   if (map_) b200reg_map_destroy(ctx_, map_);
+  if (workerCtx_) b200reg_ctx_destroy(workerCtx_);
 }
 
 void Mapper::setMapToRangeSensor(const double T[16]) {
@@ -86,35 +97,89 @@ void Mapper::setMapToRangeSensor(const double T[16]) {
 
 // ScanToMapIcp::processForScanMatchingAndMerging (ScanToMapRegistration.cpp:36-69), every step on the device: the raw scan is
 // the only host -> device copy of a mapping step
-bool Mapper::process() {
+bool Mapper::process(b200reg_ctx* ctx, ScanSet& s) {
   StageClock clk;
-  auto fail = [&]() { error_ = b200reg_last_error(ctx_); return false; };
+  auto fail = [&]() { s.error = b200reg_last_error(ctx); return false; };
+  auto say = [&](const char* msg) { s.error = msg; return false; };
   // wide crop: mapBuilderCropper_->crop(in) — that cropper instance never gets a pose, i.e. it sits at the identity (:30-37)
   const b200reg_crop_spec wide = at(params_.mapBuilderCropper, nullptr);
-  if (b200reg_cloud64_crop(ctx_, &wide, raw_, &cropped_) != B200REG_OK) return fail();
-  clk.lap(&stats_.stageMs[MapperStepStats::kWideCrop]);
+  if (b200reg_cloud64_crop(ctx, &wide, s.raw, &s.cropped) != B200REG_OK) return fail();
+  clk.lap(&s.stageMs[0]);
   // o3d_slam::voxelize (helpers.cpp:108-115): no-op for voxel <= 0
-  if (params_.scanVoxelSize > 0.0 && b200reg_cloud64_size(cropped_) > 0) {
-    if (b200reg_cloud64_voxel_down_sample(ctx_, params_.scanVoxelSize, cropped_, &merge_) != B200REG_OK) return fail();
+  if (params_.scanVoxelSize > 0.0 && b200reg_cloud64_size(s.cropped) > 0) {
+    if (b200reg_cloud64_voxel_down_sample(ctx, params_.scanVoxelSize, s.cropped, &s.merge) != B200REG_OK) return fail();
   } else {
-    std::swap(cropped_, merge_);
-    if (!merge_) { error_ = "ScanToMapIcp::wideCropped cropped size is zero"; return false; }
+    std::swap(s.cropped, s.merge);
+    if (!s.merge) return say("ScanToMapIcp::wideCropped cropped size is zero");
   }
-  if (b200reg_cloud64_size(merge_) == 0) { error_ = "ScanToMapIcp::wideCropped cropped size is zero"; return false; }   // assert_gt (:66)
-  clk.lap(&stats_.stageMs[MapperStepStats::kVoxelize]);
+  if (b200reg_cloud64_size(s.merge) == 0) return say("ScanToMapIcp::wideCropped cropped size is zero");   // assert_gt (:66)
+  clk.lap(&s.stageMs[1]);
   // estimateNormalsOrCovariancesIfNeeded (CloudRegistration.cpp:62-75): only when the cloud has no normals;
   // EstimateNormals(Hybrid(radius, knn)) + NormalizeNormals + OrientNormalsTowardsCameraLocation(origin)
-  if (!b200reg_cloud64_has_normals(merge_)) {
+  if (!b200reg_cloud64_has_normals(s.merge)) {
     const double origin[3] = {0.0, 0.0, 0.0};
     int32_t degenerate = 0;
-    if (b200reg_cloud64_estimate_normals(ctx_, merge_, params_.normalsKnn, params_.normalsRadius, origin, &degenerate) != B200REG_OK) return fail();
+    if (b200reg_cloud64_estimate_normals(ctx, s.merge, params_.normalsKnn, params_.normalsRadius, origin, &degenerate) != B200REG_OK) return fail();
   }
-  clk.lap(&stats_.stageMs[MapperStepStats::kNormals]);
+  clk.lap(&s.stageMs[2]);
   // narrow crop at the identity pose (:62-63)
   const b200reg_crop_spec narrow = at(params_.scanMatcherCropper, nullptr);
-  if (b200reg_cloud64_crop(ctx_, &narrow, merge_, &match_) != B200REG_OK) return fail();
-  if (b200reg_cloud64_size(match_) == 0) { error_ = "ScanToMapIcp::narrow cropped size is zero"; return false; }   // assert_gt (:65)
-  clk.lap(&stats_.stageMs[MapperStepStats::kNarrowCrop]);
+  if (b200reg_cloud64_crop(ctx, &narrow, s.merge, &s.match) != B200REG_OK) return fail();
+  if (b200reg_cloud64_size(s.match) == 0) return say("ScanToMapIcp::narrow cropped size is zero");   // assert_gt (:65)
+  clk.lap(&s.stageMs[3]);
+  // open3dToPointmatcher (Mapper.cpp:307-309), device to device
+  if (b200reg_cloud64_to_f32(ctx, s.match, &s.reading) != B200REG_OK) return fail();
+  clk.lap(&s.stageMs[4]);
+  return true;
+}
+
+// The worker of prefetch(): takes the queued set, uploads the scan and runs the chain on its own context, marks the set ready.
+void Mapper::workerLoop() {
+  for (;;) {
+    int j;
+    {
+      std::unique_lock<std::mutex> lock(mu_);
+      cv_.wait(lock, [&] { return stop_ || job_ >= 0; });
+      if (stop_) return;
+      j = job_;
+      job_ = -1;
+    }
+    ScanSet& s = sets_[j];
+    StageClock clk;
+    for (double& v : s.stageMs) v = 0.0;
+    s.error.clear();
+    bool ok = b200reg_cloud64_upload(workerCtx_, s.srcPtr, nullptr, s.srcN, &s.raw) == B200REG_OK;
+    if (!ok) s.error = b200reg_last_error(workerCtx_);
+    clk.lap(&s.stageMs[0]);   // (the upload is booked with the first stage)
+    if (ok) ok = process(workerCtx_, s);
+    if (b200reg_ctx_sync(workerCtx_) != B200REG_OK && ok) { ok = false; s.error = b200reg_last_error(workerCtx_); }
+    {
+      std::lock_guard<std::mutex> lock(mu_);
+      s.ok = ok;
+      s.state = 2;
+    }
+    cv_.notify_all();
+  }
+}
+
+bool Mapper::prefetch(const double* xyz, int64_t n) {
+  if (!xyz || n < 0) { error_ = "prefetch: bad arguments"; return false; }
+  if (!workerCtx_) {
+    if (b200reg_ctx_create(b200reg_ctx_device(ctx_), &workerCtx_) != B200REG_OK) { error_ = "prefetch: cannot create the worker context"; workerCtx_ = nullptr; return false; }
+    worker_ = std::thread(&Mapper::workerLoop, this);
+  }
+  std::unique_lock<std::mutex> lock(mu_);
+  // a free set, else the older pending one (waiting for the worker to let go of it)
+  int j = (sets_[0].state == 0) ? 0 : (sets_[1].state == 0) ? 1 : (sets_[0].ticket < sets_[1].ticket ? 0 : 1);
+  cv_.wait(lock, [&] { return sets_[j].state != 1 && job_ < 0; });
+  ScanSet& s = sets_[j];
+  s.srcPtr = xyz;
+  s.srcN = n;
+  s.state = 1;
+  s.ticket = ++tickets_;
+  job_ = j;
+  lock.unlock();
+  cv_.notify_all();
   return true;
 }
 
@@ -126,13 +191,13 @@ bool Mapper::insert() {
   if (params_.carvingEnabled && b200reg_map_size(map_) > 0 && params_.carveSpaceEveryNscans > 0 &&
       nScansInsertedMap_ % params_.carveSpaceEveryNscans == 0) {
     const b200reg_crop_spec carveVol = at(params_.mapBuilderCropper, cropperPose_);
-    if (b200reg_map_carve_cloud64(ctx_, map_, raw_, mapToRangeSensor_, &carveVol, &params_.carving, &stats_.carvedPoints) != B200REG_OK) {
+    if (b200reg_map_carve_cloud64(ctx_, map_, sets_[cur_].raw, mapToRangeSensor_, &carveVol, &params_.carving, &stats_.carvedPoints) != B200REG_OK) {
       error_ = b200reg_last_error(ctx_);
       return false;
     }
   }
   const b200reg_crop_spec vol = at(params_.mapBuilderCropper, mapToRangeSensor_);
-  if (b200reg_map_insert_cloud64(ctx_, map_, merge_, mapToRangeSensor_, &vol) != B200REG_OK) {
+  if (b200reg_map_insert_cloud64(ctx_, map_, sets_[cur_].merge, mapToRangeSensor_, &vol) != B200REG_OK) {
     const std::string earlier = error_;   // a failed registration only keeps the estimate; its message must not be lost here
     error_ = b200reg_last_error(ctx_);
     if (!earlier.empty()) error_ = earlier + " | " + error_;
@@ -148,53 +213,81 @@ bool Mapper::addRangeMeasurement(const double* xyz, const double* normals, int64
   stats_ = MapperStepStats();
   error_.clear();
   StageClock clk;
-  int slot = -1;
-  for (int k = 0; k < 2 && !normals; ++k)
-    if (next_[k] && prefetchedPtr_[k] == xyz && prefetchedN_[k] == n) slot = k;
-  if (slot >= 0) {   // the scan prefetch() started uploading
-    prefetchedPtr_[slot] = nullptr;
-    prefetchedN_[slot] = -1;
-    std::swap(raw_, next_[slot]);
-    if (b200reg_cloud64_acquire(ctx_, raw_) != B200REG_OK) { error_ = b200reg_last_error(ctx_); return false; }
-  } else if (b200reg_cloud64_upload(ctx_, xyz, normals, n, &raw_) != B200REG_OK) {
-    error_ = b200reg_last_error(ctx_);
-    return false;
+  // ---- a scan prefetch() handed to the worker: wait for it, the map-independent half of the step is done
+  int hit = -1;
+  if (!normals && workerCtx_) {
+    std::unique_lock<std::mutex> lock(mu_);
+    for (int k = 0; k < 2; ++k)
+      if (sets_[k].state != 0 && sets_[k].srcPtr == xyz && sets_[k].srcN == n && (hit < 0 || sets_[k].ticket < sets_[hit].ticket)) hit = k;
+    if (hit >= 0) {
+      cv_.wait(lock, [&] { return sets_[hit].state == 2; });
+      sets_[hit].state = 0;
+      sets_[hit].srcPtr = nullptr;
+    }
   }
+  if (hit >= 0) {
+    cur_ = hit;
+    ScanSet& s = sets_[cur_];
+    clk.lap(&stats_.prefetchWaitMs);
+    stats_.prefetched = 1;
+    for (int i = 0; i < 5; ++i) stats_.stageMs[i] = s.stageMs[i];   // measured on the worker, concurrent with the previous step
+    if (!s.ok) { error_ = s.error; return false; }
+    return step(time, odom, true);
+  }
+  // ---- inline: a set no pending prefetch owns
+  {
+    std::unique_lock<std::mutex> lock(mu_);
+    cur_ = (sets_[0].state == 0) ? 0 : (sets_[1].state == 0) ? 1 : -1;
+    if (cur_ < 0) {   // both sets hold scans that were prefetched and never asked for: give up the older one
+      cur_ = sets_[0].ticket < sets_[1].ticket ? 0 : 1;
+      cv_.wait(lock, [&] { return sets_[cur_].state == 2; });
+      sets_[cur_].state = 0;
+      sets_[cur_].srcPtr = nullptr;
+    }
+  }
+  if (b200reg_cloud64_upload(ctx_, xyz, normals, n, &sets_[cur_].raw) != B200REG_OK) { error_ = b200reg_last_error(ctx_); return false; }
   clk.lap(&stats_.stageMs[MapperStepStats::kWideCrop]);   // (the upload is booked with the first stage)
-  return step(time, odom);
-}
-
-bool Mapper::prefetch(const double* xyz, int64_t n) {
-  int slot = prefetchSlot_;
-  if (prefetchedPtr_[slot] && !prefetchedPtr_[slot ^ 1]) slot ^= 1;   // keep a pending scan when the other slot is free
-  prefetchSlot_ = slot ^ 1;
-  prefetchedPtr_[slot] = nullptr;
-  prefetchedN_[slot] = -1;
-  if (b200reg_cloud64_prefetch(ctx_, xyz, nullptr, n, &next_[slot]) != B200REG_OK) { error_ = b200reg_last_error(ctx_); return false; }
-  prefetchedPtr_[slot] = xyz;
-  prefetchedN_[slot] = n;
-  return true;
+  return step(time, odom, false);
 }
 
 bool Mapper::addRangeMeasurementPointCloud2(const uint8_t* data, size_t bytes, const b200reg_pc2_layout& layout, double time, const double odom[16]) {
   stats_ = MapperStepStats();
   error_.clear();
   StageClock clk;
-  if (b200reg_cloud64_from_pointcloud2(ctx_, data, bytes, &layout, &raw_) != B200REG_OK) { error_ = b200reg_last_error(ctx_); return false; }
+  {
+    std::unique_lock<std::mutex> lock(mu_);
+    cur_ = (sets_[0].state == 0) ? 0 : (sets_[1].state == 0) ? 1 : -1;
+    if (cur_ < 0) {
+      cur_ = sets_[0].ticket < sets_[1].ticket ? 0 : 1;
+      cv_.wait(lock, [&] { return sets_[cur_].state == 2; });
+      sets_[cur_].state = 0;
+      sets_[cur_].srcPtr = nullptr;
+    }
+  }
+  if (b200reg_cloud64_from_pointcloud2(ctx_, data, bytes, &layout, &sets_[cur_].raw) != B200REG_OK) { error_ = b200reg_last_error(ctx_); return false; }
   clk.lap(&stats_.stageMs[MapperStepStats::kWideCrop]);
-  return step(time, odom);
+  return step(time, odom, false);
 }
 
-bool Mapper::step(double time, const double odom[16]) {
+bool Mapper::step(double time, const double odom[16], bool processed) {
+  ScanSet& cur = sets_[cur_];
+  auto processInline = [&]() {   // the scan-processing chain on this thread's context (no prefetch for this scan)
+    if (processed) return true;
+    for (double& v : cur.stageMs) v = 0.0;
+    const bool ok = process(ctx_, cur);
+    for (int i = 0; i < 5; ++i) stats_.stageMs[i] += cur.stageMs[i];
+    if (!ok) error_ = cur.error;
+    return ok;
+  };
   // ---- first scan (Mapper.cpp:179-193)
   if (b200reg_map_size(map_) == 0) {
     std::memcpy(mapToRangeSensorPrev_, mapToRangeSensor_, sizeof(mapToRangeSensor_));
-    if (!process()) return false;
+    if (!processInline()) return false;
     if (!insert()) return false;
     std::memcpy(odomPrev_, odom, sizeof(odomPrev_));   // (the reference reads its odometry buffer at the previous scan's stamp)
     haveOdomPrev_ = true;
     stats_.inserted = 1;
-    stats_.mergePoints = b200reg_cloud64_size(merge_);
+    stats_.mergePoints = b200reg_cloud64_size(cur.merge);
     stats_.mapPoints = b200reg_map_size(map_);
     return true;
   }
@@ -208,15 +301,10 @@ bool Mapper::step(double time, const double odom[16]) {
     mul(mapToRangeSensorPrev_, motion, estimate);
   }
   // ---- scan processing and the fp64 -> fp32 conversion (:307-309)
-  if (!process()) return false;
-  stats_.readingPoints = b200reg_cloud64_size(match_);
-  stats_.mergePoints = b200reg_cloud64_size(merge_);
+  if (!processInline()) return false;
+  stats_.readingPoints = b200reg_cloud64_size(cur.match);
+  stats_.mergePoints = b200reg_cloud64_size(cur.merge);
   StageClock clk;
-  if (b200reg_cloud64_to_f32(ctx_, match_, &reading_) != B200REG_OK) {   // open3dToPointmatcher, device to device
-    error_ = b200reg_last_error(ctx_);
-    return false;
-  }
-  clk.lap(&stats_.stageMs[MapperStepStats::kUpload]);
   float guess[16];
   for (int i = 0; i < 16; ++i) guess[i] = (float)estimate[i];
   // ---- map patch around the PREVIOUS pose (:328)
@@ -252,7 +340,7 @@ bool Mapper::step(double time, const double odom[16]) {
   if (!failed) {
     b200reg_icp_stats st;
     float T[16];
-    const int code = b200reg_icp_register(icp_, reading_, guess, T, &st);
+    const int code = b200reg_icp_register(icp_, cur.reading, guess, T, &st);
     stats_.icpStatus = code;
     stats_.iterations = st.iterations;
     if (code == B200REG_OK) std::memcpy(corrected, T, sizeof(corrected));

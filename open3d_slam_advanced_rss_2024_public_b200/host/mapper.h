@@ -16,8 +16,11 @@
 // odometry pose of each scan), RandomDownSample (ratio 1 only — the reference itself requires that for reproducibility,
 // ScanToMapRegistration.cpp:43), the initial-map mode, motion compensation.
 #pragma once
+#include <condition_variable>
 #include <cstdint>
+#include <mutex>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "../../include/b200reg.h"
@@ -53,6 +56,10 @@ struct MapperStepStats {
   // reading upload, map-patch crop, initReference, registration, insertion
   enum { kWideCrop, kVoxelize, kNormals, kNarrowCrop, kUpload, kPatch, kReference, kRegister, kInsert, kStages };
   double stageMs[kStages] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+  // prefetch(): the scan-processing stages ran on the worker, concurrently with the previous step (their times are the worker's);
+  // prefetchWaitMs is what this step still had to wait for them
+  double prefetchWaitMs = 0;
+  int32_t prefetched = 0;
 };
 
 class Mapper {
@@ -73,10 +80,13 @@ class Mapper {
   bool addRangeMeasurementPointCloud2(const uint8_t* data, size_t bytes, const b200reg_pc2_layout& layout, double time,
                                       const double odomToRangeSensor[16]);
 
-  // Start uploading a coming scan on the context's copy stream (what SlamWrapper's scan buffer gives the mapping worker the
-  // chance to do): called BEFORE addRangeMeasurement of the current scan, the copy overlaps that scan's kernels.  Two scans may
-  // be pending (the current one and the next); xyz must stay unchanged until the addRangeMeasurement(xyz, nullptr, n, ...) call
-  // that consumes it.  A measurement whose arguments match no pending prefetch is uploaded as usual.
+  // Process a coming scan AHEAD: a worker thread with a context (stream, scratch) of its own uploads it and runs the whole
+  // scan-processing chain (wide crop -> voxelize -> normals -> narrow crop -> fp32 reading, ScanToMapRegistration.cpp:36-69 — nothing
+  // in it depends on the map or the pose) while this thread registers and inserts the current scan; what SlamWrapper's scan buffer in
+  // front of the mapping worker gives room for.  Call it BEFORE addRangeMeasurement of the current scan.  Two scans may be pending
+  // (the current one and the next); xyz must stay unchanged until the addRangeMeasurement(xyz, nullptr, n, ...) call that consumes
+  // it, which waits for the worker and then only has the map-dependent half of the step left.  A measurement whose arguments match no
+  // pending scan is processed inline as before.  Results are identical either way.
   bool prefetch(const double* xyz, int64_t n);
 
   const double* mapToRangeSensor() const { return mapToRangeSensor_; }
@@ -85,21 +95,39 @@ class Mapper {
   const std::string& lastError() const { return error_; }
 
  private:
-  // ProcessedScans (ScanToMapRegistration.hpp): merge_ (wide) and match_ (narrow), device-resident fp64 clouds reused scan after scan
-  bool process();   // raw_ -> merge_ / match_
-  bool step(double time, const double odomToRangeSensor[16]);
+  // ProcessedScans (ScanToMapRegistration.hpp) of ONE scan on the device: merge (wide) and match (narrow) fp64 clouds + the fp32
+  // DataPoints mirror of match; two sets, reused scan after scan — one being consumed by the step, one being filled ahead
+  struct ScanSet {
+    b200reg_cloud64 *raw = nullptr, *cropped = nullptr, *merge = nullptr, *match = nullptr;
+    b200reg_cloud* reading = nullptr;   // open3dToPointmatcher(match), device to device
+    const double* srcPtr = nullptr;     // host scan a pending prefetch was given
+    int64_t srcN = -1;
+    int state = 0;                      // 0 free / consumed, 1 queued or being processed by the worker, 2 ready
+    uint64_t ticket = 0;                // order of the prefetch calls (the older pending scan is replaced first)
+    bool ok = false;
+    std::string error;
+    double stageMs[5] = {0, 0, 0, 0, 0};   // wide crop (+ upload), voxelize, normals, narrow crop, fp32 conversion
+  };
+  bool process(b200reg_ctx* ctx, ScanSet& s);   // s.raw -> s.merge / s.match / s.reading
+  bool step(double time, const double odomToRangeSensor[16], bool processed);
   bool insert();
+  void workerLoop();
+  void freeSet(ScanSet& s);
 
   b200reg_ctx* ctx_;
   MapperParams params_;
   b200reg_map* map_ = nullptr;
   b200reg_icp* icp_ = nullptr;
-  b200reg_cloud* reading_ = nullptr;   // fp32 DataPoints mirror of match_ (open3dToPointmatcher on the device)
-  b200reg_cloud64 *raw_ = nullptr, *cropped_ = nullptr, *merge_ = nullptr, *match_ = nullptr;
-  b200reg_cloud64* next_[2] = {nullptr, nullptr};   // prefetched scans (one is swapped with raw_ when it is consumed)
-  const double* prefetchedPtr_[2] = {nullptr, nullptr};
-  int64_t prefetchedN_[2] = {-1, -1};
-  int prefetchSlot_ = 0;
+  ScanSet sets_[2];
+  int cur_ = 0;                        // the set the current step works on
+  // the worker of prefetch(): created on first use
+  b200reg_ctx* workerCtx_ = nullptr;
+  std::thread worker_;
+  std::mutex mu_;
+  std::condition_variable cv_;
+  int job_ = -1;                       // set the worker has to process next
+  bool stop_ = false;
+  uint64_t tickets_ = 0;
   double mapToRangeSensor_[16], mapToRangeSensorPrev_[16], lastInsertion_[16], odomPrev_[16];
   double cropperPose_[16];             // mapBuilderCropper_'s pose: set AFTER each insertion (Submap.cpp:86), so carving sees the previous one
   int64_t nScansInsertedMap_ = 0;

@@ -205,6 +205,8 @@ typedef struct b200map_stats {
   int64_t reading_points, merge_points, patch_points, map_points;
   double stage_ms[9];   // MapperStepStats::stageMs
   int64_t carved_points;
+  double prefetch_wait_ms;
+  int64_t prefetched;
 } b200map_stats;
 
 void* b200map_create(b200reg_ctx* ctx, const b200map_params* p) {
@@ -236,6 +238,8 @@ int32_t b200map_add_range_measurement(void* m, const double* xyz, const double* 
     *stats = b200map_stats{s.iterations, s.icpStatus, s.referenceRefreshed, s.inserted, s.readingPoints, s.mergePoints, s.patchPoints, s.mapPoints, {}};
     for (int i = 0; i < b200::MapperStepStats::kStages; ++i) stats->stage_ms[i] = s.stageMs[i];
     stats->carved_points = s.carvedPoints;
+    stats->prefetch_wait_ms = s.prefetchWaitMs;
+    stats->prefetched = s.prefetched;
   }
   setMsg(err, err_cap, mp->lastError());
   return ok ? 1 : 0;
@@ -250,6 +254,8 @@ int32_t b200map_add_pointcloud2(void* m, const uint8_t* data, size_t bytes, cons
     *stats = b200map_stats{s.iterations, s.icpStatus, s.referenceRefreshed, s.inserted, s.readingPoints, s.mergePoints, s.patchPoints, s.mapPoints, {}};
     for (int i = 0; i < b200::MapperStepStats::kStages; ++i) stats->stage_ms[i] = s.stageMs[i];
     stats->carved_points = s.carvedPoints;
+    stats->prefetch_wait_ms = s.prefetchWaitMs;
+    stats->prefetched = s.prefetched;
   }
   setMsg(err, err_cap, mp->lastError());
   return ok ? 1 : 0;

@@ -17,7 +17,8 @@ class MapperParams(C.Structure):
 class MapperStats(C.Structure):
     _fields_ = [("iterations", C.c_int32), ("icp_status", C.c_int32), ("reference_refreshed", C.c_int32), ("inserted", C.c_int32),
                 ("reading_points", C.c_int64), ("merge_points", C.c_int64), ("patch_points", C.c_int64), ("map_points", C.c_int64),
-                ("stage_ms", C.c_double * 9), ("carved_points", C.c_int64)]
+                ("stage_ms", C.c_double * 9), ("carved_points", C.c_int64),
+                ("prefetch_wait_ms", C.c_double), ("prefetched", C.c_int64)]
 
     STAGES = ("wide_crop", "voxelize", "normals", "narrow_crop", "upload", "patch_crop", "init_reference", "register", "insert")
 
@@ -76,8 +77,9 @@ class Mapper:
         return bool(ok), pose.reshape(4, 4), st, err.value.decode("utf-8", "replace")
 
     def prefetch(self, xyz):
-        """Start uploading the NEXT scan (a C-contiguous float64 n x 3 array, ideally pinned) on the copy stream; the array must
-        stay alive and unchanged until the add_range_measurement(xyz, ...) call that passes the SAME array."""
+        """Hand a COMING scan (a C-contiguous float64 n x 3 array) to the Mapper's worker, which uploads it and runs the scan-processing
+        chain ahead while this thread registers the current scan; the array must stay alive and unchanged until the
+        add_range_measurement(xyz, ...) call that passes the SAME array."""
         if not (isinstance(xyz, np.ndarray) and xyz.dtype == np.float64 and xyz.flags.c_contiguous):
             raise ValueError("prefetch needs a C-contiguous float64 array (the same object is passed to add_range_measurement)")
         if not _lib().b200map_prefetch(self.h, xyz.ctypes.data_as(C.c_void_p), xyz.shape[0]):

@@ -258,7 +258,7 @@ def run_config3(args, rank, local_rank, world):
             ctx.sync()
             t0 = time.perf_counter()
             if prefetch and i + 1 < len(inputs):
-                m.prefetch(inputs[i + 1])                      # uploads on the copy stream while scan i is processed
+                m.prefetch(inputs[i + 1])                      # the Mapper's worker uploads and processes scan i + 1 while scan i is registered
             ok, pose, st, err = m.add_range_measurement(sc, 0.1 * i, od)
             ts.append(time.perf_counter() - t0)
             assert ok, err
@@ -274,7 +274,7 @@ def run_config3(args, rank, local_rank, world):
     time.sleep(0.3)
     ts, traj, sts, launches = one_pass(scans)                      # `value`: pageable numpy scans
     pinned = [torch.from_numpy(s).pin_memory().numpy() for s in scans]
-    ts_e, traj_e, _, _ = one_pass(pinned, prefetch=True)           # `e2e`: pinned scans, the next one uploading on the copy stream meanwhile
+    ts_e, traj_e, _, _ = one_pass(pinned, prefetch=True)           # `e2e`: pinned scans, the next one uploaded and processed ahead by the Mapper's worker
     clocks = sampler.stop()
     assert all(np.array_equal(a, b) for a, b in zip(traj, traj_e))
     err = [float(np.linalg.norm((np.linalg.inv(T) @ p)[:3, 3])) for T, p in zip(poses, traj)]
