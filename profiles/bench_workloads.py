@@ -450,10 +450,14 @@ def run_config5(args, rank, local_rank, world):
     assert sample_ok and self_ok
     big.free()
     # (iii) SurfaceNormal k = 20 once over the whole map (stress)
+    ctx.sync()
+    t0 = time.perf_counter()
+    info = ref.surface_normals(20, max_dist=1.0)        # first call: 12 GB of neighbour scratch (ids, d2, positions: 240 B/pt) come out of a growing pool
+    map_normals_cold_s = time.perf_counter() - t0
     ctx.flush_l2()
     ctx.sync()
     t0 = time.perf_counter()
-    info = ref.surface_normals(20, max_dist=1.0)
+    info = ref.surface_normals(20, max_dist=1.0)        # the timed one: the pool holds the blocks
     map_normals_s = time.perf_counter() - t0
     knn_t = float(np.mean(knn_ms))
     scan_ms = float(np.mean([p[1] + p[2] for p in res]))
@@ -466,7 +470,7 @@ def run_config5(args, rank, local_rank, world):
                        "map_upload_s": upload_s, "index_build_ms": build_warm, "index_build_ms_cold_first": build_ms[0], "index_build_frac": B.B_BUILD * M / (build_warm * 1e-3) / 1e9 / peak,
                        "cell_m": icp.index.cell, "normals_ms_per_scan": float(np.mean([p[1] for p in res])), "registration_ms_per_scan": float(np.mean([p[2] for p in res])),
                        "iterations": [p[3] for p in res], "worst_pose_error_m": max(p[4] for p in res), "worst_pose_error_deg": max(p[5] for p in res),
-                       "map_normals_k20_s": map_normals_s, "map_normals_frac": B.B_NORMALS * M / map_normals_s / 1e9 / peak, "map_normals_degenerate": info["degenerate"],
+                       "map_normals_k20_s": map_normals_s, "map_normals_k20_first_call_s": map_normals_cold_s, "map_normals_frac": B.B_NORMALS * M / map_normals_s / 1e9 / peak, "map_normals_degenerate": info["degenerate"],
                        "parity": {"sampled_queries_vs_brute_force_over_the_whole_map": sample_ok, "map_points_find_themselves": self_ok}, "gen_s": gen_s},
             "knn_queries_per_s": n / (knn_t * 1e-3), "knn_visits_per_query": visits / (n * n_scans),
             "roofline": {"bound": "hbm", "kernel": "knn1GroupKernel<8> (k = 1 match at the converged pose, stand-alone, L2 flushed)", "achieved": B.B_KNN1 * n / (knn_t * 1e-3) / 1e9,
