@@ -1074,9 +1074,15 @@ struct b200reg_batch {
   struct Lane {
     b200reg_ctx* ctx = nullptr;
     b200reg_icp* icp = nullptr;
-    b200reg_cloud* ref = nullptr;       // reusable device clouds of the host-buffer entry point
-    b200reg_cloud* reading = nullptr;
     int32_t inFlight = -1;              // pair index
+    // the host-buffer entry point stages a pair's clouds one lane-cycle AHEAD: pair i + lanes is uploaded on the lane's copy context
+    // (a stream and staging scratch of its own) into the other of two buffer sets while pair i iterates
+    b200reg_ctx* copyCtx = nullptr;
+    b200reg_cloud* ref[2] = {nullptr, nullptr};       // reusable device clouds, ping-pong
+    b200reg_cloud* reading[2] = {nullptr, nullptr};
+    cudaEvent_t staged[2] = {nullptr, nullptr};       // the uploads into set b are complete (copy stream)
+    int stageCode[2] = {0, 0};
+    int32_t stagedPair[2] = {-1, -1};
   } lane[BATCH_MAX_LANES];
 };
 
@@ -1108,16 +1114,21 @@ void batchFail(b200reg_batch* B, b200reg_batch::Lane& L, int32_t i, int code, co
 }
 
 // the loop of both batch entry points; `fetch` brings pair i's clouds to the lane (device pointers or uploads)
-template <class Fetch>
-int batchRun(b200reg_batch* B, int32_t n, const float* T_init, float* T_out, b200reg_icp_stats* stats, int32_t* status, Fetch fetch) {
+// `stage(L, j)` (host-buffer entry point; a no-op otherwise) starts the uploads of pair j on the lane's copy context: it is called one
+// lane-cycle ahead — pair i + lanes right after pair i - lanes was collected, i.e. when the buffer set it goes into is free — so the
+// copies of the next pair of a lane overlap the loop of the current one.
+template <class Stage, class Fetch>
+int batchRun(b200reg_batch* B, int32_t n, const float* T_init, float* T_out, b200reg_icp_stats* stats, int32_t* status, Stage stage, Fetch fetch) {
   b200reg_ctx* P = B->parent;
   CUDA_TRY(P, cudaSetDevice(P->device));
   CUDA_TRY(P, cudaEventRecord(B->parentReady, P->stream));
   for (int l = 0; l < B->lanes; ++l) CUDA_TRY(P, cudaStreamWaitEvent(B->lane[l].ctx->stream, B->parentReady, 0));
   int first = B200REG_OK;
+  for (int32_t i = 0; i < n && i < B->lanes; ++i) stage(B->lane[i], i);   // the first cycle's uploads go first, in pair order: lane 0 starts after ONE copy
   for (int32_t i = 0; i < n; ++i) {
     b200reg_batch::Lane& L = B->lane[i % B->lanes];
     batchCollect(B, L, T_init, T_out, stats, status, &first);
+    if (i + B->lanes < n) stage(L, i + B->lanes);
     const b200reg_cloud *ref = nullptr, *reading = nullptr;
     memset(&L.icp->pendStats, 0, sizeof(L.icp->pendStats));
     int code = fetch(L, i, &ref, &reading);
@@ -1167,6 +1178,9 @@ int32_t b200reg_batch_create(b200reg_ctx* ctx, const b200reg_icp_config* cfg, in
     if (code != B200REG_OK) { setErr(ctx, code, "batch_create: %s", L.ctx->err); break; }
     L.icp->graphState = (buildLoopGraph(L.icp) == 0) ? 1 : -1;
     if (L.icp->graphState != 1) code = setErr(ctx, B200REG_E_CUDA, "batch_create: the device-resident loop (conditional graph nodes) is unavailable");
+    if (code == B200REG_OK && (cudaEventCreateWithFlags(&L.staged[0], cudaEventDisableTiming) != cudaSuccess ||
+                               cudaEventCreateWithFlags(&L.staged[1], cudaEventDisableTiming) != cudaSuccess))
+      code = setErr(ctx, B200REG_E_CUDA, "batch_create: event");
   }
   if (code != B200REG_OK) { b200reg_batch_destroy(B); return code; }
   *out = B;
@@ -1181,8 +1195,13 @@ void b200reg_batch_destroy(b200reg_batch* B) {
     if (!L.ctx) continue;
     cudaStreamSynchronize(L.ctx->stream);
     if (L.icp) { L.icp->pending = false; b200reg_icp_destroy(L.icp); }   // a shared index is not the lane's to free
-    if (L.ref) b200reg_cloud_free(L.ctx, L.ref);
-    if (L.reading) b200reg_cloud_free(L.ctx, L.reading);
+    if (L.copyCtx) cudaStreamSynchronize(L.copyCtx->stream);
+    for (int b = 0; b < 2; ++b) {
+      if (L.ref[b]) b200reg_cloud_free(L.ctx, L.ref[b]);
+      if (L.reading[b]) b200reg_cloud_free(L.ctx, L.reading[b]);
+      if (L.staged[b]) cudaEventDestroy(L.staged[b]);
+    }
+    if (L.copyCtx) b200reg_ctx_destroy(L.copyCtx);
     b200reg_ctx_destroy(L.ctx);
   }
   if (B->shared) b200reg_index_free(B->parent, B->shared);
@@ -1215,7 +1234,8 @@ int32_t b200reg_batch_register(b200reg_batch* B, int32_t n, const b200reg_cloud*
                                const float* T_init, float* T_out, b200reg_icp_stats* stats, int32_t* status) {
   if (!B) return B200REG_E_INVALID_PARAM;
   if (n < 0 || (n > 0 && (!readings || !T_init || !T_out))) return setErr(B->parent, B200REG_E_INVALID_PARAM, "batch_register: bad arguments");
-  return batchRun(B, n, T_init, T_out, stats, status, [&](b200reg_batch::Lane& L, int32_t i, const b200reg_cloud** ref, const b200reg_cloud** reading) {
+  return batchRun(B, n, T_init, T_out, stats, status, [](b200reg_batch::Lane&, int32_t) {},
+                  [&](b200reg_batch::Lane& L, int32_t i, const b200reg_cloud** ref, const b200reg_cloud** reading) {
     if ((refs && !refs[i]) || !readings[i]) return setErr(L.ctx, B200REG_E_INVALID_PARAM, "batch_register: null cloud");
     *ref = refs ? refs[i] : nullptr;
     *reading = readings[i];
@@ -1227,23 +1247,42 @@ int32_t b200reg_batch_register_host(b200reg_batch* B, int32_t n, const b200reg_h
                                     const float* T_init, float* T_out, b200reg_icp_stats* stats, int32_t* status) {
   if (!B) return B200REG_E_INVALID_PARAM;
   if (n < 0 || (n > 0 && (!readings || !T_init || !T_out))) return setErr(B->parent, B200REG_E_INVALID_PARAM, "batch_register_host: bad arguments");
-  return batchRun(B, n, T_init, T_out, stats, status, [&](b200reg_batch::Lane& L, int32_t i, const b200reg_cloud** ref, const b200reg_cloud** reading) {
-    const b200reg_host_cloud& hq = readings[i];
-    // asynchronous uploads on the lane's stream (pinned host memory overlaps with the other lanes' kernels; pageable memory is
-    // staged by the runtime and only the staging copy blocks this thread)
+  const int lanes = B->lanes;
+  for (int l = 0; l < lanes && n > 0; ++l) {   // the copy contexts are created the first time host clouds come in
+    b200reg_batch::Lane& L = B->lane[l];
+    if (L.copyCtx) continue;
+    const int code = b200reg_ctx_create(B->parent->device, &L.copyCtx);
+    if (code != B200REG_OK) { L.copyCtx = nullptr; return setErr(B->parent, code, "batch_register_host: lane copy context"); }
+  }
+  // uploads of pair j on the lane's copy context into buffer set (j / lanes) & 1: asynchronous for pinned host memory (pageable memory is
+  // staged by the runtime and only the staging copy blocks this thread)
+  auto stage = [&](b200reg_batch::Lane& L, int32_t j) {
+    const int b = (j / lanes) & 1;
+    const b200reg_host_cloud& hq = readings[j];
     int code = B200REG_OK;
-    *ref = nullptr;
     if (refs) {
-      const b200reg_host_cloud& hr = refs[i];
-      code = L.ref ? b200reg_cloud_update_f32(L.ctx, L.ref, hr.feat, hr.feat_stride, hr.normals, hr.n, 1)
-                   : b200reg_cloud_upload_f32(L.ctx, hr.feat, hr.feat_stride, hr.normals, hr.n, &L.ref);
-      if (code != B200REG_OK) return code;
-      *ref = L.ref;
+      const b200reg_host_cloud& hr = refs[j];
+      code = L.ref[b] ? b200reg_cloud_update_f32(L.copyCtx, L.ref[b], hr.feat, hr.feat_stride, hr.normals, hr.n, 1)
+                      : b200reg_cloud_upload_f32(L.copyCtx, hr.feat, hr.feat_stride, hr.normals, hr.n, &L.ref[b]);
     }
-    code = L.reading ? b200reg_cloud_update_f32(L.ctx, L.reading, hq.feat, hq.feat_stride, hq.normals, hq.n, 1)
-                     : b200reg_cloud_upload_f32(L.ctx, hq.feat, hq.feat_stride, hq.normals, hq.n, &L.reading);
-    if (code != B200REG_OK) return code;
-    *reading = L.reading;
+    if (code == B200REG_OK)
+      code = L.reading[b] ? b200reg_cloud_update_f32(L.copyCtx, L.reading[b], hq.feat, hq.feat_stride, hq.normals, hq.n, 1)
+                          : b200reg_cloud_upload_f32(L.copyCtx, hq.feat, hq.feat_stride, hq.normals, hq.n, &L.reading[b]);
+    if (code != B200REG_OK) setErr(L.ctx, code, "%s", L.copyCtx->err);
+    else if (cudaEventRecord(L.staged[b], L.copyCtx->stream) != cudaSuccess) code = setErr(L.ctx, B200REG_E_CUDA, "batch_register_host: event record failed");
+    L.stageCode[b] = code;
+    L.stagedPair[b] = j;
+  };
+  return batchRun(B, n, T_init, T_out, stats, status, stage,
+                  [&](b200reg_batch::Lane& L, int32_t i, const b200reg_cloud** ref, const b200reg_cloud** reading) {
+    const int b = (i / lanes) & 1;
+    *ref = nullptr;
+    if (L.stagedPair[b] != i) return setErr(L.ctx, B200REG_E_INVALID_PARAM, "batch_register_host: pair %d was not staged", (int)i);
+    L.stagedPair[b] = -1;
+    if (L.stageCode[b] != B200REG_OK) return L.stageCode[b];
+    if (cudaStreamWaitEvent(L.ctx->stream, L.staged[b], 0) != cudaSuccess) return setErr(L.ctx, B200REG_E_CUDA, "batch_register_host: stream wait failed");
+    if (refs) *ref = L.ref[b];
+    *reading = L.reading[b];
     return (int)B200REG_OK;
   });
 }
