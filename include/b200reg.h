@@ -251,7 +251,7 @@ int32_t b200reg_icp_register(b200reg_icp* icp, const b200reg_cloud* reading, con
  *      runs on lane i mod lanes and up to `lanes` pairs are in flight at once — uploads, index build, reading preparation, the
  *      device-resident loop and the read-back of one pair are enqueued without a host wait, and the kernels of different lanes
  *      interleave on the device.  Every pair's result is bit-identical to b200reg_icp_set_reference + b200reg_icp_register.
- *      lanes <= 0: default (4, or env B200REG_BATCH_LANES).  The configuration must have knn == 1.
+ *      lanes <= 0: default (8, or env B200REG_BATCH_LANES).  The configuration must have knn == 1.
  *      stats / status: arrays of n, nullable.  With `status` the call returns OK and reports per-pair codes (a failed pair keeps
  *      T_out = T_init, what Mapper.cpp:420-428 falls back to); without it the first failure code is returned.
  *      One batch per (thread, device); sharding pairs over GPUs and gathering the results: b200reg_multi_* below. */

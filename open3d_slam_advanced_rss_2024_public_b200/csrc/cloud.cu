@@ -154,6 +154,7 @@ int32_t b200reg_ctx_create(int32_t device, b200reg_ctx** out) {
   ctx->debugSync = (dbg && dbg[0] == '1') ? 1 : 0;
   const char* seed = getenv("B200REG_KNN_SEED");
   ctx->knnSeed = (seed && seed[0] == '0') ? 0 : 1;
+  { int l2 = 0; if (cudaDeviceGetAttribute(&l2, cudaDevAttrL2CacheSize, device) == cudaSuccess && l2 > 0) ctx->l2Bytes = (size_t)l2; }
   const char* lanes = getenv("B200REG_KNN_LANES");
   if (lanes && (lanes[0] == '1' || lanes[0] == '4' || lanes[0] == '8')) ctx->knnLanes = lanes[0] - '0';
   *out = ctx;

@@ -40,6 +40,8 @@ struct b200reg_ctx {
   int select3 = 0;           // env B200REG_SELECT_3PASS=1: three-launch radix select inside the graph loop too (A/B)
   int hostLoop = 0;          // env B200REG_HOST_LOOP=1: keep the ICP iterate loop on the host (A/B against the graph loop)
   int debugSync = 0;         // env B200REG_DEBUG_SYNC=1: synchronise after every checked launch (fault localisation)
+  int loopGridPerSm = 0;     // working blocks per SM of the graph loop's match kernel when the reference exceeds the L2 (0: all; the lanes of a batch: 2)
+  size_t l2Bytes = 0;        // cudaDevAttrL2CacheSize
   int knnSeed = 1;           // env B200REG_KNN_SEED=0: do not seed the k = 1 match with the previous iteration's matches (A/B)
   int knnLanes = 0;          // lanes per query of the k = 1 match kernel: 0 automatic (8; the loop switches to 4 once far queries are rare),
                              // 8, 4, or 1 (the general kernel) forced by env B200REG_KNN_LANES for A/B runs
@@ -161,6 +163,7 @@ struct IcpDevParams {   // written by the host once per registration
   float minDiffRot, minDiffTrans, boundRot, boundTrans;
   int checkerOrder[3];
   int lanesForced;
+  int matchBlocks;        // blocks of the match kernel's resident grid that take work (the rest return at once)
   int seedOn;             // 0: chosen per iteration from the far-query count
   // fused trimmed-distance selection (nullable = filter off): the match kernel histograms the top 11 bits of d2 into fhist0
   unsigned* fhist0;            // 2048 bins, zero between iterations

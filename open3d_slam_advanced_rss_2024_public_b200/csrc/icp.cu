@@ -664,7 +664,10 @@ int buildLoopGraph(b200reg_icp* icp) {
   struct Restore { b200reg_ctx* c; int v; ~Restore() { c->debugSync = v; } } restore{ctx, debugSync};
   const bool useTrim = icp->cfg.trim_ratio > 0.f;
   SelState* st = selState(ctx);
-  const int knnBlocks = KNN1_LOOP_MINB * ctx->sm_count /* the resident grid of knn1LoopKernel: its warps pull work from a counter */, redBlocks = 2 * ctx->sm_count;
+  // the graph launches the match kernel on the full resident grid; IcpDevParams::matchBlocks (icpEnqueue) says how many of its blocks work
+  int perSm = KNN1_LOOP_MINB;
+  if (const char* e = getenv("B200REG_KNN_GRID_PER_SM")) { const int v = atoi(e); if (v >= 1 && v <= KNN1_LOOP_MINB) perSm = v; }   // A/B
+  const int knnBlocks = perSm * ctx->sm_count /* the resident grid of knn1LoopKernel: its warps pull work from a counter */, redBlocks = 2 * ctx->sm_count;
   if (ensureBuf(ctx, ctx->partials, sizeof(double) * NUM_MOM * (size_t)redBlocks) != B200REG_OK) return -1;
   {
     cudaGraphConditionalHandle handle;
@@ -898,6 +901,13 @@ int icpEnqueue(b200reg_icp* icp, const b200reg_cloud* reading, const float T_ini
     hP->fcnt = (unsigned*)((char*)ctx->dstate + DSTATE_FCNT_OFF);
     hP->cand = (unsigned*)ctx->cand.p;
   }
+  // Blocks of the resident match grid that take work.  A registration on its own uses them all.  The lanes of a batch (loopGridPerSm = 2)
+  // take HALF the machine each when the reference does not fit the L2 (32 B per point): those match kernels wait on DRAM, and two of them
+  // side by side — plus room for the other lanes' small kernels — beat one after the other (config #2, 5 M points: 3450 -> 3555
+  // registrations/s); an L2-resident reference is searched faster by the full grid (config #4, 200 k points: 1139 vs 1109 pairs/s).
+  int perSm = KNN1_LOOP_MINB;
+  if (ctx->loopGridPerSm > 0 && ctx->loopGridPerSm < perSm && (size_t)icp->index->m * 32 > ctx->l2Bytes) perSm = ctx->loopGridPerSm;
+  hP->matchBlocks = perSm * ctx->sm_count;
   hP->lanesForced = (ctx->knnLanes == 4 || ctx->knnLanes == 8) ? ctx->knnLanes : 0;
   hP->seedOn = ctx->knnSeed;
   hP->trace = ctx->trace ? (unsigned long long*)((char*)ctx->dstate + DSTATE_TRACE_OFF) : nullptr;
@@ -1064,6 +1074,8 @@ int32_t b200reg_icp_register(b200reg_icp* icp, const b200reg_cloud* reading, con
 // Results are those of the serial path, bit for bit: a lane runs exactly the code b200reg_icp_register runs.
 // =================================================================================================================
 #define BATCH_MAX_LANES 16
+#define BATCH_DEFAULT_LANES 8
+#define BATCH_LOOP_GRID_PER_SM 2   /* resident match-kernel blocks per SM of a lane (buildLoopGraph) */
 struct b200reg_batch {
   b200reg_ctx* parent = nullptr;
   b200reg_icp_config cfg{};
@@ -1159,7 +1171,7 @@ int32_t b200reg_batch_create(b200reg_ctx* ctx, const b200reg_icp_config* cfg, in
   if (lanes <= 0) {
     const char* env = getenv("B200REG_BATCH_LANES");
     lanes = env ? atoi(env) : 0;
-    if (lanes <= 0) lanes = 4;
+    if (lanes <= 0) lanes = BATCH_DEFAULT_LANES;
   }
   if (lanes > BATCH_MAX_LANES) lanes = BATCH_MAX_LANES;
   CUDA_TRY(ctx, cudaSetDevice(ctx->device));
@@ -1174,6 +1186,7 @@ int32_t b200reg_batch_create(b200reg_ctx* ctx, const b200reg_icp_config* cfg, in
     code = b200reg_ctx_create(ctx->device, &L.ctx);
     if (code != B200REG_OK) { setErr(ctx, code, "batch_create: lane context"); break; }
     L.ctx->profile = 0; L.ctx->hostLoop = 0;   // lanes always run the graph loop
+    L.ctx->loopGridPerSm = BATCH_LOOP_GRID_PER_SM;
     code = b200reg_icp_create(L.ctx, cfg, &L.icp);
     if (code != B200REG_OK) { setErr(ctx, code, "batch_create: %s", L.ctx->err); break; }
     L.icp->graphState = (buildLoopGraph(L.icp) == 0) ? 1 : -1;
@@ -1294,7 +1307,7 @@ int32_t b200reg_icp_register_batch(b200reg_ctx* ctx, const b200reg_icp_config* c
   if (!ctx || !cfg || n < 0 || (n > 0 && (!refs || !readings || !T_init || !T_out)))
     return setErr(ctx, B200REG_E_INVALID_PARAM, "icp_register_batch: bad arguments");
   b200reg_batch* B = nullptr;
-  TRY(b200reg_batch_create(ctx, cfg, n < 4 ? (n > 0 ? n : 1) : 0, &B));
+  TRY(b200reg_batch_create(ctx, cfg, n < BATCH_DEFAULT_LANES ? (n > 0 ? n : 1) : 0, &B));
   const int code = b200reg_batch_register(B, n, refs, readings, T_init, T_out, stats, status);
   b200reg_batch_destroy(B);
   return code;

@@ -536,6 +536,7 @@ __device__ __forceinline__ void knn1LoopBody(const IcpDevParams* __restrict__ P,
 // query while many queries need rings >= 2 (the first iterations of a badly aligned scan), 4 once they are rare.
 __global__ void __launch_bounds__(256, KNN1_LOOP_MINB) knn1LoopKernel(const IcpDevParams* __restrict__ P, const IcpDevState* __restrict__ S,
                                                          unsigned long long* __restrict__ visitCounter) {
+  if ((int)blockIdx.x >= P->matchBlocks) return;   // the registration asked for a part of the resident grid (icp.cu icpEnqueue)
   __shared__ unsigned sVisits, sFarQ, sTicket;
   __shared__ unsigned sHistBuf[2050];   // pass-0 histogram of the block's d2 + touched bin range
   unsigned* gHist = P->fhist0;

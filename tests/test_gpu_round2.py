@@ -33,7 +33,7 @@ def _pairs(oracle, n_pairs, seed0, m=40_000, beams=16, az=256):
     return out
 
 
-@pytest.mark.parametrize("lanes", [1, 2, 3, 4])
+@pytest.mark.parametrize("lanes", [1, 2, 3, 4, 8])
 def test_batch_lanes_bit_identical_to_serial(ctx, oracle, lanes):
     """b200reg_batch with R lanes in flight: every pair's transform, iteration count, tau and kept count are those of the
     stand-alone b200reg_icp_set_reference + b200reg_icp_register, bit for bit — for device clouds and for host clouds
