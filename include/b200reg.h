@@ -266,7 +266,9 @@ int32_t b200reg_batch_set_reference(b200reg_batch* batch, const b200reg_cloud* r
 int32_t b200reg_batch_register(b200reg_batch* batch, int32_t n, const b200reg_cloud* const* refs, const b200reg_cloud* const* readings,
                                const float* T_init, float* T_out, b200reg_icp_stats* stats, int32_t* status);
 /* HOST clouds (layout of b200reg_cloud_upload_f32; normals nullable for readings, required for references; refs == NULL as above):
- * the uploads are part of the pipeline.  The buffers must stay valid until the call returns; pinned memory lets the copies overlap the other lanes' kernels. */
+ * the uploads are part of the pipeline — every lane has a copy stream and two sets of device clouds, and the clouds of a lane's NEXT pair
+ * are uploaded while its current pair iterates.  The buffers must stay valid until the call returns; pinned memory makes the copies truly
+ * asynchronous (pageable memory is staged by the runtime and blocks the calling thread for the staging copy only). */
 typedef struct b200reg_host_cloud {
   const float* feat;
   int32_t feat_stride;
