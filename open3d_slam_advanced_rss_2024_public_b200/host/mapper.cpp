@@ -77,17 +77,16 @@ void Mapper::freeSet(ScanSet& s) {
 }
 
 Mapper::~Mapper() {
-  if (worker_.joinable()) {
+  if (workersUp_) {
     { std::lock_guard<std::mutex> lock(mu_); stop_ = true; }
     cv_.notify_all();
-    worker_.join();
+    for (std::thread& t : worker_) if (t.joinable()) t.join();
   }
-  if (workerCtx_) b200reg_ctx_sync(workerCtx_);
-  freeSet(sets_[0]);
-  freeSet(sets_[1]);
+  for (b200reg_ctx* c : workerCtx_) if (c) b200reg_ctx_sync(c);
+  for (ScanSet& s : sets_) freeSet(s);
   if (icp_) b200reg_icp_destroy(icp_);
   if (map_) b200reg_map_destroy(ctx_, map_);
-  if (workerCtx_) b200reg_ctx_destroy(workerCtx_);
+  for (b200reg_ctx* c : workerCtx_) if (c) b200reg_ctx_destroy(c);
 }
 
 void Mapper::setMapToRangeSensor(const double T[16]) {
@@ -133,26 +132,27 @@ bool Mapper::process(b200reg_ctx* ctx, ScanSet& s) {
   return true;
 }
 
-// The worker of prefetch(): takes the queued set, uploads the scan and runs the chain on its own context, marks the set ready.
-void Mapper::workerLoop() {
+// A worker of prefetch(): takes the next queued set, uploads the scan and runs the chain on its own context, marks the set ready.
+void Mapper::workerLoop(int w) {
+  b200reg_ctx* ctx = workerCtx_[w];
   for (;;) {
     int j;
     {
       std::unique_lock<std::mutex> lock(mu_);
-      cv_.wait(lock, [&] { return stop_ || job_ >= 0; });
+      cv_.wait(lock, [&] { return stop_ || !jobs_.empty(); });
       if (stop_) return;
-      j = job_;
-      job_ = -1;
+      j = jobs_.front();
+      jobs_.pop_front();
     }
     ScanSet& s = sets_[j];
     StageClock clk;
     for (double& v : s.stageMs) v = 0.0;
     s.error.clear();
-    bool ok = b200reg_cloud64_upload(workerCtx_, s.srcPtr, nullptr, s.srcN, &s.raw) == B200REG_OK;
-    if (!ok) s.error = b200reg_last_error(workerCtx_);
+    bool ok = b200reg_cloud64_upload(ctx, s.srcPtr, nullptr, s.srcN, &s.raw) == B200REG_OK;
+    if (!ok) s.error = b200reg_last_error(ctx);
     clk.lap(&s.stageMs[0]);   // (the upload is booked with the first stage)
-    if (ok) ok = process(workerCtx_, s);
-    if (b200reg_ctx_sync(workerCtx_) != B200REG_OK && ok) { ok = false; s.error = b200reg_last_error(workerCtx_); }
+    if (ok) ok = process(ctx, s);
+    if (b200reg_ctx_sync(ctx) != B200REG_OK && ok) { ok = false; s.error = b200reg_last_error(ctx); }
     {
       std::lock_guard<std::mutex> lock(mu_);
       s.ok = ok;
@@ -162,23 +162,41 @@ void Mapper::workerLoop() {
   }
 }
 
+// a set nobody is waiting for: a free one, else the oldest pending one once its worker has finished with it (mu_ held)
+int Mapper::takeSetLocked(std::unique_lock<std::mutex>& lock) {
+  for (int k = 0; k < kSets; ++k)
+    if (sets_[k].state == 0) return k;
+  int j = 0;
+  for (int k = 1; k < kSets; ++k)
+    if (sets_[k].ticket < sets_[j].ticket) j = k;
+  cv_.wait(lock, [&] { return sets_[j].state == 2; });
+  sets_[j].state = 0;
+  sets_[j].srcPtr = nullptr;
+  return j;
+}
+
 bool Mapper::prefetch(const double* xyz, int64_t n) {
   if (!xyz || n < 0) { error_ = "prefetch: bad arguments"; return false; }
-  if (!workerCtx_) {
-    if (b200reg_ctx_create(b200reg_ctx_device(ctx_), &workerCtx_) != B200REG_OK) { error_ = "prefetch: cannot create the worker context"; workerCtx_ = nullptr; return false; }
-    worker_ = std::thread(&Mapper::workerLoop, this);
+  if (!workersUp_) {
+    for (int w = 0; w < kWorkers; ++w)
+      if (b200reg_ctx_create(b200reg_ctx_device(ctx_), &workerCtx_[w]) != B200REG_OK) {
+        error_ = "prefetch: cannot create a worker context";
+        for (b200reg_ctx*& c : workerCtx_) { if (c) b200reg_ctx_destroy(c); c = nullptr; }
+        return false;
+      }
+    for (int w = 0; w < kWorkers; ++w) worker_[w] = std::thread(&Mapper::workerLoop, this, w);
+    workersUp_ = true;
   }
-  std::unique_lock<std::mutex> lock(mu_);
-  // a free set, else the older pending one (waiting for the worker to let go of it)
-  int j = (sets_[0].state == 0) ? 0 : (sets_[1].state == 0) ? 1 : (sets_[0].ticket < sets_[1].ticket ? 0 : 1);
-  cv_.wait(lock, [&] { return sets_[j].state != 1 && job_ < 0; });
-  ScanSet& s = sets_[j];
-  s.srcPtr = xyz;
-  s.srcN = n;
-  s.state = 1;
-  s.ticket = ++tickets_;
-  job_ = j;
-  lock.unlock();
+  {
+    std::unique_lock<std::mutex> lock(mu_);
+    const int j = takeSetLocked(lock);
+    ScanSet& s = sets_[j];
+    s.srcPtr = xyz;
+    s.srcN = n;
+    s.state = 1;
+    s.ticket = ++tickets_;
+    jobs_.push_back(j);
+  }
   cv_.notify_all();
   return true;
 }
@@ -215,9 +233,9 @@ bool Mapper::addRangeMeasurement(const double* xyz, const double* normals, int64
   StageClock clk;
   // ---- a scan prefetch() handed to the worker: wait for it, the map-independent half of the step is done
   int hit = -1;
-  if (!normals && workerCtx_) {
+  if (!normals && workersUp_) {
     std::unique_lock<std::mutex> lock(mu_);
-    for (int k = 0; k < 2; ++k)
+    for (int k = 0; k < kSets; ++k)
       if (sets_[k].state != 0 && sets_[k].srcPtr == xyz && sets_[k].srcN == n && (hit < 0 || sets_[k].ticket < sets_[hit].ticket)) hit = k;
     if (hit >= 0) {
       cv_.wait(lock, [&] { return sets_[hit].state == 2; });
@@ -230,20 +248,14 @@ bool Mapper::addRangeMeasurement(const double* xyz, const double* normals, int64
     ScanSet& s = sets_[cur_];
     clk.lap(&stats_.prefetchWaitMs);
     stats_.prefetched = 1;
-    for (int i = 0; i < 5; ++i) stats_.stageMs[i] = s.stageMs[i];   // measured on the worker, concurrent with the previous step
+    for (int i = 0; i < 5; ++i) stats_.stageMs[i] = s.stageMs[i];   // measured on the worker, concurrent with the previous steps
     if (!s.ok) { error_ = s.error; return false; }
     return step(time, odom, true);
   }
   // ---- inline: a set no pending prefetch owns
   {
     std::unique_lock<std::mutex> lock(mu_);
-    cur_ = (sets_[0].state == 0) ? 0 : (sets_[1].state == 0) ? 1 : -1;
-    if (cur_ < 0) {   // both sets hold scans that were prefetched and never asked for: give up the older one
-      cur_ = sets_[0].ticket < sets_[1].ticket ? 0 : 1;
-      cv_.wait(lock, [&] { return sets_[cur_].state == 2; });
-      sets_[cur_].state = 0;
-      sets_[cur_].srcPtr = nullptr;
-    }
+    cur_ = takeSetLocked(lock);
   }
   if (b200reg_cloud64_upload(ctx_, xyz, normals, n, &sets_[cur_].raw) != B200REG_OK) { error_ = b200reg_last_error(ctx_); return false; }
   clk.lap(&stats_.stageMs[MapperStepStats::kWideCrop]);   // (the upload is booked with the first stage)
@@ -256,13 +268,7 @@ bool Mapper::addRangeMeasurementPointCloud2(const uint8_t* data, size_t bytes, c
   StageClock clk;
   {
     std::unique_lock<std::mutex> lock(mu_);
-    cur_ = (sets_[0].state == 0) ? 0 : (sets_[1].state == 0) ? 1 : -1;
-    if (cur_ < 0) {
-      cur_ = sets_[0].ticket < sets_[1].ticket ? 0 : 1;
-      cv_.wait(lock, [&] { return sets_[cur_].state == 2; });
-      sets_[cur_].state = 0;
-      sets_[cur_].srcPtr = nullptr;
-    }
+    cur_ = takeSetLocked(lock);
   }
   if (b200reg_cloud64_from_pointcloud2(ctx_, data, bytes, &layout, &sets_[cur_].raw) != B200REG_OK) { error_ = b200reg_last_error(ctx_); return false; }
   clk.lap(&stats_.stageMs[MapperStepStats::kWideCrop]);

@@ -18,6 +18,7 @@
 #pragma once
 #include <condition_variable>
 #include <cstdint>
+#include <deque>
 #include <mutex>
 #include <string>
 #include <thread>
@@ -80,13 +81,13 @@ class Mapper {
   bool addRangeMeasurementPointCloud2(const uint8_t* data, size_t bytes, const b200reg_pc2_layout& layout, double time,
                                       const double odomToRangeSensor[16]);
 
-  // Process a coming scan AHEAD: a worker thread with a context (stream, scratch) of its own uploads it and runs the whole
+  // Process a coming scan AHEAD: worker threads with contexts (stream, scratch) of their own upload it and run the whole
   // scan-processing chain (wide crop -> voxelize -> normals -> narrow crop -> fp32 reading, ScanToMapRegistration.cpp:36-69 — nothing
   // in it depends on the map or the pose) while this thread registers and inserts the current scan; what SlamWrapper's scan buffer in
-  // front of the mapping worker gives room for.  Call it BEFORE addRangeMeasurement of the current scan.  Two scans may be pending
-  // (the current one and the next); xyz must stay unchanged until the addRangeMeasurement(xyz, nullptr, n, ...) call that consumes
-  // it, which waits for the worker and then only has the map-dependent half of the step left.  A measurement whose arguments match no
-  // pending scan is processed inline as before.  Results are identical either way.
+  // front of the mapping worker gives room for.  Call it BEFORE addRangeMeasurement of the current scan.  kWorkers scans are processed
+  // concurrently and kSets - 1 may be pending; xyz must stay unchanged until the addRangeMeasurement(xyz, nullptr, n, ...) call that
+  // consumes it, which waits for the worker and then only has the map-dependent half of the step left.  A measurement whose arguments
+  // match no pending scan is processed inline as before.  Results are identical either way.
   bool prefetch(const double* xyz, int64_t n);
 
   const double* mapToRangeSensor() const { return mapToRangeSensor_; }
@@ -96,7 +97,7 @@ class Mapper {
 
  private:
   // ProcessedScans (ScanToMapRegistration.hpp) of ONE scan on the device: merge (wide) and match (narrow) fp64 clouds + the fp32
-  // DataPoints mirror of match; two sets, reused scan after scan — one being consumed by the step, one being filled ahead
+  // DataPoints mirror of match; kSets of them, reused scan after scan — one being consumed by the step, the others being filled ahead
   struct ScanSet {
     b200reg_cloud64 *raw = nullptr, *cropped = nullptr, *merge = nullptr, *match = nullptr;
     b200reg_cloud* reading = nullptr;   // open3dToPointmatcher(match), device to device
@@ -111,21 +112,24 @@ class Mapper {
   bool process(b200reg_ctx* ctx, ScanSet& s);   // s.raw -> s.merge / s.match / s.reading
   bool step(double time, const double odomToRangeSensor[16], bool processed);
   bool insert();
-  void workerLoop();
+  void workerLoop(int w);
   void freeSet(ScanSet& s);
+  int takeSetLocked(std::unique_lock<std::mutex>& lock);   // a free set, else the oldest pending one once its worker is done with it
+  static constexpr int kSets = 3, kWorkers = 2;
 
   b200reg_ctx* ctx_;
   MapperParams params_;
   b200reg_map* map_ = nullptr;
   b200reg_icp* icp_ = nullptr;
-  ScanSet sets_[2];
+  ScanSet sets_[kSets];
   int cur_ = 0;                        // the set the current step works on
-  // the worker of prefetch(): created on first use
-  b200reg_ctx* workerCtx_ = nullptr;
-  std::thread worker_;
+  // the workers of prefetch(): created on first use
+  b200reg_ctx* workerCtx_[kWorkers] = {nullptr, nullptr};
+  std::thread worker_[kWorkers];
+  bool workersUp_ = false;
   std::mutex mu_;
   std::condition_variable cv_;
-  int job_ = -1;                       // set the worker has to process next
+  std::deque<int> jobs_;               // sets waiting for a worker, in prefetch order
   bool stop_ = false;
   uint64_t tickets_ = 0;
   double mapToRangeSensor_[16], mapToRangeSensorPrev_[16], lastInsertion_[16], odomPrev_[16];

@@ -257,8 +257,10 @@ def run_config3(args, rank, local_rank, world):
         for i, (sc, od) in enumerate(zip(inputs, odom)):
             ctx.sync()
             t0 = time.perf_counter()
-            if prefetch and i + 1 < len(inputs):
-                m.prefetch(inputs[i + 1])                      # the Mapper's worker uploads and processes scan i + 1 while scan i is registered
+            if prefetch and i == 0 and len(inputs) > 1:
+                m.prefetch(inputs[1])
+            if prefetch and i + 2 < len(inputs):
+                m.prefetch(inputs[i + 2])                      # the Mapper's two workers upload and process scans i + 1 and i + 2 while scan i is registered
             ok, pose, st, err = m.add_range_measurement(sc, 0.1 * i, od)
             ts.append(time.perf_counter() - t0)
             assert ok, err

@@ -320,9 +320,10 @@ def test_mapper_pointcloud2_entry_equals_array_entry(ctx):
 
 
 def test_mapper_prefetch_gives_the_same_trajectory(ctx):
-    """Mapper.prefetch (b200reg_cloud64_prefetch on the copy stream, two scans pending) changes WHEN a scan is uploaded, never what
-    the step computes: poses, counts and the final map equal the plain add_range_measurement run bit for bit — also when a
-    prefetched scan is never consumed, and when the scan sizes differ (storage of the slots is recycled and grown)."""
+    """Mapper.prefetch (worker threads with their own contexts run the scan-processing chain ahead; the sets of device clouds rotate)
+    changes WHEN a scan is uploaded and processed, never what the step computes: poses, counts and the final map equal the plain
+    add_range_measurement run bit for bit — also when prefetched scans are never consumed or are pushed out by later ones, when a
+    prefetched scan fails in the chain, and when the scan sizes differ (storage of the sets is recycled and grown)."""
     import torch
     from open3d_slam_advanced_rss_2024_public_b200 import capi
     from open3d_slam_advanced_rss_2024_public_b200.mapper import Mapper
@@ -338,12 +339,13 @@ def test_mapper_prefetch_gives_the_same_trajectory(ctx):
     ma, mb = mk(), mk()
     ma.set_pose(poses[0]); mb.set_pose(poses[0])
     mb.prefetch(pinned[0])
-    decoy = np.ascontiguousarray(scans[3][:1000])
+    decoys = [np.ascontiguousarray(scans[3][k:1000 + k]) for k in range(3)]
     for i, od in enumerate(odom):
         if i + 1 < len(pinned):
             mb.prefetch(pinned[i + 1])          # uploads while scan i is processed
-        if i == 4:
-            mb.prefetch(decoy)                  # a third prefetch replaces a pending one: that scan is then uploaded as usual
+        if i == 4:                              # more prefetches than sets: the oldest pending scans are replaced and then processed inline
+            for d in decoys:
+                mb.prefetch(d)
         ok_a, pose_a, st_a, err_a = ma.add_range_measurement(scans[i], 0.1 * i, od)
         ok_b, pose_b, st_b, err_b = mb.add_range_measurement(pinned[i], 0.1 * i, od)
         assert ok_a and ok_b, (err_a, err_b)
@@ -352,6 +354,16 @@ def test_mapper_prefetch_gives_the_same_trajectory(ctx):
     xa, na = ma.map_points()
     xb, nb = mb.map_points()
     assert np.array_equal(xa, xb) and np.array_equal(na, nb)
+    # a scan the wide crop empties (everything inside the minimum radius): the worker's failure is reported by the step that consumes it,
+    # with the message of the inline path, and the next scan goes through
+    near = np.ascontiguousarray(scans[0] * (0.5 / np.linalg.norm(scans[0], axis=1, keepdims=True)))
+    mb.prefetch(near)
+    ok_a, _, _, err_a = ma.add_range_measurement(near, 0.8, odom[-1])
+    ok_b, _, _, err_b = mb.add_range_measurement(near, 0.8, odom[-1])
+    assert not ok_a and not ok_b and err_a == err_b and "cropped size is zero" in err_b
+    ok_a, pose_a, _, _ = ma.add_range_measurement(scans[-1], 0.9, odom[-1])
+    ok_b, pose_b, _, _ = mb.add_range_measurement(pinned[-1], 0.9, odom[-1])
+    assert ok_a and ok_b and np.array_equal(pose_a, pose_b)
     ma.close(); mb.close()
     # the cloud-level entry points
     c = capi.Cloud64.prefetch(ctx, pinned[2])
