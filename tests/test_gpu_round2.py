@@ -457,3 +457,100 @@ def test_pointcloud2_reference_test_layouts_round_trip(ctx, oracle):
         if feat.shape[0] <= 10000:
             st, f4, n3, x64, n64 = oracle.pointcloud2(data, feat.shape[0], step, fields)
             assert np.array_equal(f4.view(np.uint32), feat.view(np.uint32)) and (nrm is None or np.array_equal(n3, nrm))
+
+
+def _c3_scan_job(job):
+    """(worker process) one 128x1024 ray-cast scan of BASELINE config #3's hall (profiles/bench_workloads.py uses the same scene and seeds)"""
+    i, T = job
+    scene = scenes.Scene(2001, size=(200.0, 60.0, 10.0), n_boxes=60, n_cyl=40)
+    return scenes.lidar_scan(scene, T, n_beams=128, n_az=1024, noise_sigma=0.01, seed=2002 + i).astype(np.float64)
+
+
+def test_config3_full_scan_size_follows_the_oracle_trajectory(ctx, oracle):
+    """BASELINE config #3 at its real scan size (128x1024 rays, crop 2-80 m, voxel 0.1, fp64 normals k = 20 / 1 m, ICP, map voxel 0.15): the C++
+    Mapper over the C ABI against the oracle's composition of the same steps, scan by scan, along the first 30 poses of the figure-eight —
+    iteration counts, poses within 1e-4 m / 1e-4 (chord), cloud sizes within 0.2 % (a pose that differs in the 7th digit moves a few of
+    ~10^5 points across a voxel face), and both within 2 cm of the ray-cast truth despite the drifting odometry."""
+    import multiprocessing as mp
+    from open3d_slam_advanced_rss_2024_public_b200 import capi
+    from open3d_slam_advanced_rss_2024_public_b200.mapper import Mapper
+    from test_gpu_mapper import OracleMapper
+    n_scans = 30
+    poses = []
+    for i in range(n_scans):
+        s = 0.2 * i
+        a = 2 * np.pi * s / 120.0
+        x, y = 40.0 * np.sin(a), 12.0 * np.sin(2 * a)
+        dx, dy = 40.0 * np.cos(a), 24.0 * np.cos(2 * a)
+        poses.append(scenes.rigid(scenes.rot_axis_angle(np.array([0, 0, 1.0]), np.arctan2(dy, dx)), np.array([x, y, 1.8])))
+    rng = np.random.default_rng(2003)
+    D = np.eye(4)
+    odom = []
+    for T in poses:
+        D = D @ scenes.rigid(scenes.rot_axis_angle(rng.normal(size=3), np.deg2rad(0.02) * rng.normal()), rng.normal(size=3) * 0.002)
+        odom.append(T @ D)
+    with mp.get_context("spawn").Pool(16) as pool:
+        scans = pool.map(_c3_scan_job, list(enumerate(poses)), chunksize=1)
+    icp_kw = dict(knn=1, max_dist=0.5, trim_ratio=0.9, max_angle=1.57, max_iter=15, min_diff_rot=1e-3, min_diff_trans=1e-2, smooth_length=3)
+    om = OracleMapper(oracle, dict(kind=capi.CROP_MINMAX_RADIUS, rmin=2.0, rmax=80.0), dict(kind=capi.CROP_MAX_RADIUS, rmax=80.0), icp_kw,
+                      scan_voxel=0.1, knn=20, radius=1.0, map_voxel=0.15, min_move=0.0, period=2.0)
+    gm = Mapper(ctx, capi.crop_spec(capi.CROP_MINMAX_RADIUS, np.zeros(3), rmin=2.0, rmax=80.0), capi.crop_spec(capi.CROP_MAX_RADIUS, np.zeros(3), rmax=80.0),
+                capi.icp_config(**icp_kw), scan_voxel_size=0.1, normals_knn=20, normals_radius=1.0, map_voxel_size=0.15, min_movement=0.0,
+                reference_period=2.0)
+    om.pose = poses[0].copy()
+    gm.set_pose(poses[0])
+    near = lambda a, b: abs(a - b) <= max(2, 0.002 * b)  # noqa: E731
+    err_g = []
+    for i, (T, od, scan) in enumerate(zip(poses, odom, scans)):
+        if i + 1 < n_scans:
+            gm.prefetch(scans[i + 1])                    # the worker path at full size as well
+        ok_o, so = om.add(scan, 0.1 * i, od)
+        ok_g, pose_g, sg, err = gm.add_range_measurement(scan, 0.1 * i, od)
+        assert ok_o and ok_g, (i, err)
+        assert near(sg.merge_points, so["merge"]) and near(sg.map_points, so["map"]), (i, sg.merge_points, sg.map_points, so)
+        if i > 0:
+            assert near(sg.reading_points, so["reading"]) and near(sg.patch_points, so["patch"])
+            assert sg.icp_status == so["code"] == 0 and sg.reference_refreshed == so["refreshed"]
+            assert abs(sg.iterations - so["iterations"]) <= 1, (i, sg.iterations, so["iterations"])
+        assert np.abs(pose_g[:3, 3] - om.pose[:3, 3]).max() < 1e-4, (i, pose_g, om.pose)
+        assert np.linalg.norm(pose_g[:3, :3] - om.pose[:3, :3]) / np.sqrt(2) < 1e-4
+        err_g.append(float(np.linalg.norm((np.linalg.inv(T) @ pose_g)[:3, 3])))
+    assert max(err_g) < 0.02, err_g
+    assert sg.map_points > 150_000 and sg.reading_points > 60_000
+    gm.close()
+
+
+def test_config4_full_size_pairs_match_oracle(ctx, oracle):
+    """BASELINE config #4 at its real pair size (200 000 x 200 000 points, SURVEY 8d row 4: scenes 3000 + i, |t| <= 0.5 m, angle <= 5 deg,
+    T_init = I, maxDist 1, TrimmedDist 0.8, Counter 40): four pairs through b200reg_batch_register_host (uploads staged ahead on the copy
+    streams) against the oracle — iteration counts, kept pairs, tau bits, transforms within 1e-5 m / 1e-5 rad — and against the generating
+    transform."""
+    from open3d_slam_advanced_rss_2024_public_b200 import capi
+    kw = dict(knn=1, max_dist=1.0, trim_ratio=0.8, max_iter=40, min_diff_rot=1e-3, min_diff_trans=1e-2, smooth_length=3)
+    N = 200_000
+    pairs = []
+    for i in (0, 1, 2, 7):
+        rng = np.random.default_rng(3500 + i)
+        sc = scenes.Scene(3000 + i, size=(40.0, 40.0, 8.0), n_boxes=12, n_cyl=8)
+        a, an = sc.sample_surface(N, 3100 + 2 * i)
+        b, _ = sc.sample_surface(N, 3101 + 2 * i)
+        t = rng.normal(size=3)
+        t *= rng.uniform(0, 0.5) / np.linalg.norm(t)
+        T_true = scenes.rigid(scenes.rot_axis_angle(rng.normal(size=3), np.deg2rad(rng.uniform(0, 5.0))), t)
+        b_local = (b - T_true[:3, 3]) @ T_true[:3, :3]
+        pairs.append((oracle.feat4(a), np.ascontiguousarray(an, dtype=np.float32), oracle.feat4(b_local), T_true))
+    batch = capi.Batch(ctx, lanes=2, **kw)
+    Ti = np.stack([np.eye(4, dtype=np.float32)] * len(pairs))
+    T, stats, status = batch.register_host(batch.host_clouds([(p[0], p[1]) for p in pairs]), batch.host_clouds([(p[2], None) for p in pairs]), Ti)
+    assert not status.any()
+    cfg = oracle.icp_config(precision=oracle.ORC_MIXED, nthreads=16, **kw)
+    for j, (ref, rn, q, T_true) in enumerate(pairs):
+        code, T_o, st_o = oracle.icp(cfg, ref, rn, q, None, Ti[j])
+        assert code == 0
+        assert stats[j].iterations == st_o.iterations, (j, stats[j].iterations, st_o.iterations)
+        assert stats[j].kept_last == st_o.kept_last
+        assert np.float32(stats[j].last_tau).tobytes() == np.float32(st_o.last_tau).tobytes()
+        assert_same_T(T[j], T_o)
+        E = np.linalg.inv(T_true) @ T[j].astype(np.float64)
+        assert np.abs(E[:3, 3]).max() < 2e-3 and rot_angle(np.eye(3), E[:3, :3]) < 2e-3, (j, E)
+    batch.close()
