@@ -284,7 +284,9 @@ int32_t b200reg_icp_register_batch(b200reg_ctx* ctx, const b200reg_icp_config* c
 /* ---- the batch sharded over the GPUs of one box from ONE process: pair i -> devices[i mod G]; every device runs its pairs
  *      through its own b200reg_batch, driven by its own host thread; then ONE ncclAllGather of 96-byte records (4x4, status,
  *      iterations, kept, tau, owner) over NVLink leaves every device with every pair's result, and T_out / status are read from
- *      the gathered block.  NCCL is resolved at run time (dlopen of libnccl.so.2) and used for this gather only.
+ *      the gathered block.  NCCL is resolved at run time and used for this gather only: the path in env B200REG_NCCL_LIB, else an NCCL
+ *      the process already holds, else the system's libnccl.so.2.  (A process keeps ONE libnccl.so.2: an application that loads a newer
+ *      NCCL under that soname later — `import torch` with its bundled copy — must load it before the first b200reg_multi_create.)
  *      devices == NULL / n_devices == 0: every visible GPU.  On failure *out is still returned so that b200reg_multi_last_error can be
  *      read; destroy it.  gather_ms (nullable): CUDA-event time of the all-gather on device 0. */
 typedef struct b200reg_multi b200reg_multi;

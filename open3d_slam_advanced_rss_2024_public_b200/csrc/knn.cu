@@ -602,6 +602,32 @@ struct KnnList {
   }
 };
 
+// compare-exchange of a bitonic network over the W lanes of a group: lane l and lane l ^ j; the lower lane keeps the minimum when `up`
+template <int W>
+__device__ __forceinline__ void bitonicStep(unsigned long long& k, int& p, int j, bool up, unsigned gmask, int l) {
+  const unsigned long long ok = __shfl_xor_sync(gmask, k, j, W);
+  const int op = __shfl_xor_sync(gmask, p, j, W);
+  const bool takeMin = ((l & j) == 0) == up;
+  if (takeMin ? (ok < k) : (ok > k)) { k = ok; p = op; }
+}
+// A chunk with many accepted candidates is not inserted one by one (a shuffle-up of the whole list per candidate): the chunk is sorted by
+// a bitonic network, reversed against the list — the W smallest of the union are then min(list[l], chunk[W - 1 - l]), a bitonic sequence
+// — and one bitonic merge restores the order.  ~(log2 W (log2 W + 1) / 2 + log2 W + 1) exchange steps whatever the number of candidates;
+// the same list results (the W best keys are the W best keys however they got there).
+#define KNN_BULK_MIN 12
+template <int W>
+__device__ __forceinline__ void bulkMerge(unsigned long long& key, int& pos, unsigned long long ck, int cp, unsigned gmask, int l) {
+#pragma unroll
+  for (int size = 2; size <= W; size <<= 1)
+#pragma unroll
+    for (int j = size >> 1; j > 0; j >>= 1) bitonicStep<W>(ck, cp, j, (l & size) == 0 || size == W, gmask, l);
+  const unsigned long long rk = __shfl_sync(gmask, ck, W - 1 - l, W);
+  const int rp = __shfl_sync(gmask, cp, W - 1 - l, W);
+  if (rk < key) { key = rk; pos = rp; }
+#pragma unroll
+  for (int j = W >> 1; j > 0; j >>= 1) bitonicStep<W>(key, pos, j, true, gmask, l);
+}
+
 template <int W, bool SELFCHK, bool TWO>
 __device__ __forceinline__ void scanList(const float4* __restrict__ pts, uint32_t s, uint32_t e, const float3 q, int selfId, KnnList<W, TWO>& L,
                                          unsigned& visits) {
@@ -615,8 +641,14 @@ __device__ __forceinline__ void scanList(const float4* __restrict__ pts, uint32_
     const bool ok = (j < e) && !(SELFCHK && id == selfId);
     const unsigned long long key = packKey(dist2_rn(q.x, q.y, q.z, p.x, p.y, p.z), id);
     visits += ok ? 1u : 0u;
-    unsigned m = __ballot_sync(L.gmask, ok && key < L.kth);
+    const bool accept = ok && key < L.kth;
+    unsigned m = __ballot_sync(L.gmask, accept);
     if (W < 32) m = (m >> gbase) & ((1u << (W & 31)) - 1u);
+    if (!TWO && W == 32 && __popc(m) >= KNN_BULK_MIN) {   // uniform over the group
+      bulkMerge<W>(L.key, L.pos, accept ? key : ~0ull, (int)j, L.gmask, L.l);
+      L.kth = __shfl_sync(L.gmask, L.key, L.kLane, W);
+      m = 0;
+    }
     while (m) {
       const int b = __ffs(m) - 1;
       m &= m - 1u;
@@ -629,7 +661,7 @@ __device__ __forceinline__ void scanList(const float4* __restrict__ pts, uint32_
 }
 
 template <int W, bool SELFCHK, bool TWO>
-__global__ void __launch_bounds__(256) knnListKernel(const float4* __restrict__ pts, const uint32_t* __restrict__ cellStart, const GridDesc* __restrict__ gp,
+__global__ void __launch_bounds__(256, 4) knnListKernel(const float4* __restrict__ pts, const uint32_t* __restrict__ cellStart, const GridDesc* __restrict__ gp,
                                                      const float4* __restrict__ queries, int64_t n, int hasT, Rigid12 T, int k, float maxd2,
                                                      int* __restrict__ outIds, float* __restrict__ outD2, int* __restrict__ outPos,
                                                      unsigned long long* __restrict__ visitCounter) {

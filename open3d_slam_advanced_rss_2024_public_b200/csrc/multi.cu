@@ -6,8 +6,9 @@
 // (lanes in flight, csrc/icp.cu) driven by its own host thread, and ONE ncclAllGather of fixed-size records over NVLink leaves every
 // device — and the caller — with every pair's result.  There is no other collective and no data-path exchange.
 //
-// NCCL is resolved at run time (dlopen of libnccl.so.2): libb200reg.so carries no link-time dependency on it, a process that
-// already holds an NCCL (e.g. one that imported torch) shares that copy, and single-GPU users never load it.
+// NCCL is resolved at run time (dlopen of libnccl.so.2, or the path in env B200REG_NCCL_LIB): libb200reg.so carries no link-time
+// dependency on it, a process that already holds an NCCL (e.g. one that imported torch) shares that copy, and single-GPU users never
+// load it.
 #include <dlfcn.h>
 #include <nccl.h>
 
@@ -34,11 +35,15 @@ struct NcclApi {
 NcclApi& nccl() {
   static NcclApi api;
   if (api.lib) return api;
+  // order: the library the user names (env B200REG_NCCL_LIB), an NCCL the process already holds (RTLD_NOLOAD), the system's.  A process
+  // that will load a NEWER NCCL under the same soname later (e.g. `import torch` after this call) should load it first or name it here:
+  // the dynamic loader keeps one libnccl.so.2 per process.
   const char* names[] = {"libnccl.so.2", "libnccl.so"};
-  for (const char* nm : names) {
-    api.lib = dlopen(nm, RTLD_NOW | RTLD_GLOBAL);
-    if (api.lib) break;
-  }
+  if (const char* user = getenv("B200REG_NCCL_LIB")) api.lib = dlopen(user, RTLD_NOW | RTLD_GLOBAL);
+  for (const char* nm : names)
+    if (!api.lib) api.lib = dlopen(nm, RTLD_NOW | RTLD_NOLOAD | RTLD_GLOBAL);
+  for (const char* nm : names)
+    if (!api.lib) api.lib = dlopen(nm, RTLD_NOW | RTLD_GLOBAL);
   if (!api.lib) return api;
 #define LOAD(field, sym) api.field = reinterpret_cast<decltype(api.field)>(dlsym(api.lib, sym))
   LOAD(GetErrorString, "ncclGetErrorString");

@@ -327,6 +327,7 @@ def test_multi_gpu_host_matches_single_device_batch(ctx, oracle):
     """b200reg_multi (one process, one host thread + batch per visible GPU, pair i -> device i mod G, ONE ncclAllGather of the
     96-byte records): T / status come out of the gathered block and equal the single-device batch bit for bit.  On a 1-GPU box
     G = 1 (the communicator has one rank); the 2/4/8-GPU runs are profiles/r2/config4_multi_*.json."""
+    import torch  # noqa: F401  (its bundled NCCL must be the process's libnccl.so.2: b200reg_multi dlopen()s whatever is loaded, else the system's older one)
     from open3d_slam_advanced_rss_2024_public_b200 import capi
     kw = dict(knn=1, max_dist=1.0, trim_ratio=0.8, max_iter=40)
     P = _pairs(oracle, 5, 4800)
