@@ -18,8 +18,25 @@ ctx = capi.Context(0)
 icp = capi.ICP(ctx, knn=1, max_dist=1.0, trim_ratio=0.8, max_iter=40, min_diff_rot=1e-3, min_diff_trans=1e-2, smooth_length=3,
               cell=float(os.environ.get("PROF_CELL", 0.0)))
 icp.set_reference(ctx.upload(f4(c["map_xyz"]), c["map_nrm"].astype(np.float32)))
-scan = ctx.upload(f4(c["scan"]))
 Ti = c["T_init"].astype(np.float32)
+pts = c["scan"]
+if os.environ.get("PROF_SORT"):   # experiment: queries in the index's cell order (x fastest) under T_init instead of sensor order
+    cell = float(os.environ.get("PROF_SORT_CELL", 0.208))
+    w = (pts.astype(np.float64) @ Ti[:3, :3].T.astype(np.float64) + Ti[:3, 3]) / cell
+    ijk = np.floor(w).astype(np.int64)
+    ijk -= ijk.min(0)
+    mode = os.environ["PROF_SORT"]
+    if mode == "morton":
+        def spread(v):
+            r = np.zeros_like(v)
+            for b in range(12):
+                r |= ((v >> b) & 1) << (3 * b)
+            return r
+        key = spread(ijk[:, 0]) | (spread(ijk[:, 1]) << 1) | (spread(ijk[:, 2]) << 2)
+    else:
+        key = ijk[:, 0] + (ijk[:, 1] << 14) + (ijk[:, 2] << 28)
+    pts = pts[np.argsort(key, kind="stable")]
+scan = ctx.upload(f4(pts))
 for _ in range(3):
     icp.register(scan, Ti)
 ctx.set_trace(True)
