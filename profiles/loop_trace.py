@@ -26,7 +26,15 @@ if os.environ.get("PROF_SORT"):   # experiment: queries in the index's cell orde
     ijk = np.floor(w).astype(np.int64)
     ijk -= ijk.min(0)
     mode = os.environ["PROF_SORT"]
-    if mode == "morton":
+    if mode.startswith("stride"):   # chunks of 8 consecutive queries dealt out in a strided order: runs of far queries are spread over the launch
+        ch = int(os.environ.get("PROF_CHUNK", 8))
+        nchunk = pts.shape[0] // ch
+        order = (np.arange(nchunk, dtype=np.int64) * 40503) % nchunk
+        assert len(np.unique(order)) == nchunk
+        key = np.empty(pts.shape[0], dtype=np.int64)
+        key[:nchunk * ch] = np.repeat(np.argsort(order), ch) * ch + np.tile(np.arange(ch), nchunk)
+        key[nchunk * ch:] = np.arange(nchunk * ch, pts.shape[0])
+    elif mode == "morton":
         def spread(v):
             r = np.zeros_like(v)
             for b in range(12):
