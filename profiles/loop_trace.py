@@ -26,7 +26,12 @@ if os.environ.get("PROF_SORT"):   # experiment: queries in the index's cell orde
     ijk = np.floor(w).astype(np.int64)
     ijk -= ijk.min(0)
     mode = os.environ["PROF_SORT"]
-    if mode.startswith("stride"):   # chunks of 8 consecutive queries dealt out in a strided order: runs of far queries are spread over the launch
+    if mode == "tile":   # the [128 beams][1024 azimuths] grid re-ordered into tiles of tb x ta rays (a warp's queries form a patch, not a line)
+        tb, ta = (int(v) for v in os.environ.get("PROF_TILE", "4x8").split("x"))
+        idx = np.arange(128 * 1024).reshape(128, 1024)
+        key = np.empty(128 * 1024, dtype=np.int64)
+        key[idx.reshape(128 // tb, tb, 1024 // ta, ta).transpose(0, 2, 1, 3).reshape(-1)] = np.arange(128 * 1024)
+    elif mode.startswith("stride"):   # chunks of 8 consecutive queries dealt out in a strided order: runs of far queries are spread over the launch
         ch = int(os.environ.get("PROF_CHUNK", 8))
         nchunk = pts.shape[0] // ch
         order = (np.arange(nchunk, dtype=np.int64) * 40503) % nchunk
