@@ -67,9 +67,9 @@ int enqueueStep(b200reg_ctx* ctx, const b200reg_index* ix, const float4* reading
   P.cosAngle = cosf(maxAngle);
   P.force2D = force2D;
   P.w = nullptr;
-  const int rblocks = (int)fmax(1.0, fmin((double)divUp(total, 512), (double)(2 * ctx->sm_count)));
+  const int rblocks = (int)fmax(1.0, fmin((double)divUp(total, 2 * RED_THREADS), (double)((512 / RED_THREADS) * ctx->sm_count)));
   TRY(ensureBuf(ctx, ctx->partials, sizeof(double) * NUM_MOM * (size_t)rblocks));
-  reduceKernel<<<rblocks, 256, 0, ctx->stream>>>(P, st, (double*)ctx->partials.p, &st->ticket[3], resultPtr(ctx), nullptr, nullptr);
+  reduceKernel<<<rblocks, RED_THREADS, 0, ctx->stream>>>(P, st, (double*)ctx->partials.p, &st->ticket[3], resultPtr(ctx), nullptr, nullptr);
   LAUNCH_CHECK(ctx);
   HostStep* h = (HostStep*)ctx->pinned;
   CUDA_TRY(ctx, cudaMemcpyAsync(h->mom, resultPtr(ctx), sizeof(double) * NUM_MOM, cudaMemcpyDeviceToHost, ctx->stream));
@@ -667,7 +667,7 @@ int buildLoopGraph(b200reg_icp* icp) {
   // the graph launches the match kernel on the full resident grid; IcpDevParams::matchBlocks (icpEnqueue) says how many of its blocks work
   int perSm = KNN1_LOOP_MINB;
   if (const char* e = getenv("B200REG_KNN_GRID_PER_SM")) { const int v = atoi(e); if (v >= 1 && v <= KNN1_LOOP_MINB) perSm = v; }   // A/B
-  const int knnBlocks = perSm * ctx->sm_count /* the resident grid of knn1LoopKernel: its warps pull work from a counter */, redBlocks = 2 * ctx->sm_count;
+  const int knnBlocks = perSm * ctx->sm_count /* the resident grid of knn1LoopKernel: its warps pull work from a counter */, redBlocks = (512 / RED_THREADS) * ctx->sm_count;
   if (ensureBuf(ctx, ctx->partials, sizeof(double) * NUM_MOM * (size_t)redBlocks) != B200REG_OK) return -1;
   {
     cudaGraphConditionalHandle handle;
@@ -695,7 +695,7 @@ int buildLoopGraph(b200reg_icp* icp) {
     ctx->launches = l0;
     ReduceParams RP;
     memset(&RP, 0, sizeof(RP));
-    reduceKernel<<<redBlocks, 256, 0, ctx->stream>>>(RP, st, nullptr, &st->ticket[3], resultPtr(ctx), icp->dP, icp->dS);
+    reduceKernel<<<redBlocks, RED_THREADS, 0, ctx->stream>>>(RP, st, nullptr, &st->ticket[3], resultPtr(ctx), icp->dP, icp->dS);
     icpTailKernel<<<1, 32, 0, ctx->stream>>>(icp->dP, icp->dS, resultPtr(ctx), st, (unsigned long long*)icp->dBlock, handle);
     nodes += 2;
     GRAPH_TRY(cudaGetLastError());
@@ -1468,9 +1468,9 @@ int32_t b200reg_point_to_plane(b200reg_ctx* ctx, const b200reg_cloud* reading, c
   P.force2D = force2D;
   P.w = (const float*)ctx->misc.p;
   SelState* st = selState(ctx);
-  const int rblocks = (int)fmax(1.0, fmin((double)divUp(total, 512), (double)(2 * ctx->sm_count)));
+  const int rblocks = (int)fmax(1.0, fmin((double)divUp(total, 2 * RED_THREADS), (double)((512 / RED_THREADS) * ctx->sm_count)));
   TRY(ensureBuf(ctx, ctx->partials, sizeof(double) * NUM_MOM * (size_t)rblocks));
-  reduceKernel<<<rblocks, 256, 0, ctx->stream>>>(P, st, (double*)ctx->partials.p, &st->ticket[3], resultPtr(ctx), nullptr, nullptr);
+  reduceKernel<<<rblocks, RED_THREADS, 0, ctx->stream>>>(P, st, (double*)ctx->partials.p, &st->ticket[3], resultPtr(ctx), nullptr, nullptr);
   LAUNCH_CHECK(ctx);
   HostStep* h = (HostStep*)ctx->pinned;
   CUDA_TRY(ctx, cudaMemcpyAsync(h->mom, resultPtr(ctx), sizeof(double) * NUM_MOM, cudaMemcpyDeviceToHost, ctx->stream));

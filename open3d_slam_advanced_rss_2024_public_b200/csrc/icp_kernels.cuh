@@ -23,6 +23,11 @@ struct SelState {
 #define DSTATE_RESULT_OFF (256 + 8192)   /* NUM_MOM doubles */
 
 #define NUM_MOM 36
+// threads per block of reduceKernel.  128-thread blocks (16 K registers: the footprint of one block of the match kernel, so a lane's
+// reduction could start in the first slot another lane frees) were measured: 3635 vs 3730 registrations/s on the lanes, 1975 vs 2200 alone
+#ifndef RED_THREADS
+#define RED_THREADS 256
+#endif
 // moment slots
 enum {
   M_CNT = 0, M_VALID = 1,
@@ -156,7 +161,7 @@ __device__ __forceinline__ void pickBin2(unsigned c0, unsigned c1, unsigned rank
   __syncthreads();
 }
 
-__global__ void __launch_bounds__(SELF_THREADS, 1) selectFusedKernel(const IcpDevParams* __restrict__ DP, SelState* st) {
+__global__ void __launch_bounds__(SELF_THREADS, 2) selectFusedKernel(const IcpDevParams* __restrict__ DP, SelState* st) {
   __shared__ unsigned hist[2048];
   __shared__ unsigned warpSums[40];
   __shared__ unsigned bcast[2];
@@ -310,7 +315,7 @@ __device__ __forceinline__ bool pairKept(const ReduceParams& P, int64_t o, float
 // un-centred; the matched-mean centring of PointToPlane.cpp:263-268 is applied algebraically afterwards.
 // Reduction: 36 fp64 moments per thread -> warp shuffle -> block tree -> per-block partial -> the last block adds the
 // partials in a fixed order (deterministic for a given grid).
-__global__ void __launch_bounds__(256, 2) reduceKernel(ReduceParams P, const SelState* __restrict__ st, double* __restrict__ partials,
+__global__ void __launch_bounds__(RED_THREADS, 512 / RED_THREADS) reduceKernel(ReduceParams P, const SelState* __restrict__ st, double* __restrict__ partials,
                                                     unsigned* ticket, double* __restrict__ result, const IcpDevParams* __restrict__ DP,
                                                     const IcpDevState* __restrict__ DS) {
   if (DP) {   // graph-driven loop: arguments from the device-resident blocks, T_iter from the loop state
@@ -367,7 +372,7 @@ __global__ void __launch_bounds__(256, 2) reduceKernel(ReduceParams P, const Sel
     }
   }
   // warp shuffle -> block tree (shared) -> per-block partial
-  __shared__ double sm[8][NUM_MOM];
+  __shared__ double sm[RED_THREADS / 32][NUM_MOM];
   __shared__ bool last;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   {
@@ -385,7 +390,7 @@ __global__ void __launch_bounds__(256, 2) reduceKernel(ReduceParams P, const Sel
   __syncthreads();
   if (threadIdx.x < NUM_MOM) {
     double v = 0.0;
-    for (int w = 0; w < 8; ++w) v += sm[w][threadIdx.x];
+    for (int w = 0; w < RED_THREADS / 32; ++w) v += sm[w][threadIdx.x];
     partials[(size_t)blockIdx.x * NUM_MOM + threadIdx.x] = v;
   }
   __threadfence();
@@ -394,7 +399,7 @@ __global__ void __launch_bounds__(256, 2) reduceKernel(ReduceParams P, const Sel
   if (!last) return;
   __threadfence();
   // the last block: 7 slices x 36 moments; slice s adds partials s, s+7, ... in order, then the slices are added in order
-  constexpr int SL = 7;
+  constexpr int SL = RED_THREADS / NUM_MOM;   // slices of NUM_MOM threads
   const int j = threadIdx.x % NUM_MOM, sl = threadIdx.x / NUM_MOM;
   if (sl < SL) {
     double v = 0.0;
