@@ -1187,6 +1187,7 @@ int32_t b200reg_batch_create(b200reg_ctx* ctx, const b200reg_icp_config* cfg, in
     if (code != B200REG_OK) { setErr(ctx, code, "batch_create: lane context"); break; }
     L.ctx->profile = 0; L.ctx->hostLoop = 0;   // lanes always run the graph loop
     L.ctx->loopGridPerSm = BATCH_LOOP_GRID_PER_SM;
+    if (const char* e = getenv("B200REG_BATCH_GRID_PER_SM")) { const int v = atoi(e); if (v >= 1 && v <= KNN1_LOOP_MINB) L.ctx->loopGridPerSm = v; }   // A/B
     code = b200reg_icp_create(L.ctx, cfg, &L.icp);
     if (code != B200REG_OK) { setErr(ctx, code, "batch_create: %s", L.ctx->err); break; }
     L.icp->graphState = (buildLoopGraph(L.icp) == 0) ? 1 : -1;
