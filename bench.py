@@ -119,7 +119,7 @@ def gather_floats(torch, dist, local_rank, vals):
 
 def spread(a):
     a = np.asarray(a, dtype=np.float64)
-    return {"min": float(a.min()), "median": float(np.median(a)), "max": float(a.max())}
+    return {"min": float(a.min()), "median": float(np.median(a)), "p95": float(np.percentile(a, 95)), "max": float(a.max())}
 
 
 # =====================================================================================================================
