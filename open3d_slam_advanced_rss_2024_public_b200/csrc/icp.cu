@@ -667,7 +667,7 @@ int buildLoopGraph(b200reg_icp* icp) {
   // the graph launches the match kernel on the full resident grid; IcpDevParams::matchBlocks (icpEnqueue) says how many of its blocks work
   int perSm = KNN1_LOOP_MINB;
   if (const char* e = getenv("B200REG_KNN_GRID_PER_SM")) { const int v = atoi(e); if (v >= 1 && v <= KNN1_LOOP_MINB) perSm = v; }   // A/B
-  const int knnBlocks = perSm * ctx->sm_count /* the resident grid of knn1LoopKernel: its warps pull work from a counter */, redBlocks = (512 / RED_THREADS) * ctx->sm_count;
+  const int knnBlocks = perSm * ctx->sm_count /* the resident grid of knn1LoopKernel: its warps pull work from a counter */, redBlocks = ((getenv("B200REG_RED_GRID_PER_SM") && atoi(getenv("B200REG_RED_GRID_PER_SM")) == 2) ? 2 : 1) * ctx->sm_count;   /* one 256-thread block per SM: fewer 32 K-register blocks to place between the lanes' match kernels (3667 -> 3805 registrations/s; env = 2: the old grid, A/B) */
   if (ensureBuf(ctx, ctx->partials, sizeof(double) * NUM_MOM * (size_t)redBlocks) != B200REG_OK) return -1;
   {
     cudaGraphConditionalHandle handle;
