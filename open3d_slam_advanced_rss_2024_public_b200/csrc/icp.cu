@@ -688,7 +688,9 @@ int buildLoopGraph(b200reg_icp* icp) {
     ++nodes;
     const uint64_t l0 = ctx->launches;
     if (useTrim && !ctx->select3) {
-      selectFusedKernel<<<ctx->sm_count, SELF_THREADS, 0, ctx->stream>>>(icp->dP, st);
+      int selBlocks = ctx->sm_count;
+      if (const char* e = getenv("B200REG_SEL_BLOCKS")) { const int v = atoi(e); if (v >= 1 && v <= 4 * ctx->sm_count) selBlocks = v; }   // A/B
+      selectFusedKernel<<<selBlocks, SELF_THREADS, 0, ctx->stream>>>(icp->dP, st);
       LAUNCH_CHECK(ctx);
     } else if (useTrim && launchSelect(ctx, nullptr, 0, 0.f, icp->dP) != B200REG_OK) { why = "select launch"; code = cudaErrorUnknown; goto fail; }
     nodes += (int)(ctx->launches - l0);
