@@ -560,3 +560,98 @@ def test_pointcloud2_reference_test_layouts_oracle(oracle):
         assert np.array_equal(f4.view(np.uint32), feat.view(np.uint32)), case[0]
         assert (n3 is None) == (nrm is None) and (nrm is None or np.array_equal(n3, nrm)), case[0]
         assert np.array_equal(x64, feat[:, :3].astype(np.float64))
+
+
+def test_residual_error_equals_numpy_restatement(oracle):
+    """PointToPlaneErrorMinimizer::computeResidualError (PointToPlane.cpp:372-407) over the ErrorElements pairs (finite distance, non-zero
+    weight, ErrorMinimizer.cpp:103-108): sum of w ((p - q) . n)^2, z dropped under force2D — against a direct numpy evaluation."""
+    rng = np.random.default_rng(5)
+    n, m, k = 400, 300, 3
+    q = np.concatenate([rng.normal(size=(n, 3)), np.ones((n, 1))], axis=1).astype(np.float32)
+    ref = np.concatenate([rng.normal(size=(m, 3)), np.ones((m, 1))], axis=1).astype(np.float32)
+    nrm = rng.normal(size=(m, 3))
+    nrm = (nrm / np.linalg.norm(nrm, axis=1, keepdims=True)).astype(np.float32)
+    ids = rng.integers(0, m, size=(n, k)).astype(np.int32)
+    d2 = rng.uniform(0, 1, size=(n, k)).astype(np.float32)
+    miss = rng.random((n, k)) < 0.2
+    d2[miss] = np.inf
+    ids[miss] = -1
+    w = rng.choice(np.array([0.0, 0.5, 1.0], np.float32), size=(n, k))
+    for force2D in (False, True):
+        dims = 2 if force2D else 3
+        keep = np.isfinite(d2) & (w != 0)
+        p = np.repeat(q[:, None, :3].astype(np.float64), k, axis=1)[keep]
+        r = ref[ids[keep], :3].astype(np.float64)
+        nn = nrm[ids[keep]].astype(np.float64)
+        want = float((w[keep].astype(np.float64) * ((p - r)[:, :dims] * nn[:, :dims]).sum(1) ** 2).sum())
+        got = oracle.point_to_plane_residual(q, ref, nrm, ids, d2, w, force2D=force2D)
+        assert abs(got - want) <= 1e-12 * max(1.0, want), (force2D, got, want)
+        got32 = oracle.point_to_plane_residual(q, ref, nrm, ids, d2, w, force2D=force2D, precision=oracle.ORC_REF32)
+        assert abs(got32 - want) <= 1e-4 * max(1.0, want)          # the reference's own float accumulation
+
+
+def test_smooth_normals_equals_the_sequential_sweep(oracle):
+    """smoothNormals (SurfaceNormal.cpp:299-323): an IN-PLACE sweep in index order — point i averages the (already smoothed, for j < i)
+    normals of its matched neighbours, each flipped onto its own current normal — restated literally in float32 Python."""
+    rng = np.random.default_rng(9)
+    n, knn, md = 250, 6, 0.9
+    pts = np.concatenate([rng.uniform(-1, 1, size=(n, 2)), 0.05 * rng.normal(size=(n, 1)), np.ones((n, 1))], axis=1).astype(np.float32)
+    nrm = rng.normal(size=(n, 3)) * np.array([0.3, 0.3, 1.0])
+    nrm = (nrm / np.linalg.norm(nrm, axis=1, keepdims=True)).astype(np.float32)
+    ids, d2, _ = oracle.KdTree(pts).knn(pts, k=knn, max_dist=md)
+    want = nrm.copy()
+    for i in range(n):
+        cur = want[i].copy()
+        mean = np.zeros(3, np.float32)
+        cnt = 0
+        for j in range(knn):
+            if d2[i, j] == np.inf:
+                continue
+            v = want[ids[i, j]]
+            dot = np.float32(np.float32(np.float32(cur[0] * v[0]) + np.float32(cur[1] * v[1])) + np.float32(cur[2] * v[2]))
+            mean = (mean + v if dot > 0 else mean - v).astype(np.float32)
+            cnt += 1
+        want[i] = mean / np.float32(cnt)
+    got = oracle.smooth_normals(pts, nrm, knn, max_dist=md)
+    assert np.abs(got - want).max() <= 2e-7, np.abs(got - want).max()
+    assert np.abs(got - nrm).max() > 1e-2                              # and it did something
+
+
+def test_estimate_normals_f64_equals_numpy_pca(oracle):
+    """Open3D EstimateNormals(KDTreeSearchParamHybrid(radius, knn)) + OrientNormalsTowardsCameraLocation in fp64: covariance of the (at most
+    knn, within radius) nearest neighbours incl. the point itself, eigenvector of the smallest eigenvalue, flipped towards the origin —
+    against numpy (brute-force neighbours, eigh); the candidate-list mode used above 20 000 points gives the same normals."""
+    rng = np.random.default_rng(13)
+    n, knn, radius = 1500, 12, 0.35
+    uv = rng.uniform(-1, 1, size=(n, 2))
+    xyz = np.stack([uv[:, 0], uv[:, 1], 0.3 * np.sin(2 * uv[:, 0]) + 0.002 * rng.normal(size=n)], axis=1) + np.array([0.0, 0.0, 3.0])
+    origin = np.zeros(3)
+    got, deg = oracle.estimate_normals_f64(xyz, knn, radius, origin=origin, exact=True)
+    got_c, _ = oracle.estimate_normals_f64(xyz, knn, radius, origin=origin, exact=False)
+    D = ((xyz[:, None, :] - xyz[None, :, :]) ** 2).sum(-1)
+    worst = 0.0
+    for i in range(0, n, 7):
+        order = np.argsort(D[i], kind="stable")[:knn]
+        nb = order[D[i, order] <= radius * radius]
+        if nb.size < 3:
+            continue
+        P = xyz[nb]
+        C = np.cov(P.T, bias=True)
+        wv, V = np.linalg.eigh(C)
+        v = V[:, 0]
+        if np.dot(v, origin - xyz[i]) < 0:
+            v = -v
+        worst = max(worst, float(np.linalg.norm(got[i] - v)), float(np.linalg.norm(got_c[i] - v)))
+    assert deg == 0 and worst < 1e-7, (deg, worst)
+
+
+@pytest.mark.parametrize("k", [33, 48, 64])
+def test_kdtree_large_k_vs_brute(oracle, k):
+    """k above 32 (served on the GPU by the two-entries-per-lane list kernel): the oracle's k-d tree against its brute-force scan."""
+    rng = np.random.default_rng(k)
+    ref = np.concatenate([rng.uniform(-2, 2, size=(3000, 3)), np.ones((3000, 1))], axis=1).astype(np.float32)
+    q = np.concatenate([rng.uniform(-2.5, 2.5, size=(200, 3)), np.ones((200, 1))], axis=1).astype(np.float32)
+    for md in (np.inf, 0.6):
+        ids_t, d2_t, _ = oracle.KdTree(ref).knn(q, k=k, max_dist=md)
+        ids_b, d2_b = oracle.knn_brute(ref, q, k=k, max_dist=md)
+        assert np.array_equal(ids_t, ids_b) and np.array_equal(d2_t.view(np.uint32), d2_b.view(np.uint32))
