@@ -655,3 +655,29 @@ def test_kdtree_large_k_vs_brute(oracle, k):
         ids_t, d2_t, _ = oracle.KdTree(ref).knn(q, k=k, max_dist=md)
         ids_b, d2_b = oracle.knn_brute(ref, q, k=k, max_dist=md)
         assert np.array_equal(ids_t, ids_b) and np.array_equal(d2_t.view(np.uint32), d2_b.view(np.uint32))
+
+
+def test_surface_normal_extra_descriptors_vs_numpy(oracle):
+    """The descriptors added in round 2 (SurfaceNormal.cpp:256-259,294-296; utils.h:91-103): eigVectors = the eigenvector matrix serialised
+    ROW-major (row k = k-th components of the three eigenvectors, columns in ascending-eigenvalue order), meanDists = |p - mean(neighbours)|,
+    matchedIds = the neighbour ids as floats — against numpy on the neighbours the oracle itself reports."""
+    rng = np.random.default_rng(21)
+    n, knn = 800, 9
+    pts = np.concatenate([rng.uniform(-1, 1, size=(n, 2)), 0.1 * rng.normal(size=(n, 1))], axis=1).astype(np.float32)
+    feat = oracle.feat4(pts)
+    o = oracle.surface_normals(feat, knn, nthreads=4, keep=("normals", "eig_values", "eig_vectors", "matched_ids", "mean_dists"))
+    ids, d2, _ = oracle.KdTree(feat).knn(feat, k=knn)
+    assert np.array_equal(o["matched_ids"], ids.astype(np.float32))
+    worst_md = worst_ev = worst_vec = 0.0
+    for i in range(0, n, 5):
+        P = pts[ids[i]].astype(np.float64)
+        mean = P.mean(0)
+        worst_md = max(worst_md, abs(float(o["mean_dists"][i]) - float(np.linalg.norm(pts[i].astype(np.float64) - mean))))
+        C = (P - mean).T @ (P - mean) / P.shape[0]          # SurfaceNormal.cpp:201-204: NN NN^T / realKnn
+        wv, V = np.linalg.eigh(C)
+        E = o["eig_vectors"][i].astype(np.float64).reshape(3, 3)      # row-major: E[k, c] = component k of eigenvector c
+        worst_ev = max(worst_ev, float(np.abs(o["eig_values"][i] - wv).max() / max(wv.max(), 1e-12)))
+        for c in range(3):
+            worst_vec = max(worst_vec, 1.0 - abs(float(E[:, c] @ V[:, c])))
+        assert 1.0 - abs(float(o["normals"][i].astype(np.float64) @ V[:, 0])) < 1e-5     # the normal is the first column
+    assert worst_md < 1e-6 and worst_ev < 1e-5 and worst_vec < 1e-4, (worst_md, worst_ev, worst_vec)
