@@ -681,3 +681,24 @@ def test_surface_normal_extra_descriptors_vs_numpy(oracle):
             worst_vec = max(worst_vec, 1.0 - abs(float(E[:, c] @ V[:, c])))
         assert 1.0 - abs(float(o["normals"][i].astype(np.float64) @ V[:, 0])) < 1e-5     # the normal is the first column
     assert worst_md < 1e-6 and worst_ev < 1e-5 and worst_vec < 1e-4, (worst_md, worst_ev, worst_vec)
+
+
+def test_counter_checker_semantics(oracle, golden):
+    """CounterTransformationChecker (TransformationCheckersImpl.cpp:58-77): the counter is compared with maxIterationCount AFTER the
+    increment, so 0 and 1 both stop after one iteration and 2 after two, with maxNumIterationsReached set; a negative count means the
+    checker is not in the chain and the Differential checker alone ends the loop."""
+    car = golden["car"]
+    ref, rn, q = oracle.feat4(car["ref_xyz"]), car["ref_normals"].astype(np.float32), oracle.feat4(car["data_xyz"])
+    Ti = np.eye(4, dtype=np.float32)
+    for mi, want in ((0, 1), (1, 1), (2, 2), (3, 3)):
+        cfg = oracle.icp_config(precision=oracle.ORC_MIXED, nthreads=2, knn=1, max_dist=np.inf, trim_ratio=0.8, max_iter=mi, smooth_length=-1)
+        code, T, st = oracle.icp(cfg, ref, rn, q, None, Ti)
+        assert code == 0 and st.iterations == want and st.max_iterations_reached == 1, (mi, st.iterations)
+    cfg = oracle.icp_config(precision=oracle.ORC_MIXED, nthreads=2, knn=1, max_dist=np.inf, trim_ratio=0.8, max_iter=-1, smooth_length=3,
+                            min_diff_rot=1e-3, min_diff_trans=1e-2)
+    code, T, st = oracle.icp(cfg, ref, rn, q, None, Ti)
+    assert code == 0 and st.max_iterations_reached == 0 and 3 < st.iterations < 200
+    cfg40 = oracle.icp_config(precision=oracle.ORC_MIXED, nthreads=2, knn=1, max_dist=np.inf, trim_ratio=0.8, max_iter=1000, smooth_length=3,
+                              min_diff_rot=1e-3, min_diff_trans=1e-2)
+    code2, T2, st2 = oracle.icp(cfg40, ref, rn, q, None, Ti)
+    assert code2 == 0 and st2.iterations == st.iterations and np.array_equal(T, T2)      # an unreached Counter changes nothing
